@@ -1,0 +1,236 @@
+"""ctypes access to oracle/_ref/libkgref.so (the unmodified reference, see oracle/Makefile, oracle/ref_driver.cpp).
+TEST INFRASTRUCTURE ONLY -- may be imported from tests/, bench.py's cpu_baseline / --impl reference leg and
+oracle/make_golden.py, never from the product package."""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+BOLTZMANN = 1.38064852e-23
+AVOGADRO = 8.31446261815324 / BOLTZMANN
+
+dp = C.POINTER(C.c_double)
+ip = C.POINTER(C.c_int)
+
+
+def available():
+    return os.path.exists(os.path.join(_HERE, "_ref", "libkgref.so"))
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        L = C.CDLL(os.path.join(_HERE, "_ref", "libkgref.so"))
+        L.kgref_mie_create.restype = C.c_void_p
+        L.kgref_mie_create.argtypes = [C.c_int, dp, dp, dp, dp, dp, C.c_int, C.c_int]
+        L.kgref_last_error.restype = C.c_char_p
+        L.kgref_last_error.argtypes = [C.c_void_p]
+        for n in ("kgref_destroy", "kgref_clear_cache"):
+            getattr(L, n).argtypes = [C.c_void_p]
+        L.kgref_set_omega_correlation_active.argtypes = [C.c_void_p, C.c_int]
+        L.kgref_set_tl_model.argtypes = [C.c_void_p, C.c_int]
+        L.kgref_set_eos_tables_nc.argtypes = [C.c_void_p, C.c_int, dp, dp, C.c_double, C.c_double, dp]
+        for n in ("kgref_potential", "kgref_potential_r"):
+            getattr(L, n).restype = C.c_double
+            getattr(L, n).argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double]
+        for n in ("kgref_chi", "kgref_theta", "kgref_get_R"):
+            getattr(L, n).restype = C.c_double
+            getattr(L, n).argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double]
+        for n in ("kgref_chi_batch", "kgref_get_R_batch"):
+            getattr(L, n).argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_int, dp, dp, dp]
+        L.kgref_w_integrand.restype = C.c_double
+        L.kgref_w_integrand.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int, C.c_int]
+        for n in ("kgref_omega", "kgref_omega_model"):
+            getattr(L, n).argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, dp]
+        L.kgref_w_integral_tester.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int,
+                                              C.c_double, C.c_double, C.c_double, C.c_double, C.c_int, C.c_int, C.c_double, dp]
+        L.kgref_w_integral_trace.argtypes = L.kgref_w_integral_tester.argtypes + [dp, C.c_int, ip]
+        L.kgref_integrate2d_table.restype = C.c_double
+        L.kgref_integrate2d_table.argtypes = [dp, C.c_int, C.c_int] + [C.c_double] * 6 + [C.c_int, C.c_int, C.c_double, ip]
+        L.kgref_tanh_sinh_test.restype = C.c_double
+        L.kgref_tanh_sinh_test.argtypes = [C.c_int, C.c_double, C.c_double, C.c_double]
+        for n in ("kgref_mtl", "kgref_etl", "kgref_rdf"):
+            getattr(L, n).argtypes = [C.c_void_p, C.c_double, C.c_double, dp, dp]
+        L.kgref_bh_diameters.argtypes = [C.c_void_p, C.c_double, dp]
+        L.kgref_K_factors.argtypes = [C.c_void_p, C.c_double, C.c_double, dp, dp, dp]
+        L.kgref_matrix_vector.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, dp, C.c_int, dp, dp, ip]
+        for n in ("kgref_viscosity", "kgref_thermal_conductivity", "kgref_thermal_conductivity_contribs"):
+            getattr(L, n).argtypes = [C.c_void_p, C.c_double, C.c_double, dp, C.c_int, C.c_int, dp]
+        L.kgref_interdiffusion.argtypes = [C.c_void_p, C.c_double, C.c_double, dp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                           C.c_int, dp, ip, ip]
+        L.kgref_thermal_diffusion_coeff.argtypes = [C.c_void_p, C.c_double, C.c_double, dp, C.c_int, C.c_int, C.c_int, C.c_int,
+                                                    C.c_int, dp, ip]
+        _LIB = L
+    return _LIB
+
+
+def _p(a):
+    return a.ctypes.data_as(dp)
+
+
+def lattice_regime(T):
+    """The T-dependent lattice switch of Spherical::w_integral (cpp/Spherical.cpp:60-84)."""
+    end = (8.0, 5.0)
+    dg, db, rlg, rlb = 0.5, 0.03125, 4, 16
+    if T < 70:
+        dg /= 4.0
+        end = (6.0, 3.5)
+    if T < 50:
+        rlb //= 2
+    if T < 35:
+        dg /= 2
+        rlg *= 2
+        db /= 2
+        end = (3.5, 3.5)
+    if T < 20:
+        dg /= 2
+        rlg *= 2
+        db /= 2
+        rlb *= 2
+    return end[0], end[1], dg, db, rlg, rlb, 1e-5
+
+
+class RefMie:
+    """The reference's MieKinGas built through its vector constructor (cpp/MieKinGas.cpp:14-17), parameters mixed
+    the way pykingas/MieType.py:201-260 does (kij = lij = 0)."""
+
+    def __init__(self, Mw, sigma, eps_div_k, la, lr, is_idealgas=False):
+        single = len(Mw) == 1
+        if single:
+            Mw, sigma, eps_div_k, la, lr = [list(v) * 2 for v in (Mw, sigma, eps_div_k, la, lr)]
+        self.nc = len(Mw)
+        self.single = single
+        self.m = np.array(Mw, float) * 1e-3 / AVOGADRO
+        s = np.array(sigma, float)
+        e = np.array(eps_div_k, float) * BOLTZMANN
+        self.sigma = 0.5 * (s[:, None] + s[None, :])
+        self.eps = np.sqrt(e[None, :] * e[:, None])
+        la_, lr_ = np.array(la, float), np.array(lr, float)
+        self.la = 3 + np.sqrt((la_[:, None] - 3) * (la_[None, :] - 3))
+        self.lr = 3 + np.sqrt((lr_[:, None] - 3) * (lr_[None, :] - 3))
+        for a in ("sigma", "eps", "la", "lr"):
+            setattr(self, a, np.ascontiguousarray(getattr(self, a)))
+        self.L = lib()
+        self.h = self.L.kgref_mie_create(self.nc, _p(self.m), _p(self.sigma), _p(self.eps), _p(self.la), _p(self.lr),
+                                         int(is_idealgas), int(single))
+
+    def __del__(self):
+        try:
+            self.L.kgref_destroy(self.h)
+        except Exception:
+            pass
+
+    def _chk(self, rc):
+        if rc != 0:
+            raise RuntimeError(self.L.kgref_last_error(self.h).decode())
+
+    def set_omega_correlation_active(self, a):
+        self.L.kgref_set_omega_correlation_active(self.h, int(a))
+
+    def clear_cache(self):
+        self.L.kgref_clear_cache(self.h)
+
+    def chi(self, i, j, T, g, b):
+        g = np.ascontiguousarray(np.atleast_1d(g), float)
+        b = np.ascontiguousarray(np.atleast_1d(b), float)
+        out = np.empty_like(g)
+        self._chk(self.L.kgref_chi_batch(self.h, i, j, T, g.size, _p(g), _p(b), _p(out)))
+        return out
+
+    def get_R(self, i, j, T, g, b):
+        g = np.ascontiguousarray(np.atleast_1d(g), float)
+        b = np.ascontiguousarray(np.atleast_1d(b), float)
+        out = np.empty_like(g)
+        self._chk(self.L.kgref_get_R_batch(self.h, i, j, T, g.size, _p(g), _p(b), _p(out)))
+        return out
+
+    def omega(self, i, j, l, r, T, model=False):
+        out = C.c_double()
+        f = self.L.kgref_omega_model if model else self.L.kgref_omega
+        self._chk(f(self.h, i, j, l, r, T, C.byref(out)))
+        return out.value
+
+    def w_integral(self, i, j, T, l, r, regime=None):
+        out = C.c_double()
+        reg = regime or lattice_regime(T)
+        self._chk(self.L.kgref_w_integral_tester(self.h, i, j, T, l, r, *reg, C.byref(out)))
+        return out.value
+
+    def w_integral_trace(self, i, j, T, l, r, regime=None, max_pts=200000):
+        out = C.c_double()
+        n = C.c_int()
+        pts = np.zeros((max_pts, 3))
+        reg = regime or lattice_regime(T)
+        self._chk(self.L.kgref_w_integral_trace(self.h, i, j, T, l, r, *reg, C.byref(out), _p(pts), max_pts, C.byref(n)))
+        return out.value, pts[:n.value]
+
+    def _mat(self, f, rho, T, x):
+        x = np.ascontiguousarray(x, float)
+        out = np.empty((self.nc, self.nc))
+        self._chk(f(self.h, rho, T, _p(x), _p(out)))
+        return out
+
+    def mtl(self, rho, T, x):
+        return self._mat(self.L.kgref_mtl, rho, T, x)
+
+    def etl(self, rho, T, x):
+        return self._mat(self.L.kgref_etl, rho, T, x)
+
+    def rdf(self, rho, T, x):
+        return self._mat(self.L.kgref_rdf, rho, T, x)
+
+    def K_factors(self, rho, T, x):
+        x = np.ascontiguousarray(x, float)
+        K, Kp = np.empty(self.nc), np.empty(self.nc)
+        self._chk(self.L.kgref_K_factors(self.h, rho, T, _p(x), _p(K), _p(Kp)))
+        return K, Kp
+
+    def matrix_vector(self, which, rho, T, x, N):
+        x = np.ascontiguousarray(x, float)
+        dim = C.c_int()
+        self._chk(self.L.kgref_matrix_vector(self.h, which, rho, T, _p(x), N, None, None, C.byref(dim)))
+        d = dim.value
+        M, v = np.empty((d, d)), np.empty(d)
+        self._chk(self.L.kgref_matrix_vector(self.h, which, rho, T, _p(x), N, _p(M), _p(v), C.byref(dim)))
+        return M, v
+
+    def set_eos(self, dmudn=None, cp_id=None, p=0.0, vm=0.0, dvdn=None):
+        nc_eos = 1 if self.single else self.nc
+        a = [None if v is None else np.ascontiguousarray(v, float) for v in (dmudn, cp_id, dvdn)]
+        self._eos_keep = a
+        self.L.kgref_set_eos_tables_nc(self.h, nc_eos, None if a[0] is None else _p(a[0]), None if a[1] is None else _p(a[1]),
+                                       p, vm, None if a[2] is None else _p(a[2]))
+
+    def _scalar(self, f, T, Vm, x, N):
+        x = np.ascontiguousarray(x, float)
+        out = C.c_double()
+        self._chk(f(self.h, T, Vm, _p(x), x.size, N, C.byref(out)))
+        return out.value
+
+    def viscosity(self, T, Vm, x, N=2):
+        return self._scalar(self.L.kgref_viscosity, T, Vm, x, N)
+
+    def thermal_conductivity(self, T, Vm, x, N=2):
+        return self._scalar(self.L.kgref_thermal_conductivity, T, Vm, x, N)
+
+    def thermal_conductivity_contribs(self, T, Vm, x, N=2):
+        x = np.ascontiguousarray(x, float)
+        out = np.empty(3)
+        self._chk(self.L.kgref_thermal_conductivity_contribs(self.h, T, Vm, _p(x), x.size, N, _p(out)))
+        return out
+
+    def interdiffusion(self, T, Vm, x, N=2, frame=0, dep=-1, solvent=-1, do_compress=True):
+        x = np.ascontiguousarray(x, float)
+        out = np.empty(self.nc * self.nc)
+        r, c = C.c_int(), C.c_int()
+        self._chk(self.L.kgref_interdiffusion(self.h, T, Vm, _p(x), x.size, N, frame, dep, solvent, int(do_compress), _p(out),
+                                              C.byref(r), C.byref(c)))
+        return out[:r.value * c.value].reshape(r.value, c.value).copy()
+
+    def thermal_diffusion_coeff(self, T, Vm, x, N=2, frame=0, dep=-1, solvent=-1):
+        x = np.ascontiguousarray(x, float)
+        out = np.empty(self.nc)
+        n = C.c_int()
+        self._chk(self.L.kgref_thermal_diffusion_coeff(self.h, T, Vm, _p(x), x.size, N, frame, dep, solvent, _p(out), C.byref(n)))
+        return out[:n.value].copy()

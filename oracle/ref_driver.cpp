@@ -1,0 +1,247 @@
+// oracle/ref_driver.cpp -- TEST INFRASTRUCTURE ONLY (never imported by the product path).
+//
+// Thin extern "C" driver around the UNMODIFIED reference sources (compiled from where they lie under
+// /root/reference/cpp by oracle/Makefile into oracle/_ref/libkgref.so). It exposes the reference's own
+// chi / get_R / omega / w_integral / transfer lengths / rdf / matrices / transport properties so that
+//   (1) the C restatement in oracle/kg_oracle.c can be pinned against the real thing, and
+//   (2) golden fixtures under tests/golden/ can be generated (oracle/make_golden.py).
+// EoS-derived inputs enter through a table-backed GenericEoS (cpp/eos_interface.h:57-119) because
+// thermopack's Fortran core cannot be built in this image.
+#include "MieKinGas.h"
+#include "Integration/Integration.h"
+#include <cstring>
+#include <set>
+#include <mutex>
+
+namespace {
+
+struct TableEoS {
+    int VAPPH{2};
+    int nc{0};
+    std::vector<double> dmudn_tab;   // nc*nc, J/mol^2, for n = x (1 mol total), V = Vm
+    std::vector<double> cp_id;       // nc
+    double p{0.}, vm{0.};
+    std::vector<double> dvdn_tab;    // nc
+    std::vector<std::vector<double>> dmudn(double, double, const std::vector<double>) const {
+        std::vector<std::vector<double>> out(nc, std::vector<double>(nc));
+        for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) out[i][j] = dmudn_tab[i * nc + j];
+        return out;
+    }
+    double Cp_ideal(double, int c) const { return cp_id.at(c - 1); }
+    double Cp_real(double, double, const std::vector<double>) const { throw std::runtime_error("TableEoS: Cp_real"); }
+    double pressure_tv(double, double, const std::vector<double>) const { return p; }
+    double specific_volume(double, double, const std::vector<double>, int) const { return vm; }
+    std::vector<double> dvdn(double, double, const std::vector<double>, int) const { return dvdn_tab; }
+};
+
+struct Handle {
+    std::unique_ptr<MieKinGas> kin;
+    int nc;
+    std::string err;
+};
+
+vector2d to2d(const double* a, int n) {
+    vector2d v(n, vector1d(n));
+    for (int i = 0; i < n; i++) for (int j = 0; j < n; j++) v[i][j] = a[i * n + j];
+    return v;
+}
+
+template<class F> int guarded(Handle* h, F&& f) {
+    try { f(); return 0; }
+    catch (const std::exception& e) { h->err = e.what(); return -1; }
+}
+
+// Expose protected/private-free members we need through a derived type
+struct MieAccess : public MieKinGas {
+    using MieKinGas::MieKinGas;
+    using KineticGas::cache;
+    void clear_cache() { cache.clear(); }
+};
+
+} // namespace
+
+extern "C" {
+
+void* kgref_mie_create(int nc, const double* m, const double* sigma, const double* eps,
+                       const double* la, const double* lr, int is_idealgas, int is_singlecomp) {
+    Handle* h = new Handle;
+    h->nc = nc;
+    h->kin.reset(new MieAccess(vector1d(m, m + nc), to2d(sigma, nc), to2d(eps, nc), to2d(la, nc), to2d(lr, nc),
+                               is_idealgas != 0, is_singlecomp != 0));
+    return h;
+}
+void kgref_destroy(void* hv) { delete static_cast<Handle*>(hv); }
+const char* kgref_last_error(void* hv) { return static_cast<Handle*>(hv)->err.c_str(); }
+void kgref_clear_cache(void* hv) { static_cast<MieAccess*>(static_cast<Handle*>(hv)->kin.get())->clear_cache(); }
+void kgref_set_omega_correlation_active(void* hv, int active) { static_cast<Handle*>(hv)->kin->set_omega_correlation_active(active != 0); }
+void kgref_set_tl_model(void* hv, int id) { static_cast<Handle*>(hv)->kin->set_transfer_length_model(id); }
+
+void kgref_set_eos_tables(void* hv, const double* dmudn, const double* cp_id, double p, double vm, const double* dvdn) {
+    Handle* h = static_cast<Handle*>(hv);
+    TableEoS e;
+    e.nc = h->nc;   // note: for single-component models the EoS sees 1 component; caller passes matching tables
+    if (dmudn) e.dmudn_tab.assign(dmudn, dmudn + h->nc * h->nc);
+    if (cp_id) e.cp_id.assign(cp_id, cp_id + h->nc);
+    if (dvdn) e.dvdn_tab.assign(dvdn, dvdn + h->nc);
+    e.p = p; e.vm = vm;
+    h->kin->set_eos(GenericEoS(std::move(e)));
+}
+void kgref_set_eos_tables_nc(void* hv, int nc_eos, const double* dmudn, const double* cp_id, double p, double vm, const double* dvdn) {
+    Handle* h = static_cast<Handle*>(hv);
+    TableEoS e;
+    e.nc = nc_eos;
+    if (dmudn) e.dmudn_tab.assign(dmudn, dmudn + nc_eos * nc_eos);
+    if (cp_id) e.cp_id.assign(cp_id, cp_id + nc_eos);
+    if (dvdn) e.dvdn_tab.assign(dvdn, dvdn + nc_eos);
+    e.p = p; e.vm = vm;
+    h->kin->set_eos(GenericEoS(std::move(e)));
+}
+
+// ---- collision dynamics (cpp/Spherical.cpp) ----
+double kgref_potential(void* hv, int i, int j, double r) { return static_cast<Handle*>(hv)->kin->potential(i, j, r); }
+double kgref_potential_r(void* hv, int i, int j, double r) { return static_cast<Handle*>(hv)->kin->potential_derivative_r(i, j, r); }
+double kgref_chi(void* hv, int i, int j, double T, double g, double b) { return static_cast<Handle*>(hv)->kin->chi(i, j, T, g, b); }
+double kgref_theta(void* hv, int i, int j, double T, double g, double b) { return static_cast<Handle*>(hv)->kin->theta(i, j, T, g, b); }
+double kgref_get_R(void* hv, int i, int j, double T, double g, double b) { return static_cast<Handle*>(hv)->kin->get_R(i, j, T, g, b); }
+int kgref_chi_batch(void* hv, int i, int j, double T, int n, const double* g, const double* b, double* out) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{ for (int k = 0; k < n; k++) out[k] = h->kin->chi(i, j, T, g[k], b[k]); });
+}
+int kgref_get_R_batch(void* hv, int i, int j, double T, int n, const double* g, const double* b, double* out) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{ for (int k = 0; k < n; k++) out[k] = h->kin->get_R(i, j, T, g[k], b[k]); });
+}
+double kgref_w_integrand(void* hv, int i, int j, double T, double g, double b, int l, int r) {
+    return static_cast<Handle*>(hv)->kin->w_integrand(i, j, T, g, b, l, r);
+}
+// omega through the normal (cached, correlation-aware) path: MieKinGas::omega -> Spherical::omega
+int kgref_omega(void* hv, int i, int j, int l, int r, double T, double* out) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{ *out = static_cast<Spherical*>(h->kin.get())->Spherical::omega(i, j, l, r, T); });
+}
+int kgref_omega_model(void* hv, int i, int j, int l, int r, double T, double* out) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{ *out = h->kin->omega(i, j, l, r, T); });
+}
+// dimensionless W via the tester entry (no cache, explicit lattice)
+int kgref_w_integral_tester(void* hv, int i, int j, double T, int l, int r,
+                            double end_g, double end_b, double dg, double db, int rlg, int rlb, double lim, double* out) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{
+        IntegrationParam p({1e-7, 1e-7}, {end_g, end_b}, dg, db, rlg, rlb, lim);
+        *out = h->kin->w_integral_tester(i, j, T, l, r, p);
+    });
+}
+// Same integral, but through integrate2d with a recording integrand: returns the lattice points
+// (first-visit coordinates) the reference's adaptive mesh evaluates. pts: [max_pts][3] = (g, b, value)
+int kgref_w_integral_trace(void* hv, int i, int j, double T, int l, int r,
+                           double end_g, double end_b, double dg, double db, int rlg, int rlb, double lim,
+                           double* out, double* pts, int max_pts, int* npts) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{
+        int n = 0;
+        auto f = [&](double g, double b) {
+            double v = h->kin->w_integrand(i, j, T, g, b, l, r);
+            if (n < max_pts) { pts[3 * n] = g; pts[3 * n + 1] = b; pts[3 * n + 2] = v; }
+            n++;
+            return v;
+        };
+        *out = integrate2d(Point{1e-7, 1e-7}, Point{end_g, end_b}, dg, db, rlg, rlb, lim, f);
+        *npts = n;
+    });
+}
+// integrate2d on a caller-supplied table f[Nx][Ny] (pins the mesh replay independently of chi)
+double kgref_integrate2d_table(const double* tab, int nx, int ny, double ox, double oy, double ex, double ey,
+                               double dx, double dy, int rlx, int rly, double lim, int* nevals) {
+    int n = 0;
+    auto f = [&](double x, double y) {
+        int ix = (int) ((x - ox) / dx + 0.5), iy = (int) ((y - oy) / dy + 0.5);
+        n++;
+        if (ix < 0 || iy < 0 || ix >= nx || iy >= ny) return 0.0;
+        return tab[ix * ny + iy];
+    };
+    double v = integrate2d(Point{ox, oy}, Point{ex, ey}, dx, dy, rlx, rly, lim, f);
+    if (nevals) *nevals = n;
+    return v;
+}
+double kgref_tanh_sinh_test(int which, double a, double h_, double tol) {
+    // which=0: f(u)=1/sqrt(1-u*u) ; which=1: f(u)=exp(a*u)
+    if (which == 0) return tanh_sinh([&](double u){ return 1.0 / sqrt(1.0 - u * u); }, h_, tol);
+    return tanh_sinh([&](double u){ return exp(a * u); }, h_, tol);
+}
+
+// ---- state-point level (cpp/KineticGas.cpp, KineticGas_properties.cpp, transfer_lengths.cpp, MieKinGas.cpp) ----
+static void flat(const vector2d& v, double* out) { size_t k = 0; for (auto& r : v) for (double x : r) out[k++] = x; }
+int kgref_mtl(void* hv, double rho, double T, const double* x, double* out) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{ flat(h->kin->get_mtl(rho, T, vector1d(x, x + h->nc)), out); });
+}
+int kgref_etl(void* hv, double rho, double T, const double* x, double* out) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{ flat(h->kin->get_etl(rho, T, vector1d(x, x + h->nc)), out); });
+}
+int kgref_rdf(void* hv, double rho, double T, const double* x, double* out) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{ flat(h->kin->get_rdf(rho, T, vector1d(x, x + h->nc)), out); });
+}
+int kgref_bh_diameters(void* hv, double T, double* out) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{ flat(h->kin->get_BH_diameters(T), out); });
+}
+int kgref_K_factors(void* hv, double rho, double T, const double* x, double* K, double* Kp) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{
+        vector1d xv(x, x + h->nc);
+        vector1d a = h->kin->get_K_factors(rho, T, xv), b = h->kin->get_K_prime_factors(rho, T, xv);
+        for (int i = 0; i < h->nc; i++) { K[i] = a[i]; Kp[i] = b[i]; }
+    });
+}
+// which: 0 conductivity, 1 diffusion, 2 viscosity. mat is (dim x dim) row-major, vec dim. returns dim via *dim
+int kgref_matrix_vector(void* hv, int which, double rho, double T, const double* x, int N, double* mat, double* vec, int* dim) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{
+        vector1d xv(x, x + h->nc);
+        vector2d M; vector1d v;
+        if (which == 0) { M = h->kin->get_conductivity_matrix(rho, T, xv, N); v = h->kin->get_conductivity_vector(rho, T, xv, N); }
+        else if (which == 1) { M = h->kin->get_diffusion_matrix(rho, T, xv, N); v = h->kin->get_diffusion_vector(rho, T, xv, N); }
+        else { M = h->kin->get_viscosity_matrix(rho, T, xv, N); v = h->kin->get_viscosity_vector(rho, T, xv, N); }
+        *dim = (int) v.size();
+        if (mat) flat(M, mat);
+        if (vec) for (size_t k = 0; k < v.size(); k++) vec[k] = v[k];
+    });
+}
+int kgref_viscosity(void* hv, double T, double Vm, const double* x, int nx, int N, double* out) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{ *out = h->kin->viscosity(T, Vm, vector1d(x, x + nx), N); });
+}
+int kgref_thermal_conductivity(void* hv, double T, double Vm, const double* x, int nx, int N, double* out) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{ *out = h->kin->thermal_conductivity(T, Vm, vector1d(x, x + nx), N); });
+}
+int kgref_thermal_conductivity_contribs(void* hv, double T, double Vm, const double* x, int nx, int N, double* out3) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{
+        auto m = h->kin->thermal_conductivity_contributions(T, Vm, vector1d(x, x + nx), N, "tdi");
+        out3[0] = m["t"]; out3[1] = m["d"]; out3[2] = m["i"];
+    });
+}
+int kgref_interdiffusion(void* hv, double T, double Vm, const double* x, int nx, int N, int frame, int dep, int solvent,
+                         int do_compress, double* out, int* rows, int* cols) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{
+        Eigen::MatrixXd D = h->kin->interdiffusion(T, Vm, vector1d(x, x + nx), N, frame, dep, solvent, do_compress != 0);
+        *rows = (int) D.rows(); *cols = (int) D.cols();
+        for (int i = 0; i < D.rows(); i++) for (int j = 0; j < D.cols(); j++) out[i * D.cols() + j] = D(i, j);
+    });
+}
+int kgref_thermal_diffusion_coeff(void* hv, double T, double Vm, const double* x, int nx, int N, int frame, int dep, int solvent,
+                                  double* out, int* n) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{
+        Eigen::VectorXd D = h->kin->thermal_diffusion_coeff(T, Vm, vector1d(x, x + nx), N, frame, dep, solvent);
+        *n = (int) D.size();
+        for (int i = 0; i < D.size(); i++) out[i] = D(i);
+    });
+}
+
+} // extern "C"
