@@ -1,0 +1,52 @@
+"""Loader for libkgcuda.so (the C-ABI library, include/kgcuda.h). There is no CPU fallback: if the library is
+missing or no CUDA device is present, calls fail loudly."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libkgcuda.so")
+KG_MAX_TERMS = 6
+dp = C.POINTER(C.c_double)
+ip = C.POINTER(C.c_int32)
+
+# every symbol include/kgcuda.h declares
+EXPORTS = [
+    "kg_model_create", "kg_model_destroy", "kg_last_error", "kg_model_npairs", "kg_chi_points", "kg_omega_batch",
+    "kg_omega_plan_create", "kg_omega_plan_run", "kg_omega_plan_sync", "kg_omega_plan_fetch", "kg_omega_plan_omega_dev",
+    "kg_omega_plan_destroy", "kg_omega_plan_counters", "kg_measure_fp64_peak",
+]
+
+
+class PotentialDesc(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("nterms", C.c_int32), ("sigma", C.c_double), ("eps", C.c_double),
+                ("C", C.c_double * KG_MAX_TERMS), ("lam", C.c_double * KG_MAX_TERMS)]
+
+
+_LIB = None
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                               "(the CUDA path has no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        L.kg_model_create.argtypes = [C.POINTER(PotentialDesc), C.c_int, dp, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        L.kg_model_destroy.argtypes = [C.c_void_p]
+        L.kg_last_error.restype = C.c_char_p
+        L.kg_last_error.argtypes = [C.c_void_p]
+        L.kg_model_npairs.argtypes = [C.c_void_p]
+        L.kg_chi_points.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int, dp, dp, dp, dp, dp, ip]
+        L.kg_omega_batch.argtypes = [C.c_void_p, C.c_int, dp, C.c_int, ip, ip, dp, dp, dp, ip]
+        L.kg_omega_plan_create.argtypes = [C.c_void_p, C.c_int, dp, C.c_int, ip, ip, dp, C.POINTER(C.c_void_p)]
+        for n in ("kg_omega_plan_run", "kg_omega_plan_sync", "kg_omega_plan_destroy"):
+            getattr(L, n).argtypes = [C.c_void_p]
+        L.kg_omega_plan_destroy.restype = None
+        L.kg_omega_plan_fetch.argtypes = [C.c_void_p, dp, dp, ip]
+        L.kg_omega_plan_omega_dev.restype = C.c_void_p
+        L.kg_omega_plan_omega_dev.argtypes = [C.c_void_p]
+        L.kg_omega_plan_counters.argtypes = [C.c_void_p, dp]
+        L.kg_measure_fp64_peak.argtypes = [C.c_int, dp, dp]
+        _LIB = L
+    return _LIB

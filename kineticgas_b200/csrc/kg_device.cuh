@@ -1,0 +1,237 @@
+// kg_device.cuh -- device-side collision dynamics for sm_100a (FP64, register resident).
+//
+// What the reference computes (cpp/Spherical.cpp:259-465, cpp/Integration/Integration.cpp:417-510):
+//   R     = outermost root of  u(r)/(kT g^2) + (b/r)^2 - 1                       (get_R: shrink x0.95, bisect, Newton)
+//   I     = sum_k w_k (R/u_k^2) [ r^4/b^2 (1 - u(r)/(kT g^2)) - r^2 ]^(-1/2), r = R/u_k   (tanh-sinh, h = 1e-3, truncated)
+//   theta = I(R,g,b) - I(R_lim,g,100 sigma) + PI/2 ;  chi = PI - 2 theta
+// How it is laid out here: one lane per deflection angle. The tanh-sinh abscissae are problem independent, so the
+// host tabulates, per pair, rows  { w_k/u_k, 1/u_k^2, u_k^lam_0, .., u_k^lam_{NT-1} }  (same libm calls as the
+// reference). With s = sigma/r = u (sigma/R), every power-law term factorises, (sigma/r)^lam = u^lam (sigma/R)^lam, so
+//   term_k = (w_k/u_k) * rsqrt( X_k ),   X_k = (R/b)^2 (1/u_k^2) (1 - sum_t A_t u_k^lam_t) - 1,
+//   A_t = eps C_t (sigma/R)^lam_t / (kT g^2)   (per lane, once)
+// which is algebraically the reference integrand; no transcendental is left in the node loop. The sequential stop
+// rule (add, then test the next term against the running sum, break on NaN/Inf) is kept node for node.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace kg {
+
+// cpp/global_params.h:4-7 -- PI is truncated in the reference and must be truncated here (parity)
+__device__ constexpr double BOLTZMANN = 1.38064852e-23;
+__device__ constexpr double PI_REF = 3.14159265359;
+
+constexpr int KMAX = 3328;          // tanh-sinh rows tabulated (u_k == 1.0 in double from k ~ 3170)
+constexpr int MAX_TERMS = 6;
+constexpr double TS_TOL = 1e-5;     // tanh_sinh default tol, cpp/Integration/Integration.h
+
+struct PairParams {                 // staged in shared memory per CTA
+    double sigma, eps;
+    int nterms, ntpad;              // ntpad in {2,4,6}: row width = 2 + ntpad doubles
+    double C[MAX_TERMS];
+    double lam[MAX_TERMS];
+};
+
+// Per-lane collision context in reduced units (lengths / sigma)
+template<int NT>
+struct Lane {
+    double Bt[NT];     // eps C_t / (kT g^2)
+    double lam[NT];
+    double b;          // impact parameter / sigma
+};
+
+// u(r)/(kT g^2) and sigma u'(r)/(kT g^2) at r = ri sigma, sharing one log: s^lam = exp(lam ln s)
+template<int NT>
+__device__ __forceinline__ void pot_eval(const Lane<NT>& c, double ri, double& U, double& dU) {
+    const double ls = -log(ri);
+    const double inv = 1.0 / ri;
+    double u = 0.0, du = 0.0;
+#pragma unroll
+    for (int t = 0; t < NT; t++) {
+        const double p = c.Bt[t] * exp(c.lam[t] * ls);
+        u += p;
+        du -= c.lam[t] * p;
+    }
+    U = u;
+    dU = du * inv;
+}
+
+template<int NT>
+__device__ __forceinline__ double rootfun(const Lane<NT>& c, double ri) {
+    // cpp/Spherical.cpp:368
+    double U, dU;
+    pot_eval<NT>(c, ri, U, dU);
+    const double q = c.b / ri;
+    return U + q * q - 1.0;
+}
+
+template<int NT>
+__device__ __forceinline__ void rootfun_d(const Lane<NT>& c, double ri, double& f, double& df) {
+    // cpp/Spherical.cpp:368-369
+    double U, dU;
+    pot_eval<NT>(c, ri, U, dU);
+    const double q = c.b / ri;
+    f = U + q * q - 1.0;
+    df = dU - (2.0 / c.b) * (q * q * q);
+}
+
+// cpp/Integration/Integration.cpp:456-471 (ftol = -1: only the step criterion is live)
+template<int NT>
+__device__ double newton_usafe(const Lane<NT>& c, double x0, double dtol, int& ierr) {
+    int niter = 0;
+    double prev_x, f, df;
+    do {
+        prev_x = x0;
+        rootfun_d<NT>(c, x0, f, df);
+        x0 -= f / df;
+        if (niter++ > 50) { ierr = 1; return x0; }
+    } while (fabs(x0 - prev_x) > dtol);
+    if (isnan(x0)) { ierr = 2; return x0; }
+    if (isinf(x0)) { ierr = 3; return x0; }
+    return x0;
+}
+
+// cpp/Integration/Integration.cpp:494-510 (ftol = -1)
+template<int NT>
+__device__ void bracket_root_usafe(const Lane<NT>& c, double& x0, double& x1, double& f0, double& f1, double dtol) {
+    while (fabs(x0 - x1) > dtol) {
+        const double xm = 0.5 * (x0 + x1);
+        const double fm = rootfun<NT>(c, xm);
+        if (f0 * fm > 0) { x0 = xm; f0 = fm; }
+        else { x1 = xm; f1 = fm; }
+    }
+    if (fabs(f0) > fabs(f1)) {
+        double t = x0; x0 = x1; x1 = t;
+        t = f0; f0 = f1; f1 = t;
+    }
+}
+
+// cpp/Spherical.cpp:437-453 : head-on turning point, u(R0) = kT g^2. Reduced units; Bt already carries 1/(kT g^2),
+// so f = U - 1 and the convergence test |f / (dfdr sigma)| is unchanged by the common scale.
+template<int NT>
+__device__ double get_R0(const Lane<NT>& c) {
+    double r = 0.9, U, dU;
+    pot_eval<NT>(c, r, U, dU);
+    double f = U - 1.0;
+    int guard = 0;
+    while (f < 0 && guard++ < 2000) {
+        r *= 0.8;
+        pot_eval<NT>(c, r, U, dU);
+        f = U - 1.0;
+    }
+    guard = 0;
+    while (fabs(f / dU) > 1e-6 && guard++ < 10000) {
+        r -= f / dU;
+        pot_eval<NT>(c, r, U, dU);
+        f = U - 1.0;
+    }
+    return r;
+}
+
+// cpp/Spherical.cpp:358-435 ; returns R / sigma. g enters through Bt; g < 1e-6 or b < 1e-5 -> get_R0.
+template<int NT>
+__device__ double get_R(const Lane<NT>& c, double g, int& status) {
+    if ((c.b < 1e-5) || (g < 1e-6)) return get_R0<NT>(c);
+    double r0, r1, bracket_dtol;
+    const double newton_dtol = 1e-6;
+    if (c.b > 1) { r0 = r1 = c.b; bracket_dtol = 0.1; }
+    else { r0 = r1 = 1; bracket_dtol = 0.05; }
+    double f0 = rootfun<NT>(c, r0);
+    double f1 = f0;
+    int guard = 0;
+    while (f0 < 0 && guard++ < 4000) { r0 *= 0.95; f0 = rootfun<NT>(c, r0); }
+    if (r1 - r0 > bracket_dtol) bracket_root_usafe<NT>(c, r0, r1, f0, f1, bracket_dtol);
+    if (fabs(f0) < 1e-8) return r0;
+
+    int ierr = 0;
+    double R = newton_usafe<NT>(c, r0, newton_dtol, ierr);
+    if (ierr != 0) { ierr = 0; R = newton_usafe<NT>(c, r1, newton_dtol, ierr); }
+    if (ierr != 0) { ierr = 0; R = newton_usafe<NT>(c, 0.5 * (r0 + r1), newton_dtol, ierr); }
+    int niter = 0;
+    while (ierr != 0) {
+        const double prev_r0 = r0;
+        while ((prev_r0 == r0) && (bracket_dtol > newton_dtol)) {
+            if (fabs(r1 - r0) < bracket_dtol) bracket_dtol /= 2;
+            bracket_root_usafe<NT>(c, r0, r1, f0, f1, bracket_dtol);
+        }
+        if (bracket_dtol < newton_dtol) { R = r0; break; }
+        ierr = 0;
+        R = newton_usafe<NT>(c, r0, newton_dtol, ierr);
+        if (niter++ > 50) { status |= 1; return nan(""); }   // "get_R reached max iter!"
+    }
+    return R;
+}
+
+// One tanh-sinh term from a table row. row = { w/u, 1/u^2, u^lam_0 .. }
+template<int NT>
+__device__ __forceinline__ double ts_term(const double* __restrict__ row, const double (&A)[NT], double c2, double& X) {
+    double P = 1.0;
+#pragma unroll
+    for (int t = 0; t < NT; t++) P = fma(-A[t], row[2 + t], P);
+    X = fma(c2 * row[1], P, -1.0);
+    return row[0] * rsqrt(X);
+}
+
+// Two consecutive nodes (k+1, k+2) evaluated together, then the reference's sequential stop rule applied in order:
+// break on NaN/Inf of the new integrand value (radicand <= 0 or NaN; Integration.cpp:430), stop when
+// |w f / I| <= tol (Integration.cpp:431), otherwise add. Returns true when the sum has terminated.
+template<int NT>
+__device__ __forceinline__ bool ts_step2(const double* __restrict__ ra, const double (&A)[NT], double c2, double& I, int& k) {
+    constexpr int W = 2 + NT;
+    double Xa, Xb;
+    const double ta = ts_term<NT>(ra, A, c2, Xa);
+    const double tb = ts_term<NT>(ra + W, A, c2, Xb);
+    k += 1;
+    if (!(Xa > 0.0) || !(fabs(ta) > TS_TOL * fabs(I))) return true;
+    I += ta;
+    k += 1;
+    if (!(Xb > 0.0) || !(fabs(tb) > TS_TOL * fabs(I))) return true;
+    I += tb;
+    return false;
+}
+
+// cpp/Spherical.cpp:321-329 + cpp/Integration/Integration.cpp:417-437, on tabulated nodes.
+// srows: first KS rows in shared memory (KS even); grows: all KMAX rows in global memory. Returns the truncated
+// sum; nodes += k at exit (the value the reference's loop variable reaches). Row j holds node k = j + 1.
+template<int NT>
+__device__ double theta_integral(const double* __restrict__ srows, const double* __restrict__ grows, int KS,
+                                 const double (&A)[NT], double c2, unsigned& nodes, int& status) {
+    constexpr int W = 2 + NT;
+    double X;
+    double I = ts_term<NT>(srows, A, c2, X);        // k = 1 is added unconditionally (Integration.cpp:425)
+    int k = 1;
+    bool stop = false;
+    while (!stop && k + 1 < KS) stop = ts_step2<NT>(srows + (size_t) k * W, A, c2, I, k);
+    while (!stop) {
+        if (k + 2 >= KMAX) { status |= 2; break; }
+        stop = ts_step2<NT>(grows + (size_t) k * W, A, c2, I, k);
+    }
+    nodes += (unsigned) k;
+    return I;
+}
+
+// Full single-lane evaluation of the theta integral for (g, b): R, A_t, c2, then the sum. Returns I; R_out in sigma.
+template<int NT>
+__device__ double lane_theta_integral(const PairParams& pp, const double* coeff, const double* __restrict__ srows,
+                                      const double* __restrict__ grows, int KS, double T, double g, double b,
+                                      double& R_out, unsigned& nodes, int& status) {
+    Lane<NT> c;
+    const double E = BOLTZMANN * T * (g * g);
+#pragma unroll
+    for (int t = 0; t < NT; t++) {
+        const double Ct = (t < pp.nterms) ? (coeff ? coeff[t] : pp.C[t]) : 0.0;
+        c.Bt[t] = pp.eps * Ct / E;
+        c.lam[t] = (t < pp.nterms) ? pp.lam[t] : 1.0;
+    }
+    c.b = b;
+    const double R = get_R<NT>(c, g, status);
+    R_out = R;
+    double A[NT];
+    const double s = 1.0 / R;
+#pragma unroll
+    for (int t = 0; t < NT; t++) A[t] = c.Bt[t] * pow(s, c.lam[t]);
+    const double q = R / b;
+    return theta_integral<NT>(srows, grows, KS, A, q * q, nodes, status);
+}
+
+} // namespace kg

@@ -1,0 +1,870 @@
+// kg_omega.cu -- batched collision integrals Omega^(l,r)_ij(T) on B200 (sm_100a), behind the C-ABI of include/kgcuda.h.
+//
+// Reference path replaced (thermotools/KineticGas @ 75848b1):
+//   KineticGas::precompute_omega fan-out              cpp/KineticGas_mthr.cpp:40-46,58-143
+//   Spherical::omega -> w_integral -> integrate2d     cpp/Spherical.cpp:37-102, cpp/Integration/Integration.cpp:145-307
+//   chi / theta / get_R / tanh_sinh                   cpp/Spherical.cpp:259-465, cpp/Integration/Integration.cpp:417-510
+//
+// Design (not a translation): the reference evaluates the integrand lazily, point by point, inside a recursive
+// triangulation, recomputing the deflection angle for every (l,r). Here one *item* = (pair, T) owns a lattice of
+// cos(chi) in HBM shared by all (l,r); the adaptive mesh is a decision tree over that lattice and is walked
+// level-synchronously:
+//     mesh_kernel   : one CTA per (item,(l,r)), one thread per coarse cell, DFS of the refinement tree using the
+//                     reference's exact refinement predicate; lattice nodes that are needed but unknown are marked
+//     count/scan/fill: compaction of the newly marked nodes of all items into one work list (sorted by pair, item,
+//                     column, row -> neighbouring lanes integrate neighbouring trajectories)
+//     theta_kernel  : one lane per theta integral (kg_device.cuh), persistent CTAs, 512-node tiles, tanh-sinh rows of
+//                     the pair staged in shared memory
+//     finalize      : cos(chi) from I - I_lim, publish nodes as known
+// repeated until no mesh thread meets an unknown node (depth of the refinement tree + 1 passes). Only nodes the
+// reference's mesh touches are ever integrated.
+#include "kg_device.cuh"
+#include "../../include/kgcuda.h"
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <algorithm>
+
+using namespace kg;
+
+#define CUDA_OK(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { \
+    set_error(std::string(#expr) + ": " + cudaGetErrorString(e_)); return -2; } } while (0)
+
+static thread_local std::string g_create_error;
+
+namespace {
+
+constexpr int THETA_THREADS = 512;
+constexpr int KS_ROWS = 2560;          // tanh-sinh rows staged in shared memory (rest read through L1/L2)
+constexpr unsigned LIM_ROW = 0xFFFFu;  // work-list entry that is a theta_lim evaluation of its column
+
+struct Regime {            // the T-dependent lattice of Spherical::w_integral (cpp/Spherical.cpp:60-84)
+    int nx, ny;            // allocated lattice incl. the +2-step over-reach of the refinement probes
+    int Nx_end, Ny_end, rlg, rlb, nwords;
+    double dg, db, lim;
+};
+
+struct Item {              // one (pair, T)
+    int pair, regime;
+    double T;
+    double pref;           // Omega = pref * W (cpp/Spherical.cpp:46-47)
+    long long tab_off;     // into the cos(chi) lattice pool   [nx][ny]
+    long long mask_off;    // into the want/known bit pools     [nx][nwords]
+    long long col_off;     // into the per-column pools (I_lim, have_lim, task index) [nx]
+    int coeff_off;         // into coeff pool (doubles) or -1
+    int pad;
+};
+
+struct WorkEntry { int item; unsigned short nx, ny; };
+
+__device__ __forceinline__ double lattice_coord(int n, double d) { return 1e-7 + n * d; }   // cpp/Spherical.cpp:60
+
+// ------------------------------------------------------------------------------------------------------------
+// mesh kernel
+// ------------------------------------------------------------------------------------------------------------
+struct MeshView {
+    const double* tab;
+    const unsigned* known;
+    unsigned* want;
+    const double* gfac;     // [nx] : 2 exp(-g^2) g^(2r+3) for this (regime, r)
+    int ny, nwords, l;
+    double dg, db, lim, cospi;
+    bool incomplete;
+};
+
+// integrand value at lattice node (Nx,Ny): cpp/Spherical.cpp:96-102. Returns false (and marks the node) if chi is not known yet.
+__device__ __forceinline__ bool mesh_fetch(MeshView& v, int Nx, int Ny, double& f) {
+    const double g = lattice_coord(Nx, v.dg), b = lattice_coord(Ny, v.db);
+    if ((b > 2.5) && (g > 1.5)) { f = 0.0; return true; }
+    double c;
+    if (Ny == 0) c = v.cospi;                 // b/sigma < 1e-3 -> theta = 0 -> chi = PI (cpp/Spherical.cpp:267)
+    else {
+        const int w = Nx * v.nwords + (Ny >> 5);
+        const unsigned bit = 1u << (Ny & 31);
+        if (!(v.known[w] & bit)) {
+            if (!(v.want[w] & bit)) atomicOr(&v.want[w], bit);
+            v.incomplete = true;
+            f = 0.0;
+            return false;
+        }
+        c = v.tab[(long long) Nx * v.ny + Ny];
+    }
+    double cl = c;
+    for (int i = 1; i < v.l; i++) cl *= c;
+    f = __dmul_rn(__dmul_rn(v.gfac[Nx], __dsub_rn(1.0, cl)), b);
+    return true;
+}
+
+struct Frame { short x0, y0, x1, y1, sx, sy, row, col; };
+
+// One integration_step of the reference (cpp/Integration/Integration.cpp:145-236) at entry corner (Nx,Ny) with signed
+// step sx and step sy. Returns 0 = pending (unknown values), 1 = leaf (integral added), 2 = refine (sub steps set).
+__device__ int mesh_cell(MeshView& v, int Nx, int Ny, int sx, int sy, double& integral, int& sub_sx, int& sub_sy) {
+    const int ax = abs(sx), ay = sy;
+    double f, f1x, f2x, f1y, f2y, f1x1y, f2x2y;
+    bool ok = mesh_fetch(v, Nx, Ny, f);
+    ok &= mesh_fetch(v, Nx + ax, Ny, f1x);
+    ok &= mesh_fetch(v, Nx + 2 * ax, Ny, f2x);
+    ok &= mesh_fetch(v, Nx, Ny + ay, f1y);
+    ok &= mesh_fetch(v, Nx, Ny + 2 * ay, f2y);
+    ok &= mesh_fetch(v, Nx + ax, Ny + ay, f1x1y);
+    ok &= mesh_fetch(v, Nx + 2 * ax, Ny + 2 * ay, f2x2y);
+    if (!ok) return 0;
+    // second-difference estimator, in the reference's operation order, no FMA contraction (decision predicate)
+    const double hx = fabs(v.dg * sx), hy = fabs(v.db * sy);
+    const double hx2 = __dmul_rn(hx, hx), hy2 = __dmul_rn(hy, hy);
+    const double fxx = __dadd_rn(__dsub_rn(f, __dmul_rn(2.0, f1x)), f2x) / hx2;
+    const double fyy = __dadd_rn(__dsub_rn(f, __dmul_rn(2.0, f1y)), f2y) / hy2;
+    double t = __dadd_rn(__dsub_rn(f2x2y, __dmul_rn(2.0, f1x1y)), f);
+    t = __dsub_rn(t, __dmul_rn(hx2, fxx));
+    t = __dsub_rn(t, __dmul_rn(hy2, fyy));
+    const double fxy = t / __dmul_rn(__dmul_rn(2.0, hx), hy);
+    const double dblder = __dadd_rn(__dadd_rn(fabs(fxx), fabs(fyy)), fabs(fxy));
+    const double hs = __dadd_rn(hx, hy);
+    const double hs3 = __dmul_rn(__dmul_rn(hs, hs), hs);
+    if ((__dmul_rn(dblder, hs3) > v.lim) && ((ax > 1) || (ay > 1))) {
+        const double cx = __dmul_rn(fabs(fxx), __dmul_rn(hx2, hx));
+        const double cy = __dmul_rn(fabs(fyy), __dmul_rn(hy2, hy));
+        sub_sx = sx; sub_sy = sy;
+        if (cx > v.lim && (cy < v.lim) && (fabs(fxy) < v.lim) && (ax > 1)) sub_sx = sx / 2;
+        else if (cy > v.lim && (cx < v.lim) && (fabs(fxy) < v.lim) && (ay > 1)) sub_sy = sy / 2;
+        else {
+            if (ax > 1) sub_sx = sx / 2;
+            if (ay > 1) sub_sy = sy / 2;
+        }
+        return 2;
+    }
+    // leaf: the two triangles the sweep adds for this cell, (Eb,Et,Xb) and (Et,Xb,Xt)  (Integration.cpp:218-234);
+    // a linear interpolant integrates to area * mean of the corner values.
+    double fXb, fXt;
+    if (sx > 0) { fXb = f1x; fXt = f1x1y; }
+    else {
+        bool ok2 = mesh_fetch(v, Nx + sx, Ny, fXb);
+        ok2 &= mesh_fetch(v, Nx + sx, Ny + ay, fXt);
+        if (!ok2) return 0;
+    }
+    integral += (hx * hy / 6.0) * (f + 2.0 * f1y + 2.0 * fXb + fXt);
+    return 1;
+}
+
+// grid: (nlr, nitems); block: 64 threads striding over the coarse cells of the item's top-level domain.
+__global__ void __launch_bounds__(64) mesh_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
+                                                  const double* __restrict__ tab_pool, const unsigned* __restrict__ known_pool,
+                                                  unsigned* __restrict__ want_pool, const double* __restrict__ gfac_pool,
+                                                  const int* __restrict__ lr_l, const int* __restrict__ lr_r_index, int nr_distinct,
+                                                  int gfac_stride, double cospi, int nlr,
+                                                  double* __restrict__ W_out, double* __restrict__ omega_out, int* __restrict__ flags) {
+    const int lr = blockIdx.x, it = blockIdx.y;
+    const Item item = items[it];
+    const Regime rg = regimes[item.regime];
+    MeshView v;
+    v.tab = tab_pool + item.tab_off;
+    v.known = known_pool + item.mask_off;
+    v.want = want_pool + item.mask_off;
+    v.gfac = gfac_pool + ((long long) item.regime * nr_distinct + lr_r_index[lr]) * gfac_stride;
+    v.ny = rg.ny; v.nwords = rg.nwords; v.l = lr_l[lr];
+    v.dg = rg.dg; v.db = rg.db; v.lim = rg.lim; v.cospi = cospi;
+    v.incomplete = false;
+
+    const int ncx = rg.Nx_end / rg.rlg, ncy = rg.Ny_end / rg.rlb;
+    double acc = 0.0;
+    Frame stack[12];
+    for (int cell = threadIdx.x; cell < ncx * ncy; cell += blockDim.x) {
+        // top-level sweep (cpp/Integration/Integration.cpp:240-280): row k runs +x for even k, -x for odd k
+        const int row = cell / ncx, col = cell % ncx;
+        const int d0 = (row & 1) ? -1 : 1;
+        const int ex0 = ((row & 1) ? rg.Nx_end : 0) + col * d0 * rg.rlg, ey0 = row * rg.rlb;
+        int ssx, ssy, top = 0;
+        int kind = mesh_cell(v, ex0, ey0, d0 * rg.rlg, rg.rlb, acc, ssx, ssy);
+        if (kind == 2) {
+            stack[0] = Frame{(short) ex0, (short) ey0, (short) (ex0 + d0 * rg.rlg), (short) (ey0 + rg.rlb), (short) ssx, (short) ssy, 0, 0};
+            top = 1;
+        }
+        while (top > 0) {
+            Frame& fr = stack[top - 1];
+            const int asx = abs((int) fr.sx);
+            const int ncols = abs(fr.x1 - fr.x0) / asx, nrows = (fr.y1 - fr.y0) / fr.sy;
+            if (fr.row >= nrows) { top--; continue; }
+            const int sgn = (fr.sx > 0) ? 1 : -1;
+            const int d = (fr.row & 1) ? -sgn : sgn;
+            const int ex = ((fr.row & 1) ? fr.x1 : fr.x0) + fr.col * d * asx;
+            const int ey = fr.y0 + fr.row * fr.sy;
+            const int csy = fr.sy;
+            if (++fr.col >= ncols) { fr.col = 0; fr.row++; }
+            kind = mesh_cell(v, ex, ey, d * asx, csy, acc, ssx, ssy);
+            if (kind == 2) {
+                stack[top] = Frame{(short) ex, (short) ey, (short) (ex + d * asx), (short) (ey + csy), (short) ssx, (short) ssy, 0, 0};
+                top++;
+            }
+        }
+    }
+    __shared__ double part[64];
+    __shared__ int inc;
+    if (threadIdx.x == 0) inc = 0;
+    __syncthreads();
+    part[threadIdx.x] = acc;
+    if (v.incomplete) inc = 1;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0.0;
+        for (int i = 0; i < blockDim.x; i++) s += part[i];
+        const long long o = (long long) it * nlr + lr;
+        W_out[o] = s;
+        omega_out[o] = item.pref * s;
+        if (inc) flags[0] = 1;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// work-list compaction: count -> scan -> fill.  A task is one lattice column (item, Nx).
+// ------------------------------------------------------------------------------------------------------------
+__global__ void count_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes, const int2* __restrict__ tasks, int ntasks,
+                             const unsigned* __restrict__ want_pool, const unsigned* __restrict__ known_pool,
+                             const unsigned char* __restrict__ have_lim, int* __restrict__ counts) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= ntasks) return;
+    const Item item = items[tasks[t].x];
+    const Regime rg = regimes[item.regime];
+    const long long w0 = item.mask_off + (long long) tasks[t].y * rg.nwords;
+    int c = 0;
+    for (int w = 0; w < rg.nwords; w++) c += __popc(want_pool[w0 + w] & ~known_pool[w0 + w]);
+    if (c > 0 && !have_lim[item.col_off + tasks[t].y]) c += 1;
+    counts[t] = c;
+}
+
+// single-CTA exclusive scan (ntasks is a few 1e5 at most); total -> counts_out[ntasks]
+__global__ void __launch_bounds__(1024) scan_kernel(const int* __restrict__ counts, int* __restrict__ offsets, int n) {
+    __shared__ int sums[1024];
+    const int per = (n + 1023) / 1024;
+    const int lo = threadIdx.x * per, hi = min(n, lo + per);
+    int s = 0;
+    for (int i = lo; i < hi; i++) s += counts[i];
+    sums[threadIdx.x] = s;
+    __syncthreads();
+    for (int off = 1; off < 1024; off <<= 1) {
+        int v = (threadIdx.x >= off) ? sums[threadIdx.x - off] : 0;
+        __syncthreads();
+        sums[threadIdx.x] += v;
+        __syncthreads();
+    }
+    int base = sums[threadIdx.x] - s;
+    for (int i = lo; i < hi; i++) { offsets[i] = base; base += counts[i]; }
+    if (threadIdx.x == 1023) offsets[n] = sums[1023];
+}
+
+__global__ void fill_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes, const int2* __restrict__ tasks, int ntasks,
+                            const unsigned* __restrict__ want_pool, const unsigned* __restrict__ known_pool,
+                            const unsigned char* __restrict__ have_lim, const int* __restrict__ offsets, WorkEntry* __restrict__ list) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= ntasks) return;
+    int o = offsets[t];
+    if (offsets[t + 1] == o) return;
+    const int it = tasks[t].x, nx = tasks[t].y;
+    const Item item = items[it];
+    const Regime rg = regimes[item.regime];
+    const long long w0 = item.mask_off + (long long) nx * rg.nwords;
+    if (!have_lim[item.col_off + nx]) list[o++] = WorkEntry{it, (unsigned short) nx, (unsigned short) LIM_ROW};
+    for (int w = 0; w < rg.nwords; w++) {
+        unsigned m = want_pool[w0 + w] & ~known_pool[w0 + w];
+        while (m) {
+            const int bpos = __ffs(m) - 1;
+            m &= m - 1;
+            list[o++] = WorkEntry{it, (unsigned short) nx, (unsigned short) (w * 32 + bpos)};
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// theta kernel: one lane per theta integral, persistent CTAs pulling 512-entry tiles
+// ------------------------------------------------------------------------------------------------------------
+template<int NT>
+__global__ void __launch_bounds__(THETA_THREADS, 2)
+theta_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes, const PairParams* __restrict__ pairs,
+             const double* const* __restrict__ rows_by_pair, const double* __restrict__ coeff_pool,
+             const WorkEntry* __restrict__ list, const int* __restrict__ nlist_ptr, int* __restrict__ tile_counter,
+             double* __restrict__ tab_pool, double* __restrict__ lim_pool, int* __restrict__ status_pool,
+             unsigned long long* __restrict__ counters) {
+    extern __shared__ double srows[];
+    __shared__ PairParams spair;
+    __shared__ int s_tile, s_pair_loaded;
+    constexpr int W = 2 + NT;
+    const int nlist = *nlist_ptr;
+    const int ntiles = (nlist + THETA_THREADS - 1) / THETA_THREADS;
+    if (threadIdx.x == 0) s_pair_loaded = -1;
+    unsigned long long my_nodes = 0, my_evals = 0, my_lim_nodes = 0, my_lim_evals = 0;
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_tile = atomicAdd(tile_counter, 1);
+        __syncthreads();
+        const int tile = s_tile;
+        if (tile >= ntiles) break;
+        const int e = tile * THETA_THREADS + threadIdx.x;
+        const bool active = e < nlist;
+        WorkEntry we = active ? list[e] : WorkEntry{0, 0, 0};
+        Item item = items[we.item];
+        // the list is sorted by pair: a tile spans pairs [p_first, p_last]
+        const int p_first = items[list[tile * THETA_THREADS].item].pair;
+        const int p_last = items[list[min(nlist, (tile + 1) * THETA_THREADS) - 1].item].pair;
+        for (int p = p_first; p <= p_last; p++) {
+            if (s_pair_loaded != p) {
+                __syncthreads();
+                const double* src = rows_by_pair[p];
+                for (int i = threadIdx.x; i < KS_ROWS * W; i += THETA_THREADS) srows[i] = src[i];
+                if (threadIdx.x == 0) { spair = pairs[p]; s_pair_loaded = p; }
+                __syncthreads();
+            }
+            if (active && item.pair == p) {
+                const Regime rg = regimes[item.regime];
+                const double g = lattice_coord(we.nx, rg.dg);
+                const bool is_lim = (we.ny == LIM_ROW);
+                const double b = is_lim ? 100.0 : lattice_coord(we.ny, rg.db);   // theta_lim: b = 100 sigma (Spherical.cpp:316)
+                const double* coeff = (item.coeff_off >= 0) ? coeff_pool + item.coeff_off : nullptr;
+                double R; unsigned nodes = 0; int st = 0;
+                const double I = lane_theta_integral<NT>(spair, coeff, srows, rows_by_pair[p], KS_ROWS, item.T, g, b, R, nodes, st);
+                if (is_lim) { lim_pool[item.col_off + we.nx] = I; my_lim_nodes += nodes; my_lim_evals++; }
+                else { tab_pool[item.tab_off + (long long) we.nx * rg.ny + we.ny] = I; my_nodes += nodes; my_evals++; }
+                if (st) atomicOr(&status_pool[we.item], st);
+            }
+        }
+    }
+    // counters: [0] chi evals [1] chi nodes [2] lim evals [3] lim nodes
+    for (int off = 16; off > 0; off >>= 1) {
+        my_nodes += __shfl_down_sync(0xffffffffu, my_nodes, off);
+        my_evals += __shfl_down_sync(0xffffffffu, my_evals, off);
+        my_lim_nodes += __shfl_down_sync(0xffffffffu, my_lim_nodes, off);
+        my_lim_evals += __shfl_down_sync(0xffffffffu, my_lim_evals, off);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (my_evals) { atomicAdd(&counters[0], my_evals); atomicAdd(&counters[1], my_nodes); }
+        if (my_lim_evals) { atomicAdd(&counters[2], my_lim_evals); atomicAdd(&counters[3], my_lim_nodes); }
+    }
+}
+
+// finalize: chi = PI - 2 (I - I_lim + PI/2) (cpp/Spherical.cpp:269,464), store cos(chi), publish the node as known.
+__global__ void finalize_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes, const WorkEntry* __restrict__ list,
+                                const int* __restrict__ nlist_ptr, double* __restrict__ tab_pool, const double* __restrict__ lim_pool,
+                                unsigned* __restrict__ known_pool, unsigned char* __restrict__ have_lim) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= *nlist_ptr) return;
+    const WorkEntry we = list[e];
+    const Item item = items[we.item];
+    const Regime rg = regimes[item.regime];
+    if (we.ny == LIM_ROW) { have_lim[item.col_off + we.nx] = 1; return; }
+    const long long o = item.tab_off + (long long) we.nx * rg.ny + we.ny;
+    const double I = tab_pool[o];
+    const double th = __dadd_rn(__dsub_rn(I, lim_pool[item.col_off + we.nx]), PI_REF / 2);
+    const double chi = __dsub_rn(PI_REF, __dmul_rn(2.0, th));
+    tab_pool[o] = cos(chi);
+    atomicOr(&known_pool[item.mask_off + (long long) we.nx * rg.nwords + (we.ny >> 5)], 1u << (we.ny & 31));
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// point kernel (kg_chi_points): one lane per (g,b), theta_lim evaluated by the same lane
+// ------------------------------------------------------------------------------------------------------------
+template<int NT>
+__global__ void __launch_bounds__(256) chi_points_kernel(PairParams pp, const double* __restrict__ rows, const double* __restrict__ coeff,
+                                                         double T, int n, const double* __restrict__ g, const double* __restrict__ b,
+                                                         double* __restrict__ chi_out, double* __restrict__ R_out, int* __restrict__ status) {
+    extern __shared__ double srows[];
+    constexpr int W = 2 + NT;
+    for (int i = threadIdx.x; i < KS_ROWS * W; i += blockDim.x) srows[i] = rows[i];
+    __syncthreads();
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    const double gi = g[e], bi = b[e];
+    int st = 0; unsigned nodes = 0;
+    double R = nan(""), chi;
+    if (bi > 100) chi = 0.0;                                  // cpp/Spherical.cpp:462
+    else if (bi < 1e-3) chi = PI_REF;                         // theta = 0 (cpp/Spherical.cpp:267)
+    else {
+        double Rl;
+        const double I = lane_theta_integral<NT>(pp, coeff, srows, rows, KS_ROWS, T, gi, bi, R, nodes, st);
+        const double Il = lane_theta_integral<NT>(pp, coeff, srows, rows, KS_ROWS, T, gi, 100.0, Rl, nodes, st);
+        const double th = __dadd_rn(__dsub_rn(I, Il), PI_REF / 2);
+        chi = __dsub_rn(PI_REF, __dmul_rn(2.0, th));
+    }
+    if (bi <= 100 && bi < 1e-3 && R_out) {
+        // get_R is still defined there (used by the transfer-length integrals)
+        Lane<NT> c;
+        const double E = BOLTZMANN * T * (gi * gi);
+#pragma unroll
+        for (int t = 0; t < NT; t++) {
+            c.Bt[t] = (t < pp.nterms) ? pp.eps * (coeff ? coeff[t] : pp.C[t]) / E : 0.0;
+            c.lam[t] = (t < pp.nterms) ? pp.lam[t] : 1.0;
+        }
+        c.b = bi;
+        R = get_R<NT>(c, gi, st);
+    }
+    if (chi_out) chi_out[e] = chi;
+    if (R_out) R_out[e] = R;
+    if (status) status[e] = st;
+}
+
+// FP64 FMA-pipe probe: 8 independent DFMA chains per thread
+__global__ void __launch_bounds__(256) dfma_probe_kernel(double* out, int iters, double a, double b) {
+    double x0 = threadIdx.x * 1e-3, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+            x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+        }
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
+}
+
+} // namespace
+
+// ================================================================================================================
+// host side
+// ================================================================================================================
+struct kg_model {
+    int device = 0, ncomps = 0, npairs = 0, is_singlecomp = 0, ntpad = 2;
+    std::vector<double> mass;
+    std::vector<kg_potential_desc> descs;
+    std::vector<PairParams> pairs;
+    std::vector<double*> d_rows;        // per pair: [KMAX][2+ntpad]
+    double** d_rows_by_pair = nullptr;
+    PairParams* d_pairs = nullptr;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    int sm_count = 148;
+    void set_error(const std::string& s) { err = s; }
+};
+
+namespace {
+
+void regime_for_T(double T, Regime& R) {
+    // cpp/Spherical.cpp:60-84
+    double end_g = 8, end_b = 5, dg = 0.5, db = 0.03125;
+    int rlg = 4, rlb = 16;
+    if (T < 70) { dg /= 4.; end_g = 6; end_b = 3.5; }
+    if (T < 50) { rlb /= 2; }
+    if (T < 35) { dg /= 2; rlg *= 2; db /= 2; end_g = 3.5; end_b = 3.5; }
+    if (T < 20) { dg /= 2; rlg *= 2; db /= 2; rlb *= 2; }
+    R.dg = dg; R.db = db; R.rlg = rlg; R.rlb = rlb; R.lim = 1e-5;
+    // cpp/Integration/Integration.cpp:290-293
+    R.Nx_end = (int) ((end_g - 1e-7) / dg + 0.5);
+    R.Ny_end = (int) ((end_b - 1e-7) / db + 0.5);
+    R.nx = R.Nx_end + 2 * rlg + 1;
+    R.ny = R.Ny_end + 2 * rlb + 1;
+    R.nwords = (R.ny + 31) / 32;
+}
+int regime_index(double T) { return T < 20 ? 4 : T < 35 ? 3 : T < 50 ? 2 : T < 70 ? 1 : 0; }
+const double REGIME_T[5] = {300.0, 60.0, 40.0, 30.0, 10.0};
+
+// tanh-sinh abscissae/weights with the reference's libm calls (cpp/Integration/Integration.cpp:421-428)
+void build_rows(const kg_potential_desc& d, int ntpad, std::vector<double>& rows) {
+    const double PI = 3.14159265359, h = 1.0e-3;
+    const int W = 2 + ntpad;
+    rows.assign((size_t) KMAX * W, 0.0);
+    for (int k = 1; k <= KMAX; k++) {
+        const double u = tanh(PI * sinh(k * h) / 2.);
+        double w;
+        if (k == 1) w = (PI / 2.) * h * cosh(k * h) / pow(cosh(PI * sinh(k * h * 1e-3) / 2.), 2);   // the 1e-3 quirk, :422
+        else w = (PI / 2) * h * cosh(k * h) / pow(cosh(PI * sinh(k * h) / 2.), 2);
+        double* r = &rows[(size_t) (k - 1) * W];
+        r[0] = w / u;
+        r[1] = 1.0 / (u * u);
+        for (int t = 0; t < ntpad; t++) r[2 + t] = (t < d.nterms) ? pow(u, d.lam[t]) : 0.0;
+    }
+}
+
+template<int NT> cudaError_t set_theta_smem() {
+    const int bytes = KS_ROWS * (2 + NT) * (int) sizeof(double);
+    cudaError_t e = cudaFuncSetAttribute(theta_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(chi_points_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+
+} // namespace
+
+extern "C" const char* kg_last_error(const kg_model* m) { return m ? m->err.c_str() : g_create_error.c_str(); }
+extern "C" int kg_model_npairs(const kg_model* m) { return m ? m->npairs : -1; }
+
+extern "C" int kg_model_create(const kg_potential_desc* pairs, int ncomps, const double* mass, int is_singlecomp, int device, kg_model** out) {
+    auto fail = [&](const std::string& s) { g_create_error = s; return -1; };
+    if (!pairs || !mass || !out || ncomps < 1) return fail("kg_model_create: invalid argument");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail("kg_model_create: no CUDA device (the GPU path has no CPU fallback)");
+    if (device < 0 || device >= ndev) return fail("kg_model_create: bad device ordinal");
+    kg_model* m = new kg_model;
+    m->device = device; m->ncomps = ncomps; m->npairs = ncomps * (ncomps + 1) / 2; m->is_singlecomp = is_singlecomp;
+    m->mass.assign(mass, mass + ncomps);
+    m->descs.assign(pairs, pairs + m->npairs);
+    int ntmax = 0;
+    for (auto& d : m->descs) {
+        if (d.kind != KG_POT_POWER_SUM || d.nterms < 1 || d.nterms > KG_MAX_TERMS) { delete m; return fail("kg_model_create: unsupported potential block"); }
+        ntmax = std::max(ntmax, d.nterms);
+    }
+    m->ntpad = ntmax <= 2 ? 2 : ntmax <= 4 ? 4 : 6;
+    auto cu = [&](cudaError_t e, const char* what) { if (e != cudaSuccess) { g_create_error = std::string(what) + ": " + cudaGetErrorString(e); return false; } return true; };
+    if (!cu(cudaSetDevice(device), "cudaSetDevice")) { delete m; return -2; }
+    cudaDeviceProp prop;
+    if (!cu(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties")) { delete m; return -2; }
+    m->sm_count = prop.multiProcessorCount;
+    if (!cu(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking), "cudaStreamCreate")) { delete m; return -2; }
+    bool ok = cu(set_theta_smem<2>(), "smem attr") && cu(set_theta_smem<4>(), "smem attr") && cu(set_theta_smem<6>(), "smem attr");
+    std::vector<double> rows;
+    for (int p = 0; ok && p < m->npairs; p++) {
+        const auto& d = m->descs[p];
+        PairParams pp; memset(&pp, 0, sizeof(pp));
+        pp.sigma = d.sigma; pp.eps = d.eps; pp.nterms = d.nterms; pp.ntpad = m->ntpad;
+        for (int t = 0; t < d.nterms; t++) { pp.C[t] = d.C[t]; pp.lam[t] = d.lam[t]; }
+        m->pairs.push_back(pp);
+        build_rows(d, m->ntpad, rows);
+        double* dptr = nullptr;
+        ok = ok && cu(cudaMalloc(&dptr, rows.size() * sizeof(double)), "cudaMalloc rows");
+        if (ok) { m->d_rows.push_back(dptr); ok = cu(cudaMemcpy(dptr, rows.data(), rows.size() * sizeof(double), cudaMemcpyHostToDevice), "H2D rows"); }
+    }
+    ok = ok && cu(cudaMalloc(&m->d_rows_by_pair, m->npairs * sizeof(double*)), "cudaMalloc") &&
+         cu(cudaMemcpy(m->d_rows_by_pair, m->d_rows.data(), m->npairs * sizeof(double*), cudaMemcpyHostToDevice), "H2D") &&
+         cu(cudaMalloc(&m->d_pairs, m->npairs * sizeof(PairParams)), "cudaMalloc") &&
+         cu(cudaMemcpy(m->d_pairs, m->pairs.data(), m->npairs * sizeof(PairParams), cudaMemcpyHostToDevice), "H2D");
+    if (!ok) { kg_model_destroy(m); return -2; }
+    *out = m;
+    return 0;
+}
+
+extern "C" void kg_model_destroy(kg_model* m) {
+    if (!m) return;
+    cudaSetDevice(m->device);
+    for (double* p : m->d_rows) cudaFree(p);
+    if (m->d_rows_by_pair) cudaFree(m->d_rows_by_pair);
+    if (m->d_pairs) cudaFree(m->d_pairs);
+    if (m->stream) cudaStreamDestroy(m->stream);
+    delete m;
+}
+
+extern "C" int kg_chi_points(kg_model* m, int pair, double T, int n, const double* g, const double* b_red,
+                             const double* coeff, double* chi_out, double* R_out, int32_t* status) {
+    if (!m) return -1;
+    auto set_error = [&](const std::string& s) { m->err = s; };
+    if (pair < 0 || pair >= m->npairs || n < 0 || !g || !b_red) { set_error("kg_chi_points: invalid argument"); return -1; }
+    if (n == 0) return 0;
+    CUDA_OK(cudaSetDevice(m->device));
+    double *dg = nullptr, *db = nullptr, *dchi = nullptr, *dR = nullptr, *dcoef = nullptr; int* dst = nullptr;
+    CUDA_OK(cudaMalloc(&dg, n * sizeof(double))); CUDA_OK(cudaMalloc(&db, n * sizeof(double)));
+    CUDA_OK(cudaMalloc(&dchi, n * sizeof(double))); CUDA_OK(cudaMalloc(&dR, n * sizeof(double)));
+    CUDA_OK(cudaMalloc(&dst, n * sizeof(int)));
+    CUDA_OK(cudaMemcpyAsync(dg, g, n * sizeof(double), cudaMemcpyHostToDevice, m->stream));
+    CUDA_OK(cudaMemcpyAsync(db, b_red, n * sizeof(double), cudaMemcpyHostToDevice, m->stream));
+    if (coeff) {
+        CUDA_OK(cudaMalloc(&dcoef, KG_MAX_TERMS * sizeof(double)));
+        CUDA_OK(cudaMemcpyAsync(dcoef, coeff, m->descs[pair].nterms * sizeof(double), cudaMemcpyHostToDevice, m->stream));
+    }
+    const int W = 2 + m->ntpad;
+    const size_t smem = (size_t) KS_ROWS * W * sizeof(double);
+    const int grid = (n + 255) / 256;
+    switch (m->ntpad) {
+        case 2: chi_points_kernel<2><<<grid, 256, smem, m->stream>>>(m->pairs[pair], m->d_rows[pair], dcoef, T, n, dg, db, dchi, dR, dst); break;
+        case 4: chi_points_kernel<4><<<grid, 256, smem, m->stream>>>(m->pairs[pair], m->d_rows[pair], dcoef, T, n, dg, db, dchi, dR, dst); break;
+        default: chi_points_kernel<6><<<grid, 256, smem, m->stream>>>(m->pairs[pair], m->d_rows[pair], dcoef, T, n, dg, db, dchi, dR, dst); break;
+    }
+    CUDA_OK(cudaGetLastError());
+    if (chi_out) CUDA_OK(cudaMemcpyAsync(chi_out, dchi, n * sizeof(double), cudaMemcpyDeviceToHost, m->stream));
+    if (R_out) CUDA_OK(cudaMemcpyAsync(R_out, dR, n * sizeof(double), cudaMemcpyDeviceToHost, m->stream));
+    if (status) CUDA_OK(cudaMemcpyAsync(status, dst, n * sizeof(int), cudaMemcpyDeviceToHost, m->stream));
+    CUDA_OK(cudaStreamSynchronize(m->stream));
+    cudaFree(dg); cudaFree(db); cudaFree(dchi); cudaFree(dR); cudaFree(dst); if (dcoef) cudaFree(dcoef);
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------- plan
+struct kg_omega_plan {
+    kg_model* m = nullptr;
+    int nT = 0, nlr = 0, nitems = 0, ntasks = 0, nr_distinct = 0, gfac_stride = 0;
+    long long max_list = 0;
+    std::vector<Item> items;            // sorted by pair
+    std::vector<int> item_out_index;    // item -> iT * npairs + pair
+    Item* d_items = nullptr; Regime* d_regimes = nullptr;
+    double* d_tab = nullptr; unsigned *d_want = nullptr, *d_known = nullptr;
+    double* d_lim = nullptr; unsigned char* d_have_lim = nullptr;
+    int2* d_tasks = nullptr; int *d_counts = nullptr, *d_offsets = nullptr;
+    WorkEntry* d_list = nullptr;
+    double* d_gfac = nullptr; int *d_lr_l = nullptr, *d_lr_ri = nullptr;
+    double* d_coeff = nullptr;
+    double *d_W = nullptr, *d_omega = nullptr;          // [item][lr] in plan order
+    double *d_W_out = nullptr, *d_omega_out = nullptr;  // [nT][npairs][nlr]
+    int *d_status = nullptr, *d_flags = nullptr, *d_tile_counter = nullptr;
+    int* d_perm = nullptr;                              // item -> output slot
+    unsigned long long* d_counters = nullptr;
+    long long tab_doubles = 0, mask_words = 0, ncols_total = 0;
+    double cospi = -1.0;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    double ms_theta = 0, ms_mesh = 0, ms_other = 0; int launches = 0, passes = 0;
+    int* h_pinned = nullptr;   // [0] flag, [1] nlist
+};
+
+namespace {
+__global__ void permute_kernel(const double* __restrict__ W, const double* __restrict__ om, const int* __restrict__ perm, int nitems, int nlr,
+                               double* __restrict__ W_out, double* __restrict__ om_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nitems * nlr) return;
+    const int it = i / nlr, lr = i % nlr;
+    const long long o = (long long) perm[it] * nlr + lr;
+    W_out[o] = W[i];
+    om_out[o] = om[i];
+}
+}
+
+extern "C" int kg_omega_plan_create(kg_model* m, int nT, const double* T, int nlr, const int32_t* l, const int32_t* r,
+                                    const double* coeff_T, kg_omega_plan** out) {
+    if (!m) return -1;
+    auto set_error = [&](const std::string& s) { m->err = s; };
+    if (nT < 1 || !T || nlr < 1 || !l || !r || !out) { set_error("kg_omega_plan_create: invalid argument"); return -1; }
+    for (int i = 0; i < nlr; i++) if (l[i] < 1 || l[i] > 12 || r[i] < 0 || r[i] > 24) { set_error("kg_omega_plan_create: (l,r) out of range"); return -1; }
+    for (int i = 0; i < nT; i++) if (!(T[i] > 0) || !std::isfinite(T[i])) { set_error("kg_omega_plan_create: temperatures must be positive and finite"); return -1; }
+    CUDA_OK(cudaSetDevice(m->device));
+    kg_omega_plan* p = new kg_omega_plan;
+    p->m = m; p->nT = nT; p->nlr = nlr;
+    const int Np = m->npairs;
+    p->nitems = nT * Np;
+    Regime regs[5];
+    for (int k = 0; k < 5; k++) regime_for_T(REGIME_T[k], regs[k]);
+    // items sorted by pair (theta tiles keep one pair's node rows in shared memory), then by T index
+    p->items.reserve(p->nitems);
+    std::vector<int> perm; perm.reserve(p->nitems);
+    const double PI = 3.14159265359, KB = 1.38064852e-23;
+    int pi = 0;
+    for (int i = 0; i < m->ncomps; i++) for (int j = i; j < m->ncomps; j++, pi++) {
+        for (int t = 0; t < nT; t++) {
+            Item it; memset(&it, 0, sizeof(it));
+            it.pair = pi; it.T = T[t]; it.regime = regime_index(T[t]);
+            const double sig = m->descs[pi].sigma;
+            if (i == j) it.pref = pow(sig, 2) * sqrt((PI * KB * T[t]) / m->mass[i]);            // cpp/Spherical.cpp:46
+            else {
+                const double m0 = m->mass[i] + m->mass[j], Mij = m->mass[i] / m0, Mji = m->mass[j] / m0;
+                it.pref = 0.5 * pow(sig, 2) * sqrt(2 * PI * KB * T[t] / (m0 * Mij * Mji));       // cpp/Spherical.cpp:47
+            }
+            const Regime& rg = regs[it.regime];
+            it.tab_off = p->tab_doubles; p->tab_doubles += (long long) rg.nx * rg.ny;
+            it.mask_off = p->mask_words; p->mask_words += (long long) rg.nx * rg.nwords;
+            it.col_off = p->ncols_total; p->ncols_total += rg.nx;
+            it.coeff_off = coeff_T ? (t * Np + pi) * KG_MAX_TERMS : -1;
+            p->items.push_back(it);
+            perm.push_back(t * Np + pi);
+        }
+    }
+    std::vector<int2> tasks; tasks.reserve(p->ncols_total);
+    for (int it = 0; it < p->nitems; it++) {
+        const Regime& rg = regs[p->items[it].regime];
+        for (int nx = 0; nx < rg.nx; nx++) tasks.push_back(make_int2(it, nx));
+        p->max_list += (long long) rg.nx * (rg.ny + 1);
+    }
+    p->ntasks = (int) tasks.size();
+    // g-factor tables 2 exp(-g^2) g^(2r+3) per (regime, distinct r): same libm calls, same order as cpp/Spherical.cpp:101
+    std::vector<int> rvals, lr_ri(nlr);
+    for (int i = 0; i < nlr; i++) {
+        auto f = std::find(rvals.begin(), rvals.end(), r[i]);
+        if (f == rvals.end()) { lr_ri[i] = (int) rvals.size(); rvals.push_back(r[i]); } else lr_ri[i] = (int) (f - rvals.begin());
+    }
+    p->nr_distinct = (int) rvals.size();
+    p->gfac_stride = 160;
+    std::vector<double> gfac((size_t) 5 * p->nr_distinct * p->gfac_stride, 0.0);
+    for (int k = 0; k < 5; k++) for (int ri = 0; ri < p->nr_distinct; ri++) for (int nx = 0; nx < regs[k].nx; nx++) {
+        const double g = 1e-7 + nx * regs[k].dg;
+        gfac[((size_t) k * p->nr_distinct + ri) * p->gfac_stride + nx] = 2 * exp(-pow(g, 2)) * pow(g, 2.0 * rvals[ri] + 3.0);
+    }
+    p->cospi = cos(PI - 2.0 * 0.0);
+    // The worst case list (every node of every lattice) is never reached: nodes in the cut-off region (b>2.5, g>1.5) are
+    // never requested. Cap by the count of requestable nodes.
+    long long cap = 0;
+    for (int it = 0; it < p->nitems; it++) {
+        const Regime& rg = regs[p->items[it].regime];
+        for (int nx = 0; nx < rg.nx; nx++) {
+            const double g = 1e-7 + nx * rg.dg;
+            int nyreq = rg.ny;
+            if (g > 1.5) nyreq = std::min(rg.ny, (int) (2.5 / rg.db) + 2);
+            cap += nyreq + 1;
+        }
+    }
+    p->max_list = cap;
+
+#define PLAN_CUDA(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { set_error(std::string(#expr) + ": " + cudaGetErrorString(e_)); kg_omega_plan_destroy(p); return -2; } } while (0)
+    PLAN_CUDA(cudaMalloc(&p->d_items, p->nitems * sizeof(Item)));
+    PLAN_CUDA(cudaMalloc(&p->d_regimes, 5 * sizeof(Regime)));
+    PLAN_CUDA(cudaMalloc(&p->d_tab, p->tab_doubles * sizeof(double)));
+    PLAN_CUDA(cudaMalloc(&p->d_want, p->mask_words * sizeof(unsigned)));
+    PLAN_CUDA(cudaMalloc(&p->d_known, p->mask_words * sizeof(unsigned)));
+    PLAN_CUDA(cudaMalloc(&p->d_lim, p->ncols_total * sizeof(double)));
+    PLAN_CUDA(cudaMalloc(&p->d_have_lim, p->ncols_total));
+    PLAN_CUDA(cudaMalloc(&p->d_tasks, p->ntasks * sizeof(int2)));
+    PLAN_CUDA(cudaMalloc(&p->d_counts, (p->ntasks + 1) * sizeof(int)));
+    PLAN_CUDA(cudaMalloc(&p->d_offsets, (p->ntasks + 1) * sizeof(int)));
+    PLAN_CUDA(cudaMalloc(&p->d_list, p->max_list * sizeof(WorkEntry)));
+    PLAN_CUDA(cudaMalloc(&p->d_gfac, gfac.size() * sizeof(double)));
+    PLAN_CUDA(cudaMalloc(&p->d_lr_l, nlr * sizeof(int)));
+    PLAN_CUDA(cudaMalloc(&p->d_lr_ri, nlr * sizeof(int)));
+    PLAN_CUDA(cudaMalloc(&p->d_W, (size_t) p->nitems * nlr * sizeof(double)));
+    PLAN_CUDA(cudaMalloc(&p->d_omega, (size_t) p->nitems * nlr * sizeof(double)));
+    PLAN_CUDA(cudaMalloc(&p->d_W_out, (size_t) p->nitems * nlr * sizeof(double)));
+    PLAN_CUDA(cudaMalloc(&p->d_omega_out, (size_t) p->nitems * nlr * sizeof(double)));
+    PLAN_CUDA(cudaMalloc(&p->d_status, p->nitems * sizeof(int)));
+    PLAN_CUDA(cudaMalloc(&p->d_flags, 4 * sizeof(int)));
+    PLAN_CUDA(cudaMalloc(&p->d_tile_counter, sizeof(int)));
+    PLAN_CUDA(cudaMalloc(&p->d_perm, p->nitems * sizeof(int)));
+    PLAN_CUDA(cudaMalloc(&p->d_counters, 8 * sizeof(unsigned long long)));
+    PLAN_CUDA(cudaMallocHost(&p->h_pinned, 4 * sizeof(int)));
+    if (coeff_T) {
+        PLAN_CUDA(cudaMalloc(&p->d_coeff, (size_t) nT * Np * KG_MAX_TERMS * sizeof(double)));
+        PLAN_CUDA(cudaMemcpy(p->d_coeff, coeff_T, (size_t) nT * Np * KG_MAX_TERMS * sizeof(double), cudaMemcpyHostToDevice));
+    }
+    PLAN_CUDA(cudaMemcpy(p->d_items, p->items.data(), p->nitems * sizeof(Item), cudaMemcpyHostToDevice));
+    PLAN_CUDA(cudaMemcpy(p->d_regimes, regs, sizeof(regs), cudaMemcpyHostToDevice));
+    PLAN_CUDA(cudaMemcpy(p->d_tasks, tasks.data(), p->ntasks * sizeof(int2), cudaMemcpyHostToDevice));
+    PLAN_CUDA(cudaMemcpy(p->d_gfac, gfac.data(), gfac.size() * sizeof(double), cudaMemcpyHostToDevice));
+    PLAN_CUDA(cudaMemcpy(p->d_lr_l, l, nlr * sizeof(int), cudaMemcpyHostToDevice));
+    PLAN_CUDA(cudaMemcpy(p->d_lr_ri, lr_ri.data(), nlr * sizeof(int), cudaMemcpyHostToDevice));
+    PLAN_CUDA(cudaMemcpy(p->d_perm, perm.data(), p->nitems * sizeof(int), cudaMemcpyHostToDevice));
+    for (int k = 0; k < 4; k++) PLAN_CUDA(cudaEventCreate(&p->ev[k]));
+#undef PLAN_CUDA
+    *out = p;
+    return 0;
+}
+
+extern "C" void kg_omega_plan_destroy(kg_omega_plan* p) {
+    if (!p) return;
+    cudaSetDevice(p->m->device);
+    void* ptrs[] = {p->d_items, p->d_regimes, p->d_tab, p->d_want, p->d_known, p->d_lim, p->d_have_lim, p->d_tasks, p->d_counts,
+                    p->d_offsets, p->d_list, p->d_gfac, p->d_lr_l, p->d_lr_ri, p->d_coeff, p->d_W, p->d_omega, p->d_W_out,
+                    p->d_omega_out, p->d_status, p->d_flags, p->d_tile_counter, p->d_perm, p->d_counters};
+    for (void* q : ptrs) if (q) cudaFree(q);
+    if (p->h_pinned) cudaFreeHost(p->h_pinned);
+    for (int k = 0; k < 4; k++) if (p->ev[k]) cudaEventDestroy(p->ev[k]);
+    delete p;
+}
+
+extern "C" int kg_omega_plan_run(kg_omega_plan* p) {
+    if (!p) return -1;
+    kg_model* m = p->m;
+    auto set_error = [&](const std::string& s) { m->err = s; };
+    CUDA_OK(cudaSetDevice(m->device));
+    cudaStream_t s = m->stream;
+    CUDA_OK(cudaMemsetAsync(p->d_want, 0, p->mask_words * sizeof(unsigned), s));
+    CUDA_OK(cudaMemsetAsync(p->d_known, 0, p->mask_words * sizeof(unsigned), s));
+    CUDA_OK(cudaMemsetAsync(p->d_have_lim, 0, p->ncols_total, s));
+    CUDA_OK(cudaMemsetAsync(p->d_status, 0, p->nitems * sizeof(int), s));
+    CUDA_OK(cudaMemsetAsync(p->d_counters, 0, 8 * sizeof(unsigned long long), s));
+    p->ms_theta = p->ms_mesh = p->ms_other = 0; p->launches = 0; p->passes = 0;
+    const int W = 2 + m->ntpad;
+    const size_t smem = (size_t) KS_ROWS * W * sizeof(double);
+    const dim3 mesh_grid(p->nlr, p->nitems);
+    const int tgrid = (p->ntasks + 255) / 256;
+    for (int pass = 0; pass < 24; pass++) {
+        p->passes = pass + 1;
+        CUDA_OK(cudaMemsetAsync(p->d_flags, 0, 4 * sizeof(int), s));
+        CUDA_OK(cudaEventRecord(p->ev[0], s));
+        mesh_kernel<<<mesh_grid, 64, 0, s>>>(p->d_items, p->d_regimes, p->d_tab, p->d_known, p->d_want, p->d_gfac, p->d_lr_l, p->d_lr_ri,
+                                            p->nr_distinct, p->gfac_stride, p->cospi, p->nlr, p->d_W, p->d_omega, p->d_flags);
+        CUDA_OK(cudaEventRecord(p->ev[1], s));
+        count_kernel<<<tgrid, 256, 0, s>>>(p->d_items, p->d_regimes, p->d_tasks, p->ntasks, p->d_want, p->d_known, p->d_have_lim, p->d_counts);
+        scan_kernel<<<1, 1024, 0, s>>>(p->d_counts, p->d_offsets, p->ntasks);
+        CUDA_OK(cudaMemcpyAsync(&p->h_pinned[0], p->d_flags, sizeof(int), cudaMemcpyDeviceToHost, s));
+        CUDA_OK(cudaMemcpyAsync(&p->h_pinned[1], p->d_offsets + p->ntasks, sizeof(int), cudaMemcpyDeviceToHost, s));
+        CUDA_OK(cudaStreamSynchronize(s));
+        p->launches += 3;
+        float ms = 0; cudaEventElapsedTime(&ms, p->ev[0], p->ev[1]); p->ms_mesh += ms;
+        const int incomplete = p->h_pinned[0], nlist = p->h_pinned[1];
+        if (!incomplete) break;
+        if (nlist <= 0) { set_error("kg_omega_plan_run: mesh incomplete but no node requested"); return -3; }
+        if (nlist > p->max_list) { set_error("kg_omega_plan_run: work list overflow"); return -3; }
+        fill_kernel<<<tgrid, 256, 0, s>>>(p->d_items, p->d_regimes, p->d_tasks, p->ntasks, p->d_want, p->d_known, p->d_have_lim, p->d_offsets, p->d_list);
+        CUDA_OK(cudaMemsetAsync(p->d_tile_counter, 0, sizeof(int), s));
+        const int ntiles = (nlist + THETA_THREADS - 1) / THETA_THREADS;
+        const int grid = std::min(ntiles, 2 * m->sm_count);
+        CUDA_OK(cudaEventRecord(p->ev[2], s));
+#define LAUNCH_THETA(NT) theta_kernel<NT><<<grid, THETA_THREADS, smem, s>>>(p->d_items, p->d_regimes, m->d_pairs, m->d_rows_by_pair, p->d_coeff, \
+            p->d_list, p->d_offsets + p->ntasks, p->d_tile_counter, p->d_tab, p->d_lim, p->d_status, p->d_counters)
+        switch (m->ntpad) { case 2: LAUNCH_THETA(2); break; case 4: LAUNCH_THETA(4); break; default: LAUNCH_THETA(6); break; }
+#undef LAUNCH_THETA
+        CUDA_OK(cudaEventRecord(p->ev[3], s));
+        finalize_kernel<<<(nlist + 255) / 256, 256, 0, s>>>(p->d_items, p->d_regimes, p->d_list, p->d_offsets + p->ntasks, p->d_tab, p->d_lim,
+                                                           p->d_known, p->d_have_lim);
+        CUDA_OK(cudaGetLastError());
+        CUDA_OK(cudaStreamSynchronize(s));
+        cudaEventElapsedTime(&ms, p->ev[2], p->ev[3]); p->ms_theta += ms;
+        p->launches += 3;
+    }
+    if (p->h_pinned[0]) { set_error("kg_omega_plan_run: refinement did not terminate"); return -3; }
+    permute_kernel<<<(p->nitems * p->nlr + 255) / 256, 256, 0, s>>>(p->d_W, p->d_omega, p->d_perm, p->nitems, p->nlr, p->d_W_out, p->d_omega_out);
+    p->launches += 1;
+    CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int kg_omega_plan_sync(kg_omega_plan* p) {
+    if (!p) return -1;
+    auto set_error = [&](const std::string& s) { p->m->err = s; };
+    CUDA_OK(cudaStreamSynchronize(p->m->stream));
+    return 0;
+}
+
+extern "C" int kg_omega_plan_fetch(kg_omega_plan* p, double* omega, double* w, int32_t* status) {
+    if (!p) return -1;
+    kg_model* m = p->m;
+    auto set_error = [&](const std::string& s) { m->err = s; };
+    const size_t n = (size_t) p->nitems * p->nlr;
+    if (omega) CUDA_OK(cudaMemcpyAsync(omega, p->d_omega_out, n * sizeof(double), cudaMemcpyDeviceToHost, m->stream));
+    if (w) CUDA_OK(cudaMemcpyAsync(w, p->d_W_out, n * sizeof(double), cudaMemcpyDeviceToHost, m->stream));
+    std::vector<int> st;
+    if (status) { st.resize(p->nitems); CUDA_OK(cudaMemcpyAsync(st.data(), p->d_status, p->nitems * sizeof(int), cudaMemcpyDeviceToHost, m->stream)); }
+    CUDA_OK(cudaStreamSynchronize(m->stream));
+    if (status) {
+        // plan order is pair-major; caller order is [nT][npairs]
+        const int Np = m->npairs;
+        for (int pi = 0; pi < Np; pi++) for (int t = 0; t < p->nT; t++) status[t * Np + pi] = st[pi * p->nT + t];
+        if (omega) for (int i = 0; i < p->nitems; i++) for (int k = 0; k < p->nlr; k++) if (!std::isfinite(omega[(size_t) i * p->nlr + k])) status[i] |= KG_STATUS_NAN;
+    }
+    return 0;
+}
+
+extern "C" const double* kg_omega_plan_omega_dev(const kg_omega_plan* p) { return p ? p->d_omega_out : nullptr; }
+
+extern "C" int kg_omega_plan_counters(kg_omega_plan* p, double* out9) {
+    if (!p || !out9) return -1;
+    auto set_error = [&](const std::string& s) { p->m->err = s; };
+    unsigned long long c[8];
+    CUDA_OK(cudaMemcpy(c, p->d_counters, sizeof(c), cudaMemcpyDeviceToHost));
+    out9[0] = (double) c[0]; out9[1] = (double) c[1]; out9[2] = (double) c[2]; out9[3] = (double) c[3];
+    out9[4] = p->ms_theta; out9[5] = 0.0; out9[6] = p->ms_mesh; out9[7] = p->launches; out9[8] = p->passes;
+    return 0;
+}
+
+extern "C" int kg_omega_batch(kg_model* m, int nT, const double* T, int nlr, const int32_t* l, const int32_t* r,
+                              const double* coeff_T, double* omega, double* w, int32_t* status) {
+    kg_omega_plan* p = nullptr;
+    int rc = kg_omega_plan_create(m, nT, T, nlr, l, r, coeff_T, &p);
+    if (rc) return rc;
+    rc = kg_omega_plan_run(p);
+    if (!rc) rc = kg_omega_plan_fetch(p, omega, w, status);
+    kg_omega_plan_destroy(p);
+    return rc;
+}
+
+extern "C" int kg_measure_fp64_peak(int device, double* tflops, double* sm_mhz_est) {
+    if (!tflops) return -1;
+    if (cudaSetDevice(device) != cudaSuccess) return -2;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return -2;
+    const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 4096;
+    double* d = nullptr;
+    if (cudaMalloc(&d, (size_t) blocks * threads * sizeof(double)) != cudaSuccess) return -2;
+    cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
+    double best = 0;
+    for (int rep = 0; rep < 5; rep++) {
+        cudaEventRecord(a);
+        dfma_probe_kernel<<<blocks, threads>>>(d, iters, 0.999999, 1e-9);
+        cudaEventRecord(b);
+        if (cudaEventSynchronize(b) != cudaSuccess) { cudaFree(d); return -2; }
+        float ms = 0; cudaEventElapsedTime(&ms, a, b);
+        const double flops = 2.0 * 64.0 * iters * (double) blocks * threads;
+        best = std::max(best, flops / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(a); cudaEventDestroy(b); cudaFree(d);
+    *tflops = best;
+    if (sm_mhz_est) *sm_mhz_est = best * 1e12 / (2.0 * 64.0 * prop.multiProcessorCount) / 1e6;
+    return 0;
+}

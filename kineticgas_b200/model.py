@@ -1,0 +1,153 @@
+"""Thin object layer over the C-ABI (include/kgcuda.h): a device model (one per KineticGas object) and an
+omega plan (a batched sweep resident in HBM)."""
+import ctypes as C
+import numpy as np
+from . import _lib
+from ._lib import PotentialDesc, dp, ip
+
+STATUS_TEXT = {1: "get_R reached max iter!", 2: "tanh-sinh node table exhausted", 4: "non-finite collision integral"}
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(dp)
+
+
+def _pi(a):
+    return None if a is None else a.ctypes.data_as(ip)
+
+
+def power_sum_desc(sigma, eps, C_, lam):
+    d = PotentialDesc()
+    d.kind = 0
+    d.nterms = len(C_)
+    d.sigma = sigma
+    d.eps = eps
+    for k, (c, l) in enumerate(zip(C_, lam)):
+        d.C[k] = c
+        d.lam[k] = l
+    return d
+
+
+def mie_desc(sigma, eps, la, lr):
+    """Mie block: u = C eps [(sigma/r)^lr - (sigma/r)^la], C as in cpp/MieKinGas.cpp:46-56."""
+    Cm = (lr / (lr - la)) * (lr / la) ** (la / (lr - la))
+    return power_sum_desc(sigma, eps, [Cm, -Cm], [lr, la])
+
+
+class DeviceModel:
+    def __init__(self, descs, masses, is_singlecomp=False, device=0):
+        self.L = _lib.lib()
+        self.ncomps = len(masses)
+        npairs = self.ncomps * (self.ncomps + 1) // 2
+        assert len(descs) == npairs
+        arr = (PotentialDesc * npairs)(*descs)
+        m = np.ascontiguousarray(masses, float)
+        h = C.c_void_p()
+        rc = self.L.kg_model_create(arr, self.ncomps, _p(m), int(is_singlecomp), device, C.byref(h))
+        if rc != 0:
+            raise RuntimeError("kg_model_create failed: " + self.L.kg_last_error(None).decode())
+        self.h = h
+        self.npairs = npairs
+        self.descs = descs
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.kg_model_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _chk(self, rc, what):
+        if rc != 0:
+            raise RuntimeError(f"{what} failed ({rc}): " + self.L.kg_last_error(self.h).decode())
+
+    def pair_index(self, i, j):
+        i, j = min(i, j), max(i, j)
+        return i * self.ncomps - i * (i - 1) // 2 + (j - i)
+
+    def chi_points(self, pair, T, g, b_red, coeff=None, want_R=False):
+        g = np.ascontiguousarray(np.atleast_1d(g), float)
+        b = np.ascontiguousarray(np.atleast_1d(b_red), float)
+        chi, R = np.empty_like(g), np.empty_like(g)
+        st = np.zeros(g.size, np.int32)
+        cf = None if coeff is None else np.ascontiguousarray(coeff, float)
+        self._chk(self.L.kg_chi_points(self.h, pair, float(T), g.size, _p(g), _p(b), _p(cf), _p(chi), _p(R), _pi(st)), "kg_chi_points")
+        raise_on_status(st)
+        return (chi, R) if want_R else chi
+
+    def omega_batch(self, T, l, r, coeff_T=None, want_w=False):
+        T = np.ascontiguousarray(np.atleast_1d(T), float)
+        l = np.ascontiguousarray(l, np.int32)
+        r = np.ascontiguousarray(r, np.int32)
+        om = np.empty((T.size, self.npairs, l.size))
+        w = np.empty_like(om)
+        st = np.zeros((T.size, self.npairs), np.int32)
+        cf = None if coeff_T is None else np.ascontiguousarray(coeff_T, float)
+        self._chk(self.L.kg_omega_batch(self.h, T.size, _p(T), l.size, _pi(l), _pi(r), _p(cf), _p(om), _p(w), _pi(st)), "kg_omega_batch")
+        raise_on_status(st)
+        return (om, w) if want_w else om
+
+    def omega_plan(self, T, l, r, coeff_T=None):
+        return OmegaPlan(self, T, l, r, coeff_T)
+
+
+def raise_on_status(st):
+    bad = int(np.bitwise_or.reduce(np.asarray(st).ravel())) if np.size(st) else 0
+    if bad:
+        msgs = [t for b, t in STATUS_TEXT.items() if bad & b]
+        raise RuntimeError("; ".join(msgs))     # same text as the reference's throw sites (cpp/Spherical.cpp:432)
+
+
+class OmegaPlan:
+    def __init__(self, model, T, l, r, coeff_T=None):
+        self.model = model
+        self.T = np.ascontiguousarray(np.atleast_1d(T), float)
+        self.l = np.ascontiguousarray(l, np.int32)
+        self.r = np.ascontiguousarray(r, np.int32)
+        self.cf = None if coeff_T is None else np.ascontiguousarray(coeff_T, float)
+        h = C.c_void_p()
+        model._chk(model.L.kg_omega_plan_create(model.h, self.T.size, _p(self.T), self.l.size, _pi(self.l), _pi(self.r), _p(self.cf),
+                                                C.byref(h)), "kg_omega_plan_create")
+        self.h = h
+
+    def run(self, sync=True):
+        self.model._chk(self.model.L.kg_omega_plan_run(self.h), "kg_omega_plan_run")
+        if sync:
+            self.model._chk(self.model.L.kg_omega_plan_sync(self.h), "kg_omega_plan_sync")
+
+    def fetch(self, want_w=False):
+        shape = (self.T.size, self.model.npairs, self.l.size)
+        om, w = np.empty(shape), np.empty(shape)
+        st = np.zeros(shape[:2], np.int32)
+        self.model._chk(self.model.L.kg_omega_plan_fetch(self.h, _p(om), _p(w), _pi(st)), "kg_omega_plan_fetch")
+        raise_on_status(st)
+        return (om, w) if want_w else om
+
+    def counters(self):
+        out = np.zeros(9)
+        self.model._chk(self.model.L.kg_omega_plan_counters(self.h, _p(out)), "kg_omega_plan_counters")
+        keys = ["chi_evals", "chi_nodes", "lim_evals", "lim_nodes", "ms_theta", "ms_lim", "ms_mesh", "launches", "passes"]
+        return dict(zip(keys, out.tolist()))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.model.L.kg_omega_plan_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def measure_fp64_peak(device=0):
+    t, f = C.c_double(), C.c_double()
+    rc = _lib.lib().kg_measure_fp64_peak(device, C.byref(t), C.byref(f))
+    if rc != 0:
+        raise RuntimeError("kg_measure_fp64_peak failed (no CUDA device?)")
+    return t.value, f.value

@@ -1,0 +1,43 @@
+"""GPU parity of the chi / Omega kernels (through the C-ABI) against the C oracle (oracle/kg_oracle.c, itself pinned
+bit-exactly to the reference build, tests/test_oracle_vs_reference.py)."""
+import numpy as np
+import pytest
+
+from kineticgas_b200.fluids import mie_parameters, BOLTZMANN, AVOGADRO
+
+pytestmark = pytest.mark.gpu
+
+
+def _model(comp):
+    from kineticgas_b200 import DeviceModel, mie_desc
+    ids, Mw, s, e, la, lr = mie_parameters(comp)
+    return DeviceModel([mie_desc(s[0], e[0] * BOLTZMANN, la[0], lr[0])], [Mw[0] * 1e-3 / AVOGADRO], True), (s[0], e[0] * BOLTZMANN, la[0], lr[0])
+
+
+@pytest.mark.parametrize("comp,T", [("AR", 300.0), ("AR", 40.0), ("CO2", 250.0), ("LJF", 15.0)])
+def test_chi_points_vs_oracle(oracle_port, comp, T):
+    m, (s, eps, la, lr) = _model(comp)
+    p = oracle_port.mie_pair(s, eps, la, lr)
+    rng = np.random.default_rng(1)
+    g = np.concatenate([rng.uniform(0.01, 8, 300), [1e-7, 0.5, 2.0]])
+    b = np.concatenate([rng.uniform(0.002, 5, 300), [0.5, 1e-7, 150.0]])
+    chi_gpu, R_gpu = m.chi_points(0, T, g, b, want_R=True)
+    chi_ref = oracle_port.chi(p, T, g, b * s)
+    R_ref = oracle_port.get_R(p, T, g, b * s) / s
+    ok = b < 100
+    # tolerance: pointwise |chi_gpu - chi_ref| <= 1e-9, R to 1e-10 relative
+    assert np.max(np.abs(chi_gpu - chi_ref)) < 1e-9
+    sel = ok & (b >= 1e-3)
+    assert np.max(np.abs(R_gpu[sel] / R_ref[sel] - 1)) < 1e-10
+
+
+@pytest.mark.parametrize("comp,T", [("AR", 300.0), ("CO2", 250.0), ("AR", 60.0), ("LJF", 45.0)])
+def test_w_integral_vs_oracle(oracle_port, comp, T):
+    m, (s, eps, la, lr) = _model(comp)
+    p = oracle_port.mie_pair(s, eps, la, lr)
+    ls, rs = [1, 1, 2, 3], [1, 4, 2, 3]
+    om, w = m.omega_batch([T], ls, rs, want_w=True)
+    for k, (l, r) in enumerate(zip(ls, rs)):
+        w_ref = oracle_port.w_integral(p, T, l, r)
+        # north_star tolerance: 1e-6 relative on Omega
+        assert abs(w[0, 0, k] / w_ref - 1) < 1e-6, (l, r, w[0, 0, k], w_ref)
