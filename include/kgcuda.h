@@ -44,6 +44,9 @@ int kg_model_create(const kg_potential_desc* pairs, int ncomps, const double* ma
 void kg_model_destroy(kg_model* m);
 const char* kg_last_error(const kg_model* m);   /* m may be NULL: error of the last failed create */
 int kg_model_npairs(const kg_model* m);
+/* Run all work of this model on a caller-owned CUDA stream (cudaStream_t passed as void*), e.g. the host framework's
+ * current stream, so that the caller's events bracket the kernels. */
+int kg_model_set_stream(kg_model* m, void* cuda_stream);
 
 /* Replaces Spherical::chi / Spherical::get_R point calls (cpp/Spherical.cpp:455-465, 358-435; bound at
  * cpp/bindings.cpp:198-199). g dimensionless, b in units of sigma_ij. chi_out / R_out (R in units of sigma) may be NULL.
@@ -68,14 +71,16 @@ int kg_omega_plan_run(kg_omega_plan* p);                  /* asynchronous on the
 int kg_omega_plan_sync(kg_omega_plan* p);
 int kg_omega_plan_fetch(kg_omega_plan* p, double* omega, double* w, int32_t* status);  /* D2H, synchronises */
 const double* kg_omega_plan_omega_dev(const kg_omega_plan* p);   /* device pointer, [nT][npairs][nlr] */
+int kg_omega_plan_export_dev(kg_omega_plan* p, double* omega_dev, double* w_dev);   /* D2D into caller buffers, async on the model stream */
 void kg_omega_plan_destroy(kg_omega_plan* p);
 
 /* Counters of the last run of a plan (algorithmic work and kernel time, for roofline accounting):
  *  out[0] lattice nodes whose chi was evaluated (touched by the adaptive mesh)   out[1] tanh-sinh nodes of those theta integrals
  *  out[2] columns whose theta_lim was evaluated                                   out[3] tanh-sinh nodes of those
  *  out[4] milliseconds in the chi kernel (CUDA events on the model stream)        out[5] ms in the theta_lim kernel
- *  out[6] ms in the mesh kernels          out[7] number of kernel launches        out[8] refinement passes */
-int kg_omega_plan_counters(kg_omega_plan* p, double* out9);
+ *  out[6] ms in the mesh kernels          out[7] number of kernel launches        out[8] refinement passes
+ *  out[9] H2D bytes of plan creation      out[10] D2H bytes of the last fetch     out[11] bytes of lattice + mask pools in HBM */
+int kg_omega_plan_counters(kg_omega_plan* p, double* out12);
 
 /* FP64 FMA-pipe peak probe: runs a register-resident DFMA chain kernel and returns the measured TFLOP/s
  * (2 flop per DFMA). Used as the roofline denominator (MEASURED_PEAKS.json has no FP64 figure). */

@@ -162,52 +162,82 @@ __device__ double get_R(const Lane<NT>& c, double g, int& status) {
     return R;
 }
 
-// One tanh-sinh term from a table row. row = { w/u, 1/u^2, u^lam_0 .. }
-template<int NT>
-__device__ __forceinline__ double ts_term(const double* __restrict__ row, const double (&A)[NT], double c2, double& X) {
-    double P = 1.0;
-#pragma unroll
-    for (int t = 0; t < NT; t++) P = fma(-A[t], row[2 + t], P);
-    X = fma(c2 * row[1], P, -1.0);
-    return row[0] * rsqrt(X);
+// MUFU.RSQ64H seed (max relative error ~2^-22); negative -> NaN, +0 -> +Inf, which is exactly what the stop rule needs
+__device__ __forceinline__ double rsqrt_seed(double x) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    return y;
 }
 
-// Two consecutive nodes (k+1, k+2) evaluated together, then the reference's sequential stop rule applied in order:
-// break on NaN/Inf of the new integrand value (radicand <= 0 or NaN; Integration.cpp:430), stop when
-// |w f / I| <= tol (Integration.cpp:431), otherwise add. Returns true when the sum has terminated.
+#ifndef KG_RSQRT_ORDER
+#define KG_RSQRT_ORDER 3
+#endif
+
+// One tanh-sinh term  w_k f(u_k) = (w_k/u_k) X_k^(-1/2)  from a table row { w/u, 1/u^2, u^lam_0 .. }.
+// Ap[t] = c2 A_t, so X = (1/u^2) (c2 - sum_t Ap_t u^lam_t) - 1 costs NT+1 DFMA. The reciprocal square root is a MUFU
+// seed y0 plus one Householder step on e = 1 - X y0^2, fused with the weight: t = z (1 + e/2 + 3e^2/8), z = (w/u) y0
+// (relative error < 1e-19 for order 3, < 3e-14 for order 2). X <= 0 or NaN gives t = NaN, which fails the stop test.
 template<int NT>
-__device__ __forceinline__ bool ts_step2(const double* __restrict__ ra, const double (&A)[NT], double c2, double& I, int& k) {
+__device__ __forceinline__ double ts_term(const double* __restrict__ row, const double (&Ap)[NT], double c2) {
+    double P = c2;
+#pragma unroll
+    for (int t = 0; t < NT; t++) P = fma(-Ap[t], row[2 + t], P);
+    const double X = fma(row[1], P, -1.0);
+    const double y0 = rsqrt_seed(X);
+    const double e = fma(-X, y0 * y0, 1.0);
+    const double z = row[0] * y0;
+#if KG_RSQRT_ORDER == 3
+    return fma(z * e, fma(e, 0.375, 0.5), z);
+#else
+    return fma(z * e, 0.5, z);
+#endif
+}
+
+// Four consecutive nodes evaluated together (independent chains), then the reference's sequential stop rule applied in
+// order: a term is added only if all earlier ones were and |w f / I| > tol (Integration.cpp:431); NaN/Inf of the new
+// integrand value (radicand <= 0) ends the sum (Integration.cpp:430). J = tol * I is the running sum, scaled so that the
+// test is one compare. k = index of the last node examined (what the reference's loop variable holds at exit).
+template<int NT>
+__device__ __forceinline__ bool ts_step4(const double* __restrict__ r0, const double (&Ap)[NT], double c2, double& J, int& k) {
     constexpr int W = 2 + NT;
-    double Xa, Xb;
-    const double ta = ts_term<NT>(ra, A, c2, Xa);
-    const double tb = ts_term<NT>(ra + W, A, c2, Xb);
-    k += 1;
-    if (!(Xa > 0.0) || !(fabs(ta) > TS_TOL * fabs(I))) return true;
-    I += ta;
-    k += 1;
-    if (!(Xb > 0.0) || !(fabs(tb) > TS_TOL * fabs(I))) return true;
-    I += tb;
-    return false;
+    const double t0 = ts_term<NT>(r0, Ap, c2);
+    const double t1 = ts_term<NT>(r0 + W, Ap, c2);
+    const double t2 = ts_term<NT>(r0 + 2 * W, Ap, c2);
+    const double t3 = ts_term<NT>(r0 + 3 * W, Ap, c2);
+    const double J1 = fma(TS_TOL, t0, J);
+    const double J2 = fma(TS_TOL, t1, J1);
+    const double J3 = fma(TS_TOL, t2, J2);
+    const double J4 = fma(TS_TOL, t3, J3);
+    const bool ok0 = fabs(t0) > fabs(J);
+    const bool ok1 = ok0 && (fabs(t1) > fabs(J1));
+    const bool ok2 = ok1 && (fabs(t2) > fabs(J2));
+    const bool ok3 = ok2 && (fabs(t3) > fabs(J3));
+    if (ok3) { J = J4; k += 4; return false; }
+    J = ok2 ? J3 : ok1 ? J2 : ok0 ? J1 : J;
+    k += 1 + (int) ok0 + (int) ok1 + (int) ok2;
+    return true;
 }
 
 // cpp/Spherical.cpp:321-329 + cpp/Integration/Integration.cpp:417-437, on tabulated nodes.
-// srows: first KS rows in shared memory (KS even); grows: all KMAX rows in global memory. Returns the truncated
-// sum; nodes += k at exit (the value the reference's loop variable reaches). Row j holds node k = j + 1.
+// srows: first KS rows in shared memory; grows: all KMAX rows in global memory. Row j holds node k = j + 1.
+// A[t] = eps C_t (sigma/R)^lam_t / (kT g^2), c2 = (R/b)^2. nodes += k at exit.
 template<int NT>
 __device__ double theta_integral(const double* __restrict__ srows, const double* __restrict__ grows, int KS,
                                  const double (&A)[NT], double c2, unsigned& nodes, int& status) {
     constexpr int W = 2 + NT;
-    double X;
-    double I = ts_term<NT>(srows, A, c2, X);        // k = 1 is added unconditionally (Integration.cpp:425)
+    double Ap[NT];
+#pragma unroll
+    for (int t = 0; t < NT; t++) Ap[t] = c2 * A[t];
+    double J = TS_TOL * ts_term<NT>(srows, Ap, c2);     // k = 1 is added unconditionally (Integration.cpp:425)
     int k = 1;
     bool stop = false;
-    while (!stop && k + 1 < KS) stop = ts_step2<NT>(srows + (size_t) k * W, A, c2, I, k);
+    while (!stop && k + 4 <= KS) stop = ts_step4<NT>(srows + (size_t) k * W, Ap, c2, J, k);
     while (!stop) {
-        if (k + 2 >= KMAX) { status |= 2; break; }
-        stop = ts_step2<NT>(grows + (size_t) k * W, A, c2, I, k);
+        if (k + 4 > KMAX) { status |= 2; break; }
+        stop = ts_step4<NT>(grows + (size_t) k * W, Ap, c2, J, k);
     }
     nodes += (unsigned) k;
-    return I;
+    return J / TS_TOL;
 }
 
 // Full single-lane evaluation of the theta integral for (g, b): R, A_t, c2, then the sum. Returns I; R_out in sigma.

@@ -9,8 +9,9 @@
 // triangulation, recomputing the deflection angle for every (l,r). Here one *item* = (pair, T) owns a lattice of
 // cos(chi) in HBM shared by all (l,r); the adaptive mesh is a decision tree over that lattice and is walked
 // level-synchronously:
-//     mesh_kernel   : one CTA per (item,(l,r)), one thread per coarse cell, DFS of the refinement tree using the
-//                     reference's exact refinement predicate; lattice nodes that are needed but unknown are marked
+//     mesh_level    : one thread per cell of the current refinement level (breadth-first over the tree): the reference's
+//                     exact refinement predicate decides leaf (integrate two triangles) or split (emit the sub-domain
+//                     sweep's cells to the next level and mark the lattice nodes they read)
 //     count/scan/fill: compaction of the newly marked nodes of all items into one work list (sorted by pair, item,
 //                     column, row -> neighbouring lanes integrate neighbouring trajectories)
 //     theta_kernel  : one lane per theta integral (kg_device.cuh), persistent CTAs, 512-node tiles, tanh-sinh rows of
@@ -55,6 +56,7 @@ struct Item {              // one (pair, T)
     long long col_off;     // into the per-column pools (I_lim, have_lim, task index) [nx]
     int coeff_off;         // into coeff pool (doubles) or -1
     int pad;
+    long long cell0_off;   // first coarse cell of this item in the level-0 cell list
 };
 
 struct WorkEntry { int item; unsigned short nx, ny; };
@@ -62,158 +64,180 @@ struct WorkEntry { int item; unsigned short nx, ny; };
 __device__ __forceinline__ double lattice_coord(int n, double d) { return 1e-7 + n * d; }   // cpp/Spherical.cpp:60
 
 // ------------------------------------------------------------------------------------------------------------
-// mesh kernel
+// mesh kernels: the reference's recursive triangulation as a breadth-first walk over cell lists
 // ------------------------------------------------------------------------------------------------------------
+// A cell is one integration_step of the reference (cpp/Integration/Integration.cpp:145-236): entry corner (Nx,Ny), signed
+// x step, y step, owner (item,(l,r)). Packed in 64 bits: [0,26) owner, [26,34) Nx, [34,44) Ny, [44,47) log2|sx|, 47 sx<0,
+// [48,51) log2 sy.
+typedef unsigned long long Cell;
+__host__ __device__ __forceinline__ Cell pack_cell(unsigned owner, int Nx, int Ny, int sx, int sy) {
+    const int ax = sx < 0 ? -sx : sx;
+    unsigned lx = 0, ly = 0;
+    while ((1 << lx) < ax) lx++;
+    while ((1 << ly) < sy) ly++;
+    return (Cell) owner | ((Cell) Nx << 26) | ((Cell) Ny << 34) | ((Cell) lx << 44) | ((Cell) (sx < 0) << 47) | ((Cell) ly << 48);
+}
+
 struct MeshView {
     const double* tab;
-    const unsigned* known;
     unsigned* want;
     const double* gfac;     // [nx] : 2 exp(-g^2) g^(2r+3) for this (regime, r)
     int ny, nwords, l;
     double dg, db, lim, cospi;
-    bool incomplete;
 };
 
-// integrand value at lattice node (Nx,Ny): cpp/Spherical.cpp:96-102. Returns false (and marks the node) if chi is not known yet.
-__device__ __forceinline__ bool mesh_fetch(MeshView& v, int Nx, int Ny, double& f) {
+__device__ __forceinline__ bool node_is_free(const MeshView& v, int Nx, int Ny) {
+    // no chi needed: integrand cut-off (cpp/Spherical.cpp:99) or b/sigma < 1e-3 -> chi = PI (cpp/Spherical.cpp:267)
     const double g = lattice_coord(Nx, v.dg), b = lattice_coord(Ny, v.db);
-    if ((b > 2.5) && (g > 1.5)) { f = 0.0; return true; }
-    double c;
-    if (Ny == 0) c = v.cospi;                 // b/sigma < 1e-3 -> theta = 0 -> chi = PI (cpp/Spherical.cpp:267)
-    else {
-        const int w = Nx * v.nwords + (Ny >> 5);
-        const unsigned bit = 1u << (Ny & 31);
-        if (!(v.known[w] & bit)) {
-            if (!(v.want[w] & bit)) atomicOr(&v.want[w], bit);
-            v.incomplete = true;
-            f = 0.0;
-            return false;
-        }
-        c = v.tab[(long long) Nx * v.ny + Ny];
-    }
+    return ((b > 2.5) && (g > 1.5)) || Ny == 0;
+}
+
+__device__ __forceinline__ void mesh_mark(const MeshView& v, int Nx, int Ny) {
+    if (node_is_free(v, Nx, Ny)) return;
+    const int w = Nx * v.nwords + (Ny >> 5);
+    const unsigned bit = 1u << (Ny & 31);
+    if (!(v.want[w] & bit)) atomicOr(&v.want[w], bit);
+}
+
+// every lattice node a cell reads: the 7 probes of the refinement test (Integration.cpp:159-165) and, for a sweep in -x,
+// the two exit corners of its triangles
+__device__ __forceinline__ void mesh_mark_cell(const MeshView& v, int Nx, int Ny, int sx, int sy) {
+    const int ax = abs(sx);
+    mesh_mark(v, Nx, Ny); mesh_mark(v, Nx + ax, Ny); mesh_mark(v, Nx + 2 * ax, Ny);
+    mesh_mark(v, Nx, Ny + sy); mesh_mark(v, Nx, Ny + 2 * sy);
+    mesh_mark(v, Nx + ax, Ny + sy); mesh_mark(v, Nx + 2 * ax, Ny + 2 * sy);
+    if (sx < 0) { mesh_mark(v, Nx + sx, Ny); mesh_mark(v, Nx + sx, Ny + sy); }
+}
+
+// integrand value at lattice node (Nx,Ny): cpp/Spherical.cpp:96-102 (chi known by construction)
+__device__ __forceinline__ double mesh_fetch(const MeshView& v, int Nx, int Ny) {
+    const double g = lattice_coord(Nx, v.dg), b = lattice_coord(Ny, v.db);
+    if ((b > 2.5) && (g > 1.5)) return 0.0;
+    const double c = (Ny == 0) ? v.cospi : v.tab[(long long) Nx * v.ny + Ny];
     double cl = c;
     for (int i = 1; i < v.l; i++) cl *= c;
-    f = __dmul_rn(__dmul_rn(v.gfac[Nx], __dsub_rn(1.0, cl)), b);
-    return true;
+    return __dmul_rn(__dmul_rn(v.gfac[Nx], __dsub_rn(1.0, cl)), b);
 }
 
-struct Frame { short x0, y0, x1, y1, sx, sy, row, col; };
-
-// One integration_step of the reference (cpp/Integration/Integration.cpp:145-236) at entry corner (Nx,Ny) with signed
-// step sx and step sy. Returns 0 = pending (unknown values), 1 = leaf (integral added), 2 = refine (sub steps set).
-__device__ int mesh_cell(MeshView& v, int Nx, int Ny, int sx, int sy, double& integral, int& sub_sx, int& sub_sy) {
-    const int ax = abs(sx), ay = sy;
-    double f, f1x, f2x, f1y, f2y, f1x1y, f2x2y;
-    bool ok = mesh_fetch(v, Nx, Ny, f);
-    ok &= mesh_fetch(v, Nx + ax, Ny, f1x);
-    ok &= mesh_fetch(v, Nx + 2 * ax, Ny, f2x);
-    ok &= mesh_fetch(v, Nx, Ny + ay, f1y);
-    ok &= mesh_fetch(v, Nx, Ny + 2 * ay, f2y);
-    ok &= mesh_fetch(v, Nx + ax, Ny + ay, f1x1y);
-    ok &= mesh_fetch(v, Nx + 2 * ax, Ny + 2 * ay, f2x2y);
-    if (!ok) return 0;
-    // second-difference estimator, in the reference's operation order, no FMA contraction (decision predicate)
-    const double hx = fabs(v.dg * sx), hy = fabs(v.db * sy);
-    const double hx2 = __dmul_rn(hx, hx), hy2 = __dmul_rn(hy, hy);
-    const double fxx = __dadd_rn(__dsub_rn(f, __dmul_rn(2.0, f1x)), f2x) / hx2;
-    const double fyy = __dadd_rn(__dsub_rn(f, __dmul_rn(2.0, f1y)), f2y) / hy2;
-    double t = __dadd_rn(__dsub_rn(f2x2y, __dmul_rn(2.0, f1x1y)), f);
-    t = __dsub_rn(t, __dmul_rn(hx2, fxx));
-    t = __dsub_rn(t, __dmul_rn(hy2, fyy));
-    const double fxy = t / __dmul_rn(__dmul_rn(2.0, hx), hy);
-    const double dblder = __dadd_rn(__dadd_rn(fabs(fxx), fabs(fyy)), fabs(fxy));
-    const double hs = __dadd_rn(hx, hy);
-    const double hs3 = __dmul_rn(__dmul_rn(hs, hs), hs);
-    if ((__dmul_rn(dblder, hs3) > v.lim) && ((ax > 1) || (ay > 1))) {
-        const double cx = __dmul_rn(fabs(fxx), __dmul_rn(hx2, hx));
-        const double cy = __dmul_rn(fabs(fyy), __dmul_rn(hy2, hy));
-        sub_sx = sx; sub_sy = sy;
-        if (cx > v.lim && (cy < v.lim) && (fabs(fxy) < v.lim) && (ax > 1)) sub_sx = sx / 2;
-        else if (cy > v.lim && (cx < v.lim) && (fabs(fxy) < v.lim) && (ay > 1)) sub_sy = sy / 2;
-        else {
-            if (ax > 1) sub_sx = sx / 2;
-            if (ay > 1) sub_sy = sy / 2;
-        }
-        return 2;
-    }
-    // leaf: the two triangles the sweep adds for this cell, (Eb,Et,Xb) and (Et,Xb,Xt)  (Integration.cpp:218-234);
-    // a linear interpolant integrates to area * mean of the corner values.
-    double fXb, fXt;
-    if (sx > 0) { fXb = f1x; fXt = f1x1y; }
-    else {
-        bool ok2 = mesh_fetch(v, Nx + sx, Ny, fXb);
-        ok2 &= mesh_fetch(v, Nx + sx, Ny + ay, fXt);
-        if (!ok2) return 0;
-    }
-    integral += (hx * hy / 6.0) * (f + 2.0 * f1y + 2.0 * fXb + fXt);
-    return 1;
-}
-
-// grid: (nlr, nitems); block: 64 threads striding over the coarse cells of the item's top-level domain.
-__global__ void __launch_bounds__(64) mesh_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
-                                                  const double* __restrict__ tab_pool, const unsigned* __restrict__ known_pool,
-                                                  unsigned* __restrict__ want_pool, const double* __restrict__ gfac_pool,
-                                                  const int* __restrict__ lr_l, const int* __restrict__ lr_r_index, int nr_distinct,
-                                                  int gfac_stride, double cospi, int nlr,
-                                                  double* __restrict__ W_out, double* __restrict__ omega_out, int* __restrict__ flags) {
-    const int lr = blockIdx.x, it = blockIdx.y;
-    const Item item = items[it];
-    const Regime rg = regimes[item.regime];
+__device__ __forceinline__ MeshView make_view(const Item& item, const Regime& rg, const double* tab_pool, unsigned* want_pool,
+                                              const double* gfac_pool, int nr_distinct, int gfac_stride, int ri, int l, double cospi) {
     MeshView v;
     v.tab = tab_pool + item.tab_off;
-    v.known = known_pool + item.mask_off;
     v.want = want_pool + item.mask_off;
-    v.gfac = gfac_pool + ((long long) item.regime * nr_distinct + lr_r_index[lr]) * gfac_stride;
-    v.ny = rg.ny; v.nwords = rg.nwords; v.l = lr_l[lr];
+    v.gfac = gfac_pool + ((long long) item.regime * nr_distinct + ri) * gfac_stride;
+    v.ny = rg.ny; v.nwords = rg.nwords; v.l = l;
     v.dg = rg.dg; v.db = rg.db; v.lim = rg.lim; v.cospi = cospi;
-    v.incomplete = false;
+    return v;
+}
 
-    const int ncx = rg.Nx_end / rg.rlg, ncy = rg.Ny_end / rg.rlb;
-    double acc = 0.0;
-    Frame stack[12];
-    for (int cell = threadIdx.x; cell < ncx * ncy; cell += blockDim.x) {
-        // top-level sweep (cpp/Integration/Integration.cpp:240-280): row k runs +x for even k, -x for odd k
+// level 0: the coarse cells of every (item,(l,r)) in the reference's sweep order (Integration.cpp:240-280: row k runs +x
+// for even k, -x for odd k) and the lattice nodes they read. grid.x = nitems, block strides over nlr * ncells.
+__global__ void __launch_bounds__(128) mesh_init_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
+                                                        unsigned* __restrict__ want_pool, int nlr, Cell* __restrict__ cells) {
+    const int it = blockIdx.x;
+    const Item item = items[it];
+    const Regime rg = regimes[item.regime];
+    MeshView v = make_view(item, rg, nullptr, want_pool, nullptr, 0, 0, 0, 1, 0.0);
+    const int ncx = rg.Nx_end / rg.rlg, ncy = rg.Ny_end / rg.rlb, nc = ncx * ncy;
+    for (int i = threadIdx.x; i < nc * nlr; i += blockDim.x) {
+        const int lr = i / nc, cell = i % nc;
         const int row = cell / ncx, col = cell % ncx;
-        const int d0 = (row & 1) ? -1 : 1;
-        const int ex0 = ((row & 1) ? rg.Nx_end : 0) + col * d0 * rg.rlg, ey0 = row * rg.rlb;
-        int ssx, ssy, top = 0;
-        int kind = mesh_cell(v, ex0, ey0, d0 * rg.rlg, rg.rlb, acc, ssx, ssy);
-        if (kind == 2) {
-            stack[0] = Frame{(short) ex0, (short) ey0, (short) (ex0 + d0 * rg.rlg), (short) (ey0 + rg.rlb), (short) ssx, (short) ssy, 0, 0};
-            top = 1;
-        }
-        while (top > 0) {
-            Frame& fr = stack[top - 1];
-            const int asx = abs((int) fr.sx);
-            const int ncols = abs(fr.x1 - fr.x0) / asx, nrows = (fr.y1 - fr.y0) / fr.sy;
-            if (fr.row >= nrows) { top--; continue; }
-            const int sgn = (fr.sx > 0) ? 1 : -1;
-            const int d = (fr.row & 1) ? -sgn : sgn;
-            const int ex = ((fr.row & 1) ? fr.x1 : fr.x0) + fr.col * d * asx;
-            const int ey = fr.y0 + fr.row * fr.sy;
-            const int csy = fr.sy;
-            if (++fr.col >= ncols) { fr.col = 0; fr.row++; }
-            kind = mesh_cell(v, ex, ey, d * asx, csy, acc, ssx, ssy);
-            if (kind == 2) {
-                stack[top] = Frame{(short) ex, (short) ey, (short) (ex + d * asx), (short) (ey + csy), (short) ssx, (short) ssy, 0, 0};
-                top++;
+        const int d = (row & 1) ? -1 : 1;
+        const int ex = ((row & 1) ? rg.Nx_end : 0) + col * d * rg.rlg, ey = row * rg.rlb;
+        cells[item.cell0_off + i] = pack_cell((unsigned) (it * nlr + lr), ex, ey, d * rg.rlg, rg.rlb);
+        if (lr == 0) mesh_mark_cell(v, ex, ey, d * rg.rlg, rg.rlb);
+    }
+}
+
+// One level of the refinement tree: every cell of cells_in is either integrated (leaf) or split into the sub-domain sweep
+// of integrate_adaptive (Integration.cpp:172-202) whose cells go to cells_out with their nodes marked.
+__global__ void __launch_bounds__(256) mesh_level_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
+                                                         const double* __restrict__ tab_pool, unsigned* __restrict__ want_pool,
+                                                         const double* __restrict__ gfac_pool, const int* __restrict__ lr_l,
+                                                         const int* __restrict__ lr_r_index, int nr_distinct, int gfac_stride, double cospi,
+                                                         int nlr, const Cell* __restrict__ cells_in, int n_in, Cell* __restrict__ cells_out,
+                                                         int* __restrict__ n_out, int cap_out, double* __restrict__ W, int* __restrict__ flags) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool active = e < n_in;
+    const Cell c = active ? cells_in[e] : 0;
+    const unsigned owner = (unsigned) (c & 0x3FFFFFFu);
+    const int Nx = (int) ((c >> 26) & 0xFF), Ny = (int) ((c >> 34) & 0x3FF);
+    const int ax = 1 << (int) ((c >> 44) & 7), sy = 1 << (int) ((c >> 48) & 7);
+    const int sx = ((c >> 47) & 1) ? -ax : ax;
+    double contrib = 0.0;
+    int nchild = 0, sub_sx = sx, sub_sy = sy;
+    MeshView v;
+    if (active) {
+        const int it = owner / nlr, lr = owner % nlr;
+        const Item item = items[it];
+        const Regime rg = regimes[item.regime];
+        v = make_view(item, rg, tab_pool, want_pool, gfac_pool, nr_distinct, gfac_stride, lr_r_index[lr], lr_l[lr], cospi);
+        const double f = mesh_fetch(v, Nx, Ny), f1x = mesh_fetch(v, Nx + ax, Ny), f2x = mesh_fetch(v, Nx + 2 * ax, Ny);
+        const double f1y = mesh_fetch(v, Nx, Ny + sy), f2y = mesh_fetch(v, Nx, Ny + 2 * sy);
+        const double f1x1y = mesh_fetch(v, Nx + ax, Ny + sy), f2x2y = mesh_fetch(v, Nx + 2 * ax, Ny + 2 * sy);
+        // second-difference estimator in the reference's operation order, no FMA contraction (decision predicate)
+        const double hx = fabs(v.dg * sx), hy = fabs(v.db * sy);
+        const double hx2 = __dmul_rn(hx, hx), hy2 = __dmul_rn(hy, hy);
+        const double fxx = __dadd_rn(__dsub_rn(f, __dmul_rn(2.0, f1x)), f2x) / hx2;
+        const double fyy = __dadd_rn(__dsub_rn(f, __dmul_rn(2.0, f1y)), f2y) / hy2;
+        double t = __dadd_rn(__dsub_rn(f2x2y, __dmul_rn(2.0, f1x1y)), f);
+        t = __dsub_rn(t, __dmul_rn(hx2, fxx));
+        t = __dsub_rn(t, __dmul_rn(hy2, fyy));
+        const double fxy = t / __dmul_rn(__dmul_rn(2.0, hx), hy);
+        const double dblder = __dadd_rn(__dadd_rn(fabs(fxx), fabs(fyy)), fabs(fxy));
+        const double hs = __dadd_rn(hx, hy);
+        const double hs3 = __dmul_rn(__dmul_rn(hs, hs), hs);
+        if ((__dmul_rn(dblder, hs3) > v.lim) && ((ax > 1) || (sy > 1))) {
+            const double cx = __dmul_rn(fabs(fxx), __dmul_rn(hx2, hx));
+            const double cy = __dmul_rn(fabs(fyy), __dmul_rn(hy2, hy));
+            if (cx > v.lim && (cy < v.lim) && (fabs(fxy) < v.lim) && (ax > 1)) sub_sx = sx / 2;
+            else if (cy > v.lim && (cx < v.lim) && (fabs(fxy) < v.lim) && (sy > 1)) sub_sy = sy / 2;
+            else {
+                if (ax > 1) sub_sx = sx / 2;
+                if (sy > 1) sub_sy = sy / 2;
             }
+            nchild = (ax / abs(sub_sx)) * (sy / sub_sy);
+        }
+        else {
+            // leaf: the two triangles the sweep adds for this cell, (Eb,Et,Xb) and (Et,Xb,Xt) (Integration.cpp:218-234);
+            // a linear interpolant integrates to area * mean of its corner values
+            double fXb, fXt;
+            if (sx > 0) { fXb = f1x; fXt = f1x1y; }
+            else { fXb = mesh_fetch(v, Nx + sx, Ny); fXt = mesh_fetch(v, Nx + sx, Ny + sy); }
+            contrib = (hx * hy / 6.0) * (f + 2.0 * f1y + 2.0 * fXb + fXt);
         }
     }
-    __shared__ double part[64];
-    __shared__ int inc;
-    if (threadIdx.x == 0) inc = 0;
-    __syncthreads();
-    part[threadIdx.x] = acc;
-    if (v.incomplete) inc = 1;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double s = 0.0;
-        for (int i = 0; i < blockDim.x; i++) s += part[i];
-        const long long o = (long long) it * nlr + lr;
-        W_out[o] = s;
-        omega_out[o] = item.pref * s;
-        if (inc) flags[0] = 1;
+    // leaf sums: one atomic per warp when the warp belongs to one (item,(l,r)), else one per lane
+    const unsigned full = 0xffffffffu;
+    const unsigned key = active ? owner : 0xffffffffu;
+    const bool uniform = __all_sync(full, key == __shfl_sync(full, key, 0));
+    if (uniform) {
+        double sum = contrib;
+        for (int off = 16; off > 0; off >>= 1) sum += __shfl_down_sync(full, sum, off);
+        if ((threadIdx.x & 31) == 0 && active && sum != 0.0) atomicAdd(&W[owner], sum);
+    }
+    else if (contrib != 0.0) atomicAdd(&W[owner], contrib);
+    // children: warp-aggregated allocation in cells_out
+    int pre = nchild;
+    for (int off = 1; off < 32; off <<= 1) { const int nb = __shfl_up_sync(full, pre, off); if ((threadIdx.x & 31) >= off) pre += nb; }
+    const int warp_total = __shfl_sync(full, pre, 31);
+    int base = 0;
+    if ((threadIdx.x & 31) == 31 && warp_total > 0) base = atomicAdd(n_out, warp_total);
+    base = __shfl_sync(full, base, 31);
+    if (nchild > 0) {
+        int o = base + pre - nchild;
+        if (o + nchild > cap_out) { flags[1] = 1; return; }
+        // sub-domain sweep: origin (Nx,Ny), far corner (Nx+sx, Ny+sy); row k runs in direction sgn for even k, -sgn for odd k
+        const int asx = abs(sub_sx), ncols = ax / asx, nrows = sy / sub_sy, sgn = (sx > 0) ? 1 : -1;
+        for (int k = 0; k < nrows; k++) {
+            const int d = (k & 1) ? -sgn : sgn;
+            const int xs = (k & 1) ? Nx + sx : Nx;
+            for (int j = 0; j < ncols; j++) {
+                const int cxn = xs + j * d * asx, cyn = Ny + k * sub_sy;
+                cells_out[o++] = pack_cell(owner, cxn, cyn, d * asx, sub_sy);
+                mesh_mark_cell(v, cxn, cyn, d * asx, sub_sy);
+            }
+        }
     }
 }
 
@@ -277,56 +301,52 @@ __global__ void fill_kernel(const Item* __restrict__ items, const Regime* __rest
 }
 
 // ------------------------------------------------------------------------------------------------------------
-// theta kernel: one lane per theta integral, persistent CTAs pulling 512-entry tiles
+// theta kernel: one lane per theta integral. Persistent CTAs; the work list is sorted by pair, so a CTA walks the pair
+// segments in order, stages that pair's tanh-sinh rows in shared memory once, and its warps pull 32-entry tiles from
+// the segment's counter independently (no CTA barrier between tiles).
 // ------------------------------------------------------------------------------------------------------------
 template<int NT>
 __global__ void __launch_bounds__(THETA_THREADS, 2)
 theta_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes, const PairParams* __restrict__ pairs,
              const double* const* __restrict__ rows_by_pair, const double* __restrict__ coeff_pool,
-             const WorkEntry* __restrict__ list, const int* __restrict__ nlist_ptr, int* __restrict__ tile_counter,
-             double* __restrict__ tab_pool, double* __restrict__ lim_pool, int* __restrict__ status_pool,
+             const WorkEntry* __restrict__ list, const int* __restrict__ offsets, const int* __restrict__ pair_task_start, int npairs,
+             int* __restrict__ tile_counters, double* __restrict__ tab_pool, double* __restrict__ lim_pool, int* __restrict__ status_pool,
              unsigned long long* __restrict__ counters) {
     extern __shared__ double srows[];
     __shared__ PairParams spair;
-    __shared__ int s_tile, s_pair_loaded;
     constexpr int W = 2 + NT;
-    const int nlist = *nlist_ptr;
-    const int ntiles = (nlist + THETA_THREADS - 1) / THETA_THREADS;
-    if (threadIdx.x == 0) s_pair_loaded = -1;
+    const int lane = threadIdx.x & 31;
     unsigned long long my_nodes = 0, my_evals = 0, my_lim_nodes = 0, my_lim_evals = 0;
-    for (;;) {
+    for (int p = 0; p < npairs; p++) {
+        const int seg0 = offsets[pair_task_start[p]], seg1 = offsets[pair_task_start[p + 1]];
+        if (seg1 == seg0) continue;
+        __syncthreads();                                   // previous pair's rows no longer in use
+        const double* grows = rows_by_pair[p];
+        for (int i = threadIdx.x; i < KS_ROWS * W; i += THETA_THREADS) srows[i] = grows[i];
+        if (threadIdx.x == 0) spair = pairs[p];
         __syncthreads();
-        if (threadIdx.x == 0) s_tile = atomicAdd(tile_counter, 1);
-        __syncthreads();
-        const int tile = s_tile;
-        if (tile >= ntiles) break;
-        const int e = tile * THETA_THREADS + threadIdx.x;
-        const bool active = e < nlist;
-        WorkEntry we = active ? list[e] : WorkEntry{0, 0, 0};
-        Item item = items[we.item];
-        // the list is sorted by pair: a tile spans pairs [p_first, p_last]
-        const int p_first = items[list[tile * THETA_THREADS].item].pair;
-        const int p_last = items[list[min(nlist, (tile + 1) * THETA_THREADS) - 1].item].pair;
-        for (int p = p_first; p <= p_last; p++) {
-            if (s_pair_loaded != p) {
-                __syncthreads();
-                const double* src = rows_by_pair[p];
-                for (int i = threadIdx.x; i < KS_ROWS * W; i += THETA_THREADS) srows[i] = src[i];
-                if (threadIdx.x == 0) { spair = pairs[p]; s_pair_loaded = p; }
-                __syncthreads();
-            }
-            if (active && item.pair == p) {
+        const int ntiles = (seg1 - seg0 + 31) / 32;
+        for (;;) {
+            int tile = 0;
+            if (lane == 0) tile = atomicAdd(&tile_counters[p], 1);
+            tile = __shfl_sync(0xffffffffu, tile, 0);
+            if (tile >= ntiles) break;
+            const int e = seg0 + tile * 32 + lane;
+            if (e < seg1) {
+                const WorkEntry we = list[e];
+                const Item item = items[we.item];
                 const Regime rg = regimes[item.regime];
                 const double g = lattice_coord(we.nx, rg.dg);
                 const bool is_lim = (we.ny == LIM_ROW);
                 const double b = is_lim ? 100.0 : lattice_coord(we.ny, rg.db);   // theta_lim: b = 100 sigma (Spherical.cpp:316)
                 const double* coeff = (item.coeff_off >= 0) ? coeff_pool + item.coeff_off : nullptr;
                 double R; unsigned nodes = 0; int st = 0;
-                const double I = lane_theta_integral<NT>(spair, coeff, srows, rows_by_pair[p], KS_ROWS, item.T, g, b, R, nodes, st);
+                const double I = lane_theta_integral<NT>(spair, coeff, srows, grows, KS_ROWS, item.T, g, b, R, nodes, st);
                 if (is_lim) { lim_pool[item.col_off + we.nx] = I; my_lim_nodes += nodes; my_lim_evals++; }
                 else { tab_pool[item.tab_off + (long long) we.nx * rg.ny + we.ny] = I; my_nodes += nodes; my_evals++; }
                 if (st) atomicOr(&status_pool[we.item], st);
             }
+            __syncwarp();
         }
     }
     // counters: [0] chi evals [1] chi nodes [2] lim evals [3] lim nodes
@@ -336,7 +356,7 @@ theta_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
         my_lim_nodes += __shfl_down_sync(0xffffffffu, my_lim_nodes, off);
         my_lim_evals += __shfl_down_sync(0xffffffffu, my_lim_evals, off);
     }
-    if ((threadIdx.x & 31) == 0) {
+    if (lane == 0) {
         if (my_evals) { atomicAdd(&counters[0], my_evals); atomicAdd(&counters[1], my_nodes); }
         if (my_lim_evals) { atomicAdd(&counters[2], my_lim_evals); atomicAdd(&counters[3], my_lim_nodes); }
     }
@@ -429,6 +449,7 @@ struct kg_model {
     double** d_rows_by_pair = nullptr;
     PairParams* d_pairs = nullptr;
     cudaStream_t stream = nullptr;
+    bool own_stream = true;
     std::string err;
     int sm_count = 148;
     void set_error(const std::string& s) { err = s; }
@@ -534,8 +555,17 @@ extern "C" void kg_model_destroy(kg_model* m) {
     for (double* p : m->d_rows) cudaFree(p);
     if (m->d_rows_by_pair) cudaFree(m->d_rows_by_pair);
     if (m->d_pairs) cudaFree(m->d_pairs);
-    if (m->stream) cudaStreamDestroy(m->stream);
+    if (m->stream && m->own_stream) cudaStreamDestroy(m->stream);
     delete m;
+}
+
+extern "C" int kg_model_set_stream(kg_model* m, void* stream) {
+    if (!m) return -1;
+    cudaSetDevice(m->device);
+    if (m->stream && m->own_stream) { cudaStreamSynchronize(m->stream); cudaStreamDestroy(m->stream); }
+    m->stream = (cudaStream_t) stream;
+    m->own_stream = false;
+    return 0;
 }
 
 extern "C" int kg_chi_points(kg_model* m, int pair, double T, int n, const double* g, const double* b_red,
@@ -587,26 +617,29 @@ struct kg_omega_plan {
     double* d_gfac = nullptr; int *d_lr_l = nullptr, *d_lr_ri = nullptr;
     double* d_coeff = nullptr;
     double *d_W = nullptr, *d_omega = nullptr;          // [item][lr] in plan order
+    Cell* d_cells[2] = {nullptr, nullptr}; int* d_ncells = nullptr; long long cell_cap = 0, ncells0 = 0;
     double *d_W_out = nullptr, *d_omega_out = nullptr;  // [nT][npairs][nlr]
     int *d_status = nullptr, *d_flags = nullptr, *d_tile_counter = nullptr;
     int* d_perm = nullptr;                              // item -> output slot
+    int* d_pair_task_start = nullptr;                   // [npairs+1] first column task of each pair
     unsigned long long* d_counters = nullptr;
     long long tab_doubles = 0, mask_words = 0, ncols_total = 0;
     double cospi = -1.0;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     double ms_theta = 0, ms_mesh = 0, ms_other = 0; int launches = 0, passes = 0;
+    long long h2d_bytes = 0, d2h_bytes = 0;
     int* h_pinned = nullptr;   // [0] flag, [1] nlist
 };
 
 namespace {
-__global__ void permute_kernel(const double* __restrict__ W, const double* __restrict__ om, const int* __restrict__ perm, int nitems, int nlr,
+__global__ void permute_kernel(const double* __restrict__ W, const Item* __restrict__ items, const int* __restrict__ perm, int nitems, int nlr,
                                double* __restrict__ W_out, double* __restrict__ om_out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nitems * nlr) return;
     const int it = i / nlr, lr = i % nlr;
     const long long o = (long long) perm[it] * nlr + lr;
     W_out[o] = W[i];
-    om_out[o] = om[i];
+    om_out[o] = items[it].pref * W[i];     // cpp/Spherical.cpp:46-47
 }
 }
 
@@ -644,6 +677,9 @@ extern "C" int kg_omega_plan_create(kg_model* m, int nT, const double* T, int nl
             it.mask_off = p->mask_words; p->mask_words += (long long) rg.nx * rg.nwords;
             it.col_off = p->ncols_total; p->ncols_total += rg.nx;
             it.coeff_off = coeff_T ? (t * Np + pi) * KG_MAX_TERMS : -1;
+            it.cell0_off = p->ncells0;
+            p->ncells0 += (long long) nlr * (rg.Nx_end / rg.rlg) * (rg.Ny_end / rg.rlb);
+            p->cell_cap += (long long) nlr * rg.Nx_end * rg.Ny_end;     // cells of one level tile (part of) the domain
             p->items.push_back(it);
             perm.push_back(t * Np + pi);
         }
@@ -655,6 +691,9 @@ extern "C" int kg_omega_plan_create(kg_model* m, int nT, const double* T, int nl
         p->max_list += (long long) rg.nx * (rg.ny + 1);
     }
     p->ntasks = (int) tasks.size();
+    std::vector<int> pair_task_start(Np + 1, p->ntasks);
+    for (int t = p->ntasks - 1; t >= 0; t--) pair_task_start[p->items[tasks[t].x].pair] = t;
+    for (int q = Np - 1; q >= 0; q--) if (pair_task_start[q] > pair_task_start[q + 1]) pair_task_start[q] = pair_task_start[q + 1];
     // g-factor tables 2 exp(-g^2) g^(2r+3) per (regime, distinct r): same libm calls, same order as cpp/Spherical.cpp:101
     std::vector<int> rvals, lr_ri(nlr);
     for (int i = 0; i < nlr; i++) {
@@ -698,16 +737,22 @@ extern "C" int kg_omega_plan_create(kg_model* m, int nT, const double* T, int nl
     PLAN_CUDA(cudaMalloc(&p->d_gfac, gfac.size() * sizeof(double)));
     PLAN_CUDA(cudaMalloc(&p->d_lr_l, nlr * sizeof(int)));
     PLAN_CUDA(cudaMalloc(&p->d_lr_ri, nlr * sizeof(int)));
+    if ((long long) p->nitems * nlr >= (1LL << 26) || p->cell_cap >= (1LL << 31)) { set_error("kg_omega_plan_create: batch too large, split the T grid"); kg_omega_plan_destroy(p); return -1; }
+    PLAN_CUDA(cudaMalloc(&p->d_cells[0], p->cell_cap * sizeof(Cell)));
+    PLAN_CUDA(cudaMalloc(&p->d_cells[1], p->cell_cap * sizeof(Cell)));
+    PLAN_CUDA(cudaMalloc(&p->d_ncells, 2 * sizeof(int)));
     PLAN_CUDA(cudaMalloc(&p->d_W, (size_t) p->nitems * nlr * sizeof(double)));
     PLAN_CUDA(cudaMalloc(&p->d_omega, (size_t) p->nitems * nlr * sizeof(double)));
     PLAN_CUDA(cudaMalloc(&p->d_W_out, (size_t) p->nitems * nlr * sizeof(double)));
     PLAN_CUDA(cudaMalloc(&p->d_omega_out, (size_t) p->nitems * nlr * sizeof(double)));
     PLAN_CUDA(cudaMalloc(&p->d_status, p->nitems * sizeof(int)));
     PLAN_CUDA(cudaMalloc(&p->d_flags, 4 * sizeof(int)));
-    PLAN_CUDA(cudaMalloc(&p->d_tile_counter, sizeof(int)));
+    PLAN_CUDA(cudaMalloc(&p->d_tile_counter, (Np + 1) * sizeof(int)));
+    PLAN_CUDA(cudaMalloc(&p->d_pair_task_start, (Np + 1) * sizeof(int)));
+    PLAN_CUDA(cudaMemcpy(p->d_pair_task_start, pair_task_start.data(), (Np + 1) * sizeof(int), cudaMemcpyHostToDevice));
     PLAN_CUDA(cudaMalloc(&p->d_perm, p->nitems * sizeof(int)));
     PLAN_CUDA(cudaMalloc(&p->d_counters, 8 * sizeof(unsigned long long)));
-    PLAN_CUDA(cudaMallocHost(&p->h_pinned, 4 * sizeof(int)));
+    PLAN_CUDA(cudaMallocHost(&p->h_pinned, 8 * sizeof(int)));
     if (coeff_T) {
         PLAN_CUDA(cudaMalloc(&p->d_coeff, (size_t) nT * Np * KG_MAX_TERMS * sizeof(double)));
         PLAN_CUDA(cudaMemcpy(p->d_coeff, coeff_T, (size_t) nT * Np * KG_MAX_TERMS * sizeof(double), cudaMemcpyHostToDevice));
@@ -720,6 +765,8 @@ extern "C" int kg_omega_plan_create(kg_model* m, int nT, const double* T, int nl
     PLAN_CUDA(cudaMemcpy(p->d_lr_ri, lr_ri.data(), nlr * sizeof(int), cudaMemcpyHostToDevice));
     PLAN_CUDA(cudaMemcpy(p->d_perm, perm.data(), p->nitems * sizeof(int), cudaMemcpyHostToDevice));
     for (int k = 0; k < 4; k++) PLAN_CUDA(cudaEventCreate(&p->ev[k]));
+    p->h2d_bytes = (long long) p->nitems * sizeof(Item) + sizeof(regs) + (long long) p->ntasks * sizeof(int2) + gfac.size() * sizeof(double)
+                 + 2LL * nlr * sizeof(int) + (long long) p->nitems * sizeof(int) + (coeff_T ? (long long) nT * Np * KG_MAX_TERMS * sizeof(double) : 0);
 #undef PLAN_CUDA
     *out = p;
     return 0;
@@ -730,7 +777,7 @@ extern "C" void kg_omega_plan_destroy(kg_omega_plan* p) {
     cudaSetDevice(p->m->device);
     void* ptrs[] = {p->d_items, p->d_regimes, p->d_tab, p->d_want, p->d_known, p->d_lim, p->d_have_lim, p->d_tasks, p->d_counts,
                     p->d_offsets, p->d_list, p->d_gfac, p->d_lr_l, p->d_lr_ri, p->d_coeff, p->d_W, p->d_omega, p->d_W_out,
-                    p->d_omega_out, p->d_status, p->d_flags, p->d_tile_counter, p->d_perm, p->d_counters};
+                    p->d_omega_out, p->d_status, p->d_flags, p->d_tile_counter, p->d_perm, p->d_counters, p->d_cells[0], p->d_cells[1], p->d_ncells, p->d_pair_task_start};
     for (void* q : ptrs) if (q) cudaFree(q);
     if (p->h_pinned) cudaFreeHost(p->h_pinned);
     for (int k = 0; k < 4; k++) if (p->ev[k]) cudaEventDestroy(p->ev[k]);
@@ -749,47 +796,64 @@ extern "C" int kg_omega_plan_run(kg_omega_plan* p) {
     CUDA_OK(cudaMemsetAsync(p->d_status, 0, p->nitems * sizeof(int), s));
     CUDA_OK(cudaMemsetAsync(p->d_counters, 0, 8 * sizeof(unsigned long long), s));
     p->ms_theta = p->ms_mesh = p->ms_other = 0; p->launches = 0; p->passes = 0;
+    CUDA_OK(cudaMemsetAsync(p->d_W, 0, (size_t) p->nitems * p->nlr * sizeof(double), s));
+    CUDA_OK(cudaMemsetAsync(p->d_flags, 0, 4 * sizeof(int), s));
     const int W = 2 + m->ntpad;
     const size_t smem = (size_t) KS_ROWS * W * sizeof(double);
-    const dim3 mesh_grid(p->nlr, p->nitems);
     const int tgrid = (p->ntasks + 255) / 256;
-    for (int pass = 0; pass < 24; pass++) {
+    CUDA_OK(cudaEventRecord(p->ev[0], s));
+    mesh_init_kernel<<<p->nitems, 128, 0, s>>>(p->d_items, p->d_regimes, p->d_want, p->nlr, p->d_cells[0]);
+    CUDA_OK(cudaEventRecord(p->ev[1], s));
+    p->launches += 1;
+    long long n_in = p->ncells0;
+    int cur = 0;
+    float ms = 0;
+    for (int pass = 0; pass < 32 && n_in > 0; pass++) {
         p->passes = pass + 1;
-        CUDA_OK(cudaMemsetAsync(p->d_flags, 0, 4 * sizeof(int), s));
-        CUDA_OK(cudaEventRecord(p->ev[0], s));
-        mesh_kernel<<<mesh_grid, 64, 0, s>>>(p->d_items, p->d_regimes, p->d_tab, p->d_known, p->d_want, p->d_gfac, p->d_lr_l, p->d_lr_ri,
-                                            p->nr_distinct, p->gfac_stride, p->cospi, p->nlr, p->d_W, p->d_omega, p->d_flags);
-        CUDA_OK(cudaEventRecord(p->ev[1], s));
+        // 1. theta integrals of every newly marked lattice node
         count_kernel<<<tgrid, 256, 0, s>>>(p->d_items, p->d_regimes, p->d_tasks, p->ntasks, p->d_want, p->d_known, p->d_have_lim, p->d_counts);
         scan_kernel<<<1, 1024, 0, s>>>(p->d_counts, p->d_offsets, p->ntasks);
-        CUDA_OK(cudaMemcpyAsync(&p->h_pinned[0], p->d_flags, sizeof(int), cudaMemcpyDeviceToHost, s));
         CUDA_OK(cudaMemcpyAsync(&p->h_pinned[1], p->d_offsets + p->ntasks, sizeof(int), cudaMemcpyDeviceToHost, s));
         CUDA_OK(cudaStreamSynchronize(s));
-        p->launches += 3;
-        float ms = 0; cudaEventElapsedTime(&ms, p->ev[0], p->ev[1]); p->ms_mesh += ms;
-        const int incomplete = p->h_pinned[0], nlist = p->h_pinned[1];
-        if (!incomplete) break;
-        if (nlist <= 0) { set_error("kg_omega_plan_run: mesh incomplete but no node requested"); return -3; }
+        cudaEventElapsedTime(&ms, p->ev[0], p->ev[1]); p->ms_mesh += ms;
+        p->launches += 2;
+        const int nlist = p->h_pinned[1];
         if (nlist > p->max_list) { set_error("kg_omega_plan_run: work list overflow"); return -3; }
-        fill_kernel<<<tgrid, 256, 0, s>>>(p->d_items, p->d_regimes, p->d_tasks, p->ntasks, p->d_want, p->d_known, p->d_have_lim, p->d_offsets, p->d_list);
-        CUDA_OK(cudaMemsetAsync(p->d_tile_counter, 0, sizeof(int), s));
-        const int ntiles = (nlist + THETA_THREADS - 1) / THETA_THREADS;
-        const int grid = std::min(ntiles, 2 * m->sm_count);
-        CUDA_OK(cudaEventRecord(p->ev[2], s));
+        if (nlist > 0) {
+            fill_kernel<<<tgrid, 256, 0, s>>>(p->d_items, p->d_regimes, p->d_tasks, p->ntasks, p->d_want, p->d_known, p->d_have_lim, p->d_offsets, p->d_list);
+            CUDA_OK(cudaMemsetAsync(p->d_tile_counter, 0, (m->npairs + 1) * sizeof(int), s));
+            const int ntiles = (nlist + THETA_THREADS - 1) / THETA_THREADS;
+            const int grid = std::min(ntiles, 2 * m->sm_count);
+            CUDA_OK(cudaEventRecord(p->ev[2], s));
 #define LAUNCH_THETA(NT) theta_kernel<NT><<<grid, THETA_THREADS, smem, s>>>(p->d_items, p->d_regimes, m->d_pairs, m->d_rows_by_pair, p->d_coeff, \
-            p->d_list, p->d_offsets + p->ntasks, p->d_tile_counter, p->d_tab, p->d_lim, p->d_status, p->d_counters)
-        switch (m->ntpad) { case 2: LAUNCH_THETA(2); break; case 4: LAUNCH_THETA(4); break; default: LAUNCH_THETA(6); break; }
+                p->d_list, p->d_offsets, p->d_pair_task_start, m->npairs, p->d_tile_counter, p->d_tab, p->d_lim, p->d_status, p->d_counters)
+            switch (m->ntpad) { case 2: LAUNCH_THETA(2); break; case 4: LAUNCH_THETA(4); break; default: LAUNCH_THETA(6); break; }
 #undef LAUNCH_THETA
-        CUDA_OK(cudaEventRecord(p->ev[3], s));
-        finalize_kernel<<<(nlist + 255) / 256, 256, 0, s>>>(p->d_items, p->d_regimes, p->d_list, p->d_offsets + p->ntasks, p->d_tab, p->d_lim,
-                                                           p->d_known, p->d_have_lim);
+            CUDA_OK(cudaEventRecord(p->ev[3], s));
+            finalize_kernel<<<(nlist + 255) / 256, 256, 0, s>>>(p->d_items, p->d_regimes, p->d_list, p->d_offsets + p->ntasks, p->d_tab, p->d_lim,
+                                                               p->d_known, p->d_have_lim);
+            p->launches += 3;
+        }
+        // 2. evaluate this level's cells, emit the next level
+        CUDA_OK(cudaMemsetAsync(p->d_ncells, 0, sizeof(int), s));
+        CUDA_OK(cudaEventRecord(p->ev[0], s));
+        mesh_level_kernel<<<(unsigned) ((n_in + 255) / 256), 256, 0, s>>>(p->d_items, p->d_regimes, p->d_tab, p->d_want, p->d_gfac, p->d_lr_l, p->d_lr_ri,
+            p->nr_distinct, p->gfac_stride, p->cospi, p->nlr, p->d_cells[cur], (int) n_in, p->d_cells[cur ^ 1], p->d_ncells, (int) p->cell_cap,
+            p->d_W, p->d_flags);
+        CUDA_OK(cudaEventRecord(p->ev[1], s));
+        CUDA_OK(cudaMemcpyAsync(&p->h_pinned[2], p->d_ncells, sizeof(int), cudaMemcpyDeviceToHost, s));
+        CUDA_OK(cudaMemcpyAsync(&p->h_pinned[0], p->d_flags, 2 * sizeof(int), cudaMemcpyDeviceToHost, s));
         CUDA_OK(cudaGetLastError());
         CUDA_OK(cudaStreamSynchronize(s));
-        cudaEventElapsedTime(&ms, p->ev[2], p->ev[3]); p->ms_theta += ms;
-        p->launches += 3;
+        if (nlist > 0) { cudaEventElapsedTime(&ms, p->ev[2], p->ev[3]); p->ms_theta += ms; }
+        p->launches += 1;
+        if (p->h_pinned[1]) { set_error("kg_omega_plan_run: cell list overflow"); return -3; }
+        n_in = p->h_pinned[2];
+        cur ^= 1;
     }
-    if (p->h_pinned[0]) { set_error("kg_omega_plan_run: refinement did not terminate"); return -3; }
-    permute_kernel<<<(p->nitems * p->nlr + 255) / 256, 256, 0, s>>>(p->d_W, p->d_omega, p->d_perm, p->nitems, p->nlr, p->d_W_out, p->d_omega_out);
+    cudaEventElapsedTime(&ms, p->ev[0], p->ev[1]); p->ms_mesh += ms;
+    if (n_in > 0) { set_error("kg_omega_plan_run: refinement did not terminate"); return -3; }
+    permute_kernel<<<(p->nitems * p->nlr + 255) / 256, 256, 0, s>>>(p->d_W, p->d_items, p->d_perm, p->nitems, p->nlr, p->d_W_out, p->d_omega_out);
     p->launches += 1;
     CUDA_OK(cudaGetLastError());
     return 0;
@@ -812,6 +876,7 @@ extern "C" int kg_omega_plan_fetch(kg_omega_plan* p, double* omega, double* w, i
     std::vector<int> st;
     if (status) { st.resize(p->nitems); CUDA_OK(cudaMemcpyAsync(st.data(), p->d_status, p->nitems * sizeof(int), cudaMemcpyDeviceToHost, m->stream)); }
     CUDA_OK(cudaStreamSynchronize(m->stream));
+    p->d2h_bytes = (omega ? n * sizeof(double) : 0) + (w ? n * sizeof(double) : 0) + (status ? p->nitems * sizeof(int) : 0);
     if (status) {
         // plan order is pair-major; caller order is [nT][npairs]
         const int Np = m->npairs;
@@ -823,6 +888,15 @@ extern "C" int kg_omega_plan_fetch(kg_omega_plan* p, double* omega, double* w, i
 
 extern "C" const double* kg_omega_plan_omega_dev(const kg_omega_plan* p) { return p ? p->d_omega_out : nullptr; }
 
+extern "C" int kg_omega_plan_export_dev(kg_omega_plan* p, double* omega_dev, double* w_dev) {
+    if (!p) return -1;
+    auto set_error = [&](const std::string& s) { p->m->err = s; };
+    const size_t n = (size_t) p->nitems * p->nlr;
+    if (omega_dev) CUDA_OK(cudaMemcpyAsync(omega_dev, p->d_omega_out, n * sizeof(double), cudaMemcpyDeviceToDevice, p->m->stream));
+    if (w_dev) CUDA_OK(cudaMemcpyAsync(w_dev, p->d_W_out, n * sizeof(double), cudaMemcpyDeviceToDevice, p->m->stream));
+    return 0;
+}
+
 extern "C" int kg_omega_plan_counters(kg_omega_plan* p, double* out9) {
     if (!p || !out9) return -1;
     auto set_error = [&](const std::string& s) { p->m->err = s; };
@@ -830,6 +904,8 @@ extern "C" int kg_omega_plan_counters(kg_omega_plan* p, double* out9) {
     CUDA_OK(cudaMemcpy(c, p->d_counters, sizeof(c), cudaMemcpyDeviceToHost));
     out9[0] = (double) c[0]; out9[1] = (double) c[1]; out9[2] = (double) c[2]; out9[3] = (double) c[3];
     out9[4] = p->ms_theta; out9[5] = 0.0; out9[6] = p->ms_mesh; out9[7] = p->launches; out9[8] = p->passes;
+    out9[9] = (double) p->h2d_bytes; out9[10] = (double) p->d2h_bytes;
+    out9[11] = (double) (p->tab_doubles * 8 + p->mask_words * 8);
     return 0;
 }
 

@@ -65,6 +65,9 @@ class DeviceModel:
         if rc != 0:
             raise RuntimeError(f"{what} failed ({rc}): " + self.L.kg_last_error(self.h).decode())
 
+    def set_stream(self, cuda_stream_ptr):
+        self._chk(self.L.kg_model_set_stream(self.h, C.c_void_p(int(cuda_stream_ptr))), "kg_model_set_stream")
+
     def pair_index(self, i, j):
         i, j = min(i, j), max(i, j)
         return i * self.ncomps - i * (i - 1) // 2 + (j - i)
@@ -127,10 +130,16 @@ class OmegaPlan:
         raise_on_status(st)
         return (om, w) if want_w else om
 
+    def export_dev(self, omega_ptr, w_ptr=None):
+        """D2D copy of the result tables into caller-owned device buffers (e.g. torch tensors' data_ptr())."""
+        self.model._chk(self.model.L.kg_omega_plan_export_dev(self.h, C.c_void_p(int(omega_ptr)), C.c_void_p(int(w_ptr)) if w_ptr else None),
+                        "kg_omega_plan_export_dev")
+
     def counters(self):
-        out = np.zeros(9)
+        out = np.zeros(12)
         self.model._chk(self.model.L.kg_omega_plan_counters(self.h, _p(out)), "kg_omega_plan_counters")
-        keys = ["chi_evals", "chi_nodes", "lim_evals", "lim_nodes", "ms_theta", "ms_lim", "ms_mesh", "launches", "passes"]
+        keys = ["chi_evals", "chi_nodes", "lim_evals", "lim_nodes", "ms_theta", "ms_lim", "ms_mesh", "launches", "passes",
+                "h2d_bytes", "d2h_bytes", "pool_bytes"]
         return dict(zip(keys, out.tolist()))
 
     def close(self):
