@@ -67,6 +67,10 @@ typedef double (*f1d)(double u, void* ctx);
 static double tanh_sinh(f1d func, void* ctx, double h, double tol, long* nodes) {
     /* cpp/Integration/Integration.cpp:417-437, including the (k*h*1e-3) first-weight quirk at :422 */
     const int n_max_intervals = 10000;
+    /* the reference calls tanh_sinh with a run-time h: keep the compiler from folding the k = 1 node with MPFR
+       (correctly rounded) instead of the libm calls the reference makes at run time (1-ulp differences otherwise) */
+    volatile double h_runtime = h;
+    h = h_runtime;
     double I = 0.0;
     int k = 1;
     double u = tanh(PI * sinh(k * h) / 2.);
