@@ -33,6 +33,7 @@ typedef struct {
 #define KG_STATUS_GETR_MAXITER  1   /* "get_R reached max iter!"  cpp/Spherical.cpp:432 */
 #define KG_STATUS_TS_EXHAUSTED  2   /* tanh-sinh ran past the node table (reference would warn at 10000, Integration.cpp:432) */
 #define KG_STATUS_NAN           4   /* non-finite collision integral */
+#define KG_STATUS_BMID          8   /* "Unable to converge bmid!"  cpp/transfer_lengths.cpp:259-262 */
 
 typedef struct kg_model kg_model;
 typedef struct kg_omega_plan kg_omega_plan;
@@ -63,6 +64,11 @@ int kg_chi_points(kg_model* m, int pair, double T, int n, const double* g, const
  * Sutherland, cpp/ExtendedSutherland.cpp:182-200). status [nT][npairs]. */
 int kg_omega_batch(kg_model* m, int nT, const double* T, int nlr, const int32_t* l, const int32_t* r,
                    const double* coeff_T, double* omega, double* w, int32_t* status);
+
+/* Replaces Spherical::get_transfer_length for the default EWCA model (cpp/transfer_lengths.cpp:38-80,165-266; reached from
+ * KineticGas::get_mtl / get_etl, cpp/KineticGas.h:78-85): momentum and energy transfer lengths [m] for nT temperatures x all
+ * pairs, [nT][npairs]. One pass serves both (the reference recomputes every deflection angle per property). */
+int kg_transfer_lengths_batch(kg_model* m, int nT, const double* T, const double* coeff_T, double* mtl, double* etl, int32_t* status);
 
 /* Plan API: same computation with everything resident in HBM between calls (what a sweep driver / bench uses). */
 int kg_omega_plan_create(kg_model* m, int nT, const double* T, int nlr, const int32_t* l, const int32_t* r,

@@ -13,7 +13,7 @@ ip = C.POINTER(C.c_int32)
 EXPORTS = [
     "kg_model_create", "kg_model_destroy", "kg_last_error", "kg_model_npairs", "kg_chi_points", "kg_omega_batch",
     "kg_omega_plan_create", "kg_omega_plan_run", "kg_omega_plan_sync", "kg_omega_plan_fetch", "kg_omega_plan_omega_dev",
-    "kg_omega_plan_destroy", "kg_omega_plan_counters", "kg_measure_fp64_peak", "kg_model_set_stream", "kg_omega_plan_export_dev",
+    "kg_omega_plan_destroy", "kg_omega_plan_counters", "kg_measure_fp64_peak", "kg_model_set_stream", "kg_omega_plan_export_dev", "kg_transfer_lengths_batch",
 ]
 
 
@@ -49,6 +49,7 @@ def lib():
         L.kg_omega_plan_counters.argtypes = [C.c_void_p, dp]
         L.kg_model_set_stream.argtypes = [C.c_void_p, C.c_void_p]
         L.kg_omega_plan_export_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.kg_transfer_lengths_batch.argtypes = [C.c_void_p, C.c_int, dp, dp, dp, dp, ip]
         L.kg_measure_fp64_peak.argtypes = [C.c_int, dp, dp]
         _LIB = L
     return _LIB

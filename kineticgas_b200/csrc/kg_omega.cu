@@ -44,6 +44,8 @@ constexpr unsigned LIM_ROW = 0xFFFFu;  // work-list entry that is a theta_lim ev
 struct Regime {            // the T-dependent lattice of Spherical::w_integral (cpp/Spherical.cpp:60-84)
     int nx, ny;            // allocated lattice incl. the +2-step over-reach of the refinement probes
     int Nx_end, Ny_end, rlg, rlb, nwords;
+    int ldg, ldb;          // dg = 2^ldg, db = 2^ldb (all lattice steps are powers of two: exact scaling)
+    int nx_cut, ny_cut;    // first Nx with g > 1.5, first Ny with b > 2.5 (integrand cut-off, cpp/Spherical.cpp:99)
     double dg, db, lim;
 };
 
@@ -82,14 +84,15 @@ struct MeshView {
     const double* tab;
     unsigned* want;
     const double* gfac;     // [nx] : 2 exp(-g^2) g^(2r+3) for this (regime, r)
-    int ny, nwords, l;
+    int ny, nwords, l, nx_cut, ny_cut, ldg, ldb;
     double dg, db, lim, cospi;
 };
 
+__device__ __forceinline__ double pow2(int e) { return __longlong_as_double((long long) (1023 + e) << 52); }
+
 __device__ __forceinline__ bool node_is_free(const MeshView& v, int Nx, int Ny) {
-    // no chi needed: integrand cut-off (cpp/Spherical.cpp:99) or b/sigma < 1e-3 -> chi = PI (cpp/Spherical.cpp:267)
-    const double g = lattice_coord(Nx, v.dg), b = lattice_coord(Ny, v.db);
-    return ((b > 2.5) && (g > 1.5)) || Ny == 0;
+    // no chi needed: integrand cut-off b > 2.5 && g > 1.5 (cpp/Spherical.cpp:99) or b/sigma < 1e-3 -> chi = PI (:267)
+    return ((Ny >= v.ny_cut) && (Nx >= v.nx_cut)) || Ny == 0;
 }
 
 __device__ __forceinline__ void mesh_mark(const MeshView& v, int Nx, int Ny) {
@@ -111,8 +114,8 @@ __device__ __forceinline__ void mesh_mark_cell(const MeshView& v, int Nx, int Ny
 
 // integrand value at lattice node (Nx,Ny): cpp/Spherical.cpp:96-102 (chi known by construction)
 __device__ __forceinline__ double mesh_fetch(const MeshView& v, int Nx, int Ny) {
-    const double g = lattice_coord(Nx, v.dg), b = lattice_coord(Ny, v.db);
-    if ((b > 2.5) && (g > 1.5)) return 0.0;
+    if ((Ny >= v.ny_cut) && (Nx >= v.nx_cut)) return 0.0;
+    const double b = lattice_coord(Ny, v.db);
     const double c = (Ny == 0) ? v.cospi : v.tab[(long long) Nx * v.ny + Ny];
     double cl = c;
     for (int i = 1; i < v.l; i++) cl *= c;
@@ -126,6 +129,7 @@ __device__ __forceinline__ MeshView make_view(const Item& item, const Regime& rg
     v.want = want_pool + item.mask_off;
     v.gfac = gfac_pool + ((long long) item.regime * nr_distinct + ri) * gfac_stride;
     v.ny = rg.ny; v.nwords = rg.nwords; v.l = l;
+    v.nx_cut = rg.nx_cut; v.ny_cut = rg.ny_cut; v.ldg = rg.ldg; v.ldb = rg.ldb;
     v.dg = rg.dg; v.db = rg.db; v.lim = rg.lim; v.cospi = cospi;
     return v;
 }
@@ -151,7 +155,7 @@ __global__ void __launch_bounds__(128) mesh_init_kernel(const Item* __restrict__
 
 // One level of the refinement tree: every cell of cells_in is either integrated (leaf) or split into the sub-domain sweep
 // of integrate_adaptive (Integration.cpp:172-202) whose cells go to cells_out with their nodes marked.
-__global__ void __launch_bounds__(256) mesh_level_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
+__global__ void __launch_bounds__(256, 4) mesh_level_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
                                                          const double* __restrict__ tab_pool, unsigned* __restrict__ want_pool,
                                                          const double* __restrict__ gfac_pool, const int* __restrict__ lr_l,
                                                          const int* __restrict__ lr_r_index, int nr_distinct, int gfac_stride, double cospi,
@@ -162,7 +166,8 @@ __global__ void __launch_bounds__(256) mesh_level_kernel(const Item* __restrict_
     const Cell c = active ? cells_in[e] : 0;
     const unsigned owner = (unsigned) (c & 0x3FFFFFFu);
     const int Nx = (int) ((c >> 26) & 0xFF), Ny = (int) ((c >> 34) & 0x3FF);
-    const int ax = 1 << (int) ((c >> 44) & 7), sy = 1 << (int) ((c >> 48) & 7);
+    const int lx = (int) ((c >> 44) & 7), ly = (int) ((c >> 48) & 7);
+    const int ax = 1 << lx, sy = 1 << ly;
     const int sx = ((c >> 47) & 1) ? -ax : ax;
     double contrib = 0.0;
     int nchild = 0, sub_sx = sx, sub_sy = sy;
@@ -175,15 +180,17 @@ __global__ void __launch_bounds__(256) mesh_level_kernel(const Item* __restrict_
         const double f = mesh_fetch(v, Nx, Ny), f1x = mesh_fetch(v, Nx + ax, Ny), f2x = mesh_fetch(v, Nx + 2 * ax, Ny);
         const double f1y = mesh_fetch(v, Nx, Ny + sy), f2y = mesh_fetch(v, Nx, Ny + 2 * sy);
         const double f1x1y = mesh_fetch(v, Nx + ax, Ny + sy), f2x2y = mesh_fetch(v, Nx + 2 * ax, Ny + 2 * sy);
-        // second-difference estimator in the reference's operation order, no FMA contraction (decision predicate)
-        const double hx = fabs(v.dg * sx), hy = fabs(v.db * sy);
-        const double hx2 = __dmul_rn(hx, hx), hy2 = __dmul_rn(hy, hy);
-        const double fxx = __dadd_rn(__dsub_rn(f, __dmul_rn(2.0, f1x)), f2x) / hx2;
-        const double fyy = __dadd_rn(__dsub_rn(f, __dmul_rn(2.0, f1y)), f2y) / hy2;
+        // second-difference estimator in the reference's operation order, no FMA contraction (decision predicate).
+        // hx, hy are powers of two, so the reference's divisions are exact scalings and are done as multiplications.
+        const int ehx = v.ldg + lx, ehy = v.ldb + ly;
+        const double hx = pow2(ehx), hy = pow2(ehy);
+        const double hx2 = pow2(2 * ehx), hy2 = pow2(2 * ehy);
+        const double fxx = __dmul_rn(__dadd_rn(__dsub_rn(f, __dmul_rn(2.0, f1x)), f2x), pow2(-2 * ehx));
+        const double fyy = __dmul_rn(__dadd_rn(__dsub_rn(f, __dmul_rn(2.0, f1y)), f2y), pow2(-2 * ehy));
         double t = __dadd_rn(__dsub_rn(f2x2y, __dmul_rn(2.0, f1x1y)), f);
         t = __dsub_rn(t, __dmul_rn(hx2, fxx));
         t = __dsub_rn(t, __dmul_rn(hy2, fyy));
-        const double fxy = t / __dmul_rn(__dmul_rn(2.0, hx), hy);
+        const double fxy = __dmul_rn(t, pow2(-(1 + ehx + ehy)));
         const double dblder = __dadd_rn(__dadd_rn(fabs(fxx), fabs(fyy)), fabs(fxy));
         const double hs = __dadd_rn(hx, hy);
         const double hs3 = __dmul_rn(__dmul_rn(hs, hs), hs);
@@ -472,6 +479,9 @@ void regime_for_T(double T, Regime& R) {
     R.nx = R.Nx_end + 2 * rlg + 1;
     R.ny = R.Ny_end + 2 * rlb + 1;
     R.nwords = (R.ny + 31) / 32;
+    R.ldg = (int) std::lround(std::log2(dg)); R.ldb = (int) std::lround(std::log2(db));
+    R.nx_cut = 0; while (1e-7 + R.nx_cut * dg <= 1.5) R.nx_cut++;
+    R.ny_cut = 0; while (1e-7 + R.ny_cut * db <= 2.5) R.ny_cut++;
 }
 int regime_index(double T) { return T < 20 ? 4 : T < 35 ? 3 : T < 50 ? 2 : T < 70 ? 1 : 0; }
 const double REGIME_T[5] = {300.0, 60.0, 40.0, 30.0, 10.0};
@@ -944,3 +954,5 @@ extern "C" int kg_measure_fp64_peak(int device, double* tflops, double* sm_mhz_e
     if (sm_mhz_est) *sm_mhz_est = best * 1e12 / (2.0 * 64.0 * prop.multiProcessorCount) / 1e6;
     return 0;
 }
+
+#include "kg_tl.cuh"

@@ -5,7 +5,8 @@ import numpy as np
 from . import _lib
 from ._lib import PotentialDesc, dp, ip
 
-STATUS_TEXT = {1: "get_R reached max iter!", 2: "tanh-sinh node table exhausted", 4: "non-finite collision integral"}
+STATUS_TEXT = {1: "get_R reached max iter!", 2: "tanh-sinh node table exhausted", 4: "non-finite collision integral",
+               8: "Unable to converge bmid!"}
 
 
 def _p(a):
@@ -93,6 +94,16 @@ class DeviceModel:
         self._chk(self.L.kg_omega_batch(self.h, T.size, _p(T), l.size, _pi(l), _pi(r), _p(cf), _p(om), _p(w), _pi(st)), "kg_omega_batch")
         raise_on_status(st)
         return (om, w) if want_w else om
+
+    def transfer_lengths(self, T, coeff_T=None):
+        """(mtl, etl) in metres, each [nT][npairs] (EWCA model, cpp/transfer_lengths.cpp:165-179)."""
+        T = np.ascontiguousarray(np.atleast_1d(T), float)
+        mtl, etl = np.empty((T.size, self.npairs)), np.empty((T.size, self.npairs))
+        st = np.zeros((T.size, self.npairs), np.int32)
+        cf = None if coeff_T is None else np.ascontiguousarray(coeff_T, float)
+        self._chk(self.L.kg_transfer_lengths_batch(self.h, T.size, _p(T), _p(cf), _p(mtl), _p(etl), _pi(st)), "kg_transfer_lengths_batch")
+        raise_on_status(st)
+        return mtl, etl
 
     def omega_plan(self, T, l, r, coeff_T=None):
         return OmegaPlan(self, T, l, r, coeff_T)

@@ -491,3 +491,132 @@ double kgo_omega_prefactor(double sigma, double T, double m_i, double m_j, int s
     double m0 = m_i + m_j, Mij = m_i / m0, Mji = m_j / m0;
     return 0.5 * pow(sigma, 2) * sqrt(2 * PI * BOLTZMANN * T / (m0 * Mij * Mji));
 }
+
+/* ================================================================================================ transfer lengths
+ * Exchange-weighted closest approach (EWCA), cpp/transfer_lengths.cpp:151-266 */
+static double dimless_relative_vdf(double g) {
+    /* cpp/transfer_lengths.cpp:161-163 */
+    return sqrt(2. / PI) * pow(g, 2) * exp(-0.5 * pow(g, 2));
+}
+static double momentum_transfer(const kgo_pair* p, double T, double g, double b, int* st) {
+    /* cpp/transfer_lengths.cpp:207-212 */
+    double chi_val = kgo_chi(p, T, g, b * p->sigma, st);
+    return g * sqrt(2 * (1 - cos(chi_val))) * fabs(sin(chi_val / 2.));
+}
+static double energy_transfer(const kgo_pair* p, double T, double g, double b, int* st) {
+    /* cpp/transfer_lengths.cpp:214-219 */
+    double chi_val = kgo_chi(p, T, g, b * p->sigma, st);
+    return g * fabs(cos(chi_val) - sin(chi_val) - 1);
+}
+static double ewca_weight(const kgo_pair* p, double T, double g, double b, int property, int* st) {
+    /* cpp/transfer_lengths.cpp:196-205 */
+    if (property == 0) return momentum_transfer(p, T, g, b, st) * dimless_relative_vdf(g) * g * b;
+    return energy_transfer(p, T, g, b, st) * dimless_relative_vdf(g) * g * b;
+}
+double kgo_get_b_max_g(const kgo_pair* p, double g, double T, double bmid, int* st) {
+    /* cpp/transfer_lengths.cpp:221-232 */
+    double b, db, chi_val;
+    if (g == 0) return 10.;
+    b = 2 * bmid;
+    db = 0.5;
+    chi_val = kgo_chi(p, T, g, b * p->sigma, st);
+    while (fabs(chi_val + 1e-5) > 1e-3) {
+        b += db;
+        chi_val = kgo_chi(p, T, g, b * p->sigma, st);
+    }
+    return b;
+}
+double kgo_get_bmid(const kgo_pair* p, double g, double T, int* st) {
+    /* cpp/transfer_lengths.cpp:234-266 */
+    if (g == 0) return 5.;
+    double b = 0.9;
+    double db = 0.1;
+    double chi_val = kgo_chi(p, T, g, b * p->sigma, st);
+    double next_chi_val;
+    double dchidb = 10;
+    double step_tol = 1e-6;
+    double chi_tol = 1e-6;
+    while ((fabs(chi_val) > chi_tol) && (fabs(db) > step_tol)) {
+        if ((chi_val < 0 && db > 0) || (chi_val > 0 && db < 0)) db *= -0.9;
+        next_chi_val = kgo_chi(p, T, g, (b + db) * p->sigma, st);
+        while (fabs(next_chi_val) >= fabs(chi_val)) {
+            db *= 0.1;
+            next_chi_val = kgo_chi(p, T, g, (b + db) * p->sigma, st);
+            if (fabs(db) < step_tol) break;
+        }
+        if (fabs(db) > step_tol) {
+            b += db;
+            dchidb = (chi_val - next_chi_val) / db;
+            chi_val = next_chi_val;
+            db = -chi_val / dchidb;
+        }
+        if ((b > 10) || (b < 0)) { if (st) *st |= 8; /* "Unable to converge bmid!" */ return NAN; }
+    }
+    return b;
+}
+typedef struct { const kgo_pair* p; double T, g; int property; int* st; } ewctx;
+static void ws_funcs(const ewctx* c, double b, double* f, double* w) {
+    /* the func / wt lambdas of ewca_inner, cpp/transfer_lengths.cpp:186-187 */
+    *w = ewca_weight(c->p, c->T, c->g, b, c->property, c->st);
+    *f = kgo_get_R(c->p, c->T, c->g, b * c->p->sigma, c->st);
+}
+static void weighted_simpson_fw(const ewctx* c, double x0, double xN, int N_intervals, double* F_out, double* W_out) {
+    /* cpp/Integration/Integration.cpp:375-394 (note (N/2)-1 with integer division: an odd N drops a node) */
+    double dx = (xN - x0) / N_intervals;
+    double F = 0, W = 0, w1 = 0, w2 = 0, f1, f2;
+    ws_funcs(c, x0, &f1, &w1); ws_funcs(c, xN, &f2, &w2);
+    W += w1 + w2;
+    F += f1 * w1 + f2 * w2;
+    for (size_t i = 1; i <= (size_t) ((N_intervals / 2) - 1); i++) {
+        ws_funcs(c, x0 + (2 * i - 1) * dx, &f1, &w1);
+        ws_funcs(c, x0 + (2 * i) * dx, &f2, &w2);
+        W += 4. * w1 + 2. * w2;
+        F += 4. * f1 * w1 + 2. * f2 * w2;
+    }
+    ws_funcs(c, xN - dx, &f1, &w1);
+    W += 4. * w1;
+    F += 4. * f1 * w1;
+    W *= dx / 3.;
+    F *= dx / 3.;
+    *F_out = F; *W_out = W;
+}
+static void ewca_inner(const kgo_pair* p, double T, double g, int property, int* st, double* F, double* W) {
+    /* cpp/transfer_lengths.cpp:181-194 */
+    const double bmid = kgo_get_bmid(p, g, T, st);
+    const double bmax = kgo_get_b_max_g(p, g, T, bmid, st);
+    ewctx c = {p, T, g, property, st};
+    double F1, W1, F2, W2;
+    weighted_simpson_fw(&c, 0., bmid, 15, &F1, &W1);
+    weighted_simpson_fw(&c, bmid, bmax, 20, &F2, &W2);
+    *F = F1 + F2; *W = W1 + W2;
+}
+static void weighted_simpson_pair(const kgo_pair* p, double T, int property, int* st, double x0, double xN, int N_intervals, double* F_out, double* W_out) {
+    /* cpp/Integration/Integration.cpp:396-415 */
+    double dx = (xN - x0) / N_intervals;
+    double F = 0, W = 0, a1, b1, a2, b2;
+    ewca_inner(p, T, x0, property, st, &a1, &b1); ewca_inner(p, T, xN, property, st, &a2, &b2);
+    F += a1 + a2;
+    W += b1 + b2;
+    for (size_t i = 1; i <= (size_t) ((N_intervals / 2) - 1); i++) {
+        ewca_inner(p, T, x0 + (2 * i - 1) * dx, property, st, &a1, &b1);
+        ewca_inner(p, T, x0 + (2 * i) * dx, property, st, &a2, &b2);
+        F += 4. * a1 + 2. * a2;
+        W += 4. * b1 + 2. * b2;
+    }
+    ewca_inner(p, T, xN - dx, property, st, &a1, &b1);
+    F += 4. * a1;
+    W += 4. * b1;
+    F *= dx / 3;
+    W *= dx / 3;
+    *F_out = F; *W_out = W;
+}
+double kgo_tl_ewca(const kgo_pair* p, double T, int property, int* st) {
+    /* cpp/transfer_lengths.cpp:165-179 ; property 0 = MTL, 1 = ETL ; metres */
+    double g0 = 0., g1 = 3.5, gmax = 5.;
+    double F1, W1, F2, W2;
+    weighted_simpson_pair(p, T, property, st, g0, g1, 15, &F1, &W1);
+    weighted_simpson_pair(p, T, property, st, g1, gmax, 10, &F2, &W2);
+    double F = F1 + F2;
+    double W = W1 + W2;
+    return F / W;
+}

@@ -49,6 +49,11 @@ double kgo_w_integral(const kgo_pair* p, double T, int l, int r, const kgo_latti
                       long* n_chi, long* nodes_theta, long* nodes_lim);
 double kgo_omega_prefactor(double sigma, double T, double m_i, double m_j, int same);   /* cpp/Spherical.cpp:46-47 */
 long   kgo_last_nodes(void);
+/* Exchange-weighted closest approach transfer lengths (cpp/transfer_lengths.cpp:165-266); property 0 = MTL, 1 = ETL; metres.
+ * status bit 8 = "Unable to converge bmid!" */
+double kgo_get_bmid(const kgo_pair* p, double g, double T, int* status);
+double kgo_get_b_max_g(const kgo_pair* p, double g, double T, double bmid, int* status);
+double kgo_tl_ewca(const kgo_pair* p, double T, int property, int* status);
 
 #ifdef __cplusplus
 }

@@ -50,6 +50,12 @@ def lib():
         L.kgo_w_integral.restype = C.c_double
         L.kgo_w_integral.argtypes = [C.POINTER(Pair), C.c_double, C.c_int, C.c_int, C.POINTER(Lattice), C.POINTER(C.c_int),
                                      C.POINTER(C.c_long), C.POINTER(C.c_long), C.POINTER(C.c_long)]
+        L.kgo_tl_ewca.restype = C.c_double
+        L.kgo_tl_ewca.argtypes = [C.POINTER(Pair), C.c_double, C.c_int, C.POINTER(C.c_int)]
+        L.kgo_get_bmid.restype = C.c_double
+        L.kgo_get_bmid.argtypes = [C.POINTER(Pair), C.c_double, C.c_double, C.POINTER(C.c_int)]
+        L.kgo_get_b_max_g.restype = C.c_double
+        L.kgo_get_b_max_g.argtypes = [C.POINTER(Pair), C.c_double, C.c_double, C.c_double, C.POINTER(C.c_int)]
         L.kgo_omega_prefactor.restype = C.c_double
         L.kgo_omega_prefactor.argtypes = [C.c_double, C.c_double, C.c_double, C.c_double, C.c_int]
         _LIB = L
@@ -93,3 +99,12 @@ def integrate2d_table(tab, ox, oy, ex, ey, dx, dy, rlx, rly, lim):
     n = C.c_int()
     v = lib().kgo_integrate2d_table(tab.ctypes.data_as(dp), tab.shape[0], tab.shape[1], ox, oy, ex, ey, dx, dy, rlx, rly, lim, C.byref(n))
     return v, n.value
+
+
+def tl_ewca(pair, T, prop):
+    """prop 0 = MTL, 1 = ETL; metres"""
+    st = C.c_int(0)
+    v = lib().kgo_tl_ewca(C.byref(pair), T, prop, C.byref(st))
+    if st.value & 8:
+        raise RuntimeError("Unable to converge bmid!")
+    return v

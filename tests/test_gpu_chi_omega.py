@@ -41,3 +41,13 @@ def test_w_integral_vs_oracle(oracle_port, comp, T):
         w_ref = oracle_port.w_integral(p, T, l, r)
         # north_star tolerance: 1e-6 relative on Omega
         assert abs(w[0, 0, k] / w_ref - 1) < 1e-6, (l, r, w[0, 0, k], w_ref)
+
+
+@pytest.mark.parametrize("comp,T", [("AR", 300.0), ("CO2", 250.0), ("H2", 120.0)])
+def test_transfer_lengths_vs_oracle(oracle_port, comp, T):
+    m, (s, eps, la, lr) = _model(comp)
+    p = oracle_port.mie_pair(s, eps, la, lr)
+    mtl, etl = m.transfer_lengths([T])
+    # 1e-6 relative (north_star); these feed K-factors as tl^3
+    assert abs(mtl[0, 0] / oracle_port.tl_ewca(p, T, 0) - 1) < 1e-7
+    assert abs(etl[0, 0] / oracle_port.tl_ewca(p, T, 1) - 1) < 1e-7
