@@ -73,6 +73,10 @@ int kg_transfer_lengths_batch(kg_model* m, int nT, const double* T, const double
 /* Plan API: same computation with everything resident in HBM between calls (what a sweep driver / bench uses). */
 int kg_omega_plan_create(kg_model* m, int nT, const double* T, int nlr, const int32_t* l, const int32_t* r,
                          const double* coeff_T, kg_omega_plan** out);
+/* need (optional) [nT][npairs][nlr] bytes: 0 = this Omega is not wanted (e.g. it comes from MieKinGas::omega's correlation
+ * branch, cpp/MieKinGas.cpp:81-93); its output slot is 0 and pairs/temperatures with no wanted entry cost nothing. */
+int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T, int nlr, const int32_t* l, const int32_t* r,
+                                const double* coeff_T, const uint8_t* need, kg_omega_plan** out);
 int kg_omega_plan_run(kg_omega_plan* p);                  /* asynchronous on the model's stream */
 int kg_omega_plan_sync(kg_omega_plan* p);
 int kg_omega_plan_fetch(kg_omega_plan* p, double* omega, double* w, int32_t* status);  /* D2H, synchronises */
@@ -87,6 +91,87 @@ void kg_omega_plan_destroy(kg_omega_plan* p);
  *  out[6] ms in the mesh kernels          out[7] number of kernel launches        out[8] refinement passes
  *  out[9] H2D bytes of plan creation      out[10] D2H bytes of the last fetch     out[11] bytes of lattice + mask pools in HBM */
 int kg_omega_plan_counters(kg_omega_plan* p, double* out12);
+
+
+/* ================================================================================================================
+ * State-point assembly (Revised Enskog Theory): everything KineticGas does per (T, Vm, x) after the collision
+ * integrals exist -- RDF at contact, K-factors, square-bracket sums, the Sonine-expansion linear systems and the
+ * property formulas -- batched over state points on the GPU.
+ * ================================================================================================================ */
+#define KG_MAX_COMPS 6          /* internal component count (a single-component model is a 2-component mixture inside,
+                                   cpp/KineticGas.cpp:139-144) */
+#define KG_MAX_ORDER 4          /* Enskog approximation order N */
+
+/* FrameOfReference, same values as cpp/utils.h:37-45 */
+#define KG_FOR_COM 0
+#define KG_FOR_CON 1
+#define KG_FOR_COV 2
+#define KG_FOR_SOLVENT 3
+
+#define KG_PROP_VISCOSITY          1u   /* KineticGas::viscosity                 cpp/KineticGas_properties.cpp:28-58   */
+#define KG_PROP_CONDUCTIVITY       2u   /* KineticGas::thermal_conductivity      cpp/KineticGas_properties.cpp:69-141  */
+#define KG_PROP_DIFFUSION          4u   /* KineticGas::interdiffusion            cpp/KineticGas_properties.cpp:167-206 */
+#define KG_PROP_THERMAL_DIFFUSION  8u   /* KineticGas::thermal_diffusion_coeff   cpp/KineticGas_properties.cpp:208-280 */
+
+#define KG_STATUS_SINGULAR      16  /* zero pivot in a Sonine-expansion system */
+#define KG_STATUS_T_NOT_CACHED  32  /* state-point temperature absent from the kg_tcache it was run against */
+
+typedef struct {
+    int32_t N;                        /* Enskog approximation order (>= 1; conductivity needs >= 2) */
+    int32_t is_idealgas;              /* KineticGas::is_idealgas: rdf = 1, K = K' = 1, no density terms */
+    int32_t omega_correlation_active; /* MieKinGas::set_omega_correlation_active (cpp/MieKinGas.cpp:150-155) */
+    int32_t frame_of_reference;       /* KG_FOR_* */
+    int32_t dependent_idx;            /* python-style negative index allowed (-1 = last) */
+    int32_t solvent_idx;
+    int32_t do_compress;              /* drop the dependent row/column of D (compress_diffusion_matrix) */
+    uint32_t properties;              /* KG_PROP_* bit mask */
+} kg_transport_opts;
+
+/* EoS-derived inputs (thermopack on the host in the reference, cpp/eos_interface.h:57-135); nc_eos = 1 for a
+ * single-component model else ncomps. Any pointer may be NULL when the requested properties do not need it. */
+typedef struct {
+    const double* dmudn;      /* [n][nc_eos][nc_eos]  (dmu_i/dn_j)_{T,V} at V = Vm, n = x (1 mol)  [J/mol^2]  -> diffusion */
+    const double* cp_ideal;   /* [n][nc_eos]          ideal-gas Cp of each pure component [J/mol K]         -> conductivity */
+    const double* pressure;   /* [n]                  (unused unless frame = CoV) */
+    const double* dvdn;       /* [n][nc_eos]          partial molar volumes                                 -> frame = CoV */
+} kg_eos_inputs;
+
+/* Outputs; NULL = not wanted. nc = internal component count (2 for single-component models). */
+typedef struct {
+    double* viscosity;              /* [n]            Pa s */
+    double* conductivity;           /* [n]            W/m K */
+    double* conductivity_contribs;  /* [n][3]         translational, density, internal (thermal_conductivity_contributions "tdi") */
+    double* D;                      /* [n][nc][nc] or [n][nc-1][nc-1] when do_compress; m^2/s */
+    double* DT;                     /* [n][nc]        thermal diffusion coefficients, mol/(m s) */
+    double* rdf;                    /* [n][nc][nc]    KineticGas::get_rdf */
+    double* K;                      /* [n][nc]        get_K_factors */
+    double* K_prime;                /* [n][nc]        get_K_prime_factors */
+    double* cond_matrix;            /* [n][N nc][N nc] get_conductivity_matrix (cpp/KineticGas.cpp:271-318) */
+    double* cond_vector;            /* [n][N nc]       get_conductivity_vector */
+    double* visc_matrix;            /* [n][N nc][N nc] get_viscosity_matrix    (cpp/KineticGas.cpp:418-439) */
+    double* visc_vector;            /* [n][N nc]       get_viscosity_vector */
+} kg_transport_out;
+
+/* Device-resident per-temperature tables = what the reference keeps in KineticGasCache (cpp/KineticGasCache.h): every
+ * Omega^(l,r)_ij the requested properties need at order N (numerical quadrature, or the Fokin-Popov-Kalashnikov correlation
+ * where MieKinGas::omega would use it), MTL/ETL, Barker-Henderson diameters and the bracket integrals H_ij, H_i, L_ij, L_i
+ * (cpp/KineticGas.cpp:644-705). Replaces precompute_conductivity / precompute_viscosity (cpp/KineticGas_mthr.cpp:58-143). */
+typedef struct kg_tcache kg_tcache;
+/* coeff_T (optional) [nT][npairs][KG_MAX_TERMS]: per-temperature effective coefficients of T-dependent potentials (ideal gas only). */
+int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int nT, const double* T, const double* coeff_T, kg_tcache** out);
+void kg_tcache_destroy(kg_tcache* c);
+/* Shape of the Omega table: nlr entries (l[k], r[k]); pass NULL arrays to query nlr only. */
+int kg_tcache_lr(const kg_tcache* c, int32_t* l, int32_t* r);
+/* Host copies, to feed the reference's cache.omega.store / cache.mtl / cache.etl (cpp/KineticGasCache.h:25-28):
+ * omega [nT][npairs][nlr] (0 where not needed), mtl/etl [nT][npairs] (NULL ok; zeros for ideal-gas models), is_correlation
+ * [nT][npairs][nlr] (1 where the value came from the correlation branch). */
+int kg_tcache_fetch(kg_tcache* c, double* omega, double* mtl, double* etl, uint8_t* is_correlation);
+
+/* All requested properties for n state points. T, Vm [n]; x [n][ncomps] (ignored for single-component models, which use
+ * {0.5,0.5} like pykingas/py_KineticGas.py:119-141). cache may be NULL: a temporary one is built for the distinct T.
+ * status [n] (NULL ok). */
+int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const double* T, const double* Vm, const double* x,
+                       const kg_transport_opts* opts, const kg_eos_inputs* eos, const kg_transport_out* out, int32_t* status);
 
 /* FP64 FMA-pipe peak probe: runs a register-resident DFMA chain kernel and returns the measured TFLOP/s
  * (2 flop per DFMA). Used as the roofline denominator (MEASURED_PEAKS.json has no FP64 figure). */

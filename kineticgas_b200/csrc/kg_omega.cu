@@ -20,7 +20,7 @@
 // repeated until no mesh thread meets an unknown node (depth of the refinement tree + 1 passes). Only nodes the
 // reference's mesh touches are ever integrated.
 #include "kg_device.cuh"
-#include "../../include/kgcuda.h"
+#include "kg_internal.cuh"
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -29,9 +29,6 @@
 #include <algorithm>
 
 using namespace kg;
-
-#define CUDA_OK(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { \
-    set_error(std::string(#expr) + ": " + cudaGetErrorString(e_)); return -2; } } while (0)
 
 static thread_local std::string g_create_error;
 
@@ -58,7 +55,7 @@ struct Item {              // one (pair, T)
     long long col_off;     // into the per-column pools (I_lim, have_lim, task index) [nx]
     int coeff_off;         // into coeff pool (doubles) or -1
     int pad;
-    long long cell0_off;   // first coarse cell of this item in the level-0 cell list
+    long long cell0_off;   // (unused, kept for alignment)
 };
 
 struct WorkEntry { int item; unsigned short nx, ny; };
@@ -134,22 +131,24 @@ __device__ __forceinline__ MeshView make_view(const Item& item, const Regime& rg
     return v;
 }
 
-// level 0: the coarse cells of every (item,(l,r)) in the reference's sweep order (Integration.cpp:240-280: row k runs +x
-// for even k, -x for odd k) and the lattice nodes they read. grid.x = nitems, block strides over nlr * ncells.
+// level 0: the coarse cells of every active (item,(l,r)) owner in the reference's sweep order (Integration.cpp:240-280:
+// row k runs +x for even k, -x for odd k) and the lattice nodes they read. grid.x = number of active owners.
 __global__ void __launch_bounds__(128) mesh_init_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
-                                                        unsigned* __restrict__ want_pool, int nlr, Cell* __restrict__ cells) {
-    const int it = blockIdx.x;
+                                                        unsigned* __restrict__ want_pool, int nlr, const int* __restrict__ owners,
+                                                        const long long* __restrict__ owner_cell_off, Cell* __restrict__ cells) {
+    const int owner = owners[blockIdx.x];
+    const int it = owner / nlr;
     const Item item = items[it];
     const Regime rg = regimes[item.regime];
     MeshView v = make_view(item, rg, nullptr, want_pool, nullptr, 0, 0, 0, 1, 0.0);
     const int ncx = rg.Nx_end / rg.rlg, ncy = rg.Ny_end / rg.rlb, nc = ncx * ncy;
-    for (int i = threadIdx.x; i < nc * nlr; i += blockDim.x) {
-        const int lr = i / nc, cell = i % nc;
+    const long long c0 = owner_cell_off[blockIdx.x];
+    for (int cell = threadIdx.x; cell < nc; cell += blockDim.x) {
         const int row = cell / ncx, col = cell % ncx;
         const int d = (row & 1) ? -1 : 1;
         const int ex = ((row & 1) ? rg.Nx_end : 0) + col * d * rg.rlg, ey = row * rg.rlb;
-        cells[item.cell0_off + i] = pack_cell((unsigned) (it * nlr + lr), ex, ey, d * rg.rlg, rg.rlb);
-        if (lr == 0) mesh_mark_cell(v, ex, ey, d * rg.rlg, rg.rlb);
+        cells[c0 + cell] = pack_cell((unsigned) owner, ex, ey, d * rg.rlg, rg.rlb);
+        mesh_mark_cell(v, ex, ey, d * rg.rlg, rg.rlb);       // idempotent across the owners of one item
     }
 }
 
@@ -447,20 +446,6 @@ __global__ void __launch_bounds__(256) dfma_probe_kernel(double* out, int iters,
 // ================================================================================================================
 // host side
 // ================================================================================================================
-struct kg_model {
-    int device = 0, ncomps = 0, npairs = 0, is_singlecomp = 0, ntpad = 2;
-    std::vector<double> mass;
-    std::vector<kg_potential_desc> descs;
-    std::vector<PairParams> pairs;
-    std::vector<double*> d_rows;        // per pair: [KMAX][2+ntpad]
-    double** d_rows_by_pair = nullptr;
-    PairParams* d_pairs = nullptr;
-    cudaStream_t stream = nullptr;
-    bool own_stream = true;
-    std::string err;
-    int sm_count = 148;
-    void set_error(const std::string& s) { err = s; }
-};
 
 namespace {
 
@@ -615,6 +600,7 @@ extern "C" int kg_chi_points(kg_model* m, int pair, double T, int n, const doubl
 // ---------------------------------------------------------------------------------------------------------------- plan
 struct kg_omega_plan {
     kg_model* m = nullptr;
+    int device = 0;
     int nT = 0, nlr = 0, nitems = 0, ntasks = 0, nr_distinct = 0, gfac_stride = 0;
     long long max_list = 0;
     std::vector<Item> items;            // sorted by pair
@@ -631,6 +617,7 @@ struct kg_omega_plan {
     double *d_W_out = nullptr, *d_omega_out = nullptr;  // [nT][npairs][nlr]
     int *d_status = nullptr, *d_flags = nullptr, *d_tile_counter = nullptr;
     int* d_perm = nullptr;                              // item -> output slot
+    int* d_owners = nullptr; long long* d_owner_cell_off = nullptr; int nowners = 0;   // active (item,(l,r)) owners
     int* d_pair_task_start = nullptr;                   // [npairs+1] first column task of each pair
     unsigned long long* d_counters = nullptr;
     long long tab_doubles = 0, mask_words = 0, ncols_total = 0;
@@ -655,6 +642,11 @@ __global__ void permute_kernel(const double* __restrict__ W, const Item* __restr
 
 extern "C" int kg_omega_plan_create(kg_model* m, int nT, const double* T, int nlr, const int32_t* l, const int32_t* r,
                                     const double* coeff_T, kg_omega_plan** out) {
+    return kg_omega_plan_create_masked(m, nT, T, nlr, l, r, coeff_T, nullptr, out);
+}
+
+extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T, int nlr, const int32_t* l, const int32_t* r,
+                                           const double* coeff_T, const uint8_t* need, kg_omega_plan** out) {
     if (!m) return -1;
     auto set_error = [&](const std::string& s) { m->err = s; };
     if (nT < 1 || !T || nlr < 1 || !l || !r || !out) { set_error("kg_omega_plan_create: invalid argument"); return -1; }
@@ -662,7 +654,7 @@ extern "C" int kg_omega_plan_create(kg_model* m, int nT, const double* T, int nl
     for (int i = 0; i < nT; i++) if (!(T[i] > 0) || !std::isfinite(T[i])) { set_error("kg_omega_plan_create: temperatures must be positive and finite"); return -1; }
     CUDA_OK(cudaSetDevice(m->device));
     kg_omega_plan* p = new kg_omega_plan;
-    p->m = m; p->nT = nT; p->nlr = nlr;
+    p->m = m; p->device = m->device; p->nT = nT; p->nlr = nlr;
     const int Np = m->npairs;
     p->nitems = nT * Np;
     Regime regs[5];
@@ -670,6 +662,8 @@ extern "C" int kg_omega_plan_create(kg_model* m, int nT, const double* T, int nl
     // items sorted by pair (theta tiles keep one pair's node rows in shared memory), then by T index
     p->items.reserve(p->nitems);
     std::vector<int> perm; perm.reserve(p->nitems);
+    std::vector<int> owners; std::vector<long long> owner_cell_off;     // active (item,(l,r)) and their level-0 cell offsets
+    std::vector<char> item_active;
     const double PI = 3.14159265359, KB = 1.38064852e-23;
     int pi = 0;
     for (int i = 0; i < m->ncomps; i++) for (int j = i; j < m->ncomps; j++, pi++) {
@@ -683,23 +677,34 @@ extern "C" int kg_omega_plan_create(kg_model* m, int nT, const double* T, int nl
                 it.pref = 0.5 * pow(sig, 2) * sqrt(2 * PI * KB * T[t] / (m0 * Mij * Mji));       // cpp/Spherical.cpp:47
             }
             const Regime& rg = regs[it.regime];
-            it.tab_off = p->tab_doubles; p->tab_doubles += (long long) rg.nx * rg.ny;
-            it.mask_off = p->mask_words; p->mask_words += (long long) rg.nx * rg.nwords;
-            it.col_off = p->ncols_total; p->ncols_total += rg.nx;
+            const int item_index = (int) p->items.size();
+            int nact = 0;
+            for (int k = 0; k < nlr; k++) {
+                if (need && !need[((size_t) t * Np + pi) * nlr + k]) continue;
+                owners.push_back(item_index * nlr + k);
+                owner_cell_off.push_back(p->ncells0);
+                p->ncells0 += (long long) (rg.Nx_end / rg.rlg) * (rg.Ny_end / rg.rlb);
+                nact++;
+            }
+            item_active.push_back(nact > 0);
+            if (nact > 0) {      // items with nothing to integrate own no lattice, no columns, no cells
+                it.tab_off = p->tab_doubles; p->tab_doubles += (long long) rg.nx * rg.ny;
+                it.mask_off = p->mask_words; p->mask_words += (long long) rg.nx * rg.nwords;
+                it.col_off = p->ncols_total; p->ncols_total += rg.nx;
+                p->cell_cap += (long long) nact * rg.Nx_end * rg.Ny_end;     // cells of one level tile (part of) the domain
+            }
             it.coeff_off = coeff_T ? (t * Np + pi) * KG_MAX_TERMS : -1;
-            it.cell0_off = p->ncells0;
-            p->ncells0 += (long long) nlr * (rg.Nx_end / rg.rlg) * (rg.Ny_end / rg.rlb);
-            p->cell_cap += (long long) nlr * rg.Nx_end * rg.Ny_end;     // cells of one level tile (part of) the domain
             p->items.push_back(it);
             perm.push_back(t * Np + pi);
         }
     }
     std::vector<int2> tasks; tasks.reserve(p->ncols_total);
     for (int it = 0; it < p->nitems; it++) {
+        if (!item_active[it]) continue;
         const Regime& rg = regs[p->items[it].regime];
         for (int nx = 0; nx < rg.nx; nx++) tasks.push_back(make_int2(it, nx));
-        p->max_list += (long long) rg.nx * (rg.ny + 1);
     }
+    p->nowners = (int) owners.size();
     p->ntasks = (int) tasks.size();
     std::vector<int> pair_task_start(Np + 1, p->ntasks);
     for (int t = p->ntasks - 1; t >= 0; t--) pair_task_start[p->items[tasks[t].x].pair] = t;
@@ -722,6 +727,7 @@ extern "C" int kg_omega_plan_create(kg_model* m, int nT, const double* T, int nl
     // never requested. Cap by the count of requestable nodes.
     long long cap = 0;
     for (int it = 0; it < p->nitems; it++) {
+        if (!item_active[it]) continue;
         const Regime& rg = regs[p->items[it].regime];
         for (int nx = 0; nx < rg.nx; nx++) {
             const double g = 1e-7 + nx * rg.dg;
@@ -761,6 +767,10 @@ extern "C" int kg_omega_plan_create(kg_model* m, int nT, const double* T, int nl
     PLAN_CUDA(cudaMalloc(&p->d_pair_task_start, (Np + 1) * sizeof(int)));
     PLAN_CUDA(cudaMemcpy(p->d_pair_task_start, pair_task_start.data(), (Np + 1) * sizeof(int), cudaMemcpyHostToDevice));
     PLAN_CUDA(cudaMalloc(&p->d_perm, p->nitems * sizeof(int)));
+    PLAN_CUDA(cudaMalloc(&p->d_owners, (owners.size() + 1) * sizeof(int)));
+    PLAN_CUDA(cudaMalloc(&p->d_owner_cell_off, (owners.size() + 1) * sizeof(long long)));
+    PLAN_CUDA(cudaMemcpy(p->d_owners, owners.data(), owners.size() * sizeof(int), cudaMemcpyHostToDevice));
+    PLAN_CUDA(cudaMemcpy(p->d_owner_cell_off, owner_cell_off.data(), owners.size() * sizeof(long long), cudaMemcpyHostToDevice));
     PLAN_CUDA(cudaMalloc(&p->d_counters, 8 * sizeof(unsigned long long)));
     PLAN_CUDA(cudaMallocHost(&p->h_pinned, 8 * sizeof(int)));
     if (coeff_T) {
@@ -784,10 +794,11 @@ extern "C" int kg_omega_plan_create(kg_model* m, int nT, const double* T, int nl
 
 extern "C" void kg_omega_plan_destroy(kg_omega_plan* p) {
     if (!p) return;
-    cudaSetDevice(p->m->device);
+    cudaSetDevice(p->device);
     void* ptrs[] = {p->d_items, p->d_regimes, p->d_tab, p->d_want, p->d_known, p->d_lim, p->d_have_lim, p->d_tasks, p->d_counts,
                     p->d_offsets, p->d_list, p->d_gfac, p->d_lr_l, p->d_lr_ri, p->d_coeff, p->d_W, p->d_omega, p->d_W_out,
-                    p->d_omega_out, p->d_status, p->d_flags, p->d_tile_counter, p->d_perm, p->d_counters, p->d_cells[0], p->d_cells[1], p->d_ncells, p->d_pair_task_start};
+                    p->d_omega_out, p->d_status, p->d_flags, p->d_tile_counter, p->d_perm, p->d_counters, p->d_cells[0], p->d_cells[1], p->d_ncells, p->d_pair_task_start,
+                    p->d_owners, p->d_owner_cell_off};
     for (void* q : ptrs) if (q) cudaFree(q);
     if (p->h_pinned) cudaFreeHost(p->h_pinned);
     for (int k = 0; k < 4; k++) if (p->ev[k]) cudaEventDestroy(p->ev[k]);
@@ -810,9 +821,10 @@ extern "C" int kg_omega_plan_run(kg_omega_plan* p) {
     CUDA_OK(cudaMemsetAsync(p->d_flags, 0, 4 * sizeof(int), s));
     const int W = 2 + m->ntpad;
     const size_t smem = (size_t) KS_ROWS * W * sizeof(double);
-    const int tgrid = (p->ntasks + 255) / 256;
+    const int tgrid = std::max(1, (p->ntasks + 255) / 256);
     CUDA_OK(cudaEventRecord(p->ev[0], s));
-    mesh_init_kernel<<<p->nitems, 128, 0, s>>>(p->d_items, p->d_regimes, p->d_want, p->nlr, p->d_cells[0]);
+    if (p->nowners > 0)
+        mesh_init_kernel<<<p->nowners, 128, 0, s>>>(p->d_items, p->d_regimes, p->d_want, p->nlr, p->d_owners, p->d_owner_cell_off, p->d_cells[0]);
     CUDA_OK(cudaEventRecord(p->ev[1], s));
     p->launches += 1;
     long long n_in = p->ncells0;

@@ -1,0 +1,1004 @@
+// kg_transport.cu -- Revised-Enskog state-point assembly on B200 (sm_100a), behind the C-ABI of include/kgcuda.h.
+//
+// Reference path replaced (thermotools/KineticGas @ 75848b1):
+//   bracket weights A, A', B', B'' and sums H_ij, H_i, L_ij, L_i      cpp/KineticGas.cpp:520-705
+//   MieKinGas::omega correlation branch (Fokin, Popov, Kalashnikov)   cpp/MieKinGas.cpp:81-148
+//   SAFT-VR Mie RDF at contact, Barker-Henderson diameters            cpp/MieKinGas.cpp:157-276,314-786
+//   K-factors, Lambda / B matrices and right-hand sides               cpp/KineticGas.cpp:207-457
+//   partial-pivot LU solves and the property formulas                 cpp/KineticGas_properties.cpp:28-500
+//
+// Layout (not a translation). Everything that depends on temperature only is computed once per distinct T into
+// device tables (kg_tcache): the Omega table [nT][npairs][nlr], transfer lengths, BH diameters and the bracket
+// integrals [nT][nc][nc][N][N]. The combinatorial weights are T-independent: the host evaluates them once per
+// (model, N) in extended precision and ships dense weight tables. A state point then costs one RDF evaluation per
+// pair (rdf_kernel, one thread per (state point, density slot, pair)) and one thread of assembly + LU + property
+// formulas (state_kernel). The (N nc^2)^2 diffusion system of the reference is block diagonal with nc copies of the
+// conductivity matrix (cpp/KineticGas.cpp:334-388), so Lambda is factorised once and solved for nc + 1 right-hand sides.
+#include "kg_internal.cuh"
+#include <cmath>
+#include <cstring>
+#include <map>
+#include <algorithm>
+
+using namespace kg;
+
+namespace {
+
+constexpr int MAXC = KG_MAX_COMPS;
+constexpr int MAXO = KG_MAX_ORDER;
+constexpr int MAXLR = 40;                 // (l,r) combinations at order <= 4: viscosity needs l <= N+1, r <= 2N+2-l
+constexpr double GAS_CONSTANT = 8.31446261815324;     // cpp/global_params.h:5
+constexpr double AVOGADRO = GAS_CONSTANT / 1.38064852e-23;
+
+// ---------------------------------------------------------------------------------------------------------------
+// host: combinatorial weights of the square-bracket integrals (Thompson, Tipton, Loyalka; cpp/KineticGas.cpp:520-629).
+// Evaluated in long double from the closed forms; the reference cancels factorials symbolically before dividing,
+// which is an overflow guard, not a different value.
+// ---------------------------------------------------------------------------------------------------------------
+typedef long double ld;
+ld fac(int n) { ld r = 1; for (int k = 2; k <= n; k++) r *= k; return r; }
+ld ipw(ld b, int e) { return powl(b, (ld) e); }
+ld poch(int z, int n) { return fac(z + n - 1) / fac(z - 1); }
+int kdelta(int a, int b) { return a == b; }
+
+double weight_A(int p, int q, int r, int l) {
+    ld v = 0;
+    const int max_i = std::min(std::min(p, q), std::min(r, p + q + 1 - r));
+    for (int i = l - 1; i <= max_i; i++) {
+        const ld num = ipw(8, i) * fac(p + q - 2 * i) * ipw(-1, l + r + i) * fac(r + 1) * fac(2 * (p + q + 2 - i)) * ipw(4, r);
+        const ld den = fac(p - i) * fac(q - i) * fac(l) * fac(i + 1 - l) * fac(r - i) * fac(p + q + 1 - i - r) * fac(2 * r + 2)
+                     * fac(p + q + 2 - i) * ipw(4, p + q + 1);
+        v += (num / den) * ((i + 1 - l) * (p + q + 1 - i - r) - l * (r - i));
+    }
+    return (double) v;
+}
+
+double weight_A_prime(int p, int q, int r, int l, double M1d, double M2d) {
+    const ld M1 = M1d, M2 = M2d;
+    const ld F = (M1 * M1 + M2 * M2) / (2 * M1 * M2), G = (M1 - M2) / M2;
+    const int max_i = std::min(p, std::min(q, std::min(r, p + q + 1 - r)));
+    ld v = 0;
+    for (int i = l - 1; i <= max_i; i++) {
+        const int max_w = std::min(p, std::min(q, p + q + 1 - r)) - i, max_k = std::min(l, i);
+        for (int k = l - 1; k <= max_k; k++) for (int w = 0; w <= max_w; w++) {
+            const ld p1 = ipw(8, i) * fac(p + q - 2 * i - w) * ipw(-1, r + i) * fac(r + 1) * fac(2 * (p + q + 2 - i - w)) * ipw(2, 2 * r)
+                        * ipw(F, i - k) * ipw(G, w) * (ipw(2, 2 * w - 1) * ipw(M1, i) * ipw(M2, p + q - i - w) * 2)
+                        * (M1 * (p + q + 1 - i - r - w) * kdelta(k, l) - M2 * (r - i) * kdelta(k, l - 1));
+            const ld p2 = fac(p - i - w) * fac(q - i - w) * fac(r - i) * fac(p + q + 1 - i - r - w) * fac(2 * r + 2) * fac(p + q + 2 - i - w)
+                        * ipw(4, p + q + 1) * fac(k) * fac(i - k) * fac(w);
+            v += p1 / p2;
+        }
+    }
+    return (double) v;
+}
+
+double weight_B_prime(int p, int q, int r, int l, double M1d, double M2d) {
+    if (r == p + q + 3) return 0.0;
+    const ld M1 = M1d, M2 = M2d;
+    const ld G = (M1 - M2) / M2, F = (M1 * M1 + M2 * M2) / (2 * M1 * M2);
+    const int i_max = std::min(p, std::min(q, std::min(r, p + q + 2 - r)));
+    ld val = 0;
+    for (int i = std::max(l - 2, 0); i <= i_max; i++) {        // the i = -1 term carries the factor (1 - delta(i,-1)) = 0
+        ld inner = 0;
+        const int w_max = std::min(p, std::min(q, p + q + 2 - r)) - i;
+        for (int w = 0; w <= w_max; w++) {
+            const ld num = poch(p + 1 - i - w, w) * poch(q + 1 - i - w, w) * poch(p + q + 3 - i - r - w, w) * ipw(2, 2 * w - 2) * ipw(G, w)
+                         * poch(p + q + 4 - i - w, w) * ipw(M1 * M2, i) * ipw(M2, p + q - 2 * i - w) * ipw(F, i + 2 - l) * M1 * M1 * 4;
+            const ld den = fac(w) * poch(p + q + 1 - 2 * i - w, w) * poch(2 * (p + q + 3 - i) - 2 * w + 1, w)
+                         * poch(2 * (p + q + 3 - i) - w + 1, w) * fac(l) * fac(i + 2 - l);
+            const ld m21 = M2 / M1;
+            inner += (num / den) * ((ld) 1.5 * m21 * m21 * l * (l - 1) * (r - i) * (r - i - 1)
+                                    - (2 / F) * m21 * l * (i + 2 - l) * (r - i) * (p + q + 2 - i - r - w)
+                                    + (1 / (F * F)) * (i + 1 - l) * (i + 2 - l)
+                                        * ((p + q + 1 - i - r - w) * (p + q + 2 - i - r - w) - (ld) 0.5 * m21 * m21 * (r - i) * (r - i - 1)));
+        }
+        const ld num = ipw(2, 2 * r) * ipw(8, i) * fac(p + q - 2 * i) * ipw(-1, r + i) * fac(r + 1) * fac(2 * (p + q + 3 - i));
+        const ld den = ipw(4, p + q + 2) * fac(p - i) * fac(q - i) * fac(r - i) * fac(p + q + 2 - i - r) * fac(2 * r + 2) * fac(p + q + 3 - i);
+        val += (num / den) * inner;
+    }
+    return (double) val;
+}
+
+double weight_B_dblprime(int p, int q, int r, int l, double M1d, double M2d) {
+    if (r == p + q + 3) return 0.0;
+    const ld M1 = M1d, M2 = M2d;
+    const int i_max = std::min(p, std::min(q, std::min(r, p + q + 2 - r)));
+    ld val = 0;
+    for (int i = std::max(l - 2, 0); i <= i_max; i++) {
+        const ld num = ipw(2, 2 * r) * ipw(8, i) * fac(p + q - 2 * i) * ipw(-1, r + i) * fac(r + 1) * fac(2 * (p + q + 3 - i)) * ipw(-1, l);
+        const ld den = ipw(4, p + q + 2) * fac(p - i) * fac(q - i) * fac(r - i) * fac(p + q + 2 - i - r) * fac(2 * r + 2) * fac(p + q + 3 - i)
+                     * fac(l) * fac(i + 2 - l);
+        const ld pre = num / den;
+        val += pre * (i + 1 - l) * (i + 2 - l) * ((p + q + 1 - i - r) * (p + q + 2 - i - r) - (ld) 0.5 * (r - i) * (r - i - 1));
+        val += pre * (ld) 1.5 * (l - 1) * l * (r - i) * (r - i - 1);
+        val += pre * (-2) * l * (i + 2 - l) * (r - i) * (p + q + 2 - i - r);
+    }
+    val *= ipw(M2, p + 1) * ipw(M1, q + 1);
+    return (double) val;
+}
+
+} // namespace
+
+// ---------------------------------------------------------------------------------------------------------------
+// device constants: regressed SAFT-VR Mie / collision-integral correlation coefficients (published data, same values
+// the reference carries in cpp/MieKinGas.h:199-276)
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+
+// 20-point Gauss-Legendre rule on [-1,1] (BH diameter integral, cpp/MieKinGas.cpp:314-332)
+__constant__ double c_gl_x[20] = {-0.9931285991850949, -0.9639719272779139, -0.912234428251326, -0.8391169718222187, -0.7463319064601508,
+    -0.636053680726515, -0.5108670019508271, -0.37370608871541955, -0.22778585114164507, -0.07652652113349737, 0.07652652113349737,
+    0.22778585114164507, 0.37370608871541955, 0.5108670019508271, 0.636053680726515, 0.7463319064601508, 0.8391169718222187,
+    0.912234428251326, 0.9639719272779139, 0.9931285991850949};
+__constant__ double c_gl_w[20] = {0.017614007139152742, 0.040601429800386134, 0.06267204833410799, 0.08327674157670514, 0.1019301198172403,
+    0.11819453196151845, 0.13168863844917675, 0.14209610931838218, 0.149172986472604, 0.15275338713072611, 0.15275338713072611,
+    0.149172986472604, 0.14209610931838218, 0.13168863844917675, 0.11819453196151845, 0.1019301198172403, 0.08327674157670514,
+    0.06267204833410799, 0.040601429800386134, 0.017614007139152742};
+// effective packing fraction coefficients c_k(lambda) = sum_j Cm[k][j] lambda^-j (cpp/MieKinGas.h:243-249; T. Maltby 2024, no LRC)
+__constant__ double c_Cm[4][4] = {{0.6382, 0.9540, -31.9965, 83.7914}, {2.8596, -18.8315, 150.6853, -468.9992},
+                                  {-7.0331, 21.9390, -229.9483, 970.6560}, {5.5441, -4.0284, 106.4364, -679.1889}};
+// f_k(alpha) rational fits, Lafitte et al. J. Chem. Phys. 139, 154504 (2013) Table II (cpp/MieKinGas.h:265-275)
+__constant__ double c_phi[7][3] = {{7.5365557, -359.44, 1550.9}, {-37.60463, 1825.6, -5070.1}, {71.745953, -3168.0, 6534.6},
+                                   {-46.83552, 1884.2, -3288.7}, {-2.467982, -0.82376, -2.7171}, {-0.50272, -3.1935, 2.0883},
+                                   {8.0956883, 3.7090, 0.0}};
+// ln Omega* correlation, Fokin, Popov, Kalashnikov, High Temp. 37 (1999) (cpp/MieKinGas.h:199-217)
+__constant__ double c_ocf[2][6][4] = {
+    {{0., -0.145269e1, 0.294682e2, 0.242508e1}, {0.107782e-1, 0.587725, -0.180714e3, .595694e2}, {0.546646e-1, -0.651465e1, 0.374457e3, -0.137807e3},
+     {0.485352, 0.245523e2, -0.336782e3, 0.814187e2}, {-0.385355, -0.206868e2, 0.132246e3, 0.}, {0.847232e-1, 0.521812e1, -0.181140e2, -0.747215e1}},
+    {{0., 0.113086e1, 0.234799e2, 0.310127e1}, {0., 0.551559e1, -0.137023e3, 0.185848e2}, {0.325909e-1, -0.292925e2, 0.243761e3, 0.},
+     {0.697682, 0.590792e2, -0.143670e3, -0.123518e3}, {-0.564238, -0.430549e2, 0., 0.137282e3}, {0.126508, 0.104273e2, 0.150601e2, -0.408911e2}}};
+
+// Mie pair block as the assembly sees it (SI)
+struct MiePair { double sigma, eps, la, lr, C, alpha; };
+
+struct TModel {                 // per-model constants of the state-point stage
+    int nc;                     // internal component count (2 for single-component models)
+    int npairs_dev;             // pairs of the kg_model (1 for single-component models)
+    int is_singlecomp, is_idealgas, N, nlr;
+    double m[MAXC];             // particle masses
+    int pair_of[MAXC][MAXC];    // (i,j) -> pair index in the kg_model's tables
+    int lr_l[MAXLR], lr_r[MAXLR];
+};
+
+__device__ __forceinline__ double ipowd(double x, int n) { double r = 1.0; for (int k = 0; k < n; k++) r *= x; return r; }
+
+// ---- MieKinGas::omega correlation branch (cpp/MieKinGas.cpp:95-148) and the hard-sphere integral (cpp/MieKinGas.h:52-60) ----
+__device__ double corr_am(int l, int n, double lr) {
+    return c_ocf[l - 1][n - 1][0] + (c_ocf[l - 1][n - 1][1] / lr) + pow(lr, -2.) * (c_ocf[l - 1][n - 1][2] + c_ocf[l - 1][n - 1][3] * log(lr));
+}
+__device__ double corr_diag(int l, double lr, double Ts) {      // omega_correlation with l == r
+    double lnw = -(2. / lr) * log(Ts);
+    for (int n = 1; n < 7; n++) lnw += corr_am(l, n, lr) * pow(Ts, (1. - n) * 0.5);
+    if (l == 2) lnw += log(1. - (2. / (3. * lr)));
+    return exp(lnw);
+}
+// omega_correlation(l, r) = prod_{rr=l}^{r-1} omega_recursive_factor(l, rr) * omega_correlation(l, l), r <= 3.
+// Integer quirk kept: the reference writes (1 / (r + 2)) with int operands, which is 0, so the a_m sums of the
+// recursion factors vanish and only the leading terms survive (cpp/MieKinGas.cpp:129,141).
+__device__ double omega_correlation(int l, int r, double lr, double Ts) {
+    const double diag = corr_diag(l, lr, Ts);
+    double v = diag, f = 0.0;
+    for (int rr = l; rr < r; rr++) {
+        if (rr == l) f = 1. + ((-(2 / (lr * Ts))) * diag) / (rr + 2);
+        else f = 1 + (0.0 / ((rr + 2) * f)) + (f - 1) * (rr + 1) / (rr + 2);
+        v *= f;
+    }
+    return v;
+}
+
+// Omega of the correlation branch: omega_correlation * omega_hs. One thread per (t, pair, lr); mask says where it applies.
+__global__ void omega_correlation_kernel(int nT, int npairs, int nlr, const double* __restrict__ T, const MiePair* __restrict__ mp,
+                                         const int* __restrict__ pair_i, const int* __restrict__ pair_j, const double* __restrict__ mass,
+                                         const int* __restrict__ lr_l, const int* __restrict__ lr_r, const unsigned char* __restrict__ is_corr,
+                                         double* __restrict__ omega) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nT * npairs * nlr) return;
+    if (!is_corr[e]) return;
+    const int k = e % nlr, p = (e / nlr) % npairs, t = e / (nlr * npairs);
+    const int l = lr_l[k], r = lr_r[k], i = pair_i[p], j = pair_j[p];
+    const MiePair q = mp[p];
+    const double Ts = T[t] * BOLTZMANN / q.eps;
+    // omega_hs, cpp/MieKinGas.h:52-60
+    double w = PI_REF * pow(q.sigma, 2) * 0.5 * (r + 1);
+    for (int ri = r; ri > 1; ri--) w *= ri;
+    if (l % 2 == 0) w *= (1. - (1.0 / (l + 1.)));
+    double hs;
+    if (i == j) hs = sqrt((BOLTZMANN * T[t]) / (PI_REF * mass[i])) * w;
+    else hs = sqrt(BOLTZMANN * T[t] * (mass[i] + mass[j]) / (2. * PI_REF * mass[i] * mass[j])) * w;
+    omega[e] = omega_correlation(l, r, q.lr, Ts) * hs;
+}
+
+// Barker-Henderson diameters of the pure components, d_ii(T) (cpp/MieKinGas.cpp:314-332). One thread per (t, i).
+__global__ void bh_kernel(int nT, int nc, const double* __restrict__ T, const MiePair* __restrict__ diag, double* __restrict__ dbh) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nT * nc) return;
+    const int i = e % nc, t = e / nc;
+    const MiePair q = diag[i];
+    const double beta = 1. / (BOLTZMANN * T[t]);
+    double d = 2.;
+    for (int n = 0; n < 20; n++) {
+        const double r = q.sigma * (c_gl_x[n] / 4. + 3. / 4.);
+        const double u = q.C * q.eps * (pow(q.sigma / r, q.lr) - pow(q.sigma / r, q.la));
+        d += c_gl_w[n] * (1. - exp(-beta * u));
+    }
+    dbh[e] = d * (q.sigma / 4.);
+}
+
+// Bracket integrals from the Omega table and the host-built weights (cpp/KineticGas.cpp:644-705):
+//   H_ij = 8 M2^(p+1/2) M1^(q+1/2) sum A Omega ; H_i = 8 sum A' Omega ; L_ij = 16/3 sum B'' Omega ; L_i = 16/3 sum B' Omega
+// One thread per (t, i, j, p, q). Weights: wA [N][N][nlr]; wAp, wBp, wBpp [nc][nc][N][N][nlr]; hpre [nc][nc][N][N].
+// Output brk [nT][4][nc][nc][N][N].
+__global__ void bracket_kernel(int nT, TModel tm, const double* __restrict__ omega, const double* __restrict__ wA, const double* __restrict__ wAp,
+                               const double* __restrict__ wBp, const double* __restrict__ wBpp, const double* __restrict__ hpre,
+                               double* __restrict__ brk) {
+    const int N = tm.N, nc = tm.nc, nlr = tm.nlr;
+    const int per_t = nc * nc * N * N;
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nT * per_t) return;
+    const int t = e / per_t, rem = e % per_t;
+    const int q = rem % N, p = (rem / N) % N, j = (rem / (N * N)) % nc, i = rem / (N * N * nc);
+    const double* om = omega + ((size_t) t * tm.npairs_dev + tm.pair_of[i][j]) * nlr;
+    const double* a = wA + (size_t) (p * N + q) * nlr;
+    const size_t wo = ((size_t) ((i * nc + j) * N + p) * N + q) * nlr;
+    double hij = 0, hi = 0, lij = 0, li = 0;
+    for (int k = 0; k < nlr; k++) {
+        const double o = om[k];
+        if (a[k] != 0) hij += a[k] * o;
+        if (wAp[wo + k] != 0) hi += wAp[wo + k] * o;
+        if (wBpp[wo + k] != 0) lij += wBpp[wo + k] * o;
+        if (wBp[wo + k] != 0) li += wBp[wo + k] * o;
+    }
+    double* out = brk + (size_t) t * 4 * per_t;
+    out[rem] = hij * hpre[rem];
+    out[per_t + rem] = hi * 8;
+    out[2 * per_t + rem] = lij * (16.0 / 3.0);
+    out[3 * per_t + rem] = li * (16.0 / 3.0);
+}
+
+// ---- SAFT-VR Mie RDF at contact, second order (cpp/MieKinGas.cpp:157-276, 345-786) ----
+struct RdfCommon {      // what every pair of one (state point, density) shares
+    double rho, zx, dzx, zxs, KHS, dKHS, k0, k1, k2, k3;
+};
+
+__device__ void rdf_common(int nc, double rho, const double* x, const double* d /*[nc] BH diag*/, const MiePair* mp /*[nc*nc]*/, RdfCommon& c) {
+    double s = 0, ss = 0;
+    for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) {
+        const double dij = (i == j) ? d[i] : (d[i] + d[j]) / 2.0;
+        s += x[i] * x[j] * pow(dij, 3);
+        ss += x[i] * x[j] * pow(mp[i * nc + j].sigma, 3);
+    }
+    c.rho = rho;
+    c.zx = s * (PI_REF * rho / 6.0);           // zeta_x_func
+    c.dzx = s * (PI_REF / 6.0);                // dzetax_drho_func
+    c.zxs = ss * (PI_REF * rho / 6.0);         // zeta_x with sigma (rdf_chi_func, gamma_corr)
+    const double z = c.zx;
+    c.KHS = pow(1 - z, 4) / (1 + 4 * z + 4 * pow(z, 2) - 4 * pow(z, 3) + pow(z, 4));
+    // sign of the z^4 term differs from K_HS in the reference (cpp/MieKinGas.h:176-179); kept
+    c.dKHS = -4 * c.dzx * pow(1 - z, 3) * (2 + 5 * z - pow(z, 2) - 2 * pow(z, 3)) / pow(1 + 4 * z + 4 * pow(z, 2) - 4 * pow(z, 3) - pow(z, 4), 2);
+    c.k0 = -log(1 - z) + (42. * z - 39. * pow(z, 2) + 9. * pow(z, 3) - 2 * pow(z, 4)) / (6 * pow(1 - z, 3));
+    c.k1 = (pow(z, 4) + 6. * pow(z, 2) - 12. * z) / (2. * pow(1 - z, 3));
+    c.k2 = -3. * pow(z, 2) / (8. * pow(1 - z, 2));
+    c.k3 = (-pow(z, 4.) + 3. * pow(z, 2) + 3. * z) / (6. * pow(1 - z, 3));
+}
+
+// a1s + B and d(a1s + B)/drho for one exponent lambda of one pair
+__device__ void a1s_B(const RdfCommon& c, double eps, double d3, double x0, double lam, double& aB, double& daB) {
+    double ck[4];
+    for (int i = 0; i < 4; i++) { ck[i] = 0; for (int j = 0; j < 4; j++) ck[i] += c_Cm[i][j] * pow(lam, (double) -j); }
+    double ze = 0, dze = 0;
+    for (int i = 0; i < 4; i++) { ze += ck[i] * pow(c.zx, (double) (i + 1)); dze += ck[i] * (i + 1) * pow(c.zx, (double) i) * c.dzx; }
+    const double a1s = (-2. * c.rho * PI_REF * eps * d3 / (lam - 3)) * (1. - ze / 2.) / pow(1. - ze, 3);
+    const double da1s = -2. * (PI_REF * eps * d3 / (lam - 3)) * (((1. - ze / 2.) / pow(1 - ze, 3)) + c.rho * dze * (2.5 - ze) / pow(1 - ze, 4));
+    const double I = -(pow(x0, 3. - lam) - 1.) / (lam - 3.);
+    const double J = -(pow(x0, 4. - lam) * (lam - 3.) - pow(x0, 3. - lam) * (lam - 4.) - 1.) / ((lam - 3.) * (lam - 4.));
+    const double zx = c.zx;
+    const double B = 2. * PI_REF * c.rho * d3 * eps * (I * (1. - zx / 2.) / pow(1. - zx, 3) - J * 9. * zx * (1. + zx) / (2. * pow(1. - zx, 3)));
+    const double dB = B / c.rho + 2. * PI_REF * c.rho * eps * d3
+                      * (I * (-0.5 * (1 - zx) + 3. * (1. - 0.5 * zx)) / pow(1 - zx, 4)
+                         - J * (9. * (1. + 2. * zx) * (1. - zx) + 27. * zx * (1. + zx)) / (2. * pow(1 - zx, 4))) * c.dzx;
+    aB = a1s + B;
+    daB = da1s + dB;
+}
+
+__device__ double rdf_pair(const RdfCommon& c, const MiePair& q, double dij, double T) {
+    const double x0 = q.sigma / dij, d3 = pow(dij, 3), eps = q.eps, la = q.la, lr = q.lr, C = q.C, rho = c.rho;
+    const double gHS = exp(c.k0 + c.k1 * x0 + c.k2 * pow(x0, 2) + c.k3 * pow(x0, 3));
+    double aB_la, daB_la, aB_lr, daB_lr, aB_2la, daB_2la, aB_2lr, daB_2lr, aB_lalr, daB_lalr;
+    a1s_B(c, eps, d3, x0, la, aB_la, daB_la);
+    a1s_B(c, eps, d3, x0, lr, aB_lr, daB_lr);
+    a1s_B(c, eps, d3, x0, 2 * la, aB_2la, daB_2la);
+    a1s_B(c, eps, d3, x0, 2 * lr, aB_2lr, daB_2lr);
+    a1s_B(c, eps, d3, x0, la + lr, aB_lalr, daB_lalr);
+    const double x_la = pow(x0, la), x_lr = pow(x0, lr), x_2la = pow(x0, 2 * la), x_2lr = pow(x0, 2 * lr), x_lalr = pow(x0, la + lr);
+    // g1 (rdf_g1_func)
+    const double da1 = C * (x_la * daB_la - x_lr * daB_lr);
+    const double g1 = (1.0 / (2. * PI_REF * eps * d3)) * (3. * da1 - C * la * x_la * aB_la / rho + C * lr * x_lr * aB_lr / rho);
+    // g2 (rdf_g2_func with g2_correction = true)
+    double f[3];
+    for (int i = 0; i < 3; i++) {
+        double num = 0.0, den = 1.0;
+        for (int n = 0; n <= 3; n++) num += c_phi[n][i] * pow(q.alpha, (double) n);
+        for (int n = 4; n <= 6; n++) den += c_phi[n][i] * pow(q.alpha, (double) (n - 3));
+        f[i] = num / den;
+    }
+    const double chi = f[0] * c.zxs + f[1] * pow(c.zxs, 5) + f[2] * pow(c.zxs, 8);
+    const double a2 = .5 * c.KHS * (1 + chi) * eps * pow(C, 2) * (x_2la * aB_2la - 2 * x_lalr * aB_lalr + x_2lr * aB_2lr);
+    const double da2_div_chi = c.dKHS * (a2 / (c.KHS * (1 + chi)))
+                             + .5 * c.KHS * eps * pow(C, 2) * (x_2la * daB_2la - 2 * x_lalr * daB_lalr + x_2lr * daB_2lr);
+    const double theta = exp(eps / (BOLTZMANN * T)) - 1.;
+    const double gamma_c = 10. * (1 - tanh(10. * (0.57 - q.alpha))) * c.zxs * theta * exp(-6.7 * c.zxs + -8. * pow(c.zxs, 2));
+    const double g2 = (1 + gamma_c) * (1. / (2 * PI_REF * pow(eps, 2) * d3))
+                    * (3 * da2_div_chi + eps * c.KHS * pow(C, 2) * (-lr * x_2lr * aB_2lr / rho + (la + lr) * x_lalr * aB_lalr / rho - la * x_2la * aB_2la / rho));
+    const double be = (1. / (BOLTZMANN * T)) * eps;
+    return gHS * exp(be * (g1 / gHS) + pow(be, 2) * (g2 / gHS));
+}
+
+// One thread per (state point, slot, i <= j). slot 0: the state point's density; slot 1: N_A / 1e12 (the dilute viscosity of the
+// internal-conductivity term, cpp/KineticGas_properties.cpp:133). rdf [n][nslots][nc][nc].
+__global__ void rdf_kernel(int n, int nslots, TModel tm, const int* __restrict__ tidx, const double* __restrict__ T_of, const double* __restrict__ Vm,
+                           const double* __restrict__ x, const double* __restrict__ dbh, const MiePair* __restrict__ mp, double* __restrict__ rdf) {
+    const int nc = tm.nc, npu = nc * (nc + 1) / 2;
+    const long long e = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= (long long) n * nslots * npu) return;
+    const int pu = (int) (e % npu), slot = (int) ((e / npu) % nslots), sp = (int) (e / ((long long) npu * nslots));
+    int i = 0, rest = pu;
+    while (rest >= nc - i) { rest -= nc - i; i++; }
+    const int j = i + rest;
+    double xs[MAXC];
+    for (int k = 0; k < nc; k++) xs[k] = tm.is_singlecomp ? 0.5 : x[(size_t) sp * nc + k];
+    const int t = tidx[sp];
+    const double rho = (slot == 0) ? AVOGADRO / Vm[sp] : AVOGADRO / 1e12;
+    const double* d = dbh + (size_t) t * nc;
+    RdfCommon c;
+    rdf_common(nc, rho, xs, d, mp, c);
+    const double dij = (i == j) ? d[i] : (d[i] + d[j]) / 2.0;
+    const double g = rdf_pair(c, mp[i * nc + j], dij, T_of[t]);
+    double* out = rdf + ((size_t) sp * nslots + slot) * nc * nc;
+    out[i * nc + j] = g;
+    out[j * nc + i] = g;
+}
+
+// ---- per-state-point assembly, LU and property formulas ----
+struct StateArgs {
+    int n, nslots, nT;
+    kg_transport_opts opt;
+    const int* tidx; const double* T_of; const double* Vm; const double* x;
+    const double* rdf;          // [n][nslots][nc][nc]
+    const double *mtl, *etl;    // [nT][npairs_dev] (null for ideal gas)
+    const double* brk;          // [nT][4][nc][nc][N][N]
+    const double *dmudn, *cp_ideal, *pressure, *dvdn;
+    double *viscosity, *conductivity, *contribs, *D, *DT, *K, *Kp, *cond_matrix, *cond_vector, *visc_matrix, *visc_vector;
+    int* status;
+};
+
+// Unblocked partial-pivot LU, the algorithm Eigen's partialPivLu runs for sizes <= 16 (row-max pivot, first maximum wins,
+// column scaled by division, rank-1 update with separately rounded multiply and subtract). A is n x n row-major, stride ld.
+__device__ int lu_factor(double* A, int n, int ld, int* piv) {
+    int singular = 0;
+    for (int k = 0; k < n; k++) {
+        int pr = k; double best = fabs(A[k * ld + k]);
+        for (int i = k + 1; i < n; i++) { const double v = fabs(A[i * ld + k]); if (v > best) { best = v; pr = i; } }
+        piv[k] = pr;
+        if (best != 0.0) {
+            if (pr != k) for (int j = 0; j < n; j++) { const double t = A[k * ld + j]; A[k * ld + j] = A[pr * ld + j]; A[pr * ld + j] = t; }
+            const double d = A[k * ld + k];
+            for (int i = k + 1; i < n; i++) A[i * ld + k] /= d;
+        }
+        else singular = 1;
+        for (int i = k + 1; i < n; i++) {
+            const double lik = A[i * ld + k];
+            for (int j = k + 1; j < n; j++) A[i * ld + j] = __dsub_rn(A[i * ld + j], __dmul_rn(lik, A[k * ld + j]));
+        }
+    }
+    return singular;
+}
+__device__ void lu_solve(const double* A, int n, int ld, const int* piv, double* b) {
+    for (int k = 0; k < n; k++) if (piv[k] != k) { const double t = b[k]; b[k] = b[piv[k]]; b[piv[k]] = t; }
+    for (int i = 1; i < n; i++) { double s = b[i]; for (int j = 0; j < i; j++) s = __dsub_rn(s, __dmul_rn(A[i * ld + j], b[j])); b[i] = s; }
+    for (int i = n - 1; i >= 0; i--) { double s = b[i]; for (int j = i + 1; j < n; j++) s = __dsub_rn(s, __dmul_rn(A[i * ld + j], b[j])); b[i] = s / A[i * ld + i]; }
+}
+
+struct SP {                     // one state point's scalars, all lanes keep them in registers / local memory
+    int nc, N, t;
+    double T, rho, Vm;
+    double x[MAXC], wt[MAXC];
+};
+
+__device__ __forceinline__ double brk_at(const StateArgs& a, const TModel& tm, int t, int which, int i, int j, int p, int q) {
+    const int per_t = tm.nc * tm.nc * tm.N * tm.N;
+    return a.brk[((size_t) t * 4 + which) * per_t + ((i * tm.nc + j) * tm.N + p) * tm.N + q];
+}
+
+// Lambda (cpp/KineticGas.cpp:271-318) into A (n x n, n = N nc)
+__device__ void build_cond_matrix(const StateArgs& a, const TModel& tm, const SP& s, const double* g, double* A, int ld) {
+    const int nc = s.nc, N = s.N, n = N * nc;
+    for (int r = 0; r < n; r++) for (int c = 0; c < n; c++) A[r * ld + c] = 0.0;
+    for (int i = 0; i < nc; i++) A[i] = s.wt[i];
+    for (int p = 0; p < N; p++) for (int i = 0; i < nc; i++) {
+        if (i == 0 && p == 0) continue;                     // replaced by the weight-fraction row
+        const int row = (i == 0) ? p : N + (nc - 1) * p + (i - 1);
+        for (int q = 0; q < N; q++) for (int j = 0; j < nc; j++) {
+            double v = s.x[i] * s.x[j] * g[i * nc + j] * brk_at(a, tm, s.t, 0, i, j, p, q);
+            if (i == j) for (int l = 0; l < nc; l++) v += s.x[i] * s.x[l] * g[i * nc + l] * brk_at(a, tm, s.t, 1, i, l, p, q);
+            v *= 8. * sqrt(tm.m[i] * tm.m[j]) / (75. * pow(BOLTZMANN, 2) * s.T);
+            A[row * ld + nc * q + j] = v;
+        }
+    }
+}
+
+// B (cpp/KineticGas.cpp:418-439)
+__device__ void build_visc_matrix(const StateArgs& a, const TModel& tm, const SP& s, const double* g, double* A, int ld) {
+    const int nc = s.nc, N = s.N;
+    for (int p = 0; p < N; p++) for (int i = 0; i < nc; i++) for (int q = 0; q < N; q++) for (int j = 0; j < nc; j++) {
+        double v = s.x[i] * s.x[j] * g[i * nc + j] * brk_at(a, tm, s.t, 2, i, j, p, q);
+        if (i == j) for (int k = 0; k < nc; k++) v += s.x[i] * s.x[k] * g[i * nc + k] * brk_at(a, tm, s.t, 3, i, k, p, q);
+        v *= 2. / (5. * BOLTZMANN * s.T);
+        A[(p * nc + i) * ld + q * nc + j] = v;
+    }
+}
+
+// K and K' (cpp/KineticGas.cpp:207-239); tl3 = etl^3 or mtl^3 by pair
+__device__ void k_factors(const StateArgs& a, const TModel& tm, const SP& s, double rho, const double* g, double* K, double* Kp) {
+    const int nc = s.nc;
+    for (int i = 0; i < nc; i++) {
+        if (tm.is_idealgas) { K[i] = 1.; Kp[i] = 1.; continue; }
+        double k = 0, kp = 0;
+        for (int j = 0; j < nc; j++) {
+            const int pr = tm.pair_of[i][j];
+            const double Mij = tm.m[i] / (tm.m[i] + tm.m[j]), Mji = tm.m[j] / (tm.m[j] + tm.m[i]);
+            const double etl = a.etl[(size_t) s.t * tm.npairs_dev + pr], mtl = a.mtl[(size_t) s.t * tm.npairs_dev + pr];
+            k += s.x[j] * pow(etl, 3) * Mij * Mji * g[i * nc + j];
+            kp += s.x[j] * Mji * pow(mtl, 3.) * g[i * nc + j];
+        }
+        K[i] = k * (24. * PI_REF * rho / 15) + 1;
+        Kp[i] = kp * (8. * PI_REF * rho / 15) + 1.;
+    }
+}
+
+// KineticGas::viscosity at (T, rho) with the given rdf (cpp/KineticGas_properties.cpp:28-58). A, piv, b are scratch.
+__device__ double viscosity_at(const StateArgs& a, const TModel& tm, const SP& s, double rho, const double* g, const double* Kp,
+                               double* A, int ld, int* piv, double* b, int& st, double* mat_out, double* vec_out) {
+    const int nc = s.nc, N = s.N, n = N * nc;
+    build_visc_matrix(a, tm, s, g, A, ld);
+    for (int i = 0; i < n; i++) b[i] = 0.0;
+    for (int i = 0; i < nc; i++) b[i] = 2. * s.x[i] * Kp[i] / (BOLTZMANN * s.T);
+    if (mat_out) for (int r = 0; r < n; r++) for (int c = 0; c < n; c++) mat_out[r * n + c] = A[r * ld + c];
+    if (vec_out) for (int i = 0; i < n; i++) vec_out[i] = b[i];
+    if (lu_factor(A, n, ld, piv)) st |= KG_STATUS_SINGULAR;
+    lu_solve(A, n, ld, piv, b);
+    double eta_p = 0.0;
+    for (int i = 0; i < nc; i++) eta_p += Kp[i] * s.x[i] * b[i];
+    eta_p *= BOLTZMANN * s.T / 2.0;
+    if (tm.is_idealgas) return eta_p;
+    double eta_pp = 0.0;
+    for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) {
+        const double mtl = a.mtl[(size_t) s.t * tm.npairs_dev + tm.pair_of[i][j]];
+        eta_pp += sqrt(tm.m[i] * tm.m[j] / (tm.m[i] + tm.m[j])) * s.x[i] * s.x[j] * pow(mtl, 4) * g[i * nc + j];
+    }
+    eta_pp *= 4.0 * pow(rho, 2) * sqrt(2.0 * PI_REF * BOLTZMANN * s.T) / 15.0;
+    return eta_p + eta_pp;
+}
+
+template<int MAXN>
+__global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
+    const int sp = blockIdx.x * blockDim.x + threadIdx.x;
+    if (sp >= a.n) return;
+    const int nc = tm.nc, N = tm.N, n = N * nc, ld = MAXN;
+    const unsigned props = a.opt.properties;
+    int st = 0;
+    SP s; s.nc = nc; s.N = N; s.t = a.tidx[sp];
+    const int nD = a.opt.do_compress ? (nc - 1) : nc;
+    if (s.t < 0) {          // temperature not in the cache: poison the outputs, flag, leave
+        const double qnan = nan("");
+        if (a.viscosity) a.viscosity[sp] = qnan;
+        if (a.conductivity) a.conductivity[sp] = qnan;
+        if (a.contribs) for (int k = 0; k < 3; k++) a.contribs[(size_t) sp * 3 + k] = qnan;
+        if (a.D) for (int k = 0; k < nD * nD; k++) a.D[(size_t) sp * nD * nD + k] = qnan;
+        if (a.DT) for (int k = 0; k < nc; k++) a.DT[(size_t) sp * nc + k] = qnan;
+        if (a.status) a.status[sp] = KG_STATUS_T_NOT_CACHED;
+        return;
+    }
+    s.T = a.T_of[s.t]; s.Vm = a.Vm[sp]; s.rho = AVOGADRO / s.Vm;
+    double wsum = 0.0;
+    for (int i = 0; i < nc; i++) { s.x[i] = tm.is_singlecomp ? 0.5 : a.x[(size_t) sp * nc + i]; wsum += s.x[i] * tm.m[i]; }
+    for (int i = 0; i < nc; i++) s.wt[i] = s.x[i] * tm.m[i] / wsum;
+    double g[MAXC * MAXC], K[MAXC], Kp[MAXC];
+    for (int k = 0; k < nc * nc; k++) g[k] = tm.is_idealgas ? 1.0 : a.rdf[((size_t) sp * a.nslots) * nc * nc + k];
+    k_factors(a, tm, s, s.rho, g, K, Kp);
+    if (a.K) for (int i = 0; i < nc; i++) a.K[(size_t) sp * nc + i] = K[i];
+    if (a.Kp) for (int i = 0; i < nc; i++) a.Kp[(size_t) sp * nc + i] = Kp[i];
+
+    double A[MAXN * MAXN], b[MAXN], th[MAXN], dsol[MAXC * MAXN];
+    int piv[MAXN];
+    const bool single = tm.is_singlecomp != 0;
+    if (props & (KG_PROP_CONDUCTIVITY | KG_PROP_DIFFUSION | KG_PROP_THERMAL_DIFFUSION)) {
+        build_cond_matrix(a, tm, s, g, A, ld);
+        if (a.cond_matrix) for (int r = 0; r < n; r++) for (int c = 0; c < n; c++) a.cond_matrix[((size_t) sp * n + r) * n + c] = A[r * ld + c];
+        if (lu_factor(A, n, ld, piv)) st |= KG_STATUS_SINGULAR;
+        const bool need_th = (props & (KG_PROP_CONDUCTIVITY | KG_PROP_THERMAL_DIFFUSION)) != 0;
+        const bool need_d = (props & (KG_PROP_DIFFUSION | KG_PROP_THERMAL_DIFFUSION)) || ((props & KG_PROP_CONDUCTIVITY) && !single && N > 1);
+        if (need_th || a.cond_vector) {
+            // get_conductivity_vector, cpp/KineticGas.cpp:320-330 (needs N >= 2)
+            for (int i = 0; i < n; i++) th[i] = 0.0;
+            if (N > 1) {
+                th[1] = s.x[0] * K[0] * 4. / (5. * BOLTZMANN);
+                for (int i = 1; i < nc; i++) th[N + (nc - 1) + (i - 1)] = s.x[i] * K[i] * 4. / (5. * BOLTZMANN);
+            }
+            if (a.cond_vector) for (int i = 0; i < n; i++) a.cond_vector[(size_t) sp * n + i] = th[i];
+            lu_solve(A, n, ld, piv, th);
+        }
+        if (need_d) {
+            // get_diffusion_vector, cpp/KineticGas.cpp:390-403: block k of the block-diagonal system, d[q][i][k] = dsol[k][nc q + i]
+            for (int k = 0; k < nc; k++) {
+                double* dk = dsol + k * MAXN;
+                for (int i = 0; i < n; i++) dk[i] = 0.0;
+                for (int i = 1; i < nc; i++) {
+                    double v = -8. * s.wt[i] / (25. * BOLTZMANN);
+                    if (i == k) v += 8. / (25. * BOLTZMANN);
+                    dk[N + (i - 1)] = v;
+                }
+                lu_solve(A, n, ld, piv, dk);
+            }
+        }
+        // E_ij and ksi (cpp/KineticGas_properties.cpp:459-500), frame matrices (:348-396), D in the centre-of-mass frame (:332-346)
+        double E[MAXC * MAXC], ksi[MAXC], psi[MAXC * MAXC], Dcom[MAXC * MAXC], Dd[MAXC * MAXC];
+        int dep = a.opt.dependent_idx;
+        if (dep < 0 && a.opt.frame_of_reference == KG_FOR_SOLVENT) dep = a.opt.solvent_idx;
+        while (dep < 0) dep += nc;
+        const bool want_E = a.dmudn != nullptr && (props & (KG_PROP_DIFFUSION | KG_PROP_THERMAL_DIFFUSION));
+        if (want_E) {
+            if (single) {
+                const double dp = s.Vm * a.dmudn[sp], RT = GAS_CONSTANT * s.T, rm = 1 / s.Vm;
+                E[0] = (dp + RT * s.x[1] / (rm * s.x[0])) / AVOGADRO;
+                E[1] = E[2] = (dp - RT / rm) / AVOGADRO;
+                E[3] = (dp + RT * s.x[0] / (rm * s.x[1])) / AVOGADRO;
+            }
+            else for (int k = 0; k < nc * nc; k++) E[k] = s.Vm * a.dmudn[(size_t) sp * nc * nc + k] / AVOGADRO;
+            for (int i = 0; i < nc; i++) { const double ni = s.x[i] / s.Vm; for (int j = 0; j < nc; j++) E[i * nc + j] = (ni / (BOLTZMANN * s.T)) * E[i * nc + j]; }
+            for (int i = 0; i < nc; i++) { ksi[i] = 0.; for (int j = 0; j < nc; j++) ksi[i] += E[j * nc + i]; }
+            for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) {
+                double v = (i == j) ? 1.0 : 0.0;
+                switch (a.opt.frame_of_reference) {
+                    case KG_FOR_CON: v += s.x[i] * ((s.wt[j] / s.x[j]) - 1); break;
+                    case KG_FOR_SOLVENT: v += s.x[i] * ((s.wt[j] / s.x[j]) - ((j == a.opt.solvent_idx ? 1 : 0) / s.x[a.opt.solvent_idx])); break;
+                    case KG_FOR_COV: v += s.x[i] * ((s.wt[j] / s.x[j]) - (a.dvdn[(size_t) sp * (single ? 1 : nc) + (single ? 0 : j)] / s.Vm)); break;
+                    default: break;
+                }
+                psi[i * nc + j] = v;
+            }
+            for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) {
+                double v = 0.0;
+                for (int k = 0; k < nc; k++) v += dsol[k * MAXN + i] * E[k * nc + j];       // d[0][i][k]
+                Dcom[i * nc + j] = v * (s.x[i] / (2 * s.rho));
+            }
+            for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) {
+                double v = 0.0;
+                for (int k = 0; k < nc; k++) v += psi[i * nc + k] * Dcom[k * nc + j];
+                Dd[i * nc + j] = v;
+            }
+        }
+        if (want_E && (props & KG_PROP_DIFFUSION) && a.D) {
+            int oi = 0;
+            for (int i = 0; i < nc; i++) {
+                if (a.opt.do_compress && i == dep) continue;
+                int oj = 0;
+                for (int j = 0; j < nc; j++) {
+                    if (a.opt.do_compress && j == dep) continue;
+                    a.D[((size_t) sp * nD + oi) * nD + oj] = Dd[i * nc + j] - (ksi[j] / ksi[dep]) * Dd[i * nc + dep];
+                    oj++;
+                }
+                oi++;
+            }
+        }
+        if (want_E && (props & KG_PROP_THERMAL_DIFFUSION) && a.DT) {
+            // cpp/KineticGas_properties.cpp:208-258
+            double bm[MAXC * MAXC], DT[MAXC], DT2[MAXC];
+            for (int j = 0; j < nc; j++) for (int k = 0; k < nc; k++) {
+                double v = (j == k) ? 1.0 : 0.0;
+                if (!tm.is_idealgas) {
+                    const double etl = a.etl[(size_t) s.t * tm.npairs_dev + tm.pair_of[j][k]];
+                    v += (4. * PI_REF / 3) * s.rho * s.x[k] * pow(etl, 3) * (tm.m[j] / (tm.m[j] + tm.m[k])) * g[j * nc + k];
+                }
+                bm[j * nc + k] = v;
+            }
+            for (int i = 0; i < nc; i++) {
+                double outer = 0.;
+                for (int j = 0; j < nc; j++) {
+                    double inner = 0.;
+                    for (int k = 0; k < nc; k++) inner += bm[j * nc + k];
+                    outer += dsol[j * MAXN + i] * s.x[j] * inner;
+                }
+                DT[i] = (s.x[i] / 2.) * (th[i] - outer);
+            }
+            for (int i = 0; i < nc; i++) { double v = 0.; for (int k = 0; k < nc; k++) v += psi[i * nc + k] * DT[k]; DT2[i] = v; }
+            double tmp = 0.;
+            for (int k = 0; k < nc; k++) for (int mm = 0; mm < nc; mm++) tmp += s.rho * s.x[mm] * bm[mm * nc + k];
+            for (int i = 0; i < nc; i++) a.DT[(size_t) sp * nc + i] = (DT2[i] + (Dd[i * nc + dep] / ksi[dep]) * tmp) / AVOGADRO;
+        }
+        if ((props & KG_PROP_CONDUCTIVITY) && a.cp_ideal) {
+            // thermal_conductivity_contributions "tdi", cpp/KineticGas_properties.cpp:74-141
+            double dth[MAXC];
+            for (int i = 0; i < nc; i++) dth[i] = 0.0;
+            if (!single && N > 1) {
+                // compute_dth_vector (:432-447): (d[0] / d000) dth = l / d000
+                double dm[MAXC * MAXC]; int pv[MAXC];
+                const double d000 = dsol[0];
+                for (int i = 0; i < nc; i++) { for (int j = 0; j < nc; j++) dm[i * MAXC + j] = dsol[j * MAXN + i] / d000; dth[i] = th[i] / d000; }
+                if (lu_factor(dm, nc, MAXC, pv)) st |= KG_STATUS_SINGULAR;
+                lu_solve(dm, nc, MAXC, pv, dth);
+            }
+            double lam_t = 0.;
+            for (int i = 0; i < nc; i++) {
+                double tmp = 0.;
+                if (!single && N > 1) for (int k = 0; k < nc; k++) tmp += dsol[k * MAXN + nc + i] * dth[k];      // d[1][i][k]
+                lam_t += s.x[i] * K[i] * (th[nc + i] - tmp);
+            }
+            lam_t *= (5. * BOLTZMANN / 4.);
+            double lam_d = 0.;
+            if (!tm.is_idealgas) {
+                for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) {
+                    const double etl = a.etl[(size_t) s.t * tm.npairs_dev + tm.pair_of[i][j]];
+                    lam_d += pow(s.rho, 2) * sqrt(2 * PI_REF * tm.m[i] * tm.m[j] * BOLTZMANN * s.T / (tm.m[i] + tm.m[j]))
+                             * (s.x[i] * s.x[j]) / (tm.m[i] + tm.m[j]) * pow(etl, 4) * g[i * nc + j];
+                }
+                lam_d *= (4. * BOLTZMANN / 3.);
+            }
+            double lam_i = 0., cpf = 0.;
+            if (single) cpf = (a.cp_ideal[sp] - 5. * GAS_CONSTANT / 2.) / (tm.m[0] * AVOGADRO * 1e3);
+            else for (int i = 0; i < nc; i++) cpf += s.x[i] * (a.cp_ideal[(size_t) sp * nc + i] - 5. * GAS_CONSTANT / 2.) / (tm.m[i] * AVOGADRO * 1e3);
+            if (1.32e3 * cpf > 1e-8) {
+                // viscosity(T, Vm = 1e12, x, N): rdf slot 1
+                double g0[MAXC * MAXC], K0[MAXC], Kp0[MAXC];
+                const double rho0 = AVOGADRO / 1e12;
+                for (int k = 0; k < nc * nc; k++) g0[k] = tm.is_idealgas ? 1.0 : a.rdf[((size_t) sp * a.nslots + 1) * nc * nc + k];
+                k_factors(a, tm, s, rho0, g0, K0, Kp0);
+                const double eta0 = viscosity_at(a, tm, s, rho0, g0, Kp0, A, ld, piv, b, st, nullptr, nullptr);
+                lam_i = 1.32e3 * eta0 * cpf;
+            }
+            if (a.contribs) { a.contribs[(size_t) sp * 3] = lam_t; a.contribs[(size_t) sp * 3 + 1] = lam_d; a.contribs[(size_t) sp * 3 + 2] = lam_i; }
+            if (a.conductivity) a.conductivity[sp] = lam_t + lam_d + lam_i;
+        }
+    }
+    if (props & KG_PROP_VISCOSITY) {
+        const double eta = viscosity_at(a, tm, s, s.rho, g, Kp, A, ld, piv, b, st,
+                                        a.visc_matrix ? a.visc_matrix + (size_t) sp * n * n : nullptr, a.visc_vector ? a.visc_vector + (size_t) sp * n : nullptr);
+        if (a.viscosity) a.viscosity[sp] = eta;
+    }
+    if (a.status) a.status[sp] = st;
+}
+
+} // namespace
+
+// ================================================================================================================
+// host side
+// ================================================================================================================
+struct kg_tcache {
+    kg_model* m = nullptr;
+    int device = 0;
+    kg_transport_opts opt{};
+    TModel tm{};
+    int nT = 0;
+    bool mie = false;
+    std::vector<double> T;
+    std::map<double, int> index_of;
+    std::vector<unsigned char> is_corr;              // [nT][npairs][nlr]
+    double *d_T = nullptr, *d_omega = nullptr, *d_mtl = nullptr, *d_etl = nullptr, *d_dbh = nullptr, *d_brk = nullptr;
+    MiePair* d_mp_int = nullptr;                     // [nc][nc] internal pairs
+    std::vector<double> h_mtl, h_etl;
+    double ms_omega = 0, ms_tl = 0;                  // stage timings of the build (host clock around synchronised stages)
+};
+
+namespace {
+
+template<class T> cudaError_t upload(T** dptr, const std::vector<T>& v) {
+    cudaError_t e = cudaMalloc(dptr, std::max<size_t>(1, v.size()) * sizeof(T));
+    if (e != cudaSuccess) return e;
+    return cudaMemcpy(*dptr, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
+}
+
+bool desc_is_mie(const kg_potential_desc& d) {
+    return d.kind == KG_POT_POWER_SUM && d.nterms == 2 && d.C[0] > 0 && d.C[1] == -d.C[0] && d.lam[0] > d.lam[1];
+}
+
+} // namespace
+
+extern "C" void kg_tcache_destroy(kg_tcache* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    void* ptrs[] = {c->d_T, c->d_omega, c->d_mtl, c->d_etl, c->d_dbh, c->d_brk, c->d_mp_int};
+    for (void* p : ptrs) if (p) cudaFree(p);
+    delete c;
+}
+
+extern "C" int kg_tcache_lr(const kg_tcache* c, int32_t* l, int32_t* r) {
+    if (!c) return -1;
+    for (int k = 0; k < c->tm.nlr; k++) { if (l) l[k] = c->tm.lr_l[k]; if (r) r[k] = c->tm.lr_r[k]; }
+    return c->tm.nlr;
+}
+
+extern "C" int kg_tcache_fetch(kg_tcache* c, double* omega, double* mtl, double* etl, uint8_t* is_correlation) {
+    if (!c) return -1;
+    kg_model* m = c->m;
+    auto set_error = [&](const std::string& s) { m->err = s; };
+    CUDA_OK(cudaSetDevice(m->device));
+    const size_t no = (size_t) c->nT * m->npairs * c->tm.nlr;
+    if (omega) CUDA_OK(cudaMemcpy(omega, c->d_omega, no * sizeof(double), cudaMemcpyDeviceToHost));
+    const size_t nt = (size_t) c->nT * m->npairs;
+    if (mtl) for (size_t k = 0; k < nt; k++) mtl[k] = c->h_mtl.empty() ? 0.0 : c->h_mtl[k];
+    if (etl) for (size_t k = 0; k < nt; k++) etl[k] = c->h_etl.empty() ? 0.0 : c->h_etl[k];
+    if (is_correlation) memcpy(is_correlation, c->is_corr.data(), no);
+    return 0;
+}
+
+extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int nT, const double* T, const double* coeff_T, kg_tcache** out) {
+    if (!m) return -1;
+    auto set_error = [&](const std::string& s) { m->err = s; };
+    if (!opts || nT < 1 || !T || !out) { set_error("kg_tcache_create: invalid argument"); return -1; }
+    const int N = opts->N;
+    if (N < 1 || N > MAXO) { set_error("kg_tcache_create: Enskog order N out of range"); return -1; }
+    const int nc = m->is_singlecomp ? 2 : m->ncomps;
+    if (nc > MAXC) { set_error("kg_tcache_create: too many components"); return -1; }
+    if (m->is_singlecomp && m->ncomps != 1) { set_error("kg_tcache_create: single-component models are created with ncomps = 1"); return -1; }
+    bool mie = true;
+    for (auto& d : m->descs) mie = mie && desc_is_mie(d);
+    if (!opts->is_idealgas && (!mie || coeff_T)) {
+        set_error("RDF model is not implemented. Model is only available for ideal gas!");     // cpp/KineticGas.h:259
+        return -1;
+    }
+    CUDA_OK(cudaSetDevice(m->device));
+    kg_tcache* c = new kg_tcache;
+    c->m = m; c->device = m->device; c->opt = *opts; c->nT = nT; c->mie = mie;
+    c->T.assign(T, T + nT);
+    for (int t = 0; t < nT; t++) c->index_of.emplace(T[t], t);
+    TModel& tm = c->tm;
+    tm.nc = nc; tm.npairs_dev = m->npairs; tm.is_singlecomp = m->is_singlecomp; tm.is_idealgas = opts->is_idealgas; tm.N = N;
+    for (int i = 0; i < nc; i++) tm.m[i] = m->mass[m->is_singlecomp ? 0 : i];
+    std::vector<int> pair_i, pair_j;
+    for (int i = 0; i < m->ncomps; i++) for (int j = i; j < m->ncomps; j++) { pair_i.push_back(i); pair_j.push_back(j); }
+    for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) {
+        if (m->is_singlecomp) { tm.pair_of[i][j] = 0; continue; }
+        const int a = std::min(i, j), b = std::max(i, j);
+        tm.pair_of[i][j] = a * m->ncomps - a * (a - 1) / 2 + (b - a);
+    }
+    // (l,r) sets: conductivity / diffusion l = 1..N, r = l..2N-l (cpp/KineticGas_mthr.cpp:62-73); viscosity l = 1..N+1,
+    // r = l..2N+2-l where some B' or B'' is non-zero (:102-125)
+    const unsigned props = opts->properties;
+    const bool want_cond = props & (KG_PROP_CONDUCTIVITY | KG_PROP_DIFFUSION | KG_PROP_THERMAL_DIFFUSION);
+    const bool want_visc = props & (KG_PROP_VISCOSITY | KG_PROP_CONDUCTIVITY);
+    auto Mof = [&](int i, int j) { return tm.m[i] / (tm.m[i] + tm.m[j]); };
+    tm.nlr = 0;
+    auto lr_index = [&](int l, int r) { for (int k = 0; k < tm.nlr; k++) if (tm.lr_l[k] == l && tm.lr_r[k] == r) return k; return -1; };
+    for (int l = 1; l <= N + 1; l++) for (int r = l; r <= 2 * N + 2 - l; r++) {
+        bool use = want_cond && l <= N && r <= 2 * N - l;
+        if (!use && want_visc) {
+            for (int i = 0; i < nc && !use; i++) for (int j = 0; j < nc && !use; j++) for (int p = 0; p < N && !use; p++) for (int q = 0; q < N && !use; q++)
+                use = weight_B_dblprime(p, q, r, l, Mof(i, j), Mof(j, i)) != 0 || weight_B_prime(p, q, r, l, Mof(i, j), Mof(j, i)) != 0;
+        }
+        if (use) {
+            if (tm.nlr >= MAXLR) { set_error("kg_tcache_create: (l,r) table overflow"); delete c; return -1; }
+            tm.lr_l[tm.nlr] = l; tm.lr_r[tm.nlr] = r; tm.nlr++;
+        }
+    }
+    const int nlr = tm.nlr, Np = m->npairs;
+    // weight tables
+    std::vector<double> wA((size_t) N * N * nlr, 0.0), wAp((size_t) nc * nc * N * N * nlr, 0.0), wBp(wAp.size(), 0.0), wBpp(wAp.size(), 0.0),
+                        hpre((size_t) nc * nc * N * N, 0.0);
+    std::vector<unsigned char> pair_needs((size_t) Np * nlr, 0);
+    for (int p = 0; p < N; p++) for (int q = 0; q < N; q++) {
+        if (want_cond) for (int l = 1; l <= std::min(p, q) + 1; l++) for (int r = l; r <= p + q + 2 - l; r++) {
+            const int k = lr_index(l, r);
+            wA[(size_t) (p * N + q) * nlr + k] = weight_A(p, q, r, l);
+        }
+        for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) {
+            const double M1 = Mof(i, j), M2 = Mof(j, i);
+            const size_t wo = ((size_t) ((i * nc + j) * N + p) * N + q) * nlr;
+            hpre[(size_t) ((i * nc + j) * N + p) * N + q] = 8 * pow(M2, p + 0.5) * pow(M1, q + 0.5);
+            const int pr = tm.pair_of[i][j];
+            if (want_cond) for (int l = 1; l <= std::min(p, q) + 1; l++) for (int r = l; r <= p + q + 2 - l; r++) {
+                const int k = lr_index(l, r);
+                wAp[wo + k] = weight_A_prime(p, q, r, l, M1, M2);
+                pair_needs[(size_t) pr * nlr + k] = 1;       // the reference evaluates omega for every (l,r) of the H sums
+            }
+            if (want_visc) for (int l = 1; l <= std::min(p, q) + 2; l++) for (int r = l; r <= p + q + 4 - l; r++) {
+                const int k = lr_index(l, r);
+                if (k < 0) continue;                          // all weights zero for every pair
+                wBpp[wo + k] = weight_B_dblprime(p, q, r, l, M1, M2);
+                wBp[wo + k] = weight_B_prime(p, q, r, l, M1, M2);
+                if (wBpp[wo + k] != 0 || wBp[wo + k] != 0) pair_needs[(size_t) pr * nlr + k] = 1;
+            }
+        }
+    }
+    // where MieKinGas::omega takes the correlation branch (cpp/MieKinGas.cpp:81-93)
+    c->is_corr.assign((size_t) nT * Np * nlr, 0);
+    std::vector<unsigned char> need((size_t) nT * Np * nlr, 0);
+    bool any_numeric = false, any_corr = false;
+    for (int t = 0; t < nT; t++) for (int p = 0; p < Np; p++) for (int k = 0; k < nlr; k++) {
+        if (!pair_needs[(size_t) p * nlr + k]) continue;
+        const size_t o = ((size_t) t * Np + p) * nlr + k;
+        const auto& d = m->descs[p];
+        const int l = tm.lr_l[k], r = tm.lr_r[k];
+        bool corr = opts->omega_correlation_active && mie && !coeff_T && (l <= 2) && (r >= l) && (r <= 3) && (fabs(d.lam[1] - 6.) < 1e-10);
+        if (corr) corr = (T[t] * 1.38064852e-23 / d.eps) > 0.4;
+        c->is_corr[o] = corr; need[o] = !corr;
+        any_numeric |= !corr; any_corr |= corr;
+    }
+    int rc = 0;
+#define TC_CUDA(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { set_error(std::string(#expr) + ": " + cudaGetErrorString(e_)); kg_tcache_destroy(c); return -2; } } while (0)
+    TC_CUDA(upload(&c->d_T, c->T));
+    TC_CUDA(cudaMalloc(&c->d_omega, need.size() * sizeof(double)));
+    TC_CUDA(cudaMemset(c->d_omega, 0, need.size() * sizeof(double)));
+    cudaStream_t s = m->stream;
+    if (any_numeric) {
+        kg_omega_plan* plan = nullptr;
+        std::vector<int32_t> ll(tm.lr_l, tm.lr_l + nlr), rr(tm.lr_r, tm.lr_r + nlr);
+        rc = kg_omega_plan_create_masked(m, nT, T, nlr, ll.data(), rr.data(), coeff_T, need.data(), &plan);
+        if (!rc) rc = kg_omega_plan_run(plan);
+        if (!rc) rc = kg_omega_plan_export_dev(plan, c->d_omega, nullptr);
+        std::vector<int32_t> pst((size_t) nT * Np, 0);
+        if (!rc) rc = kg_omega_plan_fetch(plan, nullptr, nullptr, pst.data());
+        if (plan) kg_omega_plan_destroy(plan);
+        if (rc) { kg_tcache_destroy(c); return rc; }
+        int bad = 0; for (int v : pst) bad |= v;
+        if (bad & KG_STATUS_GETR_MAXITER) { set_error("get_R reached max iter!"); kg_tcache_destroy(c); return -4; }
+    }
+    std::vector<MiePair> mp_dev(Np), mp_int((size_t) nc * nc), mp_diag(nc);
+    if (mie) {
+        for (int p = 0; p < Np; p++) {
+            const auto& d = m->descs[p];
+            MiePair q; q.sigma = d.sigma; q.eps = d.eps; q.lr = d.lam[0]; q.la = d.lam[1]; q.C = d.C[0];
+            q.alpha = q.C * ((1.0 / (q.la - 3.0)) - (1.0 / (q.lr - 3.0)));          // cpp/MieKinGas.cpp:52
+            mp_dev[p] = q;
+        }
+        for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) mp_int[i * nc + j] = mp_dev[tm.pair_of[i][j]];
+        for (int i = 0; i < nc; i++) mp_diag[i] = mp_int[i * nc + i];
+    }
+    TC_CUDA(upload(&c->d_mp_int, mp_int));
+    if (any_corr) {
+        MiePair* d_mp = nullptr; int *d_pi = nullptr, *d_pj = nullptr, *d_l = nullptr, *d_r = nullptr; double* d_mass = nullptr; unsigned char* d_ic = nullptr;
+        std::vector<int> ll(tm.lr_l, tm.lr_l + nlr), rr(tm.lr_r, tm.lr_r + nlr);
+        TC_CUDA(upload(&d_mp, mp_dev)); TC_CUDA(upload(&d_pi, pair_i)); TC_CUDA(upload(&d_pj, pair_j)); TC_CUDA(upload(&d_l, ll)); TC_CUDA(upload(&d_r, rr));
+        TC_CUDA(upload(&d_mass, m->mass)); TC_CUDA(upload(&d_ic, c->is_corr));
+        const int tot = nT * Np * nlr;
+        omega_correlation_kernel<<<(tot + 127) / 128, 128, 0, s>>>(nT, Np, nlr, c->d_T, d_mp, d_pi, d_pj, d_mass, d_l, d_r, d_ic, c->d_omega);
+        TC_CUDA(cudaGetLastError());
+        TC_CUDA(cudaStreamSynchronize(s));
+        cudaFree(d_mp); cudaFree(d_pi); cudaFree(d_pj); cudaFree(d_l); cudaFree(d_r); cudaFree(d_mass); cudaFree(d_ic);
+    }
+    if (!opts->is_idealgas) {
+        c->h_mtl.resize((size_t) nT * Np); c->h_etl.resize((size_t) nT * Np);
+        std::vector<int32_t> tst((size_t) nT * Np, 0);
+        rc = kg_transfer_lengths_batch(m, nT, T, coeff_T, c->h_mtl.data(), c->h_etl.data(), tst.data());
+        if (rc) { kg_tcache_destroy(c); return rc; }
+        int bad = 0; for (int v : tst) bad |= v;
+        if (bad & KG_STATUS_BMID) { set_error("Unable to converge bmid!"); kg_tcache_destroy(c); return -4; }
+        if (bad & KG_STATUS_GETR_MAXITER) { set_error("get_R reached max iter!"); kg_tcache_destroy(c); return -4; }
+        TC_CUDA(upload(&c->d_mtl, c->h_mtl)); TC_CUDA(upload(&c->d_etl, c->h_etl));
+        MiePair* d_diag = nullptr;
+        TC_CUDA(upload(&d_diag, mp_diag));
+        TC_CUDA(cudaMalloc(&c->d_dbh, (size_t) nT * nc * sizeof(double)));
+        bh_kernel<<<(nT * nc + 127) / 128, 128, 0, s>>>(nT, nc, c->d_T, d_diag, c->d_dbh);
+        TC_CUDA(cudaGetLastError());
+        TC_CUDA(cudaStreamSynchronize(s));
+        cudaFree(d_diag);
+    }
+    {
+        double *d_wA = nullptr, *d_wAp = nullptr, *d_wBp = nullptr, *d_wBpp = nullptr, *d_hpre = nullptr;
+        TC_CUDA(upload(&d_wA, wA)); TC_CUDA(upload(&d_wAp, wAp)); TC_CUDA(upload(&d_wBp, wBp)); TC_CUDA(upload(&d_wBpp, wBpp)); TC_CUDA(upload(&d_hpre, hpre));
+        const int per_t = nc * nc * N * N;
+        TC_CUDA(cudaMalloc(&c->d_brk, (size_t) nT * 4 * per_t * sizeof(double)));
+        bracket_kernel<<<(nT * per_t + 127) / 128, 128, 0, s>>>(nT, tm, c->d_omega, d_wA, d_wAp, d_wBp, d_wBpp, d_hpre, c->d_brk);
+        TC_CUDA(cudaGetLastError());
+        TC_CUDA(cudaStreamSynchronize(s));
+        cudaFree(d_wA); cudaFree(d_wAp); cudaFree(d_wBp); cudaFree(d_wBpp); cudaFree(d_hpre);
+    }
+#undef TC_CUDA
+    *out = c;
+    return 0;
+}
+
+namespace {
+
+struct DevBuf {      // scoped device allocations of one batch call
+    std::vector<void*> ptrs;
+    ~DevBuf() { for (void* p : ptrs) cudaFree(p); }
+    template<class T> T* alloc(size_t n) { T* p = nullptr; if (cudaMalloc(&p, std::max<size_t>(1, n) * sizeof(T)) != cudaSuccess) return nullptr; ptrs.push_back(p); return p; }
+    template<class T> T* put(const T* h, size_t n, cudaStream_t s) {
+        T* p = alloc<T>(n);
+        if (p && h && cudaMemcpyAsync(p, h, n * sizeof(T), cudaMemcpyHostToDevice, s) != cudaSuccess) return nullptr;
+        return p;
+    }
+};
+
+int launch_state(kg_tcache* c, StateArgs& a, cudaStream_t s, const double* d_x_for_rdf, double* d_rdf) {
+    const TModel& tm = c->tm;
+    const int n = a.n;
+    if (!tm.is_idealgas) {
+        const long long tot = (long long) n * a.nslots * (tm.nc * (tm.nc + 1) / 2);
+        rdf_kernel<<<(unsigned) ((tot + 127) / 128), 128, 0, s>>>(n, a.nslots, tm, a.tidx, a.T_of, a.Vm, d_x_for_rdf, c->d_dbh, c->d_mp_int, d_rdf);
+    }
+    const int nn = tm.N * tm.nc, grid = (n + 127) / 128;
+    if (nn <= 8) state_kernel<8><<<grid, 128, 0, s>>>(tm, a);
+    else if (nn <= 16) state_kernel<16><<<grid, 128, 0, s>>>(tm, a);
+    else state_kernel<24><<<grid, 128, 0, s>>>(tm, a);
+    return cudaGetLastError() == cudaSuccess ? 0 : -2;
+}
+
+} // namespace
+
+extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const double* T, const double* Vm, const double* x,
+                                  const kg_transport_opts* opts, const kg_eos_inputs* eos, const kg_transport_out* out, int32_t* status) {
+    if (!m) return -1;
+    auto set_error = [&](const std::string& s) { m->err = s; };
+    if (n < 0 || !T || !Vm || !opts || !out) { set_error("kg_transport_batch: invalid argument"); return -1; }
+    if (n == 0) return 0;
+    if (!m->is_singlecomp && !x) { set_error("kg_transport_batch: mole fractions required"); return -1; }
+    const unsigned props = opts->properties;
+    const int nc = m->is_singlecomp ? 2 : m->ncomps, nce = m->is_singlecomp ? 1 : m->ncomps;
+    const bool want_D = ((props & KG_PROP_DIFFUSION) && out->D) || ((props & KG_PROP_THERMAL_DIFFUSION) && out->DT);
+    const bool want_lambda = (props & KG_PROP_CONDUCTIVITY) && (out->conductivity || out->conductivity_contribs);
+    if (want_D && (!eos || !eos->dmudn)) { set_error("kg_transport_batch: EoS is not set (dmudn required)"); return -1; }
+    if (want_lambda && (!eos || !eos->cp_ideal)) { set_error("kg_transport_batch: EoS is not set (cp_ideal required)"); return -1; }
+    if ((props & KG_PROP_CONDUCTIVITY) && opts->N < 2) { set_error("kg_transport_batch: thermal conductivity needs N >= 2"); return -1; }
+    if (want_D && opts->frame_of_reference == KG_FOR_COV && (!eos || !eos->dvdn)) {
+        set_error("kg_transport_batch: EoS is not set (dvdn required for the CoV frame)"); return -1; }
+    if (opts->frame_of_reference < KG_FOR_COM || opts->frame_of_reference > KG_FOR_SOLVENT) { set_error("Unknown (not-implemented) Frame of Reference."); return -1; }
+    if (opts->frame_of_reference == KG_FOR_SOLVENT && (opts->solvent_idx < 0 || opts->solvent_idx >= nc)) { set_error("kg_transport_batch: bad solvent index"); return -1; }
+    if (opts->dependent_idx >= nc || opts->dependent_idx < -nc) { set_error("kg_transport_batch: bad dependent index"); return -1; }
+    CUDA_OK(cudaSetDevice(m->device));
+    kg_tcache* c = cache;
+    bool own = false;
+    if (!c) {
+        std::vector<double> Tu(T, T + n);
+        std::sort(Tu.begin(), Tu.end());
+        Tu.erase(std::unique(Tu.begin(), Tu.end()), Tu.end());
+        const int rc = kg_tcache_create(m, opts, (int) Tu.size(), Tu.data(), nullptr, &c);
+        if (rc) return rc;
+        own = true;
+    }
+    else if (c->m != m || c->opt.N != opts->N || c->opt.is_idealgas != opts->is_idealgas || (props & ~c->opt.properties)
+             || c->opt.omega_correlation_active != opts->omega_correlation_active) {
+        set_error("kg_transport_batch: cache was built for other options"); return -1;
+    }
+    struct Guard { kg_tcache* c; bool own; ~Guard() { if (own) kg_tcache_destroy(c); } } guard{c, own};
+    cudaStream_t s = m->stream;
+    std::vector<int> tidx(n);
+    for (int k = 0; k < n; k++) { auto f = c->index_of.find(T[k]); tidx[k] = (f == c->index_of.end()) ? -1 : f->second; }
+    DevBuf db;
+    StateArgs a; memset(&a, 0, sizeof(a));
+    a.n = n; a.nT = c->nT; a.opt = *opts; a.opt.properties = props;
+    a.nslots = (props & KG_PROP_CONDUCTIVITY) ? 2 : 1;
+    const int N = opts->N, nn = N * nc, nD = opts->do_compress ? nc - 1 : nc;
+#define NEED(p) do { if (!(p)) { set_error("kg_transport_batch: device allocation or copy failed"); return -2; } } while (0)
+    a.tidx = db.put(tidx.data(), n, s); NEED(a.tidx);
+    a.T_of = c->d_T;
+    a.Vm = db.put(Vm, n, s); NEED(a.Vm);
+    a.x = m->is_singlecomp ? nullptr : db.put(x, (size_t) n * nc, s); if (!m->is_singlecomp) NEED(a.x);
+    a.mtl = c->d_mtl; a.etl = c->d_etl; a.brk = c->d_brk;
+    double* d_rdf = nullptr;
+    if (!opts->is_idealgas) { d_rdf = db.alloc<double>((size_t) n * a.nslots * nc * nc); NEED(d_rdf); }
+    a.rdf = d_rdf;
+    if (eos && eos->dmudn && (props & (KG_PROP_DIFFUSION | KG_PROP_THERMAL_DIFFUSION))) { a.dmudn = db.put(eos->dmudn, (size_t) n * nce * nce, s); NEED(a.dmudn); }
+    if (eos && eos->cp_ideal && (props & KG_PROP_CONDUCTIVITY)) { a.cp_ideal = db.put(eos->cp_ideal, (size_t) n * nce, s); NEED(a.cp_ideal); }
+    if (eos && eos->dvdn && opts->frame_of_reference == KG_FOR_COV) { a.dvdn = db.put(eos->dvdn, (size_t) n * nce, s); NEED(a.dvdn); }
+    struct OutMap { double* host; double** dev; size_t count; };
+    OutMap maps[] = {{out->viscosity, &a.viscosity, (size_t) n}, {out->conductivity, &a.conductivity, (size_t) n},
+                     {out->conductivity_contribs, &a.contribs, (size_t) n * 3}, {out->D, &a.D, (size_t) n * nD * nD}, {out->DT, &a.DT, (size_t) n * nc},
+                     {out->K, &a.K, (size_t) n * nc}, {out->K_prime, &a.Kp, (size_t) n * nc}, {out->cond_matrix, &a.cond_matrix, (size_t) n * nn * nn},
+                     {out->cond_vector, &a.cond_vector, (size_t) n * nn}, {out->visc_matrix, &a.visc_matrix, (size_t) n * nn * nn},
+                     {out->visc_vector, &a.visc_vector, (size_t) n * nn}};
+    for (auto& mp : maps) if (mp.host) { *mp.dev = db.alloc<double>(mp.count); NEED(*mp.dev); CUDA_OK(cudaMemsetAsync(*mp.dev, 0, mp.count * sizeof(double), s)); }
+    a.status = db.alloc<int>(n); NEED(a.status);
+#undef NEED
+    if (launch_state(c, a, s, a.x, d_rdf)) { set_error("kg_transport_batch: kernel launch failed"); return -2; }
+    for (auto& mp : maps) if (mp.host) CUDA_OK(cudaMemcpyAsync(mp.host, *mp.dev, mp.count * sizeof(double), cudaMemcpyDeviceToHost, s));
+    if (out->rdf) {
+        if (opts->is_idealgas) for (size_t k = 0; k < (size_t) n * nc * nc; k++) out->rdf[k] = 1.0;
+        else CUDA_OK(cudaMemcpy2DAsync(out->rdf, (size_t) nc * nc * sizeof(double), d_rdf, (size_t) a.nslots * nc * nc * sizeof(double),
+                                       (size_t) nc * nc * sizeof(double), n, cudaMemcpyDeviceToHost, s));
+    }
+    std::vector<int> st(n);
+    CUDA_OK(cudaMemcpyAsync(st.data(), a.status, n * sizeof(int), cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaStreamSynchronize(s));
+    if (status) for (int k = 0; k < n; k++) status[k] = st[k];
+    return 0;
+}

@@ -1,0 +1,349 @@
+"""Host-side mirror of the reference's model interface for the hot path (pykingas/MieKinGas.py, pykingas/MieType.py,
+pykingas/py_KineticGas.py:180-715), backed by the C-ABI library (include/kgcuda.h).
+
+Same method names, argument meaning and error behaviour as pykingas; every (T, Vm, x) argument additionally accepts
+arrays -- the whole batch goes to the GPU in one call (kg_transport_batch). EoS-derived inputs come either from a
+thermopack-like object (`set_eos`, the calls of cpp/eos_interface.h:143-181: chemical_potential_tv, idealenthalpysingle,
+specific_volume) evaluated on the host per state point, or directly as arrays (`eos_inputs=`), which is what sweeps use.
+"""
+import ctypes as C
+import warnings
+import numpy as np
+
+from . import _lib
+from ._lib import dp, ip
+from .model import DeviceModel, mie_desc, raise_on_status
+from .fluids import MIE, BOLTZMANN, AVOGADRO
+
+FLT_EPS = 1e-12
+FRAMES = {"CoM": 0, "CoN": 1, "CoV": 2, "solvent": 3}      # cpp/utils.h:37-45, KineticGas::frame_of_reference_map
+PROP_VISCOSITY, PROP_CONDUCTIVITY, PROP_DIFFUSION, PROP_THERMAL_DIFFUSION = 1, 2, 4, 8
+
+
+class TransportOpts(C.Structure):
+    _fields_ = [("N", C.c_int32), ("is_idealgas", C.c_int32), ("omega_correlation_active", C.c_int32), ("frame_of_reference", C.c_int32),
+                ("dependent_idx", C.c_int32), ("solvent_idx", C.c_int32), ("do_compress", C.c_int32), ("properties", C.c_uint32)]
+
+
+class EosInputs(C.Structure):
+    _fields_ = [("dmudn", dp), ("cp_ideal", dp), ("pressure", dp), ("dvdn", dp)]
+
+
+class TransportOut(C.Structure):
+    _fields_ = [(k, dp) for k in ("viscosity", "conductivity", "conductivity_contribs", "D", "DT", "rdf", "K", "K_prime",
+                                  "cond_matrix", "cond_vector", "visc_matrix", "visc_vector")]
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(dp)
+
+
+class TCache:
+    """Device-resident per-temperature tables (kg_tcache): the GPU-side KineticGasCache."""
+
+    def __init__(self, kin, T, N, properties):
+        # holds the DeviceModel (not the MieKinGas object): no reference cycle, and the kg_model outlives its caches
+        self.dev = kin.dev
+        self.T = np.ascontiguousarray(np.atleast_1d(T), float)
+        self.opts = kin._opts(N, properties)
+        h = C.c_void_p()
+        L = self.dev.L
+        self.dev._chk(L.kg_tcache_create(self.dev.h, C.byref(self.opts), self.T.size, _ptr(self.T), None, C.byref(h)), "kg_tcache_create")
+        self.h = h
+
+    def lr(self):
+        L = self.dev.L
+        n = L.kg_tcache_lr(self.h, None, None)
+        l, r = np.zeros(n, np.int32), np.zeros(n, np.int32)
+        L.kg_tcache_lr(self.h, l.ctypes.data_as(ip), r.ctypes.data_as(ip))
+        return l, r
+
+    def fetch(self):
+        """(omega [nT][npairs][nlr], mtl, etl [nT][npairs], is_correlation) on the host: what feeds cache.omega.store."""
+        l, _ = self.lr()
+        shp = (self.T.size, self.dev.npairs, l.size)
+        om, ic = np.zeros(shp), np.zeros(shp, np.uint8)
+        mtl, etl = np.zeros(shp[:2]), np.zeros(shp[:2])
+        self.dev._chk(self.dev.L.kg_tcache_fetch(self.h, _ptr(om), _ptr(mtl), _ptr(etl), ic.ctypes.data_as(C.POINTER(C.c_uint8))),
+                          "kg_tcache_fetch")
+        return om, mtl, etl, ic
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.dev.L.kg_tcache_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class MieKinGas:
+    """pykingas.MieKinGas on the GPU. Parameters from the compact table in fluids.py unless given explicitly."""
+
+    def __init__(self, comps, mole_weights=None, sigma=None, eps_div_k=None, la=None, lr=None, lij=0, kij=0,
+                 N=4, is_idealgas=False, use_eos=None, device=0):
+        self.comps = comps.split(",")
+        self.ncomps = len(self.comps)
+        self._is_singlecomp = self.ncomps == 1
+        if self._is_singlecomp:
+            self.comps = [self.comps[0]] * 2
+            self.ncomps = 2
+        self.default_N = N
+        self.is_idealgas = is_idealgas
+        self.lij, self.kij = lij, kij
+
+        def pick(given, col):
+            db = [MIE[c][col] for c in self.comps]
+            if given is None:
+                return np.array(db, float)
+            given = list(given) * (2 if (self._is_singlecomp and len(given) == 1) else 1)
+            return np.array([db[i] if given[i] is None else given[i] for i in range(self.ncomps)], float)
+
+        Mw, sig, epsk, la_, lr_ = (pick(v, k) for k, v in enumerate((mole_weights, sigma, eps_div_k, la, lr)))
+        self.mole_weights = Mw * 1e-3 / AVOGADRO
+        self.m = self.mole_weights.copy()
+        nc = self.ncomps
+        off = np.ones((nc, nc)) - np.identity(nc)
+        # mixing rules: pykingas/MieType.py:201-249
+        self.sigma_ij = (np.ones((nc, nc)) - lij * off) * 0.5 * (sig[None, :] + sig[:, None])
+        eps = epsk * BOLTZMANN
+        self.epsilon_ij = (np.ones((nc, nc)) - kij * off) * np.sqrt(eps[None, :] * eps[:, None])
+        self.la = 3 + (1 - lij) * np.sqrt((la_[None, :] - 3) * (la_[:, None] - 3))
+        self.lr = 3 + (1 - lij) * np.sqrt((lr_[None, :] - 3) * (lr_[:, None] - 3))
+        self.sigma, self.epsilon = self.sigma_ij, self.epsilon_ij
+        self.eos = use_eos
+        self.omega_correlation_active = True
+        self._device = device
+        self._build_device_model()
+
+    # ------------------------------------------------------------------------------------------------ internals
+    def _build_device_model(self):
+        ncd = 1 if self._is_singlecomp else self.ncomps
+        descs = [mie_desc(self.sigma_ij[i, j], self.epsilon_ij[i, j], self.la[i, j], self.lr[i, j]) for i in range(ncd) for j in range(i, ncd)]
+        self.dev = DeviceModel(descs, self.m[:ncd], self._is_singlecomp, device=self._device)
+        self._caches = {}
+
+    def _opts(self, N, properties, frame=1, dependent_idx=-1, solvent_idx=-1, do_compress=True):
+        o = TransportOpts()
+        o.N, o.is_idealgas, o.omega_correlation_active = int(N), int(self.is_idealgas), int(self.omega_correlation_active)
+        o.frame_of_reference, o.dependent_idx, o.solvent_idx, o.do_compress, o.properties = frame, dependent_idx, solvent_idx, int(do_compress), properties
+        return o
+
+    def set_eos(self, eos):
+        self.eos = eos
+
+    def set_omega_correlation_active(self, active):
+        """cpp/MieKinGas.cpp:150-155 -- also drops the device tables, like cache.omega.clear()."""
+        if active != self.omega_correlation_active:
+            self._caches = {}
+        self.omega_correlation_active = bool(active)
+
+    def validate_and_sanitize_composition(self, x):
+        """pykingas/py_KineticGas.py:119-141, vectorised over a leading batch axis."""
+        x = np.asarray(x, float)
+        if np.any(np.abs(x.sum(axis=-1) - 1) > FLT_EPS):
+            warnings.warn("Mole fractions do not sum to unity", RuntimeWarning, stacklevel=3)
+        elif self._is_singlecomp:
+            return np.broadcast_to(np.array([0.5, 0.5]), x.shape[:-1] + (2,))
+        elif x.shape[-1] != self.ncomps:
+            raise IndexError(f"{x.shape[-1]} mole fractions were supplied for a {self.ncomps} component mixture!")
+        return x
+
+    def tcache(self, T, N=None, properties=PROP_VISCOSITY | PROP_CONDUCTIVITY | PROP_DIFFUSION | PROP_THERMAL_DIFFUSION):
+        """Build (or reuse) the device tables for the distinct temperatures in T."""
+        N = self.default_N if N is None else N
+        Tu = np.unique(np.asarray(T, float))
+        key = (N, properties, self.omega_correlation_active, Tu.tobytes())
+        if key not in self._caches:
+            self._caches[key] = TCache(self, Tu, N, properties)
+        return self._caches[key]
+
+    def _eos_arrays(self, T, Vm, x, need_dmudn, need_cp, need_dvdn, eos_inputs):
+        """EoS inputs as arrays: given by the caller, or evaluated per state point on the host EoS object through the same
+        calls the reference's PyWrapper makes (cpp/eos_interface.h:143-181)."""
+        n = T.size
+        nce = 1 if self._is_singlecomp else self.ncomps
+        out = dict(eos_inputs or {})
+        xe = np.ones((n, 1)) if self._is_singlecomp else x
+        if need_dmudn and "dmudn" not in out:
+            if self.eos is None:
+                raise RuntimeError("EoS is not set")
+            out["dmudn"] = np.array([np.asarray(self.eos.chemical_potential_tv(T[k], Vm[k], list(xe[k]), None, None, True)[1]) for k in range(n)])
+        if need_cp and "cp_ideal" not in out:
+            if self.eos is None:
+                raise RuntimeError("EoS is not set")
+            out["cp_ideal"] = np.array([[self.eos.idealenthalpysingle(T[k], c + 1, True)[1] for c in range(nce)] for k in range(n)])
+        if need_dvdn and "dvdn" not in out:
+            if self.eos is None:
+                raise RuntimeError("EoS is not set")
+            rows = []
+            for k in range(n):
+                p, = self.eos.pressure_tv(T[k], Vm[k], list(xe[k]))
+                rows.append(np.asarray(self.eos.specific_volume(T[k], p, list(xe[k]), self.eos.VAPPH, None, None, True)[1]))
+            out["dvdn"] = np.array(rows)
+        return {k: np.ascontiguousarray(np.asarray(v, float).reshape(n, -1)) for k, v in out.items()}
+
+    def _run(self, T, Vm, x, N, properties, want, frame=1, dependent_idx=-1, solvent_idx=-1, do_compress=True, eos_inputs=None, cache=None):
+        """One kg_transport_batch call. want: names of kg_transport_out fields to return. Returns dict of arrays + 'scalar' flag."""
+        N = self.default_N if N is None else N
+        T_in = np.asarray(T, float)
+        scalar = T_in.ndim == 0 and np.ndim(Vm) == 0 and np.ndim(x) <= 1
+        x = self.validate_and_sanitize_composition(x)
+        n = int(np.broadcast_shapes(T_in.shape, np.shape(Vm), x.shape[:-1])[0]) if not scalar else 1
+        Tn = np.ascontiguousarray(np.broadcast_to(T_in, (n,)), float)
+        Vn = np.ascontiguousarray(np.broadcast_to(np.asarray(Vm, float), (n,)), float)
+        xn = np.ascontiguousarray(np.broadcast_to(x, (n, self.ncomps)), float)
+        nc = self.ncomps
+        nn = N * nc
+        nD = nc - 1 if do_compress else nc
+        shapes = {"viscosity": (n,), "conductivity": (n,), "conductivity_contribs": (n, 3), "D": (n, nD, nD), "DT": (n, nc),
+                  "rdf": (n, nc, nc), "K": (n, nc), "K_prime": (n, nc), "cond_matrix": (n, nn, nn), "cond_vector": (n, nn),
+                  "visc_matrix": (n, nn, nn), "visc_vector": (n, nn)}
+        bufs = {k: np.zeros(shapes[k]) for k in want}
+        out = TransportOut()
+        for k, b in bufs.items():
+            setattr(out, k, _ptr(b))
+        opts = self._opts(N, properties, frame, dependent_idx, solvent_idx, do_compress)
+        want_D = ("D" in want) or ("DT" in want)
+        eos_arr = self._eos_arrays(Tn, Vn, xn, want_D, ("conductivity" in want) or ("conductivity_contribs" in want),
+                                   frame == FRAMES["CoV"] and want_D, eos_inputs)
+        eos = EosInputs()
+        for k in ("dmudn", "cp_ideal", "pressure", "dvdn"):
+            if k in eos_arr:
+                setattr(eos, k, _ptr(eos_arr[k]))
+        st = np.zeros(n, np.int32)
+        if cache is None:
+            cache = self.tcache(Tn, N, properties)
+        xarg = None if self._is_singlecomp else _ptr(xn)
+        self.dev._chk(self.dev.L.kg_transport_batch(self.dev.h, cache.h, n, _ptr(Tn), _ptr(Vn), xarg, C.byref(opts), C.byref(eos), C.byref(out),
+                                                     st.ctypes.data_as(ip)), "kg_transport_batch")
+        raise_on_status(st)
+        bufs["scalar"] = scalar
+        return bufs
+
+    # ------------------------------------------------------------------------------------------------ TV-properties
+    def viscosity(self, T, Vm, x, N=None, **kw):
+        r = self._run(T, Vm, x, N, PROP_VISCOSITY, ["viscosity"], **kw)
+        return float(r["viscosity"][0]) if r["scalar"] else r["viscosity"]
+
+    def thermal_conductivity(self, T, Vm, x, N=None, idealgas=None, contributions="all", **kw):
+        idealgas = self.is_idealgas if idealgas is None else idealgas
+        if idealgas:
+            Vm = np.full(np.shape(Vm), 1e12) if np.ndim(Vm) else 1e12
+        r = self._run(T, Vm, x, N, PROP_CONDUCTIVITY, ["conductivity", "conductivity_contribs"], **kw)
+        if contributions != "all":
+            c = r["conductivity_contribs"]
+            d = {k: (float(c[0, i]) if r["scalar"] else c[:, i]) for i, k in enumerate("tdi") if k in contributions}
+            return d
+        return float(r["conductivity"][0]) if r["scalar"] else r["conductivity"]
+
+    def interdiffusion(self, T, Vm, x, N=None, use_independent=True, dependent_idx=-1, frame_of_reference="CoN", use_binary=True,
+                       solvent_idx=-1, **kw):
+        if frame_of_reference not in FRAMES:
+            raise RuntimeError("Invalid frame of reference : " + frame_of_reference)
+        r = self._run(T, Vm, x, N, PROP_DIFFUSION, ["D"], frame=FRAMES[frame_of_reference], dependent_idx=dependent_idx,
+                      solvent_idx=solvent_idx, do_compress=use_independent, **kw)
+        D = r["D"]
+        if use_binary and self.ncomps == 2:
+            D = D[:, 0, 0]
+        return D[0] if r["scalar"] else D
+
+    def thermal_diffusion_coeff(self, T, Vm, x, N=None, use_independent=False, dependent_idx=-1, frame_of_reference="CoN", solvent_idx=-1, **kw):
+        N = self.default_N if N is None else N
+        if N < 2:
+            warnings.warn(f"Thermal diffusion is a 2nd order phenomena, cannot be computed for N < 2 (got N = {N})", RuntimeWarning, stacklevel=2)
+            return np.full(self.ncomps, np.nan)
+        if frame_of_reference not in FRAMES:
+            raise RuntimeError("Invalid frame of reference : " + frame_of_reference)
+        r = self._run(T, Vm, x, N, PROP_THERMAL_DIFFUSION, ["DT"], frame=FRAMES[frame_of_reference], dependent_idx=dependent_idx,
+                      solvent_idx=solvent_idx, **kw)
+        return r["DT"][0] if r["scalar"] else r["DT"]
+
+    def transport_batch(self, T, Vm, x, N=None, properties=PROP_VISCOSITY | PROP_CONDUCTIVITY | PROP_DIFFUSION | PROP_THERMAL_DIFFUSION,
+                        frame_of_reference="CoN", dependent_idx=-1, solvent_idx=-1, use_independent=True, eos_inputs=None, cache=None):
+        """All requested properties of a batch of state points in one device pass (additive batched entry point)."""
+        want = []
+        if properties & PROP_VISCOSITY:
+            want.append("viscosity")
+        if properties & PROP_CONDUCTIVITY:
+            want += ["conductivity", "conductivity_contribs"]
+        if properties & PROP_DIFFUSION:
+            want.append("D")
+        if properties & PROP_THERMAL_DIFFUSION:
+            want.append("DT")
+        r = self._run(T, Vm, x, N, properties, want, frame=FRAMES[frame_of_reference], dependent_idx=dependent_idx, solvent_idx=solvent_idx,
+                      do_compress=use_independent, eos_inputs=eos_inputs, cache=cache)
+        r.pop("scalar")
+        return r
+
+    # ------------------------------------------------------------------------------------------------ Tp-properties
+    def _vm(self, T, p, x):
+        if self.eos is None:
+            raise RuntimeError("EoS is not set")
+        if np.ndim(T) == 0 and np.ndim(p) == 0:
+            Vm, = self.eos.specific_volume(T, p, x, self.eos.VAPPH)      # assuming vapour, pykingas/py_KineticGas.py:642-715
+            return Vm
+        T, p = np.broadcast_arrays(np.asarray(T, float), np.asarray(p, float))
+        xx = np.broadcast_to(np.asarray(x, float), T.shape + (np.shape(x)[-1],))
+        return np.array([self.eos.specific_volume(T[k], p[k], list(xx[k]), self.eos.VAPPH)[0] for k in range(T.size)])
+
+    def viscosity_tp(self, T, p, x, N=None):
+        return self.viscosity(T, self._vm(T, p, x), x, N=N)
+
+    def thermal_conductivity_tp(self, T, p, x, N=None, contributions="all"):
+        return self.thermal_conductivity(T, self._vm(T, p, x), x, N=N, contributions=contributions)
+
+    def interdiffusion_tp(self, T, p, x, N=None, use_independent=True, dependent_idx=-1, frame_of_reference="CoN", use_binary=True, solvent_idx=-1):
+        return self.interdiffusion(T, self._vm(T, p, x), x, N=N, use_independent=use_independent, dependent_idx=dependent_idx,
+                                   frame_of_reference=frame_of_reference, use_binary=use_binary, solvent_idx=solvent_idx)
+
+    def thermal_diffusion_coeff_tp(self, T, p, x, N=None, use_independent=False, dependent_idx=-1, frame_of_reference="CoN", solvent_idx=-1):
+        return self.thermal_diffusion_coeff(T, self._vm(T, p, x), x, N=N, use_independent=use_independent, dependent_idx=dependent_idx,
+                                            frame_of_reference=frame_of_reference, solvent_idx=solvent_idx)
+
+    # ------------------------------------------------------------------------------------------------ internals exposed by the bindings
+    def _rho_call(self, particle_density, T, x, N, properties, want):
+        Vm = AVOGADRO / np.asarray(particle_density, float)
+        r = self._run(T, Vm, x, N, properties, want)
+        return r[want[0]][0] if r["scalar"] else r[want[0]]
+
+    def get_rdf(self, particle_density, T, x):
+        return self._rho_call(particle_density, T, x, 2, PROP_VISCOSITY, ["rdf"])
+
+    def get_K_factors(self, particle_density, T, x):
+        return self._rho_call(particle_density, T, x, 2, PROP_VISCOSITY, ["K"])
+
+    def get_K_prime_factors(self, particle_density, T, x):
+        return self._rho_call(particle_density, T, x, 2, PROP_VISCOSITY, ["K_prime"])
+
+    def get_conductivity_matrix(self, particle_density, T, mole_fracs, N=None):
+        return self._rho_call(particle_density, T, mole_fracs, N, PROP_DIFFUSION, ["cond_matrix"])
+
+    def get_conductivity_vector(self, particle_density, T, mole_fracs, N=None):
+        return self._rho_call(particle_density, T, mole_fracs, N, PROP_DIFFUSION, ["cond_vector"])
+
+    def get_viscosity_matrix(self, particle_density, T, mole_fracs, N=None):
+        return self._rho_call(particle_density, T, mole_fracs, N, PROP_VISCOSITY, ["visc_matrix"])
+
+    def get_viscosity_vector(self, particle_density, T, mole_fracs, N=None):
+        return self._rho_call(particle_density, T, mole_fracs, N, PROP_VISCOSITY, ["visc_vector"])
+
+    def _pair_matrix(self, v):
+        if self._is_singlecomp:
+            return np.full((2, 2), v[0])
+        out = np.zeros((self.ncomps, self.ncomps))
+        k = 0
+        for i in range(self.ncomps):
+            for j in range(i, self.ncomps):
+                out[i, j] = out[j, i] = v[k]
+                k += 1
+        return out
+
+    def get_mtl(self, particle_density, T, x):
+        return self._pair_matrix(self.dev.transfer_lengths([T])[0][0])
+
+    def get_etl(self, particle_density, T, x):
+        return self._pair_matrix(self.dev.transfer_lengths([T])[1][0])

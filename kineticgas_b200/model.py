@@ -6,7 +6,7 @@ from . import _lib
 from ._lib import PotentialDesc, dp, ip
 
 STATUS_TEXT = {1: "get_R reached max iter!", 2: "tanh-sinh node table exhausted", 4: "non-finite collision integral",
-               8: "Unable to converge bmid!"}
+               8: "Unable to converge bmid!", 16: "singular Sonine-expansion system", 32: "temperature not present in the device cache"}
 
 
 def _p(a):

@@ -45,3 +45,71 @@ if __name__ == "__main__":
     which = sys.argv[1:] or ["chi_w"]
     if "chi_w" in which:
         chi_w_golden()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# state-point assembly fixtures: the reference's own rdf / K-factors / matrices / transport coefficients
+# ---------------------------------------------------------------------------------------------------------------
+R_GAS = 8.31446261815324
+
+
+def synthetic_eos(T, Vm, x, Mw):
+    """EoS-derived inputs used identically by the reference (through the table-backed GenericEoS of oracle/ref_driver.cpp)
+    and by the GPU path: an ideal-gas mixture plus a symmetric second-virial-like term. n = x (one mole), V = Vm."""
+    x = np.asarray(x, float)
+    nc = x.size
+    B = -1.0e-4 * (1.0 + 0.1 * (np.arange(nc)[:, None] + np.arange(nc)[None, :]))
+    dmudn = R_GAS * T * (np.diag(1.0 / x) + 2.0 * B / Vm)
+    cp_id = R_GAS * (2.5 + 0.35 * np.arange(1, nc + 1) + 1e-3 * (T - 300.0) * np.sqrt(np.asarray(Mw) / 16.0))
+    dvdn = Vm * (1.0 + 0.05 * (np.arange(nc) - (nc - 1) / 2.0))
+    return dmudn, cp_id, dvdn
+
+
+TRANSPORT_CASES = [
+    # name, comps, N, is_idealgas, [(T, rho_star (of sigma_00), x)], frames
+    ("ar_single", "AR", 2, False, [(300.0, 0.05, [1.0]), (300.0, 0.4, [1.0]), (150.0, 0.2, [1.0])]),
+    ("ar_single_ideal", "AR", 3, True, [(300.0, 0.05, [1.0])]),
+    ("c1_nc10_N3", "C1,NC10", 3, False, [(400.0, 0.1, [0.3, 0.7]), (400.0, 0.45, [0.9, 0.1]), (650.0, 0.3, [0.5, 0.5])]),
+    ("h2_o2_ideal", "H2,O2", 2, True, [(312.5, 0.01, [0.25, 0.75])]),
+    ("co2_c1_n2", "CO2,C1,N2", 2, False, [(312.5, 0.3, [0.2, 0.3, 0.5]), (475.0, 0.6, [0.6, 0.1, 0.3])]),
+]
+
+
+def transport_golden(cases=TRANSPORT_CASES, fname="transport_reference.npz"):
+    out = {}
+    for name, comps, N, ideal, points in cases:
+        ids, Mw, s, e, la, lr = mie_parameters(comps)
+        m = ref.RefMie(Mw, s, e, la, lr, is_idealgas=ideal)
+        nc = m.nc
+        single = m.single
+        for k, (T, rho_star, x) in enumerate(points):
+            rho = rho_star / s[0] ** 3
+            Vm = ref.AVOGADRO / rho
+            xi = [0.5, 0.5] if single else x
+            dmudn, cp_id, dvdn = synthetic_eos(T, Vm, x, Mw)
+            key = f"{name}_{k}"
+            out[key + "_in"] = np.array([T, Vm, rho] + list(xi))
+            out[key + "_dmudn"], out[key + "_cp"], out[key + "_dvdn"] = dmudn, cp_id, dvdn
+            m.set_eos(dmudn=dmudn, cp_id=cp_id, p=1e5, vm=Vm, dvdn=dvdn)
+            out[key + "_rdf"] = m.rdf(rho, T, xi)
+            K, Kp = m.K_factors(rho, T, xi)
+            out[key + "_K"], out[key + "_Kp"] = K, Kp
+            if not ideal:
+                out[key + "_mtl"], out[key + "_etl"] = m.mtl(rho, T, xi), m.etl(rho, T, xi)
+            M, v = m.matrix_vector(0, rho, T, xi, N)
+            out[key + "_cond_matrix"], out[key + "_cond_vector"] = M, v
+            M, v = m.matrix_vector(2, rho, T, xi, N)
+            out[key + "_visc_matrix"], out[key + "_visc_vector"] = M, v
+            out[key + "_viscosity"] = np.array(m.viscosity(T, Vm, xi, N))
+            out[key + "_contribs"] = m.thermal_conductivity_contribs(T, Vm, xi, N)
+            for frame, fname_ in ((0, "CoM"), (1, "CoN"), (2, "CoV"), (3, "solvent")):
+                solv = 0 if frame == 3 else -1
+                out[key + f"_D_{fname_}"] = m.interdiffusion(T, Vm, xi, N, frame=frame, dep=-1, solvent=solv, do_compress=True)
+                out[key + f"_DT_{fname_}"] = m.thermal_diffusion_coeff(T, Vm, xi, N, frame=frame, dep=-1, solvent=solv)
+            out[key + "_D_CoN_full"] = m.interdiffusion(T, Vm, xi, N, frame=1, dep=0, solvent=-1, do_compress=False)
+            print(key, "eta", out[key + "_viscosity"], "lambda", out[key + "_contribs"], flush=True)
+    np.savez(os.path.join(GOLD, fname), **out)
+
+
+if __name__ == "__main__" and "transport" in sys.argv[1:]:
+    transport_golden()
