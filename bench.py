@@ -25,6 +25,7 @@ sys.path.insert(0, ROOT)
 
 NT_PER_GPU = 4096
 LR = [(l, r) for l in range(1, 5) for r in range(l, 5)]
+FP64_INSTR_PER_NODE = 11.0   # ts_term + stop rule for a 2-term potential: 6 DFMA + 3 DMUL + 1 DFMA (running sum) + 1 DSETP (kg_device.cuh)
 F_NODE = 98.0    # nominal FP64 flop per tanh-sinh node for a 2-term (Mie/LJ) potential, SURVEY.md 8(d): 52 + 23 n_terms
 METRIC = "collision integrals/s"
 
@@ -87,6 +88,114 @@ def host_cores():
         return os.cpu_count() or 1
 
 
+# ------------------------------------------------------------------------------------------------ RET state points (configs[2])
+SP_COMPS, SP_N = "C1,NC10", 3
+SP_GRID = (64, 64, 16)        # T x rho* x x1
+R_GAS = 8.31446261815324
+
+
+def sp_grid(n_gpus, rank, shape=SP_GRID):
+    """BASELINE.json configs[2] / SURVEY 8(d).3: T = linspace(300,700,64) K, rho* = rho sigma_11^3 = linspace(0.01,0.6,64),
+    x_1 = linspace(0.02,0.98,16) -> 65 536 state points per GPU (weak scaling: rank k owns every n_gpus-th temperature of an
+    n_gpus-times denser T grid)."""
+    from kineticgas_b200.fluids import mie_parameters, AVOGADRO
+    ids, Mw, s, e, la, lr = mie_parameters(SP_COMPS)
+    nT, nr, nx = shape
+    T = np.linspace(300.0, 700.0, nT * n_gpus)[rank::n_gpus]
+    rho = np.linspace(0.01, 0.6, nr) / s[0] ** 3
+    x1 = np.linspace(0.02, 0.98, nx)
+    Tg, rg, xg = np.meshgrid(T, rho, x1, indexing="ij")
+    Tn, Vm = Tg.ravel(), AVOGADRO / rg.ravel()
+    x = np.stack([xg.ravel(), 1.0 - xg.ravel()], axis=1)
+    return np.ascontiguousarray(Tn), np.ascontiguousarray(Vm), np.ascontiguousarray(x), Mw
+
+
+def sp_eos(T, Vm, x):
+    """Synthetic EoS-derived inputs (host-side inputs at the boundary): ideal-gas mixture plus a symmetric
+    second-virial-like term. Same formula as oracle/make_golden.py synthetic_eos, vectorised."""
+    nc = x.shape[1]
+    B = -1.0e-4 * (1.0 + 0.1 * (np.arange(nc)[:, None] + np.arange(nc)[None, :]))
+    eye = np.eye(nc)[None, :, :] / x[:, :, None]
+    return np.ascontiguousarray(R_GAS * T[:, None, None] * (eye + 2.0 * B[None] / Vm[:, None, None]))
+
+
+def _sp_cpu_worker(task):
+    """Reference arm of the state-point leg: interdiffusion + thermal_diffusion_coeff at the sample's state points of ONE
+    temperature through the unmodified reference (oracle/_ref): the first point pays the Omega / transfer-length fan-out."""
+    T, pts = task
+    from oracle import ref
+    from kineticgas_b200.fluids import mie_parameters
+    ids, Mw, s, e, la, lr = mie_parameters(SP_COMPS)
+    m = ref.RefMie(Mw, s, e, la, lr, is_idealgas=False)
+    times = []
+    for Vm, x1 in pts:
+        x = np.array([x1, 1.0 - x1])
+        dm = sp_eos(np.array([T]), np.array([Vm]), x[None, :])[0]
+        m.set_eos(dmudn=dm, cp_id=np.zeros(2), p=1e5, vm=Vm, dvdn=np.zeros(2))
+        t0 = time.perf_counter()
+        m.interdiffusion(T, Vm, x, SP_N)
+        m.thermal_diffusion_coeff(T, Vm, x, SP_N)
+        times.append(time.perf_counter() - t0)
+    return times
+
+
+def sp_cpu_baseline(cores, n_T=4, pts_per_T=4):
+    from oracle import ref
+    if not ref.available():
+        return None
+    T, Vm, x, _ = sp_grid(1, 0)
+    Tu = np.unique(T)
+    Tsel = Tu[((np.arange(n_T) + 0.5) * Tu.size / n_T).astype(int)]
+    rng = np.random.default_rng(7)
+    tasks = []
+    for Tk in Tsel:
+        idx = rng.choice(np.flatnonzero(T == Tk), pts_per_T, replace=False)
+        tasks.append((float(Tk), [(float(Vm[i]), float(x[i, 0])) for i in idx]))
+    t0 = time.perf_counter()
+    with mp.get_context("spawn").Pool(min(cores, len(tasks))) as pool:
+        res = pool.map(_sp_cpu_worker, tasks, chunksize=1)
+    wall = time.perf_counter() - t0
+    cold = float(np.mean([r[0] for r in res]))
+    warm = float(np.mean([t for r in res for t in r[1:]]))
+    nT, n = Tu.size, T.size
+    est = (nT * cold + (n - nT) * warm) / cores         # one worker per core, temperatures split over workers
+    return {"value": n / est, "unit": "state points/s", "cores": cores, "kind": "reference",
+            "sample": f"{n_T} temperatures x {pts_per_T} state points through the reference's interdiffusion + thermal_diffusion_coeff "
+                      f"(N={SP_N}); measured {cold:.2f} s for the first point of a temperature (Omega + transfer-length fan-out, 8 threads) "
+                      f"and {warm * 1e3:.1f} ms per further point; extrapolated to {nT} T / {n} points on {cores} cores; {wall:.1f} s wall"}
+
+
+def run_state_points(local_rank, rank, world, n_gpus, steps):
+    """configs[2] on this rank's GPU: per step, build the device tables for the 64 temperatures (Omega by quadrature where the
+    reference integrates, correlation elsewhere, transfer lengths, brackets) and assemble + solve all state points. Host buffers
+    in, host buffers out (this IS the end-to-end path). Returns per-step milliseconds and stage split."""
+    from kineticgas_b200 import MieKinGas
+    from kineticgas_b200.kingas import PROP_DIFFUSION, PROP_THERMAL_DIFFUSION
+    kin = MieKinGas(SP_COMPS, N=SP_N, is_idealgas=False, device=local_rank)
+    T, Vm, x, _ = sp_grid(n_gpus, rank)
+    eos = {"dmudn": sp_eos(T, Vm, x)}
+    props = PROP_DIFFUSION | PROP_THERMAL_DIFFUSION
+    out = {"ms": [], "ms_tables": [], "ms_state_kernels": [], "launches": 0}
+    res = None
+    for step in range(steps + 1):                 # first pass is the warm-up
+        kin._caches = {}
+        t0 = time.perf_counter()
+        cache = kin.tcache(T, SP_N, props)
+        t1 = time.perf_counter()
+        res = kin.transport_batch(T, Vm, x, N=SP_N, properties=props, eos_inputs=eos, cache=cache)
+        t2 = time.perf_counter()
+        tm = kin.dev.last_timings()
+        if step > 0:
+            out["ms"].append(1e3 * (t2 - t0)); out["ms_tables"].append(1e3 * (t1 - t0)); out["ms_state_kernels"].append(tm["ms_state_kernels"])
+            out["launches"] += int(tm["launches_tcache"] + tm["launches_batch"])
+    out["n"] = int(T.size)
+    out["stage_ms"] = {k: tm[k] for k in ("ms_omega_stage", "ms_tl_stage", "ms_bracket_stage", "ms_state_kernels")}
+    out["h2d"] = int(T.nbytes + Vm.nbytes + x.nbytes + eos["dmudn"].nbytes)
+    out["d2h"] = int(res["D"].nbytes + res["DT"].nbytes + 4 * T.size)
+    out["finite"] = bool(np.isfinite(res["D"]).all() and np.isfinite(res["DT"]).all())
+    return out
+
+
 # ------------------------------------------------------------------------------------------------ clocks
 class ClockSampler:
     Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
@@ -139,6 +248,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cpu-sample", type=int, default=0, help="Omega count of the CPU sample (default: scaled to the host cores)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-state-points", action="store_true", help="skip the RET state-point leg (profiling runs of the Omega kernels)")
     ap.add_argument("--nt", type=int, default=0, help="profiling only: shrink the per-GPU T grid (a line produced with --nt is not a bench value)")
     args = ap.parse_args()
     if args.nt:
@@ -247,8 +357,19 @@ def main():
         dist.all_reduce(t2, op=dist.ReduceOp.MAX)
     e2e_value = n_out * world * args.steps / (float(t2.item()) * 1e-3)
 
+    # RET state points (configs[2]): every rank runs its own grid; max over ranks
+    sp = None
+    if not args.no_state_points:
+        plan.close()
+        barrier()
+        sp = run_state_points(local_rank, rank, world, n_gpus, max(1, min(args.steps, 3)))
+        barrier()
+        t3 = torch.tensor([float(np.mean(sp["ms"]))], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t3, op=dist.ReduceOp.MAX)
+        sp["ms_max"] = float(t3.item())
+
     if rank == 0:
-        c = plan.counters()
         achieved = nodes * F_NODE / (theta_ms * 1e-3) / 1e12 if theta_ms > 0 else None
         out = {"metric": METRIC, "value": value, "unit": "Omega/s", "n_gpus": n_gpus, "steps": args.steps, "warmup": max(args.warmup, 3),
                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
@@ -260,7 +381,27 @@ def main():
                                            "datasheet 37 TFLOP/s)",
                             "algorithmic": f"{F_NODE:.0f} nominal flop per tanh-sinh node (SURVEY 8d) x touched nodes",
                             "nodes_per_step": nodes / args.steps, "chi_evals_per_step": c["chi_evals"], "kernel_ms_per_step": theta_ms / args.steps,
-                            "kernel_share_of_step": theta_ms / ms, "mesh_ms_per_step": mesh_ms / args.steps, "passes": c["passes"]}}
+                            "kernel_share_of_step": theta_ms / ms, "mesh_ms_per_step": mesh_ms / args.steps, "passes": c["passes"],
+                            "executed": {"fp64_instr_per_node": FP64_INSTR_PER_NODE,
+                                         "fp64_pipe_util_est": (nodes * FP64_INSTR_PER_NODE / (theta_ms * 1e-3)) / (peak_tflops * 1e12 / 2.0) if theta_ms > 0 else None,
+                                         "note": "frac > 1 because the algorithmic count (SURVEY 8d) prices the reference's per-node log/exp/div/rsqrt (76 of 98 "
+                                                 "nominal flop); the kernel removes them algebraically ((sigma/r)^lam = u^lam (sigma/R)^lam with u^lam tabulated) "
+                                                 "and issues ~11 FP64-pipe instructions per node. fp64_pipe_util_est = executed FP64 instructions / DFMA issue peak; "
+                                                 "the ncu-measured pipe utilisation is in profiles/"}}}
+        if sp is not None:
+            out["gpu_launches"] = launches + sp["launches"]
+            n_sp = sp["n"] * world
+            out["state_points"] = {"workload": f"configs[2]: RET-Mie {SP_COMPS}, N={SP_N}, interdiffusion (CoN) + thermal_diffusion_coeff on a "
+                                               f"{SP_GRID[0]}x{SP_GRID[1]}x{SP_GRID[2]} T x rho* x x grid per GPU, device tables rebuilt every step",
+                                   "value": n_sp / (sp["ms_max"] * 1e-3), "unit": "state points/s", "ms_per_step": sp["ms_max"],
+                                   "ms_tables": float(np.mean(sp["ms_tables"])), "stage_ms": sp["stage_ms"], "n_per_gpu": sp["n"],
+                                   "e2e": {"value": n_sp / (sp["ms_max"] * 1e-3), "unit": "state points/s", "h2d_bytes_per_step": sp["h2d"],
+                                           "d2h_bytes_per_step": sp["d2h"]},
+                                   "all_finite": sp["finite"],
+                                   "note": "host buffers in and out through kg_tcache_create + kg_transport_batch (the e2e path); EoS inputs (dmu/dn) "
+                                           "are synthetic arrays prepared outside the timed region"}
+            if not args.no_cpu_baseline:
+                out["state_points"]["cpu_baseline"] = sp_cpu_baseline(cores)
         if not args.no_cpu_baseline:
             n_sample = args.cpu_sample or min(64, max(16, cores))
             cb, _ = run_cpu_reference(n_gpus, n_sample, min(cores, n_sample))

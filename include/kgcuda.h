@@ -173,6 +173,13 @@ int kg_tcache_fetch(kg_tcache* c, double* omega, double* mtl, double* etl, uint8
 int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const double* T, const double* Vm, const double* x,
                        const kg_transport_opts* opts, const kg_eos_inputs* eos, const kg_transport_out* out, int32_t* status);
 
+/* Stage timings of the last kg_tcache_create / kg_transport_batch on this model (bench accounting):
+ *  out[0] ms in rdf_kernel + state_kernel of the last batch (CUDA events on the model stream)
+ *  out[1] ms of the tcache Omega stage (numerical quadrature, host clock around the synchronised stage)
+ *  out[2] ms of the tcache transfer-length stage      out[3] ms of correlation + BH diameters + bracket sums
+ *  out[4] kernel launches of the last tcache build     out[5] kernel launches of the last batch */
+int kg_last_timings(const kg_model* m, double* out8);
+
 /* FP64 FMA-pipe peak probe: runs a register-resident DFMA chain kernel and returns the measured TFLOP/s
  * (2 flop per DFMA). Used as the roofline denominator (MEASURED_PEAKS.json has no FP64 figure). */
 int kg_measure_fp64_peak(int device, double* tflops, double* sm_mhz_est);

@@ -14,7 +14,7 @@ EXPORTS = [
     "kg_model_create", "kg_model_destroy", "kg_last_error", "kg_model_npairs", "kg_chi_points", "kg_omega_batch",
     "kg_omega_plan_create", "kg_omega_plan_run", "kg_omega_plan_sync", "kg_omega_plan_fetch", "kg_omega_plan_omega_dev",
     "kg_omega_plan_destroy", "kg_omega_plan_counters", "kg_measure_fp64_peak", "kg_model_set_stream", "kg_omega_plan_export_dev", "kg_transfer_lengths_batch",
-    "kg_omega_plan_create_masked", "kg_tcache_create", "kg_tcache_destroy", "kg_tcache_lr", "kg_tcache_fetch", "kg_transport_batch",
+    "kg_omega_plan_create_masked", "kg_tcache_create", "kg_tcache_destroy", "kg_tcache_lr", "kg_tcache_fetch", "kg_transport_batch", "kg_last_timings",
 ]
 
 
@@ -54,6 +54,7 @@ def lib():
         L.kg_measure_fp64_peak.argtypes = [C.c_int, dp, dp]
         L.kg_omega_plan_create_masked.argtypes = [C.c_void_p, C.c_int, dp, C.c_int, ip, ip, dp, C.POINTER(C.c_uint8), C.POINTER(C.c_void_p)]
         L.kg_tcache_create.argtypes = [C.c_void_p, C.c_void_p, C.c_int, dp, dp, C.POINTER(C.c_void_p)]
+        L.kg_last_timings.argtypes = [C.c_void_p, dp]
         L.kg_tcache_destroy.argtypes = [C.c_void_p]
         L.kg_tcache_destroy.restype = None
         L.kg_tcache_lr.argtypes = [C.c_void_p, ip, ip]

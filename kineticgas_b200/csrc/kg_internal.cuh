@@ -20,6 +20,8 @@ struct kg_model {
     bool own_stream = true;
     std::string err;
     int sm_count = 148;
+    // stage timings of the last kg_tcache_create / kg_transport_batch on this model (kg_last_timings)
+    double timings[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     void set_error(const std::string& s) { err = s; }
 };
 

@@ -19,6 +19,7 @@
 #include <cstring>
 #include <map>
 #include <algorithm>
+#include <chrono>
 
 using namespace kg;
 
@@ -828,6 +829,10 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
     TC_CUDA(cudaMalloc(&c->d_omega, need.size() * sizeof(double)));
     TC_CUDA(cudaMemset(c->d_omega, 0, need.size() * sizeof(double)));
     cudaStream_t s = m->stream;
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto ms_since = [&](std::chrono::steady_clock::time_point t0) { return std::chrono::duration<double, std::milli>(now() - t0).count(); };
+    auto t_stage = now();
+    m->timings[1] = m->timings[2] = m->timings[3] = m->timings[4] = 0;
     if (any_numeric) {
         kg_omega_plan* plan = nullptr;
         std::vector<int32_t> ll(tm.lr_l, tm.lr_l + nlr), rr(tm.lr_r, tm.lr_r + nlr);
@@ -836,11 +841,13 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
         if (!rc) rc = kg_omega_plan_export_dev(plan, c->d_omega, nullptr);
         std::vector<int32_t> pst((size_t) nT * Np, 0);
         if (!rc) rc = kg_omega_plan_fetch(plan, nullptr, nullptr, pst.data());
+        if (!rc) { double cnt[12]; if (!kg_omega_plan_counters(plan, cnt)) m->timings[4] += cnt[7]; }
         if (plan) kg_omega_plan_destroy(plan);
         if (rc) { kg_tcache_destroy(c); return rc; }
         int bad = 0; for (int v : pst) bad |= v;
         if (bad & KG_STATUS_GETR_MAXITER) { set_error("get_R reached max iter!"); kg_tcache_destroy(c); return -4; }
     }
+    m->timings[1] = ms_since(t_stage); t_stage = now();
     std::vector<MiePair> mp_dev(Np), mp_int((size_t) nc * nc), mp_diag(nc);
     if (mie) {
         for (int p = 0; p < Np; p++) {
@@ -872,6 +879,7 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
         int bad = 0; for (int v : tst) bad |= v;
         if (bad & KG_STATUS_BMID) { set_error("Unable to converge bmid!"); kg_tcache_destroy(c); return -4; }
         if (bad & KG_STATUS_GETR_MAXITER) { set_error("get_R reached max iter!"); kg_tcache_destroy(c); return -4; }
+        m->timings[2] = ms_since(t_stage); m->timings[4] += 3.0 * Np;
         TC_CUDA(upload(&c->d_mtl, c->h_mtl)); TC_CUDA(upload(&c->d_etl, c->h_etl));
         MiePair* d_diag = nullptr;
         TC_CUDA(upload(&d_diag, mp_diag));
@@ -892,6 +900,8 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
         cudaFree(d_wA); cudaFree(d_wAp); cudaFree(d_wBp); cudaFree(d_wBpp); cudaFree(d_hpre);
     }
 #undef TC_CUDA
+    m->timings[3] = ms_since(t_stage) - m->timings[2];
+    m->timings[4] += (any_corr ? 1 : 0) + (opts->is_idealgas ? 0 : 1) + 1;
     *out = c;
     return 0;
 }
@@ -989,7 +999,11 @@ extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const do
     for (auto& mp : maps) if (mp.host) { *mp.dev = db.alloc<double>(mp.count); NEED(*mp.dev); CUDA_OK(cudaMemsetAsync(*mp.dev, 0, mp.count * sizeof(double), s)); }
     a.status = db.alloc<int>(n); NEED(a.status);
 #undef NEED
+    cudaEvent_t ev0, ev1;
+    CUDA_OK(cudaEventCreate(&ev0)); CUDA_OK(cudaEventCreate(&ev1));
+    CUDA_OK(cudaEventRecord(ev0, s));
     if (launch_state(c, a, s, a.x, d_rdf)) { set_error("kg_transport_batch: kernel launch failed"); return -2; }
+    CUDA_OK(cudaEventRecord(ev1, s));
     for (auto& mp : maps) if (mp.host) CUDA_OK(cudaMemcpyAsync(mp.host, *mp.dev, mp.count * sizeof(double), cudaMemcpyDeviceToHost, s));
     if (out->rdf) {
         if (opts->is_idealgas) for (size_t k = 0; k < (size_t) n * nc * nc; k++) out->rdf[k] = 1.0;
@@ -999,6 +1013,14 @@ extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const do
     std::vector<int> st(n);
     CUDA_OK(cudaMemcpyAsync(st.data(), a.status, n * sizeof(int), cudaMemcpyDeviceToHost, s));
     CUDA_OK(cudaStreamSynchronize(s));
+    float kms = 0; cudaEventElapsedTime(&kms, ev0, ev1); cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+    m->timings[0] = kms; m->timings[5] = opts->is_idealgas ? 1 : 2;
     if (status) for (int k = 0; k < n; k++) status[k] = st[k];
+    return 0;
+}
+
+extern "C" int kg_last_timings(const kg_model* m, double* out8) {
+    if (!m || !out8) return -1;
+    for (int k = 0; k < 8; k++) out8[k] = m->timings[k];
     return 0;
 }

@@ -105,6 +105,11 @@ class DeviceModel:
         raise_on_status(st)
         return mtl, etl
 
+    def last_timings(self):
+        out = np.zeros(8)
+        self.L.kg_last_timings(self.h, _p(out))
+        return dict(zip(["ms_state_kernels", "ms_omega_stage", "ms_tl_stage", "ms_bracket_stage", "launches_tcache", "launches_batch"], out.tolist()))
+
     def omega_plan(self, T, l, r, coeff_T=None):
         return OmegaPlan(self, T, l, r, coeff_T)
 
