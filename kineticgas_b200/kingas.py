@@ -41,14 +41,15 @@ def _ptr(a):
 class TCache:
     """Device-resident per-temperature tables (kg_tcache): the GPU-side KineticGasCache."""
 
-    def __init__(self, kin, T, N, properties):
+    def __init__(self, kin, T, N, properties, coeff_T=None):
         # holds the DeviceModel (not the MieKinGas object): no reference cycle, and the kg_model outlives its caches
         self.dev = kin.dev
         self.T = np.ascontiguousarray(np.atleast_1d(T), float)
         self.opts = kin._opts(N, properties)
         h = C.c_void_p()
         L = self.dev.L
-        self.dev._chk(L.kg_tcache_create(self.dev.h, C.byref(self.opts), self.T.size, _ptr(self.T), None, C.byref(h)), "kg_tcache_create")
+        self.coeff_T = None if coeff_T is None else np.ascontiguousarray(coeff_T, float)
+        self.dev._chk(L.kg_tcache_create(self.dev.h, C.byref(self.opts), self.T.size, _ptr(self.T), _ptr(self.coeff_T), C.byref(h)), "kg_tcache_create")
         self.h = h
 
     def lr(self):
@@ -135,6 +136,16 @@ class MieKinGas:
     def set_eos(self, eos):
         self.eos = eos
 
+    def _coeff_T(self, T):
+        """Per-temperature effective coefficients [nT][npairs][6] of T-dependent potentials; None for plain Mie."""
+        return None
+
+    def omega_table(self, T, l, r):
+        """Additive batched entry point (SURVEY 8b.3): Omega^(l,r)_ij by numerical quadrature (Spherical::omega, no
+        correlation) for every T, pair and (l,r): [nT][npairs][nlr], SI units."""
+        T = np.atleast_1d(np.asarray(T, float))
+        return self.dev.omega_batch(T, l, r, coeff_T=self._coeff_T(T))
+
     def set_omega_correlation_active(self, active):
         """cpp/MieKinGas.cpp:150-155 -- also drops the device tables, like cache.omega.clear()."""
         if active != self.omega_correlation_active:
@@ -158,7 +169,7 @@ class MieKinGas:
         Tu = np.unique(np.asarray(T, float))
         key = (N, properties, self.omega_correlation_active, Tu.tobytes())
         if key not in self._caches:
-            self._caches[key] = TCache(self, Tu, N, properties)
+            self._caches[key] = TCache(self, Tu, N, properties, self._coeff_T(Tu))
         return self._caches[key]
 
     def _eos_arrays(self, T, Vm, x, need_dmudn, need_cp, need_dvdn, eos_inputs):
@@ -347,3 +358,99 @@ class MieKinGas:
 
     def get_etl(self, particle_density, T, x):
         return self._pair_matrix(self.dev.transfer_lengths([T])[1][0])
+
+
+class QuantumMie(MieKinGas):
+    """pykingas.QuantumMie (Feynman-Hibbs corrected Mie, cpp/QuantumMie.cpp, cpp/ExtendedSutherland.cpp) on the GPU.
+
+    u(r;T) = eps sum_k C_k beta^(bexp_k) (sigma/r)^lam_k with beta = eps/kT: 2, 4 or 6 power-law terms for FH order 0, 1, 2
+    (cpp/QuantumMie.cpp:73-109). The device kernels take the terms' exponents from the model and the T-dependent
+    effective coefficients C_eff(T) = C_k beta^bexp_k (cpp/ExtendedSutherland.cpp:182-200) per temperature. Collision
+    integrals are always integrated (ExtSutherland has no correlation branch). Only is_idealgas=True models can run the
+    state-point assembly (the extended-Sutherland RDF is not built yet)."""
+
+    def __init__(self, comps, mole_weights=None, sigma=None, eps_div_k=None, la=None, lr=None, lij=0, kij=0,
+                 N=4, FH_orders=None, is_idealgas=False, use_eos=None, device=0):
+        from .fluids import MIE_FH, HBAR
+        ids = comps.split(",")
+        if isinstance(FH_orders, int):
+            FH_orders = [FH_orders] * len(ids)
+        if FH_orders is None:
+            FH_orders = [0] * len(ids)          # database default_fh_order is 0 for HE, H2 (fluids/HE.json:117, fluids/H2.json:128)
+        if len(set(FH_orders)) != 1:
+            raise RuntimeError("All FH orders must be equal!")        # cpp/QuantumMie.cpp:39-41
+        self.FH_order = int(FH_orders[0])
+
+        def db(col):
+            return [(MIE_FH[(c, self.FH_order)][col] if self.FH_order > 0 else MIE[c][col + 1]) for c in ids]
+
+        def merged(given, col):
+            base = db(col)
+            return base if given is None else [base[i] if given[i] is None else given[i] for i in range(len(ids))]
+
+        self._HBAR = HBAR
+        super().__init__(comps, mole_weights=mole_weights, sigma=merged(sigma, 0), eps_div_k=merged(eps_div_k, 1),
+                         la=merged(la, 2), lr=merged(lr, 3), lij=lij, kij=kij, N=N, is_idealgas=is_idealgas, use_eos=use_eos, device=device)
+        self.omega_correlation_active = False
+
+    def _build_device_model(self):
+        from .model import power_sum_desc
+        nt = 2 * (self.FH_order + 1)
+        ncd = 1 if self._is_singlecomp else self.ncomps
+        self._C, self._bexp, descs = [], [], []
+        for i in range(ncd):
+            for j in range(i, ncd):
+                la, lr, sig, eps = self.la[i, j], self.lr[i, j], self.sigma_ij[i, j], self.epsilon_ij[i, j]
+                C0 = (lr / (lr - la)) * (lr / la) ** (la / (lr - la))
+                q1 = lambda lam: lam * (lam - 1)                                   # cpp/QuantumMie.h:52-58
+                q2 = lambda lam: 0.5 * (lam + 2) * (lam + 1) * q1(lam)
+                mu_inv = 1.0 / self.m[i] + 1.0 / self.m[j]
+                D1 = self._HBAR ** 2 * (mu_inv if self.FH_order > 0 else 0.0) / 24.0
+                D2 = self._HBAR ** 2 * (mu_inv if self.FH_order > 1 else 0.0) / 24.0
+                Ck = [C0, -C0, C0 * D1 * q1(lr) * sig ** -2 * eps ** -1, -C0 * D1 * q1(la) * sig ** -2 * eps ** -1,
+                      C0 * D2 ** 2 * q2(lr) * sig ** -4 * eps ** -2, -C0 * D2 ** 2 * q2(la) * sig ** -4 * eps ** -2][:nt]
+                lam = [lr, la, lr + 2.0, la + 2.0, lr + 4.0, la + 4.0][:nt]
+                self._C.append(Ck)
+                self._bexp.append([0, 0, 1, 1, 2, 2][:nt])
+                descs.append(power_sum_desc(sig, eps, Ck, lam))
+        self._pair_eps = [d.eps for d in descs]
+        self.dev = DeviceModel(descs, self.m[:ncd], self._is_singlecomp, device=self._device)
+        self._caches = {}
+
+    def _coeff_T(self, T):
+        T = np.atleast_1d(np.asarray(T, float))
+        out = np.zeros((T.size, len(self._C), _lib.KG_MAX_TERMS))
+        for p, (Ck, be, eps) in enumerate(zip(self._C, self._bexp, self._pair_eps)):
+            beta = eps / (BOLTZMANN * T)
+            for k, (c, b) in enumerate(zip(Ck, be)):
+                out[:, p, k] = c * beta ** b if b else c
+        return out
+
+    def potential(self, i, j, r, T):
+        """u_ij(r; T) [J] (ExtSutherland::potential(i, j, r, T, rho), cpp/ExtendedSutherland.cpp:121-130)."""
+        p = self.dev.pair_index(0 if self._is_singlecomp else i, 0 if self._is_singlecomp else j)
+        cf = self._coeff_T([T])[0, p]
+        d = self.dev.descs[p]
+        return d.eps * sum(cf[k] * (d.sigma / r) ** d.lam[k] for k in range(d.nterms))
+
+    def get_sigma_eff(self, T):
+        """Root of u(r;T) by the reference's Newton iteration (cpp/ExtendedSutherland.cpp:202-217), host side utility."""
+        out = np.zeros((self.ncomps, self.ncomps))
+        for i in range(self.ncomps):
+            for j in range(i, self.ncomps):
+                s = self.sigma_ij[i, j]
+                while True:
+                    h = s * 1e-7
+                    u = self.potential(i, j, s, T)
+                    ur = (self.potential(i, j, s + h, T) - self.potential(i, j, s - h, T)) / (2 * h)
+                    s -= u / ur
+                    if abs(u) / self.epsilon_ij[i, j] <= 1e-6:
+                        break
+                out[i, j] = out[j, i] = s
+        return out
+
+    def get_mtl(self, particle_density, T, x):
+        return self._pair_matrix(self.dev.transfer_lengths([T], coeff_T=self._coeff_T([T]))[0][0])
+
+    def get_etl(self, particle_density, T, x):
+        return self._pair_matrix(self.dev.transfer_lengths([T], coeff_T=self._coeff_T([T]))[1][0])

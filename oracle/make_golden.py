@@ -113,3 +113,45 @@ def transport_golden(cases=TRANSPORT_CASES, fname="transport_reference.npz"):
 
 if __name__ == "__main__" and "transport" in sys.argv[1:]:
     transport_golden()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Feynman-Hibbs Mie (QuantumMie, configs[3]): Omega by quadrature with T-dependent coefficients, ideal-gas properties
+# ---------------------------------------------------------------------------------------------------------------
+QMIE_LR = [(1, 1), (1, 2), (1, 3), (2, 2), (2, 3), (2, 4), (3, 3)]
+QMIE_CASES = [("HE", 1, [25.0, 60.0, 300.0]), ("H2", 1, [40.0, 150.0]), ("HE", 2, [80.0])]
+
+
+def qmie_golden(fname="qmie_reference.npz"):
+    from kineticgas_b200.fluids import MIE, MIE_FH
+    out = {}
+    rng = np.random.default_rng(99)
+    for comp, fh, Ts in QMIE_CASES:
+        sig, epsk, la, lr = MIE_FH[(comp, fh)]
+        Mw = MIE[comp][0]
+        m = ref.RefQuantumMie([Mw], [sig], [epsk], [la], [lr], fh, is_idealgas=True)
+        for T in Ts:
+            key = f"{comp}_FH{fh}_{T:g}"
+            m.set_internals(T)
+            out[key + "_ceff"] = m.c_eff(0, 0)
+            g = rng.uniform(0.05, 4, 24)
+            b = rng.uniform(0.01, 3, 24)
+            out[key + "_g"], out[key + "_b"] = g, b
+            out[key + "_chi"] = m.chi(0, 0, T, g, b * sig)
+            out[key + "_omega"] = np.array([m.omega(0, 0, l, r, T) for (l, r) in QMIE_LR])
+            Vm = 8.314 * T / 1e5
+            m.set_eos(dmudn=np.array([[8.314 * T]]), cp_id=np.array([2.5 * 8.31446261815324 + 1.0]), p=1e5, vm=Vm, dvdn=np.array([Vm]))
+            out[key + "_eta"] = np.array(m.viscosity(T, Vm, [0.5, 0.5], 2))
+            out[key + "_lambda"] = m.thermal_conductivity_contribs(T, Vm, [0.5, 0.5], 2)
+            out[key + "_D"] = m.interdiffusion(T, Vm, [0.5, 0.5], 2, frame=1)
+            print(key, out[key + "_omega"], out[key + "_eta"], out[key + "_lambda"], out[key + "_D"], flush=True)
+    np.savez(os.path.join(GOLD, fname), **out)
+
+
+if __name__ == "__main__" and "qmie" in sys.argv[1:]:
+    qmie_golden()
+
+FIVE_CASES = [("five_comp", "C1,C2,C3,N2,CO2", 2, False, [(400.0, 0.25, [0.35, 0.2, 0.1, 0.15, 0.2]), (400.0, 0.5, [0.05, 0.05, 0.3, 0.5, 0.1])])]
+
+if __name__ == "__main__" and "five" in sys.argv[1:]:
+    transport_golden(FIVE_CASES, "transport5_reference.npz")

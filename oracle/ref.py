@@ -61,6 +61,10 @@ def lib():
                                            C.c_int, dp, ip, ip]
         L.kgref_thermal_diffusion_coeff.argtypes = [C.c_void_p, C.c_double, C.c_double, dp, C.c_int, C.c_int, C.c_int, C.c_int,
                                                     C.c_int, dp, ip]
+        L.kgref_qmie_create.restype = C.c_void_p
+        L.kgref_qmie_create.argtypes = [C.c_int, dp, dp, dp, dp, dp, C.c_int, C.c_int, C.c_int]
+        L.kgref_set_internals.argtypes = [C.c_void_p, C.c_double, C.c_double]
+        L.kgref_c_eff.argtypes = [C.c_void_p, C.c_int, C.c_int, dp, ip]
         _LIB = L
     return _LIB
 
@@ -234,3 +238,44 @@ class RefMie:
         n = C.c_int()
         self._chk(self.L.kgref_thermal_diffusion_coeff(self.h, T, Vm, _p(x), x.size, N, frame, dep, solvent, _p(out), C.byref(n)))
         return out[:n.value].copy()
+
+
+class RefQuantumMie(RefMie):
+    """The reference's QuantumMie through its vector constructor (cpp/QuantumMie.cpp:5-49); parameters mixed like
+    pykingas/MieType.py (kij = lij = 0). Every call that needs the T-dependent coefficients first calls set_internals,
+    as the reference's public property methods do."""
+
+    def __init__(self, Mw, sigma, eps_div_k, la, lr, fh_order, is_idealgas=True):
+        single = len(Mw) == 1
+        if single:
+            Mw, sigma, eps_div_k, la, lr = [list(v) * 2 for v in (Mw, sigma, eps_div_k, la, lr)]
+        self.nc = len(Mw)
+        self.single = single
+        self.m = np.array(Mw, float) * 1e-3 / AVOGADRO
+        s = np.array(sigma, float)
+        e = np.array(eps_div_k, float) * BOLTZMANN
+        self.sigma = np.ascontiguousarray(0.5 * (s[:, None] + s[None, :]))
+        self.eps = np.ascontiguousarray(np.sqrt(e[None, :] * e[:, None]))
+        la_, lr_ = np.array(la, float), np.array(lr, float)
+        self.la = np.ascontiguousarray(3 + np.sqrt((la_[:, None] - 3) * (la_[None, :] - 3)))
+        self.lr = np.ascontiguousarray(3 + np.sqrt((lr_[:, None] - 3) * (lr_[None, :] - 3)))
+        self.L = lib()
+        self.h = self.L.kgref_qmie_create(self.nc, _p(self.m), _p(self.sigma), _p(self.eps), _p(self.la), _p(self.lr), int(fh_order),
+                                          int(is_idealgas), int(single))
+
+    def set_internals(self, T, rho=1e20):
+        self._chk(self.L.kgref_set_internals(self.h, rho, T))
+
+    def c_eff(self, i, j):
+        out = np.zeros(6)
+        n = C.c_int()
+        self._chk(self.L.kgref_c_eff(self.h, i, j, _p(out), C.byref(n)))
+        return out[:n.value]
+
+    def omega(self, i, j, l, r, T, model=False):
+        self.set_internals(T)
+        return super().omega(i, j, l, r, T, model=model)
+
+    def chi(self, i, j, T, g, b):
+        self.set_internals(T)
+        return super().chi(i, j, T, g, b)

@@ -8,6 +8,7 @@
 // EoS-derived inputs enter through a table-backed GenericEoS (cpp/eos_interface.h:57-119) because
 // thermopack's Fortran core cannot be built in this image.
 #include "MieKinGas.h"
+#include "QuantumMie.h"
 #include "Integration/Integration.h"
 #include <cstring>
 #include <set>
@@ -35,7 +36,9 @@ struct TableEoS {
 };
 
 struct Handle {
-    std::unique_ptr<MieKinGas> kin;
+    std::unique_ptr<Spherical> kin;
+    MieKinGas* mie = nullptr;          // set when kin is a MieKinGas
+    QuantumMie* qmie = nullptr;        // set when kin is a QuantumMie
     int nc;
     std::string err;
 };
@@ -66,14 +69,41 @@ void* kgref_mie_create(int nc, const double* m, const double* sigma, const doubl
                        const double* la, const double* lr, int is_idealgas, int is_singlecomp) {
     Handle* h = new Handle;
     h->nc = nc;
-    h->kin.reset(new MieAccess(vector1d(m, m + nc), to2d(sigma, nc), to2d(eps, nc), to2d(la, nc), to2d(lr, nc),
-                               is_idealgas != 0, is_singlecomp != 0));
+    MieAccess* mk = new MieAccess(vector1d(m, m + nc), to2d(sigma, nc), to2d(eps, nc), to2d(la, nc), to2d(lr, nc),
+                                  is_idealgas != 0, is_singlecomp != 0);
+    h->kin.reset(mk);
+    h->mie = mk;
     return h;
+}
+// QuantumMie through its vector constructor (cpp/QuantumMie.cpp:5-49)
+void* kgref_qmie_create(int nc, const double* m, const double* sigma, const double* eps, const double* la, const double* lr,
+                        int fh_order, int is_idealgas, int is_singlecomp) {
+    Handle* h = new Handle;
+    h->nc = nc;
+    QuantumMie* q = new QuantumMie(vector1d(m, m + nc), to2d(sigma, nc), to2d(eps, nc), to2d(la, nc), to2d(lr, nc),
+                                   std::vector<int>(nc, fh_order), is_idealgas != 0, is_singlecomp != 0);
+    h->kin.reset(q);
+    h->qmie = q;
+    return h;
+}
+// T-dependent potentials: ExtSutherland::set_internals -> set_effective_params (cpp/ExtendedSutherland.h:140, .cpp:168-180)
+int kgref_set_internals(void* hv, double rho, double T) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{ if (h->qmie) h->qmie->set_internals(rho, T, vector1d(h->nc, 1.0 / h->nc)); });
+}
+// effective coefficients C_eff[k][i][j] after set_internals (what the device path receives as coeff_T)
+int kgref_c_eff(void* hv, int i, int j, double* out, int* nterms) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{
+        if (!h->qmie) throw std::runtime_error("not an ExtSutherland model");
+        *nterms = (int) h->qmie->nterms;
+        for (size_t k = 0; k < h->qmie->nterms; k++) out[k] = static_cast<double>(h->qmie->C_eff[k][i][j]);
+    });
 }
 void kgref_destroy(void* hv) { delete static_cast<Handle*>(hv); }
 const char* kgref_last_error(void* hv) { return static_cast<Handle*>(hv)->err.c_str(); }
-void kgref_clear_cache(void* hv) { static_cast<MieAccess*>(static_cast<Handle*>(hv)->kin.get())->clear_cache(); }
-void kgref_set_omega_correlation_active(void* hv, int active) { static_cast<Handle*>(hv)->kin->set_omega_correlation_active(active != 0); }
+void kgref_clear_cache(void* hv) { Handle* h = static_cast<Handle*>(hv); if (h->mie) static_cast<MieAccess*>(h->mie)->clear_cache(); }
+void kgref_set_omega_correlation_active(void* hv, int active) { Handle* h = static_cast<Handle*>(hv); if (h->mie) h->mie->set_omega_correlation_active(active != 0); }
 void kgref_set_tl_model(void* hv, int id) { static_cast<Handle*>(hv)->kin->set_transfer_length_model(id); }
 
 void kgref_set_eos_tables(void* hv, const double* dmudn, const double* cp_id, double p, double vm, const double* dvdn) {
@@ -117,7 +147,7 @@ double kgref_w_integrand(void* hv, int i, int j, double T, double g, double b, i
 // omega through the normal (cached, correlation-aware) path: MieKinGas::omega -> Spherical::omega
 int kgref_omega(void* hv, int i, int j, int l, int r, double T, double* out) {
     Handle* h = static_cast<Handle*>(hv);
-    return guarded(h, [&]{ *out = static_cast<Spherical*>(h->kin.get())->Spherical::omega(i, j, l, r, T); });
+    return guarded(h, [&]{ *out = h->kin->Spherical::omega(i, j, l, r, T); });
 }
 int kgref_omega_model(void* hv, int i, int j, int l, int r, double T, double* out) {
     Handle* h = static_cast<Handle*>(hv);
@@ -186,7 +216,7 @@ int kgref_rdf(void* hv, double rho, double T, const double* x, double* out) {
 }
 int kgref_bh_diameters(void* hv, double T, double* out) {
     Handle* h = static_cast<Handle*>(hv);
-    return guarded(h, [&]{ flat(h->kin->get_BH_diameters(T), out); });
+    return guarded(h, [&]{ if (!h->mie) throw std::runtime_error("not a MieKinGas model"); flat(h->mie->get_BH_diameters(T), out); });
 }
 int kgref_K_factors(void* hv, double rho, double T, const double* x, double* K, double* Kp) {
     Handle* h = static_cast<Handle*>(hv);

@@ -64,6 +64,12 @@ template<class T> Dual<T> operator/(const Dual<T>& a, const Dual<T>& b) {
     T q = a.val / b.val;
     return mk<T>(q, (a.grad - q * b.grad) / b.val);
 }
+// ---- mixed order (dual op dual2nd): the lower-order operand is promoted (no seed)
+#define KG_AD_MIXED(op) \
+    template<class T> Dual<Dual<T>> operator op(const Dual<T>& a, const Dual<Dual<T>>& b) { return Dual<Dual<T>>(a) op b; } \
+    template<class T> Dual<Dual<T>> operator op(const Dual<Dual<T>>& a, const Dual<T>& b) { return a op Dual<Dual<T>>(b); }
+KG_AD_MIXED(+) KG_AD_MIXED(-) KG_AD_MIXED(*) KG_AD_MIXED(/)
+#undef KG_AD_MIXED
 // ---- dual (op) arithmetic
 #define KG_AD_ARITH template<class T, class A, std::enable_if_t<detail::is_arith<A>, int> = 0>
 KG_AD_ARITH Dual<T> operator+(const Dual<T>& a, A b) { return mk<T>(a.val + T(static_cast<double>(b)), a.grad); }
@@ -101,6 +107,8 @@ template<class T> Dual<T> pow(const Dual<T>& x, const Dual<T>& p) {
     T v = pow(x.val, p.val);
     return mk<T>(v, v * (p.grad * log(x.val) + p.val * x.grad / x.val));
 }
+template<class T> Dual<Dual<T>> pow(const Dual<T>& x, const Dual<Dual<T>>& p) { return pow(Dual<Dual<T>>(x), p); }
+template<class T> Dual<Dual<T>> pow(const Dual<Dual<T>>& x, const Dual<T>& p) { return pow(x, Dual<Dual<T>>(p)); }
 KG_AD_ARITH Dual<T> pow(A b_, const Dual<T>& p) {
     const double b = static_cast<double>(b_);
     T v = pow(T(b), p.val);
