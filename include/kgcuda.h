@@ -89,8 +89,9 @@ void kg_omega_plan_destroy(kg_omega_plan* p);
  *  out[2] columns whose theta_lim was evaluated                                   out[3] tanh-sinh nodes of those
  *  out[4] milliseconds in the chi kernel (CUDA events on the model stream)        out[5] ms in the theta_lim kernel
  *  out[6] ms in the mesh kernels          out[7] number of kernel launches        out[8] refinement passes
- *  out[9] H2D bytes of plan creation      out[10] D2H bytes of the last fetch     out[11] bytes of lattice + mask pools in HBM */
-int kg_omega_plan_counters(kg_omega_plan* p, double* out12);
+ *  out[9] H2D bytes of plan creation      out[10] D2H bytes of the last fetch     out[11] bytes of lattice + mask pools in HBM
+ *  out[12] largest cell list of one refinement level   out[13] cell-list capacity   out[14] its hard bound   out[15] times it was grown */
+int kg_omega_plan_counters(kg_omega_plan* p, double* out16);
 
 
 /* ================================================================================================================

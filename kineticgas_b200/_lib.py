@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libkgcuda.so")
+LIB_PATH = os.environ.get("KGCUDA_LIB", os.path.join(_HERE, "libkgcuda.so"))     # override: debug builds of the same library
 KG_MAX_TERMS = 6
 dp = C.POINTER(C.c_double)
 ip = C.POINTER(C.c_int32)

@@ -193,27 +193,67 @@ __device__ __forceinline__ double ts_term(const double* __restrict__ row, const 
 #endif
 }
 
-// Four consecutive nodes evaluated together (independent chains), then the reference's sequential stop rule applied in
-// order: a term is added only if all earlier ones were and |w f / I| > tol (Integration.cpp:431); NaN/Inf of the new
-// integrand value (radicand <= 0) ends the sum (Integration.cpp:430). J = tol * I is the running sum, scaled so that the
-// test is one compare. k = index of the last node examined (what the reference's loop variable holds at exit).
+// Fast form of the same term for the bulk of the sum. With halved per-lane constants (exact scalings)
+//   Xh = X/2 = (1/u^2) (c2/2 - sum_t (Ap_t/2) u^lam_t) - 1/2                    NT+1 DFMA
+//   q  = MUFU.RSQ64H seed of X, taken from the high word of Xh with its exponent bumped by one (integer pipe)
+//   c  = 3/2 - (Xh q) q   (one Newton step: rsqrt(X) = q c, relative error 1.5 delta^2 < 2e-13)    DMUL + DFMA
+//   z  = (w/u) q ,  I += z c                                                                        DMUL + DFMA
+// i.e. NT+5 FP64-pipe instructions per node and no FP64 compare: the stop rule is checked conservatively for four
+// nodes at once on the high words (positive doubles order like integers): every z_i must exceed tol * I_4 by two
+// high-word ulps (c = 1 +- 2^-20, I_i <= I_4 because all terms are positive) and I_4 must be finite and < 1e100.
+// Anything else -- the end of the sum, a non-positive radicand, NaN/Inf -- falls through to the exact sequential
+// replay below, which is the reference's rule term by term.
 template<int NT>
-__device__ __forceinline__ bool ts_step4(const double* __restrict__ r0, const double (&Ap)[NT], double c2, double& J, int& k) {
+__device__ __forceinline__ void ts_fast(const double* __restrict__ row, const double (&Aph)[NT], double c2h, double& z, double& c) {
+    double P = c2h;
+#pragma unroll
+    for (int t = 0; t < NT; t++) P = fma(-Aph[t], row[2 + t], P);
+    const double Xh = fma(row[1], P, -0.5);
+    const double q = rsqrt_seed(__hiloint2double(__double2hiint(Xh) + 0x00100000, 0));
+    const double a = Xh * q;
+    c = fma(-a, q, 1.5);
+    z = row[0] * q;
+}
+
+constexpr int HI_1E100 = 0x54B249AD;      // high word of 1e100
+
+// Four consecutive nodes evaluated together (independent chains), then the reference's sequential stop rule: a term is
+// added only if all earlier ones were and |w f / I| > tol (Integration.cpp:431); NaN/Inf of the new integrand value
+// (radicand <= 0) ends the sum (Integration.cpp:430). I is the running sum, k = index of the last node examined (what
+// the reference's loop variable holds at exit).
+template<int NT>
+__device__ __forceinline__ bool ts_step4(const double* __restrict__ r0, const double (&Aph)[NT], double c2h, double& I, int& k) {
     constexpr int W = 2 + NT;
-    const double t0 = ts_term<NT>(r0, Ap, c2);
-    const double t1 = ts_term<NT>(r0 + W, Ap, c2);
-    const double t2 = ts_term<NT>(r0 + 2 * W, Ap, c2);
-    const double t3 = ts_term<NT>(r0 + 3 * W, Ap, c2);
-    const double J1 = fma(TS_TOL, t0, J);
-    const double J2 = fma(TS_TOL, t1, J1);
-    const double J3 = fma(TS_TOL, t2, J2);
-    const double J4 = fma(TS_TOL, t3, J3);
-    const bool ok0 = fabs(t0) > fabs(J);
-    const bool ok1 = ok0 && (fabs(t1) > fabs(J1));
-    const bool ok2 = ok1 && (fabs(t2) > fabs(J2));
-    const bool ok3 = ok2 && (fabs(t3) > fabs(J3));
-    if (ok3) { J = J4; k += 4; return false; }
-    J = ok2 ? J3 : ok1 ? J2 : ok0 ? J1 : J;
+    double z0, z1, z2, z3, c0, c1, c2, c3;
+    ts_fast<NT>(r0, Aph, c2h, z0, c0);
+    ts_fast<NT>(r0 + W, Aph, c2h, z1, c1);
+    ts_fast<NT>(r0 + 2 * W, Aph, c2h, z2, c2);
+    ts_fast<NT>(r0 + 3 * W, Aph, c2h, z3, c3);
+    const double I1 = fma(z0, c0, I);
+    const double I2 = fma(z1, c1, I1);
+    const double I3 = fma(z2, c2, I2);
+    const double I4 = fma(z3, c3, I3);
+    const int lim = __double2hiint(TS_TOL * I4);
+    const int zmin = min(min(__double2hiint(z0), __double2hiint(z1)), min(__double2hiint(z2), __double2hiint(z3)));
+#ifndef KG_TS_NOFAST
+    if ((zmin > lim + 2) && (lim < HI_1E100) && (lim >= 0)) { I = I4; k += 4; return false; }
+#endif
+    // exact replay of these four nodes
+    double Ap[NT];
+#pragma unroll
+    for (int t = 0; t < NT; t++) Ap[t] = Aph[t] + Aph[t];
+    const double cc = c2h + c2h;
+    const double t0 = ts_term<NT>(r0, Ap, cc);
+    const double t1 = ts_term<NT>(r0 + W, Ap, cc);
+    const double t2 = ts_term<NT>(r0 + 2 * W, Ap, cc);
+    const double t3 = ts_term<NT>(r0 + 3 * W, Ap, cc);
+    const double S1 = I + t0, S2 = S1 + t1, S3 = S2 + t2, S4 = S3 + t3;
+    const bool ok0 = fabs(t0) > fabs(TS_TOL * I);
+    const bool ok1 = ok0 && (fabs(t1) > fabs(TS_TOL * S1));
+    const bool ok2 = ok1 && (fabs(t2) > fabs(TS_TOL * S2));
+    const bool ok3 = ok2 && (fabs(t3) > fabs(TS_TOL * S3));
+    if (ok3) { I = S4; k += 4; return false; }
+    I = ok2 ? S3 : ok1 ? S2 : ok0 ? S1 : I;
     k += 1 + (int) ok0 + (int) ok1 + (int) ok2;
     return true;
 }
@@ -225,19 +265,20 @@ template<int NT>
 __device__ double theta_integral(const double* __restrict__ srows, const double* __restrict__ grows, int KS,
                                  const double (&A)[NT], double c2, unsigned& nodes, int& status) {
     constexpr int W = 2 + NT;
-    double Ap[NT];
+    double Ap[NT], Aph[NT];
 #pragma unroll
-    for (int t = 0; t < NT; t++) Ap[t] = c2 * A[t];
-    double J = TS_TOL * ts_term<NT>(srows, Ap, c2);     // k = 1 is added unconditionally (Integration.cpp:425)
+    for (int t = 0; t < NT; t++) { Ap[t] = c2 * A[t]; Aph[t] = 0.5 * Ap[t]; }
+    double I = ts_term<NT>(srows, Ap, c2);              // k = 1 is added unconditionally (Integration.cpp:425)
+    const double c2h = 0.5 * c2;
     int k = 1;
     bool stop = false;
-    while (!stop && k + 4 <= KS) stop = ts_step4<NT>(srows + (size_t) k * W, Ap, c2, J, k);
+    while (!stop && k + 4 <= KS) stop = ts_step4<NT>(srows + (size_t) k * W, Aph, c2h, I, k);
     while (!stop) {
         if (k + 4 > KMAX) { status |= 2; break; }
-        stop = ts_step4<NT>(grows + (size_t) k * W, Ap, c2, J, k);
+        stop = ts_step4<NT>(grows + (size_t) k * W, Aph, c2h, I, k);
     }
     nodes += (unsigned) k;
-    return J / TS_TOL;
+    return I;
 }
 
 // Full single-lane evaluation of the theta integral for (g, b): R, A_t, c2, then the sum. Returns I; R_out in sigma.

@@ -66,23 +66,24 @@ __device__ __forceinline__ double lattice_coord(int n, double d) { return 1e-7 +
 // mesh kernels: the reference's recursive triangulation as a breadth-first walk over cell lists
 // ------------------------------------------------------------------------------------------------------------
 // A cell is one integration_step of the reference (cpp/Integration/Integration.cpp:145-236): entry corner (Nx,Ny), signed
-// x step, y step, owner (item,(l,r)). Packed in 64 bits: [0,26) owner, [26,34) Nx, [34,44) Ny, [44,47) log2|sx|, 47 sx<0,
-// [48,51) log2 sy.
-typedef unsigned long long Cell;
-__host__ __device__ __forceinline__ Cell pack_cell(unsigned owner, int Nx, int Ny, int sx, int sy) {
+// x step, y step. The refinement trees of the (l,r) of one item share most of their geometry, so a cell carries the
+// SET of (l,r) that reach it: the lattice is read once per cell and the predicate is evaluated per member.
+// lo: [0,22) item, [22,30) Nx, [30,40) Ny, [40,43) log2|sx|, 43 sx<0, [44,47) log2 sy.   hi: (l,r) membership bits.
+struct Cell { unsigned long long lo, hi; };
+__host__ __device__ __forceinline__ unsigned long long pack_cell(unsigned item, int Nx, int Ny, int sx, int sy) {
     const int ax = sx < 0 ? -sx : sx;
     unsigned lx = 0, ly = 0;
     while ((1 << lx) < ax) lx++;
     while ((1 << ly) < sy) ly++;
-    return (Cell) owner | ((Cell) Nx << 26) | ((Cell) Ny << 34) | ((Cell) lx << 44) | ((Cell) (sx < 0) << 47) | ((Cell) ly << 48);
+    return (unsigned long long) item | ((unsigned long long) Nx << 22) | ((unsigned long long) Ny << 30) | ((unsigned long long) lx << 40)
+         | ((unsigned long long) (sx < 0) << 43) | ((unsigned long long) ly << 44);
 }
 
 struct MeshView {
     const double* tab;
     unsigned* want;
-    const double* gfac;     // [nx] : 2 exp(-g^2) g^(2r+3) for this (regime, r)
-    int ny, nwords, l, nx_cut, ny_cut, ldg, ldb;
-    double dg, db, lim, cospi;
+    int ny, nwords, nx_cut, ny_cut, ldg, ldb;
+    double db, lim, cospi;
 };
 
 __device__ __forceinline__ double pow2(int e) { return __longlong_as_double((long long) (1023 + e) << 52); }
@@ -109,121 +110,161 @@ __device__ __forceinline__ void mesh_mark_cell(const MeshView& v, int Nx, int Ny
     if (sx < 0) { mesh_mark(v, Nx + sx, Ny); mesh_mark(v, Nx + sx, Ny + sy); }
 }
 
-// integrand value at lattice node (Nx,Ny): cpp/Spherical.cpp:96-102 (chi known by construction)
-__device__ __forceinline__ double mesh_fetch(const MeshView& v, int Nx, int Ny) {
-    if ((Ny >= v.ny_cut) && (Nx >= v.nx_cut)) return 0.0;
-    const double b = lattice_coord(Ny, v.db);
-    const double c = (Ny == 0) ? v.cospi : v.tab[(long long) Nx * v.ny + Ny];
-    double cl = c;
-    for (int i = 1; i < v.l; i++) cl *= c;
-    return __dmul_rn(__dmul_rn(v.gfac[Nx], __dsub_rn(1.0, cl)), b);
+// cos(chi) at lattice node (Nx,Ny) (known by construction); cut-off nodes return NaN as the "integrand is 0" marker
+__device__ __forceinline__ double mesh_cos(const MeshView& v, int Nx, int Ny) {
+    if ((Ny >= v.ny_cut) && (Nx >= v.nx_cut)) return __longlong_as_double(0x7ff8000000000000LL);
+    return (Ny == 0) ? v.cospi : v.tab[(long long) Nx * v.ny + Ny];
 }
 
-__device__ __forceinline__ MeshView make_view(const Item& item, const Regime& rg, const double* tab_pool, unsigned* want_pool,
-                                              const double* gfac_pool, int nr_distinct, int gfac_stride, int ri, int l, double cospi) {
+// integrand value, cpp/Spherical.cpp:96-102: gf = 2 exp(-g^2) g^(2r+3), c = cos(chi), b = impact parameter / sigma
+__device__ __forceinline__ double mesh_f(double gf, double c, double b, int l) {
+    if (c != c) return 0.0;
+    double cl = c;
+    for (int i = 1; i < l; i++) cl *= c;
+    return __dmul_rn(__dmul_rn(gf, __dsub_rn(1.0, cl)), b);
+}
+
+__device__ __forceinline__ MeshView make_view(const Item& item, const Regime& rg, const double* tab_pool, unsigned* want_pool, double cospi) {
     MeshView v;
-    v.tab = tab_pool + item.tab_off;
+    v.tab = tab_pool ? tab_pool + item.tab_off : nullptr;
     v.want = want_pool + item.mask_off;
-    v.gfac = gfac_pool + ((long long) item.regime * nr_distinct + ri) * gfac_stride;
-    v.ny = rg.ny; v.nwords = rg.nwords; v.l = l;
+    v.ny = rg.ny; v.nwords = rg.nwords;
     v.nx_cut = rg.nx_cut; v.ny_cut = rg.ny_cut; v.ldg = rg.ldg; v.ldb = rg.ldb;
-    v.dg = rg.dg; v.db = rg.db; v.lim = rg.lim; v.cospi = cospi;
+    v.db = rg.db; v.lim = rg.lim; v.cospi = cospi;
     return v;
 }
 
-// level 0: the coarse cells of every active (item,(l,r)) owner in the reference's sweep order (Integration.cpp:240-280:
-// row k runs +x for even k, -x for odd k) and the lattice nodes they read. grid.x = number of active owners.
+// level 0: the coarse cells of every active item in the reference's sweep order (Integration.cpp:240-280: row k runs +x
+// for even k, -x for odd k), owned by all requested (l,r) of the item, and the lattice nodes they read. grid.x = active items.
 __global__ void __launch_bounds__(128) mesh_init_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
-                                                        unsigned* __restrict__ want_pool, int nlr, const int* __restrict__ owners,
-                                                        const long long* __restrict__ owner_cell_off, Cell* __restrict__ cells) {
-    const int owner = owners[blockIdx.x];
-    const int it = owner / nlr;
+                                                        unsigned* __restrict__ want_pool, const int* __restrict__ active,
+                                                        const unsigned long long* __restrict__ active_mask,
+                                                        const long long* __restrict__ active_cell_off, Cell* __restrict__ cells) {
+    const int it = active[blockIdx.x];
     const Item item = items[it];
     const Regime rg = regimes[item.regime];
-    MeshView v = make_view(item, rg, nullptr, want_pool, nullptr, 0, 0, 0, 1, 0.0);
+    MeshView v = make_view(item, rg, nullptr, want_pool, 0.0);
     const int ncx = rg.Nx_end / rg.rlg, ncy = rg.Ny_end / rg.rlb, nc = ncx * ncy;
-    const long long c0 = owner_cell_off[blockIdx.x];
+    const long long c0 = active_cell_off[blockIdx.x];
+    const unsigned long long mask = active_mask[blockIdx.x];
     for (int cell = threadIdx.x; cell < nc; cell += blockDim.x) {
         const int row = cell / ncx, col = cell % ncx;
         const int d = (row & 1) ? -1 : 1;
         const int ex = ((row & 1) ? rg.Nx_end : 0) + col * d * rg.rlg, ey = row * rg.rlb;
-        cells[c0 + cell] = pack_cell((unsigned) owner, ex, ey, d * rg.rlg, rg.rlb);
-        mesh_mark_cell(v, ex, ey, d * rg.rlg, rg.rlb);       // idempotent across the owners of one item
+        cells[c0 + cell] = Cell{pack_cell((unsigned) it, ex, ey, d * rg.rlg, rg.rlb), mask};
+        mesh_mark_cell(v, ex, ey, d * rg.rlg, rg.rlb);
     }
 }
 
-// One level of the refinement tree: every cell of cells_in is either integrated (leaf) or split into the sub-domain sweep
-// of integrate_adaptive (Integration.cpp:172-202) whose cells go to cells_out with their nodes marked.
-__global__ void __launch_bounds__(256, 4) mesh_level_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
+// children of one split class: the sub-domain sweep of integrate_adaptive (Integration.cpp:172-202) over the parent cell,
+// origin (Nx,Ny), far corner (Nx+sx, Ny+sy); row k runs in direction sgn for even k, -sgn for odd k
+__device__ __forceinline__ int mesh_emit(const MeshView& v, Cell* __restrict__ out, int o, unsigned item, unsigned long long members,
+                                         int Nx, int Ny, int sx, int sy, int sub_sx, int sub_sy) {
+    const int ax = abs(sx), asx = abs(sub_sx), ncols = ax / asx, nrows = sy / sub_sy, sgn = (sx > 0) ? 1 : -1;
+    for (int k = 0; k < nrows; k++) {
+        const int d = (k & 1) ? -sgn : sgn;
+        const int xs = (k & 1) ? Nx + sx : Nx;
+        for (int j = 0; j < ncols; j++) {
+            const int cxn = xs + j * d * asx, cyn = Ny + k * sub_sy;
+            out[o++] = Cell{pack_cell(item, cxn, cyn, d * asx, sub_sy), members};
+            mesh_mark_cell(v, cxn, cyn, d * asx, sub_sy);
+        }
+    }
+    return o;
+}
+
+// One level of the refinement trees: every member (l,r) of a cell either integrates it (leaf) or splits it; members that
+// split the same way share the child cells, which go to cells_out with their nodes marked.
+__global__ void __launch_bounds__(256) mesh_level_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
                                                          const double* __restrict__ tab_pool, unsigned* __restrict__ want_pool,
                                                          const double* __restrict__ gfac_pool, const int* __restrict__ lr_l,
                                                          const int* __restrict__ lr_r_index, int nr_distinct, int gfac_stride, double cospi,
                                                          int nlr, const Cell* __restrict__ cells_in, int n_in, Cell* __restrict__ cells_out,
                                                          int* __restrict__ n_out, int cap_out, double* __restrict__ W, int* __restrict__ flags) {
+    const unsigned full = 0xffffffffu;
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     const bool active = e < n_in;
-    const Cell c = active ? cells_in[e] : 0;
-    const unsigned owner = (unsigned) (c & 0x3FFFFFFu);
-    const int Nx = (int) ((c >> 26) & 0xFF), Ny = (int) ((c >> 34) & 0x3FF);
-    const int lx = (int) ((c >> 44) & 7), ly = (int) ((c >> 48) & 7);
+    Cell c = Cell{0ull, 0ull};
+    if (active) c = cells_in[e];
+    const unsigned item_id = (unsigned) (c.lo & 0x3FFFFFu);
+    const int Nx = (int) ((c.lo >> 22) & 0xFF), Ny = (int) ((c.lo >> 30) & 0x3FF);
+    const int lx = (int) ((c.lo >> 40) & 7), ly = (int) ((c.lo >> 44) & 7);
     const int ax = 1 << lx, sy = 1 << ly;
-    const int sx = ((c >> 47) & 1) ? -ax : ax;
-    double contrib = 0.0;
-    int nchild = 0, sub_sx = sx, sub_sy = sy;
-    MeshView v;
+    const int sx = ((c.lo >> 43) & 1) ? -ax : ax;
+    MeshView v = {};
+    double c0 = 0, c1x = 0, c2x = 0, c1y = 0, c2y = 0, c11 = 0, c22 = 0, cXb = 0, cXt = 0, b0 = 0, b1 = 0, b2 = 0;
+    int regime = 0;
     if (active) {
-        const int it = owner / nlr, lr = owner % nlr;
-        const Item item = items[it];
+        const Item item = items[item_id];
         const Regime rg = regimes[item.regime];
-        v = make_view(item, rg, tab_pool, want_pool, gfac_pool, nr_distinct, gfac_stride, lr_r_index[lr], lr_l[lr], cospi);
-        const double f = mesh_fetch(v, Nx, Ny), f1x = mesh_fetch(v, Nx + ax, Ny), f2x = mesh_fetch(v, Nx + 2 * ax, Ny);
-        const double f1y = mesh_fetch(v, Nx, Ny + sy), f2y = mesh_fetch(v, Nx, Ny + 2 * sy);
-        const double f1x1y = mesh_fetch(v, Nx + ax, Ny + sy), f2x2y = mesh_fetch(v, Nx + 2 * ax, Ny + 2 * sy);
-        // second-difference estimator in the reference's operation order, no FMA contraction (decision predicate).
-        // hx, hy are powers of two, so the reference's divisions are exact scalings and are done as multiplications.
-        const int ehx = v.ldg + lx, ehy = v.ldb + ly;
-        const double hx = pow2(ehx), hy = pow2(ehy);
-        const double hx2 = pow2(2 * ehx), hy2 = pow2(2 * ehy);
-        const double fxx = __dmul_rn(__dadd_rn(__dsub_rn(f, __dmul_rn(2.0, f1x)), f2x), pow2(-2 * ehx));
-        const double fyy = __dmul_rn(__dadd_rn(__dsub_rn(f, __dmul_rn(2.0, f1y)), f2y), pow2(-2 * ehy));
-        double t = __dadd_rn(__dsub_rn(f2x2y, __dmul_rn(2.0, f1x1y)), f);
-        t = __dsub_rn(t, __dmul_rn(hx2, fxx));
-        t = __dsub_rn(t, __dmul_rn(hy2, fyy));
-        const double fxy = __dmul_rn(t, pow2(-(1 + ehx + ehy)));
-        const double dblder = __dadd_rn(__dadd_rn(fabs(fxx), fabs(fyy)), fabs(fxy));
-        const double hs = __dadd_rn(hx, hy);
-        const double hs3 = __dmul_rn(__dmul_rn(hs, hs), hs);
-        if ((__dmul_rn(dblder, hs3) > v.lim) && ((ax > 1) || (sy > 1))) {
-            const double cx = __dmul_rn(fabs(fxx), __dmul_rn(hx2, hx));
-            const double cy = __dmul_rn(fabs(fyy), __dmul_rn(hy2, hy));
-            if (cx > v.lim && (cy < v.lim) && (fabs(fxy) < v.lim) && (ax > 1)) sub_sx = sx / 2;
-            else if (cy > v.lim && (cx < v.lim) && (fabs(fxy) < v.lim) && (sy > 1)) sub_sy = sy / 2;
-            else {
-                if (ax > 1) sub_sx = sx / 2;
-                if (sy > 1) sub_sy = sy / 2;
+        regime = item.regime;
+        v = make_view(item, rg, tab_pool, want_pool, cospi);
+        c0 = mesh_cos(v, Nx, Ny); c1x = mesh_cos(v, Nx + ax, Ny); c2x = mesh_cos(v, Nx + 2 * ax, Ny);
+        c1y = mesh_cos(v, Nx, Ny + sy); c2y = mesh_cos(v, Nx, Ny + 2 * sy);
+        c11 = mesh_cos(v, Nx + ax, Ny + sy); c22 = mesh_cos(v, Nx + 2 * ax, Ny + 2 * sy);
+        if (sx < 0) { cXb = mesh_cos(v, Nx + sx, Ny); cXt = mesh_cos(v, Nx + sx, Ny + sy); }
+        b0 = lattice_coord(Ny, v.db); b1 = lattice_coord(Ny + sy, v.db); b2 = lattice_coord(Ny + 2 * sy, v.db);
+    }
+    // hx, hy are powers of two, so the reference's divisions are exact scalings and are done as multiplications
+    const int ehx = v.ldg + lx, ehy = v.ldb + ly;
+    const double hx = pow2(ehx), hy = pow2(ehy), hx2 = pow2(2 * ehx), hy2 = pow2(2 * ehy);
+    const double ihx2 = pow2(-2 * ehx), ihy2 = pow2(-2 * ehy), ihxy = pow2(-(1 + ehx + ehy));
+    const double hs = __dadd_rn(hx, hy);
+    const double hs3 = __dmul_rn(__dmul_rn(hs, hs), hs);
+    const double hx3 = __dmul_rn(hx2, hx), hy3 = __dmul_rn(hy2, hy);
+    const bool can_x = ax > 1, can_y = sy > 1;
+    const unsigned item0 = __shfl_sync(full, item_id, 0);
+    const bool uniform = __all_sync(full, !active || item_id == item0);
+    unsigned long long mx = 0, my = 0, mb = 0;
+    const unsigned um_lo = __reduce_or_sync(full, (unsigned) c.hi), um_hi = __reduce_or_sync(full, (unsigned) (c.hi >> 32));
+    unsigned long long um = ((unsigned long long) um_hi << 32) | um_lo;
+    while (um) {
+        const int lr = __ffsll((long long) um) - 1;
+        um &= um - 1;
+        double contrib = 0.0;
+        if (active && ((c.hi >> lr) & 1ull)) {
+            const int l = lr_l[lr];
+            const double* gf = gfac_pool + ((long long) regime * nr_distinct + lr_r_index[lr]) * gfac_stride;
+            const double g0 = gf[Nx], g1 = gf[Nx + ax], g2 = gf[Nx + 2 * ax];
+            const double f = mesh_f(g0, c0, b0, l), f1x = mesh_f(g1, c1x, b0, l), f2x = mesh_f(g2, c2x, b0, l);
+            const double f1y = mesh_f(g0, c1y, b1, l), f2y = mesh_f(g0, c2y, b2, l);
+            const double f1x1y = mesh_f(g1, c11, b1, l), f2x2y = mesh_f(g2, c22, b2, l);
+            // second-difference estimator in the reference's operation order, no FMA contraction (decision predicate)
+            const double fxx = __dmul_rn(__dadd_rn(__dsub_rn(f, __dmul_rn(2.0, f1x)), f2x), ihx2);
+            const double fyy = __dmul_rn(__dadd_rn(__dsub_rn(f, __dmul_rn(2.0, f1y)), f2y), ihy2);
+            double t = __dadd_rn(__dsub_rn(f2x2y, __dmul_rn(2.0, f1x1y)), f);
+            t = __dsub_rn(t, __dmul_rn(hx2, fxx));
+            t = __dsub_rn(t, __dmul_rn(hy2, fyy));
+            const double fxy = __dmul_rn(t, ihxy);
+            const double dblder = __dadd_rn(__dadd_rn(fabs(fxx), fabs(fyy)), fabs(fxy));
+            if ((__dmul_rn(dblder, hs3) > v.lim) && (can_x || can_y)) {
+                const double cx = __dmul_rn(fabs(fxx), hx3);
+                const double cy = __dmul_rn(fabs(fyy), hy3);
+                const unsigned long long bit = 1ull << lr;
+                if (cx > v.lim && (cy < v.lim) && (fabs(fxy) < v.lim) && can_x) mx |= bit;
+                else if (cy > v.lim && (cx < v.lim) && (fabs(fxy) < v.lim) && can_y) my |= bit;
+                else if (can_x && can_y) mb |= bit;
+                else if (can_x) mx |= bit;
+                else my |= bit;
             }
-            nchild = (ax / abs(sub_sx)) * (sy / sub_sy);
+            else {
+                // leaf: the two triangles the sweep adds for this cell, (Eb,Et,Xb) and (Et,Xb,Xt) (Integration.cpp:218-234);
+                // a linear interpolant integrates to area * mean of its corner values
+                double fXb = f1x, fXt = f1x1y;
+                if (sx < 0) { const double gm = gf[Nx + sx]; fXb = mesh_f(gm, cXb, b0, l); fXt = mesh_f(gm, cXt, b1, l); }
+                contrib = (hx * hy / 6.0) * (f + 2.0 * f1y + 2.0 * fXb + fXt);
+            }
         }
-        else {
-            // leaf: the two triangles the sweep adds for this cell, (Eb,Et,Xb) and (Et,Xb,Xt) (Integration.cpp:218-234);
-            // a linear interpolant integrates to area * mean of its corner values
-            double fXb, fXt;
-            if (sx > 0) { fXb = f1x; fXt = f1x1y; }
-            else { fXb = mesh_fetch(v, Nx + sx, Ny); fXt = mesh_fetch(v, Nx + sx, Ny + sy); }
-            contrib = (hx * hy / 6.0) * (f + 2.0 * f1y + 2.0 * fXb + fXt);
+        // leaf sums: one atomic per warp when the warp belongs to one item, else one per lane
+        if (uniform) {
+            double sum = contrib;
+            for (int off = 16; off > 0; off >>= 1) sum += __shfl_down_sync(full, sum, off);
+            if ((threadIdx.x & 31) == 0 && sum != 0.0) atomicAdd(&W[(size_t) item0 * nlr + lr], sum);
         }
+        else if (contrib != 0.0) atomicAdd(&W[(size_t) item_id * nlr + lr], contrib);
     }
-    // leaf sums: one atomic per warp when the warp belongs to one (item,(l,r)), else one per lane
-    const unsigned full = 0xffffffffu;
-    const unsigned key = active ? owner : 0xffffffffu;
-    const bool uniform = __all_sync(full, key == __shfl_sync(full, key, 0));
-    if (uniform) {
-        double sum = contrib;
-        for (int off = 16; off > 0; off >>= 1) sum += __shfl_down_sync(full, sum, off);
-        if ((threadIdx.x & 31) == 0 && active && sum != 0.0) atomicAdd(&W[owner], sum);
-    }
-    else if (contrib != 0.0) atomicAdd(&W[owner], contrib);
     // children: warp-aggregated allocation in cells_out
+    const int nchild = (mx ? 2 : 0) + (my ? 2 : 0) + (mb ? 4 : 0);
     int pre = nchild;
     for (int off = 1; off < 32; off <<= 1) { const int nb = __shfl_up_sync(full, pre, off); if ((threadIdx.x & 31) >= off) pre += nb; }
     const int warp_total = __shfl_sync(full, pre, 31);
@@ -233,17 +274,9 @@ __global__ void __launch_bounds__(256, 4) mesh_level_kernel(const Item* __restri
     if (nchild > 0) {
         int o = base + pre - nchild;
         if (o + nchild > cap_out) { flags[1] = 1; return; }
-        // sub-domain sweep: origin (Nx,Ny), far corner (Nx+sx, Ny+sy); row k runs in direction sgn for even k, -sgn for odd k
-        const int asx = abs(sub_sx), ncols = ax / asx, nrows = sy / sub_sy, sgn = (sx > 0) ? 1 : -1;
-        for (int k = 0; k < nrows; k++) {
-            const int d = (k & 1) ? -sgn : sgn;
-            const int xs = (k & 1) ? Nx + sx : Nx;
-            for (int j = 0; j < ncols; j++) {
-                const int cxn = xs + j * d * asx, cyn = Ny + k * sub_sy;
-                cells_out[o++] = pack_cell(owner, cxn, cyn, d * asx, sub_sy);
-                mesh_mark_cell(v, cxn, cyn, d * asx, sub_sy);
-            }
-        }
+        if (mx) o = mesh_emit(v, cells_out, o, item_id, mx, Nx, Ny, sx, sy, sx / 2, sy);
+        if (my) o = mesh_emit(v, cells_out, o, item_id, my, Nx, Ny, sx, sy, sx, sy / 2);
+        if (mb) o = mesh_emit(v, cells_out, o, item_id, mb, Nx, Ny, sx, sy, sx / 2, sy / 2);
     }
 }
 
@@ -613,11 +646,12 @@ struct kg_omega_plan {
     double* d_gfac = nullptr; int *d_lr_l = nullptr, *d_lr_ri = nullptr;
     double* d_coeff = nullptr;
     double *d_W = nullptr, *d_omega = nullptr;          // [item][lr] in plan order
-    Cell* d_cells[2] = {nullptr, nullptr}; int* d_ncells = nullptr; long long cell_cap = 0, ncells0 = 0;
+    Cell* d_cells[2] = {nullptr, nullptr}; int* d_ncells = nullptr; long long cell_cap = 0, ncells0 = 0, cell_cap_limit = 0;
     double *d_W_out = nullptr, *d_omega_out = nullptr;  // [nT][npairs][nlr]
     int *d_status = nullptr, *d_flags = nullptr, *d_tile_counter = nullptr;
     int* d_perm = nullptr;                              // item -> output slot
-    int* d_owners = nullptr; long long* d_owner_cell_off = nullptr; int nowners = 0;   // active (item,(l,r)) owners
+    int* d_active = nullptr; unsigned long long* d_active_mask = nullptr; long long* d_active_cell_off = nullptr; int nactive = 0;   // items with work, their (l,r) sets
+    int max_cells_seen = 0, regrows = 0;
     int* d_pair_task_start = nullptr;                   // [npairs+1] first column task of each pair
     unsigned long long* d_counters = nullptr;
     long long tab_doubles = 0, mask_words = 0, ncols_total = 0;
@@ -662,7 +696,7 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
     // items sorted by pair (theta tiles keep one pair's node rows in shared memory), then by T index
     p->items.reserve(p->nitems);
     std::vector<int> perm; perm.reserve(p->nitems);
-    std::vector<int> owners; std::vector<long long> owner_cell_off;     // active (item,(l,r)) and their level-0 cell offsets
+    std::vector<int> active; std::vector<unsigned long long> active_mask; std::vector<long long> active_cell_off;   // items with work, their (l,r) sets, level-0 cell offsets
     std::vector<char> item_active;
     const double PI = 3.14159265359, KB = 1.38064852e-23;
     int pi = 0;
@@ -679,19 +713,24 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
             const Regime& rg = regs[it.regime];
             const int item_index = (int) p->items.size();
             int nact = 0;
+            unsigned long long members = 0;
             for (int k = 0; k < nlr; k++) {
                 if (need && !need[((size_t) t * Np + pi) * nlr + k]) continue;
-                owners.push_back(item_index * nlr + k);
-                owner_cell_off.push_back(p->ncells0);
-                p->ncells0 += (long long) (rg.Nx_end / rg.rlg) * (rg.Ny_end / rg.rlb);
+                members |= 1ull << k;
                 nact++;
             }
             item_active.push_back(nact > 0);
             if (nact > 0) {      // items with nothing to integrate own no lattice, no columns, no cells
+                active.push_back(item_index); active_mask.push_back(members); active_cell_off.push_back(p->ncells0);
+                p->ncells0 += (long long) (rg.Nx_end / rg.rlg) * (rg.Ny_end / rg.rlb);
                 it.tab_off = p->tab_doubles; p->tab_doubles += (long long) rg.nx * rg.ny;
                 it.mask_off = p->mask_words; p->mask_words += (long long) rg.nx * rg.nwords;
                 it.col_off = p->ncols_total; p->ncols_total += rg.nx;
-                p->cell_cap += (long long) nact * rg.Nx_end * rg.Ny_end;     // cells of one level tile (part of) the domain
+                // cells of one level: the members of an item mostly share their cells, so one tiling of the domain at the
+                // finest step is the working estimate; the hard bound is one tiling per member (kg_omega_plan_run grows the
+                // lists on overflow)
+                p->cell_cap += (long long) rg.Nx_end * rg.Ny_end * 5 / 4 + 64;
+                p->cell_cap_limit += (long long) nact * rg.Nx_end * rg.Ny_end + 64;
             }
             it.coeff_off = coeff_T ? (t * Np + pi) * KG_MAX_TERMS : -1;
             p->items.push_back(it);
@@ -704,7 +743,7 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
         const Regime& rg = regs[p->items[it].regime];
         for (int nx = 0; nx < rg.nx; nx++) tasks.push_back(make_int2(it, nx));
     }
-    p->nowners = (int) owners.size();
+    p->nactive = (int) active.size();
     p->ntasks = (int) tasks.size();
     std::vector<int> pair_task_start(Np + 1, p->ntasks);
     for (int t = p->ntasks - 1; t >= 0; t--) pair_task_start[p->items[tasks[t].x].pair] = t;
@@ -753,7 +792,8 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
     PLAN_CUDA(cudaMalloc(&p->d_gfac, gfac.size() * sizeof(double)));
     PLAN_CUDA(cudaMalloc(&p->d_lr_l, nlr * sizeof(int)));
     PLAN_CUDA(cudaMalloc(&p->d_lr_ri, nlr * sizeof(int)));
-    if ((long long) p->nitems * nlr >= (1LL << 26) || p->cell_cap >= (1LL << 31)) { set_error("kg_omega_plan_create: batch too large, split the T grid"); kg_omega_plan_destroy(p); return -1; }
+    p->cell_cap = std::max(p->cell_cap, p->ncells0);
+    if (p->nitems >= (1 << 22) || nlr > 64 || p->cell_cap >= (1LL << 31)) { set_error("kg_omega_plan_create: batch too large, split the T grid"); kg_omega_plan_destroy(p); return -1; }
     PLAN_CUDA(cudaMalloc(&p->d_cells[0], p->cell_cap * sizeof(Cell)));
     PLAN_CUDA(cudaMalloc(&p->d_cells[1], p->cell_cap * sizeof(Cell)));
     PLAN_CUDA(cudaMalloc(&p->d_ncells, 2 * sizeof(int)));
@@ -767,10 +807,12 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
     PLAN_CUDA(cudaMalloc(&p->d_pair_task_start, (Np + 1) * sizeof(int)));
     PLAN_CUDA(cudaMemcpy(p->d_pair_task_start, pair_task_start.data(), (Np + 1) * sizeof(int), cudaMemcpyHostToDevice));
     PLAN_CUDA(cudaMalloc(&p->d_perm, p->nitems * sizeof(int)));
-    PLAN_CUDA(cudaMalloc(&p->d_owners, (owners.size() + 1) * sizeof(int)));
-    PLAN_CUDA(cudaMalloc(&p->d_owner_cell_off, (owners.size() + 1) * sizeof(long long)));
-    PLAN_CUDA(cudaMemcpy(p->d_owners, owners.data(), owners.size() * sizeof(int), cudaMemcpyHostToDevice));
-    PLAN_CUDA(cudaMemcpy(p->d_owner_cell_off, owner_cell_off.data(), owners.size() * sizeof(long long), cudaMemcpyHostToDevice));
+    PLAN_CUDA(cudaMalloc(&p->d_active, (active.size() + 1) * sizeof(int)));
+    PLAN_CUDA(cudaMalloc(&p->d_active_mask, (active.size() + 1) * sizeof(unsigned long long)));
+    PLAN_CUDA(cudaMalloc(&p->d_active_cell_off, (active.size() + 1) * sizeof(long long)));
+    PLAN_CUDA(cudaMemcpy(p->d_active, active.data(), active.size() * sizeof(int), cudaMemcpyHostToDevice));
+    PLAN_CUDA(cudaMemcpy(p->d_active_mask, active_mask.data(), active.size() * sizeof(unsigned long long), cudaMemcpyHostToDevice));
+    PLAN_CUDA(cudaMemcpy(p->d_active_cell_off, active_cell_off.data(), active.size() * sizeof(long long), cudaMemcpyHostToDevice));
     PLAN_CUDA(cudaMalloc(&p->d_counters, 8 * sizeof(unsigned long long)));
     PLAN_CUDA(cudaMallocHost(&p->h_pinned, 8 * sizeof(int)));
     if (coeff_T) {
@@ -798,7 +840,7 @@ extern "C" void kg_omega_plan_destroy(kg_omega_plan* p) {
     void* ptrs[] = {p->d_items, p->d_regimes, p->d_tab, p->d_want, p->d_known, p->d_lim, p->d_have_lim, p->d_tasks, p->d_counts,
                     p->d_offsets, p->d_list, p->d_gfac, p->d_lr_l, p->d_lr_ri, p->d_coeff, p->d_W, p->d_omega, p->d_W_out,
                     p->d_omega_out, p->d_status, p->d_flags, p->d_tile_counter, p->d_perm, p->d_counters, p->d_cells[0], p->d_cells[1], p->d_ncells, p->d_pair_task_start,
-                    p->d_owners, p->d_owner_cell_off};
+                    p->d_active, p->d_active_mask, p->d_active_cell_off};
     for (void* q : ptrs) if (q) cudaFree(q);
     if (p->h_pinned) cudaFreeHost(p->h_pinned);
     for (int k = 0; k < 4; k++) if (p->ev[k]) cudaEventDestroy(p->ev[k]);
@@ -823,8 +865,8 @@ extern "C" int kg_omega_plan_run(kg_omega_plan* p) {
     const size_t smem = (size_t) KS_ROWS * W * sizeof(double);
     const int tgrid = std::max(1, (p->ntasks + 255) / 256);
     CUDA_OK(cudaEventRecord(p->ev[0], s));
-    if (p->nowners > 0)
-        mesh_init_kernel<<<p->nowners, 128, 0, s>>>(p->d_items, p->d_regimes, p->d_want, p->nlr, p->d_owners, p->d_owner_cell_off, p->d_cells[0]);
+    if (p->nactive > 0)
+        mesh_init_kernel<<<p->nactive, 128, 0, s>>>(p->d_items, p->d_regimes, p->d_want, p->d_active, p->d_active_mask, p->d_active_cell_off, p->d_cells[0]);
     CUDA_OK(cudaEventRecord(p->ev[1], s));
     p->launches += 1;
     long long n_in = p->ncells0;
@@ -869,7 +911,18 @@ extern "C" int kg_omega_plan_run(kg_omega_plan* p) {
         CUDA_OK(cudaStreamSynchronize(s));
         if (nlist > 0) { cudaEventElapsedTime(&ms, p->ev[2], p->ev[3]); p->ms_theta += ms; }
         p->launches += 1;
-        if (p->h_pinned[1]) { set_error("kg_omega_plan_run: cell list overflow"); return -3; }
+        if (p->h_pinned[1]) {
+            // the working estimate of the cell lists was too small: grow them and start over (results are rebuilt from scratch)
+            if (p->cell_cap >= p->cell_cap_limit) { set_error("kg_omega_plan_run: cell list overflow"); return -3; }
+            const long long grown = std::min(p->cell_cap_limit, 2 * p->cell_cap);
+            if (grown >= (1LL << 31)) { set_error("kg_omega_plan_run: batch too large, split the T grid"); return -3; }
+            cudaFree(p->d_cells[0]); cudaFree(p->d_cells[1]); p->d_cells[0] = p->d_cells[1] = nullptr;
+            CUDA_OK(cudaMalloc(&p->d_cells[0], grown * sizeof(Cell)));
+            CUDA_OK(cudaMalloc(&p->d_cells[1], grown * sizeof(Cell)));
+            p->cell_cap = grown; p->regrows++;
+            return kg_omega_plan_run(p);
+        }
+        p->max_cells_seen = std::max(p->max_cells_seen, p->h_pinned[2]);
         n_in = p->h_pinned[2];
         cur ^= 1;
     }
@@ -919,15 +972,16 @@ extern "C" int kg_omega_plan_export_dev(kg_omega_plan* p, double* omega_dev, dou
     return 0;
 }
 
-extern "C" int kg_omega_plan_counters(kg_omega_plan* p, double* out9) {
-    if (!p || !out9) return -1;
+extern "C" int kg_omega_plan_counters(kg_omega_plan* p, double* out16) {
+    if (!p || !out16) return -1;
     auto set_error = [&](const std::string& s) { p->m->err = s; };
     unsigned long long c[8];
     CUDA_OK(cudaMemcpy(c, p->d_counters, sizeof(c), cudaMemcpyDeviceToHost));
-    out9[0] = (double) c[0]; out9[1] = (double) c[1]; out9[2] = (double) c[2]; out9[3] = (double) c[3];
-    out9[4] = p->ms_theta; out9[5] = 0.0; out9[6] = p->ms_mesh; out9[7] = p->launches; out9[8] = p->passes;
-    out9[9] = (double) p->h2d_bytes; out9[10] = (double) p->d2h_bytes;
-    out9[11] = (double) (p->tab_doubles * 8 + p->mask_words * 8);
+    out16[0] = (double) c[0]; out16[1] = (double) c[1]; out16[2] = (double) c[2]; out16[3] = (double) c[3];
+    out16[4] = p->ms_theta; out16[5] = 0.0; out16[6] = p->ms_mesh; out16[7] = p->launches; out16[8] = p->passes;
+    out16[9] = (double) p->h2d_bytes; out16[10] = (double) p->d2h_bytes;
+    out16[11] = (double) (p->tab_doubles * 8 + p->mask_words * 8);
+    out16[5] = 0.0; out16[12] = (double) p->max_cells_seen; out16[13] = (double) p->cell_cap; out16[14] = (double) p->cell_cap_limit; out16[15] = (double) p->regrows;
     return 0;
 }
 

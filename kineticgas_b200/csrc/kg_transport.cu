@@ -16,6 +16,7 @@
 // conductivity matrix (cpp/KineticGas.cpp:334-388), so Lambda is factorised once and solved for nc + 1 right-hand sides.
 #include "kg_internal.cuh"
 #include <cmath>
+#include <cfloat>
 #include <cstring>
 #include <map>
 #include <algorithm>
@@ -374,8 +375,10 @@ struct StateArgs {
 
 // Unblocked partial-pivot LU, the algorithm Eigen's partialPivLu runs for sizes <= 16 (row-max pivot, first maximum wins,
 // column scaled by division, rank-1 update with separately rounded multiply and subtract). A is n x n row-major, stride ld.
-__device__ int lu_factor(double* A, int n, int ld, int* piv) {
+__device__ int lu_factor(double* A, int n, int ld, int* piv, double zero_pivot_rel = 0.0) {
     int singular = 0;
+    double scale = 0.0;
+    if (zero_pivot_rel > 0.0) for (int i = 0; i < n; i++) for (int j = 0; j < n; j++) scale = fmax(scale, fabs(A[i * ld + j]));
     for (int k = 0; k < n; k++) {
         int pr = k; double best = fabs(A[k * ld + k]);
         for (int i = k + 1; i < n; i++) { const double v = fabs(A[i * ld + k]); if (v > best) { best = v; pr = i; } }
@@ -385,6 +388,7 @@ __device__ int lu_factor(double* A, int n, int ld, int* piv) {
             const double d = A[k * ld + k];
             for (int i = k + 1; i < n; i++) A[i * ld + k] /= d;
         }
+        else if (zero_pivot_rel > 0.0) A[k * ld + k] = zero_pivot_rel * scale;
         else singular = 1;
         for (int i = k + 1; i < n; i++) {
             const double lik = A[i * ld + k];
@@ -625,7 +629,11 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
                 double dm[MAXC * MAXC]; int pv[MAXC];
                 const double d000 = dsol[0];
                 for (int i = 0; i < nc; i++) { for (int j = 0; j < nc; j++) dm[i * MAXC + j] = dsol[j * MAXN + i] / d000; dth[i] = th[i] / d000; }
-                if (lu_factor(dm, nc, MAXC, pv)) st |= KG_STATUS_SINGULAR;
+                // d[0] has rank nc - 1 (the diffusive expansion coefficients of the nc driving forces are linearly dependent), so
+                // the reference's partialPivLu ends on a pivot that is pure rounding noise and lambda' does not depend on it
+                // (d[1] annihilates the null vector). When that noise happens to be exactly 0.0 the reference would return NaN;
+                // here the pivot is replaced by one ulp of the matrix scale, which is what it is in every other case.
+                lu_factor(dm, nc, MAXC, pv, DBL_EPSILON);
                 lu_solve(dm, nc, MAXC, pv, dth);
             }
             double lam_t = 0.;
@@ -841,7 +849,7 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
         if (!rc) rc = kg_omega_plan_export_dev(plan, c->d_omega, nullptr);
         std::vector<int32_t> pst((size_t) nT * Np, 0);
         if (!rc) rc = kg_omega_plan_fetch(plan, nullptr, nullptr, pst.data());
-        if (!rc) { double cnt[12]; if (!kg_omega_plan_counters(plan, cnt)) m->timings[4] += cnt[7]; }
+        if (!rc) { double cnt[16]; if (!kg_omega_plan_counters(plan, cnt)) m->timings[4] += cnt[7]; }
         if (plan) kg_omega_plan_destroy(plan);
         if (rc) { kg_tcache_destroy(c); return rc; }
         int bad = 0; for (int v : pst) bad |= v;

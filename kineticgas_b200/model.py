@@ -152,10 +152,10 @@ class OmegaPlan:
                         "kg_omega_plan_export_dev")
 
     def counters(self):
-        out = np.zeros(12)
+        out = np.zeros(16)
         self.model._chk(self.model.L.kg_omega_plan_counters(self.h, _p(out)), "kg_omega_plan_counters")
         keys = ["chi_evals", "chi_nodes", "lim_evals", "lim_nodes", "ms_theta", "ms_lim", "ms_mesh", "launches", "passes",
-                "h2d_bytes", "d2h_bytes", "pool_bytes"]
+                "h2d_bytes", "d2h_bytes", "pool_bytes", "max_cells_per_level", "cell_capacity", "cell_capacity_limit", "cell_regrows"]
         return dict(zip(keys, out.tolist()))
 
     def close(self):
