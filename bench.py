@@ -25,7 +25,8 @@ sys.path.insert(0, ROOT)
 
 NT_PER_GPU = 4096
 LR = [(l, r) for l in range(1, 5) for r in range(l, 5)]
-FP64_INSTR_PER_NODE = 11.0   # ts_term + stop rule for a 2-term potential: 6 DFMA + 3 DMUL + 1 DFMA (running sum) + 1 DSETP (kg_device.cuh)
+FP64_INSTR_PER_NODE = 7.125  # fast node of a 2-term potential: 3 DFMA (radicand) + DMUL, DFMA (Newton step) + DMUL (weight) + DFMA (running sum),
+                             # plus one DMUL per 8-node block for the stop check (kg_device.cuh ts_fast / theta_integral)
 F_NODE = 98.0    # nominal FP64 flop per tanh-sinh node for a 2-term (Mie/LJ) potential, SURVEY.md 8(d): 52 + 23 n_terms
 METRIC = "collision integrals/s"
 
@@ -196,6 +197,79 @@ def run_state_points(local_rank, rank, world, n_gpus, steps):
     return out
 
 
+# ------------------------------------------------------------------------------------------------ Feynman-Hibbs sweep (configs[3])
+QM_NT = 10000
+QM_LR = [(1, 1), (1, 2), (1, 3), (2, 2), (2, 3), (2, 4), (3, 3)]     # N = 2 viscosity + conductivity (cpp/KineticGas_mthr.cpp:62-125)
+QM_F_NODE = 144.0                                                    # 52 + 23 * 4 terms (FH1-Mie)
+
+
+def run_qmie_sweep(local_rank, rank, n_gpus, steps):
+    """configs[3]: QuantumMie('HE', FH1) and QuantumMie('H2', FH1), Omega(l,r) of the N = 2 viscosity + conductivity set on a
+    10^4-point T grid 10-500 K per GPU (T-dependent potential: effective coefficients per temperature, every Omega integrated).
+    Host T array in, host Omega table out (omega_table = kg_omega_batch)."""
+    from kineticgas_b200 import QuantumMie
+    T = np.linspace(10.0, 500.0, QM_NT * n_gpus)[rank::n_gpus]
+    ls, rs = [l for l, r in QM_LR], [r for l, r in QM_LR]
+    out = {"ms": [], "finite": True}
+    kins = [QuantumMie(c, FH_orders=1, N=2, is_idealgas=True, device=local_rank) for c in ("HE", "H2")]
+    for step in range(steps + 1):                 # first pass is the warm-up
+        t0 = time.perf_counter()
+        for kin in kins:
+            om = kin.omega_table(T, ls, rs)
+            out["finite"] = out["finite"] and bool(np.isfinite(om).all())
+        if step > 0:
+            out["ms"].append(1e3 * (time.perf_counter() - t0))
+    out["n_omega"] = int(2 * T.size * len(QM_LR))
+    out["h2d"] = int(2 * (T.nbytes + T.size * 6 * 8)); out["d2h"] = int(2 * T.size * len(QM_LR) * 8)
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ 5-component surface (configs[4])
+FC_COMPS, FC_N = "C1,C2,C3,N2,CO2", 2
+FC_GRID = (25, 40, 100)       # T x rho* x compositions = 10^5 state points
+
+
+def fc_grid(n_gpus, rank):
+    """25 T (250-700 K) x 40 rho* (0.01-0.6) x 100 Dirichlet(1,1,1,1,1) compositions (seed 1234, clipped to
+    x_i >= 1e-3, renormalised). Weak scaling: rank k owns every n_gpus-th temperature of an n_gpus-times denser T grid."""
+    from kineticgas_b200.fluids import mie_parameters, AVOGADRO
+    ids, Mw, s, e, la, lr = mie_parameters(FC_COMPS)
+    nT, nr, nx = FC_GRID
+    T = np.linspace(250.0, 700.0, nT * n_gpus)[rank::n_gpus]
+    rho = np.linspace(0.01, 0.6, nr) / s[0] ** 3
+    xs = np.random.default_rng(1234).dirichlet(np.ones(5), nx)
+    xs = np.clip(xs, 1e-3, None); xs /= xs.sum(axis=1, keepdims=True)
+    Tg, rg, ig = np.meshgrid(T, rho, np.arange(nx), indexing="ij")
+    return np.ascontiguousarray(Tg.ravel()), np.ascontiguousarray(AVOGADRO / rg.ravel()), np.ascontiguousarray(xs[ig.ravel()])
+
+
+def run_five_comp(local_rank, rank, n_gpus, steps):
+    """configs[4]: full transport surface (eta, lambda, D 4x4 CoN, D_T) of the 5-component RET-Mie mixture, 10^5 state points per
+    GPU, device tables (15 pairs; the 5 CO2 pairs fully integrated) rebuilt every step. Host buffers in and out."""
+    from kineticgas_b200 import MieKinGas
+    kin = MieKinGas(FC_COMPS, N=FC_N, is_idealgas=False, device=local_rank)
+    T, Vm, x = fc_grid(n_gpus, rank)
+    eos = {"dmudn": sp_eos(T, Vm, x), "cp_ideal": np.full((T.size, 5), 4.5 * R_GAS)}
+    out = {"ms": [], "ms_tables": []}
+    res = None
+    for step in range(steps + 1):
+        kin._caches = {}
+        t0 = time.perf_counter()
+        cache = kin.tcache(T, FC_N)
+        t1 = time.perf_counter()
+        res = kin.transport_batch(T, Vm, x, N=FC_N, eos_inputs=eos, cache=cache)
+        t2 = time.perf_counter()
+        if step > 0:
+            out["ms"].append(1e3 * (t2 - t0)); out["ms_tables"].append(1e3 * (t1 - t0))
+    tm = kin.dev.last_timings()
+    out["n"] = int(T.size)
+    out["stage_ms"] = {k: tm[k] for k in ("ms_omega_stage", "ms_tl_stage", "ms_bracket_stage", "ms_state_kernels")}
+    out["h2d"] = int(T.nbytes + Vm.nbytes + x.nbytes + eos["dmudn"].nbytes + eos["cp_ideal"].nbytes)
+    out["d2h"] = int(sum(res[k].nbytes for k in ("viscosity", "conductivity", "conductivity_contribs", "D", "DT")) + 4 * T.size)
+    out["finite"] = bool(all(np.isfinite(res[k]).all() for k in ("viscosity", "conductivity", "D", "DT")))
+    return out
+
+
 # ------------------------------------------------------------------------------------------------ clocks
 class ClockSampler:
     Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
@@ -249,6 +323,7 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=0, help="Omega count of the CPU sample (default: scaled to the host cores)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-state-points", action="store_true", help="skip the RET state-point leg (profiling runs of the Omega kernels)")
+    ap.add_argument("--no-extra-configs", action="store_true", help="skip the configs[3] (Feynman-Hibbs sweep) and configs[4] (5-component surface) legs")
     ap.add_argument("--nt", type=int, default=0, help="profiling only: shrink the per-GPU T grid (a line produced with --nt is not a bench value)")
     args = ap.parse_args()
     if args.nt:
@@ -369,6 +444,18 @@ def main():
             dist.all_reduce(t3, op=dist.ReduceOp.MAX)
         sp["ms_max"] = float(t3.item())
 
+    qm = fc = None
+    if not args.no_extra_configs and not args.no_state_points:
+        barrier()
+        qm = run_qmie_sweep(local_rank, rank, n_gpus, max(1, min(args.steps, 2)))
+        barrier()
+        fc = run_five_comp(local_rank, rank, n_gpus, max(1, min(args.steps, 2)))
+        barrier()
+        t4 = torch.tensor([float(np.mean(qm["ms"])), float(np.mean(fc["ms"]))], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t4, op=dist.ReduceOp.MAX)
+        qm["ms_max"], fc["ms_max"] = float(t4[0].item()), float(t4[1].item())
+
     if rank == 0:
         achieved = nodes * F_NODE / (theta_ms * 1e-3) / 1e12 if theta_ms > 0 else None
         out = {"metric": METRIC, "value": value, "unit": "Omega/s", "n_gpus": n_gpus, "steps": args.steps, "warmup": max(args.warmup, 3),
@@ -386,7 +473,7 @@ def main():
                                          "fp64_pipe_util_est": (nodes * FP64_INSTR_PER_NODE / (theta_ms * 1e-3)) / (peak_tflops * 1e12 / 2.0) if theta_ms > 0 else None,
                                          "note": "frac > 1 because the algorithmic count (SURVEY 8d) prices the reference's per-node log/exp/div/rsqrt (76 of 98 "
                                                  "nominal flop); the kernel removes them algebraically ((sigma/r)^lam = u^lam (sigma/R)^lam with u^lam tabulated) "
-                                                 "and issues ~11 FP64-pipe instructions per node. fp64_pipe_util_est = executed FP64 instructions / DFMA issue peak; "
+                                                 "and issues ~7 FP64-pipe instructions per node. fp64_pipe_util_est = executed FP64 instructions / DFMA issue peak; "
                                                  "the ncu-measured pipe utilisation is in profiles/"}}}
         if sp is not None:
             out["gpu_launches"] = launches + sp["launches"]
@@ -402,6 +489,24 @@ def main():
                                            "are synthetic arrays prepared outside the timed region"}
             if not args.no_cpu_baseline:
                 out["state_points"]["cpu_baseline"] = sp_cpu_baseline(cores)
+        if qm is not None:
+            out["qmie_sweep"] = {"workload": f"configs[3]: QuantumMie HE + H2, Feynman-Hibbs order 1 (4 power-law terms, C_eff(T) per temperature), "
+                                             f"{len(QM_LR)} Omega(l,r) of the N=2 viscosity + conductivity set on a {QM_NT}-point T grid 10-500 K per GPU",
+                                 "value": qm["n_omega"] * world / (qm["ms_max"] * 1e-3), "unit": "Omega/s", "ms_per_step": qm["ms_max"],
+                                 "e2e": {"value": qm["n_omega"] * world / (qm["ms_max"] * 1e-3), "unit": "Omega/s",
+                                         "h2d_bytes_per_step": qm["h2d"], "d2h_bytes_per_step": qm["d2h"]},
+                                 "f_node": QM_F_NODE, "all_finite": qm["finite"],
+                                 "note": "host T grid in, host Omega table out through kg_omega_batch (plan creation, kernels, D2H inside the timed region)"}
+            n_fc = fc["n"] * world
+            out["five_component"] = {"workload": f"configs[4]: RET-Mie {FC_COMPS}, N={FC_N}, eta + lambda + D (4x4, CoN) + D_T on "
+                                                 f"{FC_GRID[0]} T x {FC_GRID[1]} rho* x {FC_GRID[2]} compositions = {fc['n']} state points per GPU, device tables rebuilt every step",
+                                     "value": n_fc / (fc["ms_max"] * 1e-3), "unit": "state points/s", "ms_per_step": fc["ms_max"],
+                                     "ms_tables": float(np.mean(fc["ms_tables"])), "stage_ms": fc["stage_ms"],
+                                     "e2e": {"value": n_fc / (fc["ms_max"] * 1e-3), "unit": "state points/s", "h2d_bytes_per_step": fc["h2d"],
+                                             "d2h_bytes_per_step": fc["d2h"]},
+                                     "all_finite": fc["finite"],
+                                     "note": "host buffers in and out through kg_tcache_create + kg_transport_batch; EoS inputs (dmu/dn, Cp_id) are synthetic "
+                                             "arrays prepared outside the timed region"}
         if not args.no_cpu_baseline:
             n_sample = args.cpu_sample or min(64, max(16, cores))
             cb, _ = run_cpu_reference(n_gpus, n_sample, min(cores, n_sample))

@@ -5,7 +5,7 @@
 //   I     = sum_k w_k (R/u_k^2) [ r^4/b^2 (1 - u(r)/(kT g^2)) - r^2 ]^(-1/2), r = R/u_k   (tanh-sinh, h = 1e-3, truncated)
 //   theta = I(R,g,b) - I(R_lim,g,100 sigma) + PI/2 ;  chi = PI - 2 theta
 // How it is laid out here: one lane per deflection angle. The tanh-sinh abscissae are problem independent, so the
-// host tabulates, per pair, rows  { w_k/u_k, 1/u_k^2, u_k^lam_0, .., u_k^lam_{NT-1} }  (same libm calls as the
+// host tabulates, per pair, rows  { w_k/(2 u_k), 1/u_k^2, u_k^lam_0, .., u_k^lam_{NT-1} }  (same libm calls as the
 // reference). With s = sigma/r = u (sigma/R), every power-law term factorises, (sigma/r)^lam = u^lam (sigma/R)^lam, so
 //   term_k = (w_k/u_k) * rsqrt( X_k ),   X_k = (R/b)^2 (1/u_k^2) (1 - sum_t A_t u_k^lam_t) - 1,
 //   A_t = eps C_t (sigma/R)^lam_t / (kT g^2)   (per lane, once)
@@ -173,10 +173,11 @@ __device__ __forceinline__ double rsqrt_seed(double x) {
 #define KG_RSQRT_ORDER 3
 #endif
 
-// One tanh-sinh term  w_k f(u_k) = (w_k/u_k) X_k^(-1/2)  from a table row { w/u, 1/u^2, u^lam_0 .. }.
+// One tanh-sinh term  w_k f(u_k) = (w_k/u_k) X_k^(-1/2)  from a table row { (w/u)/2, 1/u^2, u^lam_0 .. }.
 // Ap[t] = c2 A_t, so X = (1/u^2) (c2 - sum_t Ap_t u^lam_t) - 1 costs NT+1 DFMA. The reciprocal square root is a MUFU
-// seed y0 plus one Householder step on e = 1 - X y0^2, fused with the weight: t = z (1 + e/2 + 3e^2/8), z = (w/u) y0
+// seed y0 plus one Householder step on e = 1 - X y0^2, fused with the weight: t = 2 z (1 + e/2 + 3e^2/8), z = (w/2u) y0
 // (relative error < 1e-19 for order 3, < 3e-14 for order 2). X <= 0 or NaN gives t = NaN, which fails the stop test.
+// This exact form is used for the first node and wherever the stop rule may trigger.
 template<int NT>
 __device__ __forceinline__ double ts_term(const double* __restrict__ row, const double (&Ap)[NT], double c2) {
     double P = c2;
@@ -185,7 +186,7 @@ __device__ __forceinline__ double ts_term(const double* __restrict__ row, const 
     const double X = fma(row[1], P, -1.0);
     const double y0 = rsqrt_seed(X);
     const double e = fma(-X, y0 * y0, 1.0);
-    const double z = row[0] * y0;
+    const double z = (row[0] + row[0]) * y0;
 #if KG_RSQRT_ORDER == 3
     return fma(z * e, fma(e, 0.375, 0.5), z);
 #else
@@ -193,56 +194,37 @@ __device__ __forceinline__ double ts_term(const double* __restrict__ row, const 
 #endif
 }
 
-// Fast form of the same term for the bulk of the sum. With halved per-lane constants (exact scalings)
-//   Xh = X/2 = (1/u^2) (c2/2 - sum_t (Ap_t/2) u^lam_t) - 1/2                    NT+1 DFMA
-//   q  = MUFU.RSQ64H seed of X, taken from the high word of Xh with its exponent bumped by one (integer pipe)
-//   c  = 3/2 - (Xh q) q   (one Newton step: rsqrt(X) = q c, relative error 1.5 delta^2 < 2e-13)    DMUL + DFMA
-//   z  = (w/u) q ,  I += z c                                                                        DMUL + DFMA
-// i.e. NT+5 FP64-pipe instructions per node and no FP64 compare: the stop rule is checked conservatively for four
-// nodes at once on the high words (positive doubles order like integers): every z_i must exceed tol * I_4 by two
-// high-word ulps (c = 1 +- 2^-20, I_i <= I_4 because all terms are positive) and I_4 must be finite and < 1e100.
-// Anything else -- the end of the sum, a non-positive radicand, NaN/Inf -- falls through to the exact sequential
-// replay below, which is the reference's rule term by term.
+// Fast form of the same term for the bulk of the sum:
+//   X  = (1/u^2) (c2 - sum_t Ap_t u^lam_t) - 1                                                     NT+1 DFMA
+//   q  = MUFU.RSQ64H seed of X (relative error delta < 2^-21)
+//   c  = 3 - (X q) q = 2 (3/2 - X q^2 / 2)   (one Newton step: rsqrt(X) = q c / 2, error 1.5 delta^2 < 4e-13)   DMUL + DFMA
+//   z  = (w/2u) q ,  I += z c                                                                      DMUL + DFMA
+// i.e. NT+5 FP64-pipe instructions per node and no FP64 compare: the stop rule is checked conservatively for a block
+// of nodes at once on the high words (positive doubles order like integers): with c = 2 (1 +- 2^-20) and I_i <= I_n
+// (all terms positive) it is enough that every z_i exceeds (tol/2) I_n by two high-word ulps and that I_n is finite
+// and < 1e100. Anything else -- the end of the sum, a non-positive radicand, NaN/Inf -- falls through to the exact
+// sequential replay, which is the reference's rule term by term.
 template<int NT>
-__device__ __forceinline__ void ts_fast(const double* __restrict__ row, const double (&Aph)[NT], double c2h, double& z, double& c) {
-    double P = c2h;
+__device__ __forceinline__ void ts_fast(const double* __restrict__ row, const double (&Ap)[NT], double c2, double& z, double& c) {
+    double P = c2;
 #pragma unroll
-    for (int t = 0; t < NT; t++) P = fma(-Aph[t], row[2 + t], P);
-    const double Xh = fma(row[1], P, -0.5);
-    const double q = rsqrt_seed(__hiloint2double(__double2hiint(Xh) + 0x00100000, 0));
-    const double a = Xh * q;
-    c = fma(-a, q, 1.5);
+    for (int t = 0; t < NT; t++) P = fma(-Ap[t], row[2 + t], P);
+    const double X = fma(row[1], P, -1.0);
+    const double q = rsqrt_seed(X);
+    const double a = X * q;
+    c = fma(-a, q, 3.0);
     z = row[0] * q;
 }
 
 constexpr int HI_1E100 = 0x54B249AD;      // high word of 1e100
 
-// Four consecutive nodes evaluated together (independent chains), then the reference's sequential stop rule: a term is
-// added only if all earlier ones were and |w f / I| > tol (Integration.cpp:431); NaN/Inf of the new integrand value
-// (radicand <= 0) ends the sum (Integration.cpp:430). I is the running sum, k = index of the last node examined (what
-// the reference's loop variable holds at exit).
+// Exact replay of four consecutive nodes with the reference's sequential stop rule: a term is added only if all earlier
+// ones were and |w f / I| > tol (Integration.cpp:431); NaN/Inf of the new integrand value (radicand <= 0) ends the sum
+// (Integration.cpp:430). I is the running sum, k = index of the last node examined (what the reference's loop variable
+// holds at exit). Returns true when the sum has ended.
 template<int NT>
-__device__ __forceinline__ bool ts_step4(const double* __restrict__ r0, const double (&Aph)[NT], double c2h, double& I, int& k) {
+__device__ __noinline__ bool ts_exact4(const double* __restrict__ r0, const double (&Ap)[NT], double cc, double& I, int& k) {
     constexpr int W = 2 + NT;
-    double z0, z1, z2, z3, c0, c1, c2, c3;
-    ts_fast<NT>(r0, Aph, c2h, z0, c0);
-    ts_fast<NT>(r0 + W, Aph, c2h, z1, c1);
-    ts_fast<NT>(r0 + 2 * W, Aph, c2h, z2, c2);
-    ts_fast<NT>(r0 + 3 * W, Aph, c2h, z3, c3);
-    const double I1 = fma(z0, c0, I);
-    const double I2 = fma(z1, c1, I1);
-    const double I3 = fma(z2, c2, I2);
-    const double I4 = fma(z3, c3, I3);
-    const int lim = __double2hiint(TS_TOL * I4);
-    const int zmin = min(min(__double2hiint(z0), __double2hiint(z1)), min(__double2hiint(z2), __double2hiint(z3)));
-#ifndef KG_TS_NOFAST
-    if ((zmin > lim + 2) && (lim < HI_1E100) && (lim >= 0)) { I = I4; k += 4; return false; }
-#endif
-    // exact replay of these four nodes
-    double Ap[NT];
-#pragma unroll
-    for (int t = 0; t < NT; t++) Ap[t] = Aph[t] + Aph[t];
-    const double cc = c2h + c2h;
     const double t0 = ts_term<NT>(r0, Ap, cc);
     const double t1 = ts_term<NT>(r0 + W, Ap, cc);
     const double t2 = ts_term<NT>(r0 + 2 * W, Ap, cc);
@@ -258,24 +240,45 @@ __device__ __forceinline__ bool ts_step4(const double* __restrict__ r0, const do
     return true;
 }
 
+#ifndef KG_TS_BLOCK
+#define KG_TS_BLOCK 8
+#endif
+
 // cpp/Spherical.cpp:321-329 + cpp/Integration/Integration.cpp:417-437, on tabulated nodes.
 // srows: first KS rows in shared memory; grows: all KMAX rows in global memory. Row j holds node k = j + 1.
 // A[t] = eps C_t (sigma/R)^lam_t / (kT g^2), c2 = (R/b)^2. nodes += k at exit.
+// The bulk of the sum runs in blocks of KG_TS_BLOCK fast nodes with one conservative high-word stop check per block;
+// a block that may contain the stop (or anything irregular) is replayed exactly, four nodes at a time.
 template<int NT>
 __device__ double theta_integral(const double* __restrict__ srows, const double* __restrict__ grows, int KS,
                                  const double (&A)[NT], double c2, unsigned& nodes, int& status) {
     constexpr int W = 2 + NT;
-    double Ap[NT], Aph[NT];
+    double Ap[NT];
 #pragma unroll
-    for (int t = 0; t < NT; t++) { Ap[t] = c2 * A[t]; Aph[t] = 0.5 * Ap[t]; }
+    for (int t = 0; t < NT; t++) Ap[t] = c2 * A[t];
     double I = ts_term<NT>(srows, Ap, c2);              // k = 1 is added unconditionally (Integration.cpp:425)
-    const double c2h = 0.5 * c2;
     int k = 1;
-    bool stop = false;
-    while (!stop && k + 4 <= KS) stop = ts_step4<NT>(srows + (size_t) k * W, Aph, c2h, I, k);
-    while (!stop) {
+    for (;;) {
+#ifndef KG_TS_NOFAST
+        while (k + KG_TS_BLOCK <= KS) {
+            const double* __restrict__ r = srows + (size_t) k * W;
+            double In = I;
+            int zmin = 0x7fffffff;
+#pragma unroll
+            for (int j = 0; j < KG_TS_BLOCK; j++) {
+                double z, c;
+                ts_fast<NT>(r + j * W, Ap, c2, z, c);
+                In = fma(z, c, In);
+                zmin = min(zmin, __double2hiint(z));
+            }
+            const int lim = __double2hiint((0.5 * TS_TOL) * In);
+            if (!((zmin > lim + 2) && (lim < HI_1E100) && (lim >= 0))) break;
+            I = In; k += KG_TS_BLOCK;
+        }
+#endif
         if (k + 4 > KMAX) { status |= 2; break; }
-        stop = ts_step4<NT>(grows + (size_t) k * W, Aph, c2h, I, k);
+        const double* r = (k + 4 <= KS) ? srows + (size_t) k * W : grows + (size_t) k * W;
+        if (ts_exact4<NT>(r, Ap, c2, I, k)) break;
     }
     nodes += (unsigned) k;
     return I;

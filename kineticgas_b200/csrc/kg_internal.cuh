@@ -22,6 +22,7 @@ struct kg_model {
     int sm_count = 148;
     // stage timings of the last kg_tcache_create / kg_transport_batch on this model (kg_last_timings)
     double timings[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int tl_launches = 0;       // kernel launches of the last kg_transfer_lengths_batch
     void set_error(const std::string& s) { err = s; }
 };
 

@@ -515,7 +515,7 @@ void build_rows(const kg_potential_desc& d, int ntpad, std::vector<double>& rows
         if (k == 1) w = (PI / 2.) * h * cosh(k * h) / pow(cosh(PI * sinh(k * h * 1e-3) / 2.), 2);   // the 1e-3 quirk, :422
         else w = (PI / 2) * h * cosh(k * h) / pow(cosh(PI * sinh(k * h) / 2.), 2);
         double* r = &rows[(size_t) (k - 1) * W];
-        r[0] = w / u;
+        r[0] = 0.5 * (w / u);       // halved: the fast node form carries the factor 2 in its Newton step (kg_device.cuh)
         r[1] = 1.0 / (u * u);
         for (int t = 0; t < ntpad; t++) r[2 + t] = (t < d.nterms) ? pow(u, d.lam[t]) : 0.0;
     }
@@ -792,6 +792,8 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
     PLAN_CUDA(cudaMalloc(&p->d_gfac, gfac.size() * sizeof(double)));
     PLAN_CUDA(cudaMalloc(&p->d_lr_l, nlr * sizeof(int)));
     PLAN_CUDA(cudaMalloc(&p->d_lr_ri, nlr * sizeof(int)));
+    // small batches take the hard bound outright (never grows); large ones start from the estimate, at least 32 M cells
+    p->cell_cap = std::min(p->cell_cap_limit, std::max(p->cell_cap, (long long) 32 << 20));
     p->cell_cap = std::max(p->cell_cap, p->ncells0);
     if (p->nitems >= (1 << 22) || nlr > 64 || p->cell_cap >= (1LL << 31)) { set_error("kg_omega_plan_create: batch too large, split the T grid"); kg_omega_plan_destroy(p); return -1; }
     PLAN_CUDA(cudaMalloc(&p->d_cells[0], p->cell_cap * sizeof(Cell)));

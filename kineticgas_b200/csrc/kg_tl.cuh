@@ -31,13 +31,17 @@ __device__ double chi_with_lim(const PairParams& pp, const double* coeff, const 
 }
 
 template<int NT>
-__global__ void __launch_bounds__(256) tl_search_kernel(PairParams pp, const double* __restrict__ rows, const TlItem* __restrict__ items,
-                                                        int item0, int nitems, const double* __restrict__ coeff_pool,
+__global__ void __launch_bounds__(256) tl_search_kernel(const PairParams* __restrict__ pairs, const double* const* __restrict__ rows_by_pair,
+                                                        const TlItem* __restrict__ items, int pair0, int nitems, const double* __restrict__ coeff_pool,
                                                         const double* __restrict__ gnodes, double* __restrict__ ilim,
                                                         double* __restrict__ bmid_out, double* __restrict__ bmax_out, int* __restrict__ status) {
     extern __shared__ double srows[];
+    __shared__ PairParams pp;
     constexpr int W = 2 + NT;
+    const int pair = pair0 + blockIdx.y, item0 = pair * nitems;       // grid.y walks the pairs of this launch, nitems = nT
+    const double* __restrict__ rows = rows_by_pair[pair];
     for (int i = threadIdx.x; i < KS_ROWS * W; i += blockDim.x) srows[i] = rows[i];
+    if (threadIdx.x == 0) pp = pairs[pair];
     __syncthreads();
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= nitems * TL_NG) return;
@@ -101,14 +105,18 @@ __device__ __forceinline__ double tl_bnode(int k, double bmid, double bmax, doub
 }
 
 template<int NT>
-__global__ void __launch_bounds__(256) tl_node_kernel(PairParams pp, const double* __restrict__ rows, const TlItem* __restrict__ items,
-                                                      int item0, int nitems, const double* __restrict__ coeff_pool,
+__global__ void __launch_bounds__(256) tl_node_kernel(const PairParams* __restrict__ pairs, const double* const* __restrict__ rows_by_pair,
+                                                      const TlItem* __restrict__ items, int pair0, int nitems, const double* __restrict__ coeff_pool,
                                                       const double* __restrict__ gnodes, const double* __restrict__ ilim,
                                                       const double* __restrict__ bmid_in, const double* __restrict__ bmax_in,
                                                       double4* __restrict__ fw, int* __restrict__ status) {
     extern __shared__ double srows[];
+    __shared__ PairParams pp;
     constexpr int W = 2 + NT;
+    const int pair = pair0 + blockIdx.y, item0 = pair * nitems;
+    const double* __restrict__ rows = rows_by_pair[pair];
     for (int i = threadIdx.x; i < KS_ROWS * W; i += blockDim.x) srows[i] = rows[i];
+    if (threadIdx.x == 0) pp = pairs[pair];
     __syncthreads();
     const long long e = (long long) blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= (long long) nitems * TL_NG * TL_NB) return;
@@ -143,13 +151,13 @@ __global__ void __launch_bounds__(256) tl_node_kernel(PairParams pp, const doubl
         out = make_double4(Rm * wm, wm, Rm * we, we);
         if (st) atomicOr(&status[it], st);
     }
-    fw[e + (long long) item0 * 0] = out;
+    fw[(long long) blockIdx.y * nitems * TL_NG * TL_NB + e] = out;      // fw holds the pairs of one launch
 }
 
 // nested Simpson sums in the reference's order (Integration.cpp:375-415, transfer_lengths.cpp:165-194)
 __global__ void tl_reduce_kernel(int item0, int nitems, const double* __restrict__ bmid_in, const double* __restrict__ bmax_in,
                                  const double4* __restrict__ fw, double* __restrict__ mtl, double* __restrict__ etl) {
-    const int li = blockIdx.x * blockDim.x + threadIdx.x;
+    const int li = blockIdx.x * blockDim.x + threadIdx.x;     // item within this launch (pairs of the launch are contiguous)
     if (li >= nitems) return;
     const int it = item0 + li;
     double Fg[2][2] = {{0, 0}, {0, 0}}, Wg[2][2] = {{0, 0}, {0, 0}};   // [g interval][property]
@@ -225,7 +233,11 @@ extern "C" int kg_transfer_lengths_batch(kg_model* m, int nT, const double* T, c
     CUDA_OK(cudaMalloc(&d_ilim, (size_t) nitems * TL_NG * sizeof(double)));
     CUDA_OK(cudaMalloc(&d_bmid, (size_t) nitems * TL_NG * sizeof(double)));
     CUDA_OK(cudaMalloc(&d_bmax, (size_t) nitems * TL_NG * sizeof(double)));
-    CUDA_OK(cudaMalloc(&d_fw, (size_t) nT * TL_NG * TL_NB * sizeof(double4)));     // one pair at a time
+    // all pairs in one launch (grid.y) unless the node buffer would exceed 1 GiB
+    const size_t fw_per_pair = (size_t) nT * TL_NG * TL_NB * sizeof(double4);
+    const int pairs_per_launch = (int) std::max<size_t>(1, std::min<size_t>((size_t) Np, ((size_t) 1 << 30) / fw_per_pair));
+    CUDA_OK(cudaMalloc(&d_fw, fw_per_pair * pairs_per_launch));
+    m->tl_launches = 0;
     CUDA_OK(cudaMalloc(&d_mtl, nitems * sizeof(double)));
     CUDA_OK(cudaMalloc(&d_etl, nitems * sizeof(double)));
     CUDA_OK(cudaMalloc(&d_status, nitems * sizeof(int)));
@@ -237,20 +249,21 @@ extern "C" int kg_transfer_lengths_batch(kg_model* m, int nT, const double* T, c
         CUDA_OK(cudaMemcpyAsync(d_coeff, coeff_T, (size_t) nT * Np * KG_MAX_TERMS * sizeof(double), cudaMemcpyHostToDevice, s));
     }
     const size_t smem = (size_t) KS_ROWS * (2 + m->ntpad) * sizeof(double);
-    for (int p = 0; p < Np; p++) {
-        const int item0 = p * nT;
-        const int g1 = (nT * TL_NG + 255) / 256;
+    for (int p0 = 0; p0 < Np; p0 += pairs_per_launch) {
+        const int np = std::min(pairs_per_launch, Np - p0);
+        const dim3 g1((nT * TL_NG + 255) / 256, np);
         const long long n2 = (long long) nT * TL_NG * TL_NB;
-        const int g2 = (int) ((n2 + 255) / 256);
+        const dim3 g2((unsigned) ((n2 + 255) / 256), np);
 #define TL_LAUNCH(NT) do { \
         cudaFuncSetAttribute(tl_search_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem); \
         cudaFuncSetAttribute(tl_node_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem); \
-        tl_search_kernel<NT><<<g1, 256, smem, s>>>(m->pairs[p], m->d_rows[p], d_items, item0, nT, d_coeff, d_g, d_ilim, d_bmid, d_bmax, d_status); \
-        tl_node_kernel<NT><<<g2, 256, smem, s>>>(m->pairs[p], m->d_rows[p], d_items, item0, nT, d_coeff, d_g, d_ilim, d_bmid, d_bmax, d_fw, d_status); } while (0)
+        tl_search_kernel<NT><<<g1, 256, smem, s>>>(m->d_pairs, m->d_rows_by_pair, d_items, p0, nT, d_coeff, d_g, d_ilim, d_bmid, d_bmax, d_status); \
+        tl_node_kernel<NT><<<g2, 256, smem, s>>>(m->d_pairs, m->d_rows_by_pair, d_items, p0, nT, d_coeff, d_g, d_ilim, d_bmid, d_bmax, d_fw, d_status); } while (0)
         switch (m->ntpad) { case 2: TL_LAUNCH(2); break; case 4: TL_LAUNCH(4); break; default: TL_LAUNCH(6); break; }
 #undef TL_LAUNCH
-        tl_reduce_kernel<<<(nT + 127) / 128, 128, 0, s>>>(item0, nT, d_bmid, d_bmax, d_fw, d_mtl, d_etl);
+        tl_reduce_kernel<<<(np * nT + 127) / 128, 128, 0, s>>>(p0 * nT, np * nT, d_bmid, d_bmax, d_fw, d_mtl, d_etl);
         CUDA_OK(cudaGetLastError());
+        m->tl_launches += 3;
     }
     std::vector<double> hm(nitems), he(nitems); std::vector<int> hs(nitems);
     CUDA_OK(cudaMemcpyAsync(hm.data(), d_mtl, nitems * sizeof(double), cudaMemcpyDeviceToHost, s));

@@ -887,7 +887,7 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
         int bad = 0; for (int v : tst) bad |= v;
         if (bad & KG_STATUS_BMID) { set_error("Unable to converge bmid!"); kg_tcache_destroy(c); return -4; }
         if (bad & KG_STATUS_GETR_MAXITER) { set_error("get_R reached max iter!"); kg_tcache_destroy(c); return -4; }
-        m->timings[2] = ms_since(t_stage); m->timings[4] += 3.0 * Np;
+        m->timings[2] = ms_since(t_stage); m->timings[4] += m->tl_launches;
         TC_CUDA(upload(&c->d_mtl, c->h_mtl)); TC_CUDA(upload(&c->d_etl, c->h_etl));
         MiePair* d_diag = nullptr;
         TC_CUDA(upload(&d_diag, mp_diag));
