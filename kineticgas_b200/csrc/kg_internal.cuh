@@ -4,6 +4,9 @@
 #include "../../include/kgcuda.h"
 #include <string>
 #include <vector>
+#include <map>
+#include <unordered_map>
+#include <algorithm>
 
 #define CUDA_OK(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { \
     set_error(std::string(#expr) + ": " + cudaGetErrorString(e_)); return -2; } } while (0)
@@ -24,5 +27,42 @@ struct kg_model {
     double timings[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     int tl_launches = 0;       // kernel launches of the last kg_transfer_lengths_batch
     void set_error(const std::string& s) { err = s; }
+
+    // Device-memory pool of this model. A batch call allocates a few dozen buffers whose sizes repeat from call to call;
+    // cudaMalloc/cudaFree are driver calls that serialise across the processes of a multi-GPU job, so freed blocks are
+    // kept and handed out again (smallest cached block within 25 % of the request). Everything a model does runs on its
+    // stream, and dfree() waits for that stream before the block can be reused by a host-synchronous copy.
+    std::multimap<size_t, void*> pool_free;
+    std::unordered_map<void*, size_t> pool_live;
+    size_t pool_cached = 0;
+    int* h_pinned = nullptr;            // 16 ints of pinned host memory for the small D2H reads of the pass loop
+    cudaError_t dmalloc_bytes(void** out, size_t bytes) {
+        bytes = (std::max<size_t>(bytes, 1) + 511) & ~(size_t) 511;
+        auto f = pool_free.lower_bound(bytes);
+        if (f != pool_free.end() && f->first <= bytes + bytes / 4 + 65536) {
+            *out = f->second; pool_live[f->second] = f->first; pool_cached -= f->first; pool_free.erase(f);
+            return cudaSuccess;
+        }
+        cudaError_t e = cudaMalloc(out, bytes);
+        if (e != cudaSuccess) { cudaGetLastError(); pool_release(); e = cudaMalloc(out, bytes); }
+        if (e == cudaSuccess) pool_live[*out] = bytes;
+        return e;
+    }
+    void dfree(void* p) {
+        if (!p) return;
+        auto f = pool_live.find(p);
+        if (f == pool_live.end()) { cudaFree(p); return; }
+        if (stream) cudaStreamSynchronize(stream);
+        const size_t bytes = f->second;
+        pool_live.erase(f);
+        if (pool_cached + bytes > ((size_t) 48 << 30)) { cudaFree(p); return; }
+        pool_free.emplace(bytes, p); pool_cached += bytes;
+    }
+    void pool_release() {
+        for (auto& kv : pool_free) cudaFree(kv.second);
+        pool_free.clear(); pool_cached = 0;
+    }
 };
+
+template<class T> inline cudaError_t kg_dmalloc(kg_model* m, T** out, size_t bytes) { return m->dmalloc_bytes((void**) out, bytes); }
 

@@ -572,6 +572,7 @@ extern "C" int kg_model_create(const kg_potential_desc* pairs, int ncomps, const
          cu(cudaMemcpy(m->d_rows_by_pair, m->d_rows.data(), m->npairs * sizeof(double*), cudaMemcpyHostToDevice), "H2D") &&
          cu(cudaMalloc(&m->d_pairs, m->npairs * sizeof(PairParams)), "cudaMalloc") &&
          cu(cudaMemcpy(m->d_pairs, m->pairs.data(), m->npairs * sizeof(PairParams), cudaMemcpyHostToDevice), "H2D");
+    ok = ok && cu(cudaMallocHost(&m->h_pinned, 16 * sizeof(int)), "cudaMallocHost");
     if (!ok) { kg_model_destroy(m); return -2; }
     *out = m;
     return 0;
@@ -583,6 +584,10 @@ extern "C" void kg_model_destroy(kg_model* m) {
     for (double* p : m->d_rows) cudaFree(p);
     if (m->d_rows_by_pair) cudaFree(m->d_rows_by_pair);
     if (m->d_pairs) cudaFree(m->d_pairs);
+    if (m->stream) cudaStreamSynchronize(m->stream);
+    m->pool_release();
+    for (auto& kv : m->pool_live) cudaFree(kv.first);
+    if (m->h_pinned) cudaFreeHost(m->h_pinned);
     if (m->stream && m->own_stream) cudaStreamDestroy(m->stream);
     delete m;
 }
@@ -604,13 +609,13 @@ extern "C" int kg_chi_points(kg_model* m, int pair, double T, int n, const doubl
     if (n == 0) return 0;
     CUDA_OK(cudaSetDevice(m->device));
     double *dg = nullptr, *db = nullptr, *dchi = nullptr, *dR = nullptr, *dcoef = nullptr; int* dst = nullptr;
-    CUDA_OK(cudaMalloc(&dg, n * sizeof(double))); CUDA_OK(cudaMalloc(&db, n * sizeof(double)));
-    CUDA_OK(cudaMalloc(&dchi, n * sizeof(double))); CUDA_OK(cudaMalloc(&dR, n * sizeof(double)));
-    CUDA_OK(cudaMalloc(&dst, n * sizeof(int)));
+    CUDA_OK(kg_dmalloc(m, &dg, n * sizeof(double))); CUDA_OK(kg_dmalloc(m, &db, n * sizeof(double)));
+    CUDA_OK(kg_dmalloc(m, &dchi, n * sizeof(double))); CUDA_OK(kg_dmalloc(m, &dR, n * sizeof(double)));
+    CUDA_OK(kg_dmalloc(m, &dst, n * sizeof(int)));
     CUDA_OK(cudaMemcpyAsync(dg, g, n * sizeof(double), cudaMemcpyHostToDevice, m->stream));
     CUDA_OK(cudaMemcpyAsync(db, b_red, n * sizeof(double), cudaMemcpyHostToDevice, m->stream));
     if (coeff) {
-        CUDA_OK(cudaMalloc(&dcoef, KG_MAX_TERMS * sizeof(double)));
+        CUDA_OK(kg_dmalloc(m, &dcoef, KG_MAX_TERMS * sizeof(double)));
         CUDA_OK(cudaMemcpyAsync(dcoef, coeff, m->descs[pair].nterms * sizeof(double), cudaMemcpyHostToDevice, m->stream));
     }
     const int W = 2 + m->ntpad;
@@ -626,7 +631,7 @@ extern "C" int kg_chi_points(kg_model* m, int pair, double T, int n, const doubl
     if (R_out) CUDA_OK(cudaMemcpyAsync(R_out, dR, n * sizeof(double), cudaMemcpyDeviceToHost, m->stream));
     if (status) CUDA_OK(cudaMemcpyAsync(status, dst, n * sizeof(int), cudaMemcpyDeviceToHost, m->stream));
     CUDA_OK(cudaStreamSynchronize(m->stream));
-    cudaFree(dg); cudaFree(db); cudaFree(dchi); cudaFree(dR); cudaFree(dst); if (dcoef) cudaFree(dcoef);
+    m->dfree(dg); m->dfree(db); m->dfree(dchi); m->dfree(dR); m->dfree(dst); m->dfree(dcoef);
     return 0;
 }
 
@@ -778,47 +783,47 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
     p->max_list = cap;
 
 #define PLAN_CUDA(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { set_error(std::string(#expr) + ": " + cudaGetErrorString(e_)); kg_omega_plan_destroy(p); return -2; } } while (0)
-    PLAN_CUDA(cudaMalloc(&p->d_items, p->nitems * sizeof(Item)));
-    PLAN_CUDA(cudaMalloc(&p->d_regimes, 5 * sizeof(Regime)));
-    PLAN_CUDA(cudaMalloc(&p->d_tab, p->tab_doubles * sizeof(double)));
-    PLAN_CUDA(cudaMalloc(&p->d_want, p->mask_words * sizeof(unsigned)));
-    PLAN_CUDA(cudaMalloc(&p->d_known, p->mask_words * sizeof(unsigned)));
-    PLAN_CUDA(cudaMalloc(&p->d_lim, p->ncols_total * sizeof(double)));
-    PLAN_CUDA(cudaMalloc(&p->d_have_lim, p->ncols_total));
-    PLAN_CUDA(cudaMalloc(&p->d_tasks, p->ntasks * sizeof(int2)));
-    PLAN_CUDA(cudaMalloc(&p->d_counts, (p->ntasks + 1) * sizeof(int)));
-    PLAN_CUDA(cudaMalloc(&p->d_offsets, (p->ntasks + 1) * sizeof(int)));
-    PLAN_CUDA(cudaMalloc(&p->d_list, p->max_list * sizeof(WorkEntry)));
-    PLAN_CUDA(cudaMalloc(&p->d_gfac, gfac.size() * sizeof(double)));
-    PLAN_CUDA(cudaMalloc(&p->d_lr_l, nlr * sizeof(int)));
-    PLAN_CUDA(cudaMalloc(&p->d_lr_ri, nlr * sizeof(int)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_items, p->nitems * sizeof(Item)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_regimes, 5 * sizeof(Regime)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_tab, p->tab_doubles * sizeof(double)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_want, p->mask_words * sizeof(unsigned)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_known, p->mask_words * sizeof(unsigned)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_lim, p->ncols_total * sizeof(double)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_have_lim, p->ncols_total));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_tasks, p->ntasks * sizeof(int2)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_counts, (p->ntasks + 1) * sizeof(int)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_offsets, (p->ntasks + 1) * sizeof(int)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_list, p->max_list * sizeof(WorkEntry)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_gfac, gfac.size() * sizeof(double)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_lr_l, nlr * sizeof(int)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_lr_ri, nlr * sizeof(int)));
     // small batches take the hard bound outright (never grows); large ones start from the estimate, at least 32 M cells
     p->cell_cap = std::min(p->cell_cap_limit, std::max(p->cell_cap, (long long) 32 << 20));
     p->cell_cap = std::max(p->cell_cap, p->ncells0);
     if (p->nitems >= (1 << 22) || nlr > 64 || p->cell_cap >= (1LL << 31)) { set_error("kg_omega_plan_create: batch too large, split the T grid"); kg_omega_plan_destroy(p); return -1; }
-    PLAN_CUDA(cudaMalloc(&p->d_cells[0], p->cell_cap * sizeof(Cell)));
-    PLAN_CUDA(cudaMalloc(&p->d_cells[1], p->cell_cap * sizeof(Cell)));
-    PLAN_CUDA(cudaMalloc(&p->d_ncells, 2 * sizeof(int)));
-    PLAN_CUDA(cudaMalloc(&p->d_W, (size_t) p->nitems * nlr * sizeof(double)));
-    PLAN_CUDA(cudaMalloc(&p->d_omega, (size_t) p->nitems * nlr * sizeof(double)));
-    PLAN_CUDA(cudaMalloc(&p->d_W_out, (size_t) p->nitems * nlr * sizeof(double)));
-    PLAN_CUDA(cudaMalloc(&p->d_omega_out, (size_t) p->nitems * nlr * sizeof(double)));
-    PLAN_CUDA(cudaMalloc(&p->d_status, p->nitems * sizeof(int)));
-    PLAN_CUDA(cudaMalloc(&p->d_flags, 4 * sizeof(int)));
-    PLAN_CUDA(cudaMalloc(&p->d_tile_counter, (Np + 1) * sizeof(int)));
-    PLAN_CUDA(cudaMalloc(&p->d_pair_task_start, (Np + 1) * sizeof(int)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_cells[0], p->cell_cap * sizeof(Cell)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_cells[1], p->cell_cap * sizeof(Cell)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_ncells, 2 * sizeof(int)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_W, (size_t) p->nitems * nlr * sizeof(double)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_omega, (size_t) p->nitems * nlr * sizeof(double)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_W_out, (size_t) p->nitems * nlr * sizeof(double)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_omega_out, (size_t) p->nitems * nlr * sizeof(double)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_status, p->nitems * sizeof(int)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_flags, 4 * sizeof(int)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_tile_counter, (Np + 1) * sizeof(int)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_pair_task_start, (Np + 1) * sizeof(int)));
     PLAN_CUDA(cudaMemcpy(p->d_pair_task_start, pair_task_start.data(), (Np + 1) * sizeof(int), cudaMemcpyHostToDevice));
-    PLAN_CUDA(cudaMalloc(&p->d_perm, p->nitems * sizeof(int)));
-    PLAN_CUDA(cudaMalloc(&p->d_active, (active.size() + 1) * sizeof(int)));
-    PLAN_CUDA(cudaMalloc(&p->d_active_mask, (active.size() + 1) * sizeof(unsigned long long)));
-    PLAN_CUDA(cudaMalloc(&p->d_active_cell_off, (active.size() + 1) * sizeof(long long)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_perm, p->nitems * sizeof(int)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_active, (active.size() + 1) * sizeof(int)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_active_mask, (active.size() + 1) * sizeof(unsigned long long)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_active_cell_off, (active.size() + 1) * sizeof(long long)));
     PLAN_CUDA(cudaMemcpy(p->d_active, active.data(), active.size() * sizeof(int), cudaMemcpyHostToDevice));
     PLAN_CUDA(cudaMemcpy(p->d_active_mask, active_mask.data(), active.size() * sizeof(unsigned long long), cudaMemcpyHostToDevice));
     PLAN_CUDA(cudaMemcpy(p->d_active_cell_off, active_cell_off.data(), active.size() * sizeof(long long), cudaMemcpyHostToDevice));
-    PLAN_CUDA(cudaMalloc(&p->d_counters, 8 * sizeof(unsigned long long)));
-    PLAN_CUDA(cudaMallocHost(&p->h_pinned, 8 * sizeof(int)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_counters, 8 * sizeof(unsigned long long)));
+    p->h_pinned = m->h_pinned;
     if (coeff_T) {
-        PLAN_CUDA(cudaMalloc(&p->d_coeff, (size_t) nT * Np * KG_MAX_TERMS * sizeof(double)));
+        PLAN_CUDA(kg_dmalloc(m, &p->d_coeff, (size_t) nT * Np * KG_MAX_TERMS * sizeof(double)));
         PLAN_CUDA(cudaMemcpy(p->d_coeff, coeff_T, (size_t) nT * Np * KG_MAX_TERMS * sizeof(double), cudaMemcpyHostToDevice));
     }
     PLAN_CUDA(cudaMemcpy(p->d_items, p->items.data(), p->nitems * sizeof(Item), cudaMemcpyHostToDevice));
@@ -843,8 +848,7 @@ extern "C" void kg_omega_plan_destroy(kg_omega_plan* p) {
                     p->d_offsets, p->d_list, p->d_gfac, p->d_lr_l, p->d_lr_ri, p->d_coeff, p->d_W, p->d_omega, p->d_W_out,
                     p->d_omega_out, p->d_status, p->d_flags, p->d_tile_counter, p->d_perm, p->d_counters, p->d_cells[0], p->d_cells[1], p->d_ncells, p->d_pair_task_start,
                     p->d_active, p->d_active_mask, p->d_active_cell_off};
-    for (void* q : ptrs) if (q) cudaFree(q);
-    if (p->h_pinned) cudaFreeHost(p->h_pinned);
+    for (void* q : ptrs) p->m->dfree(q);
     for (int k = 0; k < 4; k++) if (p->ev[k]) cudaEventDestroy(p->ev[k]);
     delete p;
 }
@@ -918,9 +922,9 @@ extern "C" int kg_omega_plan_run(kg_omega_plan* p) {
             if (p->cell_cap >= p->cell_cap_limit) { set_error("kg_omega_plan_run: cell list overflow"); return -3; }
             const long long grown = std::min(p->cell_cap_limit, 2 * p->cell_cap);
             if (grown >= (1LL << 31)) { set_error("kg_omega_plan_run: batch too large, split the T grid"); return -3; }
-            cudaFree(p->d_cells[0]); cudaFree(p->d_cells[1]); p->d_cells[0] = p->d_cells[1] = nullptr;
-            CUDA_OK(cudaMalloc(&p->d_cells[0], grown * sizeof(Cell)));
-            CUDA_OK(cudaMalloc(&p->d_cells[1], grown * sizeof(Cell)));
+            m->dfree(p->d_cells[0]); m->dfree(p->d_cells[1]); p->d_cells[0] = p->d_cells[1] = nullptr;
+            CUDA_OK(kg_dmalloc(m, &p->d_cells[0], grown * sizeof(Cell)));
+            CUDA_OK(kg_dmalloc(m, &p->d_cells[1], grown * sizeof(Cell)));
             p->cell_cap = grown; p->regrows++;
             return kg_omega_plan_run(p);
         }

@@ -228,24 +228,24 @@ extern "C" int kg_transfer_lengths_batch(kg_model* m, int nT, const double* T, c
     TlItem* d_items = nullptr; double *d_g = nullptr, *d_ilim = nullptr, *d_bmid = nullptr, *d_bmax = nullptr, *d_mtl = nullptr, *d_etl = nullptr, *d_coeff = nullptr;
     double4* d_fw = nullptr; int* d_status = nullptr;
     cudaStream_t s = m->stream;
-    CUDA_OK(cudaMalloc(&d_items, nitems * sizeof(TlItem)));
-    CUDA_OK(cudaMalloc(&d_g, TL_NG * sizeof(double)));
-    CUDA_OK(cudaMalloc(&d_ilim, (size_t) nitems * TL_NG * sizeof(double)));
-    CUDA_OK(cudaMalloc(&d_bmid, (size_t) nitems * TL_NG * sizeof(double)));
-    CUDA_OK(cudaMalloc(&d_bmax, (size_t) nitems * TL_NG * sizeof(double)));
+    CUDA_OK(kg_dmalloc(m, &d_items, nitems * sizeof(TlItem)));
+    CUDA_OK(kg_dmalloc(m, &d_g, TL_NG * sizeof(double)));
+    CUDA_OK(kg_dmalloc(m, &d_ilim, (size_t) nitems * TL_NG * sizeof(double)));
+    CUDA_OK(kg_dmalloc(m, &d_bmid, (size_t) nitems * TL_NG * sizeof(double)));
+    CUDA_OK(kg_dmalloc(m, &d_bmax, (size_t) nitems * TL_NG * sizeof(double)));
     // all pairs in one launch (grid.y) unless the node buffer would exceed 1 GiB
     const size_t fw_per_pair = (size_t) nT * TL_NG * TL_NB * sizeof(double4);
     const int pairs_per_launch = (int) std::max<size_t>(1, std::min<size_t>((size_t) Np, ((size_t) 1 << 30) / fw_per_pair));
-    CUDA_OK(cudaMalloc(&d_fw, fw_per_pair * pairs_per_launch));
+    CUDA_OK(kg_dmalloc(m, &d_fw, fw_per_pair * pairs_per_launch));
     m->tl_launches = 0;
-    CUDA_OK(cudaMalloc(&d_mtl, nitems * sizeof(double)));
-    CUDA_OK(cudaMalloc(&d_etl, nitems * sizeof(double)));
-    CUDA_OK(cudaMalloc(&d_status, nitems * sizeof(int)));
+    CUDA_OK(kg_dmalloc(m, &d_mtl, nitems * sizeof(double)));
+    CUDA_OK(kg_dmalloc(m, &d_etl, nitems * sizeof(double)));
+    CUDA_OK(kg_dmalloc(m, &d_status, nitems * sizeof(int)));
     CUDA_OK(cudaMemsetAsync(d_status, 0, nitems * sizeof(int), s));
     CUDA_OK(cudaMemcpyAsync(d_items, items.data(), nitems * sizeof(TlItem), cudaMemcpyHostToDevice, s));
     CUDA_OK(cudaMemcpyAsync(d_g, gn, sizeof(gn), cudaMemcpyHostToDevice, s));
     if (coeff_T) {
-        CUDA_OK(cudaMalloc(&d_coeff, (size_t) nT * Np * KG_MAX_TERMS * sizeof(double)));
+        CUDA_OK(kg_dmalloc(m, &d_coeff, (size_t) nT * Np * KG_MAX_TERMS * sizeof(double)));
         CUDA_OK(cudaMemcpyAsync(d_coeff, coeff_T, (size_t) nT * Np * KG_MAX_TERMS * sizeof(double), cudaMemcpyHostToDevice, s));
     }
     const size_t smem = (size_t) KS_ROWS * (2 + m->ntpad) * sizeof(double);
@@ -274,7 +274,6 @@ extern "C" int kg_transfer_lengths_batch(kg_model* m, int nT, const double* T, c
         mtl[t * Np + p] = hm[p * nT + t]; etl[t * Np + p] = he[p * nT + t];
         if (status) status[t * Np + p] = hs[p * nT + t];
     }
-    cudaFree(d_items); cudaFree(d_g); cudaFree(d_ilim); cudaFree(d_bmid); cudaFree(d_bmax); cudaFree(d_fw); cudaFree(d_mtl); cudaFree(d_etl);
-    cudaFree(d_status); if (d_coeff) cudaFree(d_coeff);
+    for (void* q : {(void*) d_items, (void*) d_g, (void*) d_ilim, (void*) d_bmid, (void*) d_bmax, (void*) d_fw, (void*) d_mtl, (void*) d_etl, (void*) d_status, (void*) d_coeff}) m->dfree(q);
     return 0;
 }

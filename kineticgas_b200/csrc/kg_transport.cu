@@ -699,8 +699,8 @@ struct kg_tcache {
 
 namespace {
 
-template<class T> cudaError_t upload(T** dptr, const std::vector<T>& v) {
-    cudaError_t e = cudaMalloc(dptr, std::max<size_t>(1, v.size()) * sizeof(T));
+template<class T> cudaError_t upload(kg_model* m, T** dptr, const std::vector<T>& v) {
+    cudaError_t e = kg_dmalloc(m, dptr, std::max<size_t>(1, v.size()) * sizeof(T));
     if (e != cudaSuccess) return e;
     return cudaMemcpy(*dptr, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
 }
@@ -715,7 +715,7 @@ extern "C" void kg_tcache_destroy(kg_tcache* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     void* ptrs[] = {c->d_T, c->d_omega, c->d_mtl, c->d_etl, c->d_dbh, c->d_brk, c->d_mp_int};
-    for (void* p : ptrs) if (p) cudaFree(p);
+    for (void* p : ptrs) c->m->dfree(p);
     delete c;
 }
 
@@ -833,10 +833,10 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
     }
     int rc = 0;
 #define TC_CUDA(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { set_error(std::string(#expr) + ": " + cudaGetErrorString(e_)); kg_tcache_destroy(c); return -2; } } while (0)
-    TC_CUDA(upload(&c->d_T, c->T));
-    TC_CUDA(cudaMalloc(&c->d_omega, need.size() * sizeof(double)));
-    TC_CUDA(cudaMemset(c->d_omega, 0, need.size() * sizeof(double)));
+    TC_CUDA(upload(m, &c->d_T, c->T));
+    TC_CUDA(kg_dmalloc(m, &c->d_omega, need.size() * sizeof(double)));
     cudaStream_t s = m->stream;
+    TC_CUDA(cudaMemsetAsync(c->d_omega, 0, need.size() * sizeof(double), s));
     auto now = [] { return std::chrono::steady_clock::now(); };
     auto ms_since = [&](std::chrono::steady_clock::time_point t0) { return std::chrono::duration<double, std::milli>(now() - t0).count(); };
     auto t_stage = now();
@@ -867,17 +867,17 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
         for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) mp_int[i * nc + j] = mp_dev[tm.pair_of[i][j]];
         for (int i = 0; i < nc; i++) mp_diag[i] = mp_int[i * nc + i];
     }
-    TC_CUDA(upload(&c->d_mp_int, mp_int));
+    TC_CUDA(upload(m, &c->d_mp_int, mp_int));
     if (any_corr) {
         MiePair* d_mp = nullptr; int *d_pi = nullptr, *d_pj = nullptr, *d_l = nullptr, *d_r = nullptr; double* d_mass = nullptr; unsigned char* d_ic = nullptr;
         std::vector<int> ll(tm.lr_l, tm.lr_l + nlr), rr(tm.lr_r, tm.lr_r + nlr);
-        TC_CUDA(upload(&d_mp, mp_dev)); TC_CUDA(upload(&d_pi, pair_i)); TC_CUDA(upload(&d_pj, pair_j)); TC_CUDA(upload(&d_l, ll)); TC_CUDA(upload(&d_r, rr));
-        TC_CUDA(upload(&d_mass, m->mass)); TC_CUDA(upload(&d_ic, c->is_corr));
+        TC_CUDA(upload(m, &d_mp, mp_dev)); TC_CUDA(upload(m, &d_pi, pair_i)); TC_CUDA(upload(m, &d_pj, pair_j)); TC_CUDA(upload(m, &d_l, ll)); TC_CUDA(upload(m, &d_r, rr));
+        TC_CUDA(upload(m, &d_mass, m->mass)); TC_CUDA(upload(m, &d_ic, c->is_corr));
         const int tot = nT * Np * nlr;
         omega_correlation_kernel<<<(tot + 127) / 128, 128, 0, s>>>(nT, Np, nlr, c->d_T, d_mp, d_pi, d_pj, d_mass, d_l, d_r, d_ic, c->d_omega);
         TC_CUDA(cudaGetLastError());
         TC_CUDA(cudaStreamSynchronize(s));
-        cudaFree(d_mp); cudaFree(d_pi); cudaFree(d_pj); cudaFree(d_l); cudaFree(d_r); cudaFree(d_mass); cudaFree(d_ic);
+        for (void* q : {(void*) d_mp, (void*) d_pi, (void*) d_pj, (void*) d_l, (void*) d_r, (void*) d_mass, (void*) d_ic}) m->dfree(q);
     }
     if (!opts->is_idealgas) {
         c->h_mtl.resize((size_t) nT * Np); c->h_etl.resize((size_t) nT * Np);
@@ -888,24 +888,24 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
         if (bad & KG_STATUS_BMID) { set_error("Unable to converge bmid!"); kg_tcache_destroy(c); return -4; }
         if (bad & KG_STATUS_GETR_MAXITER) { set_error("get_R reached max iter!"); kg_tcache_destroy(c); return -4; }
         m->timings[2] = ms_since(t_stage); m->timings[4] += m->tl_launches;
-        TC_CUDA(upload(&c->d_mtl, c->h_mtl)); TC_CUDA(upload(&c->d_etl, c->h_etl));
+        TC_CUDA(upload(m, &c->d_mtl, c->h_mtl)); TC_CUDA(upload(m, &c->d_etl, c->h_etl));
         MiePair* d_diag = nullptr;
-        TC_CUDA(upload(&d_diag, mp_diag));
-        TC_CUDA(cudaMalloc(&c->d_dbh, (size_t) nT * nc * sizeof(double)));
+        TC_CUDA(upload(m, &d_diag, mp_diag));
+        TC_CUDA(kg_dmalloc(m, &c->d_dbh, (size_t) nT * nc * sizeof(double)));
         bh_kernel<<<(nT * nc + 127) / 128, 128, 0, s>>>(nT, nc, c->d_T, d_diag, c->d_dbh);
         TC_CUDA(cudaGetLastError());
         TC_CUDA(cudaStreamSynchronize(s));
-        cudaFree(d_diag);
+        m->dfree(d_diag);
     }
     {
         double *d_wA = nullptr, *d_wAp = nullptr, *d_wBp = nullptr, *d_wBpp = nullptr, *d_hpre = nullptr;
-        TC_CUDA(upload(&d_wA, wA)); TC_CUDA(upload(&d_wAp, wAp)); TC_CUDA(upload(&d_wBp, wBp)); TC_CUDA(upload(&d_wBpp, wBpp)); TC_CUDA(upload(&d_hpre, hpre));
+        TC_CUDA(upload(m, &d_wA, wA)); TC_CUDA(upload(m, &d_wAp, wAp)); TC_CUDA(upload(m, &d_wBp, wBp)); TC_CUDA(upload(m, &d_wBpp, wBpp)); TC_CUDA(upload(m, &d_hpre, hpre));
         const int per_t = nc * nc * N * N;
-        TC_CUDA(cudaMalloc(&c->d_brk, (size_t) nT * 4 * per_t * sizeof(double)));
+        TC_CUDA(kg_dmalloc(m, &c->d_brk, (size_t) nT * 4 * per_t * sizeof(double)));
         bracket_kernel<<<(nT * per_t + 127) / 128, 128, 0, s>>>(nT, tm, c->d_omega, d_wA, d_wAp, d_wBp, d_wBpp, d_hpre, c->d_brk);
         TC_CUDA(cudaGetLastError());
         TC_CUDA(cudaStreamSynchronize(s));
-        cudaFree(d_wA); cudaFree(d_wAp); cudaFree(d_wBp); cudaFree(d_wBpp); cudaFree(d_hpre);
+        for (void* q : {(void*) d_wA, (void*) d_wAp, (void*) d_wBp, (void*) d_wBpp, (void*) d_hpre}) m->dfree(q);
     }
 #undef TC_CUDA
     m->timings[3] = ms_since(t_stage) - m->timings[2];
@@ -917,9 +917,11 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
 namespace {
 
 struct DevBuf {      // scoped device allocations of one batch call
+    kg_model* m;
     std::vector<void*> ptrs;
-    ~DevBuf() { for (void* p : ptrs) cudaFree(p); }
-    template<class T> T* alloc(size_t n) { T* p = nullptr; if (cudaMalloc(&p, std::max<size_t>(1, n) * sizeof(T)) != cudaSuccess) return nullptr; ptrs.push_back(p); return p; }
+    explicit DevBuf(kg_model* model) : m(model) {}
+    ~DevBuf() { for (void* p : ptrs) m->dfree(p); }
+    template<class T> T* alloc(size_t n) { T* p = nullptr; if (kg_dmalloc(m, &p, std::max<size_t>(1, n) * sizeof(T)) != cudaSuccess) return nullptr; ptrs.push_back(p); return p; }
     template<class T> T* put(const T* h, size_t n, cudaStream_t s) {
         T* p = alloc<T>(n);
         if (p && h && cudaMemcpyAsync(p, h, n * sizeof(T), cudaMemcpyHostToDevice, s) != cudaSuccess) return nullptr;
@@ -981,7 +983,7 @@ extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const do
     cudaStream_t s = m->stream;
     std::vector<int> tidx(n);
     for (int k = 0; k < n; k++) { auto f = c->index_of.find(T[k]); tidx[k] = (f == c->index_of.end()) ? -1 : f->second; }
-    DevBuf db;
+    DevBuf db(m);
     StateArgs a; memset(&a, 0, sizeof(a));
     a.n = n; a.nT = c->nT; a.opt = *opts; a.opt.properties = props;
     a.nslots = (props & KG_PROP_CONDUCTIVITY) ? 2 : 1;
