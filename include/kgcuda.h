@@ -18,7 +18,14 @@ extern "C" {
  * (cpp/MieKinGas.h:16,26-42; cpp/ExtendedSutherland.h:124-128, ExtendedSutherland.cpp:113-119):
  *     u(r) = eps * sum_k C[k] * (sigma / r)^lam[k]
  * Mie: nterms = 2, C = {+C, -C}, lam = {lambda_r, lambda_a}. */
-typedef enum { KG_POT_POWER_SUM = 0 } kg_potential_kind;
+typedef enum {
+    KG_POT_POWER_SUM = 0,      /* Mie, Feynman-Hibbs Mie, extended Sutherland: kg_potential_desc below */
+    KG_POT_LJ_SPLINE = 1,      /* cpp/LJSpline.h:45-82        no parameters beyond sigma, eps */
+    KG_POT_LJTS = 2,           /* cpp/LJTS.h:28-60            truncated (2.5 sigma) and shifted LJ */
+    KG_POT_TANG_TOENNIES = 3,  /* cpp/multiparam.cpp:5-89     params {A, b, A_tilde, a_tilde, a1, a2, am1, am2, L_unit, short_range_lim, C6, C8, C10, C12, C14, C16} (TangToennisParam, energies in K) */
+    KG_POT_HFD_B2 = 4,         /* cpp/multiparam.cpp:91-182   params {A, alpha, c6, c8, c10, beta_star, D, rm[nm]} (HFD_B2_Param) */
+    KG_POT_PATKOWSKI = 5       /* cpp/multiparam.cpp:184-279  params {Rc, Ac, Bc, Cex1, Cex2, Csp1, Csp2, Csp3, Csp4, delta, C6, C8, C10} (PatowskiParam) */
+} kg_potential_kind;
 typedef struct {
     int32_t kind;        /* kg_potential_kind */
     int32_t nterms;      /* <= KG_MAX_TERMS */
@@ -27,6 +34,22 @@ typedef struct {
     double C[KG_MAX_TERMS];
     double lam[KG_MAX_TERMS];
 } kg_potential_desc;
+
+/* Per-pair block of the non-power-law potentials (kinds 1-5). sigma/eps are Spherical::sigma / eps of the pair (the
+ * length and energy scales of the reduced (g, b) lattice). fh_order > 0 adds the Feynman-Hibbs correction of
+ * FH_Corrected<T> (cpp/extentions.h:228-273) with fh_D = hbar^2 / (24 mu_ij) [J m^2] (set_D_factors, :308-314); the
+ * T-dependent effective potential is rebuilt inside the library for every temperature of a batch. */
+#define KG_MAX_POT_PARAMS 24
+typedef struct {
+    int32_t kind;        /* kg_potential_kind, 1..5 */
+    int32_t fh_order;    /* 0, 1 or 2 */
+    double sigma;        /* m */
+    double eps;          /* J */
+    double fh_D;         /* J m^2; ignored when fh_order == 0 */
+    int32_t nparams;
+    int32_t reserved;
+    double params[KG_MAX_POT_PARAMS];
+} kg_potential_desc_ex;
 
 /* Per-work-item status bits (mirror the reference's throw sites) */
 #define KG_STATUS_OK            0
@@ -42,6 +65,14 @@ typedef struct kg_omega_plan kg_omega_plan;
  * (0,0),(0,1),..,(0,nc-1),(1,1),.. ; for is_singlecomp models pass ncomps = 1 (cpp/Spherical.cpp:38-40 forces i=j=0).
  * mass: particle masses [kg], length ncomps. device: CUDA ordinal. */
 int kg_model_create(const kg_potential_desc* pairs, int ncomps, const double* mass, int is_singlecomp, int device, kg_model** out);
+/* Same for models built on kg_potential_desc_ex blocks: LJSpline, LJTS, ModTangToennis, HFD_B2, Patowski and their
+ * FH_Corrected variants (cpp/multiparam.h:36-131; Quantum::omega forwards to Spherical::omega for them,
+ * cpp/Quantum.cpp:1261-1268). Every entry point below accepts such a model; coeff / coeff_T arguments are ignored. */
+int kg_model_create_ex(const kg_potential_desc_ex* pairs, int ncomps, const double* mass, int is_singlecomp, int device, kg_model** out);
+/* Host-only: the piecewise polynomial-times-exponential form of one potential block at temperature T as the device will
+ * evaluate it (layout: struct GenPot of kineticgas_b200/csrc/kg_genpot.h, as raw doubles). Returns the number of doubles
+ * written, or minus the required capacity. Used by the CPU tests to pin the Feynman-Hibbs folding. */
+int kg_genpot_describe(const kg_potential_desc_ex* d, double T, double* out, int cap_doubles);
 void kg_model_destroy(kg_model* m);
 const char* kg_last_error(const kg_model* m);   /* m may be NULL: error of the last failed create */
 int kg_model_npairs(const kg_model* m);
@@ -54,6 +85,9 @@ int kg_model_set_stream(kg_model* m, void* cuda_stream);
  * coeff (optional, nterms doubles) overrides C[] for this call (T-dependent effective coefficients). */
 int kg_chi_points(kg_model* m, int pair, double T, int n, const double* g, const double* b_red,
                   const double* coeff, double* chi_out, double* R_out, int32_t* status);
+/* Replaces Spherical::potential / potential_derivative_r (cpp/bindings.cpp:187-189) for n radii r [m] at temperature T
+ * (T matters for Feynman-Hibbs corrected models only): u [J], du/dr [J/m]. Either output may be NULL. */
+int kg_potential_points(kg_model* m, int pair, double T, int n, const double* r, double* u_out, double* du_out);
 
 /* Replaces the omega fan-out KineticGas::precompute_omega / precompute_conductivity / precompute_viscosity
  * (cpp/KineticGas_mthr.cpp:40-46,58-143) plus Spherical::omega -> w_integral (cpp/Spherical.cpp:37-94):

@@ -14,6 +14,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include "kg_genpot.h"
 
 namespace kg {
 
@@ -30,6 +31,7 @@ struct PairParams {                 // staged in shared memory per CTA
     int nterms, ntpad;              // ntpad in {2,4,6}: row width = 2 + ntpad doubles
     double C[MAX_TERMS];
     double lam[MAX_TERMS];
+    const GenPot* gen;              // device pointer: non-power-law potential of this pair (ntpad == 1), else null
 };
 
 // Per-lane collision context in reduced units (lengths / sigma)
@@ -39,6 +41,56 @@ struct Lane {
     double lam[NT];
     double b;          // impact parameter / sigma
 };
+
+// NT == 1 is the tag of the generic (piecewise polynomial x exponential) potentials: node rows { w/2u, 1/u^2, 1/u }
+template<>
+struct Lane<1> {
+    const GenPot* gp;
+    double invE;       // 1 / (kT g^2)
+    double b;
+};
+
+__device__ __forceinline__ double ipow_pos(double x, int n) {      // x^n, n >= 0, by squaring
+    double r = 1.0;
+    while (n) { if (n & 1) r *= x; x *= x; n >>= 1; }
+    return r;
+}
+
+// sum_{k<n} c[k] r^(kmin+k) ; s = 1/r. Horner runs in the variable that is <= 1 so no partial sum overflows.
+__device__ __forceinline__ double laurent(const double* __restrict__ c, int kmin, int n, double r, double s) {
+    if (n <= 0) return 0.0;
+    double acc; int e;
+    if (r >= 1.0) {
+        acc = c[0];
+        for (int k = 1; k < n; k++) acc = fma(acc, s, c[k]);
+        e = kmin + n - 1;
+    } else {
+        acc = c[n - 1];
+        for (int k = n - 2; k >= 0; k--) acc = fma(acc, r, c[k]);
+        e = kmin;
+    }
+    return acc * (e >= 0 ? ipow_pos(r, e) : ipow_pos(s, -e));
+}
+
+// u(r) and du/d(r/sigma) in J of a generic potential at r = ri sigma
+static __device__ __noinline__ void gen_eval(const GenPot* __restrict__ gp, double ri, int want_d, double& U, double& dU) {
+    const double r = ri * gp->len_scale;
+    int p = 0;
+    while (p < gp->npieces && !(r < gp->piece[p].r_hi)) p++;
+    U = 0.0; dU = 0.0;
+    if (p == gp->npieces) return;
+    const GenPiece& pc = gp->piece[p];
+    const double s = 1.0 / r;
+    double u = 0.0, du = 0.0;
+    for (int t = 0; t < pc.nterms; t++) {
+        const GenTerm& tm = pc.t[t];
+        const double E = tm.qn > 0 ? exp(laurent(tm.qc, tm.qmin, tm.qn, r, s)) : 1.0;
+        u = fma(laurent(tm.pc, tm.pmin, tm.pn, r, s), E, u);
+        if (want_d) du = fma(laurent(tm.dc, tm.dmin, tm.dn, r, s), E, du);
+    }
+    U = u * gp->e_scale;
+    dU = du * (gp->e_scale * gp->len_scale);
+}
 
 // u(r)/(kT g^2) and sigma u'(r)/(kT g^2) at r = ri sigma, sharing one log: s^lam = exp(lam ln s)
 template<int NT>
@@ -54,6 +106,11 @@ __device__ __forceinline__ void pot_eval(const Lane<NT>& c, double ri, double& U
     }
     U = u;
     dU = du * inv;
+}
+template<>
+__device__ __forceinline__ void pot_eval<1>(const Lane<1>& c, double ri, double& U, double& dU) {
+    gen_eval(c.gp, ri, 1, U, dU);
+    U *= c.invE; dU *= c.invE;
 }
 
 template<int NT>
@@ -284,12 +341,9 @@ __device__ double theta_integral(const double* __restrict__ srows, const double*
     return I;
 }
 
-// Full single-lane evaluation of the theta integral for (g, b): R, A_t, c2, then the sum. Returns I; R_out in sigma.
+// Lane set-up shared by every caller: Bt = eps C_t / (kT g^2) (coeff overrides C[] for T-dependent potentials)
 template<int NT>
-__device__ double lane_theta_integral(const PairParams& pp, const double* coeff, const double* __restrict__ srows,
-                                      const double* __restrict__ grows, int KS, double T, double g, double b,
-                                      double& R_out, unsigned& nodes, int& status) {
-    Lane<NT> c;
+__device__ __forceinline__ void make_lane(Lane<NT>& c, const PairParams& pp, const double* coeff, double T, double g, double b) {
     const double E = BOLTZMANN * T * (g * g);
 #pragma unroll
     for (int t = 0; t < NT; t++) {
@@ -298,6 +352,61 @@ __device__ double lane_theta_integral(const PairParams& pp, const double* coeff,
         c.lam[t] = (t < pp.nterms) ? pp.lam[t] : 1.0;
     }
     c.b = b;
+}
+template<>
+__device__ __forceinline__ void make_lane<1>(Lane<1>& c, const PairParams& pp, const double* coeff, double T, double g, double b) {
+    c.gp = coeff ? reinterpret_cast<const GenPot*>(coeff) : pp.gen;     // per-T effective potential (Feynman-Hibbs) or the base one
+    c.invE = 1.0 / (BOLTZMANN * T * (g * g));
+    c.b = b;
+}
+
+// get_R for a caller that has no lane yet (the chi short-cuts b < 1e-3 still need R for the transfer lengths)
+template<int NT>
+__device__ double lane_get_R(const PairParams& pp, const double* coeff, double T, double g, double b, int& status) {
+    Lane<NT> c;
+    make_lane<NT>(c, pp, coeff, T, g, b);
+    return get_R<NT>(c, g, status);
+}
+
+// Generic potentials: the reference's loop node for node (cpp/Integration/Integration.cpp:417-437) with
+// f(u) = (R/u^2) [ r^4/b^2 (1 - u(r)/(kT g^2)) - r^2 ]^(-1/2) = (1/u) X^(-1/2), X = (R/b)^2 (1/u^2) (1 - U) - 1, r = R/u.
+static __device__ double theta_integral_gen(const double* __restrict__ srows, const double* __restrict__ grows, int KS,
+                                     const Lane<1>& c, double R, unsigned& nodes, int& status) {
+    const double q = R / c.b, c2 = q * q;
+    const int zero_neg = c.gp->zero_on_negative;
+    auto term = [&](int k, bool& bad) {
+        const double* __restrict__ row = ((k <= KS) ? srows : grows) + (size_t) (k - 1) * 3;
+        double U, dU;
+        gen_eval(c.gp, R * row[2], 0, U, dU);
+        const double X = fma(row[1], c2 * (1.0 - U * c.invE), -1.0);
+        if (zero_neg && X < 0) { bad = false; return 0.0; }          // cpp/LJSpline.h:40
+        const double f = (row[0] + row[0]) / sqrt(X);
+        bad = isnan(f) || isinf(f);
+        return f;
+    };
+    bool bad;
+    double t = term(1, bad);
+    double I = 0.0;
+    int k = 1;
+    for (;;) {
+        I += t;                                           // Integration.cpp:425 (k = 1 unconditionally), :431
+        k += 1;
+        if (k > KMAX) { status |= 2; break; }
+        t = term(k, bad);
+        if (bad) break;                                   // Integration.cpp:430
+        if (!(fabs(t) > fabs(TS_TOL * I))) break;         // Integration.cpp:431
+    }
+    nodes += (unsigned) k;
+    return I;
+}
+
+// Full single-lane evaluation of the theta integral for (g, b): R, A_t, c2, then the sum. Returns I; R_out in sigma.
+template<int NT>
+__device__ double lane_theta_integral(const PairParams& pp, const double* coeff, const double* __restrict__ srows,
+                                      const double* __restrict__ grows, int KS, double T, double g, double b,
+                                      double& R_out, unsigned& nodes, int& status) {
+    Lane<NT> c;
+    make_lane<NT>(c, pp, coeff, T, g, b);
     const double R = get_R<NT>(c, g, status);
     R_out = R;
     double A[NT];
@@ -306,6 +415,16 @@ __device__ double lane_theta_integral(const PairParams& pp, const double* coeff,
     for (int t = 0; t < NT; t++) A[t] = c.Bt[t] * pow(s, c.lam[t]);
     const double q = R / b;
     return theta_integral<NT>(srows, grows, KS, A, q * q, nodes, status);
+}
+template<>
+__device__ inline double lane_theta_integral<1>(const PairParams& pp, const double* coeff, const double* __restrict__ srows,
+                                                const double* __restrict__ grows, int KS, double T, double g, double b,
+                                                double& R_out, unsigned& nodes, int& status) {
+    Lane<1> c;
+    make_lane<1>(c, pp, coeff, T, g, b);
+    const double R = get_R<1>(c, g, status);
+    R_out = R;
+    return theta_integral_gen(srows, grows, KS, c, R, nodes, status);
 }
 
 } // namespace kg

@@ -16,6 +16,11 @@ struct kg_model {
     std::vector<double> mass;
     std::vector<kg_potential_desc> descs;
     std::vector<kg::PairParams> pairs;
+    // generic (non-power-law) models: ntpad == 1, node rows { w/2u, 1/u^2, 1/u }
+    bool generic = false, gen_T_dependent = false;
+    std::vector<kg_potential_desc_ex> gdescs;
+    kg::GenPot* d_gpots = nullptr;      // base potentials, one per pair
+    int coeff_stride = KG_MAX_TERMS;    // doubles per (T, pair) block of a coefficient pool (GP_DOUBLES for generic models)
     std::vector<double*> d_rows;        // per pair: [KMAX][2+ntpad]
     double** d_rows_by_pair = nullptr;
     kg::PairParams* d_pairs = nullptr;
@@ -63,6 +68,12 @@ struct kg_model {
         pool_free.clear(); pool_cached = 0;
     }
 };
+
+// kg_genpot.cu: effective (Feynman-Hibbs folded) generic potential of one pair at temperature T
+int kg_genpot_build(const kg_potential_desc_ex& d, double T, kg::GenPot& out, std::string& err);
+// Per-(T, pair) coefficient pool of a batch: the caller's coeff_T for power-sum models, the folded potentials for
+// T-dependent generic models (built into buf), NULL otherwise. Layout [nT][npairs][m->coeff_stride].
+int kg_effective_coeff(kg_model* m, int nT, const double* T, const double* coeff_T_user, std::vector<double>& buf, const double** out);
 
 template<class T> inline cudaError_t kg_dmalloc(kg_model* m, T** out, size_t bytes) { return m->dmalloc_bytes((void**) out, bytes); }
 

@@ -446,15 +446,7 @@ __global__ void __launch_bounds__(256) chi_points_kernel(PairParams pp, const do
     }
     if (bi <= 100 && bi < 1e-3 && R_out) {
         // get_R is still defined there (used by the transfer-length integrals)
-        Lane<NT> c;
-        const double E = BOLTZMANN * T * (gi * gi);
-#pragma unroll
-        for (int t = 0; t < NT; t++) {
-            c.Bt[t] = (t < pp.nterms) ? pp.eps * (coeff ? coeff[t] : pp.C[t]) / E : 0.0;
-            c.lam[t] = (t < pp.nterms) ? pp.lam[t] : 1.0;
-        }
-        c.b = bi;
-        R = get_R<NT>(c, gi, st);
+        R = lane_get_R<NT>(pp, coeff, T, gi, bi, st);
     }
     if (chi_out) chi_out[e] = chi;
     if (R_out) R_out[e] = R;
@@ -517,7 +509,8 @@ void build_rows(const kg_potential_desc& d, int ntpad, std::vector<double>& rows
         double* r = &rows[(size_t) (k - 1) * W];
         r[0] = 0.5 * (w / u);       // halved: the fast node form carries the factor 2 in its Newton step (kg_device.cuh)
         r[1] = 1.0 / (u * u);
-        for (int t = 0; t < ntpad; t++) r[2 + t] = (t < d.nterms) ? pow(u, d.lam[t]) : 0.0;
+        if (ntpad == 1) r[2] = 1.0 / u;      // generic potentials evaluate u(r) at r = R / u
+        else for (int t = 0; t < ntpad; t++) r[2 + t] = (t < d.nterms) ? pow(u, d.lam[t]) : 0.0;
     }
 }
 
@@ -533,35 +526,30 @@ template<int NT> cudaError_t set_theta_smem() {
 extern "C" const char* kg_last_error(const kg_model* m) { return m ? m->err.c_str() : g_create_error.c_str(); }
 extern "C" int kg_model_npairs(const kg_model* m) { return m ? m->npairs : -1; }
 
-extern "C" int kg_model_create(const kg_potential_desc* pairs, int ncomps, const double* mass, int is_singlecomp, int device, kg_model** out) {
-    auto fail = [&](const std::string& s) { g_create_error = s; return -1; };
-    if (!pairs || !mass || !out || ncomps < 1) return fail("kg_model_create: invalid argument");
-    int ndev = 0;
-    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail("kg_model_create: no CUDA device (the GPU path has no CPU fallback)");
-    if (device < 0 || device >= ndev) return fail("kg_model_create: bad device ordinal");
-    kg_model* m = new kg_model;
-    m->device = device; m->ncomps = ncomps; m->npairs = ncomps * (ncomps + 1) / 2; m->is_singlecomp = is_singlecomp;
-    m->mass.assign(mass, mass + ncomps);
-    m->descs.assign(pairs, pairs + m->npairs);
-    int ntmax = 0;
-    for (auto& d : m->descs) {
-        if (d.kind != KG_POT_POWER_SUM || d.nterms < 1 || d.nterms > KG_MAX_TERMS) { delete m; return fail("kg_model_create: unsupported potential block"); }
-        ntmax = std::max(ntmax, d.nterms);
-    }
-    m->ntpad = ntmax <= 2 ? 2 : ntmax <= 4 ? 4 : 6;
+namespace {
+// device resources shared by both constructors: stream, node-row tables, pair blocks
+int finish_model(kg_model* m, int device, kg_model** out) {
     auto cu = [&](cudaError_t e, const char* what) { if (e != cudaSuccess) { g_create_error = std::string(what) + ": " + cudaGetErrorString(e); return false; } return true; };
     if (!cu(cudaSetDevice(device), "cudaSetDevice")) { delete m; return -2; }
     cudaDeviceProp prop;
     if (!cu(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties")) { delete m; return -2; }
     m->sm_count = prop.multiProcessorCount;
     if (!cu(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking), "cudaStreamCreate")) { delete m; return -2; }
-    bool ok = cu(set_theta_smem<2>(), "smem attr") && cu(set_theta_smem<4>(), "smem attr") && cu(set_theta_smem<6>(), "smem attr");
+    bool ok = cu(set_theta_smem<1>(), "smem attr") && cu(set_theta_smem<2>(), "smem attr") && cu(set_theta_smem<4>(), "smem attr") && cu(set_theta_smem<6>(), "smem attr");
+    if (ok && m->generic) {
+        std::vector<GenPot> base(m->npairs);
+        for (int p = 0; ok && p < m->npairs; p++)
+            if (kg_genpot_build(m->gdescs[p], 300.0, base[p], g_create_error)) ok = false;     // T only matters when fh_order > 0 (then per-T pools are used)
+        ok = ok && cu(cudaMalloc(&m->d_gpots, m->npairs * sizeof(GenPot)), "cudaMalloc") &&
+             cu(cudaMemcpy(m->d_gpots, base.data(), m->npairs * sizeof(GenPot), cudaMemcpyHostToDevice), "H2D");
+    }
     std::vector<double> rows;
     for (int p = 0; ok && p < m->npairs; p++) {
         const auto& d = m->descs[p];
         PairParams pp; memset(&pp, 0, sizeof(pp));
         pp.sigma = d.sigma; pp.eps = d.eps; pp.nterms = d.nterms; pp.ntpad = m->ntpad;
         for (int t = 0; t < d.nterms; t++) { pp.C[t] = d.C[t]; pp.lam[t] = d.lam[t]; }
+        if (m->generic) pp.gen = m->d_gpots + p;
         m->pairs.push_back(pp);
         build_rows(d, m->ntpad, rows);
         double* dptr = nullptr;
@@ -577,6 +565,51 @@ extern "C" int kg_model_create(const kg_potential_desc* pairs, int ncomps, const
     *out = m;
     return 0;
 }
+int check_device(int device) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { g_create_error = "kg_model_create: no CUDA device (the GPU path has no CPU fallback)"; return -1; }
+    if (device < 0 || device >= ndev) { g_create_error = "kg_model_create: bad device ordinal"; return -1; }
+    return 0;
+}
+} // namespace
+
+extern "C" int kg_model_create(const kg_potential_desc* pairs, int ncomps, const double* mass, int is_singlecomp, int device, kg_model** out) {
+    auto fail = [&](const std::string& s) { g_create_error = s; return -1; };
+    if (!pairs || !mass || !out || ncomps < 1) return fail("kg_model_create: invalid argument");
+    if (check_device(device)) return -1;
+    kg_model* m = new kg_model;
+    m->device = device; m->ncomps = ncomps; m->npairs = ncomps * (ncomps + 1) / 2; m->is_singlecomp = is_singlecomp;
+    m->mass.assign(mass, mass + ncomps);
+    m->descs.assign(pairs, pairs + m->npairs);
+    int ntmax = 0;
+    for (auto& d : m->descs) {
+        if (d.kind != KG_POT_POWER_SUM || d.nterms < 1 || d.nterms > KG_MAX_TERMS) { delete m; return fail("kg_model_create: unsupported potential block"); }
+        ntmax = std::max(ntmax, d.nterms);
+    }
+    m->ntpad = ntmax <= 2 ? 2 : ntmax <= 4 ? 4 : 6;
+    return finish_model(m, device, out);
+}
+
+extern "C" int kg_model_create_ex(const kg_potential_desc_ex* pairs, int ncomps, const double* mass, int is_singlecomp, int device, kg_model** out) {
+    auto fail = [&](const std::string& s) { g_create_error = s; return -1; };
+    if (!pairs || !mass || !out || ncomps < 1) return fail("kg_model_create_ex: invalid argument");
+    if (check_device(device)) return -1;
+    kg_model* m = new kg_model;
+    m->device = device; m->ncomps = ncomps; m->npairs = ncomps * (ncomps + 1) / 2; m->is_singlecomp = is_singlecomp;
+    m->mass.assign(mass, mass + ncomps);
+    m->generic = true; m->ntpad = 1; m->coeff_stride = GP_DOUBLES;
+    m->gdescs.assign(pairs, pairs + m->npairs);
+    for (auto& g : m->gdescs) {
+        if (g.kind < KG_POT_LJ_SPLINE || g.kind > KG_POT_PATKOWSKI || !(g.sigma > 0) || !(g.eps > 0) || g.nparams < 0 || g.nparams > KG_MAX_POT_PARAMS) { delete m; return fail("kg_model_create_ex: unsupported potential block"); }
+        if (g.fh_order > 0) { m->gen_T_dependent = true; if (!(g.fh_D > 0)) { delete m; return fail("kg_model_create_ex: fh_order > 0 needs fh_D > 0"); } }
+        GenPot probe;
+        if (kg_genpot_build(g, 300.0, probe, g_create_error)) { delete m; return -1; }
+        kg_potential_desc d; memset(&d, 0, sizeof(d));       // sigma / eps for the Omega prefactors and the TL scaling
+        d.kind = g.kind; d.sigma = g.sigma; d.eps = g.eps;
+        m->descs.push_back(d);
+    }
+    return finish_model(m, device, out);
+}
 
 extern "C" void kg_model_destroy(kg_model* m) {
     if (!m) return;
@@ -584,6 +617,7 @@ extern "C" void kg_model_destroy(kg_model* m) {
     for (double* p : m->d_rows) cudaFree(p);
     if (m->d_rows_by_pair) cudaFree(m->d_rows_by_pair);
     if (m->d_pairs) cudaFree(m->d_pairs);
+    if (m->d_gpots) cudaFree(m->d_gpots);
     if (m->stream) cudaStreamSynchronize(m->stream);
     m->pool_release();
     for (auto& kv : m->pool_live) cudaFree(kv.first);
@@ -614,7 +648,14 @@ extern "C" int kg_chi_points(kg_model* m, int pair, double T, int n, const doubl
     CUDA_OK(kg_dmalloc(m, &dst, n * sizeof(int)));
     CUDA_OK(cudaMemcpyAsync(dg, g, n * sizeof(double), cudaMemcpyHostToDevice, m->stream));
     CUDA_OK(cudaMemcpyAsync(db, b_red, n * sizeof(double), cudaMemcpyHostToDevice, m->stream));
-    if (coeff) {
+    GenPot gp_T;
+    if (m->generic) {
+        if (m->gen_T_dependent) {          // Feynman-Hibbs corrected: the effective potential of this temperature
+            if (kg_genpot_build(m->gdescs[pair], T, gp_T, m->err)) return -1;
+            CUDA_OK(kg_dmalloc(m, &dcoef, sizeof(GenPot)));
+            CUDA_OK(cudaMemcpyAsync(dcoef, &gp_T, sizeof(GenPot), cudaMemcpyHostToDevice, m->stream));
+        }
+    } else if (coeff) {
         CUDA_OK(kg_dmalloc(m, &dcoef, KG_MAX_TERMS * sizeof(double)));
         CUDA_OK(cudaMemcpyAsync(dcoef, coeff, m->descs[pair].nterms * sizeof(double), cudaMemcpyHostToDevice, m->stream));
     }
@@ -622,6 +663,7 @@ extern "C" int kg_chi_points(kg_model* m, int pair, double T, int n, const doubl
     const size_t smem = (size_t) KS_ROWS * W * sizeof(double);
     const int grid = (n + 255) / 256;
     switch (m->ntpad) {
+        case 1: chi_points_kernel<1><<<grid, 256, smem, m->stream>>>(m->pairs[pair], m->d_rows[pair], dcoef, T, n, dg, db, dchi, dR, dst); break;
         case 2: chi_points_kernel<2><<<grid, 256, smem, m->stream>>>(m->pairs[pair], m->d_rows[pair], dcoef, T, n, dg, db, dchi, dR, dst); break;
         case 4: chi_points_kernel<4><<<grid, 256, smem, m->stream>>>(m->pairs[pair], m->d_rows[pair], dcoef, T, n, dg, db, dchi, dR, dst); break;
         default: chi_points_kernel<6><<<grid, 256, smem, m->stream>>>(m->pairs[pair], m->d_rows[pair], dcoef, T, n, dg, db, dchi, dR, dst); break;
@@ -632,6 +674,66 @@ extern "C" int kg_chi_points(kg_model* m, int pair, double T, int n, const doubl
     if (status) CUDA_OK(cudaMemcpyAsync(status, dst, n * sizeof(int), cudaMemcpyDeviceToHost, m->stream));
     CUDA_OK(cudaStreamSynchronize(m->stream));
     m->dfree(dg); m->dfree(db); m->dfree(dchi); m->dfree(dR); m->dfree(dst); m->dfree(dcoef);
+    return 0;
+}
+
+int kg_effective_coeff(kg_model* m, int nT, const double* T, const double* coeff_T_user, std::vector<double>& buf, const double** out) {
+    if (!m->generic) { *out = coeff_T_user; return 0; }
+    *out = nullptr;
+    if (!m->gen_T_dependent) return 0;
+    if ((long long) nT * m->npairs * GP_DOUBLES >= (1LL << 31)) { m->err = "generic potential: batch too large, split the T grid"; return -1; }
+    buf.resize((size_t) nT * m->npairs * GP_DOUBLES);
+    for (int t = 0; t < nT; t++) for (int p = 0; p < m->npairs; p++) {
+        GenPot gp;
+        if (kg_genpot_build(m->gdescs[p], T[t], gp, m->err)) return -1;
+        memcpy(&buf[((size_t) t * m->npairs + p) * GP_DOUBLES], &gp, sizeof(GenPot));
+    }
+    *out = buf.data();
+    return 0;
+}
+
+namespace {
+template<int NT>
+__global__ void potential_points_kernel(PairParams pp, const double* __restrict__ coeff, int n, const double* __restrict__ r,
+                                        double* __restrict__ u_out, double* __restrict__ du_out) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    Lane<NT> c;
+    make_lane<NT>(c, pp, coeff, 1.0 / BOLTZMANN, 1.0, 1.0);      // kT g^2 = 1: pot_eval returns joules
+    double U, dU;
+    pot_eval<NT>(c, r[e] / pp.sigma, U, dU);
+    if (u_out) u_out[e] = U;
+    if (du_out) du_out[e] = dU / pp.sigma;
+}
+}
+
+extern "C" int kg_potential_points(kg_model* m, int pair, double T, int n, const double* r, double* u_out, double* du_out) {
+    if (!m) return -1;
+    auto set_error = [&](const std::string& s) { m->err = s; };
+    if (pair < 0 || pair >= m->npairs || n < 0 || !r) { set_error("kg_potential_points: invalid argument"); return -1; }
+    if (n == 0) return 0;
+    CUDA_OK(cudaSetDevice(m->device));
+    double *dr = nullptr, *du = nullptr, *ddu = nullptr, *dcoef = nullptr;
+    CUDA_OK(kg_dmalloc(m, &dr, n * sizeof(double))); CUDA_OK(kg_dmalloc(m, &du, n * sizeof(double))); CUDA_OK(kg_dmalloc(m, &ddu, n * sizeof(double)));
+    CUDA_OK(cudaMemcpyAsync(dr, r, n * sizeof(double), cudaMemcpyHostToDevice, m->stream));
+    GenPot gp_T;
+    if (m->generic && m->gen_T_dependent) {
+        if (kg_genpot_build(m->gdescs[pair], T, gp_T, m->err)) return -1;
+        CUDA_OK(kg_dmalloc(m, &dcoef, sizeof(GenPot)));
+        CUDA_OK(cudaMemcpyAsync(dcoef, &gp_T, sizeof(GenPot), cudaMemcpyHostToDevice, m->stream));
+    }
+    const int grid = (n + 127) / 128;
+    switch (m->ntpad) {
+        case 1: potential_points_kernel<1><<<grid, 128, 0, m->stream>>>(m->pairs[pair], dcoef, n, dr, du, ddu); break;
+        case 2: potential_points_kernel<2><<<grid, 128, 0, m->stream>>>(m->pairs[pair], dcoef, n, dr, du, ddu); break;
+        case 4: potential_points_kernel<4><<<grid, 128, 0, m->stream>>>(m->pairs[pair], dcoef, n, dr, du, ddu); break;
+        default: potential_points_kernel<6><<<grid, 128, 0, m->stream>>>(m->pairs[pair], dcoef, n, dr, du, ddu); break;
+    }
+    CUDA_OK(cudaGetLastError());
+    if (u_out) CUDA_OK(cudaMemcpyAsync(u_out, du, n * sizeof(double), cudaMemcpyDeviceToHost, m->stream));
+    if (du_out) CUDA_OK(cudaMemcpyAsync(du_out, ddu, n * sizeof(double), cudaMemcpyDeviceToHost, m->stream));
+    CUDA_OK(cudaStreamSynchronize(m->stream));
+    m->dfree(dr); m->dfree(du); m->dfree(ddu); m->dfree(dcoef);
     return 0;
 }
 
@@ -689,6 +791,8 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
     if (!m) return -1;
     auto set_error = [&](const std::string& s) { m->err = s; };
     if (nT < 1 || !T || nlr < 1 || !l || !r || !out) { set_error("kg_omega_plan_create: invalid argument"); return -1; }
+    std::vector<double> coeff_buf;
+    if (kg_effective_coeff(m, nT, T, coeff_T, coeff_buf, &coeff_T)) return -1;
     for (int i = 0; i < nlr; i++) if (l[i] < 1 || l[i] > 12 || r[i] < 0 || r[i] > 24) { set_error("kg_omega_plan_create: (l,r) out of range"); return -1; }
     for (int i = 0; i < nT; i++) if (!(T[i] > 0) || !std::isfinite(T[i])) { set_error("kg_omega_plan_create: temperatures must be positive and finite"); return -1; }
     CUDA_OK(cudaSetDevice(m->device));
@@ -737,7 +841,7 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
                 p->cell_cap += (long long) rg.Nx_end * rg.Ny_end * 5 / 4 + 64;
                 p->cell_cap_limit += (long long) nact * rg.Nx_end * rg.Ny_end + 64;
             }
-            it.coeff_off = coeff_T ? (t * Np + pi) * KG_MAX_TERMS : -1;
+            it.coeff_off = coeff_T ? (t * Np + pi) * m->coeff_stride : -1;
             p->items.push_back(it);
             perm.push_back(t * Np + pi);
         }
@@ -823,8 +927,8 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
     PLAN_CUDA(kg_dmalloc(m, &p->d_counters, 8 * sizeof(unsigned long long)));
     p->h_pinned = m->h_pinned;
     if (coeff_T) {
-        PLAN_CUDA(kg_dmalloc(m, &p->d_coeff, (size_t) nT * Np * KG_MAX_TERMS * sizeof(double)));
-        PLAN_CUDA(cudaMemcpy(p->d_coeff, coeff_T, (size_t) nT * Np * KG_MAX_TERMS * sizeof(double), cudaMemcpyHostToDevice));
+        PLAN_CUDA(kg_dmalloc(m, &p->d_coeff, (size_t) nT * Np * m->coeff_stride * sizeof(double)));
+        PLAN_CUDA(cudaMemcpy(p->d_coeff, coeff_T, (size_t) nT * Np * m->coeff_stride * sizeof(double), cudaMemcpyHostToDevice));
     }
     PLAN_CUDA(cudaMemcpy(p->d_items, p->items.data(), p->nitems * sizeof(Item), cudaMemcpyHostToDevice));
     PLAN_CUDA(cudaMemcpy(p->d_regimes, regs, sizeof(regs), cudaMemcpyHostToDevice));
@@ -835,7 +939,7 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
     PLAN_CUDA(cudaMemcpy(p->d_perm, perm.data(), p->nitems * sizeof(int), cudaMemcpyHostToDevice));
     for (int k = 0; k < 4; k++) PLAN_CUDA(cudaEventCreate(&p->ev[k]));
     p->h2d_bytes = (long long) p->nitems * sizeof(Item) + sizeof(regs) + (long long) p->ntasks * sizeof(int2) + gfac.size() * sizeof(double)
-                 + 2LL * nlr * sizeof(int) + (long long) p->nitems * sizeof(int) + (coeff_T ? (long long) nT * Np * KG_MAX_TERMS * sizeof(double) : 0);
+                 + 2LL * nlr * sizeof(int) + (long long) p->nitems * sizeof(int) + (coeff_T ? (long long) nT * Np * m->coeff_stride * sizeof(double) : 0);
 #undef PLAN_CUDA
     *out = p;
     return 0;
@@ -897,7 +1001,7 @@ extern "C" int kg_omega_plan_run(kg_omega_plan* p) {
             CUDA_OK(cudaEventRecord(p->ev[2], s));
 #define LAUNCH_THETA(NT) theta_kernel<NT><<<grid, THETA_THREADS, smem, s>>>(p->d_items, p->d_regimes, m->d_pairs, m->d_rows_by_pair, p->d_coeff, \
                 p->d_list, p->d_offsets, p->d_pair_task_start, m->npairs, p->d_tile_counter, p->d_tab, p->d_lim, p->d_status, p->d_counters)
-            switch (m->ntpad) { case 2: LAUNCH_THETA(2); break; case 4: LAUNCH_THETA(4); break; default: LAUNCH_THETA(6); break; }
+            switch (m->ntpad) { case 1: LAUNCH_THETA(1); break; case 2: LAUNCH_THETA(2); break; case 4: LAUNCH_THETA(4); break; default: LAUNCH_THETA(6); break; }
 #undef LAUNCH_THETA
             CUDA_OK(cudaEventRecord(p->ev[3], s));
             finalize_kernel<<<(nlist + 255) / 256, 256, 0, s>>>(p->d_items, p->d_regimes, p->d_list, p->d_offsets + p->ntasks, p->d_tab, p->d_lim,

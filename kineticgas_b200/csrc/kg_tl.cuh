@@ -132,15 +132,7 @@ __global__ void __launch_bounds__(256) tl_node_kernel(const PairParams* __restri
         int st = 0; unsigned nodes = 0; double R = 0.0;
         const double chi = chi_with_lim<NT>(pp, coeff, srows, rows, T, g, b, ilim[o], R, nodes, st);
         if (b < 1e-3 || b > 100) {        // chi short-cuts do not compute R; the integrand's func(b) = get_R still needs it
-            Lane<NT> c;
-            const double E = BOLTZMANN * T * (g * g);
-#pragma unroll
-            for (int t = 0; t < NT; t++) {
-                c.Bt[t] = (t < pp.nterms) ? pp.eps * (coeff ? coeff[t] : pp.C[t]) / E : 0.0;
-                c.lam[t] = (t < pp.nterms) ? pp.lam[t] : 1.0;
-            }
-            c.b = b;
-            R = get_R<NT>(c, g, st);
+            R = lane_get_R<NT>(pp, coeff, T, g, b, st);
         }
         // cpp/transfer_lengths.cpp:161-163,196-219
         const double vdf = sqrt(2. / PI_REF) * (g * g) * exp(-0.5 * (g * g));
@@ -219,10 +211,12 @@ extern "C" int kg_transfer_lengths_batch(kg_model* m, int nT, const double* T, c
     if (nT < 1 || !T || !mtl || !etl) { set_error("kg_transfer_lengths_batch: invalid argument"); return -1; }
     CUDA_OK(cudaSetDevice(m->device));
     const int Np = m->npairs, nitems = nT * Np;
+    std::vector<double> coeff_buf;
+    if (kg_effective_coeff(m, nT, T, coeff_T, coeff_buf, &coeff_T)) return -1;
     std::vector<TlItem> items(nitems);
     for (int p = 0; p < Np; p++) for (int t = 0; t < nT; t++) {
         TlItem& it = items[p * nT + t];
-        it.pair = p; it.T = T[t]; it.coeff_off = coeff_T ? (t * Np + p) * KG_MAX_TERMS : -1;
+        it.pair = p; it.T = T[t]; it.coeff_off = coeff_T ? (t * Np + p) * m->coeff_stride : -1;
     }
     double gn[TL_NG]; tl_gnodes(gn);
     TlItem* d_items = nullptr; double *d_g = nullptr, *d_ilim = nullptr, *d_bmid = nullptr, *d_bmax = nullptr, *d_mtl = nullptr, *d_etl = nullptr, *d_coeff = nullptr;
@@ -245,8 +239,8 @@ extern "C" int kg_transfer_lengths_batch(kg_model* m, int nT, const double* T, c
     CUDA_OK(cudaMemcpyAsync(d_items, items.data(), nitems * sizeof(TlItem), cudaMemcpyHostToDevice, s));
     CUDA_OK(cudaMemcpyAsync(d_g, gn, sizeof(gn), cudaMemcpyHostToDevice, s));
     if (coeff_T) {
-        CUDA_OK(kg_dmalloc(m, &d_coeff, (size_t) nT * Np * KG_MAX_TERMS * sizeof(double)));
-        CUDA_OK(cudaMemcpyAsync(d_coeff, coeff_T, (size_t) nT * Np * KG_MAX_TERMS * sizeof(double), cudaMemcpyHostToDevice, s));
+        CUDA_OK(kg_dmalloc(m, &d_coeff, (size_t) nT * Np * m->coeff_stride * sizeof(double)));
+        CUDA_OK(cudaMemcpyAsync(d_coeff, coeff_T, (size_t) nT * Np * m->coeff_stride * sizeof(double), cudaMemcpyHostToDevice, s));
     }
     const size_t smem = (size_t) KS_ROWS * (2 + m->ntpad) * sizeof(double);
     for (int p0 = 0; p0 < Np; p0 += pairs_per_launch) {
@@ -259,7 +253,7 @@ extern "C" int kg_transfer_lengths_batch(kg_model* m, int nT, const double* T, c
         cudaFuncSetAttribute(tl_node_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem); \
         tl_search_kernel<NT><<<g1, 256, smem, s>>>(m->d_pairs, m->d_rows_by_pair, d_items, p0, nT, d_coeff, d_g, d_ilim, d_bmid, d_bmax, d_status); \
         tl_node_kernel<NT><<<g2, 256, smem, s>>>(m->d_pairs, m->d_rows_by_pair, d_items, p0, nT, d_coeff, d_g, d_ilim, d_bmid, d_bmax, d_fw, d_status); } while (0)
-        switch (m->ntpad) { case 2: TL_LAUNCH(2); break; case 4: TL_LAUNCH(4); break; default: TL_LAUNCH(6); break; }
+        switch (m->ntpad) { case 1: TL_LAUNCH(1); break; case 2: TL_LAUNCH(2); break; case 4: TL_LAUNCH(4); break; default: TL_LAUNCH(6); break; }
 #undef TL_LAUNCH
         tl_reduce_kernel<<<(np * nT + 127) / 128, 128, 0, s>>>(p0 * nT, np * nT, d_bmid, d_bmax, d_fw, d_mtl, d_etl);
         CUDA_OK(cudaGetLastError());

@@ -454,3 +454,108 @@ class QuantumMie(MieKinGas):
 
     def get_etl(self, particle_density, T, x):
         return self._pair_matrix(self.dev.transfer_lengths([T], coeff_T=self._coeff_T([T]))[1][0])
+
+
+class _GenericSpherical(MieKinGas):
+    """Single-component models on the non-power-law potentials of include/kgcuda.h (kinds 1-5). The reference classes
+    (cpp/LJSpline.h, cpp/LJTS.h, cpp/multiparam.h) are single-component; collision integrals always come from the
+    quadrature (Quantum::omega forwards to Spherical::omega when quantum_is_active is false, cpp/Quantum.cpp:1261-1268).
+    Dilute-gas (is_idealgas) properties run through the same device tables as MieKinGas."""
+    KIND = None
+
+    def _setup(self, comp_id, Mw, sigma, eps_div_k, params, FH_order, N, device, use_eos):
+        from .fluids import HBAR
+        self.comps = [comp_id, comp_id]
+        self.ncomps, self._is_singlecomp = 2, True
+        self.default_N, self.is_idealgas = N, True
+        self.lij = self.kij = 0
+        self.m = np.array([Mw, Mw], float) * 1e-3 / AVOGADRO
+        self.mole_weights = self.m.copy()
+        self.sigma_ij = np.full((2, 2), float(sigma))
+        self.epsilon_ij = np.full((2, 2), float(eps_div_k) * BOLTZMANN)
+        self.sigma, self.epsilon = self.sigma_ij, self.epsilon_ij
+        self.eos = use_eos
+        self.omega_correlation_active = False
+        self.FH_order = int(FH_order)
+        self._params = list(params)
+        self._fh_D = HBAR ** 2 / (24.0 * (self.m[0] * self.m[0] / (self.m[0] + self.m[0])))    # cpp/extentions.h:308-314
+        self._device = device
+        self._build_device_model()
+
+    def _build_device_model(self):
+        from .model import generic_desc
+        d = generic_desc(self.KIND, self.sigma_ij[0, 0], self.epsilon_ij[0, 0], self._params, self.FH_order,
+                         self._fh_D if self.FH_order > 0 else 0.0)
+        self.dev = DeviceModel([d], self.m[:1], True, device=self._device)
+        self._caches = {}
+
+    def set_FH_order(self, order):
+        """FH_Corrected::set_FH_order (cpp/extentions.h:316-321): drops every cached table."""
+        if int(order) != self.FH_order:
+            self.FH_order = int(order)
+            self._build_device_model()
+
+    def potential(self, i, j, r, T=300.0):
+        return self.dev.potential_points(0, T, r)[0]
+
+    def potential_derivative_r(self, i, j, r, T=300.0):
+        return self.dev.potential_points(0, T, r)[1]
+
+    def chi(self, i, j, T, g, b):
+        """Spherical::chi (cpp/Spherical.cpp:455-465); b in metres like the reference binding."""
+        return self.dev.chi_points(0, T, g, np.asarray(b, float) / self.sigma_ij[0, 0])
+
+    def get_R(self, i, j, T, g, b):
+        return self.dev.chi_points(0, T, g, np.asarray(b, float) / self.sigma_ij[0, 0], want_R=True)[1] * self.sigma_ij[0, 0]
+
+
+class LJSpline(_GenericSpherical):
+    """pykingas.LJSpline collision dynamics (cpp/LJSpline.h:13-30: argon-like sigma, eps, mass are fixed by the class)."""
+    KIND = 1
+
+    def __init__(self, N=4, device=0, use_eos=None):
+        self._setup("LJS", 6.64e-26 * AVOGADRO * 1e3, 3.42e-10, 1.71200476e-21 / BOLTZMANN, [], 0, N, device, use_eos)
+
+
+class LJTS(_GenericSpherical):
+    """cpp/LJTS.h: Lennard-Jones truncated at 2.5 sigma and shifted, dilute gas only."""
+    KIND = 2
+
+    def __init__(self, mole_weight=None, sigma=3.42e-10, eps_div_k=None, N=4, device=0, use_eos=None):
+        # defaults: the argon-like values pykingas passes (same numbers as cpp/LJSpline.h:16-18)
+        mole_weight = 6.64e-26 * AVOGADRO * 1e3 if mole_weight is None else mole_weight
+        eps_div_k = 1.71200476e-21 / BOLTZMANN if eps_div_k is None else eps_div_k
+        self._setup("LJTS", mole_weight, sigma, eps_div_k, [], 0, N, device, use_eos)
+
+
+class ModTangToennis(_GenericSpherical):
+    """pykingas.multiparam.ModTangToennis / FH_ModTangToennies (cpp/multiparam.cpp:5-89): Ar, Ne, He."""
+    KIND = 3
+
+    def __init__(self, comps, FH_order=0, N=4, device=0, use_eos=None):
+        from .fluids import TANG_TOENNIES
+        from .model import tang_toennies_params
+        p = TANG_TOENNIES[comps]
+        self._setup(comps, MIE[comps][0], p["sigma"], p["eps_div_k"], tang_toennies_params(p), FH_order, N, device, use_eos)
+
+
+class HFD_B2(_GenericSpherical):
+    """pykingas.multiparam.HFD_B2 / FH_HFD_B2 (cpp/multiparam.cpp:91-182): helium."""
+    KIND = 4
+
+    def __init__(self, comps="HE", FH_order=0, N=4, device=0, use_eos=None):
+        from .fluids import HFD_B2 as TAB
+        from .model import hfd_b2_params
+        p = TAB[comps]
+        self._setup(comps, MIE[comps][0], p["sigma"], p["eps_div_k"], hfd_b2_params(p), FH_order, N, device, use_eos)
+
+
+class Patowski(_GenericSpherical):
+    """pykingas.multiparam.Patowski / PatowskiFH (cpp/multiparam.cpp:184-279): hydrogen."""
+    KIND = 5
+
+    def __init__(self, comps="H2", FH_order=0, N=4, device=0, use_eos=None):
+        from .fluids import PATKOWSKI
+        from .model import patkowski_params
+        p = PATKOWSKI[comps]
+        self._setup(comps, MIE[comps][0], p["sigma"], p["eps_div_k"], patkowski_params(p), FH_order, N, device, use_eos)

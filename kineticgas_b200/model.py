@@ -3,7 +3,7 @@ omega plan (a batched sweep resident in HBM)."""
 import ctypes as C
 import numpy as np
 from . import _lib
-from ._lib import PotentialDesc, dp, ip
+from ._lib import PotentialDesc, PotentialDescEx, dp, ip
 
 STATUS_TEXT = {1: "get_R reached max iter!", 2: "tanh-sinh node table exhausted", 4: "non-finite collision integral",
                8: "Unable to converge bmid!", 16: "singular Sonine-expansion system", 32: "temperature not present in the device cache"}
@@ -35,16 +35,74 @@ def mie_desc(sigma, eps, la, lr):
     return power_sum_desc(sigma, eps, [Cm, -Cm], [lr, la])
 
 
+KIND_LJ_SPLINE, KIND_LJTS, KIND_TANG_TOENNIES, KIND_HFD_B2, KIND_PATKOWSKI = 1, 2, 3, 4, 5
+HBAR = 1.054571817e-34      # cpp/global_params.h
+
+
+def generic_desc(kind, sigma, eps, params=(), fh_order=0, fh_D=0.0):
+    """Block of a non-power-law potential (include/kgcuda.h: kg_potential_desc_ex)."""
+    d = PotentialDescEx()
+    d.kind, d.fh_order, d.sigma, d.eps, d.fh_D, d.nparams = kind, fh_order, sigma, eps, fh_D, len(params)
+    for k, v in enumerate(params):
+        d.params[k] = v
+    return d
+
+
+def tang_toennies_params(p):
+    """Parameter list of KG_POT_TANG_TOENNIES from a fluid-file block (TangToennisParam(json), cpp/multiparam.h:27-41)."""
+    return [p["A_div_k"], p["b"], p["A_tilde_div_k"], p["a_tilde"], p["a1"], p["a2"], p["am1"], p["am2"], p["L_unit"],
+            p["short_range_lim"]] + list(p["C"])
+
+
+def hfd_b2_params(p):
+    """cpp/multiparam.cpp:91-131"""
+    return [p["A"], p["alpha"], p["c6"], p["c8"], p["c10"], p["beta_star"], p["D"], p["rm"]]
+
+
+def patkowski_params(p):
+    """cpp/multiparam.cpp:184-226"""
+    return [p["Rc"], p["Ac"], p["Bc"], p["Cex1"], p["Cex2"], p["Csp1"], p["Csp2"], p["Csp3"], p["Csp4"], p["delta"],
+            p["C6"], p["C8"], p["C10"]]
+
+
+def describe_generic(desc, T=300.0):
+    """Host-only: the effective piecewise P(r) exp(Q(r)) form the device evaluates, as a dict (kg_genpot_describe)."""
+    L = _lib.lib()
+    n = -L.kg_genpot_describe(C.byref(desc), float(T), None, 0)
+    buf = np.zeros(n)
+    if L.kg_genpot_describe(C.byref(desc), float(T), _p(buf), n) != n:
+        raise RuntimeError("kg_genpot_describe failed")
+    MAXC, MAXQ, MAXT, MAXP = 40, 6, 4, 3
+    ints = buf.view(np.int32)
+    out = {"len_scale": buf[0], "e_scale": buf[1], "npieces": int(ints[4]), "zero_on_negative": int(ints[5]), "pieces": []}
+    term_d = 4 + 2 * MAXC + MAXQ
+    piece_d = 2 + MAXT * term_d
+    for p in range(out["npieces"]):
+        o = 3 + p * piece_d
+        piece = {"r_hi": buf[o], "terms": []}
+        for t in range(int(ints[2 * (o + 1)])):
+            ot = o + 2 + t * term_d
+            pmin, pn, dmin, dn, qmin, qn = [int(v) for v in ints[2 * ot:2 * ot + 6]]
+            piece["terms"].append({"pmin": pmin, "pc": buf[ot + 4:ot + 4 + pn].copy(), "dmin": dmin, "dc": buf[ot + 4 + MAXC:ot + 4 + MAXC + dn].copy(),
+                                   "qmin": qmin, "qc": buf[ot + 4 + 2 * MAXC:ot + 4 + 2 * MAXC + qn].copy()})
+        out["pieces"].append(piece)
+    return out
+
+
 class DeviceModel:
     def __init__(self, descs, masses, is_singlecomp=False, device=0):
         self.L = _lib.lib()
         self.ncomps = len(masses)
         npairs = self.ncomps * (self.ncomps + 1) // 2
         assert len(descs) == npairs
-        arr = (PotentialDesc * npairs)(*descs)
         m = np.ascontiguousarray(masses, float)
         h = C.c_void_p()
-        rc = self.L.kg_model_create(arr, self.ncomps, _p(m), int(is_singlecomp), device, C.byref(h))
+        if isinstance(descs[0], PotentialDescEx):
+            arr = (PotentialDescEx * npairs)(*descs)
+            rc = self.L.kg_model_create_ex(arr, self.ncomps, _p(m), int(is_singlecomp), device, C.byref(h))
+        else:
+            arr = (PotentialDesc * npairs)(*descs)
+            rc = self.L.kg_model_create(arr, self.ncomps, _p(m), int(is_singlecomp), device, C.byref(h))
         if rc != 0:
             raise RuntimeError("kg_model_create failed: " + self.L.kg_last_error(None).decode())
         self.h = h
@@ -82,6 +140,13 @@ class DeviceModel:
         self._chk(self.L.kg_chi_points(self.h, pair, float(T), g.size, _p(g), _p(b), _p(cf), _p(chi), _p(R), _pi(st)), "kg_chi_points")
         raise_on_status(st)
         return (chi, R) if want_R else chi
+
+    def potential_points(self, pair, T, r):
+        """u(r) [J] and du/dr [J/m] (Spherical::potential / potential_derivative_r) at temperature T."""
+        r = np.ascontiguousarray(np.atleast_1d(r), float)
+        u, du = np.empty_like(r), np.empty_like(r)
+        self._chk(self.L.kg_potential_points(self.h, pair, float(T), r.size, _p(r), _p(u), _p(du)), "kg_potential_points")
+        return u, du
 
     def omega_batch(self, T, l, r, coeff_T=None, want_w=False):
         T = np.ascontiguousarray(np.atleast_1d(T), float)

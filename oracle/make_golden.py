@@ -155,3 +155,49 @@ FIVE_CASES = [("five_comp", "C1,C2,C3,N2,CO2", 2, False, [(400.0, 0.25, [0.35, 0
 
 if __name__ == "__main__" and "five" in sys.argv[1:]:
     transport_golden(FIVE_CASES, "transport5_reference.npz")
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# non-power-law potentials (LJ/spline, LJTS, modified Tang-Toennies, HFD-B2, Patkowski, Feynman-Hibbs corrected)
+# ---------------------------------------------------------------------------------------------------------------
+GENERIC_CASES = [  # (key, kind, fluid, fh_order, temperatures of the chi points, [(T, l, r)] of the W / Omega values)
+    ("ljs", 1, "", 0, [300.0, 60.0], [(300.0, 1, 1), (300.0, 2, 2), (100.0, 1, 1)]),
+    ("ljts", 2, "", 0, [300.0], [(300.0, 1, 1), (150.0, 2, 2)]),
+    ("tt_ar", 3, "AR", 0, [300.0], [(300.0, 1, 1), (300.0, 2, 2)]),
+    ("tt_ne_fh1", 3, "NE", 1, [100.0, 40.0], [(100.0, 1, 1), (100.0, 2, 2)]),
+    ("tt_he_fh2", 3, "HE", 2, [80.0], [(80.0, 2, 2)]),
+    ("hfd_he", 4, "HE", 0, [300.0], [(300.0, 1, 1)]),
+    ("hfd_he_fh1", 4, "HE", 1, [75.0, 30.0], [(75.0, 1, 1), (75.0, 2, 2)]),
+    ("hfd_he_fh2", 4, "HE", 2, [75.0], [(75.0, 2, 2)]),
+    ("pat_h2", 5, "H2", 0, [300.0], [(300.0, 2, 2)]),
+    ("pat_h2_fh1", 5, "H2", 1, [100.0, 50.0], [(100.0, 1, 1), (100.0, 2, 2)]),
+]
+
+
+def generic_golden(fname="generic_reference.npz"):
+    import time
+    out = {}
+    rng = np.random.default_rng(20261105)
+    for key, kind, comp, fh, chiT, wcases in GENERIC_CASES:
+        m = ref.RefGeneric(kind, comp, fh)
+        out[key + "_scales"] = np.array([m.sigma0, m.eps0, m.m0, m.fh_D])
+        rr = np.concatenate([np.linspace(0.35, 3.0, 30), [5.0, 30.0, 1000.0]]) * m.sigma0
+        for T in chiT:
+            g = np.concatenate([rng.uniform(0.05, 8, 28), [1e-7, 0.25, 3.0, 7.5]])
+            b = np.concatenate([rng.uniform(0.002, 4, 28), [0.7, 1e-7, 2.0, 0.01]])
+            k = f"{key}_{T:g}"
+            out[k + "_r"] = rr
+            out[k + "_u"] = m.potential(rr, T)
+            out[k + "_du"] = m.potential_r(rr, T)
+            out[k + "_g"], out[k + "_b"] = g, b
+            out[k + "_chi"] = m.chi(0, 0, T, g, b * m.sigma0)
+            out[k + "_R"] = m.get_R(0, 0, T, g, b * m.sigma0) / m.sigma0
+        for (T, l, r) in wcases:
+            t0 = time.time()
+            out[f"W_{key}_{T:g}_{l}_{r}"] = np.array([m.w_integral(0, 0, T, l, r), m.omega(0, 0, l, r, T)])
+            print("W", key, T, l, r, out[f"W_{key}_{T:g}_{l}_{r}"], f"{time.time() - t0:.1f} s", flush=True)
+    np.savez(os.path.join(GOLD, fname), **out)
+
+
+if __name__ == "__main__" and "generic" in sys.argv[1:]:
+    generic_golden()

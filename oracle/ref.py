@@ -65,6 +65,11 @@ def lib():
         L.kgref_qmie_create.argtypes = [C.c_int, dp, dp, dp, dp, dp, C.c_int, C.c_int, C.c_int]
         L.kgref_set_internals.argtypes = [C.c_void_p, C.c_double, C.c_double]
         L.kgref_c_eff.argtypes = [C.c_void_p, C.c_int, C.c_int, dp, ip]
+        L.kgref_generic_create.restype = C.c_void_p
+        L.kgref_generic_create.argtypes = [C.c_int, C.c_char_p, C.c_int, C.c_char_p, C.c_int]
+        L.kgref_generic_scales.argtypes = [C.c_void_p, dp]
+        L.kgref_potential_rr.restype = C.c_double
+        L.kgref_potential_rr.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double]
         _LIB = L
     return _LIB
 
@@ -279,3 +284,48 @@ class RefQuantumMie(RefMie):
     def chi(self, i, j, T, g, b):
         self.set_internals(T)
         return super().chi(i, j, T, g, b)
+
+
+class RefGeneric(RefMie):
+    """The reference's non-power-law models: kind 1 LJSpline, 2 LJTS, 3 ModTangToennis, 4 HFD_B2, 5 Patowski, with
+    fh_order > 0 selecting the FH_Corrected class (cpp/multiparam.h:36-131). Single-component, classical omega."""
+
+    def __init__(self, kind, comps="", fh_order=0):
+        self.L = lib()
+        err = C.create_string_buffer(512)
+        self.h = self.L.kgref_generic_create(kind, comps.encode(), fh_order, err, 512)
+        if not self.h:
+            raise RuntimeError(err.value.decode())
+        self.nc, self.single, self.kind, self.fh_order = 1, True, kind, fh_order
+        sc = np.zeros(4)
+        self._chk(self.L.kgref_generic_scales(self.h, _p(sc)))
+        self.sigma0, self.eps0, self.m0, self.fh_D = sc
+
+    def set_internals(self, T):
+        self._chk(self.L.kgref_set_internals(self.h, 0.0, T))
+
+    def potential(self, r, T=None):
+        if T is not None:
+            self.set_internals(T)
+        return np.array([self.L.kgref_potential(self.h, 0, 0, float(x)) for x in np.atleast_1d(r)])
+
+    def potential_r(self, r, T=None):
+        if T is not None:
+            self.set_internals(T)
+        return np.array([self.L.kgref_potential_r(self.h, 0, 0, float(x)) for x in np.atleast_1d(r)])
+
+    def omega(self, i, j, l, r, T, model=False):
+        self.set_internals(T)
+        return super().omega(i, j, l, r, T, model=model)
+
+    def chi(self, i, j, T, g, b):
+        self.set_internals(T)
+        return super().chi(i, j, T, g, b)
+
+    def get_R(self, i, j, T, g, b):
+        self.set_internals(T)
+        return super().get_R(i, j, T, g, b)
+
+    def w_integral(self, i, j, T, l, r, regime=None):
+        self.set_internals(T)
+        return super().w_integral(i, j, T, l, r, regime)

@@ -9,6 +9,9 @@
 // thermopack's Fortran core cannot be built in this image.
 #include "MieKinGas.h"
 #include "QuantumMie.h"
+#include "LJSpline.h"
+#include "LJTS.h"
+#include "multiparam.h"
 #include "Integration/Integration.h"
 #include <cstring>
 #include <set>
@@ -39,6 +42,9 @@ struct Handle {
     std::unique_ptr<Spherical> kin;
     MieKinGas* mie = nullptr;          // set when kin is a MieKinGas
     QuantumMie* qmie = nullptr;        // set when kin is a QuantumMie
+    std::function<void(double)> set_T; // T hook of Feynman-Hibbs corrected models (FH_Corrected::set_internals)
+    std::function<void()> clear;       // cache.clear() of the non-Mie models
+    std::function<void(double*)> scales;
     int nc;
     std::string err;
 };
@@ -61,9 +67,55 @@ struct MieAccess : public MieKinGas {
     void clear_cache() { cache.clear(); }
 };
 
+// set_internals / cache are protected: open them up per model type
+template<class B> struct Open : public B {
+    using B::B;
+    using B::set_internals;
+    void clear_cache() { this->cache.clear(); }
+    void scales(double* o) { o[0] = this->sigma[0][0]; o[1] = this->eps[0][0]; o[2] = this->m[0]; o[3] = pow(HBAR, 2) / (24 * this->red_mass[0][0]); }
+};
+template<class M, class... A> Handle* make_open(int nc, A&&... args) {
+    Handle* h = new Handle;
+    h->nc = nc;
+    auto* k = new Open<M>(std::forward<A>(args)...);
+    h->kin.reset(k);
+    h->set_T = [k](double T) { k->set_internals(0., T, vector1d{1.}); };
+    h->clear = [k]() { k->clear_cache(); };
+    h->scales = [k](double* o) { k->scales(o); };
+    return h;
+}
+
 } // namespace
 
 extern "C" {
+
+// kind: 1 LJSpline, 2 LJTS, 3 ModTangToennis / FH_ModTangToennies, 4 HFD_B2 / FH_HFD_B2, 5 Patowski / PatowskiFH
+// (cpp/LJSpline.h, cpp/LJTS.h, cpp/multiparam.h:36-131). comps names the fluid file; fh_order 0 = uncorrected class with
+// set_quantum_active(false), so that omega is the classical Spherical::omega (cpp/Quantum.cpp:1261-1268).
+void* kgref_generic_create(int kind, const char* comps, int fh_order, char* errbuf, int errcap) {
+    try {
+        Handle* h = nullptr;
+        if (kind == 1) h = make_open<LJSpline>(1, false, true);
+        else if (kind == 2) {
+            const double s = 3.42e-10, e = 1.71200476e-21;
+            h = make_open<LJTS>(1, vector1d{6.64e-26, 6.64e-26}, vector2d{{s, s}, {s, s}}, vector2d{{e, e}, {e, e}}, true, true);
+        }
+        else if (kind == 3 && fh_order == 0) { h = make_open<ModTangToennis>(1, std::string(comps), std::string("default")); static_cast<Quantum*>(h->kin.get())->set_quantum_active(false); }
+        else if (kind == 3) h = make_open<FH_ModTangToennies>(1, std::string(comps), (size_t) fh_order, std::string("default"));
+        else if (kind == 4 && fh_order == 0) { h = make_open<HFD_B2>(1, std::string(comps)); static_cast<Quantum*>(h->kin.get())->set_quantum_active(false); }
+        else if (kind == 4) h = make_open<FH_HFD_B2>(1, std::string(comps), (size_t) fh_order);
+        else if (kind == 5 && fh_order == 0) { h = make_open<Patowski>(1, std::string(comps)); static_cast<Quantum*>(h->kin.get())->set_quantum_active(false); }
+        else if (kind == 5) h = make_open<PatowskiFH>(1, std::string(comps), (size_t) fh_order);
+        else throw std::runtime_error("unknown kind");
+        return h;
+    } catch (const std::exception& e) { if (errbuf) { strncpy(errbuf, e.what(), errcap - 1); errbuf[errcap - 1] = 0; } return nullptr; }
+}
+// sigma, eps, mass of component 0 and the FH D factor hbar^2 / (24 mu_00) (cpp/extentions.h:308-314)
+int kgref_generic_scales(void* hv, double* out4) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{ if (!h->scales) throw std::runtime_error("not a generic model"); h->scales(out4); });
+}
+double kgref_potential_rr(void* hv, int i, int j, double r) { return static_cast<Handle*>(hv)->kin->potential_dblderivative_rr(i, j, r); }
 
 void* kgref_mie_create(int nc, const double* m, const double* sigma, const double* eps,
                        const double* la, const double* lr, int is_idealgas, int is_singlecomp) {
@@ -89,7 +141,7 @@ void* kgref_qmie_create(int nc, const double* m, const double* sigma, const doub
 // T-dependent potentials: ExtSutherland::set_internals -> set_effective_params (cpp/ExtendedSutherland.h:140, .cpp:168-180)
 int kgref_set_internals(void* hv, double rho, double T) {
     Handle* h = static_cast<Handle*>(hv);
-    return guarded(h, [&]{ if (h->qmie) h->qmie->set_internals(rho, T, vector1d(h->nc, 1.0 / h->nc)); });
+    return guarded(h, [&]{ if (h->qmie) h->qmie->set_internals(rho, T, vector1d(h->nc, 1.0 / h->nc)); else if (h->set_T) h->set_T(T); });
 }
 // effective coefficients C_eff[k][i][j] after set_internals (what the device path receives as coeff_T)
 int kgref_c_eff(void* hv, int i, int j, double* out, int* nterms) {
@@ -102,7 +154,7 @@ int kgref_c_eff(void* hv, int i, int j, double* out, int* nterms) {
 }
 void kgref_destroy(void* hv) { delete static_cast<Handle*>(hv); }
 const char* kgref_last_error(void* hv) { return static_cast<Handle*>(hv)->err.c_str(); }
-void kgref_clear_cache(void* hv) { Handle* h = static_cast<Handle*>(hv); if (h->mie) static_cast<MieAccess*>(h->mie)->clear_cache(); }
+void kgref_clear_cache(void* hv) { Handle* h = static_cast<Handle*>(hv); if (h->mie) static_cast<MieAccess*>(h->mie)->clear_cache(); else if (h->clear) h->clear(); }
 void kgref_set_omega_correlation_active(void* hv, int active) { Handle* h = static_cast<Handle*>(hv); if (h->mie) h->mie->set_omega_correlation_active(active != 0); }
 void kgref_set_tl_model(void* hv, int id) { static_cast<Handle*>(hv)->kin->set_transfer_length_model(id); }
 
