@@ -185,6 +185,8 @@ typedef struct {
     double* cond_vector;            /* [n][N nc]       get_conductivity_vector */
     double* visc_matrix;            /* [n][N nc][N nc] get_viscosity_matrix    (cpp/KineticGas.cpp:418-439) */
     double* visc_vector;            /* [n][N nc]       get_viscosity_vector */
+    double* thermal_diffusion_ratio; /* [n][nc]       k_T, KineticGas::thermal_diffusion_ratio (cpp/KineticGas_properties.cpp:282-312); needs
+                                                      KG_PROP_THERMAL_DIFFUSION. thermal_diffusion_factor is alpha_ij = k_T,i - k_T,j (:314-323) */
 } kg_transport_out;
 
 /* Device-resident per-temperature tables = what the reference keeps in KineticGasCache (cpp/KineticGasCache.h): every

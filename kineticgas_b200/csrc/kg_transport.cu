@@ -369,7 +369,7 @@ struct StateArgs {
     const double *mtl, *etl;    // [nT][npairs_dev] (null for ideal gas)
     const double* brk;          // [nT][4][nc][nc][N][N]
     const double *dmudn, *cp_ideal, *pressure, *dvdn;
-    double *viscosity, *conductivity, *contribs, *D, *DT, *K, *Kp, *cond_matrix, *cond_vector, *visc_matrix, *visc_vector;
+    double *viscosity, *conductivity, *contribs, *D, *DT, *kT, *K, *Kp, *cond_matrix, *cond_vector, *visc_matrix, *visc_vector;
     int* status;
 };
 
@@ -500,6 +500,7 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
         if (a.contribs) for (int k = 0; k < 3; k++) a.contribs[(size_t) sp * 3 + k] = qnan;
         if (a.D) for (int k = 0; k < nD * nD; k++) a.D[(size_t) sp * nD * nD + k] = qnan;
         if (a.DT) for (int k = 0; k < nc; k++) a.DT[(size_t) sp * nc + k] = qnan;
+        if (a.kT) for (int k = 0; k < nc; k++) a.kT[(size_t) sp * nc + k] = qnan;
         if (a.status) a.status[sp] = KG_STATUS_T_NOT_CACHED;
         return;
     }
@@ -595,7 +596,7 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
                 oi++;
             }
         }
-        if (want_E && (props & KG_PROP_THERMAL_DIFFUSION) && a.DT) {
+        if (want_E && (props & KG_PROP_THERMAL_DIFFUSION) && (a.DT || a.kT)) {
             // cpp/KineticGas_properties.cpp:208-258
             double bm[MAXC * MAXC], DT[MAXC], DT2[MAXC];
             for (int j = 0; j < nc; j++) for (int k = 0; k < nc; k++) {
@@ -618,7 +619,31 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
             for (int i = 0; i < nc; i++) { double v = 0.; for (int k = 0; k < nc; k++) v += psi[i * nc + k] * DT[k]; DT2[i] = v; }
             double tmp = 0.;
             for (int k = 0; k < nc; k++) for (int mm = 0; mm < nc; mm++) tmp += s.rho * s.x[mm] * bm[mm * nc + k];
-            for (int i = 0; i < nc; i++) a.DT[(size_t) sp * nc + i] = (DT2[i] + (Dd[i * nc + dep] / ksi[dep]) * tmp) / AVOGADRO;
+            if (a.DT) for (int i = 0; i < nc; i++) a.DT[(size_t) sp * nc + i] = (DT2[i] + (Dd[i * nc + dep] / ksi[dep]) * tmp) / AVOGADRO;
+            if (a.kT) {
+                // KineticGas::thermal_diffusion_ratio (cpp/KineticGas_properties.cpp:282-312): always from the centre-of-mass
+                // frame quantities with the last component dependent, whatever frame the D / D_T outputs use.
+                const int last = nc - 1;
+                double Am[MAXC * MAXC], rhs[MAXC]; int pv[MAXC];
+                for (int i = 0; i < last; i++) {
+                    for (int j = 0; j < nc; j++) {
+                        const double Dij = Dcom[i * nc + j] - (ksi[j] / ksi[last]) * Dcom[i * nc + last];
+                        Am[i * MAXC + j] = -Dij * s.x[j] * (1 / s.Vm);
+                    }
+                    Am[last * MAXC + i] = s.x[i] * ksi[i];
+                    rhs[i] = (DT[i] + (Dcom[i * nc + last] / ksi[last]) * tmp) / AVOGADRO;
+                }
+                Am[last * MAXC + last] = s.x[last] * ksi[last];
+                if (tm.is_idealgas) rhs[last] = 1;
+                else {
+                    double v = 0.;
+                    for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) v += s.x[i] * bm[i * nc + j];     // bm = delta_ij + (4 pi / 3) rho x_j etl^3 M_ij g_ij
+                    rhs[last] = v;
+                }
+                if (lu_factor(Am, nc, MAXC, pv)) st |= KG_STATUS_SINGULAR;
+                lu_solve(Am, nc, MAXC, pv, rhs);
+                for (int i = 0; i < nc; i++) a.kT[(size_t) sp * nc + i] = rhs[i];
+            }
         }
         if ((props & KG_PROP_CONDUCTIVITY) && a.cp_ideal) {
             // thermal_conductivity_contributions "tdi", cpp/KineticGas_properties.cpp:74-141
@@ -954,7 +979,7 @@ extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const do
     if (!m->is_singlecomp && !x) { set_error("kg_transport_batch: mole fractions required"); return -1; }
     const unsigned props = opts->properties;
     const int nc = m->is_singlecomp ? 2 : m->ncomps, nce = m->is_singlecomp ? 1 : m->ncomps;
-    const bool want_D = ((props & KG_PROP_DIFFUSION) && out->D) || ((props & KG_PROP_THERMAL_DIFFUSION) && out->DT);
+    const bool want_D = ((props & KG_PROP_DIFFUSION) && out->D) || ((props & KG_PROP_THERMAL_DIFFUSION) && (out->DT || out->thermal_diffusion_ratio));
     const bool want_lambda = (props & KG_PROP_CONDUCTIVITY) && (out->conductivity || out->conductivity_contribs);
     if (want_D && (!eos || !eos->dmudn)) { set_error("kg_transport_batch: EoS is not set (dmudn required)"); return -1; }
     if (want_lambda && (!eos || !eos->cp_ideal)) { set_error("kg_transport_batch: EoS is not set (cp_ideal required)"); return -1; }
@@ -1002,7 +1027,7 @@ extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const do
     if (eos && eos->dvdn && opts->frame_of_reference == KG_FOR_COV) { a.dvdn = db.put(eos->dvdn, (size_t) n * nce, s); NEED(a.dvdn); }
     struct OutMap { double* host; double** dev; size_t count; };
     OutMap maps[] = {{out->viscosity, &a.viscosity, (size_t) n}, {out->conductivity, &a.conductivity, (size_t) n},
-                     {out->conductivity_contribs, &a.contribs, (size_t) n * 3}, {out->D, &a.D, (size_t) n * nD * nD}, {out->DT, &a.DT, (size_t) n * nc},
+                     {out->conductivity_contribs, &a.contribs, (size_t) n * 3}, {out->D, &a.D, (size_t) n * nD * nD}, {out->DT, &a.DT, (size_t) n * nc}, {out->thermal_diffusion_ratio, &a.kT, (size_t) n * nc},
                      {out->K, &a.K, (size_t) n * nc}, {out->K_prime, &a.Kp, (size_t) n * nc}, {out->cond_matrix, &a.cond_matrix, (size_t) n * nn * nn},
                      {out->cond_vector, &a.cond_vector, (size_t) n * nn}, {out->visc_matrix, &a.visc_matrix, (size_t) n * nn * nn},
                      {out->visc_vector, &a.visc_vector, (size_t) n * nn}};

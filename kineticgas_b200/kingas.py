@@ -31,7 +31,7 @@ class EosInputs(C.Structure):
 
 class TransportOut(C.Structure):
     _fields_ = [(k, dp) for k in ("viscosity", "conductivity", "conductivity_contribs", "D", "DT", "rdf", "K", "K_prime",
-                                  "cond_matrix", "cond_vector", "visc_matrix", "visc_vector")]
+                                  "cond_matrix", "cond_vector", "visc_matrix", "visc_vector", "thermal_diffusion_ratio")]
 
 
 def _ptr(a):
@@ -212,13 +212,13 @@ class MieKinGas:
         nD = nc - 1 if do_compress else nc
         shapes = {"viscosity": (n,), "conductivity": (n,), "conductivity_contribs": (n, 3), "D": (n, nD, nD), "DT": (n, nc),
                   "rdf": (n, nc, nc), "K": (n, nc), "K_prime": (n, nc), "cond_matrix": (n, nn, nn), "cond_vector": (n, nn),
-                  "visc_matrix": (n, nn, nn), "visc_vector": (n, nn)}
+                  "visc_matrix": (n, nn, nn), "visc_vector": (n, nn), "thermal_diffusion_ratio": (n, nc)}
         bufs = {k: np.zeros(shapes[k]) for k in want}
         out = TransportOut()
         for k, b in bufs.items():
             setattr(out, k, _ptr(b))
         opts = self._opts(N, properties, frame, dependent_idx, solvent_idx, do_compress)
-        want_D = ("D" in want) or ("DT" in want)
+        want_D = ("D" in want) or ("DT" in want) or ("thermal_diffusion_ratio" in want)
         eos_arr = self._eos_arrays(Tn, Vn, xn, want_D, ("conductivity" in want) or ("conductivity_contribs" in want),
                                    frame == FRAMES["CoV"] and want_D, eos_inputs)
         eos = EosInputs()
@@ -272,6 +272,26 @@ class MieKinGas:
         r = self._run(T, Vm, x, N, PROP_THERMAL_DIFFUSION, ["DT"], frame=FRAMES[frame_of_reference], dependent_idx=dependent_idx,
                       solvent_idx=solvent_idx, **kw)
         return r["DT"][0] if r["scalar"] else r["DT"]
+
+    def thermal_diffusion_ratio(self, T, Vm, x, N=None, **kw):
+        """k_T,i (pykingas/py_KineticGas.py:279-315 -> KineticGas::thermal_diffusion_ratio, cpp/KineticGas_properties.cpp:282-312)."""
+        N = self.default_N if N is None else N
+        if N < 2:
+            warnings.warn(f"Thermal diffusion is a 2nd order phenomena, cannot be computed for N < 2 (got N = {N})", RuntimeWarning, stacklevel=2)
+            return np.full(self.ncomps, np.nan)
+        r = self._run(T, Vm, x, N, PROP_THERMAL_DIFFUSION, ["thermal_diffusion_ratio"], frame=FRAMES["CoM"], do_compress=False, **kw)
+        return r["thermal_diffusion_ratio"][0] if r["scalar"] else r["thermal_diffusion_ratio"]
+
+    def thermal_diffusion_factor(self, T, Vm, x, N=None, **kw):
+        """alpha_ij = k_T,i - k_T,j (cpp/KineticGas_properties.cpp:314-323)."""
+        kT = np.asarray(self.thermal_diffusion_ratio(T, Vm, x, N=N, **kw))
+        return kT[..., :, None] - kT[..., None, :]
+
+    def soret_coefficient(self, T, Vm, x, N=None, **kw):
+        """S_T = alpha_T / T, the non-Zarate branch of pykingas/py_KineticGas.py:347-399."""
+        a = self.thermal_diffusion_factor(T, Vm, x, N=N, **kw)
+        T = np.asarray(T, float)
+        return a / (T[..., None, None] if T.ndim else T)
 
     def transport_batch(self, T, Vm, x, N=None, properties=PROP_VISCOSITY | PROP_CONDUCTIVITY | PROP_DIFFUSION | PROP_THERMAL_DIFFUSION,
                         frame_of_reference="CoN", dependent_idx=-1, solvent_idx=-1, use_independent=True, eos_inputs=None, cache=None):

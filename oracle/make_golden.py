@@ -201,3 +201,26 @@ def generic_golden(fname="generic_reference.npz"):
 
 if __name__ == "__main__" and "generic" in sys.argv[1:]:
     generic_golden()
+
+
+def kt_golden(fname="kt_reference.npz"):
+    """Thermal diffusion ratios k_T of the state points of TRANSPORT_CASES (inputs are those of transport_reference.npz)."""
+    out = {}
+    for name, comps, N, ideal, points in TRANSPORT_CASES:
+        if N < 2:
+            continue
+        ids, Mw, s, e, la, lr = mie_parameters(comps)
+        m = ref.RefMie(Mw, s, e, la, lr, is_idealgas=ideal)
+        for k, (T, rho_star, x) in enumerate(points):
+            rho = rho_star / s[0] ** 3
+            Vm = ref.AVOGADRO / rho
+            xi = [0.5, 0.5] if m.single else x
+            dmudn, cp_id, dvdn = synthetic_eos(T, Vm, x, Mw)
+            m.set_eos(dmudn=dmudn, cp_id=cp_id, p=1e5, vm=Vm, dvdn=dvdn)
+            out[f"{name}_{k}_kT"] = m.thermal_diffusion_ratio(T, Vm, xi, N)
+            print(name, k, out[f"{name}_{k}_kT"], flush=True)
+    np.savez(os.path.join(GOLD, fname), **out)
+
+
+if __name__ == "__main__" and "kt" in sys.argv[1:]:
+    kt_golden()

@@ -326,4 +326,13 @@ int kgref_thermal_diffusion_coeff(void* hv, double T, double Vm, const double* x
     });
 }
 
+int kgref_thermal_diffusion_ratio(void* hv, double T, double Vm, const double* x, int nx, int N, double* out, int* n) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{
+        Eigen::VectorXd k = h->kin->thermal_diffusion_ratio(T, Vm, vector1d(x, x + nx), N);
+        *n = (int) k.size();
+        for (int i = 0; i < k.size(); i++) out[i] = k(i);
+    });
+}
+
 } // extern "C"
