@@ -188,11 +188,13 @@ __device__ double omega_correlation(int l, int r, double lr, double Ts) {
     return v;
 }
 
+__device__ double ljs_omega_correlation(int l, int r, double Ts);      // LJ/spline table, defined with the LJ/s RDF below
+
 // Omega of the correlation branch: omega_correlation * omega_hs. One thread per (t, pair, lr); mask says where it applies.
 __global__ void omega_correlation_kernel(int nT, int npairs, int nlr, const double* __restrict__ T, const MiePair* __restrict__ mp,
                                          const int* __restrict__ pair_i, const int* __restrict__ pair_j, const double* __restrict__ mass,
                                          const int* __restrict__ lr_l, const int* __restrict__ lr_r, const unsigned char* __restrict__ is_corr,
-                                         double* __restrict__ omega) {
+                                         int ljs, double* __restrict__ omega) {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= nT * npairs * nlr) return;
     if (!is_corr[e]) return;
@@ -207,7 +209,7 @@ __global__ void omega_correlation_kernel(int nT, int npairs, int nlr, const doub
     double hs;
     if (i == j) hs = sqrt((BOLTZMANN * T[t]) / (PI_REF * mass[i])) * w;
     else hs = sqrt(BOLTZMANN * T[t] * (mass[i] + mass[j]) / (2. * PI_REF * mass[i] * mass[j])) * w;
-    omega[e] = omega_correlation(l, r, q.lr, Ts) * hs;
+    omega[e] = (ljs ? ljs_omega_correlation(l, r, Ts) : omega_correlation(l, r, q.lr, Ts)) * hs;
 }
 
 // Barker-Henderson diameters of the pure components, d_ii(T) (cpp/MieKinGas.cpp:314-332). One thread per (t, i).
@@ -333,6 +335,70 @@ __device__ double rdf_pair(const RdfCommon& c, const MiePair& q, double dij, dou
                     * (3 * da2_div_chi + eps * c.KHS * pow(C, 2) * (-lr * x_2lr * aB_2lr / rho + (la + lr) * x_lalr * aB_lalr / rho - la * x_2la * aB_2la / rho));
     const double be = (1. / (BOLTZMANN * T)) * eps;
     return gHS * exp(be * (g1 / gHS) + pow(be, 2) * (g2 / gHS));
+}
+
+// ---- LJ/spline: collision-integral correlation (cpp/LJSpline.cpp:123-165, table cpp/LJSpline.h:138-142) and the RDF at
+// contact g = g0 + beta* g1 + beta*^2 g2 (cpp/LJSpline.h:113-125, cpp/LJSpline.cpp:16-118, constants cpp/LJSpline.h:167-205) ----
+__constant__ double c_ljs_ocf[2][6] = {{0.12381066, -0.19473855, -0.12605004, 1.42026419, -1.14753069, 0.25563792},
+                                       {0.2525206, -0.12502955, -1.02633768, 3.31321146, -2.58470784, 0.62745361}};
+__constant__ double c_ljs_q[4][11] = {
+    {-0.53572874, -0.37806724, -0.23016988, 0.34630713, 0.07308556, 5.27289035, -6.43165849, -1.63392187, 16.74650716, -27.36299942, -0.43778915},      // q_I1
+    {1.60718622, -7.09047972e-02, -9.43081376e-01, -5.09423352e+00, 1.36949006e+00, -5.81631691e+01, -1.39795273e+00, 3.66229139e+00, -2.77904034e+02,
+     5.65474349e+01, 1.01557784e+01},                                                                                                                  // q_J1
+    {0.3592528, 0.27758414, 0.25126487, -0.22023453, -0.11005555, -4.46920946, 6.117315, 0.95067716, -13.88450783, 24.30452001, -0.63636868},          // q_I2
+    {-0.5388792, 1.16814143e-02, 8.83906862e-02, 2.36081648e+00, -5.31094654e-01, 2.62590123e+01, -2.13956077e+00, -1.20815977e+00, 1.18753081e+02,
+     -2.84345337e+01, -2.53564086e+00}};                                                                                                               // q_J2
+__constant__ double c_ljs_phi[4] = {13.2795715, 3.84921999, -2.16074213, -1.40190623};
+
+__device__ double ljs_recursive_factor(int l, int r, double Ts) {
+    double d = -(1. / 6.);
+    for (int n = 2; n < 7; n++) d += c_ljs_ocf[l - 1][n - 1] * pow(Ts, -(n - 1.) / 2.) * (1. - n) / 2.;
+    return 1. + d / (r + 2);
+}
+__device__ double ljs_omega_correlation(int l, int r, double Ts) {
+    double lnw = -(1. / 6.) * log(Ts);
+    for (int n = 1; n < 7; n++) lnw += c_ljs_ocf[l - 1][n - 1] * pow(Ts, (1. - n) * 0.5);
+    double v = exp(lnw);
+    for (int rr = l; rr < r; rr++) v = ljs_recursive_factor(l, rr, Ts) * v;
+    return v;
+}
+__device__ double ljs_fit(const double* q, double rs, double d) {          // I1, J1, I2, J2
+    return q[0] + q[1] * rs + q[2] * pow(rs, 2) + q[3] * pow(rs, 3) + q[4] * pow(rs, 4) +
+           rs * (q[5] * pow(rs, 2) + q[6] * rs + q[7]) * (d - 1) + rs * (q[8] * pow(rs, 2) + q[9] * rs + q[10]) * pow((d - 1), 2);
+}
+__device__ double ljs_fit_diff(const double* q, double rs, double d) {     // I1_diff, I2_diff
+    return q[1] + 2 * q[2] * rs + 3 * q[3] * pow(rs, 2) + 4 * q[4] * pow(rs, 3) +
+           (3 * q[5] * pow(rs, 2) + 2 * q[6] * rs + q[7]) * (d - 1) + (3 * q[8] * pow(rs, 2) + 2 * q[9] * rs + q[10]) * pow((d - 1), 2);
+}
+__device__ double ljs_rdf(double rho, double T, double sigma, double eps, double dbh) {
+    const double eta = PI_REF * rho * pow(dbh, 3) / 6., x0 = sigma / dbh, d = dbh / sigma;
+    const double k0 = -log(1. - eta) + (42. * eta - 39. * pow(eta, 2) + 9 * pow(eta, 3) - 2. * pow(eta, 4)) / (6. * pow((1. - eta), 3));
+    const double k1 = (pow(eta, 4) + 6. * pow(eta, 2) - 12. * eta) / (2. * pow((1 - eta), 3));
+    const double k2 = -3. * pow(eta, 2) / (8. * pow((1 - eta), 2));
+    const double k3 = (-pow(eta, 4) + 3. * pow(eta, 2) + 3. * eta) / (6. * pow((1 - eta), 3));
+    const double g0 = exp(k0 + k1 * x0 + k2 * pow(x0, 2) + k3 * pow(x0, 3));
+    const double rs = rho * pow(sigma, 3);
+    const double g1 = (3 * ljs_fit_diff(c_ljs_q[0], rs, d) * rs + 3 * ljs_fit(c_ljs_q[0], rs, d) + ljs_fit(c_ljs_q[1], rs, d)) / pow(d, 3);
+    const double i2 = ljs_fit(c_ljs_q[2], rs, d), di2 = ljs_fit_diff(c_ljs_q[2], rs, d), j2 = ljs_fit(c_ljs_q[3], rs, d);
+    const double khs = pow((1 - eta), 4) / (1. + 4. * eta + 4. * pow(eta, 2) - 4. * pow(eta, 3) + pow(eta, 4));
+    const double tmp = pow(eta, 4) - 4. * pow(eta, 3) + 4. * pow(eta, 2) + 4. * eta + 1.;
+    const double dkhs = (4. * (pow(eta, 2) - 5. * eta - 2.) * pow(1. - eta, 3) / pow(tmp, 2)) * (PI_REF * pow(d, 3)) / 6;
+    const double g2_mca = (-3 / (2 * pow(d, 3))) * (i2 * khs + rs * i2 * dkhs + rs * khs * di2 + 2 * khs * j2 / 3);
+    const double Tr = T * BOLTZMANN / eps, theta = exp(1 / Tr) - 1;
+    const double gamma = c_ljs_phi[0] * eta * pow(x0, 3) * theta * exp(c_ljs_phi[1] * eta * pow(x0, 3) + c_ljs_phi[2] * pow(eta, 2) * pow(x0, 6)) * exp(c_ljs_phi[3] / Tr);
+    const double g2 = (1 + gamma) * g2_mca;
+    const double bs = eps / (BOLTZMANN * T);
+    return g0 + bs * g1 + pow(bs, 2) * g2;
+}
+// One thread per (state point, slot): the LJ/spline model is single-component, every pair shares g.
+__global__ void ljs_rdf_kernel(int n, int nslots, int nc, const int* __restrict__ tidx, const double* __restrict__ T_of, const double* __restrict__ Vm,
+                               const double* __restrict__ dbh, MiePair q, double* __restrict__ rdf) {
+    const long long e = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= (long long) n * nslots) return;
+    const int slot = (int) (e % nslots), sp = (int) (e / nslots), t = tidx[sp];
+    const double rho = (slot == 0) ? AVOGADRO / Vm[sp] : AVOGADRO / 1e12;
+    const double g = ljs_rdf(rho, T_of[t], q.sigma, q.eps, dbh[(size_t) t * nc]);
+    for (int k = 0; k < nc * nc; k++) rdf[((size_t) sp * nslots + slot) * nc * nc + k] = g;
 }
 
 // One thread per (state point, slot, i <= j). slot 0: the state point's density; slot 1: N_A / 1e12 (the dilute viscosity of the
@@ -712,12 +778,13 @@ struct kg_tcache {
     kg_transport_opts opt{};
     TModel tm{};
     int nT = 0;
-    bool mie = false;
+    bool mie = false, ljs = false;
     std::vector<double> T;
     std::map<double, int> index_of;
     std::vector<unsigned char> is_corr;              // [nT][npairs][nlr]
     double *d_T = nullptr, *d_omega = nullptr, *d_mtl = nullptr, *d_etl = nullptr, *d_dbh = nullptr, *d_brk = nullptr;
     MiePair* d_mp_int = nullptr;                     // [nc][nc] internal pairs
+    MiePair mp00{};                                  // pair (0,0) on the host (LJ/spline RDF kernel argument)
     std::vector<double> h_mtl, h_etl;
     double ms_omega = 0, ms_tl = 0;                  // stage timings of the build (host clock around synchronised stages)
 };
@@ -775,13 +842,15 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
     if (m->is_singlecomp && m->ncomps != 1) { set_error("kg_tcache_create: single-component models are created with ncomps = 1"); return -1; }
     bool mie = true;
     for (auto& d : m->descs) mie = mie && desc_is_mie(d);
-    if (!opts->is_idealgas && (!mie || coeff_T)) {
+    bool ljs = m->generic;      // LJSpline: own correlation (cpp/LJSpline.cpp:123-134) and own RDF model (cpp/LJSpline.h:89-125)
+    for (auto& g : m->gdescs) ljs = ljs && g.kind == KG_POT_LJ_SPLINE;
+    if (!opts->is_idealgas && ((!mie && !ljs) || coeff_T)) {
         set_error("RDF model is not implemented. Model is only available for ideal gas!");     // cpp/KineticGas.h:259
         return -1;
     }
     CUDA_OK(cudaSetDevice(m->device));
     kg_tcache* c = new kg_tcache;
-    c->m = m; c->device = m->device; c->opt = *opts; c->nT = nT; c->mie = mie;
+    c->m = m; c->device = m->device; c->opt = *opts; c->nT = nT; c->mie = mie; c->ljs = ljs;
     c->T.assign(T, T + nT);
     for (int t = 0; t < nT; t++) c->index_of.emplace(T[t], t);
     TModel& tm = c->tm;
@@ -852,6 +921,7 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
         const auto& d = m->descs[p];
         const int l = tm.lr_l[k], r = tm.lr_r[k];
         bool corr = opts->omega_correlation_active && mie && !coeff_T && (l <= 2) && (r >= l) && (r <= 3) && (fabs(d.lam[1] - 6.) < 1e-10);
+        if (ljs) corr = opts->omega_correlation_active && (l <= 2) && (r >= l) && (r <= 3);
         if (corr) corr = (T[t] * 1.38064852e-23 / d.eps) > 0.4;
         c->is_corr[o] = corr; need[o] = !corr;
         any_numeric |= !corr; any_corr |= corr;
@@ -882,10 +952,11 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
     }
     m->timings[1] = ms_since(t_stage); t_stage = now();
     std::vector<MiePair> mp_dev(Np), mp_int((size_t) nc * nc), mp_diag(nc);
-    if (mie) {
+    if (mie || ljs) {
         for (int p = 0; p < Np; p++) {
             const auto& d = m->descs[p];
             MiePair q; q.sigma = d.sigma; q.eps = d.eps; q.lr = d.lam[0]; q.la = d.lam[1]; q.C = d.C[0];
+            if (ljs) { q.lr = 12.; q.la = 6.; q.C = 4.; }     // inside [sigma/2, sigma] (the Barker-Henderson integral) LJ/s is plain LJ
             q.alpha = q.C * ((1.0 / (q.la - 3.0)) - (1.0 / (q.lr - 3.0)));          // cpp/MieKinGas.cpp:52
             mp_dev[p] = q;
         }
@@ -893,13 +964,14 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
         for (int i = 0; i < nc; i++) mp_diag[i] = mp_int[i * nc + i];
     }
     TC_CUDA(upload(m, &c->d_mp_int, mp_int));
+    c->mp00 = mp_int[0];
     if (any_corr) {
         MiePair* d_mp = nullptr; int *d_pi = nullptr, *d_pj = nullptr, *d_l = nullptr, *d_r = nullptr; double* d_mass = nullptr; unsigned char* d_ic = nullptr;
         std::vector<int> ll(tm.lr_l, tm.lr_l + nlr), rr(tm.lr_r, tm.lr_r + nlr);
         TC_CUDA(upload(m, &d_mp, mp_dev)); TC_CUDA(upload(m, &d_pi, pair_i)); TC_CUDA(upload(m, &d_pj, pair_j)); TC_CUDA(upload(m, &d_l, ll)); TC_CUDA(upload(m, &d_r, rr));
         TC_CUDA(upload(m, &d_mass, m->mass)); TC_CUDA(upload(m, &d_ic, c->is_corr));
         const int tot = nT * Np * nlr;
-        omega_correlation_kernel<<<(tot + 127) / 128, 128, 0, s>>>(nT, Np, nlr, c->d_T, d_mp, d_pi, d_pj, d_mass, d_l, d_r, d_ic, c->d_omega);
+        omega_correlation_kernel<<<(tot + 127) / 128, 128, 0, s>>>(nT, Np, nlr, c->d_T, d_mp, d_pi, d_pj, d_mass, d_l, d_r, d_ic, ljs ? 1 : 0, c->d_omega);
         TC_CUDA(cudaGetLastError());
         TC_CUDA(cudaStreamSynchronize(s));
         for (void* q : {(void*) d_mp, (void*) d_pi, (void*) d_pj, (void*) d_l, (void*) d_r, (void*) d_mass, (void*) d_ic}) m->dfree(q);
@@ -959,7 +1031,8 @@ int launch_state(kg_tcache* c, StateArgs& a, cudaStream_t s, const double* d_x_f
     const int n = a.n;
     if (!tm.is_idealgas) {
         const long long tot = (long long) n * a.nslots * (tm.nc * (tm.nc + 1) / 2);
-        rdf_kernel<<<(unsigned) ((tot + 127) / 128), 128, 0, s>>>(n, a.nslots, tm, a.tidx, a.T_of, a.Vm, d_x_for_rdf, c->d_dbh, c->d_mp_int, d_rdf);
+        if (c->ljs) ljs_rdf_kernel<<<(unsigned) (((long long) n * a.nslots + 127) / 128), 128, 0, s>>>(n, a.nslots, tm.nc, a.tidx, a.T_of, a.Vm, c->d_dbh, c->mp00, d_rdf);
+        else rdf_kernel<<<(unsigned) ((tot + 127) / 128), 128, 0, s>>>(n, a.nslots, tm, a.tidx, a.T_of, a.Vm, d_x_for_rdf, c->d_dbh, c->d_mp_int, d_rdf);
     }
     const int nn = tm.N * tm.nc, grid = (n + 127) / 128;
     if (nn <= 8) state_kernel<8><<<grid, 128, 0, s>>>(tm, a);

@@ -533,8 +533,12 @@ class LJSpline(_GenericSpherical):
     """pykingas.LJSpline collision dynamics (cpp/LJSpline.h:13-30: argon-like sigma, eps, mass are fixed by the class)."""
     KIND = 1
 
-    def __init__(self, N=4, device=0, use_eos=None):
+    def __init__(self, N=4, is_idealgas=False, device=0, use_eos=None):
         self._setup("LJS", 6.64e-26 * AVOGADRO * 1e3, 3.42e-10, 1.71200476e-21 / BOLTZMANN, [], 0, N, device, use_eos)
+        # RET for the LJ/s fluid: own RDF at contact (cpp/LJSpline.h:89-125) and the omega correlation of LJSpline::omega
+        # (cpp/LJSpline.cpp:123-134), which the reference applies unconditionally
+        self.is_idealgas = is_idealgas
+        self.omega_correlation_active = True
 
 
 class LJTS(_GenericSpherical):

@@ -224,3 +224,35 @@ def kt_golden(fname="kt_reference.npz"):
 
 if __name__ == "__main__" and "kt" in sys.argv[1:]:
     kt_golden()
+
+
+def ljs_transport_golden(fname="ljs_transport_reference.npz"):
+    """RET state points of the reference's LJSpline class: rdf, transfer lengths, K-factors, eta, lambda (t, d, i)."""
+    out = {}
+    m = ref.RefGeneric(1, "", 0)
+    sig = m.sigma0
+    Mw = [m.m0 * ref.AVOGADRO * 1e3]
+    pts = [(150.0, 0.05), (150.0, 0.35), (300.0, 0.2), (45.0, 0.01)]       # last: T* = 0.36 < 0.4, all Omega by quadrature
+    for k, (T, rho_star) in enumerate(pts):
+        rho = rho_star / sig ** 3
+        Vm = ref.AVOGADRO / rho
+        xi = [0.5, 0.5]
+        dmudn, cp_id, dvdn = synthetic_eos(T, Vm, [1.0], Mw)
+        m.set_eos(dmudn=dmudn, cp_id=cp_id, p=1e5, vm=Vm, dvdn=dvdn)
+        key = f"ljs_{k}"
+        out[key + "_in"] = np.array([T, Vm, rho] + xi)
+        out[key + "_cp"] = cp_id
+        out[key + "_rdf"] = m.rdf(rho, T, xi)
+        K, Kp = m.K_factors(rho, T, xi)
+        out[key + "_K"], out[key + "_Kp"] = K, Kp
+        out[key + "_mtl"], out[key + "_etl"] = m.mtl(rho, T, xi), m.etl(rho, T, xi)
+        out[key + "_viscosity"] = np.array(m.viscosity(T, Vm, xi, 2))
+        out[key + "_contribs"] = m.thermal_conductivity_contribs(T, Vm, xi, 2)
+        for (l, r) in ((1, 1), (1, 2), (1, 3), (2, 2), (2, 3)):
+            out[key + f"_omega_{l}_{r}"] = np.array(m.omega(0, 0, l, r, T, model=True))
+        print(key, "eta", out[key + "_viscosity"], "lambda", out[key + "_contribs"], "rdf", out[key + "_rdf"][0, 0], flush=True)
+    np.savez(os.path.join(GOLD, fname), **out)
+
+
+if __name__ == "__main__" and "ljs" in sys.argv[1:]:
+    ljs_transport_golden()

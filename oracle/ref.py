@@ -308,7 +308,7 @@ class RefGeneric(RefMie):
         self.h = self.L.kgref_generic_create(kind, comps.encode(), fh_order, err, 512)
         if not self.h:
             raise RuntimeError(err.value.decode())
-        self.nc, self.single, self.kind, self.fh_order = 1, True, kind, fh_order
+        self.nc, self.single, self.kind, self.fh_order = 2, True, kind, fh_order      # single-component: two identical species inside
         sc = np.zeros(4)
         self._chk(self.L.kgref_generic_scales(self.h, _p(sc)))
         self.sigma0, self.eps0, self.m0, self.fh_D = sc

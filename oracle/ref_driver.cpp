@@ -95,17 +95,17 @@ extern "C" {
 void* kgref_generic_create(int kind, const char* comps, int fh_order, char* errbuf, int errcap) {
     try {
         Handle* h = nullptr;
-        if (kind == 1) h = make_open<LJSpline>(1, false, true);
+        if (kind == 1) h = make_open<LJSpline>(2, false, true);
         else if (kind == 2) {
             const double s = 3.42e-10, e = 1.71200476e-21;
-            h = make_open<LJTS>(1, vector1d{6.64e-26, 6.64e-26}, vector2d{{s, s}, {s, s}}, vector2d{{e, e}, {e, e}}, true, true);
+            h = make_open<LJTS>(2, vector1d{6.64e-26, 6.64e-26}, vector2d{{s, s}, {s, s}}, vector2d{{e, e}, {e, e}}, true, true);
         }
-        else if (kind == 3 && fh_order == 0) { h = make_open<ModTangToennis>(1, std::string(comps), std::string("default")); static_cast<Quantum*>(h->kin.get())->set_quantum_active(false); }
-        else if (kind == 3) h = make_open<FH_ModTangToennies>(1, std::string(comps), (size_t) fh_order, std::string("default"));
-        else if (kind == 4 && fh_order == 0) { h = make_open<HFD_B2>(1, std::string(comps)); static_cast<Quantum*>(h->kin.get())->set_quantum_active(false); }
-        else if (kind == 4) h = make_open<FH_HFD_B2>(1, std::string(comps), (size_t) fh_order);
-        else if (kind == 5 && fh_order == 0) { h = make_open<Patowski>(1, std::string(comps)); static_cast<Quantum*>(h->kin.get())->set_quantum_active(false); }
-        else if (kind == 5) h = make_open<PatowskiFH>(1, std::string(comps), (size_t) fh_order);
+        else if (kind == 3 && fh_order == 0) { h = make_open<ModTangToennis>(2, std::string(comps), std::string("default")); static_cast<Quantum*>(h->kin.get())->set_quantum_active(false); }
+        else if (kind == 3) h = make_open<FH_ModTangToennies>(2, std::string(comps), (size_t) fh_order, std::string("default"));
+        else if (kind == 4 && fh_order == 0) { h = make_open<HFD_B2>(2, std::string(comps)); static_cast<Quantum*>(h->kin.get())->set_quantum_active(false); }
+        else if (kind == 4) h = make_open<FH_HFD_B2>(2, std::string(comps), (size_t) fh_order);
+        else if (kind == 5 && fh_order == 0) { h = make_open<Patowski>(2, std::string(comps)); static_cast<Quantum*>(h->kin.get())->set_quantum_active(false); }
+        else if (kind == 5) h = make_open<PatowskiFH>(2, std::string(comps), (size_t) fh_order);
         else throw std::runtime_error("unknown kind");
         return h;
     } catch (const std::exception& e) { if (errbuf) { strncpy(errbuf, e.what(), errcap - 1); errbuf[errcap - 1] = 0; } return nullptr; }

@@ -56,3 +56,33 @@ def test_ideal_gas_viscosity_runs_on_generic_model():
     kin = model("tt_ar")
     eta = kin.viscosity(300.0, 0.024, [1.0], N=2)
     assert 2.0e-5 < eta < 2.6e-5            # argon at 300 K: 22.7 uPa s
+
+
+LJS = dict(np.load(os.path.join(os.path.dirname(__file__), "golden", "ljs_transport_reference.npz")))    # oracle/make_golden.py ljs
+
+
+@pytest.mark.parametrize("k", range(4))
+def test_ljs_ret_state_point(k):
+    """Revised Enskog theory for the LJ/spline fluid: LJSpline::saft_rdf, LJSpline::omega (correlation branch for T* > 0.4),
+    EWCA transfer lengths, K-factors, viscosity and the three thermal-conductivity contributions (N = 2)."""
+    import kineticgas_b200 as kg
+    kin = _cache.setdefault("ljs_ret", kg.LJSpline(N=2, is_idealgas=False))
+    key = f"ljs_{k}"
+    T, Vm, rho = LJS[key + "_in"][:3]
+    r = kin._run(T, Vm, [1.0], 2, 1, ["rdf", "K", "K_prime"])
+    assert np.max(np.abs(r["rdf"][0] / LJS[key + "_rdf"] - 1)) < 1e-9
+    assert np.max(np.abs(r["K"][0] / LJS[key + "_K"] - 1)) < 1e-6
+    assert np.max(np.abs(r["K_prime"][0] / LJS[key + "_Kp"] - 1)) < 1e-6
+    assert np.max(np.abs(kin.get_mtl(rho, T, [1.0]) / LJS[key + "_mtl"] - 1)) < 1e-6
+    assert np.max(np.abs(kin.get_etl(rho, T, [1.0]) / LJS[key + "_etl"] - 1)) < 1e-6
+    om, _, _, is_corr = kin.tcache([T], 2, 1 | 2).fetch()
+    ls, rs = kin.tcache([T], 2, 1 | 2).lr()
+    for idx, (l, rr) in enumerate(zip(ls.tolist(), rs.tolist())):
+        name = key + f"_omega_{l}_{rr}"
+        if name in LJS:
+            assert abs(om[0, 0, idx] / float(LJS[name]) - 1) < 1e-6, (l, rr, bool(is_corr[0, 0, idx]))
+    assert abs(kin.viscosity(T, Vm, [1.0], N=2) / float(LJS[key + "_viscosity"]) - 1) < 1e-6
+    c = LJS[key + "_contribs"]
+    lam = kin.thermal_conductivity(T, Vm, [1.0], N=2, idealgas=False, contributions="tdi", eos_inputs={"cp_ideal": LJS[key + "_cp"][None, :]})
+    for i, name in enumerate("tdi"):
+        assert abs(lam[name] - c[i]) <= 1e-6 * abs(c).sum()
