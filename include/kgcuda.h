@@ -121,11 +121,19 @@ void kg_omega_plan_destroy(kg_omega_plan* p);
 /* Counters of the last run of a plan (algorithmic work and kernel time, for roofline accounting):
  *  out[0] lattice nodes whose chi was evaluated (touched by the adaptive mesh)   out[1] tanh-sinh nodes of those theta integrals
  *  out[2] columns whose theta_lim was evaluated                                   out[3] tanh-sinh nodes of those
- *  out[4] milliseconds in the chi kernel (CUDA events on the model stream)        out[5] ms in the theta_lim kernel
+ *  out[4] milliseconds in the theta kernels (CUDA events on the model stream)      out[5] tanh-sinh node evaluations actually executed
  *  out[6] ms in the mesh kernels          out[7] number of kernel launches        out[8] refinement passes
  *  out[9] H2D bytes of plan creation      out[10] D2H bytes of the last fetch     out[11] bytes of lattice + mask pools in HBM
  *  out[12] largest cell list of one refinement level   out[13] cell-list capacity   out[14] its hard bound   out[15] times it was grown */
 int kg_omega_plan_counters(kg_omega_plan* p, double* out16);
+/* Quadrature accounting of the last run: out[0] tanh-sinh nodes of the reference's sums (the algorithmic count of SURVEY 8d),
+ * out[1] node evaluations executed (the strided Euler-Maclaurin sum touches ~1/7 of them), out[2] theta integrals that were
+ * rejected by the stride-8 / stride-16 consistency check and summed node by node, out[3] theta integrals in total. */
+int kg_omega_plan_quadrature_stats(kg_omega_plan* p, double* out4);
+/* Validation switch, process wide: 1 = every theta integral is summed node by node exactly like tanh_sinh
+ * (cpp/Integration/Integration.cpp:417-437); 0 (default) = strided sum with end corrections (same result to ~4e-13, same
+ * stop index). The environment variable KG_TS_EXACT=1 selects the exact mode at model creation. */
+int kg_set_exact_quadrature(int exact);
 
 
 /* ================================================================================================================

@@ -3,6 +3,9 @@
 #include "kg_device.cuh"
 #include "../../include/kgcuda.h"
 #include <string>
+#include <mutex>
+#include <cstdio>
+#include <cstdlib>
 #include <vector>
 #include <map>
 #include <unordered_map>
@@ -10,6 +13,23 @@
 
 #define CUDA_OK(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { \
     set_error(std::string(#expr) + ": " + cudaGetErrorString(e_)); return -2; } } while (0)
+
+// Debug aid (KG_TRACE_ERRORS=1): report the entry point that leaves a CUDA error behind on exit
+struct KgTrace {
+    const char* name;
+    explicit KgTrace(const char* n) : name(n) {
+        static const bool on = getenv("KG_TRACE_ERRORS") != nullptr;
+        if (!on) { name = nullptr; return; }
+        const cudaError_t e = cudaPeekAtLastError();
+        if (e != cudaSuccess) fprintf(stderr, "[kg trace] error present on ENTRY of %s: %s\n", n, cudaGetErrorString(e));
+    }
+    ~KgTrace() {
+        if (!name) return;
+        const cudaError_t e = cudaPeekAtLastError();
+        if (e != cudaSuccess) fprintf(stderr, "[kg trace] error present on EXIT of %s: %s\n", name, cudaGetErrorString(e));
+    }
+};
+#define KG_TRACE() KgTrace kg_trace_(__func__)
 
 struct kg_model {
     int device = 0, ncomps = 0, npairs = 0, is_singlecomp = 0, ntpad = 2;
@@ -74,6 +94,23 @@ int kg_genpot_build(const kg_potential_desc_ex& d, double T, kg::GenPot& out, st
 // Per-(T, pair) coefficient pool of a batch: the caller's coeff_T for power-sum models, the folded potentials for
 // T-dependent generic models (built into buf), NULL otherwise. Layout [nT][npairs][m->coeff_stride].
 int kg_effective_coeff(kg_model* m, int nT, const double* T, const double* coeff_T_user, std::vector<double>& buf, const double** out);
+
+// Live plans / caches, process wide. A model destroys its remaining children, and destroying a child whose model is already
+// gone (garbage collectors finalise in any order) is a no-op instead of a use-after-free.
+struct KgRegistry {
+    std::mutex mu;
+    std::map<void*, kg_model*> owner;       // child handle -> model
+    static KgRegistry& get() { static KgRegistry r; return r; }
+    void add(void* child, kg_model* m) { std::lock_guard<std::mutex> g(mu); owner[child] = m; }
+    bool remove(void* child) { std::lock_guard<std::mutex> g(mu); return owner.erase(child) > 0; }     // false: unknown / already destroyed
+    std::vector<void*> children_of(kg_model* m) {
+        std::lock_guard<std::mutex> g(mu);
+        std::vector<void*> v;
+        for (auto& kv : owner) if (kv.second == m) v.push_back(kv.first);
+        return v;
+    }
+};
+void kg_destroy_child(void* child);          // kg_omega.cu: dispatches to kg_omega_plan_destroy / kg_tcache_destroy
 
 template<class T> inline cudaError_t kg_dmalloc(kg_model* m, T** out, size_t bytes) { return m->dmalloc_bytes((void**) out, bytes); }
 

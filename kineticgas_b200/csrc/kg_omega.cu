@@ -24,6 +24,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <string>
 #include <vector>
 #include <algorithm>
@@ -350,12 +351,12 @@ theta_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
              const double* const* __restrict__ rows_by_pair, const double* __restrict__ coeff_pool,
              const WorkEntry* __restrict__ list, const int* __restrict__ offsets, const int* __restrict__ pair_task_start, int npairs,
              int* __restrict__ tile_counters, double* __restrict__ tab_pool, double* __restrict__ lim_pool, int* __restrict__ status_pool,
-             unsigned long long* __restrict__ counters) {
+             unsigned long long* __restrict__ counters, int* __restrict__ redo_list, int* __restrict__ redo_count) {
     extern __shared__ double srows[];
     __shared__ PairParams spair;
     constexpr int W = 2 + NT;
     const int lane = threadIdx.x & 31;
-    unsigned long long my_nodes = 0, my_evals = 0, my_lim_nodes = 0, my_lim_evals = 0;
+    unsigned long long my_nodes = 0, my_evals = 0, my_lim_nodes = 0, my_lim_evals = 0, my_exec = 0;
     for (int p = 0; p < npairs; p++) {
         const int seg0 = offsets[pair_task_start[p]], seg1 = offsets[pair_task_start[p + 1]];
         if (seg1 == seg0) continue;
@@ -379,16 +380,77 @@ theta_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
                 const bool is_lim = (we.ny == LIM_ROW);
                 const double b = is_lim ? 100.0 : lattice_coord(we.ny, rg.db);   // theta_lim: b = 100 sigma (Spherical.cpp:316)
                 const double* coeff = (item.coeff_off >= 0) ? coeff_pool + item.coeff_off : nullptr;
-                double R; unsigned nodes = 0; int st = 0;
-                const double I = lane_theta_integral<NT>(spair, coeff, srows, grows, KS_ROWS, item.T, g, b, R, nodes, st);
-                if (is_lim) { lim_pool[item.col_off + we.nx] = I; my_lim_nodes += nodes; my_lim_evals++; }
-                else { tab_pool[item.tab_off + (long long) we.nx * rg.ny + we.ny] = I; my_nodes += nodes; my_evals++; }
-                if (st) atomicOr(&status_pool[we.item], st);
+                unsigned nodes = 0, ex = 0; int st = 0; bool redo;
+                const double I = lane_theta_integral_defer<NT>(spair, coeff, srows, grows, KS_ROWS, item.T, g, b, nodes, ex, st, redo);
+                my_exec += ex;
+                if (redo) redo_list[atomicAdd(redo_count, 1)] = e;        // summed node by node by theta_redo_kernel
+                else {
+                    if (is_lim) { lim_pool[item.col_off + we.nx] = I; my_lim_nodes += nodes; my_lim_evals++; }
+                    else { tab_pool[item.tab_off + (long long) we.nx * rg.ny + we.ny] = I; my_nodes += nodes; my_evals++; }
+                    if (st) atomicOr(&status_pool[we.item], st);
+                }
             }
             __syncwarp();
         }
     }
-    // counters: [0] chi evals [1] chi nodes [2] lim evals [3] lim nodes
+    // counters: [0] chi evals [1] chi nodes [2] lim evals [3] lim nodes [4] node evaluations actually executed [5] redo entries
+    for (int off = 16; off > 0; off >>= 1) {
+        my_exec += __shfl_down_sync(0xffffffffu, my_exec, off);
+        my_nodes += __shfl_down_sync(0xffffffffu, my_nodes, off);
+        my_evals += __shfl_down_sync(0xffffffffu, my_evals, off);
+        my_lim_nodes += __shfl_down_sync(0xffffffffu, my_lim_nodes, off);
+        my_lim_evals += __shfl_down_sync(0xffffffffu, my_lim_evals, off);
+    }
+    if (lane == 0) {
+        if (my_evals) { atomicAdd(&counters[0], my_evals); atomicAdd(&counters[1], my_nodes); }
+        if (my_lim_evals) { atomicAdd(&counters[2], my_lim_evals); atomicAdd(&counters[3], my_lim_nodes); }
+        if (my_exec) atomicAdd(&counters[4], my_exec);
+    }
+}
+
+// Entries whose strided sum was rejected: the reference's node-by-node sum, rows read through L1/L2 (no staging: the list is
+// short and mixes pairs). Persistent warps pull 32-entry tiles until the device-side count is exhausted.
+template<int NT>
+__global__ void __launch_bounds__(128)
+theta_redo_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes, const PairParams* __restrict__ pairs,
+                  const double* const* __restrict__ rows_by_pair, const double* __restrict__ coeff_pool, const WorkEntry* __restrict__ list,
+                  const int* __restrict__ redo_list, const int* __restrict__ redo_count, int* __restrict__ tile_counter,
+                  double* __restrict__ tab_pool, double* __restrict__ lim_pool, int* __restrict__ status_pool, unsigned long long* __restrict__ counters) {
+  if constexpr (NT != 1) {               // generic potentials (NT == 1) never defer
+    const int lane = threadIdx.x & 31, n = *redo_count;
+    unsigned long long my_nodes = 0, my_evals = 0, my_lim_nodes = 0, my_lim_evals = 0;
+    for (;;) {
+        int tile = 0;
+        if (lane == 0) tile = atomicAdd(tile_counter, 1);
+        tile = __shfl_sync(0xffffffffu, tile, 0);
+        if (tile * 32 >= n) break;
+        const int q = tile * 32 + lane;
+        if (q < n) {
+            const WorkEntry we = list[redo_list[q]];
+            const Item item = items[we.item];
+            const Regime rg = regimes[item.regime];
+            const PairParams pp = pairs[item.pair];
+            const double* __restrict__ rows = rows_by_pair[item.pair];
+            const double g = lattice_coord(we.nx, rg.dg);
+            const bool is_lim = (we.ny == LIM_ROW);
+            const double b = is_lim ? 100.0 : lattice_coord(we.ny, rg.db);
+            const double* coeff = (item.coeff_off >= 0) ? coeff_pool + item.coeff_off : nullptr;
+            Lane<NT> c;
+            make_lane<NT>(c, pp, coeff, item.T, g, b);
+            int st = 0; unsigned nodes = 0;
+            const double R = get_R<NT>(c, g, st);
+            double A[NT];
+            const double s = 1.0 / R;
+#pragma unroll
+            for (int t = 0; t < NT; t++) A[t] = c.Bt[t] * pow(s, c.lam[t]);
+            const double qq = R / b;
+            const double I = theta_integral<NT>(rows, rows, 0, A, qq * qq, nodes, st);
+            if (is_lim) { lim_pool[item.col_off + we.nx] = I; my_lim_nodes += nodes; my_lim_evals++; }
+            else { tab_pool[item.tab_off + (long long) we.nx * rg.ny + we.ny] = I; my_nodes += nodes; my_evals++; }
+            if (st) atomicOr(&status_pool[we.item], st);
+        }
+        __syncwarp();
+    }
     for (int off = 16; off > 0; off >>= 1) {
         my_nodes += __shfl_down_sync(0xffffffffu, my_nodes, off);
         my_evals += __shfl_down_sync(0xffffffffu, my_evals, off);
@@ -398,7 +460,9 @@ theta_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
     if (lane == 0) {
         if (my_evals) { atomicAdd(&counters[0], my_evals); atomicAdd(&counters[1], my_nodes); }
         if (my_lim_evals) { atomicAdd(&counters[2], my_lim_evals); atomicAdd(&counters[3], my_lim_nodes); }
+        if (my_evals + my_lim_evals) { atomicAdd(&counters[4], my_nodes + my_lim_nodes); atomicAdd(&counters[5], my_evals + my_lim_evals); }
     }
+  }
 }
 
 // finalize: chi = PI - 2 (I - I_lim + PI/2) (cpp/Spherical.cpp:269,464), store cos(chi), publish the node as known.
@@ -535,6 +599,7 @@ int finish_model(kg_model* m, int device, kg_model** out) {
     if (!cu(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties")) { delete m; return -2; }
     m->sm_count = prop.multiProcessorCount;
     if (!cu(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking), "cudaStreamCreate")) { delete m; return -2; }
+    if (const char* ev = getenv("KG_TS_EXACT")) { const int v = atoi(ev) ? 1 : 0; cudaMemcpyToSymbol(c_ts_exact, &v, sizeof(int)); }
     bool ok = cu(set_theta_smem<1>(), "smem attr") && cu(set_theta_smem<2>(), "smem attr") && cu(set_theta_smem<4>(), "smem attr") && cu(set_theta_smem<6>(), "smem attr");
     if (ok && m->generic) {
         std::vector<GenPot> base(m->npairs);
@@ -574,6 +639,7 @@ int check_device(int device) {
 } // namespace
 
 extern "C" int kg_model_create(const kg_potential_desc* pairs, int ncomps, const double* mass, int is_singlecomp, int device, kg_model** out) {
+    KG_TRACE();
     auto fail = [&](const std::string& s) { g_create_error = s; return -1; };
     if (!pairs || !mass || !out || ncomps < 1) return fail("kg_model_create: invalid argument");
     if (check_device(device)) return -1;
@@ -591,6 +657,7 @@ extern "C" int kg_model_create(const kg_potential_desc* pairs, int ncomps, const
 }
 
 extern "C" int kg_model_create_ex(const kg_potential_desc_ex* pairs, int ncomps, const double* mass, int is_singlecomp, int device, kg_model** out) {
+    KG_TRACE();
     auto fail = [&](const std::string& s) { g_create_error = s; return -1; };
     if (!pairs || !mass || !out || ncomps < 1) return fail("kg_model_create_ex: invalid argument");
     if (check_device(device)) return -1;
@@ -611,9 +678,24 @@ extern "C" int kg_model_create_ex(const kg_potential_desc_ex* pairs, int ncomps,
     return finish_model(m, device, out);
 }
 
+namespace { std::map<void*, int> g_child_kind; std::mutex g_child_mu; }     // 0 = plan, 1 = tcache
+void kg_register_child(void* child, kg_model* m, int kind) {
+    { std::lock_guard<std::mutex> g(g_child_mu); g_child_kind[child] = kind; }
+    KgRegistry::get().add(child, m);
+}
+extern "C" void kg_tcache_destroy(kg_tcache* c);
+void kg_destroy_child(void* child) {
+    int kind = -1;
+    { std::lock_guard<std::mutex> g(g_child_mu); auto f = g_child_kind.find(child); if (f != g_child_kind.end()) { kind = f->second; g_child_kind.erase(f); } }
+    if (kind == 0) kg_omega_plan_destroy((kg_omega_plan*) child);
+    else if (kind == 1) kg_tcache_destroy((kg_tcache*) child);
+}
+
 extern "C" void kg_model_destroy(kg_model* m) {
+    KG_TRACE();
     if (!m) return;
     cudaSetDevice(m->device);
+    for (void* child : KgRegistry::get().children_of(m)) kg_destroy_child(child);
     for (double* p : m->d_rows) cudaFree(p);
     if (m->d_rows_by_pair) cudaFree(m->d_rows_by_pair);
     if (m->d_pairs) cudaFree(m->d_pairs);
@@ -627,6 +709,7 @@ extern "C" void kg_model_destroy(kg_model* m) {
 }
 
 extern "C" int kg_model_set_stream(kg_model* m, void* stream) {
+    KG_TRACE();
     if (!m) return -1;
     cudaSetDevice(m->device);
     if (m->stream && m->own_stream) { cudaStreamSynchronize(m->stream); cudaStreamDestroy(m->stream); }
@@ -637,6 +720,7 @@ extern "C" int kg_model_set_stream(kg_model* m, void* stream) {
 
 extern "C" int kg_chi_points(kg_model* m, int pair, double T, int n, const double* g, const double* b_red,
                              const double* coeff, double* chi_out, double* R_out, int32_t* status) {
+    KG_TRACE();
     if (!m) return -1;
     auto set_error = [&](const std::string& s) { m->err = s; };
     if (pair < 0 || pair >= m->npairs || n < 0 || !g || !b_red) { set_error("kg_chi_points: invalid argument"); return -1; }
@@ -708,6 +792,7 @@ __global__ void potential_points_kernel(PairParams pp, const double* __restrict_
 }
 
 extern "C" int kg_potential_points(kg_model* m, int pair, double T, int n, const double* r, double* u_out, double* du_out) {
+    KG_TRACE();
     if (!m) return -1;
     auto set_error = [&](const std::string& s) { m->err = s; };
     if (pair < 0 || pair >= m->npairs || n < 0 || !r) { set_error("kg_potential_points: invalid argument"); return -1; }
@@ -757,6 +842,7 @@ struct kg_omega_plan {
     double *d_W_out = nullptr, *d_omega_out = nullptr;  // [nT][npairs][nlr]
     int *d_status = nullptr, *d_flags = nullptr, *d_tile_counter = nullptr;
     int* d_perm = nullptr;                              // item -> output slot
+    int* d_redo = nullptr; int* d_redo_ctl = nullptr;  // redo list of the current pass; [0] count, [1] tile counter
     int* d_active = nullptr; unsigned long long* d_active_mask = nullptr; long long* d_active_cell_off = nullptr; int nactive = 0;   // items with work, their (l,r) sets
     int max_cells_seen = 0, regrows = 0;
     int* d_pair_task_start = nullptr;                   // [npairs+1] first column task of each pair
@@ -781,6 +867,7 @@ __global__ void permute_kernel(const double* __restrict__ W, const Item* __restr
 }
 }
 
+static void plan_free(kg_omega_plan* p);
 extern "C" int kg_omega_plan_create(kg_model* m, int nT, const double* T, int nlr, const int32_t* l, const int32_t* r,
                                     const double* coeff_T, kg_omega_plan** out) {
     return kg_omega_plan_create_masked(m, nT, T, nlr, l, r, coeff_T, nullptr, out);
@@ -788,6 +875,7 @@ extern "C" int kg_omega_plan_create(kg_model* m, int nT, const double* T, int nl
 
 extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T, int nlr, const int32_t* l, const int32_t* r,
                                            const double* coeff_T, const uint8_t* need, kg_omega_plan** out) {
+    KG_TRACE();
     if (!m) return -1;
     auto set_error = [&](const std::string& s) { m->err = s; };
     if (nT < 1 || !T || nlr < 1 || !l || !r || !out) { set_error("kg_omega_plan_create: invalid argument"); return -1; }
@@ -886,7 +974,7 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
     }
     p->max_list = cap;
 
-#define PLAN_CUDA(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { set_error(std::string(#expr) + ": " + cudaGetErrorString(e_)); kg_omega_plan_destroy(p); return -2; } } while (0)
+#define PLAN_CUDA(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { set_error(std::string(#expr) + ": " + cudaGetErrorString(e_)); plan_free(p); return -2; } } while (0)
     PLAN_CUDA(kg_dmalloc(m, &p->d_items, p->nitems * sizeof(Item)));
     PLAN_CUDA(kg_dmalloc(m, &p->d_regimes, 5 * sizeof(Regime)));
     PLAN_CUDA(kg_dmalloc(m, &p->d_tab, p->tab_doubles * sizeof(double)));
@@ -904,7 +992,7 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
     // small batches take the hard bound outright (never grows); large ones start from the estimate, at least 32 M cells
     p->cell_cap = std::min(p->cell_cap_limit, std::max(p->cell_cap, (long long) 32 << 20));
     p->cell_cap = std::max(p->cell_cap, p->ncells0);
-    if (p->nitems >= (1 << 22) || nlr > 64 || p->cell_cap >= (1LL << 31)) { set_error("kg_omega_plan_create: batch too large, split the T grid"); kg_omega_plan_destroy(p); return -1; }
+    if (p->nitems >= (1 << 22) || nlr > 64 || p->cell_cap >= (1LL << 31)) { set_error("kg_omega_plan_create: batch too large, split the T grid"); plan_free(p); return -1; }
     PLAN_CUDA(kg_dmalloc(m, &p->d_cells[0], p->cell_cap * sizeof(Cell)));
     PLAN_CUDA(kg_dmalloc(m, &p->d_cells[1], p->cell_cap * sizeof(Cell)));
     PLAN_CUDA(kg_dmalloc(m, &p->d_ncells, 2 * sizeof(int)));
@@ -925,6 +1013,8 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
     PLAN_CUDA(cudaMemcpy(p->d_active_mask, active_mask.data(), active.size() * sizeof(unsigned long long), cudaMemcpyHostToDevice));
     PLAN_CUDA(cudaMemcpy(p->d_active_cell_off, active_cell_off.data(), active.size() * sizeof(long long), cudaMemcpyHostToDevice));
     PLAN_CUDA(kg_dmalloc(m, &p->d_counters, 8 * sizeof(unsigned long long)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_redo, std::max<long long>(1, p->max_list) * sizeof(int)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_redo_ctl, 2 * sizeof(int)));
     p->h_pinned = m->h_pinned;
     if (coeff_T) {
         PLAN_CUDA(kg_dmalloc(m, &p->d_coeff, (size_t) nT * Np * m->coeff_stride * sizeof(double)));
@@ -941,28 +1031,37 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
     p->h2d_bytes = (long long) p->nitems * sizeof(Item) + sizeof(regs) + (long long) p->ntasks * sizeof(int2) + gfac.size() * sizeof(double)
                  + 2LL * nlr * sizeof(int) + (long long) p->nitems * sizeof(int) + (coeff_T ? (long long) nT * Np * m->coeff_stride * sizeof(double) : 0);
 #undef PLAN_CUDA
+    kg_register_child(p, m, 0);
     *out = p;
     return 0;
 }
 
+static void plan_free(kg_omega_plan* p);
 extern "C" void kg_omega_plan_destroy(kg_omega_plan* p) {
-    if (!p) return;
+    KG_TRACE();
+    if (!p || !KgRegistry::get().remove(p)) return;       // unknown handle: already destroyed together with its model
+    plan_free(p);
+}
+static void plan_free(kg_omega_plan* p) {
     cudaSetDevice(p->device);
     void* ptrs[] = {p->d_items, p->d_regimes, p->d_tab, p->d_want, p->d_known, p->d_lim, p->d_have_lim, p->d_tasks, p->d_counts,
                     p->d_offsets, p->d_list, p->d_gfac, p->d_lr_l, p->d_lr_ri, p->d_coeff, p->d_W, p->d_omega, p->d_W_out,
                     p->d_omega_out, p->d_status, p->d_flags, p->d_tile_counter, p->d_perm, p->d_counters, p->d_cells[0], p->d_cells[1], p->d_ncells, p->d_pair_task_start,
-                    p->d_active, p->d_active_mask, p->d_active_cell_off};
+                    p->d_active, p->d_active_mask, p->d_active_cell_off, p->d_redo, p->d_redo_ctl};
     for (void* q : ptrs) p->m->dfree(q);
     for (int k = 0; k < 4; k++) if (p->ev[k]) cudaEventDestroy(p->ev[k]);
     delete p;
 }
 
 extern "C" int kg_omega_plan_run(kg_omega_plan* p) {
+    KG_TRACE();
     if (!p) return -1;
     kg_model* m = p->m;
     auto set_error = [&](const std::string& s) { m->err = s; };
     CUDA_OK(cudaSetDevice(m->device));
     cudaStream_t s = m->stream;
+#define LAUNCHED(name) do { cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { set_error(std::string("kg_omega_plan_run: launch of " name ": ") + cudaGetErrorString(e_)); return -2; } } while (0)
+    LAUNCHED("(error left by an earlier call)");
     CUDA_OK(cudaMemsetAsync(p->d_want, 0, p->mask_words * sizeof(unsigned), s));
     CUDA_OK(cudaMemsetAsync(p->d_known, 0, p->mask_words * sizeof(unsigned), s));
     CUDA_OK(cudaMemsetAsync(p->d_have_lim, 0, p->ncols_total, s));
@@ -977,6 +1076,7 @@ extern "C" int kg_omega_plan_run(kg_omega_plan* p) {
     CUDA_OK(cudaEventRecord(p->ev[0], s));
     if (p->nactive > 0)
         mesh_init_kernel<<<p->nactive, 128, 0, s>>>(p->d_items, p->d_regimes, p->d_want, p->d_active, p->d_active_mask, p->d_active_cell_off, p->d_cells[0]);
+    LAUNCHED("mesh_init_kernel");
     CUDA_OK(cudaEventRecord(p->ev[1], s));
     p->launches += 1;
     long long n_in = p->ncells0;
@@ -986,7 +1086,9 @@ extern "C" int kg_omega_plan_run(kg_omega_plan* p) {
         p->passes = pass + 1;
         // 1. theta integrals of every newly marked lattice node
         count_kernel<<<tgrid, 256, 0, s>>>(p->d_items, p->d_regimes, p->d_tasks, p->ntasks, p->d_want, p->d_known, p->d_have_lim, p->d_counts);
+        LAUNCHED("count_kernel");
         scan_kernel<<<1, 1024, 0, s>>>(p->d_counts, p->d_offsets, p->ntasks);
+        LAUNCHED("scan_kernel");
         CUDA_OK(cudaMemcpyAsync(&p->h_pinned[1], p->d_offsets + p->ntasks, sizeof(int), cudaMemcpyDeviceToHost, s));
         CUDA_OK(cudaStreamSynchronize(s));
         cudaEventElapsedTime(&ms, p->ev[0], p->ev[1]); p->ms_mesh += ms;
@@ -995,18 +1097,25 @@ extern "C" int kg_omega_plan_run(kg_omega_plan* p) {
         if (nlist > p->max_list) { set_error("kg_omega_plan_run: work list overflow"); return -3; }
         if (nlist > 0) {
             fill_kernel<<<tgrid, 256, 0, s>>>(p->d_items, p->d_regimes, p->d_tasks, p->ntasks, p->d_want, p->d_known, p->d_have_lim, p->d_offsets, p->d_list);
+            LAUNCHED("fill_kernel");
             CUDA_OK(cudaMemsetAsync(p->d_tile_counter, 0, (m->npairs + 1) * sizeof(int), s));
+            CUDA_OK(cudaMemsetAsync(p->d_redo_ctl, 0, 2 * sizeof(int), s));
             const int ntiles = (nlist + THETA_THREADS - 1) / THETA_THREADS;
             const int grid = std::min(ntiles, 2 * m->sm_count);
             CUDA_OK(cudaEventRecord(p->ev[2], s));
 #define LAUNCH_THETA(NT) theta_kernel<NT><<<grid, THETA_THREADS, smem, s>>>(p->d_items, p->d_regimes, m->d_pairs, m->d_rows_by_pair, p->d_coeff, \
-                p->d_list, p->d_offsets, p->d_pair_task_start, m->npairs, p->d_tile_counter, p->d_tab, p->d_lim, p->d_status, p->d_counters)
+                p->d_list, p->d_offsets, p->d_pair_task_start, m->npairs, p->d_tile_counter, p->d_tab, p->d_lim, p->d_status, p->d_counters, \
+                p->d_redo, p->d_redo_ctl); \
+            LAUNCHED("theta_kernel"); \
+            if (NT != 1) theta_redo_kernel<NT><<<2 * m->sm_count, 128, 0, s>>>(p->d_items, p->d_regimes, m->d_pairs, m->d_rows_by_pair, p->d_coeff, p->d_list, \
+                p->d_redo, p->d_redo_ctl, p->d_redo_ctl + 1, p->d_tab, p->d_lim, p->d_status, p->d_counters)
             switch (m->ntpad) { case 1: LAUNCH_THETA(1); break; case 2: LAUNCH_THETA(2); break; case 4: LAUNCH_THETA(4); break; default: LAUNCH_THETA(6); break; }
 #undef LAUNCH_THETA
+            LAUNCHED("theta_redo_kernel");
             CUDA_OK(cudaEventRecord(p->ev[3], s));
             finalize_kernel<<<(nlist + 255) / 256, 256, 0, s>>>(p->d_items, p->d_regimes, p->d_list, p->d_offsets + p->ntasks, p->d_tab, p->d_lim,
                                                                p->d_known, p->d_have_lim);
-            p->launches += 3;
+            p->launches += 4;
         }
         // 2. evaluate this level's cells, emit the next level
         CUDA_OK(cudaMemsetAsync(p->d_ncells, 0, sizeof(int), s));
@@ -1045,6 +1154,7 @@ extern "C" int kg_omega_plan_run(kg_omega_plan* p) {
 }
 
 extern "C" int kg_omega_plan_sync(kg_omega_plan* p) {
+    KG_TRACE();
     if (!p) return -1;
     auto set_error = [&](const std::string& s) { p->m->err = s; };
     CUDA_OK(cudaStreamSynchronize(p->m->stream));
@@ -1052,6 +1162,7 @@ extern "C" int kg_omega_plan_sync(kg_omega_plan* p) {
 }
 
 extern "C" int kg_omega_plan_fetch(kg_omega_plan* p, double* omega, double* w, int32_t* status) {
+    KG_TRACE();
     if (!p) return -1;
     kg_model* m = p->m;
     auto set_error = [&](const std::string& s) { m->err = s; };
@@ -1074,6 +1185,7 @@ extern "C" int kg_omega_plan_fetch(kg_omega_plan* p, double* omega, double* w, i
 extern "C" const double* kg_omega_plan_omega_dev(const kg_omega_plan* p) { return p ? p->d_omega_out : nullptr; }
 
 extern "C" int kg_omega_plan_export_dev(kg_omega_plan* p, double* omega_dev, double* w_dev) {
+    KG_TRACE();
     if (!p) return -1;
     auto set_error = [&](const std::string& s) { p->m->err = s; };
     const size_t n = (size_t) p->nitems * p->nlr;
@@ -1083,6 +1195,7 @@ extern "C" int kg_omega_plan_export_dev(kg_omega_plan* p, double* omega_dev, dou
 }
 
 extern "C" int kg_omega_plan_counters(kg_omega_plan* p, double* out16) {
+    KG_TRACE();
     if (!p || !out16) return -1;
     auto set_error = [&](const std::string& s) { p->m->err = s; };
     unsigned long long c[8];
@@ -1091,12 +1204,29 @@ extern "C" int kg_omega_plan_counters(kg_omega_plan* p, double* out16) {
     out16[4] = p->ms_theta; out16[5] = 0.0; out16[6] = p->ms_mesh; out16[7] = p->launches; out16[8] = p->passes;
     out16[9] = (double) p->h2d_bytes; out16[10] = (double) p->d2h_bytes;
     out16[11] = (double) (p->tab_doubles * 8 + p->mask_words * 8);
-    out16[5] = 0.0; out16[12] = (double) p->max_cells_seen; out16[13] = (double) p->cell_cap; out16[14] = (double) p->cell_cap_limit; out16[15] = (double) p->regrows;
+    out16[5] = (double) c[4]; out16[12] = (double) p->max_cells_seen; out16[13] = (double) p->cell_cap; out16[14] = (double) p->cell_cap_limit; out16[15] = (double) p->regrows;
     return 0;
+}
+
+extern "C" int kg_omega_plan_quadrature_stats(kg_omega_plan* p, double* out4) {
+    KG_TRACE();
+    if (!p || !out4) return -1;
+    auto set_error = [&](const std::string& s) { p->m->err = s; };
+    unsigned long long c[8];
+    CUDA_OK(cudaMemcpy(c, p->d_counters, sizeof(c), cudaMemcpyDeviceToHost));
+    out4[0] = (double) (c[1] + c[3]); out4[1] = (double) c[4]; out4[2] = (double) c[5]; out4[3] = (double) (c[0] + c[2]);
+    return 0;
+}
+
+extern "C" int kg_set_exact_quadrature(int exact) {
+    KG_TRACE();
+    const int v = exact ? 1 : 0;
+    return cudaMemcpyToSymbol(c_ts_exact, &v, sizeof(int)) == cudaSuccess ? 0 : -2;
 }
 
 extern "C" int kg_omega_batch(kg_model* m, int nT, const double* T, int nlr, const int32_t* l, const int32_t* r,
                               const double* coeff_T, double* omega, double* w, int32_t* status) {
+    KG_TRACE();
     kg_omega_plan* p = nullptr;
     int rc = kg_omega_plan_create(m, nT, T, nlr, l, r, coeff_T, &p);
     if (rc) return rc;
@@ -1107,6 +1237,7 @@ extern "C" int kg_omega_batch(kg_model* m, int nT, const double* T, int nlr, con
 }
 
 extern "C" int kg_measure_fp64_peak(int device, double* tflops, double* sm_mhz_est) {
+    KG_TRACE();
     if (!tflops) return -1;
     if (cudaSetDevice(device) != cudaSuccess) return -2;
     cudaDeviceProp prop;

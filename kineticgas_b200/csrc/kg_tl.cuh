@@ -206,6 +206,7 @@ void tl_gnodes(double* g) {
 } // namespace
 
 extern "C" int kg_transfer_lengths_batch(kg_model* m, int nT, const double* T, const double* coeff_T, double* mtl, double* etl, int32_t* status) {
+    KG_TRACE();
     if (!m) return -1;
     auto set_error = [&](const std::string& s) { m->err = s; };
     if (nT < 1 || !T || !mtl || !etl) { set_error("kg_transfer_lengths_batch: invalid argument"); return -1; }

@@ -788,6 +788,7 @@ struct kg_tcache {
     std::vector<double> h_mtl, h_etl;
     double ms_omega = 0, ms_tl = 0;                  // stage timings of the build (host clock around synchronised stages)
 };
+void kg_register_child(void* child, kg_model* m, int kind);      // kg_omega.cu
 
 namespace {
 
@@ -803,21 +804,27 @@ bool desc_is_mie(const kg_potential_desc& d) {
 
 } // namespace
 
-extern "C" void kg_tcache_destroy(kg_tcache* c) {
-    if (!c) return;
+static void tcache_free(kg_tcache* c) {
     cudaSetDevice(c->device);
     void* ptrs[] = {c->d_T, c->d_omega, c->d_mtl, c->d_etl, c->d_dbh, c->d_brk, c->d_mp_int};
     for (void* p : ptrs) c->m->dfree(p);
     delete c;
 }
+extern "C" void kg_tcache_destroy(kg_tcache* c) {
+    KG_TRACE();
+    if (!c || !KgRegistry::get().remove(c)) return;       // unknown handle: already destroyed together with its model
+    tcache_free(c);
+}
 
 extern "C" int kg_tcache_lr(const kg_tcache* c, int32_t* l, int32_t* r) {
+    KG_TRACE();
     if (!c) return -1;
     for (int k = 0; k < c->tm.nlr; k++) { if (l) l[k] = c->tm.lr_l[k]; if (r) r[k] = c->tm.lr_r[k]; }
     return c->tm.nlr;
 }
 
 extern "C" int kg_tcache_fetch(kg_tcache* c, double* omega, double* mtl, double* etl, uint8_t* is_correlation) {
+    KG_TRACE();
     if (!c) return -1;
     kg_model* m = c->m;
     auto set_error = [&](const std::string& s) { m->err = s; };
@@ -832,6 +839,7 @@ extern "C" int kg_tcache_fetch(kg_tcache* c, double* omega, double* mtl, double*
 }
 
 extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int nT, const double* T, const double* coeff_T, kg_tcache** out) {
+    KG_TRACE();
     if (!m) return -1;
     auto set_error = [&](const std::string& s) { m->err = s; };
     if (!opts || nT < 1 || !T || !out) { set_error("kg_tcache_create: invalid argument"); return -1; }
@@ -927,7 +935,7 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
         any_numeric |= !corr; any_corr |= corr;
     }
     int rc = 0;
-#define TC_CUDA(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { set_error(std::string(#expr) + ": " + cudaGetErrorString(e_)); kg_tcache_destroy(c); return -2; } } while (0)
+#define TC_CUDA(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { set_error(std::string(#expr) + ": " + cudaGetErrorString(e_)); tcache_free(c); return -2; } } while (0)
     TC_CUDA(upload(m, &c->d_T, c->T));
     TC_CUDA(kg_dmalloc(m, &c->d_omega, need.size() * sizeof(double)));
     cudaStream_t s = m->stream;
@@ -946,9 +954,9 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
         if (!rc) rc = kg_omega_plan_fetch(plan, nullptr, nullptr, pst.data());
         if (!rc) { double cnt[16]; if (!kg_omega_plan_counters(plan, cnt)) m->timings[4] += cnt[7]; }
         if (plan) kg_omega_plan_destroy(plan);
-        if (rc) { kg_tcache_destroy(c); return rc; }
+        if (rc) { tcache_free(c); return rc; }
         int bad = 0; for (int v : pst) bad |= v;
-        if (bad & KG_STATUS_GETR_MAXITER) { set_error("get_R reached max iter!"); kg_tcache_destroy(c); return -4; }
+        if (bad & KG_STATUS_GETR_MAXITER) { set_error("get_R reached max iter!"); tcache_free(c); return -4; }
     }
     m->timings[1] = ms_since(t_stage); t_stage = now();
     std::vector<MiePair> mp_dev(Np), mp_int((size_t) nc * nc), mp_diag(nc);
@@ -980,10 +988,10 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
         c->h_mtl.resize((size_t) nT * Np); c->h_etl.resize((size_t) nT * Np);
         std::vector<int32_t> tst((size_t) nT * Np, 0);
         rc = kg_transfer_lengths_batch(m, nT, T, coeff_T, c->h_mtl.data(), c->h_etl.data(), tst.data());
-        if (rc) { kg_tcache_destroy(c); return rc; }
+        if (rc) { tcache_free(c); return rc; }
         int bad = 0; for (int v : tst) bad |= v;
-        if (bad & KG_STATUS_BMID) { set_error("Unable to converge bmid!"); kg_tcache_destroy(c); return -4; }
-        if (bad & KG_STATUS_GETR_MAXITER) { set_error("get_R reached max iter!"); kg_tcache_destroy(c); return -4; }
+        if (bad & KG_STATUS_BMID) { set_error("Unable to converge bmid!"); tcache_free(c); return -4; }
+        if (bad & KG_STATUS_GETR_MAXITER) { set_error("get_R reached max iter!"); tcache_free(c); return -4; }
         m->timings[2] = ms_since(t_stage); m->timings[4] += m->tl_launches;
         TC_CUDA(upload(m, &c->d_mtl, c->h_mtl)); TC_CUDA(upload(m, &c->d_etl, c->h_etl));
         MiePair* d_diag = nullptr;
@@ -1007,6 +1015,7 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
 #undef TC_CUDA
     m->timings[3] = ms_since(t_stage) - m->timings[2];
     m->timings[4] += (any_corr ? 1 : 0) + (opts->is_idealgas ? 0 : 1) + 1;
+    kg_register_child(c, m, 1);
     *out = c;
     return 0;
 }
@@ -1038,13 +1047,16 @@ int launch_state(kg_tcache* c, StateArgs& a, cudaStream_t s, const double* d_x_f
     if (nn <= 8) state_kernel<8><<<grid, 128, 0, s>>>(tm, a);
     else if (nn <= 16) state_kernel<16><<<grid, 128, 0, s>>>(tm, a);
     else state_kernel<24><<<grid, 128, 0, s>>>(tm, a);
-    return cudaGetLastError() == cudaSuccess ? 0 : -2;
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { c->m->err = std::string("state kernels: ") + cudaGetErrorString(e); return -2; }
+    return 0;
 }
 
 } // namespace
 
 extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const double* T, const double* Vm, const double* x,
                                   const kg_transport_opts* opts, const kg_eos_inputs* eos, const kg_transport_out* out, int32_t* status) {
+    KG_TRACE();
     if (!m) return -1;
     auto set_error = [&](const std::string& s) { m->err = s; };
     if (n < 0 || !T || !Vm || !opts || !out) { set_error("kg_transport_batch: invalid argument"); return -1; }
@@ -1110,7 +1122,7 @@ extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const do
     cudaEvent_t ev0, ev1;
     CUDA_OK(cudaEventCreate(&ev0)); CUDA_OK(cudaEventCreate(&ev1));
     CUDA_OK(cudaEventRecord(ev0, s));
-    if (launch_state(c, a, s, a.x, d_rdf)) { set_error("kg_transport_batch: kernel launch failed"); return -2; }
+    if (launch_state(c, a, s, a.x, d_rdf)) { set_error("kg_transport_batch: kernel launch failed (" + m->err + ")"); return -2; }
     CUDA_OK(cudaEventRecord(ev1, s));
     for (auto& mp : maps) if (mp.host) CUDA_OK(cudaMemcpyAsync(mp.host, *mp.dev, mp.count * sizeof(double), cudaMemcpyDeviceToHost, s));
     if (out->rdf) {
@@ -1128,6 +1140,7 @@ extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const do
 }
 
 extern "C" int kg_last_timings(const kg_model* m, double* out8) {
+    KG_TRACE();
     if (!m || !out8) return -1;
     for (int k = 0; k < 8; k++) out8[k] = m->timings[k];
     return 0;

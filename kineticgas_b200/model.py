@@ -223,6 +223,11 @@ class OmegaPlan:
                 "h2d_bytes", "d2h_bytes", "pool_bytes", "max_cells_per_level", "cell_capacity", "cell_capacity_limit", "cell_regrows"]
         return dict(zip(keys, out.tolist()))
 
+    def quadrature_stats(self):
+        out = np.zeros(4)
+        self.model._chk(self.model.L.kg_omega_plan_quadrature_stats(self.h, _p(out)), "kg_omega_plan_quadrature_stats")
+        return dict(zip(["reference_nodes", "executed_nodes", "redo_integrals", "theta_integrals"], out.tolist()))
+
     def close(self):
         if getattr(self, "h", None):
             self.model.L.kg_omega_plan_destroy(self.h)
@@ -233,6 +238,12 @@ class OmegaPlan:
             self.close()
         except Exception:
             pass
+
+
+def set_exact_quadrature(exact):
+    """Validation switch (kg_set_exact_quadrature): node-by-node tanh-sinh sums instead of the strided ones."""
+    if _lib.lib().kg_set_exact_quadrature(int(bool(exact))) != 0:
+        raise RuntimeError("kg_set_exact_quadrature failed (no CUDA device?)")
 
 
 def measure_fp64_peak(device=0):

@@ -51,3 +51,33 @@ def test_transfer_lengths_vs_oracle(oracle_port, comp, T):
     # 1e-6 relative (north_star); these feed K-factors as tl^3
     assert abs(mtl[0, 0] / oracle_port.tl_ewca(p, T, 0) - 1) < 1e-7
     assert abs(etl[0, 0] / oracle_port.tl_ewca(p, T, 1) - 1) < 1e-7
+
+
+def test_strided_quadrature_matches_node_by_node():
+    """The Euler-Maclaurin (stride 8) theta integrals against the reference's node-by-node sums on whole adaptive lattices
+    of all five T regimes: same W to 1e-9, same number of reference nodes (i.e. the same stop index in every integral),
+    about 1/7 of the node evaluations."""
+    from kineticgas_b200 import DeviceModel, mie_desc
+    from kineticgas_b200.model import set_exact_quadrature
+    from kineticgas_b200.fluids import BOLTZMANN, AVOGADRO
+    m = DeviceModel([mie_desc(3e-10, 30.0 * BOLTZMANN, 6.0, 12.0)], [1e-3 / AVOGADRO], True)
+    T = [9.5, 14.0, 25.0, 40.0, 60.0, 300.0, 2500.0]
+    l, r = [1, 1, 2, 2, 3, 4], [1, 4, 2, 3, 3, 4]
+    res = {}
+    try:
+        for exact in (1, 0):
+            set_exact_quadrature(exact)
+            p = m.omega_plan(T, l, r)
+            p.run()
+            res[exact] = (p.fetch(want_w=True)[1], p.quadrature_stats())
+            p.close()
+    finally:
+        set_exact_quadrature(0)
+    w_exact, s_exact = res[1]
+    w_em, s_em = res[0]
+    print(s_exact, s_em, float(np.max(np.abs(w_em / w_exact - 1))))
+    assert np.max(np.abs(w_em / w_exact - 1)) < 1e-9
+    assert s_em["reference_nodes"] == s_exact["reference_nodes"] and s_em["theta_integrals"] == s_exact["theta_integrals"]
+    assert s_exact["executed_nodes"] == s_exact["reference_nodes"]
+    assert s_em["executed_nodes"] < 0.25 * s_em["reference_nodes"]
+    assert s_em["redo_integrals"] < 0.1 * s_em["theta_integrals"]
