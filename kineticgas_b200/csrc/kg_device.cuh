@@ -134,7 +134,7 @@ __device__ __forceinline__ void rootfun_d(const Lane<NT>& c, double ri, double& 
 
 // cpp/Integration/Integration.cpp:456-471 (ftol = -1: only the step criterion is live)
 template<int NT>
-__device__ double newton_usafe(const Lane<NT>& c, double x0, double dtol, int& ierr) {
+__device__ __noinline__ double newton_usafe(const Lane<NT>& c, double x0, double dtol, int& ierr) {
     int niter = 0;
     double prev_x, f, df;
     do {
@@ -150,7 +150,7 @@ __device__ double newton_usafe(const Lane<NT>& c, double x0, double dtol, int& i
 
 // cpp/Integration/Integration.cpp:494-510 (ftol = -1)
 template<int NT>
-__device__ void bracket_root_usafe(const Lane<NT>& c, double& x0, double& x1, double& f0, double& f1, double dtol) {
+__device__ __noinline__ void bracket_root_usafe(const Lane<NT>& c, double& x0, double& x1, double& f0, double& f1, double dtol) {
     while (fabs(x0 - x1) > dtol) {
         const double xm = 0.5 * (x0 + x1);
         const double fm = rootfun<NT>(c, xm);
@@ -166,7 +166,7 @@ __device__ void bracket_root_usafe(const Lane<NT>& c, double& x0, double& x1, do
 // cpp/Spherical.cpp:437-453 : head-on turning point, u(R0) = kT g^2. Reduced units; Bt already carries 1/(kT g^2),
 // so f = U - 1 and the convergence test |f / (dfdr sigma)| is unchanged by the common scale.
 template<int NT>
-__device__ double get_R0(const Lane<NT>& c) {
+__device__ __noinline__ double get_R0(const Lane<NT>& c) {
     double r = 0.9, U, dU;
     pot_eval<NT>(c, r, U, dU);
     double f = U - 1.0;
@@ -185,6 +185,32 @@ __device__ double get_R0(const Lane<NT>& c) {
     return r;
 }
 
+// The shrink loop of get_R (cpp/Spherical.cpp:381-384): r0 *= 0.95 until f(r0) >= 0. Each step scales every power-law term
+// by the constant 0.95^-lam_t, so the loop multiplies instead of re-evaluating log / exp (up to ~30 steps for b ~ 5 sigma;
+// r0 itself takes the reference's exact sequence of values, f0 differs in the last bits only and is used for its sign).
+template<int NT>
+__device__ __forceinline__ void shrink_until_nonneg(const Lane<NT>& c, double& r0, double& f0) {
+    if (!(f0 < 0)) return;
+    double p[NT], F[NT];
+    const double ls = -log(r0);
+#pragma unroll
+    for (int t = 0; t < NT; t++) { p[t] = c.Bt[t] * exp(c.lam[t] * ls); F[t] = exp(c.lam[t] * 0.05129329438755058); }    // -ln 0.95
+    int guard = 0;
+    while (f0 < 0 && guard++ < 4000) {
+        r0 *= 0.95;
+        double u = 0.0;
+#pragma unroll
+        for (int t = 0; t < NT; t++) { p[t] *= F[t]; u += p[t]; }
+        const double q = c.b / r0;
+        f0 = u + q * q - 1.0;
+    }
+}
+template<>
+__device__ __forceinline__ void shrink_until_nonneg<1>(const Lane<1>& c, double& r0, double& f0) {
+    int guard = 0;
+    while (f0 < 0 && guard++ < 4000) { r0 *= 0.95; f0 = rootfun<1>(c, r0); }
+}
+
 // cpp/Spherical.cpp:358-435 ; returns R / sigma. g enters through Bt; g < 1e-6 or b < 1e-5 -> get_R0.
 template<int NT>
 __device__ double get_R(const Lane<NT>& c, double g, int& status) {
@@ -195,8 +221,7 @@ __device__ double get_R(const Lane<NT>& c, double g, int& status) {
     else { r0 = r1 = 1; bracket_dtol = 0.05; }
     double f0 = rootfun<NT>(c, r0);
     double f1 = f0;
-    int guard = 0;
-    while (f0 < 0 && guard++ < 4000) { r0 *= 0.95; f0 = rootfun<NT>(c, r0); }
+    shrink_until_nonneg<NT>(c, r0, f0);
     if (r1 - r0 > bracket_dtol) bracket_root_usafe<NT>(c, r0, r1, f0, f1, bracket_dtol);
     if (fabs(f0) < 1e-8) return r0;
 
@@ -310,7 +335,7 @@ __device__ __noinline__ bool ts_exact4(const double* __restrict__ r0, const doub
 // The bulk of the sum runs in blocks of KG_TS_BLOCK fast nodes with one conservative high-word stop check per block;
 // a block that may contain the stop (or anything irregular) is replayed exactly, four nodes at a time.
 template<int NT>
-__device__ double theta_integral(const double* __restrict__ srows, const double* __restrict__ grows, int KS,
+__device__ __noinline__ double theta_integral(const double* __restrict__ srows, const double* __restrict__ grows, int KS,
                                  const double (&A)[NT], double c2, unsigned& nodes, int& status) {
     constexpr int W = 2 + NT;
     double Ap[NT];
@@ -367,9 +392,11 @@ __device__ __forceinline__ void fd7(const double (&f)[7], double& d1, double& d3
 
 template<int NT>
 __device__ double theta_integral_em(const double* __restrict__ srows, const double* __restrict__ grows, int KS,
-                                    const double (&A)[NT], double c2, unsigned& nodes, unsigned& exec_nodes, int& status, bool& redo) {
+                                    const double (&A)[NT], double c2, unsigned& nodes, unsigned& exec_nodes, int& status, bool& redo,
+                                    bool& redo_early) {
     constexpr int W = 2 + NT;
     constexpr int S = 8;
+    redo_early = false;
     double Ap[NT];
 #pragma unroll
     for (int t = 0; t < NT; t++) Ap[t] = c2 * A[t];
@@ -382,29 +409,61 @@ __device__ double theta_integral_em(const double* __restrict__ srows, const doub
     };
     const double t1 = ts_term<NT>(srows, Ap, c2);
     double f[7];
-#pragma unroll
-    for (int i = 0; i < 7; i++) f[i] = fast(2 + i);
+#pragma unroll 1
+    for (int i = 0; i < 7; i++) f[i] = fast(2 + i);             // rolled: executed once per integral, keep the code small
     double d1a, d3a, d5a;
     fd7(f, d1a, d3a, d5a);
     const double ga = f[0];
-    double E = ga, O = 0.0, Irun = t1 + (0.5 * S) * ga, glast = ga, gb;
+    // coarse sums in units of g: Sg = sum over coarse nodes j >= 1, Eg = the even ones; running sum I = base + S Sg
+    const double base = t1 + (0.5 * S) * ga;
+    double Sg = 0.0, Eg = 0.0, glast = ga, gb;
     int j0 = 1, bj;
+    // Blocks whose four coarse rows are staged in shared memory (practically all: sums end near node 2000 of the 2560 staged)
+    // step a pointer; the remainder selects the table per row.
+    const int j_smem = (KS - 2 - 3 * S) / S;                  // largest j0 with 2 + S (j0 + 3) <= KS
+    const double* __restrict__ rp = srows + (size_t) (1 + S) * W;      // row of coarse node j0 = 1 (node 2 + S)
     for (;;) {
         const int kb = 2 + S * j0;
         if (kb + 3 * S + 8 > KMAX) return 0.0;
-        const double g0 = fast(kb), g1 = fast(kb + S), g2 = fast(kb + 2 * S), g3 = fast(kb + 3 * S);
-        const double In = Irun + S * ((g0 + g1) + (g2 + g3));
+        double z0, c0, z1, c1, z2, c2_, z3, c3;
+        if (j0 <= j_smem) {
+            ts_fast<NT>(rp, Ap, c2, z0, c0);
+            ts_fast<NT>(rp + S * W, Ap, c2, z1, c1);
+            ts_fast<NT>(rp + 2 * S * W, Ap, c2, z2, c2_);
+            ts_fast<NT>(rp + 3 * S * W, Ap, c2, z3, c3);
+            rp += 4 * S * W;
+        } else {
+            auto rowp = [&](int k) { return ((k <= KS) ? srows : grows) + (size_t) (k - 1) * W; };
+            ts_fast<NT>(rowp(kb), Ap, c2, z0, c0);
+            ts_fast<NT>(rowp(kb + S), Ap, c2, z1, c1);
+            ts_fast<NT>(rowp(kb + 2 * S), Ap, c2, z2, c2_);
+            ts_fast<NT>(rowp(kb + 3 * S), Ap, c2, z3, c3);
+        }
+        double Sn = fma(z0, c0, Sg);
+        Sn = fma(z1, c1, Sn);
+        Sn = fma(z2, c2_, Sn);
+        Sn = fma(z3, c3, Sn);
+        const double In = fma((double) S, Sn, base);
         if (!(In < 1e300)) return 0.0;                        // NaN (radicand <= 0 somewhere) or overflow
-        const double lim = (1.02 * TS_TOL) * In;
-        if (fmin(fmin(g0, g1), fmin(g2, g3)) > lim) { O += g0 + g2; E += g1 + g3; Irun = In; glast = g3; j0 += 4; continue; }
-        if (g0 > lim && g1 > lim) { O += g0; E += g1; bj = j0 + 1; gb = g1; }
+        // every term of the block against 1.02 tol x the sum after the block, on the high words (z = g / 2 to 2^-20)
+        const int lim = __double2hiint((0.5 * 1.02 * TS_TOL) * In);
+        const int zmin = min(min(__double2hiint(z0), __double2hiint(z1)), min(__double2hiint(z2), __double2hiint(z3)));
+        if ((zmin > lim + 2) && (lim >= 0)) {
+            Eg = fma(z1, c1, Eg);
+            Eg = fma(z3, c3, Eg);
+            Sg = Sn; glast = z3 * c3; j0 += 4;
+            continue;
+        }
+        const double g0 = z0 * c0, g1 = z1 * c1, dl = (1.02 * TS_TOL) * In;
+        if (g0 > dl && g1 > dl) { Sg += g0 + g1; Eg += g1; bj = j0 + 1; gb = g1; }
         else { bj = j0 - 1; gb = glast; }
         break;
     }
-    if (bj < 8) return 0.0;
+    const double E = ga + Eg, O = Sg - Eg;
+    if (bj < 8) { redo_early = true; return 0.0; }      // the sum ends within the first ~70 nodes (g = 1e-7 column): cheap node by node
     const int b = 2 + S * bj;
     f[0] = gb;
-#pragma unroll
+#pragma unroll 1
     for (int i = 1; i < 7; i++) f[i] = fast(b + i);
     double D1, D3, D5;
     fd7(f, D1, D3, D5);
@@ -425,6 +484,39 @@ __device__ double theta_integral_em(const double* __restrict__ srows, const doub
     nodes += (unsigned) k;
     exec_nodes += (unsigned) (bj + 13 + (k - b) + 4);
     return I;
+}
+
+// Node-by-node sum of ONE theta integral by a whole warp: lane l evaluates node base + 1 + l in the exact form, a warp scan
+// gives the running sums the reference's stop rule needs, a ballot finds the first node that fails it. Used by the batched
+// kernel for the few integrals its strided sum rejects, so that no lane ever walks ~2000 nodes alone while 31 others wait.
+// All lanes must call with the same (Ap, c2). Returns I; k_out = index of the last node examined.
+template<int NT>
+__device__ double theta_integral_warp(const double* __restrict__ srows, const double* __restrict__ grows, int KS,
+                                      const double (&Ap)[NT], double c2, int& k_out, int& status) {
+    constexpr int W = 2 + NT;
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    double I = ts_term<NT>(srows, Ap, c2);                   // node 1, added unconditionally (Integration.cpp:425)
+    for (int base = 1; ; base += 32) {
+        const int k = base + 1 + lane;
+        double t = 0.0;
+        bool ok = false;
+        if (k <= KMAX) {
+            t = ts_term<NT>(((k <= KS) ? srows : grows) + (size_t) (k - 1) * W, Ap, c2);
+            ok = !(isnan(t) || isinf(t));
+        }
+        double P = ok ? t : 0.0;                              // inclusive prefix sum over the lanes
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) { const double v = __shfl_up_sync(full, P, off); if (lane >= off) P += v; }
+        ok = ok && (fabs(t) > fabs(TS_TOL * (I + (P - t))));   // against the sum before this node (Integration.cpp:431)
+        const unsigned pass = __ballot_sync(full, ok);
+        if (pass == full) { I += __shfl_sync(full, P, 31); continue; }
+        const int ff = __ffs(~pass) - 1;                      // first failing lane
+        if (ff > 0) I += __shfl_sync(full, P, ff - 1);
+        k_out = base + 1 + ff;
+        if (k_out > KMAX) { status |= 2; k_out = KMAX; }
+        return I;
+    }
 }
 
 // Lane set-up shared by every caller: Bt = eps C_t / (kT g^2) (coeff overrides C[] for T-dependent potentials)
@@ -496,13 +588,13 @@ __device__ double lane_theta_integral(const PairParams& pp, const double* coeff,
     const double R = get_R<NT>(c, g, status);
     R_out = R;
     double A[NT];
-    const double s = 1.0 / R;
+    const double ls = -log(R);
 #pragma unroll
-    for (int t = 0; t < NT; t++) A[t] = c.Bt[t] * pow(s, c.lam[t]);
+    for (int t = 0; t < NT; t++) A[t] = c.Bt[t] * exp(c.lam[t] * ls);      // (sigma/R)^lam, as pot_eval forms it
     const double q = R / b;
     if (!c_ts_exact) {
-        bool redo; unsigned ex = 0;
-        const double I = theta_integral_em<NT>(srows, grows, KS, A, q * q, nodes, ex, status, redo);
+        bool redo, early; unsigned ex = 0;
+        const double I = theta_integral_em<NT>(srows, grows, KS, A, q * q, nodes, ex, status, redo, early);
         if (!redo) return I;
     }
     return theta_integral<NT>(srows, grows, KS, A, q * q, nodes, status);
@@ -513,27 +605,35 @@ __device__ double lane_theta_integral(const PairParams& pp, const double* coeff,
 template<int NT>
 __device__ double lane_theta_integral_defer(const PairParams& pp, const double* coeff, const double* __restrict__ srows,
                                             const double* __restrict__ grows, int KS, double T, double g, double b,
-                                            unsigned& nodes, unsigned& exec_nodes, int& status, bool& redo) {
+                                            unsigned& nodes, unsigned& exec_nodes, int& status, bool& redo, double (&Ap_out)[NT], double& c2_out) {
     Lane<NT> c;
     make_lane<NT>(c, pp, coeff, T, g, b);
     int st = 0;
     const double R = get_R<NT>(c, g, st);
     double A[NT];
-    const double s = 1.0 / R;
+    const double ls = -log(R);
 #pragma unroll
-    for (int t = 0; t < NT; t++) A[t] = c.Bt[t] * pow(s, c.lam[t]);
+    for (int t = 0; t < NT; t++) A[t] = c.Bt[t] * exp(c.lam[t] * ls);      // (sigma/R)^lam, as pot_eval forms it
     const double q = R / b;
+    c2_out = q * q;
+#pragma unroll
+    for (int t = 0; t < NT; t++) Ap_out[t] = c2_out * A[t];
     unsigned nd = 0;
     double I;
     if (c_ts_exact) { redo = false; I = theta_integral<NT>(srows, grows, KS, A, q * q, nd, st); exec_nodes += nd; }
-    else I = theta_integral_em<NT>(srows, grows, KS, A, q * q, nd, exec_nodes, st, redo);
+    else {
+        bool early;
+        I = theta_integral_em<NT>(srows, grows, KS, A, q * q, nd, exec_nodes, st, redo, early);
+        // whole columns end early together (neighbouring lanes share g), so summing them here costs no divergence
+        if (redo && early) { redo = false; nd = 0; I = theta_integral<NT>(srows, grows, KS, A, q * q, nd, st); exec_nodes += nd; }
+    }
     if (!redo) { nodes += nd; status |= st; }
     return I;
 }
 template<>
 __device__ inline double lane_theta_integral_defer<1>(const PairParams& pp, const double* coeff, const double* __restrict__ srows,
                                                       const double* __restrict__ grows, int KS, double T, double g, double b,
-                                                      unsigned& nodes, unsigned& exec_nodes, int& status, bool& redo);
+                                                      unsigned& nodes, unsigned& exec_nodes, int& status, bool& redo, double (&Ap_out)[1], double& c2_out);
 template<>
 __device__ inline double lane_theta_integral<1>(const PairParams& pp, const double* coeff, const double* __restrict__ srows,
                                                 const double* __restrict__ grows, int KS, double T, double g, double b,
@@ -547,7 +647,8 @@ __device__ inline double lane_theta_integral<1>(const PairParams& pp, const doub
 template<>
 __device__ inline double lane_theta_integral_defer<1>(const PairParams& pp, const double* coeff, const double* __restrict__ srows,
                                                       const double* __restrict__ grows, int KS, double T, double g, double b,
-                                                      unsigned& nodes, unsigned& exec_nodes, int& status, bool& redo) {
+                                                      unsigned& nodes, unsigned& exec_nodes, int& status, bool& redo, double (&Ap_out)[1], double& c2_out) {
+    Ap_out[0] = 0.0; c2_out = 0.0;
     redo = false;                  // generic potentials are always summed node by node (piecewise potentials are not smooth in k)
     double R; unsigned nd = 0;
     const double I = lane_theta_integral<1>(pp, coeff, srows, grows, KS, T, g, b, R, nd, status);

@@ -356,7 +356,7 @@ theta_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
     __shared__ PairParams spair;
     constexpr int W = 2 + NT;
     const int lane = threadIdx.x & 31;
-    unsigned long long my_nodes = 0, my_evals = 0, my_lim_nodes = 0, my_lim_evals = 0, my_exec = 0;
+    unsigned long long my_nodes = 0, my_evals = 0, my_lim_nodes = 0, my_lim_evals = 0, my_exec = 0, my_redo = 0;
     for (int p = 0; p < npairs; p++) {
         const int seg0 = offsets[pair_task_start[p]], seg1 = offsets[pair_task_start[p + 1]];
         if (seg1 == seg0) continue;
@@ -372,23 +372,44 @@ theta_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
             tile = __shfl_sync(0xffffffffu, tile, 0);
             if (tile >= ntiles) break;
             const int e = seg0 + tile * 32 + lane;
+            bool redo = false;
+            double Ap[NT], cc = 0.0, I = 0.0;
+#pragma unroll
+            for (int t = 0; t < NT; t++) Ap[t] = 0.0;
+            int st = 0; unsigned nodes = 0;
+            WorkEntry we = WorkEntry{0, 0, 0};
             if (e < seg1) {
-                const WorkEntry we = list[e];
+                we = list[e];
                 const Item item = items[we.item];
                 const Regime rg = regimes[item.regime];
                 const double g = lattice_coord(we.nx, rg.dg);
-                const bool is_lim = (we.ny == LIM_ROW);
-                const double b = is_lim ? 100.0 : lattice_coord(we.ny, rg.db);   // theta_lim: b = 100 sigma (Spherical.cpp:316)
+                const double b = (we.ny == LIM_ROW) ? 100.0 : lattice_coord(we.ny, rg.db);   // theta_lim: b = 100 sigma (Spherical.cpp:316)
                 const double* coeff = (item.coeff_off >= 0) ? coeff_pool + item.coeff_off : nullptr;
-                unsigned nodes = 0, ex = 0; int st = 0; bool redo;
-                const double I = lane_theta_integral_defer<NT>(spair, coeff, srows, grows, KS_ROWS, item.T, g, b, nodes, ex, st, redo);
+                unsigned ex = 0;
+                I = lane_theta_integral_defer<NT>(spair, coeff, srows, grows, KS_ROWS, item.T, g, b, nodes, ex, st, redo, Ap, cc);
                 my_exec += ex;
-                if (redo) redo_list[atomicAdd(redo_count, 1)] = e;        // summed node by node by theta_redo_kernel
-                else {
-                    if (is_lim) { lim_pool[item.col_off + we.nx] = I; my_lim_nodes += nodes; my_lim_evals++; }
-                    else { tab_pool[item.tab_off + (long long) we.nx * rg.ny + we.ny] = I; my_nodes += nodes; my_evals++; }
-                    if (st) atomicOr(&status_pool[we.item], st);
+            }
+            // integrals the strided sum rejected: the warp sums them node by node together, one after the other
+            if constexpr (NT != 1) {
+                unsigned pending = __ballot_sync(0xffffffffu, redo);
+                while (pending) {
+                    const int src = __ffs(pending) - 1;
+                    pending &= pending - 1;
+                    double Aw[NT];
+#pragma unroll
+                    for (int t = 0; t < NT; t++) Aw[t] = __shfl_sync(0xffffffffu, Ap[t], src);
+                    const double cw = __shfl_sync(0xffffffffu, cc, src);
+                    int kk = 0, stw = 0;
+                    const double Iw = theta_integral_warp<NT>(srows, grows, KS_ROWS, Aw, cw, kk, stw);
+                    if (lane == src) { I = Iw; nodes = (unsigned) kk; st |= stw; my_exec += (unsigned) (((kk + 31) / 32) * 32); my_redo++; }
                 }
+            }
+            if (e < seg1) {
+                const Item item = items[we.item];
+                const Regime rg = regimes[item.regime];
+                if (we.ny == LIM_ROW) { lim_pool[item.col_off + we.nx] = I; my_lim_nodes += nodes; my_lim_evals++; }
+                else { tab_pool[item.tab_off + (long long) we.nx * rg.ny + we.ny] = I; my_nodes += nodes; my_evals++; }
+                if (st) atomicOr(&status_pool[we.item], st);
             }
             __syncwarp();
         }
@@ -396,6 +417,7 @@ theta_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
     // counters: [0] chi evals [1] chi nodes [2] lim evals [3] lim nodes [4] node evaluations actually executed [5] redo entries
     for (int off = 16; off > 0; off >>= 1) {
         my_exec += __shfl_down_sync(0xffffffffu, my_exec, off);
+        my_redo += __shfl_down_sync(0xffffffffu, my_redo, off);
         my_nodes += __shfl_down_sync(0xffffffffu, my_nodes, off);
         my_evals += __shfl_down_sync(0xffffffffu, my_evals, off);
         my_lim_nodes += __shfl_down_sync(0xffffffffu, my_lim_nodes, off);
@@ -405,64 +427,8 @@ theta_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
         if (my_evals) { atomicAdd(&counters[0], my_evals); atomicAdd(&counters[1], my_nodes); }
         if (my_lim_evals) { atomicAdd(&counters[2], my_lim_evals); atomicAdd(&counters[3], my_lim_nodes); }
         if (my_exec) atomicAdd(&counters[4], my_exec);
+        if (my_redo) atomicAdd(&counters[5], my_redo);
     }
-}
-
-// Entries whose strided sum was rejected: the reference's node-by-node sum, rows read through L1/L2 (no staging: the list is
-// short and mixes pairs). Persistent warps pull 32-entry tiles until the device-side count is exhausted.
-template<int NT>
-__global__ void __launch_bounds__(128)
-theta_redo_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes, const PairParams* __restrict__ pairs,
-                  const double* const* __restrict__ rows_by_pair, const double* __restrict__ coeff_pool, const WorkEntry* __restrict__ list,
-                  const int* __restrict__ redo_list, const int* __restrict__ redo_count, int* __restrict__ tile_counter,
-                  double* __restrict__ tab_pool, double* __restrict__ lim_pool, int* __restrict__ status_pool, unsigned long long* __restrict__ counters) {
-  if constexpr (NT != 1) {               // generic potentials (NT == 1) never defer
-    const int lane = threadIdx.x & 31, n = *redo_count;
-    unsigned long long my_nodes = 0, my_evals = 0, my_lim_nodes = 0, my_lim_evals = 0;
-    for (;;) {
-        int tile = 0;
-        if (lane == 0) tile = atomicAdd(tile_counter, 1);
-        tile = __shfl_sync(0xffffffffu, tile, 0);
-        if (tile * 32 >= n) break;
-        const int q = tile * 32 + lane;
-        if (q < n) {
-            const WorkEntry we = list[redo_list[q]];
-            const Item item = items[we.item];
-            const Regime rg = regimes[item.regime];
-            const PairParams pp = pairs[item.pair];
-            const double* __restrict__ rows = rows_by_pair[item.pair];
-            const double g = lattice_coord(we.nx, rg.dg);
-            const bool is_lim = (we.ny == LIM_ROW);
-            const double b = is_lim ? 100.0 : lattice_coord(we.ny, rg.db);
-            const double* coeff = (item.coeff_off >= 0) ? coeff_pool + item.coeff_off : nullptr;
-            Lane<NT> c;
-            make_lane<NT>(c, pp, coeff, item.T, g, b);
-            int st = 0; unsigned nodes = 0;
-            const double R = get_R<NT>(c, g, st);
-            double A[NT];
-            const double s = 1.0 / R;
-#pragma unroll
-            for (int t = 0; t < NT; t++) A[t] = c.Bt[t] * pow(s, c.lam[t]);
-            const double qq = R / b;
-            const double I = theta_integral<NT>(rows, rows, 0, A, qq * qq, nodes, st);
-            if (is_lim) { lim_pool[item.col_off + we.nx] = I; my_lim_nodes += nodes; my_lim_evals++; }
-            else { tab_pool[item.tab_off + (long long) we.nx * rg.ny + we.ny] = I; my_nodes += nodes; my_evals++; }
-            if (st) atomicOr(&status_pool[we.item], st);
-        }
-        __syncwarp();
-    }
-    for (int off = 16; off > 0; off >>= 1) {
-        my_nodes += __shfl_down_sync(0xffffffffu, my_nodes, off);
-        my_evals += __shfl_down_sync(0xffffffffu, my_evals, off);
-        my_lim_nodes += __shfl_down_sync(0xffffffffu, my_lim_nodes, off);
-        my_lim_evals += __shfl_down_sync(0xffffffffu, my_lim_evals, off);
-    }
-    if (lane == 0) {
-        if (my_evals) { atomicAdd(&counters[0], my_evals); atomicAdd(&counters[1], my_nodes); }
-        if (my_lim_evals) { atomicAdd(&counters[2], my_lim_evals); atomicAdd(&counters[3], my_lim_nodes); }
-        if (my_evals + my_lim_evals) { atomicAdd(&counters[4], my_nodes + my_lim_nodes); atomicAdd(&counters[5], my_evals + my_lim_evals); }
-    }
-  }
 }
 
 // finalize: chi = PI - 2 (I - I_lim + PI/2) (cpp/Spherical.cpp:269,464), store cos(chi), publish the node as known.
@@ -842,7 +808,6 @@ struct kg_omega_plan {
     double *d_W_out = nullptr, *d_omega_out = nullptr;  // [nT][npairs][nlr]
     int *d_status = nullptr, *d_flags = nullptr, *d_tile_counter = nullptr;
     int* d_perm = nullptr;                              // item -> output slot
-    int* d_redo = nullptr; int* d_redo_ctl = nullptr;  // redo list of the current pass; [0] count, [1] tile counter
     int* d_active = nullptr; unsigned long long* d_active_mask = nullptr; long long* d_active_cell_off = nullptr; int nactive = 0;   // items with work, their (l,r) sets
     int max_cells_seen = 0, regrows = 0;
     int* d_pair_task_start = nullptr;                   // [npairs+1] first column task of each pair
@@ -1013,8 +978,6 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
     PLAN_CUDA(cudaMemcpy(p->d_active_mask, active_mask.data(), active.size() * sizeof(unsigned long long), cudaMemcpyHostToDevice));
     PLAN_CUDA(cudaMemcpy(p->d_active_cell_off, active_cell_off.data(), active.size() * sizeof(long long), cudaMemcpyHostToDevice));
     PLAN_CUDA(kg_dmalloc(m, &p->d_counters, 8 * sizeof(unsigned long long)));
-    PLAN_CUDA(kg_dmalloc(m, &p->d_redo, std::max<long long>(1, p->max_list) * sizeof(int)));
-    PLAN_CUDA(kg_dmalloc(m, &p->d_redo_ctl, 2 * sizeof(int)));
     p->h_pinned = m->h_pinned;
     if (coeff_T) {
         PLAN_CUDA(kg_dmalloc(m, &p->d_coeff, (size_t) nT * Np * m->coeff_stride * sizeof(double)));
@@ -1047,7 +1010,7 @@ static void plan_free(kg_omega_plan* p) {
     void* ptrs[] = {p->d_items, p->d_regimes, p->d_tab, p->d_want, p->d_known, p->d_lim, p->d_have_lim, p->d_tasks, p->d_counts,
                     p->d_offsets, p->d_list, p->d_gfac, p->d_lr_l, p->d_lr_ri, p->d_coeff, p->d_W, p->d_omega, p->d_W_out,
                     p->d_omega_out, p->d_status, p->d_flags, p->d_tile_counter, p->d_perm, p->d_counters, p->d_cells[0], p->d_cells[1], p->d_ncells, p->d_pair_task_start,
-                    p->d_active, p->d_active_mask, p->d_active_cell_off, p->d_redo, p->d_redo_ctl};
+                    p->d_active, p->d_active_mask, p->d_active_cell_off};
     for (void* q : ptrs) p->m->dfree(q);
     for (int k = 0; k < 4; k++) if (p->ev[k]) cudaEventDestroy(p->ev[k]);
     delete p;
@@ -1099,23 +1062,19 @@ extern "C" int kg_omega_plan_run(kg_omega_plan* p) {
             fill_kernel<<<tgrid, 256, 0, s>>>(p->d_items, p->d_regimes, p->d_tasks, p->ntasks, p->d_want, p->d_known, p->d_have_lim, p->d_offsets, p->d_list);
             LAUNCHED("fill_kernel");
             CUDA_OK(cudaMemsetAsync(p->d_tile_counter, 0, (m->npairs + 1) * sizeof(int), s));
-            CUDA_OK(cudaMemsetAsync(p->d_redo_ctl, 0, 2 * sizeof(int), s));
             const int ntiles = (nlist + THETA_THREADS - 1) / THETA_THREADS;
             const int grid = std::min(ntiles, 2 * m->sm_count);
             CUDA_OK(cudaEventRecord(p->ev[2], s));
 #define LAUNCH_THETA(NT) theta_kernel<NT><<<grid, THETA_THREADS, smem, s>>>(p->d_items, p->d_regimes, m->d_pairs, m->d_rows_by_pair, p->d_coeff, \
                 p->d_list, p->d_offsets, p->d_pair_task_start, m->npairs, p->d_tile_counter, p->d_tab, p->d_lim, p->d_status, p->d_counters, \
-                p->d_redo, p->d_redo_ctl); \
-            LAUNCHED("theta_kernel"); \
-            if (NT != 1) theta_redo_kernel<NT><<<2 * m->sm_count, 128, 0, s>>>(p->d_items, p->d_regimes, m->d_pairs, m->d_rows_by_pair, p->d_coeff, p->d_list, \
-                p->d_redo, p->d_redo_ctl, p->d_redo_ctl + 1, p->d_tab, p->d_lim, p->d_status, p->d_counters)
+                nullptr, nullptr); \
+            LAUNCHED("theta_kernel")
             switch (m->ntpad) { case 1: LAUNCH_THETA(1); break; case 2: LAUNCH_THETA(2); break; case 4: LAUNCH_THETA(4); break; default: LAUNCH_THETA(6); break; }
 #undef LAUNCH_THETA
-            LAUNCHED("theta_redo_kernel");
             CUDA_OK(cudaEventRecord(p->ev[3], s));
             finalize_kernel<<<(nlist + 255) / 256, 256, 0, s>>>(p->d_items, p->d_regimes, p->d_list, p->d_offsets + p->ntasks, p->d_tab, p->d_lim,
                                                                p->d_known, p->d_have_lim);
-            p->launches += 4;
+            p->launches += 3;
         }
         // 2. evaluate this level's cells, emit the next level
         CUDA_OK(cudaMemsetAsync(p->d_ncells, 0, sizeof(int), s));
