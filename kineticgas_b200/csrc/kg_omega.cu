@@ -176,7 +176,7 @@ __device__ __forceinline__ int mesh_emit(const MeshView& v, Cell* __restrict__ o
 
 // One level of the refinement trees: every member (l,r) of a cell either integrates it (leaf) or splits it; members that
 // split the same way share the child cells, which go to cells_out with their nodes marked.
-__global__ void __launch_bounds__(256) mesh_level_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
+__global__ void __launch_bounds__(256, 4) mesh_level_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
                                                          const double* __restrict__ tab_pool, unsigned* __restrict__ want_pool,
                                                          const double* __restrict__ gfac_pool, const int* __restrict__ lr_l,
                                                          const int* __restrict__ lr_r_index, int nr_distinct, int gfac_stride, double cospi,
