@@ -81,3 +81,45 @@ def test_strided_quadrature_matches_node_by_node():
     assert s_exact["executed_nodes"] == s_exact["reference_nodes"]
     assert s_em["executed_nodes"] < 0.25 * s_em["reference_nodes"]
     assert s_em["redo_integrals"] < 0.1 * s_em["theta_integrals"]
+
+
+def test_full_size_config1_strided_equals_node_by_node():
+    """BASELINE configs[1] at full size (LJF, 4096-point T* grid 0.3-100, the ten (l,r) with 1 <= l <= r <= 4): every one of the
+    40 960 collision integrals from the strided sums equals the node-by-node evaluation to 1e-9, the reference node totals are
+    identical (same stop index in all ~3e7 theta integrals), and the reduced integrals have the known LJ 12-6 limits."""
+    from kineticgas_b200 import DeviceModel, mie_desc
+    from kineticgas_b200.model import set_exact_quadrature
+    from kineticgas_b200.fluids import BOLTZMANN, AVOGADRO
+    sig, eps, mass = 3e-10, 30.0 * BOLTZMANN, 1e-3 / AVOGADRO
+    m = DeviceModel([mie_desc(sig, eps, 6.0, 12.0)], [mass], True)
+    Ts = np.geomspace(0.3, 100.0, 4096)
+    T = 30.0 * Ts
+    lr = [(l, r) for l in range(1, 5) for r in range(l, 5)]
+    l, r = [a for a, _ in lr], [b for _, b in lr]
+    res = {}
+    try:
+        for exact in (0, 1):
+            set_exact_quadrature(exact)
+            p = m.omega_plan(T, l, r)
+            p.run()
+            res[exact] = (p.fetch(), p.quadrature_stats())
+            p.close()
+    finally:
+        set_exact_quadrature(0)
+    om, st = res[0]
+    om_x, st_x = res[1]
+    assert np.all(np.isfinite(om)) and np.all(om > 0)
+    assert np.max(np.abs(om / om_x - 1)) < 1e-9
+    assert st["reference_nodes"] == st_x["reference_nodes"] and st["theta_integrals"] == st_x["theta_integrals"]
+    # reduced integrals Omega* = Omega / Omega_HS (cpp/MieKinGas.h:52-60): Omega*(2,2) of LJ 12-6 is 1.593 at T* = 1 and
+    # 0.5882 at T* = 100 (Hirschfelder, Curtiss & Bird table I-M; the reference's coarse lattice agrees to ~1 %)
+    def omega_hs(ll, rr, Tk):
+        w = np.pi * sig ** 2 * 0.5 * (rr + 1) * np.prod(np.arange(2, rr + 1, dtype=float))
+        if ll % 2 == 0:
+            w *= 1.0 - 1.0 / (ll + 1.0)
+        return np.sqrt(BOLTZMANN * Tk / (np.pi * mass)) * w
+    k22 = lr.index((2, 2))
+    star = om[:, 0, k22] / omega_hs(2, 2, T)
+    assert abs(star[np.argmin(np.abs(Ts - 1.0))] / 1.593 - 1) < 0.02
+    assert abs(star[-1] / 0.5882 - 1) < 0.02
+    assert np.all(np.diff(star[Ts > 1.0]) < 1e-3)          # decreasing in T* above the well depth (up to lattice noise)
