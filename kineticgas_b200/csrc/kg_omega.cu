@@ -298,30 +298,58 @@ __global__ void count_kernel(const Item* __restrict__ items, const Regime* __res
     counts[t] = c;
 }
 
-// single-CTA exclusive scan (ntasks is a few 1e5 at most); total -> counts_out[ntasks]
-__global__ void __launch_bounds__(1024) scan_kernel(const int* __restrict__ counts, int* __restrict__ offsets, int n) {
-    __shared__ int sums[1024];
-    const int per = (n + 1023) / 1024;
-    const int lo = threadIdx.x * per, hi = min(n, lo + per);
-    int s = 0;
-    for (int i = lo; i < hi; i++) s += counts[i];
-    sums[threadIdx.x] = s;
+// exclusive scan of counts[0..n) into offsets[0..n], offsets[n] = total: 4096-element chunks per CTA (coalesced), a single CTA over
+// the chunk totals, then the chunk bases are added
+constexpr int SCAN_CHUNK = 4096;
+__global__ void __launch_bounds__(1024) scan_chunk_kernel(const int* __restrict__ counts, int* __restrict__ offsets, int n, int* __restrict__ chunk_sums) {
+    __shared__ int warp_sums[32];
+    const int base = blockIdx.x * SCAN_CHUNK + threadIdx.x * 4;
+    int v[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) v[k] = (base + k < n) ? counts[base + k] : 0;
+    const int mine = v[0] + v[1] + v[2] + v[3];
+    int pre = mine;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    for (int off = 1; off < 32; off <<= 1) { const int u = __shfl_up_sync(0xffffffffu, pre, off); if (lane >= off) pre += u; }
+    if (lane == 31) warp_sums[wid] = pre;
+    __syncthreads();
+    if (wid == 0) {
+        int ws = warp_sums[lane];
+        for (int off = 1; off < 32; off <<= 1) { const int u = __shfl_up_sync(0xffffffffu, ws, off); if (lane >= off) ws += u; }
+        warp_sums[lane] = ws;
+    }
+    __syncthreads();
+    int run = pre - mine + (wid ? warp_sums[wid - 1] : 0);
+#pragma unroll
+    for (int k = 0; k < 4; k++) { if (base + k < n) offsets[base + k] = run; run += v[k]; }
+    if (threadIdx.x == 1023) chunk_sums[blockIdx.x] = warp_sums[31];
+}
+__global__ void __launch_bounds__(1024) scan_sums_kernel(int* __restrict__ chunk_sums, int nchunks, int* __restrict__ offsets, int n) {
+    // nchunks <= 1024 (n < 4 M columns); exclusive scan in place, total to offsets[n]
+    __shared__ int sh[1024];
+    const int mine = (threadIdx.x < nchunks) ? chunk_sums[threadIdx.x] : 0;
+    sh[threadIdx.x] = mine;
     __syncthreads();
     for (int off = 1; off < 1024; off <<= 1) {
-        int v = (threadIdx.x >= off) ? sums[threadIdx.x - off] : 0;
+        const int u = (threadIdx.x >= off) ? sh[threadIdx.x - off] : 0;
         __syncthreads();
-        sums[threadIdx.x] += v;
+        sh[threadIdx.x] += u;
         __syncthreads();
     }
-    int base = sums[threadIdx.x] - s;
-    for (int i = lo; i < hi; i++) { offsets[i] = base; base += counts[i]; }
-    if (threadIdx.x == 1023) offsets[n] = sums[1023];
+    if (threadIdx.x < nchunks) chunk_sums[threadIdx.x] = sh[threadIdx.x] - mine;
+    if (threadIdx.x == 1023) offsets[n] = sh[1023];
+}
+__global__ void __launch_bounds__(1024) scan_add_kernel(int* __restrict__ offsets, int n, const int* __restrict__ chunk_sums) {
+    const int base = blockIdx.x * SCAN_CHUNK + threadIdx.x * 4, add = chunk_sums[blockIdx.x];
+#pragma unroll
+    for (int k = 0; k < 4; k++) if (base + k < n) offsets[base + k] += add;
 }
 
-__global__ void fill_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes, const int2* __restrict__ tasks, int ntasks,
+// one warp per column task, one lane per 32-node mask word (a column has at most 16 words)
+__global__ void __launch_bounds__(256) fill_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes, const int2* __restrict__ tasks, int ntasks,
                             const unsigned* __restrict__ want_pool, const unsigned* __restrict__ known_pool,
                             const unsigned char* __restrict__ have_lim, const int* __restrict__ offsets, WorkEntry* __restrict__ list) {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (t >= ntasks) return;
     int o = offsets[t];
     if (offsets[t + 1] == o) return;
@@ -329,14 +357,20 @@ __global__ void fill_kernel(const Item* __restrict__ items, const Regime* __rest
     const Item item = items[it];
     const Regime rg = regimes[item.regime];
     const long long w0 = item.mask_off + (long long) nx * rg.nwords;
-    if (!have_lim[item.col_off + nx]) list[o++] = WorkEntry{it, (unsigned short) nx, (unsigned short) LIM_ROW};
-    for (int w = 0; w < rg.nwords; w++) {
-        unsigned m = want_pool[w0 + w] & ~known_pool[w0 + w];
+    if (!have_lim[item.col_off + nx]) { if (lane == 0) list[o] = WorkEntry{it, (unsigned short) nx, (unsigned short) LIM_ROW}; o++; }
+    for (int wb = 0; wb < rg.nwords; wb += 32) {
+        const int w = wb + lane;
+        unsigned m = (w < rg.nwords) ? (want_pool[w0 + w] & ~known_pool[w0 + w]) : 0u;
+        const int cnt = __popc(m);
+        int pre = cnt;
+        for (int off = 1; off < 32; off <<= 1) { const int v = __shfl_up_sync(0xffffffffu, pre, off); if (lane >= off) pre += v; }
+        int q = o + pre - cnt;
         while (m) {
             const int bpos = __ffs(m) - 1;
             m &= m - 1;
-            list[o++] = WorkEntry{it, (unsigned short) nx, (unsigned short) (w * 32 + bpos)};
+            list[q++] = WorkEntry{it, (unsigned short) nx, (unsigned short) (w * 32 + bpos)};
         }
+        o += __shfl_sync(0xffffffffu, pre, 31);
     }
 }
 
@@ -808,6 +842,7 @@ struct kg_omega_plan {
     double *d_W_out = nullptr, *d_omega_out = nullptr;  // [nT][npairs][nlr]
     int *d_status = nullptr, *d_flags = nullptr, *d_tile_counter = nullptr;
     int* d_perm = nullptr;                              // item -> output slot
+    int* d_chunk_sums = nullptr;                        // scan scratch
     int* d_active = nullptr; unsigned long long* d_active_mask = nullptr; long long* d_active_cell_off = nullptr; int nactive = 0;   // items with work, their (l,r) sets
     int max_cells_seen = 0, regrows = 0;
     int* d_pair_task_start = nullptr;                   // [npairs+1] first column task of each pair
@@ -978,6 +1013,8 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
     PLAN_CUDA(cudaMemcpy(p->d_active_mask, active_mask.data(), active.size() * sizeof(unsigned long long), cudaMemcpyHostToDevice));
     PLAN_CUDA(cudaMemcpy(p->d_active_cell_off, active_cell_off.data(), active.size() * sizeof(long long), cudaMemcpyHostToDevice));
     PLAN_CUDA(kg_dmalloc(m, &p->d_counters, 8 * sizeof(unsigned long long)));
+    PLAN_CUDA(kg_dmalloc(m, &p->d_chunk_sums, 1024 * sizeof(int)));
+    if (p->ntasks > 1024 * SCAN_CHUNK) { set_error("kg_omega_plan_create: batch too large, split the T grid"); plan_free(p); return -1; }
     p->h_pinned = m->h_pinned;
     if (coeff_T) {
         PLAN_CUDA(kg_dmalloc(m, &p->d_coeff, (size_t) nT * Np * m->coeff_stride * sizeof(double)));
@@ -1010,7 +1047,7 @@ static void plan_free(kg_omega_plan* p) {
     void* ptrs[] = {p->d_items, p->d_regimes, p->d_tab, p->d_want, p->d_known, p->d_lim, p->d_have_lim, p->d_tasks, p->d_counts,
                     p->d_offsets, p->d_list, p->d_gfac, p->d_lr_l, p->d_lr_ri, p->d_coeff, p->d_W, p->d_omega, p->d_W_out,
                     p->d_omega_out, p->d_status, p->d_flags, p->d_tile_counter, p->d_perm, p->d_counters, p->d_cells[0], p->d_cells[1], p->d_ncells, p->d_pair_task_start,
-                    p->d_active, p->d_active_mask, p->d_active_cell_off};
+                    p->d_active, p->d_active_mask, p->d_active_cell_off, p->d_chunk_sums};
     for (void* q : ptrs) p->m->dfree(q);
     for (int k = 0; k < 4; k++) if (p->ev[k]) cudaEventDestroy(p->ev[k]);
     delete p;
@@ -1050,16 +1087,21 @@ extern "C" int kg_omega_plan_run(kg_omega_plan* p) {
         // 1. theta integrals of every newly marked lattice node
         count_kernel<<<tgrid, 256, 0, s>>>(p->d_items, p->d_regimes, p->d_tasks, p->ntasks, p->d_want, p->d_known, p->d_have_lim, p->d_counts);
         LAUNCHED("count_kernel");
-        scan_kernel<<<1, 1024, 0, s>>>(p->d_counts, p->d_offsets, p->ntasks);
-        LAUNCHED("scan_kernel");
+        {
+            const int nchunks = (p->ntasks + SCAN_CHUNK - 1) / SCAN_CHUNK;
+            scan_chunk_kernel<<<nchunks, 1024, 0, s>>>(p->d_counts, p->d_offsets, p->ntasks, p->d_chunk_sums);
+            scan_sums_kernel<<<1, 1024, 0, s>>>(p->d_chunk_sums, nchunks, p->d_offsets, p->ntasks);
+            scan_add_kernel<<<nchunks, 1024, 0, s>>>(p->d_offsets, p->ntasks, p->d_chunk_sums);
+        }
+        LAUNCHED("scan kernels");
         CUDA_OK(cudaMemcpyAsync(&p->h_pinned[1], p->d_offsets + p->ntasks, sizeof(int), cudaMemcpyDeviceToHost, s));
         CUDA_OK(cudaStreamSynchronize(s));
         cudaEventElapsedTime(&ms, p->ev[0], p->ev[1]); p->ms_mesh += ms;
-        p->launches += 2;
+        p->launches += 4;
         const int nlist = p->h_pinned[1];
         if (nlist > p->max_list) { set_error("kg_omega_plan_run: work list overflow"); return -3; }
         if (nlist > 0) {
-            fill_kernel<<<tgrid, 256, 0, s>>>(p->d_items, p->d_regimes, p->d_tasks, p->ntasks, p->d_want, p->d_known, p->d_have_lim, p->d_offsets, p->d_list);
+            fill_kernel<<<(p->ntasks + 7) / 8, 256, 0, s>>>(p->d_items, p->d_regimes, p->d_tasks, p->ntasks, p->d_want, p->d_known, p->d_have_lim, p->d_offsets, p->d_list);
             LAUNCHED("fill_kernel");
             CUDA_OK(cudaMemsetAsync(p->d_tile_counter, 0, (m->npairs + 1) * sizeof(int), s));
             const int ntiles = (nlist + THETA_THREADS - 1) / THETA_THREADS;
