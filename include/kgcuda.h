@@ -202,7 +202,9 @@ typedef struct {
  * where MieKinGas::omega would use it), MTL/ETL, Barker-Henderson diameters and the bracket integrals H_ij, H_i, L_ij, L_i
  * (cpp/KineticGas.cpp:644-705). Replaces precompute_conductivity / precompute_viscosity (cpp/KineticGas_mthr.cpp:58-143). */
 typedef struct kg_tcache kg_tcache;
-/* coeff_T (optional) [nT][npairs][KG_MAX_TERMS]: per-temperature effective coefficients of T-dependent potentials (ideal gas only). */
+/* coeff_T (optional) [nT][npairs][KG_MAX_TERMS]: per-temperature effective coefficients of T-dependent potentials.
+ * Power-law sums other than plain Mie (or any model given coeff_T) use the extended Sutherland RDF of cpp/ExtendedSutherland.cpp:315-333
+ * when opts->is_idealgas == 0 (all exponents must exceed 4). */
 int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int nT, const double* T, const double* coeff_T, kg_tcache** out);
 void kg_tcache_destroy(kg_tcache* c);
 /* Shape of the Omega table: nlr entries (l[k], r[k]); pass NULL arrays to query nlr only. */

@@ -401,6 +401,176 @@ __global__ void ljs_rdf_kernel(int n, int nslots, int nc, const int* __restrict_
     for (int k = 0; k < nc * nc; k++) rdf[((size_t) sp * nslots + slot) * nc * nc + k] = g;
 }
 
+// ---- extended Sutherland / Feynman-Hibbs Mie (QuantumMie): effective parameters per temperature and the RDF at contact of
+// ExtSutherland::saft_rdf (cpp/ExtendedSutherland.cpp:168-247, 292-590). u = eps sum_k C_eff,k(T) (sigma/r)^lam_k; QuantumMie has no
+// density exponents (cpp/QuantumMie.cpp:73-109), so sigma_eff, eps_eff, alpha_vdw and the Barker-Henderson diameters depend on T only
+// and the reference's forward-mode d/drho (autodiff duals, :388-394, 483-489) acts on the explicit rho of a_1s, B, zeta_x, K_HS only.
+struct EsPair { double sigma, eps; int nterms, pad; double lam[KG_MAX_TERMS]; };
+struct EsParams { double C[KG_MAX_TERMS]; double sigma_eff, eps_eff, alpha, dbh; };     // per (T, internal pair i*nc+j)
+
+__device__ void es_pot(const EsPair& q, const double* C, double r, double& u, double& ur, double& urr) {
+    u = ur = urr = 0.0;
+    for (int k = 0; k < q.nterms; k++) {
+        const double t = C[k] * pow(q.sigma / r, q.lam[k]);
+        u += t; ur -= q.lam[k] * t / r; urr += q.lam[k] * (q.lam[k] + 1.) * t / (r * r);
+    }
+    u *= q.eps; ur *= q.eps; urr *= q.eps;
+}
+
+// One thread per (t, i <= j): Newton for sigma_eff and r_min from sigma (set_sigma_eff / set_epsilon_eff), alpha_vdw, and for
+// i == j the 20-point Gauss-Legendre Barker-Henderson diameter. Cross diameters are filled by es_dbh_mix_kernel.
+__global__ void es_params_kernel(int nT, int nc, const double* __restrict__ T, const EsPair* __restrict__ pairs, const double* __restrict__ coeff,
+                                 const int* __restrict__ pair_of, int npairs_dev, EsParams* __restrict__ out) {
+    const int npu = nc * (nc + 1) / 2;
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nT * npu) return;
+    const int t = e / npu;
+    int i = 0, rest = e % npu;
+    while (rest >= nc - i) { rest -= nc - i; i++; }
+    const int j = i + rest;
+    const int pd = pair_of[i * nc + j];
+    const EsPair q = pairs[pd];
+    EsParams P;
+    for (int k = 0; k < KG_MAX_TERMS; k++) P.C[k] = (k < q.nterms) ? coeff[((size_t) t * npairs_dev + pd) * KG_MAX_TERMS + k] : 0.0;
+    double u, ur, urr, s = q.sigma;
+    int guard = 0;
+    do { es_pot(q, P.C, s, u, ur, urr); s -= u / ur; } while (fabs(u) / q.eps > 1e-6 && guard++ < 200);
+    P.sigma_eff = s;
+    double rm = q.sigma;
+    guard = 0;
+    do { es_pot(q, P.C, rm, u, ur, urr); rm -= ur / urr; } while (fabs(ur) * rm / q.eps > 1e-10 && guard++ < 200);
+    es_pot(q, P.C, rm, u, ur, urr);
+    P.eps_eff = -u;
+    double a = 0.;
+    for (int k = 0; k < q.nterms; k++) a -= P.C[k] * q.eps * pow(q.sigma / P.sigma_eff, q.lam[k]) / (q.lam[k] - 3.);
+    P.alpha = a / P.eps_eff;
+    P.dbh = 0.0;
+    if (i == j) {
+        const double beta = 1. / (BOLTZMANN * T[t]);
+        double d = 2.;
+        for (int n = 0; n < 20; n++) {
+            es_pot(q, P.C, P.sigma_eff * (c_gl_x[n] / 4. + 3. / 4.), u, ur, urr);
+            d += c_gl_w[n] * (1. - exp(-beta * u));
+        }
+        P.dbh = d * (P.sigma_eff / 4.);
+    }
+    out[(size_t) t * nc * nc + i * nc + j] = P;
+    if (i != j) out[(size_t) t * nc * nc + j * nc + i] = P;
+}
+__global__ void es_dbh_mix_kernel(int nT, int nc, EsParams* __restrict__ out) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nT * nc * nc) return;
+    const int t = e / (nc * nc), i = (e / nc) % nc, j = e % nc;
+    if (i == j) return;
+    EsParams* base = out + (size_t) t * nc * nc;
+    base[i * nc + j].dbh = (base[i * nc + i].dbh + base[j * nc + j].dbh) / 2.0;
+}
+
+// first-order dual number in rho
+struct D1 { double v, d; };
+__device__ __forceinline__ D1 operator+(D1 a, D1 b) { return {a.v + b.v, a.d + b.d}; }
+__device__ __forceinline__ D1 operator-(D1 a, D1 b) { return {a.v - b.v, a.d - b.d}; }
+__device__ __forceinline__ D1 operator*(D1 a, D1 b) { return {a.v * b.v, a.d * b.v + a.v * b.d}; }
+__device__ __forceinline__ D1 operator/(D1 a, D1 b) { const double q = a.v / b.v; return {q, (a.d - q * b.d) / b.v}; }
+__device__ __forceinline__ D1 operator*(double a, D1 b) { return {a * b.v, a * b.d}; }
+__device__ __forceinline__ D1 operator+(double a, D1 b) { return {a + b.v, b.d}; }
+__device__ __forceinline__ D1 operator-(double a, D1 b) { return {a - b.v, -b.d}; }
+__device__ __forceinline__ D1 dpowi(D1 a, int n) { const double p = pow(a.v, (double) (n - 1)); return {p * a.v, n * p * a.d}; }
+
+struct EsState { D1 rho, zeta; double zeta_hs; };
+
+__device__ D1 es_zeta_eff(D1 zeta_x, double lam) {
+    D1 z = {0.0, 0.0};
+    for (int i = 0; i < 4; i++) {
+        double c = 0.0;
+        for (int j = 0; j < 4; j++) c += c_Cm[i][j] * pow(lam, (double) -j);
+        z = z + c * dpowi(zeta_x, i + 1);
+    }
+    return z;
+}
+// a_1s + B for exponent lam (a_1s_func, B_func, I_func, J_func; cpp/ExtendedSutherland.cpp:399-441)
+__device__ D1 es_a1s_plus_B(const EsState& S, double eps, double d, double xeff, double lam) {
+    const D1 ze = es_zeta_eff(S.zeta, lam);
+    const D1 one_m = 1.0 - ze;
+    const D1 a1s = ((-2. * PI_REF * eps * pow(d, 3) / (lam - 3)) * S.rho) * (1. - 0.5 * ze) / dpowi(one_m, 3);
+    const double I = -(pow(xeff, 3. - lam) - 1.) / (lam - 3.);
+    const double J = -(pow(xeff, 4. - lam) * (lam - 3.) - pow(xeff, 3. - lam) * (lam - 4.) - 1.) / ((lam - 3.) * (lam - 4.));
+    const D1 om = 1.0 - S.zeta;
+    const D1 om3 = dpowi(om, 3);
+    const D1 B = ((2. * PI_REF * pow(d, 3) * eps) * S.rho) * (I * ((1. - 0.5 * S.zeta) / om3) - (J * 9.) * (S.zeta * (1. + S.zeta)) / (2. * om3));
+    return a1s + B;
+}
+__device__ __forceinline__ D1 es_KHS(D1 z) {
+    return dpowi(1.0 - z, 4) / (1.0 + 4.0 * z + 4.0 * dpowi(z, 2) - 4.0 * dpowi(z, 3) + dpowi(z, 4));
+}
+
+// One thread per (state point, slot, i <= j): ExtSutherland::saft_rdf order 2 with the g2 correction (model_rdf default).
+__global__ void es_rdf_kernel(int n, int nslots, TModel tm, const int* __restrict__ tidx, const double* __restrict__ T_of, const double* __restrict__ Vm,
+                              const double* __restrict__ x, const EsPair* __restrict__ pairs_int, const EsParams* __restrict__ prm, double* __restrict__ rdf) {
+    const int nc = tm.nc, npu = nc * (nc + 1) / 2;
+    const long long e = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= (long long) n * nslots * npu) return;
+    const int pu = (int) (e % npu), slot = (int) ((e / npu) % nslots), sp = (int) (e / ((long long) npu * nslots));
+    int i = 0, rest = pu;
+    while (rest >= nc - i) { rest -= nc - i; i++; }
+    const int j = i + rest;
+    const int t = tidx[sp];
+    const double T = T_of[t];
+    const double rho = (slot == 0) ? AVOGADRO / Vm[sp] : AVOGADRO / 1e12;
+    const EsParams* P = prm + (size_t) t * nc * nc;
+    double zx = 0.0, zhs = 0.0;
+    for (int a = 0; a < nc; a++) for (int b = 0; b < nc; b++) {
+        const double xa = tm.is_singlecomp ? 0.5 : x[(size_t) sp * nc + a], xb = tm.is_singlecomp ? 0.5 : x[(size_t) sp * nc + b];
+        zx += xa * xb * pow(P[a * nc + b].dbh, 3);
+        zhs += xa * xb * pow(P[a * nc + b].sigma_eff, 3);
+    }
+    EsState S;
+    S.rho = {rho, 1.0};
+    S.zeta = {zx * (PI_REF * rho / 6.0), zx * (PI_REF / 6.0)};
+    S.zeta_hs = zhs * (PI_REF * rho / 6.0);
+    const EsPair q = pairs_int[i * nc + j];
+    const EsParams p = P[i * nc + j];
+    const double d = p.dbh, xeff = p.sigma_eff / d, x0 = q.sigma / d, z = S.zeta.v;
+    // g0, rdf_g0_func :346-362
+    const double k0 = -log(1 - z) + (42. * z - 39. * pow(z, 2) + 9. * pow(z, 3) - 2 * pow(z, 4)) / (6 * pow(1 - z, 3));
+    const double k1 = (pow(z, 4) + 6. * pow(z, 2) - 12. * z) / (2. * pow(1 - z, 3));
+    const double k2 = -3. * pow(z, 2) / (8. * pow(1 - z, 2));
+    const double k3 = (-pow(z, 4.) + 3. * pow(z, 2) + 3. * z) / (6. * pow(1 - z, 3));
+    const double g0 = exp(k0 + k1 * xeff + k2 * pow(xeff, 2) + k3 * pow(xeff, 3));
+    // g1, rdf_g1_func :376-397 ; a1 = - sum_k C_k x0^lam_k (a1s_k + B_k)
+    double g1 = 0.0;
+    D1 a1 = {0.0, 0.0};
+    for (int k = 0; k < q.nterms; k++) {
+        const D1 ab = es_a1s_plus_B(S, q.eps, d, xeff, q.lam[k]);
+        const double w = p.C[k] * pow(x0, q.lam[k]);
+        g1 += q.lam[k] * w * ab.v / rho;
+        a1 = a1 - w * ab;
+    }
+    g1 += 3. * a1.d;
+    g1 *= (1.0 / (2. * PI_REF * q.eps * pow(d, 3)));
+    // g2, rdf_g2_func :443-478 ; a2/chi = K_HS eps / 2 sum_kl C_k C_l x0^lam_kl (a1s_kl + B_kl)
+    const D1 KHS = es_KHS(S.zeta);
+    double g2 = 0.0;
+    D1 a2 = {0.0, 0.0};
+    for (int k = 0; k < q.nterms; k++) for (int l = 0; l < q.nterms; l++) {
+        const double lkl = q.lam[k] + q.lam[l];
+        const D1 ab = es_a1s_plus_B(S, q.eps, d, xeff, lkl);
+        const double w = p.C[k] * p.C[l] * pow(x0, lkl);
+        g2 -= KHS.v * q.eps * w * q.lam[k] * ab.v / rho;
+        a2 = a2 + w * ab;
+    }
+    a2 = (0.5 * q.eps) * (KHS * a2);
+    g2 += 3. * a2.d;
+    const double theta = exp(p.eps_eff / (BOLTZMANN * T)) - 1.;
+    const double gamma = 10. * (1 - tanh(10. * (0.57 - p.alpha))) * S.zeta_hs * theta * exp(-6.7 * S.zeta_hs + -8. * pow(S.zeta_hs, 2));
+    g2 *= (1 + gamma) * (1. / (2. * PI_REF * pow(q.eps, 2) * pow(d, 3)));
+    const double be = q.eps / (BOLTZMANN * T);
+    const double g = g0 * exp(be * (g1 / g0) + pow(be, 2) * (g2 / g0));
+    double* out = rdf + ((size_t) sp * nslots + slot) * nc * nc;
+    out[i * nc + j] = g;
+    out[j * nc + i] = g;
+}
+
 // One thread per (state point, slot, i <= j). slot 0: the state point's density; slot 1: N_A / 1e12 (the dilute viscosity of the
 // internal-conductivity term, cpp/KineticGas_properties.cpp:133). rdf [n][nslots][nc][nc].
 __global__ void rdf_kernel(int n, int nslots, TModel tm, const int* __restrict__ tidx, const double* __restrict__ T_of, const double* __restrict__ Vm,
@@ -778,12 +948,14 @@ struct kg_tcache {
     kg_transport_opts opt{};
     TModel tm{};
     int nT = 0;
-    bool mie = false, ljs = false;
+    bool mie = false, ljs = false, es = false;      // es: extended Sutherland RDF (power-law sums other than plain Mie)
     std::vector<double> T;
     std::map<double, int> index_of;
     std::vector<unsigned char> is_corr;              // [nT][npairs][nlr]
     double *d_T = nullptr, *d_omega = nullptr, *d_mtl = nullptr, *d_etl = nullptr, *d_dbh = nullptr, *d_brk = nullptr;
     MiePair* d_mp_int = nullptr;                     // [nc][nc] internal pairs
+    EsPair* d_es_int = nullptr;                      // [nc][nc] internal pairs (es)
+    EsParams* d_es_prm = nullptr;                    // [nT][nc][nc] effective parameters (es)
     MiePair mp00{};                                  // pair (0,0) on the host (LJ/spline RDF kernel argument)
     std::vector<double> h_mtl, h_etl;
     double ms_omega = 0, ms_tl = 0;                  // stage timings of the build (host clock around synchronised stages)
@@ -806,7 +978,7 @@ bool desc_is_mie(const kg_potential_desc& d) {
 
 static void tcache_free(kg_tcache* c) {
     cudaSetDevice(c->device);
-    void* ptrs[] = {c->d_T, c->d_omega, c->d_mtl, c->d_etl, c->d_dbh, c->d_brk, c->d_mp_int};
+    void* ptrs[] = {c->d_T, c->d_omega, c->d_mtl, c->d_etl, c->d_dbh, c->d_brk, c->d_mp_int, c->d_es_int, c->d_es_prm};
     for (void* p : ptrs) c->m->dfree(p);
     delete c;
 }
@@ -852,13 +1024,17 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
     for (auto& d : m->descs) mie = mie && desc_is_mie(d);
     bool ljs = m->generic;      // LJSpline: own correlation (cpp/LJSpline.cpp:123-134) and own RDF model (cpp/LJSpline.h:89-125)
     for (auto& g : m->gdescs) ljs = ljs && g.kind == KG_POT_LJ_SPLINE;
-    if (!opts->is_idealgas && ((!mie && !ljs) || coeff_T)) {
+    // power-law sums that are not MieKinGas (ExtSutherland / QuantumMie): SAFT-VR Mie style RDF of cpp/ExtendedSutherland.cpp:315-333
+    const bool es = !m->generic && (!mie || coeff_T);
+    if (!opts->is_idealgas && m->generic && !ljs) {
         set_error("RDF model is not implemented. Model is only available for ideal gas!");     // cpp/KineticGas.h:259
         return -1;
     }
+    if (!opts->is_idealgas && es) for (auto& d : m->descs) for (int k = 0; k < d.nterms; k++)
+        if (d.lam[k] <= 4.0) { set_error("kg_tcache_create: the extended Sutherland RDF needs exponents > 4"); return -1; }
     CUDA_OK(cudaSetDevice(m->device));
     kg_tcache* c = new kg_tcache;
-    c->m = m; c->device = m->device; c->opt = *opts; c->nT = nT; c->mie = mie; c->ljs = ljs;
+    c->m = m; c->device = m->device; c->opt = *opts; c->nT = nT; c->mie = mie; c->ljs = ljs; c->es = es;
     c->T.assign(T, T + nT);
     for (int t = 0; t < nT; t++) c->index_of.emplace(T[t], t);
     TModel& tm = c->tm;
@@ -994,13 +1170,38 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
         if (bad & KG_STATUS_GETR_MAXITER) { set_error("get_R reached max iter!"); tcache_free(c); return -4; }
         m->timings[2] = ms_since(t_stage); m->timings[4] += m->tl_launches;
         TC_CUDA(upload(m, &c->d_mtl, c->h_mtl)); TC_CUDA(upload(m, &c->d_etl, c->h_etl));
-        MiePair* d_diag = nullptr;
-        TC_CUDA(upload(m, &d_diag, mp_diag));
-        TC_CUDA(kg_dmalloc(m, &c->d_dbh, (size_t) nT * nc * sizeof(double)));
-        bh_kernel<<<(nT * nc + 127) / 128, 128, 0, s>>>(nT, nc, c->d_T, d_diag, c->d_dbh);
-        TC_CUDA(cudaGetLastError());
-        TC_CUDA(cudaStreamSynchronize(s));
-        m->dfree(d_diag);
+        if (es) {
+            std::vector<EsPair> ep_dev(Np), ep_int((size_t) nc * nc);
+            for (int p = 0; p < Np; p++) {
+                const auto& d = m->descs[p];
+                EsPair q{}; q.sigma = d.sigma; q.eps = d.eps; q.nterms = d.nterms;
+                for (int k = 0; k < d.nterms; k++) q.lam[k] = d.lam[k];
+                ep_dev[p] = q;
+            }
+            std::vector<int> pof((size_t) nc * nc);
+            for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) { pof[i * nc + j] = tm.pair_of[i][j]; ep_int[i * nc + j] = ep_dev[tm.pair_of[i][j]]; }
+            std::vector<double> cf((size_t) nT * Np * KG_MAX_TERMS);
+            for (int t = 0; t < nT; t++) for (int p = 0; p < Np; p++) for (int k = 0; k < KG_MAX_TERMS; k++)
+                cf[((size_t) t * Np + p) * KG_MAX_TERMS + k] = coeff_T ? coeff_T[((size_t) t * Np + p) * KG_MAX_TERMS + k] : m->descs[p].C[k];
+            EsPair* d_ep = nullptr; double* d_cf = nullptr; int* d_pof = nullptr;
+            TC_CUDA(upload(m, &d_ep, ep_dev)); TC_CUDA(upload(m, &d_cf, cf)); TC_CUDA(upload(m, &d_pof, pof));
+            TC_CUDA(upload(m, &c->d_es_int, ep_int));
+            TC_CUDA(kg_dmalloc(m, &c->d_es_prm, (size_t) nT * nc * nc * sizeof(EsParams)));
+            const int npu = nc * (nc + 1) / 2;
+            es_params_kernel<<<(nT * npu + 63) / 64, 64, 0, s>>>(nT, nc, c->d_T, d_ep, d_cf, d_pof, Np, c->d_es_prm);
+            es_dbh_mix_kernel<<<(nT * nc * nc + 63) / 64, 64, 0, s>>>(nT, nc, c->d_es_prm);
+            TC_CUDA(cudaGetLastError());
+            TC_CUDA(cudaStreamSynchronize(s));
+            for (void* q : {(void*) d_ep, (void*) d_cf, (void*) d_pof}) m->dfree(q);
+        } else {
+            MiePair* d_diag = nullptr;
+            TC_CUDA(upload(m, &d_diag, mp_diag));
+            TC_CUDA(kg_dmalloc(m, &c->d_dbh, (size_t) nT * nc * sizeof(double)));
+            bh_kernel<<<(nT * nc + 127) / 128, 128, 0, s>>>(nT, nc, c->d_T, d_diag, c->d_dbh);
+            TC_CUDA(cudaGetLastError());
+            TC_CUDA(cudaStreamSynchronize(s));
+            m->dfree(d_diag);
+        }
     }
     {
         double *d_wA = nullptr, *d_wAp = nullptr, *d_wBp = nullptr, *d_wBpp = nullptr, *d_hpre = nullptr;
@@ -1041,6 +1242,7 @@ int launch_state(kg_tcache* c, StateArgs& a, cudaStream_t s, const double* d_x_f
     if (!tm.is_idealgas) {
         const long long tot = (long long) n * a.nslots * (tm.nc * (tm.nc + 1) / 2);
         if (c->ljs) ljs_rdf_kernel<<<(unsigned) (((long long) n * a.nslots + 127) / 128), 128, 0, s>>>(n, a.nslots, tm.nc, a.tidx, a.T_of, a.Vm, c->d_dbh, c->mp00, d_rdf);
+        else if (c->es) es_rdf_kernel<<<(unsigned) ((tot + 63) / 64), 64, 0, s>>>(n, a.nslots, tm, a.tidx, a.T_of, a.Vm, d_x_for_rdf, c->d_es_int, c->d_es_prm, d_rdf);
         else rdf_kernel<<<(unsigned) ((tot + 127) / 128), 128, 0, s>>>(n, a.nslots, tm, a.tidx, a.T_of, a.Vm, d_x_for_rdf, c->d_dbh, c->d_mp_int, d_rdf);
     }
     const int nn = tm.N * tm.nc, grid = (n + 127) / 128;

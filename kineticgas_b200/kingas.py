@@ -386,8 +386,8 @@ class QuantumMie(MieKinGas):
     u(r;T) = eps sum_k C_k beta^(bexp_k) (sigma/r)^lam_k with beta = eps/kT: 2, 4 or 6 power-law terms for FH order 0, 1, 2
     (cpp/QuantumMie.cpp:73-109). The device kernels take the terms' exponents from the model and the T-dependent
     effective coefficients C_eff(T) = C_k beta^bexp_k (cpp/ExtendedSutherland.cpp:182-200) per temperature. Collision
-    integrals are always integrated (ExtSutherland has no correlation branch). Only is_idealgas=True models can run the
-    state-point assembly (the extended-Sutherland RDF is not built yet)."""
+    integrals are always integrated (ExtSutherland has no correlation branch). is_idealgas=False runs the Revised Enskog
+    assembly with the extended-Sutherland RDF at contact (ExtSutherland::saft_rdf, cpp/ExtendedSutherland.cpp:315-333) on the device."""
 
     def __init__(self, comps, mole_weights=None, sigma=None, eps_div_k=None, la=None, lr=None, lij=0, kij=0,
                  N=4, FH_orders=None, is_idealgas=False, use_eos=None, device=0):

@@ -53,12 +53,12 @@ if __name__ == "__main__":
 R_GAS = 8.31446261815324
 
 
-def synthetic_eos(T, Vm, x, Mw):
+def synthetic_eos(T, Vm, x, Mw, B0=-1.0e-4):
     """EoS-derived inputs used identically by the reference (through the table-backed GenericEoS of oracle/ref_driver.cpp)
     and by the GPU path: an ideal-gas mixture plus a symmetric second-virial-like term. n = x (one mole), V = Vm."""
     x = np.asarray(x, float)
     nc = x.size
-    B = -1.0e-4 * (1.0 + 0.1 * (np.arange(nc)[:, None] + np.arange(nc)[None, :]))
+    B = B0 * (1.0 + 0.1 * (np.arange(nc)[:, None] + np.arange(nc)[None, :]))
     dmudn = R_GAS * T * (np.diag(1.0 / x) + 2.0 * B / Vm)
     cp_id = R_GAS * (2.5 + 0.35 * np.arange(1, nc + 1) + 1e-3 * (T - 300.0) * np.sqrt(np.asarray(Mw) / 16.0))
     dvdn = Vm * (1.0 + 0.05 * (np.arange(nc) - (nc - 1) / 2.0))
@@ -256,3 +256,47 @@ def ljs_transport_golden(fname="ljs_transport_reference.npz"):
 
 if __name__ == "__main__" and "ljs" in sys.argv[1:]:
     ljs_transport_golden()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Non-ideal QuantumMie: extended Sutherland RDF (cpp/ExtendedSutherland.cpp:315-333), transfer lengths, K-factors and the
+# Revised Enskog properties at finite density
+# ---------------------------------------------------------------------------------------------------------------
+QMIE_RET_CASES = [
+    # name, comps, FH order, N, [(T, rho_star of sigma_00, x)]
+    ("he_fh1", "HE", 1, 2, [(40.0, 0.05, [1.0]), (40.0, 0.4, [1.0]), (150.0, 0.25, [1.0])]),
+    ("h2_fh2", "H2", 2, 2, [(60.0, 0.3, [1.0])]),
+    ("he_h2_fh1", "HE,H2", 1, 2, [(80.0, 0.2, [0.3, 0.7]), (200.0, 0.45, [0.8, 0.2])]),
+]
+
+
+def qmie_ret_golden(fname="qmie_ret_reference.npz"):
+    from kineticgas_b200.fluids import MIE, MIE_FH
+    out = {}
+    for name, comps, fh, N, points in QMIE_RET_CASES:
+        ids = comps.split(",")
+        Mw = [MIE[c][0] for c in ids]
+        sig, epsk, la, lr = [[MIE_FH[(c, fh)][k] for c in ids] for k in range(4)]
+        m = ref.RefQuantumMie(Mw, sig, epsk, la, lr, fh, is_idealgas=False)
+        for k, (T, rho_star, x) in enumerate(points):
+            rho = rho_star / sig[0] ** 3
+            Vm = ref.AVOGADRO / rho
+            xi = [0.5, 0.5] if m.single else x
+            dmudn, cp_id, dvdn = synthetic_eos(T, Vm, x, Mw, B0=-5.0e-6)
+            m.set_eos(dmudn=dmudn, cp_id=cp_id, p=1e5, vm=Vm, dvdn=dvdn)
+            key = f"{name}_{k}"
+            out[key + "_in"] = np.array([T, Vm, rho] + list(xi))
+            out[key + "_dmudn"], out[key + "_cp"], out[key + "_dvdn"] = dmudn, cp_id, dvdn
+            out[key + "_rdf"] = m.rdf(rho, T, xi)
+            K, Kp = m.K_factors(rho, T, xi)
+            out[key + "_K"], out[key + "_Kp"] = K, Kp
+            out[key + "_mtl"], out[key + "_etl"] = m.mtl(rho, T, xi), m.etl(rho, T, xi)
+            out[key + "_viscosity"] = np.array(m.viscosity(T, Vm, xi, N))
+            out[key + "_contribs"] = m.thermal_conductivity_contribs(T, Vm, xi, N)
+            out[key + "_D_CoN"] = m.interdiffusion(T, Vm, xi, N, frame=1, dep=-1, solvent=-1, do_compress=True)
+            print(key, "rdf", out[key + "_rdf"].ravel(), "eta", out[key + "_viscosity"], "lambda", out[key + "_contribs"], flush=True)
+    np.savez(os.path.join(GOLD, fname), **out)
+
+
+if __name__ == "__main__" and "qmie_ret" in sys.argv[1:]:
+    qmie_ret_golden()
