@@ -40,6 +40,7 @@ struct Lane {
     double Bt[NT];     // eps C_t / (kT g^2)
     double lam[NT];
     double b;          // impact parameter / sigma
+    int ipath;         // every exponent is a small integer: powers by repeated squaring instead of exp(lam ln s)
 };
 
 // NT == 1 is the tag of the generic (piecewise polynomial x exponential) potentials: node rows { w/2u, 1/u^2, 1/u }
@@ -92,17 +93,31 @@ static __device__ __noinline__ void gen_eval(const GenPot* __restrict__ gp, doub
     dU = du * (gp->e_scale * gp->len_scale);
 }
 
-// u(r)/(kT g^2) and sigma u'(r)/(kT g^2) at r = ri sigma, sharing one log: s^lam = exp(lam ln s)
+// Bt_t (sigma/r)^lam_t at r = sigma / inv: binary powers for integer exponents (the pair-uniform common case, LJ and most
+// Mie fluids), else s^lam = exp(lam ln s) with one shared log
+template<int NT>
+__device__ __forceinline__ void lane_powers(const Lane<NT>& c, double inv, double (&p)[NT]) {
+    if (c.ipath) {
+#pragma unroll
+        for (int t = 0; t < NT; t++) p[t] = c.Bt[t] * ipow_pos(inv, (int) c.lam[t]);
+    } else {
+        const double ls = log(inv);
+#pragma unroll
+        for (int t = 0; t < NT; t++) p[t] = c.Bt[t] * exp(c.lam[t] * ls);
+    }
+}
+
+// u(r)/(kT g^2) and sigma u'(r)/(kT g^2) at r = ri sigma
 template<int NT>
 __device__ __forceinline__ void pot_eval(const Lane<NT>& c, double ri, double& U, double& dU) {
-    const double ls = -log(ri);
     const double inv = 1.0 / ri;
+    double p[NT];
+    lane_powers<NT>(c, inv, p);
     double u = 0.0, du = 0.0;
 #pragma unroll
     for (int t = 0; t < NT; t++) {
-        const double p = c.Bt[t] * exp(c.lam[t] * ls);
-        u += p;
-        du -= c.lam[t] * p;
+        u += p[t];
+        du -= c.lam[t] * p[t];
     }
     U = u;
     dU = du * inv;
@@ -192,9 +207,9 @@ template<int NT>
 __device__ __forceinline__ void shrink_until_nonneg(const Lane<NT>& c, double& r0, double& f0) {
     if (!(f0 < 0)) return;
     double p[NT], F[NT];
-    const double ls = -log(r0);
+    lane_powers<NT>(c, 1.0 / r0, p);
 #pragma unroll
-    for (int t = 0; t < NT; t++) { p[t] = c.Bt[t] * exp(c.lam[t] * ls); F[t] = exp(c.lam[t] * 0.05129329438755058); }    // -ln 0.95
+    for (int t = 0; t < NT; t++) F[t] = c.ipath ? ipow_pos(1.0 / 0.95, (int) c.lam[t]) : exp(c.lam[t] * 0.05129329438755058);    // 0.95^-lam
     int guard = 0;
     while (f0 < 0 && guard++ < 4000) {
         r0 *= 0.95;
@@ -530,6 +545,10 @@ __device__ __forceinline__ void make_lane(Lane<NT>& c, const PairParams& pp, con
         c.lam[t] = (t < pp.nterms) ? pp.lam[t] : 1.0;
     }
     c.b = b;
+    bool ip = true;
+#pragma unroll
+    for (int t = 0; t < NT; t++) ip = ip && (c.lam[t] == (double) (int) c.lam[t]) && (c.lam[t] >= 1.0) && (c.lam[t] <= 64.0);
+    c.ipath = ip;
 }
 template<>
 __device__ __forceinline__ void make_lane<1>(Lane<1>& c, const PairParams& pp, const double* coeff, double T, double g, double b) {
@@ -588,9 +607,7 @@ __device__ double lane_theta_integral(const PairParams& pp, const double* coeff,
     const double R = get_R<NT>(c, g, status);
     R_out = R;
     double A[NT];
-    const double ls = -log(R);
-#pragma unroll
-    for (int t = 0; t < NT; t++) A[t] = c.Bt[t] * exp(c.lam[t] * ls);      // (sigma/R)^lam, as pot_eval forms it
+    lane_powers<NT>(c, 1.0 / R, A);                                        // Bt (sigma/R)^lam, as pot_eval forms it
     const double q = R / b;
     if (!c_ts_exact) {
         bool redo, early; unsigned ex = 0;
@@ -611,9 +628,7 @@ __device__ double lane_theta_integral_defer(const PairParams& pp, const double* 
     int st = 0;
     const double R = get_R<NT>(c, g, st);
     double A[NT];
-    const double ls = -log(R);
-#pragma unroll
-    for (int t = 0; t < NT; t++) A[t] = c.Bt[t] * exp(c.lam[t] * ls);      // (sigma/R)^lam, as pot_eval forms it
+    lane_powers<NT>(c, 1.0 / R, A);                                        // Bt (sigma/R)^lam, as pot_eval forms it
     const double q = R / b;
     c2_out = q * q;
 #pragma unroll
