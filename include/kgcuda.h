@@ -150,6 +150,9 @@ int kg_set_exact_quadrature(int exact);
 #define KG_FOR_CON 1
 #define KG_FOR_COV 2
 #define KG_FOR_SOLVENT 3
+#define KG_FOR_ZARATE 4     /* Ortiz de Zarate frames (ideal gas only): D is always (nc-1) x (nc-1), D_T has nc-1 entries */
+#define KG_FOR_ZARATE_X 5
+#define KG_FOR_ZARATE_W 6
 
 #define KG_PROP_VISCOSITY          1u   /* KineticGas::viscosity                 cpp/KineticGas_properties.cpp:28-58   */
 #define KG_PROP_CONDUCTIVITY       2u   /* KineticGas::thermal_conductivity      cpp/KineticGas_properties.cpp:69-141  */
@@ -195,6 +198,8 @@ typedef struct {
     double* visc_vector;            /* [n][N nc]       get_viscosity_vector */
     double* thermal_diffusion_ratio; /* [n][nc]       k_T, KineticGas::thermal_diffusion_ratio (cpp/KineticGas_properties.cpp:282-312); needs
                                                       KG_PROP_THERMAL_DIFFUSION. thermal_diffusion_factor is alpha_ij = k_T,i - k_T,j (:314-323) */
+    double* soret_zarate;            /* [n][nc]       first nc-1 entries: KineticGas::soret_coefficient (:325-330), S_T = D^-1 D_T in the Zarate
+                                                      frame; needs frame = KG_FOR_ZARATE and KG_PROP_DIFFUSION | KG_PROP_THERMAL_DIFFUSION */
 } kg_transport_out;
 
 /* Device-resident per-temperature tables = what the reference keeps in KineticGasCache (cpp/KineticGasCache.h): every

@@ -605,7 +605,7 @@ struct StateArgs {
     const double *mtl, *etl;    // [nT][npairs_dev] (null for ideal gas)
     const double* brk;          // [nT][4][nc][nc][N][N]
     const double *dmudn, *cp_ideal, *pressure, *dvdn;
-    double *viscosity, *conductivity, *contribs, *D, *DT, *kT, *K, *Kp, *cond_matrix, *cond_vector, *visc_matrix, *visc_vector;
+    double *viscosity, *conductivity, *contribs, *D, *DT, *kT, *soret, *K, *Kp, *cond_matrix, *cond_vector, *visc_matrix, *visc_vector;
     int* status;
 };
 
@@ -801,7 +801,8 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
             for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) {
                 double v = (i == j) ? 1.0 : 0.0;
                 switch (a.opt.frame_of_reference) {
-                    case KG_FOR_CON: v += s.x[i] * ((s.wt[j] / s.x[j]) - 1); break;
+                    case KG_FOR_CON: case KG_FOR_ZARATE: case KG_FOR_ZARATE_X: case KG_FOR_ZARATE_W:
+                        v += s.x[i] * ((s.wt[j] / s.x[j]) - 1); break;
                     case KG_FOR_SOLVENT: v += s.x[i] * ((s.wt[j] / s.x[j]) - ((j == a.opt.solvent_idx ? 1 : 0) / s.x[a.opt.solvent_idx])); break;
                     case KG_FOR_COV: v += s.x[i] * ((s.wt[j] / s.x[j]) - (a.dvdn[(size_t) sp * (single ? 1 : nc) + (single ? 0 : j)] / s.Vm)); break;
                     default: break;
@@ -819,7 +820,53 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
                 Dd[i * nc + j] = v;
             }
         }
-        if (want_E && (props & KG_PROP_DIFFUSION) && a.D) {
+        // Ortiz de Zarate frames (cpp/KineticGas_properties.cpp:179-193, 262-277, 325-330, 397-418): similarity transforms of
+        // the compressed molar-frame matrix D^(x) with X = diag(x) - x x^T (mole fractions) and W (weight fractions)
+        const int fr = a.opt.frame_of_reference;
+        const bool zar = fr >= KG_FOR_ZARATE;
+        const int nm = nc - 1;
+        double Dz[MAXC * MAXC], Xm[MAXC * MAXC], Xlu[MAXC * MAXC];
+        int idm[MAXC], pz[MAXC];
+        if (want_E && zar) {
+            int q = 0;
+            for (int i = 0; i < nc; i++) if (i != dep) idm[q++] = i;
+            double Dx[MAXC * MAXC];
+            for (int i = 0; i < nm; i++) for (int j = 0; j < nm; j++)
+                Dx[i * MAXC + j] = Dd[idm[i] * nc + idm[j]] - (ksi[idm[j]] / ksi[dep]) * Dd[idm[i] * nc + dep];
+            for (int i = 0; i < nm; i++) for (int j = 0; j < nm; j++) {
+                Xm[i * MAXC + j] = ((i == j) ? s.x[idm[i]] : 0.0) - s.x[idm[i]] * s.x[idm[j]];
+                Xlu[i * MAXC + j] = Xm[i * MAXC + j];
+            }
+            if (lu_factor(Xlu, nm, MAXC, pz)) st |= KG_STATUS_SINGULAR;
+            if (fr == KG_FOR_ZARATE_X) { for (int k = 0; k < nm; k++) for (int j = 0; j < nm; j++) Dz[k * MAXC + j] = Dx[k * MAXC + j]; }
+            else {
+                // D = X^-1 D^(x) X, column by column
+                for (int cidx = 0; cidx < nm; cidx++) {
+                    double col[MAXC];
+                    for (int i = 0; i < nm; i++) { double v = 0.; for (int k = 0; k < nm; k++) v += Dx[i * MAXC + k] * Xm[k * MAXC + cidx]; col[i] = v; }
+                    lu_solve(Xlu, nm, MAXC, pz, col);
+                    for (int i = 0; i < nm; i++) Dz[i * MAXC + cidx] = col[i];
+                }
+                if (fr == KG_FOR_ZARATE_W) {
+                    // D^(w) = W D W^-1: rows m_r solve W^T m_r = (W D)_r^T
+                    double Wm[MAXC * MAXC], WT[MAXC * MAXC], WD[MAXC * MAXC]; int pw[MAXC];
+                    for (int i = 0; i < nm; i++) for (int j = 0; j < nm; j++) {
+                        Wm[i * MAXC + j] = ((i == j) ? s.wt[idm[i]] : 0.0) - s.wt[idm[i]] * s.wt[idm[j]];
+                        WT[j * MAXC + i] = Wm[i * MAXC + j];
+                    }
+                    for (int i = 0; i < nm; i++) for (int j = 0; j < nm; j++) { double v = 0.; for (int k = 0; k < nm; k++) v += Wm[i * MAXC + k] * Dz[k * MAXC + j]; WD[i * MAXC + j] = v; }
+                    if (lu_factor(WT, nm, MAXC, pw)) st |= KG_STATUS_SINGULAR;
+                    for (int r = 0; r < nm; r++) {
+                        double row[MAXC];
+                        for (int j = 0; j < nm; j++) row[j] = WD[r * MAXC + j];
+                        lu_solve(WT, nm, MAXC, pw, row);
+                        for (int j = 0; j < nm; j++) Dz[r * MAXC + j] = row[j];
+                    }
+                }
+            }
+            if ((props & KG_PROP_DIFFUSION) && a.D) for (int i = 0; i < nm; i++) for (int j = 0; j < nm; j++) a.D[((size_t) sp * nD + i) * nD + j] = Dz[i * MAXC + j];
+        }
+        if (want_E && !zar && (props & KG_PROP_DIFFUSION) && a.D) {
             int oi = 0;
             for (int i = 0; i < nc; i++) {
                 if (a.opt.do_compress && i == dep) continue;
@@ -832,7 +879,7 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
                 oi++;
             }
         }
-        if (want_E && (props & KG_PROP_THERMAL_DIFFUSION) && (a.DT || a.kT)) {
+        if (want_E && (props & KG_PROP_THERMAL_DIFFUSION) && (a.DT || a.kT || a.soret)) {
             // cpp/KineticGas_properties.cpp:208-258
             double bm[MAXC * MAXC], DT[MAXC], DT2[MAXC];
             for (int j = 0; j < nc; j++) for (int k = 0; k < nc; k++) {
@@ -855,7 +902,29 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
             for (int i = 0; i < nc; i++) { double v = 0.; for (int k = 0; k < nc; k++) v += psi[i * nc + k] * DT[k]; DT2[i] = v; }
             double tmp = 0.;
             for (int k = 0; k < nc; k++) for (int mm = 0; mm < nc; mm++) tmp += s.rho * s.x[mm] * bm[mm * nc + k];
-            if (a.DT) for (int i = 0; i < nc; i++) a.DT[(size_t) sp * nc + i] = (DT2[i] + (Dd[i * nc + dep] / ksi[dep]) * tmp) / AVOGADRO;
+            if (a.DT && !zar) for (int i = 0; i < nc; i++) a.DT[(size_t) sp * nc + i] = (DT2[i] + (Dd[i * nc + dep] / ksi[dep]) * tmp) / AVOGADRO;
+            if ((a.DT || a.soret) && zar) {
+                // D_T of the Zarate relation (:262-277): (-c X) D_T = (D_T,indep^(CoN) + c D^(x) x_indep) / T, c = 1 / Vm (nc - 1 entries)
+                const double cm = 1.0 / s.Vm;
+                double rhs[MAXC], XL[MAXC * MAXC]; int px[MAXC];
+                for (int i = 0; i < nm; i++) {
+                    double v = (DT2[idm[i]] + (Dd[idm[i] * nc + dep] / ksi[dep]) * tmp) / AVOGADRO;
+                    for (int j = 0; j < nm; j++) v += cm * (Dd[idm[i] * nc + idm[j]] - (ksi[idm[j]] / ksi[dep]) * Dd[idm[i] * nc + dep]) * s.x[idm[j]];
+                    rhs[i] = v / s.T;
+                    for (int j = 0; j < nm; j++) XL[i * MAXC + j] = -cm * Xm[i * MAXC + j];
+                }
+                if (lu_factor(XL, nm, MAXC, px)) st |= KG_STATUS_SINGULAR;
+                lu_solve(XL, nm, MAXC, px, rhs);
+                if (a.DT) for (int i = 0; i < nm; i++) a.DT[(size_t) sp * nc + i] = rhs[i];
+                if (a.soret) {
+                    // KineticGas::soret_coefficient (:325-330): S_T = D^-1 D_T, both in the Zarate frame
+                    double DL[MAXC * MAXC]; int pd[MAXC];
+                    for (int i = 0; i < nm; i++) for (int j = 0; j < nm; j++) DL[i * MAXC + j] = Dz[i * MAXC + j];
+                    if (lu_factor(DL, nm, MAXC, pd)) st |= KG_STATUS_SINGULAR;
+                    lu_solve(DL, nm, MAXC, pd, rhs);
+                    for (int i = 0; i < nm; i++) a.soret[(size_t) sp * nc + i] = rhs[i];
+                }
+            }
             if (a.kT) {
                 // KineticGas::thermal_diffusion_ratio (cpp/KineticGas_properties.cpp:282-312): always from the centre-of-mass
                 // frame quantities with the last component dependent, whatever frame the D / D_T outputs use.
@@ -1266,14 +1335,23 @@ extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const do
     if (!m->is_singlecomp && !x) { set_error("kg_transport_batch: mole fractions required"); return -1; }
     const unsigned props = opts->properties;
     const int nc = m->is_singlecomp ? 2 : m->ncomps, nce = m->is_singlecomp ? 1 : m->ncomps;
-    const bool want_D = ((props & KG_PROP_DIFFUSION) && out->D) || ((props & KG_PROP_THERMAL_DIFFUSION) && (out->DT || out->thermal_diffusion_ratio));
+    const bool want_D = ((props & KG_PROP_DIFFUSION) && out->D) || ((props & KG_PROP_THERMAL_DIFFUSION) && (out->DT || out->thermal_diffusion_ratio || out->soret_zarate));
     const bool want_lambda = (props & KG_PROP_CONDUCTIVITY) && (out->conductivity || out->conductivity_contribs);
     if (want_D && (!eos || !eos->dmudn)) { set_error("kg_transport_batch: EoS is not set (dmudn required)"); return -1; }
     if (want_lambda && (!eos || !eos->cp_ideal)) { set_error("kg_transport_batch: EoS is not set (cp_ideal required)"); return -1; }
     if ((props & KG_PROP_CONDUCTIVITY) && opts->N < 2) { set_error("kg_transport_batch: thermal conductivity needs N >= 2"); return -1; }
     if (want_D && opts->frame_of_reference == KG_FOR_COV && (!eos || !eos->dvdn)) {
         set_error("kg_transport_batch: EoS is not set (dvdn required for the CoV frame)"); return -1; }
-    if (opts->frame_of_reference < KG_FOR_COM || opts->frame_of_reference > KG_FOR_SOLVENT) { set_error("Unknown (not-implemented) Frame of Reference."); return -1; }
+    if (opts->frame_of_reference < KG_FOR_COM || opts->frame_of_reference > KG_FOR_ZARATE_W) { set_error("Unknown (not-implemented) Frame of Reference."); return -1; }
+    const bool zarate = opts->frame_of_reference >= KG_FOR_ZARATE;
+    if (zarate && want_D && !opts->is_idealgas) {
+        set_error((props & KG_PROP_THERMAL_DIFFUSION) && !(props & KG_PROP_DIFFUSION) ? "Zarate relation for thermal diffusion only implemented for ideal gas!"
+                                                                                   : "Zarate relation for diffusion only implemented for ideal gas!");     // cpp/KineticGas_properties.cpp:180,263
+        return -1;
+    }
+    if ((props & KG_PROP_THERMAL_DIFFUSION) && (out->DT || out->soret_zarate) && opts->frame_of_reference > KG_FOR_ZARATE) {
+        set_error("Unknown (not-implemented) Frame of Reference."); return -1; }       // CoM_to_FoR_matr has no zarate_x / zarate_w (:348-396)
+    if (out->soret_zarate && opts->frame_of_reference != KG_FOR_ZARATE) { set_error("kg_transport_batch: soret_zarate needs frame = zarate"); return -1; }
     if (opts->frame_of_reference == KG_FOR_SOLVENT && (opts->solvent_idx < 0 || opts->solvent_idx >= nc)) { set_error("kg_transport_batch: bad solvent index"); return -1; }
     if (opts->dependent_idx >= nc || opts->dependent_idx < -nc) { set_error("kg_transport_batch: bad dependent index"); return -1; }
     CUDA_OK(cudaSetDevice(m->device));
@@ -1298,8 +1376,9 @@ extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const do
     DevBuf db(m);
     StateArgs a; memset(&a, 0, sizeof(a));
     a.n = n; a.nT = c->nT; a.opt = *opts; a.opt.properties = props;
+    if (zarate) a.opt.do_compress = 1;            // the Zarate matrices are (nc - 1) x (nc - 1) by construction
     a.nslots = (props & KG_PROP_CONDUCTIVITY) ? 2 : 1;
-    const int N = opts->N, nn = N * nc, nD = opts->do_compress ? nc - 1 : nc;
+    const int N = opts->N, nn = N * nc, nD = a.opt.do_compress ? nc - 1 : nc;
 #define NEED(p) do { if (!(p)) { set_error("kg_transport_batch: device allocation or copy failed"); return -2; } } while (0)
     a.tidx = db.put(tidx.data(), n, s); NEED(a.tidx);
     a.T_of = c->d_T;
@@ -1314,7 +1393,7 @@ extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const do
     if (eos && eos->dvdn && opts->frame_of_reference == KG_FOR_COV) { a.dvdn = db.put(eos->dvdn, (size_t) n * nce, s); NEED(a.dvdn); }
     struct OutMap { double* host; double** dev; size_t count; };
     OutMap maps[] = {{out->viscosity, &a.viscosity, (size_t) n}, {out->conductivity, &a.conductivity, (size_t) n},
-                     {out->conductivity_contribs, &a.contribs, (size_t) n * 3}, {out->D, &a.D, (size_t) n * nD * nD}, {out->DT, &a.DT, (size_t) n * nc}, {out->thermal_diffusion_ratio, &a.kT, (size_t) n * nc},
+                     {out->conductivity_contribs, &a.contribs, (size_t) n * 3}, {out->D, &a.D, (size_t) n * nD * nD}, {out->DT, &a.DT, (size_t) n * nc}, {out->thermal_diffusion_ratio, &a.kT, (size_t) n * nc}, {out->soret_zarate, &a.soret, (size_t) n * nc},
                      {out->K, &a.K, (size_t) n * nc}, {out->K_prime, &a.Kp, (size_t) n * nc}, {out->cond_matrix, &a.cond_matrix, (size_t) n * nn * nn},
                      {out->cond_vector, &a.cond_vector, (size_t) n * nn}, {out->visc_matrix, &a.visc_matrix, (size_t) n * nn * nn},
                      {out->visc_vector, &a.visc_vector, (size_t) n * nn}};

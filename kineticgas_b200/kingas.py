@@ -16,7 +16,7 @@ from .model import DeviceModel, mie_desc, raise_on_status
 from .fluids import MIE, BOLTZMANN, AVOGADRO
 
 FLT_EPS = 1e-12
-FRAMES = {"CoM": 0, "CoN": 1, "CoV": 2, "solvent": 3}      # cpp/utils.h:37-45, KineticGas::frame_of_reference_map
+FRAMES = {"CoM": 0, "CoN": 1, "CoV": 2, "solvent": 3, "zarate": 4, "zarate_x": 5, "zarate_w": 6}      # cpp/utils.h:37-45, KineticGas::frame_of_reference_map
 PROP_VISCOSITY, PROP_CONDUCTIVITY, PROP_DIFFUSION, PROP_THERMAL_DIFFUSION = 1, 2, 4, 8
 
 
@@ -31,7 +31,7 @@ class EosInputs(C.Structure):
 
 class TransportOut(C.Structure):
     _fields_ = [(k, dp) for k in ("viscosity", "conductivity", "conductivity_contribs", "D", "DT", "rdf", "K", "K_prime",
-                                  "cond_matrix", "cond_vector", "visc_matrix", "visc_vector", "thermal_diffusion_ratio")]
+                                  "cond_matrix", "cond_vector", "visc_matrix", "visc_vector", "thermal_diffusion_ratio", "soret_zarate")]
 
 
 def _ptr(a):
@@ -209,16 +209,16 @@ class MieKinGas:
         xn = np.ascontiguousarray(np.broadcast_to(x, (n, self.ncomps)), float)
         nc = self.ncomps
         nn = N * nc
-        nD = nc - 1 if do_compress else nc
+        nD = nc - 1 if (do_compress or frame >= FRAMES["zarate"]) else nc
         shapes = {"viscosity": (n,), "conductivity": (n,), "conductivity_contribs": (n, 3), "D": (n, nD, nD), "DT": (n, nc),
                   "rdf": (n, nc, nc), "K": (n, nc), "K_prime": (n, nc), "cond_matrix": (n, nn, nn), "cond_vector": (n, nn),
-                  "visc_matrix": (n, nn, nn), "visc_vector": (n, nn), "thermal_diffusion_ratio": (n, nc)}
+                  "visc_matrix": (n, nn, nn), "visc_vector": (n, nn), "thermal_diffusion_ratio": (n, nc), "soret_zarate": (n, nc)}
         bufs = {k: np.zeros(shapes[k]) for k in want}
         out = TransportOut()
         for k, b in bufs.items():
             setattr(out, k, _ptr(b))
         opts = self._opts(N, properties, frame, dependent_idx, solvent_idx, do_compress)
-        want_D = ("D" in want) or ("DT" in want) or ("thermal_diffusion_ratio" in want)
+        want_D = ("D" in want) or ("DT" in want) or ("thermal_diffusion_ratio" in want) or ("soret_zarate" in want)
         eos_arr = self._eos_arrays(Tn, Vn, xn, want_D, ("conductivity" in want) or ("conductivity_contribs" in want),
                                    frame == FRAMES["CoV"] and want_D, eos_inputs)
         eos = EosInputs()
@@ -271,7 +271,10 @@ class MieKinGas:
             raise RuntimeError("Invalid frame of reference : " + frame_of_reference)
         r = self._run(T, Vm, x, N, PROP_THERMAL_DIFFUSION, ["DT"], frame=FRAMES[frame_of_reference], dependent_idx=dependent_idx,
                       solvent_idx=solvent_idx, **kw)
-        return r["DT"][0] if r["scalar"] else r["DT"]
+        DT = r["DT"]
+        if frame_of_reference == "zarate":          # Ncomps - 1 independent coefficients (cpp/KineticGas_properties.cpp:262-277)
+            DT = DT[:, :self.ncomps - 1]
+        return DT[0] if r["scalar"] else DT
 
     def thermal_diffusion_ratio(self, T, Vm, x, N=None, **kw):
         """k_T,i (pykingas/py_KineticGas.py:279-315 -> KineticGas::thermal_diffusion_ratio, cpp/KineticGas_properties.cpp:282-312)."""
@@ -287,8 +290,20 @@ class MieKinGas:
         kT = np.asarray(self.thermal_diffusion_ratio(T, Vm, x, N=N, **kw))
         return kT[..., :, None] - kT[..., None, :]
 
-    def soret_coefficient(self, T, Vm, x, N=None, **kw):
-        """S_T = alpha_T / T, the non-Zarate branch of pykingas/py_KineticGas.py:347-399."""
+    def soret_coefficient(self, T, Vm, x, N=None, use_zarate=True, dependent_idx=-1, **kw):
+        """pykingas/py_KineticGas.py:347-399. use_zarate (the reference's default): S_T = D^-1 D_T in the Zarate frame, Ncomps - 1
+        entries, ideal gas only (KineticGas::soret_coefficient, cpp/KineticGas_properties.cpp:325-330); else alpha_T / T."""
+        if use_zarate:
+            N = self.default_N if N is None else N
+            if N < 2:
+                warnings.warn(f"Thermal diffusion is a 2nd order phenomena, cannot be computed for N < 2 (got N = {N})", RuntimeWarning, stacklevel=2)
+                return np.full((self.ncomps, self.ncomps), np.nan)
+            if not self.is_idealgas:
+                raise RuntimeError("Zarate relation for Soret coefficient only implemented for ideal gas!")
+            r = self._run(T, Vm, x, N, PROP_DIFFUSION | PROP_THERMAL_DIFFUSION, ["soret_zarate"], frame=FRAMES["zarate"],
+                          dependent_idx=dependent_idx, **kw)
+            S = r["soret_zarate"][:, :self.ncomps - 1]
+            return S[0] if r["scalar"] else S
         a = self.thermal_diffusion_factor(T, Vm, x, N=N, **kw)
         T = np.asarray(T, float)
         return a / (T[..., None, None] if T.ndim else T)

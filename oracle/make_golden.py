@@ -300,3 +300,33 @@ def qmie_ret_golden(fname="qmie_ret_reference.npz"):
 
 if __name__ == "__main__" and "qmie_ret" in sys.argv[1:]:
     qmie_ret_golden()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Ortiz de Zarate frames (ideal gas): D in zarate / zarate_x / zarate_w, D_T (zarate), Soret coefficient
+# ---------------------------------------------------------------------------------------------------------------
+ZARATE_CASES = [("h2_o2", "H2,O2", 2, [(312.5, [0.25, 0.75])], -1), ("co2_c1_n2", "CO2,C1,N2", 2, [(350.0, [0.2, 0.3, 0.5]), (500.0, [0.6, 0.1, 0.3])], 1)]
+
+
+def zarate_golden(fname="zarate_reference.npz"):
+    out = {}
+    for name, comps, N, points, dep in ZARATE_CASES:
+        ids, Mw, s, e, la, lr = mie_parameters(comps)
+        m = ref.RefMie(Mw, s, e, la, lr, is_idealgas=True)
+        for k, (T, x) in enumerate(points):
+            Vm = 8.314 * T / 1e5
+            dmudn, cp_id, dvdn = synthetic_eos(T, Vm, x, Mw)
+            m.set_eos(dmudn=dmudn, cp_id=cp_id, p=1e5, vm=Vm, dvdn=dvdn)
+            key = f"{name}_{k}"
+            out[key + "_in"] = np.array([T, Vm, dep] + list(x))
+            out[key + "_dmudn"] = dmudn
+            for fr, nm_ in ((4, "zarate"), (5, "zarate_x"), (6, "zarate_w")):
+                out[key + "_D_" + nm_] = m.interdiffusion(T, Vm, x, N, frame=fr, dep=dep, solvent=-1, do_compress=True)
+            out[key + "_DT_zarate"] = m.thermal_diffusion_coeff(T, Vm, x, N, frame=4, dep=dep, solvent=-1)
+            out[key + "_soret"] = m.soret_coefficient(T, Vm, x, N, dep)
+            print(key, out[key + "_D_zarate"].ravel(), out[key + "_DT_zarate"], out[key + "_soret"], flush=True)
+    np.savez(os.path.join(GOLD, fname), **out)
+
+
+if __name__ == "__main__" and "zarate" in sys.argv[1:]:
+    zarate_golden()

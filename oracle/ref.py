@@ -62,6 +62,7 @@ def lib():
         L.kgref_thermal_diffusion_coeff.argtypes = [C.c_void_p, C.c_double, C.c_double, dp, C.c_int, C.c_int, C.c_int, C.c_int,
                                                     C.c_int, dp, ip]
         L.kgref_thermal_diffusion_ratio.argtypes = [C.c_void_p, C.c_double, C.c_double, dp, C.c_int, C.c_int, dp, ip]
+        L.kgref_soret_coefficient.argtypes = [C.c_void_p, C.c_double, C.c_double, dp, C.c_int, C.c_int, C.c_int, dp, ip]
         L.kgref_qmie_create.restype = C.c_void_p
         L.kgref_qmie_create.argtypes = [C.c_int, dp, dp, dp, dp, dp, C.c_int, C.c_int, C.c_int]
         L.kgref_set_internals.argtypes = [C.c_void_p, C.c_double, C.c_double]
@@ -254,7 +255,18 @@ def _ref_thermal_diffusion_ratio(self, T, Vm, x, N=2):
     return out[:n.value].copy()
 
 
+
+
+def _ref_soret_coefficient(self, T, Vm, x, N=2, dep=-1):
+    x = np.ascontiguousarray(x, float)
+    out = np.empty(self.nc)
+    n = C.c_int()
+    self._chk(self.L.kgref_soret_coefficient(self.h, T, Vm, _p(x), x.size, N, dep, _p(out), C.byref(n)))
+    return out[:n.value].copy()
+
+
 RefMie.thermal_diffusion_ratio = _ref_thermal_diffusion_ratio
+RefMie.soret_coefficient = _ref_soret_coefficient
 
 
 class RefQuantumMie(RefMie):

@@ -335,4 +335,13 @@ int kgref_thermal_diffusion_ratio(void* hv, double T, double Vm, const double* x
     });
 }
 
+int kgref_soret_coefficient(void* hv, double T, double Vm, const double* x, int nx, int N, int dep, double* out, int* n) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{
+        Eigen::VectorXd k = h->kin->soret_coefficient(T, Vm, vector1d(x, x + nx), N, dep);
+        *n = (int) k.size();
+        for (int i = 0; i < k.size(); i++) out[i] = k(i);
+    });
+}
+
 } // extern "C"
