@@ -645,6 +645,35 @@ __device__ double lane_theta_integral_defer(const PairParams& pp, const double* 
     if (!redo) { nodes += nd; status |= st; }
     return I;
 }
+// The same work in two phases, for the batched Omega kernels: lane_setup does the root finding (its own kernel: every lane
+// is in get_R, small code), lane_sum_defer the strided sum from the stored A_t = Bt (sigma/R)^lam_t and c2 = (R/b)^2.
+template<int NT>
+__device__ void lane_setup(const PairParams& pp, const double* coeff, double T, double g, double b, double (&A)[NT], double& c2, int& status) {
+    Lane<NT> c;
+    make_lane<NT>(c, pp, coeff, T, g, b);
+    const double R = get_R<NT>(c, g, status);
+    lane_powers<NT>(c, 1.0 / R, A);
+    const double q = R / b;
+    c2 = q * q;
+}
+template<int NT>
+__device__ double lane_sum_defer(const double* __restrict__ srows, const double* __restrict__ grows, int KS, const double (&A)[NT], double c2,
+                                 unsigned& nodes, unsigned& exec_nodes, int& status, bool& redo, double (&Ap_out)[NT]) {
+#pragma unroll
+    for (int t = 0; t < NT; t++) Ap_out[t] = c2 * A[t];
+    unsigned nd = 0;
+    int st = 0;
+    double I;
+    if (c_ts_exact) { redo = false; I = theta_integral<NT>(srows, grows, KS, A, c2, nd, st); exec_nodes += nd; }
+    else {
+        bool early;
+        I = theta_integral_em<NT>(srows, grows, KS, A, c2, nd, exec_nodes, st, redo, early);
+        // whole columns end early together (neighbouring lanes share g), so summing them here costs no divergence
+        if (redo && early) { redo = false; nd = 0; I = theta_integral<NT>(srows, grows, KS, A, c2, nd, st); exec_nodes += nd; }
+    }
+    if (!redo) { nodes += nd; status |= st; }
+    return I;
+}
 template<>
 __device__ inline double lane_theta_integral_defer<1>(const PairParams& pp, const double* coeff, const double* __restrict__ srows,
                                                       const double* __restrict__ grows, int KS, double T, double g, double b,

@@ -375,6 +375,34 @@ __global__ void __launch_bounds__(256) fill_kernel(const Item* __restrict__ item
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// theta set-up kernel (power-law potentials): one thread per work entry finds the distance of closest approach and stores
+// A_t = eps C_t (sigma/R)^lam_t / (kT g^2) and c2 = (R/b)^2, structure-of-arrays with stride `stride`. Splitting the root
+// finding from the sums keeps each kernel's code small (the fused kernel stalled on instruction fetch) and every warp in one phase.
+// ------------------------------------------------------------------------------------------------------------
+template<int NT>
+__global__ void __launch_bounds__(256) theta_setup_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes, const PairParams* __restrict__ pairs,
+                                                          const double* __restrict__ coeff_pool, const WorkEntry* __restrict__ list, int nlist,
+                                                          double* __restrict__ prm, long long stride, int* __restrict__ status_pool) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nlist) return;
+    if constexpr (NT != 1) {
+        const WorkEntry we = list[e];
+        const Item item = items[we.item];
+        const Regime rg = regimes[item.regime];
+        const double g = lattice_coord(we.nx, rg.dg);
+        const double b = (we.ny == LIM_ROW) ? 100.0 : lattice_coord(we.ny, rg.db);
+        const double* coeff = (item.coeff_off >= 0) ? coeff_pool + item.coeff_off : nullptr;
+        double A[NT], c2;
+        int st = 0;
+        lane_setup<NT>(pairs[item.pair], coeff, item.T, g, b, A, c2, st);
+#pragma unroll
+        for (int t = 0; t < NT; t++) prm[(long long) t * stride + e] = A[t];
+        prm[(long long) NT * stride + e] = c2;
+        if (st) atomicOr(&status_pool[we.item], st);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // theta kernel: one lane per theta integral. Persistent CTAs; the work list is sorted by pair, so a CTA walks the pair
 // segments in order, stages that pair's tanh-sinh rows in shared memory once, and its warps pull 32-entry tiles from
 // the segment's counter independently (no CTA barrier between tiles).
@@ -385,7 +413,7 @@ theta_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
              const double* const* __restrict__ rows_by_pair, const double* __restrict__ coeff_pool,
              const WorkEntry* __restrict__ list, const int* __restrict__ offsets, const int* __restrict__ pair_task_start, int npairs,
              int* __restrict__ tile_counters, double* __restrict__ tab_pool, double* __restrict__ lim_pool, int* __restrict__ status_pool,
-             unsigned long long* __restrict__ counters, int* __restrict__ redo_list, int* __restrict__ redo_count) {
+             unsigned long long* __restrict__ counters, const double* __restrict__ prm, long long prm_stride) {
     extern __shared__ double srows[];
     __shared__ PairParams spair;
     constexpr int W = 2 + NT;
@@ -420,7 +448,14 @@ theta_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
                 const double b = (we.ny == LIM_ROW) ? 100.0 : lattice_coord(we.ny, rg.db);   // theta_lim: b = 100 sigma (Spherical.cpp:316)
                 const double* coeff = (item.coeff_off >= 0) ? coeff_pool + item.coeff_off : nullptr;
                 unsigned ex = 0;
-                I = lane_theta_integral_defer<NT>(spair, coeff, srows, grows, KS_ROWS, item.T, g, b, nodes, ex, st, redo, Ap, cc);
+                if constexpr (NT == 1) I = lane_theta_integral_defer<NT>(spair, coeff, srows, grows, KS_ROWS, item.T, g, b, nodes, ex, st, redo, Ap, cc);
+                else {
+                    double A[NT];
+#pragma unroll
+                    for (int t = 0; t < NT; t++) A[t] = prm[(long long) t * prm_stride + e];
+                    cc = prm[(long long) NT * prm_stride + e];
+                    I = lane_sum_defer<NT>(srows, grows, KS_ROWS, A, cc, nodes, ex, st, redo, Ap);
+                }
                 my_exec += ex;
             }
             // integrals the strided sum rejected: the warp sums them node by node together, one after the other
@@ -835,6 +870,7 @@ struct kg_omega_plan {
     double* d_lim = nullptr; unsigned char* d_have_lim = nullptr;
     int2* d_tasks = nullptr; int *d_counts = nullptr, *d_offsets = nullptr;
     WorkEntry* d_list = nullptr;
+    double* d_prm = nullptr;          // [ntpad + 1][max_list] A_t and c2 of every work entry (theta_setup_kernel -> theta_kernel)
     double* d_gfac = nullptr; int *d_lr_l = nullptr, *d_lr_ri = nullptr;
     double* d_coeff = nullptr;
     double *d_W = nullptr, *d_omega = nullptr;          // [item][lr] in plan order
@@ -986,6 +1022,7 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
     PLAN_CUDA(kg_dmalloc(m, &p->d_counts, (p->ntasks + 1) * sizeof(int)));
     PLAN_CUDA(kg_dmalloc(m, &p->d_offsets, (p->ntasks + 1) * sizeof(int)));
     PLAN_CUDA(kg_dmalloc(m, &p->d_list, p->max_list * sizeof(WorkEntry)));
+    if (m->ntpad != 1) PLAN_CUDA(kg_dmalloc(m, &p->d_prm, (size_t) p->max_list * (m->ntpad + 1) * sizeof(double)));
     PLAN_CUDA(kg_dmalloc(m, &p->d_gfac, gfac.size() * sizeof(double)));
     PLAN_CUDA(kg_dmalloc(m, &p->d_lr_l, nlr * sizeof(int)));
     PLAN_CUDA(kg_dmalloc(m, &p->d_lr_ri, nlr * sizeof(int)));
@@ -1045,7 +1082,7 @@ extern "C" void kg_omega_plan_destroy(kg_omega_plan* p) {
 static void plan_free(kg_omega_plan* p) {
     cudaSetDevice(p->device);
     void* ptrs[] = {p->d_items, p->d_regimes, p->d_tab, p->d_want, p->d_known, p->d_lim, p->d_have_lim, p->d_tasks, p->d_counts,
-                    p->d_offsets, p->d_list, p->d_gfac, p->d_lr_l, p->d_lr_ri, p->d_coeff, p->d_W, p->d_omega, p->d_W_out,
+                    p->d_offsets, p->d_list, p->d_prm, p->d_gfac, p->d_lr_l, p->d_lr_ri, p->d_coeff, p->d_W, p->d_omega, p->d_W_out,
                     p->d_omega_out, p->d_status, p->d_flags, p->d_tile_counter, p->d_perm, p->d_counters, p->d_cells[0], p->d_cells[1], p->d_ncells, p->d_pair_task_start,
                     p->d_active, p->d_active_mask, p->d_active_cell_off, p->d_chunk_sums};
     for (void* q : ptrs) p->m->dfree(q);
@@ -1107,16 +1144,18 @@ extern "C" int kg_omega_plan_run(kg_omega_plan* p) {
             const int ntiles = (nlist + THETA_THREADS - 1) / THETA_THREADS;
             const int grid = std::min(ntiles, 2 * m->sm_count);
             CUDA_OK(cudaEventRecord(p->ev[2], s));
-#define LAUNCH_THETA(NT) theta_kernel<NT><<<grid, THETA_THREADS, smem, s>>>(p->d_items, p->d_regimes, m->d_pairs, m->d_rows_by_pair, p->d_coeff, \
+#define LAUNCH_THETA(NT) if (NT != 1) theta_setup_kernel<NT><<<(nlist + 255) / 256, 256, 0, s>>>(p->d_items, p->d_regimes, m->d_pairs, p->d_coeff, p->d_list, nlist, \
+                p->d_prm, p->max_list, p->d_status); \
+            theta_kernel<NT><<<grid, THETA_THREADS, smem, s>>>(p->d_items, p->d_regimes, m->d_pairs, m->d_rows_by_pair, p->d_coeff, \
                 p->d_list, p->d_offsets, p->d_pair_task_start, m->npairs, p->d_tile_counter, p->d_tab, p->d_lim, p->d_status, p->d_counters, \
-                nullptr, nullptr); \
-            LAUNCHED("theta_kernel")
+                p->d_prm, p->max_list); \
+            LAUNCHED("theta kernels")
             switch (m->ntpad) { case 1: LAUNCH_THETA(1); break; case 2: LAUNCH_THETA(2); break; case 4: LAUNCH_THETA(4); break; default: LAUNCH_THETA(6); break; }
 #undef LAUNCH_THETA
             CUDA_OK(cudaEventRecord(p->ev[3], s));
             finalize_kernel<<<(nlist + 255) / 256, 256, 0, s>>>(p->d_items, p->d_regimes, p->d_list, p->d_offsets + p->ntasks, p->d_tab, p->d_lim,
                                                                p->d_known, p->d_have_lim);
-            p->launches += 3;
+            p->launches += (m->ntpad != 1) ? 4 : 3;
         }
         // 2. evaluate this level's cells, emit the next level
         CUDA_OK(cudaMemsetAsync(p->d_ncells, 0, sizeof(int), s));

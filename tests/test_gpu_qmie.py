@@ -53,8 +53,13 @@ def test_ideal_gas_properties(key):
     assert abs(D / GOLD[key + "_D"][0, 0] - 1) < 1e-6
 
 
-def test_nonideal_is_refused():
-    from kineticgas_b200 import QuantumMie
+def test_nonideal_models_without_rdf_are_refused():
+    """Potentials without an RDF model keep the reference's error (cpp/KineticGas.h:259); QuantumMie has one since the extended
+    Sutherland RDF runs on the device (tests/test_gpu_qmie_ret.py)."""
+    from kineticgas_b200 import QuantumMie, HFD_B2
     kin = QuantumMie("HE", FH_orders=1, N=2, is_idealgas=False)
+    assert kin.viscosity(100.0, 1e-3, [1.0], N=2) > 0
+    gen = HFD_B2("HE", N=2)
+    gen.is_idealgas = False
     with pytest.raises(RuntimeError, match="RDF model is not implemented"):
-        kin.viscosity(100.0, 1e-3, [1.0], N=2)
+        gen.viscosity(100.0, 1e-3, [1.0], N=2)
