@@ -111,17 +111,17 @@ __device__ __forceinline__ void mesh_mark_cell(const MeshView& v, int Nx, int Ny
     if (sx < 0) { mesh_mark(v, Nx + sx, Ny); mesh_mark(v, Nx + sx, Ny + sy); }
 }
 
-// cos(chi) at lattice node (Nx,Ny) (known by construction); cut-off nodes return NaN as the "integrand is 0" marker
+// cos(chi) at lattice node (Nx,Ny) (known by construction). Cut-off nodes (integrand identically 0, cpp/Spherical.cpp:99) return
+// exactly 1.0: 1 - 1^l = 0 for every l, so the integrand formula below gives +0.0 there without a special case.
 __device__ __forceinline__ double mesh_cos(const MeshView& v, int Nx, int Ny) {
-    if ((Ny >= v.ny_cut) && (Nx >= v.nx_cut)) return __longlong_as_double(0x7ff8000000000000LL);
-    return (Ny == 0) ? v.cospi : v.tab[(long long) Nx * v.ny + Ny];
+    if ((Ny >= v.ny_cut) && (Nx >= v.nx_cut)) return 1.0;
+    if (Ny == 0) return v.cospi;
+    const double t = v.tab[(long long) Nx * v.ny + Ny];
+    return (t != t) ? 1.0 : t;                       // a NaN table entry (failed root finding, flagged in status) contributes 0 as before
 }
 
-// integrand value, cpp/Spherical.cpp:96-102: gf = 2 exp(-g^2) g^(2r+3), c = cos(chi), b = impact parameter / sigma
-__device__ __forceinline__ double mesh_f(double gf, double c, double b, int l) {
-    if (c != c) return 0.0;
-    double cl = c;
-    for (int i = 1; i < l; i++) cl *= c;
+// integrand value, cpp/Spherical.cpp:96-102: gf = 2 exp(-g^2) g^(2r+3), cl = cos(chi)^l, b = impact parameter / sigma
+__device__ __forceinline__ double mesh_f(double gf, double cl, double b) {
     return __dmul_rn(__dmul_rn(gf, __dsub_rn(1.0, cl)), b);
 }
 
@@ -182,6 +182,9 @@ __global__ void __launch_bounds__(256, 4) mesh_level_kernel(const Item* __restri
                                                          const int* __restrict__ lr_r_index, int nr_distinct, int gfac_stride, double cospi,
                                                          int nlr, const Cell* __restrict__ cells_in, int n_in, Cell* __restrict__ cells_out,
                                                          int* __restrict__ n_out, int cap_out, double* __restrict__ W, int* __restrict__ flags) {
+    // cos(chi) of the nine nodes a cell reads, [node][thread]: the member loop keeps their l-th powers in registers and
+    // multiplies them up from here as l grows along the (l,r) list (l-major lists never restart)
+    __shared__ double s_c[9][256];
     const unsigned full = 0xffffffffu;
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     const bool active = e < n_in;
@@ -206,6 +209,12 @@ __global__ void __launch_bounds__(256, 4) mesh_level_kernel(const Item* __restri
         if (sx < 0) { cXb = mesh_cos(v, Nx + sx, Ny); cXt = mesh_cos(v, Nx + sx, Ny + sy); }
         b0 = lattice_coord(Ny, v.db); b1 = lattice_coord(Ny + sy, v.db); b2 = lattice_coord(Ny + 2 * sy, v.db);
     }
+    {
+        const int tx = threadIdx.x;
+        s_c[0][tx] = c0; s_c[1][tx] = c1x; s_c[2][tx] = c2x; s_c[3][tx] = c1y; s_c[4][tx] = c2y; s_c[5][tx] = c11; s_c[6][tx] = c22;
+        s_c[7][tx] = cXb; s_c[8][tx] = cXt;
+    }
+    int lcur = 1;                                    // c0 .. cXt hold cos^lcur from here on
     // hx, hy are powers of two, so the reference's divisions are exact scalings and are done as multiplications
     const int ehx = v.ldg + lx, ehy = v.ldb + ly;
     const double hx = pow2(ehx), hy = pow2(ehy), hx2 = pow2(2 * ehx), hy2 = pow2(2 * ehy);
@@ -223,13 +232,25 @@ __global__ void __launch_bounds__(256, 4) mesh_level_kernel(const Item* __restri
         const int lr = __ffsll((long long) um) - 1;
         um &= um - 1;
         double contrib = 0.0;
+        const int l = lr_l[lr];
+        if (l != lcur) {                                 // warp-uniform: same successive products as pow by repeated multiplication
+            const int tx = threadIdx.x;
+            if (l < lcur) {
+                c0 = s_c[0][tx]; c1x = s_c[1][tx]; c2x = s_c[2][tx]; c1y = s_c[3][tx]; c2y = s_c[4][tx]; c11 = s_c[5][tx]; c22 = s_c[6][tx];
+                cXb = s_c[7][tx]; cXt = s_c[8][tx];
+                lcur = 1;
+            }
+            for (; lcur < l; lcur++) {
+                c0 *= s_c[0][tx]; c1x *= s_c[1][tx]; c2x *= s_c[2][tx]; c1y *= s_c[3][tx]; c2y *= s_c[4][tx]; c11 *= s_c[5][tx]; c22 *= s_c[6][tx];
+                cXb *= s_c[7][tx]; cXt *= s_c[8][tx];
+            }
+        }
         if (active && ((c.hi >> lr) & 1ull)) {
-            const int l = lr_l[lr];
             const double* gf = gfac_pool + ((long long) regime * nr_distinct + lr_r_index[lr]) * gfac_stride;
             const double g0 = gf[Nx], g1 = gf[Nx + ax], g2 = gf[Nx + 2 * ax];
-            const double f = mesh_f(g0, c0, b0, l), f1x = mesh_f(g1, c1x, b0, l), f2x = mesh_f(g2, c2x, b0, l);
-            const double f1y = mesh_f(g0, c1y, b1, l), f2y = mesh_f(g0, c2y, b2, l);
-            const double f1x1y = mesh_f(g1, c11, b1, l), f2x2y = mesh_f(g2, c22, b2, l);
+            const double f = mesh_f(g0, c0, b0), f1x = mesh_f(g1, c1x, b0), f2x = mesh_f(g2, c2x, b0);
+            const double f1y = mesh_f(g0, c1y, b1), f2y = mesh_f(g0, c2y, b2);
+            const double f1x1y = mesh_f(g1, c11, b1), f2x2y = mesh_f(g2, c22, b2);
             // second-difference estimator in the reference's operation order, no FMA contraction (decision predicate)
             const double fxx = __dmul_rn(__dadd_rn(__dsub_rn(f, __dmul_rn(2.0, f1x)), f2x), ihx2);
             const double fyy = __dmul_rn(__dadd_rn(__dsub_rn(f, __dmul_rn(2.0, f1y)), f2y), ihy2);
@@ -252,7 +273,7 @@ __global__ void __launch_bounds__(256, 4) mesh_level_kernel(const Item* __restri
                 // leaf: the two triangles the sweep adds for this cell, (Eb,Et,Xb) and (Et,Xb,Xt) (Integration.cpp:218-234);
                 // a linear interpolant integrates to area * mean of its corner values
                 double fXb = f1x, fXt = f1x1y;
-                if (sx < 0) { const double gm = gf[Nx + sx]; fXb = mesh_f(gm, cXb, b0, l); fXt = mesh_f(gm, cXt, b1, l); }
+                if (sx < 0) { const double gm = gf[Nx + sx]; fXb = mesh_f(gm, cXb, b0); fXt = mesh_f(gm, cXt, b1); }
                 contrib = (hx * hy / 6.0) * (f + 2.0 * f1y + 2.0 * fXb + fXt);
             }
         }
