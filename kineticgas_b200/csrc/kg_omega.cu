@@ -203,9 +203,10 @@ __global__ void __launch_bounds__(256, 4) mesh_level_kernel(const Item* __restri
         const Regime rg = regimes[item.regime];
         regime = item.regime;
         v = make_view(item, rg, tab_pool, want_pool, cospi);
-        c0 = mesh_cos(v, Nx, Ny); c1x = mesh_cos(v, Nx + ax, Ny); c2x = mesh_cos(v, Nx + 2 * ax, Ny);
-        c1y = mesh_cos(v, Nx, Ny + sy); c2y = mesh_cos(v, Nx, Ny + 2 * sy);
-        c11 = mesh_cos(v, Nx + ax, Ny + sy); c22 = mesh_cos(v, Nx + 2 * ax, Ny + 2 * sy);
+        c0 = mesh_cos(v, Nx, Ny); c1x = mesh_cos(v, Nx + ax, Ny); c1y = mesh_cos(v, Nx, Ny + sy); c11 = mesh_cos(v, Nx + ax, Ny + sy);
+        // a cell at the finest step in both directions cannot split: it is integrated whatever the refinement test says, so the
+        // three far probes of the test (and the test) are skipped for it -- most cells of the last level are of this kind
+        if (ax > 1 || sy > 1) { c2x = mesh_cos(v, Nx + 2 * ax, Ny); c2y = mesh_cos(v, Nx, Ny + 2 * sy); c22 = mesh_cos(v, Nx + 2 * ax, Ny + 2 * sy); }
         if (sx < 0) { cXb = mesh_cos(v, Nx + sx, Ny); cXt = mesh_cos(v, Nx + sx, Ny + sy); }
         b0 = lattice_coord(Ny, v.db); b1 = lattice_coord(Ny + sy, v.db); b2 = lattice_coord(Ny + 2 * sy, v.db);
     }
@@ -247,10 +248,12 @@ __global__ void __launch_bounds__(256, 4) mesh_level_kernel(const Item* __restri
         }
         if (active && ((c.hi >> lr) & 1ull)) {
             const double* gf = gfac_pool + ((long long) regime * nr_distinct + lr_r_index[lr]) * gfac_stride;
-            const double g0 = gf[Nx], g1 = gf[Nx + ax], g2 = gf[Nx + 2 * ax];
-            const double f = mesh_f(g0, c0, b0), f1x = mesh_f(g1, c1x, b0), f2x = mesh_f(g2, c2x, b0);
-            const double f1y = mesh_f(g0, c1y, b1), f2y = mesh_f(g0, c2y, b2);
-            const double f1x1y = mesh_f(g1, c11, b1), f2x2y = mesh_f(g2, c22, b2);
+            const double g0 = gf[Nx], g1 = gf[Nx + ax];
+            const double f = mesh_f(g0, c0, b0), f1x = mesh_f(g1, c1x, b0), f1y = mesh_f(g0, c1y, b1), f1x1y = mesh_f(g1, c11, b1);
+            bool split = false;
+            if (can_x || can_y) {
+            const double g2 = gf[Nx + 2 * ax];
+            const double f2x = mesh_f(g2, c2x, b0), f2y = mesh_f(g0, c2y, b2), f2x2y = mesh_f(g2, c22, b2);
             // second-difference estimator in the reference's operation order, no FMA contraction (decision predicate)
             const double fxx = __dmul_rn(__dadd_rn(__dsub_rn(f, __dmul_rn(2.0, f1x)), f2x), ihx2);
             const double fyy = __dmul_rn(__dadd_rn(__dsub_rn(f, __dmul_rn(2.0, f1y)), f2y), ihy2);
@@ -259,7 +262,8 @@ __global__ void __launch_bounds__(256, 4) mesh_level_kernel(const Item* __restri
             t = __dsub_rn(t, __dmul_rn(hy2, fyy));
             const double fxy = __dmul_rn(t, ihxy);
             const double dblder = __dadd_rn(__dadd_rn(fabs(fxx), fabs(fyy)), fabs(fxy));
-            if ((__dmul_rn(dblder, hs3) > v.lim) && (can_x || can_y)) {
+            if (__dmul_rn(dblder, hs3) > v.lim) {
+                split = true;
                 const double cx = __dmul_rn(fabs(fxx), hx3);
                 const double cy = __dmul_rn(fabs(fyy), hy3);
                 const unsigned long long bit = 1ull << lr;
@@ -269,7 +273,8 @@ __global__ void __launch_bounds__(256, 4) mesh_level_kernel(const Item* __restri
                 else if (can_x) mx |= bit;
                 else my |= bit;
             }
-            else {
+            }
+            if (!split) {
                 // leaf: the two triangles the sweep adds for this cell, (Eb,Et,Xb) and (Et,Xb,Xt) (Integration.cpp:218-234);
                 // a linear interpolant integrates to area * mean of its corner values
                 double fXb = f1x, fXt = f1x1y;
