@@ -135,6 +135,17 @@ __device__ __forceinline__ MeshView make_view(const Item& item, const Regime& rg
     return v;
 }
 
+// tasks[col_off + nx] = (item, nx) for every lattice column of every active item (col_off counts columns in item order)
+__global__ void build_tasks_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes, const int* __restrict__ active, int nactive,
+                                   int2* __restrict__ tasks) {
+    const int a = blockIdx.x;
+    if (a >= nactive) return;
+    const int it = active[a];
+    const Item item = items[it];
+    const int nx = regimes[item.regime].nx;
+    for (int k = threadIdx.x; k < nx; k += blockDim.x) tasks[item.col_off + k] = make_int2(it, k);
+}
+
 // level 0: the coarse cells of every active item in the reference's sweep order (Integration.cpp:240-280: row k runs +x
 // for even k, -x for odd k), owned by all requested (l,r) of the item, and the lattice nodes they read. grid.x = active items.
 __global__ void __launch_bounds__(128) mesh_init_kernel(const Item* __restrict__ items, const Regime* __restrict__ regimes,
@@ -996,16 +1007,12 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
             perm.push_back(t * Np + pi);
         }
     }
-    std::vector<int2> tasks; tasks.reserve(p->ncols_total);
-    for (int it = 0; it < p->nitems; it++) {
-        if (!item_active[it]) continue;
-        const Regime& rg = regs[p->items[it].regime];
-        for (int nx = 0; nx < rg.nx; nx++) tasks.push_back(make_int2(it, nx));
-    }
+    // tasks (one per lattice column of an active item, in item order = pair-major) are written on the device by
+    // build_tasks_kernel; the first task of pair q is the col_off of its first active item
     p->nactive = (int) active.size();
-    p->ntasks = (int) tasks.size();
+    p->ntasks = (int) p->ncols_total;
     std::vector<int> pair_task_start(Np + 1, p->ntasks);
-    for (int t = p->ntasks - 1; t >= 0; t--) pair_task_start[p->items[tasks[t].x].pair] = t;
+    for (int a = (int) active.size() - 1; a >= 0; a--) { const Item& it = p->items[active[a]]; pair_task_start[it.pair] = (int) it.col_off; }
     for (int q = Np - 1; q >= 0; q--) if (pair_task_start[q] > pair_task_start[q + 1]) pair_task_start[q] = pair_task_start[q + 1];
     // g-factor tables 2 exp(-g^2) g^(2r+3) per (regime, distinct r): same libm calls, same order as cpp/Spherical.cpp:101
     std::vector<int> rvals, lr_ri(nlr);
@@ -1023,17 +1030,18 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
     p->cospi = cos(PI - 2.0 * 0.0);
     // The worst case list (every node of every lattice) is never reached: nodes in the cut-off region (b>2.5, g>1.5) are
     // never requested. Cap by the count of requestable nodes.
-    long long cap = 0;
-    for (int it = 0; it < p->nitems; it++) {
-        if (!item_active[it]) continue;
-        const Regime& rg = regs[p->items[it].regime];
+    long long cap = 0, cap_of_regime[5];
+    for (int k = 0; k < 5; k++) {
+        const Regime& rg = regs[k];
+        cap_of_regime[k] = 0;
         for (int nx = 0; nx < rg.nx; nx++) {
             const double g = 1e-7 + nx * rg.dg;
             int nyreq = rg.ny;
             if (g > 1.5) nyreq = std::min(rg.ny, (int) (2.5 / rg.db) + 2);
-            cap += nyreq + 1;
+            cap_of_regime[k] += nyreq + 1;
         }
     }
+    for (int it = 0; it < p->nitems; it++) if (item_active[it]) cap += cap_of_regime[p->items[it].regime];
     p->max_list = cap;
 
 #define PLAN_CUDA(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { set_error(std::string(#expr) + ": " + cudaGetErrorString(e_)); plan_free(p); return -2; } } while (0)
@@ -1085,13 +1093,16 @@ extern "C" int kg_omega_plan_create_masked(kg_model* m, int nT, const double* T,
     }
     PLAN_CUDA(cudaMemcpy(p->d_items, p->items.data(), p->nitems * sizeof(Item), cudaMemcpyHostToDevice));
     PLAN_CUDA(cudaMemcpy(p->d_regimes, regs, sizeof(regs), cudaMemcpyHostToDevice));
-    PLAN_CUDA(cudaMemcpy(p->d_tasks, tasks.data(), p->ntasks * sizeof(int2), cudaMemcpyHostToDevice));
+    if (p->nactive > 0) {
+        build_tasks_kernel<<<p->nactive, 64, 0, m->stream>>>(p->d_items, p->d_regimes, p->d_active, p->nactive, p->d_tasks);
+        PLAN_CUDA(cudaGetLastError());
+    }
     PLAN_CUDA(cudaMemcpy(p->d_gfac, gfac.data(), gfac.size() * sizeof(double), cudaMemcpyHostToDevice));
     PLAN_CUDA(cudaMemcpy(p->d_lr_l, l, nlr * sizeof(int), cudaMemcpyHostToDevice));
     PLAN_CUDA(cudaMemcpy(p->d_lr_ri, lr_ri.data(), nlr * sizeof(int), cudaMemcpyHostToDevice));
     PLAN_CUDA(cudaMemcpy(p->d_perm, perm.data(), p->nitems * sizeof(int), cudaMemcpyHostToDevice));
     for (int k = 0; k < 4; k++) PLAN_CUDA(cudaEventCreate(&p->ev[k]));
-    p->h2d_bytes = (long long) p->nitems * sizeof(Item) + sizeof(regs) + (long long) p->ntasks * sizeof(int2) + gfac.size() * sizeof(double)
+    p->h2d_bytes = (long long) p->nitems * sizeof(Item) + sizeof(regs) + gfac.size() * sizeof(double)
                  + 2LL * nlr * sizeof(int) + (long long) p->nitems * sizeof(int) + (coeff_T ? (long long) nT * Np * m->coeff_stride * sizeof(double) : 0);
 #undef PLAN_CUDA
     kg_register_child(p, m, 0);
