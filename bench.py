@@ -469,7 +469,7 @@ def main():
                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                "data": "synthetic", "config": config, "clocks": clocks, "gpu_launches": launches,
                "e2e": {"value": e2e_value, "unit": "Omega/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-               "roofline": {"bound": "fp64", "kernel": "theta_kernel<2>", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s",
+               "roofline": {"bound": "fp64", "kernel": "theta_setup_kernel<2> + theta_kernel<2> (root finding + tanh-sinh sums of one pass, timed together)", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s",
                             "frac": (achieved / peak_tflops) if achieved else None, "traffic": None,
                             "peak_source": "kg_measure_fp64_peak: DFMA chain measured in this run (MEASURED_PEAKS.json has no FP64 figure; "
                                            "datasheet 37 TFLOP/s)",
