@@ -272,18 +272,22 @@ def run_five_comp(local_rank, rank, n_gpus, steps):
 
 # ------------------------------------------------------------------------------------------------ clocks
 class ClockSampler:
-    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+    """nvidia-smi polled every 50 ms from before the warm-up (its start-up takes longer than a short timed region); stop(t0, t1)
+    keeps the samples taken between the wall-clock marks of the timed region, widened by 150 ms on both sides (the GPU is busy
+    with warm-up steps before and the end-to-end loop after)."""
+    Q = "timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
     def __init__(self, index):
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         try:
-            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50"],
                                       stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:
             self.p = None
 
-    def stop(self):
+    def stop(self, t0=None, t1=None):
+        import datetime
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
         if self.p is None:
             return out
@@ -298,6 +302,10 @@ class ClockSampler:
         sm, reasons = [], set()
         for r in rows:
             try:
+                ts = datetime.datetime.strptime(r[0].strip(), "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                if t0 is not None and not (t0 - 0.15 <= ts <= t1 + 0.15):
+                    continue
+                r = r[1:]
                 sm.append(float(r[0]))
                 out["sm_max_mhz"] = float(r[1])
                 for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[3:7]):
@@ -314,7 +322,27 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------ main
+_REAL_STDOUT = None
+
+
+def guard_stdout():
+    """Libraries (NCCL's version banner, for one) write to file descriptor 1; the contract is ONE JSON line on stdout. Everything written
+    to fd 1 from here on goes to stderr, emit() writes the line to the original stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    fd = _REAL_STDOUT if _REAL_STDOUT is not None else 1
+    os.write(fd, (line + "\n").encode())
+
+
 def main():
+    guard_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
@@ -350,7 +378,7 @@ def main():
                 vals.append(cb)
         v = float(np.mean([c["value"] for c in vals]))
         cb = dict(vals[-1]); cb["value"] = v
-        print(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": "Omega/s", "n_gpus": n_gpus, "steps": args.steps,
+        emit(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": "Omega/s", "n_gpus": n_gpus, "steps": args.steps,
                           "warmup": args.warmup, "ms_per_step": 1e3 * n_sample / v, "higher_is_better": True, "scaling": "weak",
                           "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config, "cpu_baseline": cb,
                           "e2e": {"value": v, "unit": "Omega/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
@@ -385,14 +413,15 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local_rank) if rank == 0 else None
     for _ in range(max(args.warmup, 3)):
         step()
     barrier()
     peak_tflops, peak_mhz = measure_fp64_peak(local_rank)
-    sampler = ClockSampler(local_rank) if rank == 0 else None
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     theta_ms, nodes, mesh_ms, launches, exec_nodes, redo, n_theta = 0.0, 0.0, 0.0, 0, 0.0, 0.0, 0.0
     barrier()
+    wall0 = time.time()
     ev0.record(stream)
     for _ in range(args.steps):
         step()
@@ -403,8 +432,8 @@ def main():
         exec_nodes += q["executed_nodes"]; redo += q["redo_integrals"]; n_theta += q["theta_integrals"]
     ev1.record(stream)
     barrier()
+    wall1 = time.time()
     ms = ev0.elapsed_time(ev1)
-    clocks = sampler.stop() if sampler else None
     tmax = torch.tensor([ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -438,6 +467,8 @@ def main():
     if world > 1:
         dist.all_reduce(t2, op=dist.ReduceOp.MAX)
     e2e_value = n_out * world * args.steps / (float(t2.item()) * 1e-3)
+
+    clocks = sampler.stop(wall0, wall1) if sampler else None
 
     # RET state points (configs[2]): every rank runs its own grid; max over ranks
     sp = None
@@ -524,7 +555,7 @@ def main():
             n_sample = args.cpu_sample or min(64, max(16, cores))
             cb, _ = run_cpu_reference(n_gpus, n_sample, min(cores, n_sample))
             out["cpu_baseline"] = cb
-        print(json.dumps(out))
+        emit(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
 
