@@ -14,8 +14,9 @@
 //                     sweep's cells to the next level and mark the lattice nodes they read)
 //     count/scan/fill: compaction of the newly marked nodes of all items into one work list (sorted by pair, item,
 //                     column, row -> neighbouring lanes integrate neighbouring trajectories)
-//     theta_kernel  : one lane per theta integral (kg_device.cuh), persistent CTAs, 512-node tiles, tanh-sinh rows of
-//                     the pair staged in shared memory
+//     theta_setup   : one thread per work entry: distance of closest approach (get_R), stores A_t and (R/b)^2 (power-law potentials)
+//     theta_kernel  : one lane per theta integral (kg_device.cuh), persistent CTAs, 32-entry tiles per warp, tanh-sinh rows of
+//                     the pair staged in shared memory; strided sum with Euler-Maclaurin end corrections, exact replay of the stop
 //     finalize      : cos(chi) from I - I_lim, publish nodes as known
 // repeated until no mesh thread meets an unknown node (depth of the refinement tree + 1 passes). Only nodes the
 // reference's mesh touches are ever integrated.
