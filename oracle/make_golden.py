@@ -330,3 +330,103 @@ def zarate_golden(fname="zarate_reference.npz"):
 
 if __name__ == "__main__" and "zarate" in sys.argv[1:]:
     zarate_golden()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# configs[1] / configs[3] on every lattice regime (cpp/Spherical.cpp:60-84): Omega from the reference build at a
+# down-sampled headline grid, the regime edges, and cold Feynman-Hibbs temperatures.  ~2 core-hours: run with
+#   python -m oracle.make_golden regimes [nproc]
+# Results are appended to tests/golden/regimes_reference.jsonl as they finish (restartable), then packed into npz.
+# ---------------------------------------------------------------------------------------------------------------
+REGIME_LR = [(l, r) for l in range(1, 5) for r in range(l, 5)]
+REGIME_EDGES = [19.99, 20.0, 34.99, 35.0, 49.99, 50.0, 69.99, 70.0]
+REGIME_QM_T = [10.0, 11.7, 13.3, 15.0, 16.6, 18.2, 19.95, 30.0]
+REGIME_QM_LR = [(1, 1), (1, 2), (1, 3), (2, 2), (2, 3), (2, 4), (3, 3)]
+
+
+def config1_sample_indices(n=4096):
+    """48 indices of the configs[1] grid T = 30 geomspace(0.3, 100, n): 12 below 20 K (incl. the coldest point 9.0 K), 8 in 20-35 K,
+    6 in 35-50 K, 6 in 50-70 K, 16 above (incl. the hottest point)."""
+    T = 30.0 * np.geomspace(0.3, 100.0, n)
+    out = []
+    for lo, hi, k in ((0.0, 20.0, 12), (20.0, 35.0, 8), (35.0, 50.0, 6), (50.0, 70.0, 6), (70.0, 1e9, 16)):
+        idx = np.flatnonzero((T >= lo) & (T < hi))
+        out += [int(idx[int(round(q))]) for q in np.linspace(0, idx.size - 1, k)]
+    return out
+
+
+def _regime_worker(task):
+    import time
+    kind, comp, T, l, r = task
+    t0 = time.time()
+    if kind == "mie":
+        ids, Mw, s, e, la, lr = mie_parameters(comp)
+        m = ref.RefMie(Mw, s, e, la, lr, is_idealgas=True)
+        m.set_omega_correlation_active(False)
+    else:
+        from kineticgas_b200.fluids import MIE, MIE_FH
+        sig, epsk, la, lr = MIE_FH[(comp, 1)]
+        m = ref.RefQuantumMie([MIE[comp][0]], [sig], [epsk], [la], [lr], 1, is_idealgas=True)
+    val = m.omega(0, 0, l, r, T)
+    return {"kind": kind, "comp": comp, "T": T, "l": l, "r": r, "omega": val, "cpu_s": time.time() - t0}
+
+
+def regimes_golden(nproc=8, fname="regimes_reference.npz"):
+    import json
+    import multiprocessing as mp
+    Tgrid = 30.0 * np.geomspace(0.3, 100.0, 4096)
+    idx = config1_sample_indices()
+    tasks = [("mie", "LJF", float(Tgrid[i]), l, r) for i in idx for (l, r) in REGIME_LR]
+    tasks += [("mie", "LJF", T, l, r) for T in REGIME_EDGES for (l, r) in REGIME_LR]
+    tasks += [("qmie", c, T, l, r) for c in ("HE", "H2") for T in REGIME_QM_T for (l, r) in REGIME_QM_LR]
+    log = os.path.join(GOLD, "regimes_reference.jsonl")
+    done = {}
+    if os.path.exists(log):
+        for line in open(log):
+            d = json.loads(line)
+            done[(d["kind"], d["comp"], d["T"], d["l"], d["r"])] = d
+    todo = [t for t in tasks if t not in done]
+    todo.sort(key=lambda t: t[2])              # coldest (most expensive) first
+    print(len(tasks), "tasks,", len(todo), "to do", flush=True)
+    with mp.get_context("spawn").Pool(nproc) as pool, open(log, "a") as f:
+        for d in pool.imap_unordered(_regime_worker, todo, chunksize=1):
+            done[(d["kind"], d["comp"], d["T"], d["l"], d["r"])] = d
+            f.write(json.dumps(d) + "\n"); f.flush()
+    out = {"grid_index": np.array(idx), "grid_T": Tgrid[idx], "lr": np.array(REGIME_LR), "edges_T": np.array(REGIME_EDGES),
+           "qm_T": np.array(REGIME_QM_T), "qm_lr": np.array(REGIME_QM_LR)}
+    out["grid_omega"] = np.array([[done[("mie", "LJF", float(Tgrid[i]), l, r)]["omega"] for (l, r) in REGIME_LR] for i in idx])
+    out["edges_omega"] = np.array([[done[("mie", "LJF", T, l, r)]["omega"] for (l, r) in REGIME_LR] for T in REGIME_EDGES])
+    for c in ("HE", "H2"):
+        out[f"qm_{c}_omega"] = np.array([[done[("qmie", c, T, l, r)]["omega"] for (l, r) in REGIME_QM_LR] for T in REGIME_QM_T])
+    out["cpu_core_seconds"] = np.array(sum(d["cpu_s"] for d in done.values()))
+    np.savez(os.path.join(GOLD, fname), **out)
+    print("saved", fname, "core-s", out["cpu_core_seconds"], flush=True)
+
+
+if __name__ == "__main__" and "regimes" in sys.argv[1:]:
+    regimes_golden(int(sys.argv[2]) if len(sys.argv) > 2 else 8)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Goldens the REFERENCE ITSELF holds: tests/data/viscosity_MieKinGas.csv (1 050 rows, compared at 1e-8 by
+# tests/test_unchanged_output.py:51-94 through viscosity(T, 1/rho, x, N=2); rho = rho* / (N_A sigma_11^3),
+# pykingas get_reducing_units). The rows are repacked as arrays (the CSV cannot travel to the GPU box);
+# no EoS call is involved in the shear viscosity.
+# ---------------------------------------------------------------------------------------------------------------
+def refcsv_golden(fname="ref_viscosity_csv.npz"):
+    import ast
+    import csv
+    src = "/root/reference/tests/data/viscosity_MieKinGas.csv"
+    mix, T, rho, x, val = [], [], [], [], []
+    with open(src) as f:
+        for row in csv.DictReader(f):
+            xs = ast.literal_eval(row["x"])
+            mix.append(row["mix"]); T.append(float(row["T"])); rho.append(float(row["rho*"])); val.append(float(row["value"]))
+            x.append(list(xs) + [np.nan] * (3 - len(xs)))
+    np.savez(os.path.join(GOLD, fname), mix=np.array(mix), T=np.array(T), rho_star=np.array(rho), x=np.array(x), value=np.array(val),
+             source=np.array(src))
+    print("saved", fname, len(mix), "rows", sorted(set(mix)))
+
+
+if __name__ == "__main__" and "refcsv" in sys.argv[1:]:
+    refcsv_golden()
