@@ -396,6 +396,7 @@ __global__ void ljs_rdf_kernel(int n, int nslots, int nc, const int* __restrict_
     const long long e = (long long) blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= (long long) n * nslots) return;
     const int slot = (int) (e % nslots), sp = (int) (e / nslots), t = tidx[sp];
+    if (t < 0) return;                              // temperature not in the cache: state_kernel reports KG_STATUS_T_NOT_CACHED
     const double rho = (slot == 0) ? AVOGADRO / Vm[sp] : AVOGADRO / 1e12;
     const double g = ljs_rdf(rho, T_of[t], q.sigma, q.eps, dbh[(size_t) t * nc]);
     for (int k = 0; k < nc * nc; k++) rdf[((size_t) sp * nslots + slot) * nc * nc + k] = g;
@@ -515,6 +516,7 @@ __global__ void es_rdf_kernel(int n, int nslots, TModel tm, const int* __restric
     while (rest >= nc - i) { rest -= nc - i; i++; }
     const int j = i + rest;
     const int t = tidx[sp];
+    if (t < 0) return;                              // temperature not in the cache: state_kernel reports KG_STATUS_T_NOT_CACHED
     const double T = T_of[t];
     const double rho = (slot == 0) ? AVOGADRO / Vm[sp] : AVOGADRO / 1e12;
     const EsParams* P = prm + (size_t) t * nc * nc;
@@ -585,6 +587,7 @@ __global__ void rdf_kernel(int n, int nslots, TModel tm, const int* __restrict__
     double xs[MAXC];
     for (int k = 0; k < nc; k++) xs[k] = tm.is_singlecomp ? 0.5 : x[(size_t) sp * nc + k];
     const int t = tidx[sp];
+    if (t < 0) return;                              // temperature not in the cache: state_kernel reports KG_STATUS_T_NOT_CACHED
     const double rho = (slot == 0) ? AVOGADRO / Vm[sp] : AVOGADRO / 1e12;
     const double* d = dbh + (size_t) t * nc;
     RdfCommon c;
@@ -737,6 +740,13 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
         if (a.D) for (int k = 0; k < nD * nD; k++) a.D[(size_t) sp * nD * nD + k] = qnan;
         if (a.DT) for (int k = 0; k < nc; k++) a.DT[(size_t) sp * nc + k] = qnan;
         if (a.kT) for (int k = 0; k < nc; k++) a.kT[(size_t) sp * nc + k] = qnan;
+        if (a.soret) for (int k = 0; k < nc; k++) a.soret[(size_t) sp * nc + k] = qnan;
+        if (a.K) for (int k = 0; k < nc; k++) a.K[(size_t) sp * nc + k] = qnan;
+        if (a.Kp) for (int k = 0; k < nc; k++) a.Kp[(size_t) sp * nc + k] = qnan;
+        if (a.cond_matrix) for (int k = 0; k < n * n; k++) a.cond_matrix[(size_t) sp * n * n + k] = qnan;
+        if (a.cond_vector) for (int k = 0; k < n; k++) a.cond_vector[(size_t) sp * n + k] = qnan;
+        if (a.visc_matrix) for (int k = 0; k < n * n; k++) a.visc_matrix[(size_t) sp * n * n + k] = qnan;
+        if (a.visc_vector) for (int k = 0; k < n; k++) a.visc_vector[(size_t) sp * n + k] = qnan;
         if (a.status) a.status[sp] = KG_STATUS_T_NOT_CACHED;
         return;
     }

@@ -18,62 +18,87 @@ def available():
     return os.path.exists(os.path.join(_HERE, "_ref", "libkgref.so"))
 
 
+def _declare(L):
+    L.kgref_mie_create.restype = C.c_void_p
+    L.kgref_mie_create.argtypes = [C.c_int, dp, dp, dp, dp, dp, C.c_int, C.c_int]
+    L.kgref_last_error.restype = C.c_char_p
+    L.kgref_last_error.argtypes = [C.c_void_p]
+    for n in ("kgref_destroy", "kgref_clear_cache"):
+        getattr(L, n).argtypes = [C.c_void_p]
+    L.kgref_set_omega_correlation_active.argtypes = [C.c_void_p, C.c_int]
+    L.kgref_set_tl_model.argtypes = [C.c_void_p, C.c_int]
+    L.kgref_set_eos_tables_nc.argtypes = [C.c_void_p, C.c_int, dp, dp, C.c_double, C.c_double, dp]
+    for n in ("kgref_potential", "kgref_potential_r"):
+        getattr(L, n).restype = C.c_double
+        getattr(L, n).argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double]
+    for n in ("kgref_chi", "kgref_theta", "kgref_get_R"):
+        getattr(L, n).restype = C.c_double
+        getattr(L, n).argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double]
+    for n in ("kgref_chi_batch", "kgref_get_R_batch"):
+        getattr(L, n).argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_int, dp, dp, dp]
+    L.kgref_w_integrand.restype = C.c_double
+    L.kgref_w_integrand.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int, C.c_int]
+    for n in ("kgref_omega", "kgref_omega_model"):
+        getattr(L, n).argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, dp]
+    L.kgref_w_integral_tester.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int,
+                                          C.c_double, C.c_double, C.c_double, C.c_double, C.c_int, C.c_int, C.c_double, dp]
+    L.kgref_w_integral_trace.argtypes = L.kgref_w_integral_tester.argtypes + [dp, C.c_int, ip]
+    L.kgref_integrate2d_table.restype = C.c_double
+    L.kgref_integrate2d_table.argtypes = [dp, C.c_int, C.c_int] + [C.c_double] * 6 + [C.c_int, C.c_int, C.c_double, ip]
+    L.kgref_tanh_sinh_test.restype = C.c_double
+    L.kgref_tanh_sinh_test.argtypes = [C.c_int, C.c_double, C.c_double, C.c_double]
+    for n in ("kgref_mtl", "kgref_etl", "kgref_rdf"):
+        getattr(L, n).argtypes = [C.c_void_p, C.c_double, C.c_double, dp, dp]
+    L.kgref_bh_diameters.argtypes = [C.c_void_p, C.c_double, dp]
+    L.kgref_K_factors.argtypes = [C.c_void_p, C.c_double, C.c_double, dp, dp, dp]
+    L.kgref_matrix_vector.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, dp, C.c_int, dp, dp, ip]
+    for n in ("kgref_viscosity", "kgref_thermal_conductivity", "kgref_thermal_conductivity_contribs"):
+        getattr(L, n).argtypes = [C.c_void_p, C.c_double, C.c_double, dp, C.c_int, C.c_int, dp]
+    L.kgref_interdiffusion.argtypes = [C.c_void_p, C.c_double, C.c_double, dp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                       C.c_int, dp, ip, ip]
+    L.kgref_thermal_diffusion_coeff.argtypes = [C.c_void_p, C.c_double, C.c_double, dp, C.c_int, C.c_int, C.c_int, C.c_int,
+                                                C.c_int, dp, ip]
+    L.kgref_thermal_diffusion_ratio.argtypes = [C.c_void_p, C.c_double, C.c_double, dp, C.c_int, C.c_int, dp, ip]
+    L.kgref_soret_coefficient.argtypes = [C.c_void_p, C.c_double, C.c_double, dp, C.c_int, C.c_int, C.c_int, dp, ip]
+    L.kgref_qmie_create.restype = C.c_void_p
+    L.kgref_qmie_create.argtypes = [C.c_int, dp, dp, dp, dp, dp, C.c_int, C.c_int, C.c_int]
+    L.kgref_set_internals.argtypes = [C.c_void_p, C.c_double, C.c_double]
+    L.kgref_c_eff.argtypes = [C.c_void_p, C.c_int, C.c_int, dp, ip]
+    L.kgref_generic_create.restype = C.c_void_p
+    L.kgref_generic_create.argtypes = [C.c_int, C.c_char_p, C.c_int, C.c_char_p, C.c_int]
+    L.kgref_generic_scales.argtypes = [C.c_void_p, dp]
+    L.kgref_potential_rr.restype = C.c_double
+    L.kgref_potential_rr.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double]
+    return L
+
+
 def lib():
     global _LIB
     if _LIB is None:
-        L = C.CDLL(os.path.join(_HERE, "_ref", "libkgref.so"))
-        L.kgref_mie_create.restype = C.c_void_p
-        L.kgref_mie_create.argtypes = [C.c_int, dp, dp, dp, dp, dp, C.c_int, C.c_int]
-        L.kgref_last_error.restype = C.c_char_p
-        L.kgref_last_error.argtypes = [C.c_void_p]
-        for n in ("kgref_destroy", "kgref_clear_cache"):
-            getattr(L, n).argtypes = [C.c_void_p]
-        L.kgref_set_omega_correlation_active.argtypes = [C.c_void_p, C.c_int]
-        L.kgref_set_tl_model.argtypes = [C.c_void_p, C.c_int]
-        L.kgref_set_eos_tables_nc.argtypes = [C.c_void_p, C.c_int, dp, dp, C.c_double, C.c_double, dp]
-        for n in ("kgref_potential", "kgref_potential_r"):
-            getattr(L, n).restype = C.c_double
-            getattr(L, n).argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double]
-        for n in ("kgref_chi", "kgref_theta", "kgref_get_R"):
-            getattr(L, n).restype = C.c_double
-            getattr(L, n).argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double]
-        for n in ("kgref_chi_batch", "kgref_get_R_batch"):
-            getattr(L, n).argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_int, dp, dp, dp]
-        L.kgref_w_integrand.restype = C.c_double
-        L.kgref_w_integrand.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int, C.c_int]
-        for n in ("kgref_omega", "kgref_omega_model"):
-            getattr(L, n).argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, dp]
-        L.kgref_w_integral_tester.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int,
-                                              C.c_double, C.c_double, C.c_double, C.c_double, C.c_int, C.c_int, C.c_double, dp]
-        L.kgref_w_integral_trace.argtypes = L.kgref_w_integral_tester.argtypes + [dp, C.c_int, ip]
-        L.kgref_integrate2d_table.restype = C.c_double
-        L.kgref_integrate2d_table.argtypes = [dp, C.c_int, C.c_int] + [C.c_double] * 6 + [C.c_int, C.c_int, C.c_double, ip]
-        L.kgref_tanh_sinh_test.restype = C.c_double
-        L.kgref_tanh_sinh_test.argtypes = [C.c_int, C.c_double, C.c_double, C.c_double]
-        for n in ("kgref_mtl", "kgref_etl", "kgref_rdf"):
-            getattr(L, n).argtypes = [C.c_void_p, C.c_double, C.c_double, dp, dp]
-        L.kgref_bh_diameters.argtypes = [C.c_void_p, C.c_double, dp]
-        L.kgref_K_factors.argtypes = [C.c_void_p, C.c_double, C.c_double, dp, dp, dp]
-        L.kgref_matrix_vector.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, dp, C.c_int, dp, dp, ip]
-        for n in ("kgref_viscosity", "kgref_thermal_conductivity", "kgref_thermal_conductivity_contribs"):
-            getattr(L, n).argtypes = [C.c_void_p, C.c_double, C.c_double, dp, C.c_int, C.c_int, dp]
-        L.kgref_interdiffusion.argtypes = [C.c_void_p, C.c_double, C.c_double, dp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
-                                           C.c_int, dp, ip, ip]
-        L.kgref_thermal_diffusion_coeff.argtypes = [C.c_void_p, C.c_double, C.c_double, dp, C.c_int, C.c_int, C.c_int, C.c_int,
-                                                    C.c_int, dp, ip]
-        L.kgref_thermal_diffusion_ratio.argtypes = [C.c_void_p, C.c_double, C.c_double, dp, C.c_int, C.c_int, dp, ip]
-        L.kgref_soret_coefficient.argtypes = [C.c_void_p, C.c_double, C.c_double, dp, C.c_int, C.c_int, C.c_int, dp, ip]
-        L.kgref_qmie_create.restype = C.c_void_p
-        L.kgref_qmie_create.argtypes = [C.c_int, dp, dp, dp, dp, dp, C.c_int, C.c_int, C.c_int]
-        L.kgref_set_internals.argtypes = [C.c_void_p, C.c_double, C.c_double]
-        L.kgref_c_eff.argtypes = [C.c_void_p, C.c_int, C.c_int, dp, ip]
-        L.kgref_generic_create.restype = C.c_void_p
-        L.kgref_generic_create.argtypes = [C.c_int, C.c_char_p, C.c_int, C.c_char_p, C.c_int]
-        L.kgref_generic_scales.argtypes = [C.c_void_p, dp]
-        L.kgref_potential_rr.restype = C.c_double
-        L.kgref_potential_rr.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double]
-        _LIB = L
+        _LIB = _declare(C.CDLL(os.path.join(_HERE, "_ref", "libkgref.so")))
     return _LIB
+
+
+# ---- integration/_build/libkgshim.so: the same unmodified reference objects + GpuMieKinGas (integration/gpu_miekingas.cpp),
+# i.e. the reference with its precompute_* / transfer-length entry routed to libkgcuda.so. Holds BOTH arms of the drop-in test.
+_SHIM = None
+SHIM_PATH = os.path.join(os.path.dirname(_HERE), "integration", "_build", "libkgshim.so")
+
+
+def shim_available():
+    return os.path.exists(SHIM_PATH)
+
+
+def shim_lib():
+    global _SHIM
+    if _SHIM is None:
+        L = _declare(C.CDLL(SHIM_PATH))
+        L.kgshim_mie_create.restype = C.c_void_p
+        L.kgshim_mie_create.argtypes = [C.c_int, dp, dp, dp, dp, dp, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int]
+        L.kgshim_counters.argtypes = [C.c_void_p, C.POINTER(C.c_long), C.c_int]
+        L.kgshim_omega_table.argtypes = [C.c_void_p, C.c_int, dp, C.c_int, ip, ip, dp]
+        _SHIM = L
+    return _SHIM
 
 
 def _p(a):
@@ -122,9 +147,16 @@ class RefMie:
         self.lr = 3 + np.sqrt((lr_[:, None] - 3) * (lr_[None, :] - 3))
         for a in ("sigma", "eps", "la", "lr"):
             setattr(self, a, np.ascontiguousarray(getattr(self, a)))
-        self.L = lib()
-        self.h = self.L.kgref_mie_create(self.nc, _p(self.m), _p(self.sigma), _p(self.eps), _p(self.la), _p(self.lr),
-                                         int(is_idealgas), int(single))
+        self.L = getattr(self, "_lib_override", None) or lib()
+        if getattr(self, "_gpu", False):
+            err = C.create_string_buffer(512)
+            self.h = self.L.kgshim_mie_create(self.nc, _p(self.m), _p(self.sigma), _p(self.eps), _p(self.la), _p(self.lr),
+                                              int(is_idealgas), int(single), int(self._device), err, 512)
+            if not self.h:
+                raise RuntimeError(err.value.decode())
+        else:
+            self.h = self.L.kgref_mie_create(self.nc, _p(self.m), _p(self.sigma), _p(self.eps), _p(self.la), _p(self.lr),
+                                             int(is_idealgas), int(single))
 
     def __del__(self):
         try:
@@ -353,3 +385,35 @@ class RefGeneric(RefMie):
     def w_integral(self, i, j, T, l, r, regime=None):
         self.set_internals(T)
         return super().w_integral(i, j, T, l, r, regime)
+
+
+class ShimStockMie(RefMie):
+    """The stock MieKinGas of libkgshim.so (same objects as oracle/_ref, second arm of the drop-in comparison)."""
+
+    def __init__(self, Mw, sigma, eps_div_k, la, lr, is_idealgas=False):
+        self._lib_override = shim_lib()
+        super().__init__(Mw, sigma, eps_div_k, la, lr, is_idealgas)
+
+
+class ShimGpuMie(RefMie):
+    """GpuMieKinGas (integration/gpu_miekingas.cpp): the reference's own property code, Omega / transfer lengths fed from the device."""
+
+    def __init__(self, Mw, sigma, eps_div_k, la, lr, is_idealgas=False, device=0):
+        self._lib_override = shim_lib()
+        self._gpu, self._device = True, device
+        super().__init__(Mw, sigma, eps_div_k, la, lr, is_idealgas)
+
+    def counters(self, reset=False):
+        out = (C.c_long * 3)()
+        if self.L.kgshim_counters(self.h, out, int(reset)) != 0:
+            raise RuntimeError("not a GpuMieKinGas handle")
+        return {"cpu_theta_integrand_calls": out[0], "device_feeds": out[1], "omega_values_stored": out[2]}
+
+    def omega_table(self, T, l, r):
+        T = np.ascontiguousarray(np.atleast_1d(T), float)
+        l = np.ascontiguousarray(l, np.int32)
+        r = np.ascontiguousarray(r, np.int32)
+        npairs = 1 if self.single else self.nc * (self.nc + 1) // 2
+        out = np.empty((T.size, npairs, l.size))
+        self._chk(self.L.kgshim_omega_table(self.h, T.size, _p(T), l.size, l.ctypes.data_as(ip), r.ctypes.data_as(ip), _p(out)))
+        return out

@@ -16,6 +16,9 @@
 #include <cstring>
 #include <set>
 #include <mutex>
+#ifdef KG_WITH_GPU_SHIM
+#include "gpu_miekingas.h"      // integration/gpu_miekingas.h: the reference-side shim over libkgcuda.so (integration/Makefile)
+#endif
 
 namespace {
 
@@ -154,7 +157,7 @@ int kgref_c_eff(void* hv, int i, int j, double* out, int* nterms) {
 }
 void kgref_destroy(void* hv) { delete static_cast<Handle*>(hv); }
 const char* kgref_last_error(void* hv) { return static_cast<Handle*>(hv)->err.c_str(); }
-void kgref_clear_cache(void* hv) { Handle* h = static_cast<Handle*>(hv); if (h->mie) static_cast<MieAccess*>(h->mie)->clear_cache(); else if (h->clear) h->clear(); }
+void kgref_clear_cache(void* hv) { Handle* h = static_cast<Handle*>(hv); if (h->clear) h->clear(); else if (h->mie) static_cast<MieAccess*>(h->mie)->clear_cache(); }
 void kgref_set_omega_correlation_active(void* hv, int active) { Handle* h = static_cast<Handle*>(hv); if (h->mie) h->mie->set_omega_correlation_active(active != 0); }
 void kgref_set_tl_model(void* hv, int id) { static_cast<Handle*>(hv)->kin->set_transfer_length_model(id); }
 
@@ -345,3 +348,41 @@ int kgref_soret_coefficient(void* hv, double T, double Vm, const double* x, int 
 }
 
 } // extern "C"
+
+#ifdef KG_WITH_GPU_SHIM
+// integration/_build/libkgshim.so only: the same driver over a GpuMieKinGas (the reference's MieKinGas with precompute_* and the
+// transfer-length entry routed to the device). Every kgref_* property call works on the returned handle unchanged.
+extern "C" {
+void* kgshim_mie_create(int nc, const double* m, const double* sigma, const double* eps, const double* la, const double* lr,
+                        int is_idealgas, int is_singlecomp, int device, char* errbuf, int errcap) {
+    try {
+        Handle* h = new Handle;
+        h->nc = nc;
+        GpuMieKinGas* mk = new GpuMieKinGas(vector1d(m, m + nc), to2d(sigma, nc), to2d(eps, nc), to2d(la, nc), to2d(lr, nc),
+                                            is_idealgas != 0, is_singlecomp != 0, device);
+        h->kin.reset(mk);
+        h->mie = mk;
+        h->clear = [mk]() { mk->clear_cache(); };
+        return h;
+    } catch (const std::exception& e) { if (errbuf) { strncpy(errbuf, e.what(), errcap - 1); errbuf[errcap - 1] = 0; } return nullptr; }
+}
+// out[0] CPU theta-integrand evaluations, out[1] device feeds, out[2] Omega values stored into the reference cache
+int kgshim_counters(void* hv, long* out3, int reset) {
+    Handle* h = static_cast<Handle*>(hv);
+    GpuMieKinGas* g = dynamic_cast<GpuMieKinGas*>(h->kin.get());
+    if (!g) return -1;
+    out3[0] = g->cpu_theta_integrand_calls(); out3[1] = g->device_feeds(); out3[2] = g->omega_values_stored();
+    if (reset) g->reset_counters();
+    return 0;
+}
+int kgshim_omega_table(void* hv, int nT, const double* T, int nlr, const int* l, const int* r, double* out) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{
+        GpuMieKinGas* g = dynamic_cast<GpuMieKinGas*>(h->kin.get());
+        if (!g) throw std::runtime_error("not a GpuMieKinGas");
+        const std::vector<double> om = g->omega_table(std::vector<double>(T, T + nT), std::vector<int>(l, l + nlr), std::vector<int>(r, r + nlr));
+        std::copy(om.begin(), om.end(), out);
+    });
+}
+}
+#endif

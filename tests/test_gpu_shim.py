@@ -1,0 +1,110 @@
+"""The drop-in claim, exercised: the reference's OWN property code (unmodified objects of cpp/*.cpp) with its collision integrals
+and transfer lengths fed from the device through `GpuMieKinGas` (integration/gpu_miekingas.cpp), against the stock reference.
+
+integration/_build/libkgshim.so holds both arms: `kgref_mie_create` builds the stock `MieKinGas`, `kgshim_mie_create` a
+`GpuMieKinGas : MieKinGas` that overrides precompute_conductivity / precompute_viscosity / precompute_omega
+(cpp/KineticGas.h:277-280) and model_mtl / model_etl (cpp/transfer_lengths.cpp:24-36) and stores the device results with
+cache.omega.store(get_omega_point(...)) (cpp/KineticGasCache.h:25-28). Checked here:
+
+  * viscosity, thermal_conductivity (t, d, i), interdiffusion, thermal_diffusion_coeff of the shim == stock to 1e-6 (north_star
+    tolerance) for AR, CO2/C1/N2 and C1/NC10 at N = 3;
+  * after the feed NO CPU quadrature runs: the counter on Spherical::theta_integrand (every chi, w_integral and EWCA integral goes
+    through it) stays 0 in the shim while the stock object makes millions of calls;
+  * two temperatures inside one 0.1 K cache bucket behave as in the stock build (first temperature's Omega wins);
+  * the additive `omega_table` entry point feeds the cache as well.
+"""
+import numpy as np
+import pytest
+
+from kineticgas_b200.fluids import mie_parameters
+from oracle import ref
+
+pytestmark = [pytest.mark.gpu, pytest.mark.skipif(not ref.shim_available(), reason="integration/_build/libkgshim.so not built")]
+
+R_GAS = 8.31446261815324
+TOL = 1e-6
+
+
+def synthetic_eos(T, Vm, x, Mw, B0=-1.0e-4):
+    """Same table as oracle/make_golden.py synthetic_eos (ideal mixture + symmetric second-virial-like term)."""
+    x = np.asarray(x, float)
+    nc = x.size
+    B = B0 * (1.0 + 0.1 * (np.arange(nc)[:, None] + np.arange(nc)[None, :]))
+    dmudn = R_GAS * T * (np.diag(1.0 / x) + 2.0 * B / Vm)
+    cp_id = R_GAS * (2.5 + 0.35 * np.arange(1, nc + 1) + 1e-3 * (T - 300.0) * np.sqrt(np.asarray(Mw) / 16.0))
+    dvdn = Vm * (1.0 + 0.05 * (np.arange(nc) - (nc - 1) / 2.0))
+    return dmudn, cp_id, dvdn
+
+
+CASES = [("AR", 2, [(300.0, 0.05, [1.0]), (150.0, 0.3, [1.0])]),
+         ("CO2,C1,N2", 2, [(312.5, 0.3, [0.2, 0.3, 0.5])]),
+         ("C1,NC10", 3, [(400.0, 0.1, [0.3, 0.7]), (650.0, 0.45, [0.9, 0.1])])]
+
+
+def _both(comps, ideal=False):
+    ids, Mw, s, e, la, lr = mie_parameters(comps)
+    return ref.ShimStockMie(Mw, s, e, la, lr, ideal), ref.ShimGpuMie(Mw, s, e, la, lr, ideal), Mw, s
+
+
+def _props(m, T, Vm, x, N, Mw):
+    xi = [0.5, 0.5] if m.single else x
+    dmudn, cp_id, dvdn = synthetic_eos(T, Vm, x, Mw)
+    m.set_eos(dmudn=dmudn, cp_id=cp_id, p=1e5, vm=Vm, dvdn=dvdn)
+    return {"viscosity": np.array(m.viscosity(T, Vm, xi, N)), "conductivity": m.thermal_conductivity_contribs(T, Vm, xi, N),
+            "D": m.interdiffusion(T, Vm, xi, N, frame=1), "DT": m.thermal_diffusion_coeff(T, Vm, xi, N, frame=1)}
+
+
+@pytest.mark.parametrize("comps,N,points", CASES, ids=[c[0] for c in CASES])
+def test_reference_properties_through_the_shim_equal_stock(comps, N, points):
+    stock, gpu, Mw, s = _both(comps)
+    for (T, rho_star, x) in points:
+        Vm = ref.AVOGADRO * s[0] ** 3 / rho_star
+        a, b = _props(stock, T, Vm, x, N, Mw), _props(gpu, T, Vm, x, N, Mw)
+        for k in a:
+            err = np.max(np.abs(b[k] - a[k]) / np.maximum(np.abs(a[k]), 1e-300))
+            print(comps, T, rho_star, k, "max rel err", float(err))
+            assert err < TOL, (comps, T, k, a[k], b[k])
+    c = gpu.counters()
+    print(comps, c)
+    assert c["cpu_theta_integrand_calls"] == 0          # no CPU chi / w_integral / EWCA quadrature ran behind the shim
+    assert c["device_feeds"] > 0
+
+
+def test_stock_arm_does_run_cpu_quadrature():
+    """Sanity of the counter: the same hook on a GpuMieKinGas whose cache is bypassed (chi evaluated directly) counts calls."""
+    stock, gpu, Mw, s = _both("AR")
+    gpu.counters(reset=True)
+    gpu.chi(0, 0, 300.0, [1.0], [1.0 * s[0]])            # Spherical::chi on the host: ~4000 theta_integrand evaluations
+    assert gpu.counters()["cpu_theta_integrand_calls"] > 1000
+
+
+def test_cache_bucket_semantics_match_stock():
+    """T = 299.96 K and 300.04 K share the OmegaPoint key (int)(10 T + 0.5) = 3000 (cpp/KineticGasCache.h:95-97): the second call
+    reuses the first temperature's collision integrals in the stock build, and so does the shim (store only where absent).
+    An exact Omega(300.04 K) differs from the bucket value by ~1e-5 relative -- well above the tolerance."""
+    stock, gpu, Mw, s = _both("CO2", ideal=True)
+    Vm = 0.02
+    out = {}
+    for name, m in (("stock", stock), ("gpu", gpu)):
+        m.set_eos(dmudn=np.array([[R_GAS * 300.0]]), cp_id=np.array([3.5 * R_GAS]), p=1e5, vm=Vm, dvdn=np.array([Vm]))
+        out[name] = (m.viscosity(299.96, Vm, [0.5, 0.5], 2), m.viscosity(300.04, Vm, [0.5, 0.5], 2))
+    assert abs(out["gpu"][0] / out["stock"][0] - 1) < TOL
+    assert abs(out["gpu"][1] / out["stock"][1] - 1) < TOL
+    # and a fresh object asked at 300.04 K first integrates at 300.04 K: differs from the bucket value
+    fresh = _both("CO2", ideal=True)[1]
+    eta_exact = fresh.viscosity(300.04, Vm, [0.5, 0.5], 2)
+    assert abs(eta_exact / out["gpu"][1] - 1) > 1e-6
+    assert gpu.counters()["cpu_theta_integrand_calls"] == 0
+
+
+def test_omega_table_feeds_the_reference_cache():
+    stock, gpu, Mw, s = _both("CO2", ideal=True)
+    l, r = [1, 1, 2], [1, 2, 2]
+    tab = gpu.omega_table([250.0, 400.0], l, r)
+    c0 = gpu.counters()
+    assert c0["omega_values_stored"] == 6
+    for t, T in enumerate((250.0, 400.0)):
+        for k in range(3):
+            assert gpu.omega(0, 0, l[k], r[k], T) == tab[t, 0, k]                 # cache hit: the stored device value, bit for bit
+            assert abs(tab[t, 0, k] / stock.omega(0, 0, l[k], r[k], T) - 1) < TOL
+    assert gpu.counters()["cpu_theta_integrand_calls"] == 0
