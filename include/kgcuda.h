@@ -75,6 +75,9 @@ int kg_model_create_ex(const kg_potential_desc_ex* pairs, int ncomps, const doub
 int kg_genpot_describe(const kg_potential_desc_ex* d, double T, double* out, int cap_doubles);
 void kg_model_destroy(kg_model* m);
 const char* kg_last_error(const kg_model* m);   /* m may be NULL: error of the last failed create */
+/* "libkgcuda sm_100a src-sha256:<16 hex>": hash of kineticgas_b200/csrc/* + include/kgcuda.h the binary was built from
+ * (__graft_entry__.source_sha() recomputes it from the tree; bench.py prints both so a stale binary is visible). */
+const char* kg_build_info(void);
 int kg_model_npairs(const kg_model* m);
 /* Run all work of this model on a caller-owned CUDA stream (cudaStream_t passed as void*), e.g. the host framework's
  * current stream, so that the caller's events bracket the kernels. */
@@ -126,10 +129,12 @@ void kg_omega_plan_destroy(kg_omega_plan* p);
  *  out[9] H2D bytes of plan creation      out[10] D2H bytes of the last fetch     out[11] bytes of lattice + mask pools in HBM
  *  out[12] largest cell list of one refinement level   out[13] cell-list capacity   out[14] its hard bound   out[15] times it was grown */
 int kg_omega_plan_counters(kg_omega_plan* p, double* out16);
-/* Quadrature accounting of the last run: out[0] tanh-sinh nodes of the reference's sums (the algorithmic count of SURVEY 8d),
- * out[1] node evaluations executed (the strided Euler-Maclaurin sum touches ~1/7 of them), out[2] theta integrals that were
- * rejected by the stride-8 / stride-16 consistency check and summed node by node, out[3] theta integrals in total. */
-int kg_omega_plan_quadrature_stats(kg_omega_plan* p, double* out4);
+/* Quadrature accounting of the last run (8 doubles): out[0] tanh-sinh nodes of the reference's sums (the algorithmic count of
+ * SURVEY 8d), out[1] node evaluations executed (the strided Euler-Maclaurin sums touch ~1/12 of them; rejected attempts are
+ * counted), out[2] theta integrals that both strided tiers rejected and that were summed node by node, out[3] theta integrals in
+ * total, out[4] theta integrals whose stride-16 sum was rejected (second tier, stride 8), out[5] mesh cells processed over all
+ * refinement levels, out[6..7] reserved (0). */
+int kg_omega_plan_quadrature_stats(kg_omega_plan* p, double* out8);
 /* Validation switch, process wide: 1 = every theta integral is summed node by node exactly like tanh_sinh
  * (cpp/Integration/Integration.cpp:417-437); 0 (default) = strided sum with end corrections (same result to ~4e-13, same
  * stop index). The environment variable KG_TS_EXACT=1 selects the exact mode at model creation. */

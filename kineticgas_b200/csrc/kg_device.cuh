@@ -347,17 +347,13 @@ __device__ __noinline__ bool ts_exact4(const double* __restrict__ r0, const doub
 // cpp/Spherical.cpp:321-329 + cpp/Integration/Integration.cpp:417-437, on tabulated nodes.
 // srows: first KS rows in shared memory; grows: all KMAX rows in global memory. Row j holds node k = j + 1.
 // A[t] = eps C_t (sigma/R)^lam_t / (kT g^2), c2 = (R/b)^2. nodes += k at exit.
-// The bulk of the sum runs in blocks of KG_TS_BLOCK fast nodes with one conservative high-word stop check per block;
-// a block that may contain the stop (or anything irregular) is replayed exactly, four nodes at a time.
+// The reference's loop continued from node k (running sum I): blocks of KG_TS_BLOCK fast nodes with one conservative
+// high-word stop check per block; a block that may contain the stop (or anything irregular) is replayed exactly, four nodes at
+// a time. On return k = index of the last node examined.
 template<int NT>
-__device__ __noinline__ double theta_integral(const double* __restrict__ srows, const double* __restrict__ grows, int KS,
-                                 const double (&A)[NT], double c2, unsigned& nodes, int& status) {
+__device__ __forceinline__ void ts_tail(const double* __restrict__ srows, const double* __restrict__ grows, int KS,
+                                        const double (&Ap)[NT], double c2, double& I, int& k, int& status) {
     constexpr int W = 2 + NT;
-    double Ap[NT];
-#pragma unroll
-    for (int t = 0; t < NT; t++) Ap[t] = c2 * A[t];
-    double I = ts_term<NT>(srows, Ap, c2);              // k = 1 is added unconditionally (Integration.cpp:425)
-    int k = 1;
     for (;;) {
 #ifndef KG_TS_NOFAST
         while (k + KG_TS_BLOCK <= KS) {
@@ -380,6 +376,17 @@ __device__ __noinline__ double theta_integral(const double* __restrict__ srows, 
         const double* r = (k + 4 <= KS) ? srows + (size_t) k * W : grows + (size_t) k * W;
         if (ts_exact4<NT>(r, Ap, c2, I, k)) break;
     }
+}
+
+template<int NT>
+__device__ __noinline__ double theta_integral(const double* __restrict__ srows, const double* __restrict__ grows, int KS,
+                                 const double (&A)[NT], double c2, unsigned& nodes, int& status) {
+    double Ap[NT];
+#pragma unroll
+    for (int t = 0; t < NT; t++) Ap[t] = c2 * A[t];
+    double I = ts_term<NT>(srows, Ap, c2);              // k = 1 is added unconditionally (Integration.cpp:425)
+    int k = 1;
+    ts_tail<NT>(srows, grows, KS, Ap, c2, I, k, status);
     nodes += (unsigned) k;
     return I;
 }
@@ -390,14 +397,17 @@ __device__ __noinline__ double theta_integral(const double* __restrict__ srows, 
 // 1 % per node (node 1 carries the first-weight quirk and is added on its own). The Euler-Maclaurin formula relates the
 // unit-stride sum to the stride-s trapezoid sum of the same samples,
 //   sum_{k=a}^{b} g(k) = T_s + (g_a + g_b)/2 + (1-s^2)/12 D1 - (1-s^4)/720 D3 + (1-s^6)/30240 D5 + ...,  Dn = g^(n)(b) - g^(n)(a),
-// with the end derivatives taken from 7-point forward differences of fine nodes. So: march with stride 8 in blocks of four
+// with the end derivatives taken from 7-point forward differences of fine nodes. So: march with stride S in blocks of four
 // coarse nodes until a block may contain the reference's stop (terms fall below 1.02 tol x running sum), close the coarse
-// range at an even coarse node b, then replay the reference's loop node by node from b + 1 to find the stop index exactly.
-// Every other coarse node gives the stride-16 sum for free; the two end-corrected integrals must agree to 1e-10, otherwise
+// range at an even coarse node b, then continue the reference's loop from b + 1 (ts_tail) to find the stop index exactly.
+// Every other coarse node gives the stride-2S sum for free; the two end-corrected integrals must agree to `accept`, otherwise
 // (near-orbiting trajectories whose integrand has structure on the scale of a few nodes, a non-positive radicand, the
-// early stop of the g = 1e-7 column, ...) the lane reports `redo` and the entry is summed node by node instead.
-// Measured on the LJ 12-6 lattices of all five regimes: |I_em / I_exact - 1| < 4e-13, identical stop index, 1-5 % redo,
-// ~0.14 node evaluations per reference node.
+// early stop of the g = 1e-7 column, ...) the lane reports `redo` and the entry goes to the next tier.
+//   S = 16, accept 1e-9 (first tier):  error of the accepted sums < 2e-11 relative (the stride-32 estimate is ~250x worse than
+//                                      the stride-16 one, so the difference over-estimates the error by that factor), ~96 % accepted
+//   S = 8,  accept 1e-10 (second tier): error < 5e-13, ~99 % accepted
+// (measured against the node-by-node sums on random LJ 12-6 trajectories, tools/em_stride_probe.py; whole-lattice W and the
+// reference node totals in tests/test_gpu_chi_omega.py). Third tier: node by node.
 // ------------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void fd7(const double (&f)[7], double& d1, double& d3, double& d5) {
     d1 = -2.45 * f[0] + 6. * f[1] - 7.5 * f[2] + (20. / 3.) * f[3] - 3.75 * f[4] + 1.2 * f[5] - (1. / 6.) * f[6];
@@ -405,12 +415,13 @@ __device__ __forceinline__ void fd7(const double (&f)[7], double& d1, double& d3
     d5 = -3.5 * f[0] + 20. * f[1] - 47.5 * f[2] + 60. * f[3] - 42.5 * f[4] + 16. * f[5] - 2.5 * f[6];
 }
 
-template<int NT>
+template<int NT, int S>
 __device__ double theta_integral_em(const double* __restrict__ srows, const double* __restrict__ grows, int KS,
                                     const double (&A)[NT], double c2, unsigned& nodes, unsigned& exec_nodes, int& status, bool& redo,
                                     bool& redo_early) {
     constexpr int W = 2 + NT;
-    constexpr int S = 8;
+    constexpr double ACCEPT = (S >= 16) ? 1e-9 : 1e-10;
+    constexpr double S2 = (double) S * S, S4 = S2 * S2, S6 = S4 * S2;
     redo_early = false;
     double Ap[NT];
 #pragma unroll
@@ -439,7 +450,7 @@ __device__ double theta_integral_em(const double* __restrict__ srows, const doub
     const double* __restrict__ rp = srows + (size_t) (1 + S) * W;      // row of coarse node j0 = 1 (node 2 + S)
     for (;;) {
         const int kb = 2 + S * j0;
-        if (kb + 3 * S + 8 > KMAX) return 0.0;
+        if (kb + 3 * S + 8 > KMAX) { exec_nodes += (unsigned) (j0 + 8); return 0.0; }
         double z0, c0, z1, c1, z2, c2_, z3, c3;
         if (j0 <= j_smem) {
             ts_fast<NT>(rp, Ap, c2, z0, c0);
@@ -459,7 +470,7 @@ __device__ double theta_integral_em(const double* __restrict__ srows, const doub
         Sn = fma(z2, c2_, Sn);
         Sn = fma(z3, c3, Sn);
         const double In = fma((double) S, Sn, base);
-        if (!(In < 1e300)) return 0.0;                        // NaN (radicand <= 0 somewhere) or overflow
+        if (!(In < 1e300)) { exec_nodes += (unsigned) (j0 + 11); return 0.0; }      // NaN (radicand <= 0 somewhere) or overflow
         // every term of the block against 1.02 tol x the sum after the block, on the high words (z = g / 2 to 2^-20)
         const int lim = __double2hiint((0.5 * 1.02 * TS_TOL) * In);
         const int zmin = min(min(__double2hiint(z0), __double2hiint(z1)), min(__double2hiint(z2), __double2hiint(z3)));
@@ -475,7 +486,7 @@ __device__ double theta_integral_em(const double* __restrict__ srows, const doub
         break;
     }
     const double E = ga + Eg, O = Sg - Eg;
-    if (bj < 8) { redo_early = true; return 0.0; }      // the sum ends within the first ~70 nodes (g = 1e-7 column): cheap node by node
+    if (bj * S < 64) { redo_early = true; exec_nodes += (unsigned) (j0 + 11); return 0.0; }      // the sum ends within the first ~70 nodes (g = 1e-7 column): cheap node by node
     const int b = 2 + S * bj;
     f[0] = gb;
 #pragma unroll 1
@@ -485,16 +496,12 @@ __device__ double theta_integral_em(const double* __restrict__ srows, const doub
     D1 -= d1a; D3 -= d3a; D5 -= d5a;
     const double ends = 0.5 * (ga + gb);
     // T_s - integral = s^2/12 D1 - s^4/720 D3 + s^6/30240 D5
-    const double i8 = S * (E + O - ends) - ((64. / 12.) * D1 - (4096. / 720.) * D3 + (262144. / 30240.) * D5);
-    const double i16 = 2 * S * (E - ends) - ((256. / 12.) * D1 - (65536. / 720.) * D3 + (16777216. / 30240.) * D5);
-    if (!(fabs(i8 - i16) <= 1e-10 * fabs(i8))) return 0.0;
-    double I = t1 + (i8 + ends + ((1. / 12.) * D1 - (1. / 720.) * D3 + (1. / 30240.) * D5));
+    const double is = S * (E + O - ends) - ((S2 / 12.) * D1 - (S4 / 720.) * D3 + (S6 / 30240.) * D5);
+    const double i2s = 2 * S * (E - ends) - ((4. * S2 / 12.) * D1 - (16. * S4 / 720.) * D3 + (64. * S6 / 30240.) * D5);
+    if (!(fabs(is - i2s) <= ACCEPT * fabs(is))) { exec_nodes += (unsigned) (bj + 17); return 0.0; }
+    double I = t1 + (is + ends + ((1. / 12.) * D1 - (1. / 720.) * D3 + (1. / 30240.) * D5));
     int k = b;
-    for (;;) {                                                // the reference's loop from node b + 1 (ts_exact4)
-        if (k + 4 > KMAX) { status |= 2; break; }
-        const double* r = (k + 4 <= KS) ? srows + (size_t) k * W : grows + (size_t) k * W;
-        if (ts_exact4<NT>(r, Ap, c2, I, k)) break;
-    }
+    ts_tail<NT>(srows, grows, KS, Ap, c2, I, k, status);      // the reference's loop from node b + 1
     redo = false;
     nodes += (unsigned) k;
     exec_nodes += (unsigned) (bj + 13 + (k - b) + 4);
@@ -611,40 +618,21 @@ __device__ double lane_theta_integral(const PairParams& pp, const double* coeff,
     const double q = R / b;
     if (!c_ts_exact) {
         bool redo, early; unsigned ex = 0;
-        const double I = theta_integral_em<NT>(srows, grows, KS, A, q * q, nodes, ex, status, redo, early);
+        double I = theta_integral_em<NT, 16>(srows, grows, KS, A, q * q, nodes, ex, status, redo, early);
         if (!redo) return I;
+        if (!early) {
+            I = theta_integral_em<NT, 8>(srows, grows, KS, A, q * q, nodes, ex, status, redo, early);
+            if (!redo) return I;
+        }
     }
     return theta_integral<NT>(srows, grows, KS, A, q * q, nodes, status);
 }
 
-// Same, for the batched Omega kernel: a lane whose strided sum is rejected does not fall back inline (one such lane would
-// hold its warp for a full node-by-node sum); it returns redo = true and the entry goes to the redo list.
+// For the batched Omega kernel of the generic potentials (declaration; the power-law kernels use lane_setup + lane_sum_defer)
 template<int NT>
 __device__ double lane_theta_integral_defer(const PairParams& pp, const double* coeff, const double* __restrict__ srows,
                                             const double* __restrict__ grows, int KS, double T, double g, double b,
-                                            unsigned& nodes, unsigned& exec_nodes, int& status, bool& redo, double (&Ap_out)[NT], double& c2_out) {
-    Lane<NT> c;
-    make_lane<NT>(c, pp, coeff, T, g, b);
-    int st = 0;
-    const double R = get_R<NT>(c, g, st);
-    double A[NT];
-    lane_powers<NT>(c, 1.0 / R, A);                                        // Bt (sigma/R)^lam, as pot_eval forms it
-    const double q = R / b;
-    c2_out = q * q;
-#pragma unroll
-    for (int t = 0; t < NT; t++) Ap_out[t] = c2_out * A[t];
-    unsigned nd = 0;
-    double I;
-    if (c_ts_exact) { redo = false; I = theta_integral<NT>(srows, grows, KS, A, q * q, nd, st); exec_nodes += nd; }
-    else {
-        bool early;
-        I = theta_integral_em<NT>(srows, grows, KS, A, q * q, nd, exec_nodes, st, redo, early);
-        // whole columns end early together (neighbouring lanes share g), so summing them here costs no divergence
-        if (redo && early) { redo = false; nd = 0; I = theta_integral<NT>(srows, grows, KS, A, q * q, nd, st); exec_nodes += nd; }
-    }
-    if (!redo) { nodes += nd; status |= st; }
-    return I;
-}
+                                            unsigned& nodes, unsigned& exec_nodes, int& status, bool& redo, double (&Ap_out)[NT], double& c2_out);
 // The same work in two phases, for the batched Omega kernels: lane_setup does the root finding (its own kernel: every lane
 // is in get_R, small code), lane_sum_defer the strided sum from the stored A_t = Bt (sigma/R)^lam_t and c2 = (R/b)^2.
 template<int NT>
@@ -656,7 +644,7 @@ __device__ void lane_setup(const PairParams& pp, const double* coeff, double T, 
     const double q = R / b;
     c2 = q * q;
 }
-template<int NT>
+template<int NT, int S>
 __device__ double lane_sum_defer(const double* __restrict__ srows, const double* __restrict__ grows, int KS, const double (&A)[NT], double c2,
                                  unsigned& nodes, unsigned& exec_nodes, int& status, bool& redo, double (&Ap_out)[NT]) {
 #pragma unroll
@@ -667,7 +655,7 @@ __device__ double lane_sum_defer(const double* __restrict__ srows, const double*
     if (c_ts_exact) { redo = false; I = theta_integral<NT>(srows, grows, KS, A, c2, nd, st); exec_nodes += nd; }
     else {
         bool early;
-        I = theta_integral_em<NT>(srows, grows, KS, A, c2, nd, exec_nodes, st, redo, early);
+        I = theta_integral_em<NT, S>(srows, grows, KS, A, c2, nd, exec_nodes, st, redo, early);
         // whole columns end early together (neighbouring lanes share g), so summing them here costs no divergence
         if (redo && early) { redo = false; nd = 0; I = theta_integral<NT>(srows, grows, KS, A, c2, nd, st); exec_nodes += nd; }
     }

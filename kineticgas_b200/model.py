@@ -224,9 +224,9 @@ class OmegaPlan:
         return dict(zip(keys, out.tolist()))
 
     def quadrature_stats(self):
-        out = np.zeros(4)
+        out = np.zeros(8)
         self.model._chk(self.model.L.kg_omega_plan_quadrature_stats(self.h, _p(out)), "kg_omega_plan_quadrature_stats")
-        return dict(zip(["reference_nodes", "executed_nodes", "redo_integrals", "theta_integrals"], out.tolist()))
+        return dict(zip(["reference_nodes", "executed_nodes", "redo_integrals", "theta_integrals", "stride8_integrals", "mesh_cells"], out.tolist()))
 
     def close(self):
         if getattr(self, "h", None):
