@@ -57,7 +57,7 @@ def _cpu_worker(task):
     t0 = time.perf_counter()
     if kind == "reference":
         from oracle import ref
-        m = ref.RefMie([Mw], [s], [e], [la], [lr], is_idealgas=True)
+        m = ref.RefMie([Mw], [s], [e], [la], [lr], is_idealgas=True, py_constants=False)     # same eps [J] and m [kg] as the device model
         m.set_omega_correlation_active(False)
         val = m.omega(0, 0, l, r, T)
     else:
@@ -222,8 +222,10 @@ def run_state_points(local_rank, rank, world, n_gpus, steps):
     from kineticgas_b200 import MieKinGas
     from kineticgas_b200.kingas import PROP_DIFFUSION, PROP_THERMAL_DIFFUSION
     kin = MieKinGas(SP_COMPS, N=SP_N, is_idealgas=False, device=local_rank)
+    from kineticgas_b200 import pinned_copy
     T, Vm, x, _ = sp_grid(n_gpus, rank)
-    eos = {"dmudn": sp_eos(T, Vm, x)}
+    T, Vm, x = pinned_copy(T), pinned_copy(Vm), pinned_copy(x)          # the caller's arrays live in page-locked memory (kg_host_alloc)
+    eos = {"dmudn": pinned_copy(sp_eos(T, Vm, x))}
     props = PROP_DIFFUSION | PROP_THERMAL_DIFFUSION
     out = {"ms": [], "ms_tables": [], "ms_state_kernels": [], "launches": 0}
     res = None
@@ -297,8 +299,10 @@ def run_five_comp(local_rank, rank, n_gpus, steps):
     GPU, device tables (15 pairs; the 5 CO2 pairs fully integrated) rebuilt every step. Host buffers in and out."""
     from kineticgas_b200 import MieKinGas
     kin = MieKinGas(FC_COMPS, N=FC_N, is_idealgas=False, device=local_rank)
+    from kineticgas_b200 import pinned_copy
     T, Vm, x = fc_grid(n_gpus, rank)
-    eos = {"dmudn": sp_eos(T, Vm, x), "cp_ideal": np.full((T.size, 5), 4.5 * R_GAS)}
+    T, Vm, x = pinned_copy(T), pinned_copy(Vm), pinned_copy(x)          # the caller's arrays live in page-locked memory (kg_host_alloc)
+    eos = {"dmudn": pinned_copy(sp_eos(T, Vm, x)), "cp_ideal": pinned_copy(np.full((T.size, 5), 4.5 * R_GAS))}
     out = {"ms": [], "ms_tables": []}
     res = None
     for step in range(steps + 1):

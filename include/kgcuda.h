@@ -7,6 +7,7 @@
  */
 #ifndef KGCUDA_H
 #define KGCUDA_H
+#include <stddef.h>
 #include <stdint.h>
 #ifdef __cplusplus
 extern "C" {
@@ -78,6 +79,10 @@ const char* kg_last_error(const kg_model* m);   /* m may be NULL: error of the l
 /* "libkgcuda sm_100a src-sha256:<16 hex>": hash of kineticgas_b200/csrc/* + include/kgcuda.h the binary was built from
  * (__graft_entry__.source_sha() recomputes it from the tree; bench.py prints both so a stale binary is visible). */
 const char* kg_build_info(void);
+/* Page-locked host buffers (cudaHostAlloc). Arrays passed to kg_transport_batch / kg_omega_plan_fetch from such memory are copied by
+ * asynchronous DMA, overlapped with the kernels chunk by chunk; pageable memory works too (staged by the driver). NULL on failure. */
+void* kg_host_alloc(size_t bytes);
+void kg_host_free(void* p);
 int kg_model_npairs(const kg_model* m);
 /* Run all work of this model on a caller-owned CUDA stream (cudaStream_t passed as void*), e.g. the host framework's
  * current stream, so that the caller's events bracket the kernels. */

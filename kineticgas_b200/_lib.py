@@ -15,7 +15,7 @@ EXPORTS = [
     "kg_omega_plan_create", "kg_omega_plan_run", "kg_omega_plan_sync", "kg_omega_plan_fetch", "kg_omega_plan_omega_dev",
     "kg_omega_plan_destroy", "kg_omega_plan_counters", "kg_measure_fp64_peak", "kg_model_set_stream", "kg_omega_plan_export_dev", "kg_transfer_lengths_batch",
     "kg_model_create_ex", "kg_potential_points", "kg_genpot_describe", "kg_omega_plan_quadrature_stats", "kg_set_exact_quadrature",
-    "kg_omega_plan_create_masked", "kg_build_info", "kg_tcache_create", "kg_tcache_destroy", "kg_tcache_lr", "kg_tcache_fetch", "kg_transport_batch", "kg_last_timings",
+    "kg_omega_plan_create_masked", "kg_build_info", "kg_host_alloc", "kg_host_free", "kg_tcache_create", "kg_tcache_destroy", "kg_tcache_lr", "kg_tcache_fetch", "kg_transport_batch", "kg_last_timings",
 ]
 
 
@@ -52,6 +52,10 @@ def lib():
         L.kg_last_error.restype = C.c_char_p
         L.kg_build_info.restype = C.c_char_p
         L.kg_build_info.argtypes = []
+        L.kg_host_alloc.restype = C.c_void_p
+        L.kg_host_alloc.argtypes = [C.c_size_t]
+        L.kg_host_free.restype = None
+        L.kg_host_free.argtypes = [C.c_void_p]
         L.kg_last_error.argtypes = [C.c_void_p]
         L.kg_model_npairs.argtypes = [C.c_void_p]
         L.kg_chi_points.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int, dp, dp, dp, dp, dp, ip]
@@ -78,3 +82,68 @@ def lib():
         L.kg_transport_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, dp, dp, dp, C.c_void_p, C.c_void_p, C.c_void_p, ip]
         _LIB = L
     return _LIB
+
+
+# ---- page-locked host arrays (kg_host_alloc): freed blocks are kept for reuse (cudaHostAlloc costs ~1 ms per few MB)
+_PINNED_FREE = {}          # nbytes -> [ptr, ...]
+_PINNED_CACHED = [0]
+_PINNED_CACHE_LIMIT = 2 << 30
+
+
+class _PinnedBlock:
+    """Owner of one cudaHostAlloc block; arrays made by pinned_empty (and their views) keep it alive."""
+
+    def __init__(self, nbytes):
+        self.nbytes = (max(1, nbytes) + 65535) & ~65535
+        free = _PINNED_FREE.get(self.nbytes)
+        if free:
+            self.ptr = free.pop()
+            _PINNED_CACHED[0] -= self.nbytes
+        else:
+            self.ptr = lib().kg_host_alloc(self.nbytes)
+            if not self.ptr:
+                raise MemoryError(f"kg_host_alloc({self.nbytes}) failed (no CUDA device?)")
+        self.buf = (C.c_char * self.nbytes).from_address(self.ptr)
+
+    def __del__(self):
+        try:
+            if _PINNED_CACHED[0] + self.nbytes <= _PINNED_CACHE_LIMIT:
+                _PINNED_FREE.setdefault(self.nbytes, []).append(self.ptr)
+                _PINNED_CACHED[0] += self.nbytes
+            else:
+                lib().kg_host_free(self.ptr)
+        except Exception:
+            pass
+
+
+def pinned_empty(shape, dtype=float):
+    """numpy array in page-locked host memory: H2D / D2H of the batch calls run as asynchronous DMA from / into it."""
+    import numpy as np
+
+    class PinnedArray(np.ndarray):
+        _kg_block = None
+
+        def __array_finalize__(self, obj):
+            if obj is not None:
+                self._kg_block = getattr(obj, "_kg_block", None)
+
+    global _PinnedArray
+    if _PinnedArray is None:
+        _PinnedArray = PinnedArray
+    dt = np.dtype(dtype)
+    n = int(np.prod(shape))
+    blk = _PinnedBlock(n * dt.itemsize)
+    arr = np.frombuffer(blk.buf, dtype=dt, count=n).reshape(shape).view(_PinnedArray)
+    arr._kg_block = blk
+    return arr
+
+
+_PinnedArray = None
+
+
+def pinned_copy(a, dtype=float):
+    import numpy as np
+    a = np.asarray(a, dtype)
+    out = pinned_empty(a.shape, dtype)
+    out[...] = a
+    return out

@@ -270,13 +270,45 @@ __device__ __forceinline__ double rsqrt_seed(double x) {
 #define KG_RSQRT_ORDER 3
 #endif
 
+// Where the tanh-sinh node rows of the current pair live: the first KS rows in shared memory (s = byte address in the shared
+// window, sp = the same as a generic pointer for the generic-potential path), all KMAX rows in global memory (g). Row j holds
+// node k = j + 1. The hot loops read shared rows with explicit 128-bit ld.shared (two per row at NT = 2): handed a plain pointer
+// the compiler cannot prove the address space once a row may come from either table and falls back to 64-bit generic loads with
+// 64-bit address arithmetic -- 2.5x the load instructions of a loop whose FP64 work is 7 instructions per node.
+template<int NT>
+struct NodeRows {
+    unsigned s;
+    const double* sp;
+    const double* g;
+    int KS;
+    static constexpr int W = 2 + NT;
+    __device__ __forceinline__ void load_s(int k, double (&r)[2 + NT]) const {          // node k <= KS
+        const unsigned a = s + (unsigned) (k - 1) * (unsigned) (W * 8);
+#pragma unroll
+        for (int q = 0; q < W / 2; q++)
+            asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(r[2 * q]), "=d"(r[2 * q + 1]) : "r"(a + 16u * q));
+    }
+    __device__ __forceinline__ void load_at(unsigned a, double (&r)[2 + NT]) const {    // shared byte address of the row
+#pragma unroll
+        for (int q = 0; q < W / 2; q++)
+            asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(r[2 * q]), "=d"(r[2 * q + 1]) : "r"(a + 16u * q));
+    }
+    __device__ __forceinline__ void load_g(int k, double (&r)[2 + NT]) const {
+        const double2* __restrict__ p = reinterpret_cast<const double2*>(g + (size_t) (k - 1) * W);
+#pragma unroll
+        for (int q = 0; q < W / 2; q++) { const double2 v = __ldg(p + q); r[2 * q] = v.x; r[2 * q + 1] = v.y; }
+    }
+    __device__ __forceinline__ void load(int k, double (&r)[2 + NT]) const { if (k <= KS) load_s(k, r); else load_g(k, r); }
+    __device__ __forceinline__ unsigned addr(int k) const { return s + (unsigned) (k - 1) * (unsigned) (W * 8); }
+};
+
 // One tanh-sinh term  w_k f(u_k) = (w_k/u_k) X_k^(-1/2)  from a table row { (w/u)/2, 1/u^2, u^lam_0 .. }.
 // Ap[t] = c2 A_t, so X = (1/u^2) (c2 - sum_t Ap_t u^lam_t) - 1 costs NT+1 DFMA. The reciprocal square root is a MUFU
 // seed y0 plus one Householder step on e = 1 - X y0^2, fused with the weight: t = 2 z (1 + e/2 + 3e^2/8), z = (w/2u) y0
 // (relative error < 1e-19 for order 3, < 3e-14 for order 2). X <= 0 or NaN gives t = NaN, which fails the stop test.
 // This exact form is used for the first node and wherever the stop rule may trigger.
 template<int NT>
-__device__ __forceinline__ double ts_term(const double* __restrict__ row, const double (&Ap)[NT], double c2) {
+__device__ __forceinline__ double ts_term(const double (&row)[2 + NT], const double (&Ap)[NT], double c2) {
     double P = c2;
 #pragma unroll
     for (int t = 0; t < NT; t++) P = fma(-Ap[t], row[2 + t], P);
@@ -302,7 +334,7 @@ __device__ __forceinline__ double ts_term(const double* __restrict__ row, const 
 // and < 1e100. Anything else -- the end of the sum, a non-positive radicand, NaN/Inf -- falls through to the exact
 // sequential replay, which is the reference's rule term by term.
 template<int NT>
-__device__ __forceinline__ void ts_fast(const double* __restrict__ row, const double (&Ap)[NT], double c2, double& z, double& c) {
+__device__ __forceinline__ void ts_fast(const double (&row)[2 + NT], const double (&Ap)[NT], double c2, double& z, double& c) {
     double P = c2;
 #pragma unroll
     for (int t = 0; t < NT; t++) P = fma(-Ap[t], row[2 + t], P);
@@ -317,18 +349,20 @@ constexpr int HI_1E100 = 0x54B249AD;      // high word of 1e100
 
 // 1: every theta integral is summed node by node (validation switch, kg_set_exact_quadrature); 0: Euler-Maclaurin path below
 static __constant__ int c_ts_exact = 0;
+// acceptance threshold of the first (stride 16) tier on |i16 - i32| / |i16| (tuning knob: environment KG_EM_ACCEPT16 at model creation)
+static __constant__ double c_em_accept16 = 1e-7;
 
-// Exact replay of four consecutive nodes with the reference's sequential stop rule: a term is added only if all earlier
-// ones were and |w f / I| > tol (Integration.cpp:431); NaN/Inf of the new integrand value (radicand <= 0) ends the sum
+// Exact replay of four consecutive nodes k+1 .. k+4 with the reference's sequential stop rule: a term is added only if all
+// earlier ones were and |w f / I| > tol (Integration.cpp:431); NaN/Inf of the new integrand value (radicand <= 0) ends the sum
 // (Integration.cpp:430). I is the running sum, k = index of the last node examined (what the reference's loop variable
 // holds at exit). Returns true when the sum has ended.
 template<int NT>
-__device__ __noinline__ bool ts_exact4(const double* __restrict__ r0, const double (&Ap)[NT], double cc, double& I, int& k) {
-    constexpr int W = 2 + NT;
-    const double t0 = ts_term<NT>(r0, Ap, cc);
-    const double t1 = ts_term<NT>(r0 + W, Ap, cc);
-    const double t2 = ts_term<NT>(r0 + 2 * W, Ap, cc);
-    const double t3 = ts_term<NT>(r0 + 3 * W, Ap, cc);
+__device__ __noinline__ bool ts_exact4(const NodeRows<NT>& R, const double (&Ap)[NT], double cc, double& I, int& k) {
+    double r[2 + NT];
+    R.load(k + 1, r); const double t0 = ts_term<NT>(r, Ap, cc);
+    R.load(k + 2, r); const double t1 = ts_term<NT>(r, Ap, cc);
+    R.load(k + 3, r); const double t2 = ts_term<NT>(r, Ap, cc);
+    R.load(k + 4, r); const double t3 = ts_term<NT>(r, Ap, cc);
     const double S1 = I + t0, S2 = S1 + t1, S3 = S2 + t2, S4 = S3 + t3;
     const bool ok0 = fabs(t0) > fabs(TS_TOL * I);
     const bool ok1 = ok0 && (fabs(t1) > fabs(TS_TOL * S1));
@@ -345,25 +379,23 @@ __device__ __noinline__ bool ts_exact4(const double* __restrict__ r0, const doub
 #endif
 
 // cpp/Spherical.cpp:321-329 + cpp/Integration/Integration.cpp:417-437, on tabulated nodes.
-// srows: first KS rows in shared memory; grows: all KMAX rows in global memory. Row j holds node k = j + 1.
 // A[t] = eps C_t (sigma/R)^lam_t / (kT g^2), c2 = (R/b)^2. nodes += k at exit.
 // The reference's loop continued from node k (running sum I): blocks of KG_TS_BLOCK fast nodes with one conservative
 // high-word stop check per block; a block that may contain the stop (or anything irregular) is replayed exactly, four nodes at
 // a time. On return k = index of the last node examined.
 template<int NT>
-__device__ __forceinline__ void ts_tail(const double* __restrict__ srows, const double* __restrict__ grows, int KS,
-                                        const double (&Ap)[NT], double c2, double& I, int& k, int& status) {
-    constexpr int W = 2 + NT;
+__device__ __forceinline__ void ts_tail(const NodeRows<NT>& R, const double (&Ap)[NT], double c2, double& I, int& k, int& status) {
     for (;;) {
 #ifndef KG_TS_NOFAST
-        while (k + KG_TS_BLOCK <= KS) {
-            const double* __restrict__ r = srows + (size_t) k * W;
+        while (k + KG_TS_BLOCK <= R.KS) {
+            const unsigned a0 = R.addr(k + 1);
             double In = I;
             int zmin = 0x7fffffff;
 #pragma unroll
             for (int j = 0; j < KG_TS_BLOCK; j++) {
-                double z, c;
-                ts_fast<NT>(r + j * W, Ap, c2, z, c);
+                double r[2 + NT], z, c;
+                R.load_at(a0 + (unsigned) (j * NodeRows<NT>::W * 8), r);
+                ts_fast<NT>(r, Ap, c2, z, c);
                 In = fma(z, c, In);
                 zmin = min(zmin, __double2hiint(z));
             }
@@ -373,20 +405,20 @@ __device__ __forceinline__ void ts_tail(const double* __restrict__ srows, const 
         }
 #endif
         if (k + 4 > KMAX) { status |= 2; break; }
-        const double* r = (k + 4 <= KS) ? srows + (size_t) k * W : grows + (size_t) k * W;
-        if (ts_exact4<NT>(r, Ap, c2, I, k)) break;
+        if (ts_exact4<NT>(R, Ap, c2, I, k)) break;
     }
 }
 
 template<int NT>
-__device__ __noinline__ double theta_integral(const double* __restrict__ srows, const double* __restrict__ grows, int KS,
-                                 const double (&A)[NT], double c2, unsigned& nodes, int& status) {
+__device__ __noinline__ double theta_integral(const NodeRows<NT>& R, const double (&A)[NT], double c2, unsigned& nodes, int& status) {
     double Ap[NT];
 #pragma unroll
     for (int t = 0; t < NT; t++) Ap[t] = c2 * A[t];
-    double I = ts_term<NT>(srows, Ap, c2);              // k = 1 is added unconditionally (Integration.cpp:425)
+    double r[2 + NT];
+    R.load_s(1, r);
+    double I = ts_term<NT>(r, Ap, c2);              // k = 1 is added unconditionally (Integration.cpp:425)
     int k = 1;
-    ts_tail<NT>(srows, grows, KS, Ap, c2, I, k, status);
+    ts_tail<NT>(R, Ap, c2, I, k, status);
     nodes += (unsigned) k;
     return I;
 }
@@ -403,11 +435,14 @@ __device__ __noinline__ double theta_integral(const double* __restrict__ srows, 
 // Every other coarse node gives the stride-2S sum for free; the two end-corrected integrals must agree to `accept`, otherwise
 // (near-orbiting trajectories whose integrand has structure on the scale of a few nodes, a non-positive radicand, the
 // early stop of the g = 1e-7 column, ...) the lane reports `redo` and the entry goes to the next tier.
-//   S = 16, accept 1e-9 (first tier):  error of the accepted sums < 2e-11 relative (the stride-32 estimate is ~250x worse than
-//                                      the stride-16 one, so the difference over-estimates the error by that factor), ~96 % accepted
-//   S = 8,  accept 1e-10 (second tier): error < 5e-13, ~99 % accepted
-// (measured against the node-by-node sums on random LJ 12-6 trajectories, tools/em_stride_probe.py; whole-lattice W and the
-// reference node totals in tests/test_gpu_chi_omega.py). Third tier: node by node.
+//   S = 16, accept 1e-7 (first tier):  the stride-32 estimate is far worse than the stride-16 one (256x where the end corrections
+//                                      dominate, quadratically where an interior feature does), so the difference over-estimates
+//                                      the error of the stride-16 sum by orders of magnitude: measured on configs[1] against the
+//                                      node-by-node sums, Omega agrees to 3e-11 and the reference node totals are identical
+//                                      (tools/tune_accept.py, profiles/r2_tune_accept.md); ~97 % of the integrals are accepted
+//   S = 8,  accept 1e-10 (second tier): error < 5e-13
+// (random LJ 12-6 trajectories: tools/em_stride_probe.py; whole lattices: tests/test_gpu_chi_omega.py, tests/test_gpu_regimes.py).
+// Third tier: node by node.
 // ------------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void fd7(const double (&f)[7], double& d1, double& d3, double& d5) {
     d1 = -2.45 * f[0] + 6. * f[1] - 7.5 * f[2] + (20. / 3.) * f[3] - 3.75 * f[4] + 1.2 * f[5] - (1. / 6.) * f[6];
@@ -416,74 +451,89 @@ __device__ __forceinline__ void fd7(const double (&f)[7], double& d1, double& d3
 }
 
 template<int NT, int S>
-__device__ double theta_integral_em(const double* __restrict__ srows, const double* __restrict__ grows, int KS,
-                                    const double (&A)[NT], double c2, unsigned& nodes, unsigned& exec_nodes, int& status, bool& redo,
-                                    bool& redo_early) {
-    constexpr int W = 2 + NT;
-    constexpr double ACCEPT = (S >= 16) ? 1e-9 : 1e-10;
+__device__ double theta_integral_em(const NodeRows<NT>& R, const double (&A)[NT], double c2, unsigned& nodes, unsigned& exec_nodes,
+                                    int& status, bool& redo, bool& redo_early) {
+    constexpr unsigned RB = NodeRows<NT>::W * 8;              // bytes per row
+    const double ACCEPT = (S >= 16) ? c_em_accept16 : 1e-10;
     constexpr double S2 = (double) S * S, S4 = S2 * S2, S6 = S4 * S2;
+    const int KS = R.KS;
     redo_early = false;
     double Ap[NT];
 #pragma unroll
     for (int t = 0; t < NT; t++) Ap[t] = c2 * A[t];
     redo = true;
     auto fast = [&](int k) {                                  // node k (1-based); NaN when the radicand is not positive
-        const double* __restrict__ row = ((k <= KS) ? srows : grows) + (size_t) (k - 1) * W;
-        double z, c;
-        ts_fast<NT>(row, Ap, c2, z, c);
+        double r[2 + NT], z, c;
+        R.load(k, r);
+        ts_fast<NT>(r, Ap, c2, z, c);
         return z * c;
     };
-    const double t1 = ts_term<NT>(srows, Ap, c2);
+    double row[2 + NT];
+    R.load_s(1, row);
+    const double t1 = ts_term<NT>(row, Ap, c2);
     double f[7];
-#pragma unroll 1
-    for (int i = 0; i < 7; i++) f[i] = fast(2 + i);             // rolled: executed once per integral, keep the code small
+#pragma unroll
+    for (int i = 0; i < 7; i++) { R.load_s(2 + i, row); double z, c; ts_fast<NT>(row, Ap, c2, z, c); f[i] = z * c; }
     double d1a, d3a, d5a;
     fd7(f, d1a, d3a, d5a);
     const double ga = f[0];
     // coarse sums in units of g: Sg = sum over coarse nodes j >= 1, Eg = the even ones; running sum I = base + S Sg
     const double base = t1 + (0.5 * S) * ga;
-    double Sg = 0.0, Eg = 0.0, glast = ga, gb;
+    double Sg = 0.0, Eg = 0.0, gb;
     int j0 = 1, bj;
     // Blocks whose four coarse rows are staged in shared memory (practically all: sums end near node 2000 of the 2560 staged)
-    // step a pointer; the remainder selects the table per row.
+    // step a shared-memory address; the remainder selects the table per row.
     const int j_smem = (KS - 2 - 3 * S) / S;                  // largest j0 with 2 + S (j0 + 3) <= KS
-    const double* __restrict__ rp = srows + (size_t) (1 + S) * W;      // row of coarse node j0 = 1 (node 2 + S)
-    for (;;) {
-        const int kb = 2 + S * j0;
-        if (kb + 3 * S + 8 > KMAX) { exec_nodes += (unsigned) (j0 + 8); return 0.0; }
-        double z0, c0, z1, c1, z2, c2_, z3, c3;
-        if (j0 <= j_smem) {
-            ts_fast<NT>(rp, Ap, c2, z0, c0);
-            ts_fast<NT>(rp + S * W, Ap, c2, z1, c1);
-            ts_fast<NT>(rp + 2 * S * W, Ap, c2, z2, c2_);
-            ts_fast<NT>(rp + 3 * S * W, Ap, c2, z3, c3);
-            rp += 4 * S * W;
-        } else {
-            auto rowp = [&](int k) { return ((k <= KS) ? srows : grows) + (size_t) (k - 1) * W; };
-            ts_fast<NT>(rowp(kb), Ap, c2, z0, c0);
-            ts_fast<NT>(rowp(kb + S), Ap, c2, z1, c1);
-            ts_fast<NT>(rowp(kb + 2 * S), Ap, c2, z2, c2_);
-            ts_fast<NT>(rowp(kb + 3 * S), Ap, c2, z3, c3);
-        }
-        double Sn = fma(z0, c0, Sg);
-        Sn = fma(z1, c1, Sn);
-        Sn = fma(z2, c2_, Sn);
-        Sn = fma(z3, c3, Sn);
-        const double In = fma((double) S, Sn, base);
-        if (!(In < 1e300)) { exec_nodes += (unsigned) (j0 + 11); return 0.0; }      // NaN (radicand <= 0 somewhere) or overflow
-        // every term of the block against 1.02 tol x the sum after the block, on the high words (z = g / 2 to 2^-20)
+    unsigned ra = R.addr(2 + S);                              // row of coarse node j0 = 1 (node 2 + S)
+    double z0, c0, z1, c1, z2, c2_, z3, c3, In;
+    bool closing = false;
+    while (j0 <= j_smem) {                                    // hot loop: 4 coarse nodes per trip
+        double r0[2 + NT], r1[2 + NT], r2[2 + NT], r3[2 + NT];
+        R.load_at(ra, r0); R.load_at(ra + S * RB, r1); R.load_at(ra + 2 * S * RB, r2); R.load_at(ra + 3 * S * RB, r3);
+        ts_fast<NT>(r0, Ap, c2, z0, c0);
+        ts_fast<NT>(r1, Ap, c2, z1, c1);
+        ts_fast<NT>(r2, Ap, c2, z2, c2_);
+        ts_fast<NT>(r3, Ap, c2, z3, c3);
+        const double Sa = fma(z1, c1, fma(z0, c0, Sg));
+        const double Sn = fma(z3, c3, fma(z2, c2_, Sa));
+        In = fma((double) S, Sn, base);
+        // every term of the block against 1.02 tol x the sum after the block, on the high words (z = g / 2 to 2^-20); a NaN sum
+        // (radicand <= 0 somewhere) has a high word that fails one of the two integer tests
         const int lim = __double2hiint((0.5 * 1.02 * TS_TOL) * In);
         const int zmin = min(min(__double2hiint(z0), __double2hiint(z1)), min(__double2hiint(z2), __double2hiint(z3)));
-        if ((zmin > lim + 2) && (lim >= 0)) {
-            Eg = fma(z1, c1, Eg);
-            Eg = fma(z3, c3, Eg);
-            Sg = Sn; glast = z3 * c3; j0 += 4;
-            continue;
+        if (!((zmin > lim + 2) && (lim >= 0) && (lim < HI_1E100))) { closing = true; break; }
+        Eg = fma(z3, c3, fma(z1, c1, Eg));
+        Sg = Sn; j0 += 4; ra += 4 * S * RB;
+    }
+    if (!closing) {                                           // ran off the staged rows (sums that long are rare): table chosen per row
+        for (;;) {
+            const int kb = 2 + S * j0;
+            if (kb + 3 * S + 8 > KMAX) { exec_nodes += (unsigned) (j0 + 8); return 0.0; }
+            double r0[2 + NT];
+            R.load(kb, r0); ts_fast<NT>(r0, Ap, c2, z0, c0);
+            R.load(kb + S, r0); ts_fast<NT>(r0, Ap, c2, z1, c1);
+            R.load(kb + 2 * S, r0); ts_fast<NT>(r0, Ap, c2, z2, c2_);
+            R.load(kb + 3 * S, r0); ts_fast<NT>(r0, Ap, c2, z3, c3);
+            const double Sa = fma(z1, c1, fma(z0, c0, Sg));
+            const double Sn = fma(z3, c3, fma(z2, c2_, Sa));
+            In = fma((double) S, Sn, base);
+            const int lim = __double2hiint((0.5 * 1.02 * TS_TOL) * In);
+            const int zmin = min(min(__double2hiint(z0), __double2hiint(z1)), min(__double2hiint(z2), __double2hiint(z3)));
+            if (!((zmin > lim + 2) && (lim >= 0) && (lim < HI_1E100))) break;
+            Eg = fma(z3, c3, fma(z1, c1, Eg));
+            Sg = Sn; j0 += 4;
         }
+    }
+    if (!(In < 1e300)) { exec_nodes += (unsigned) (j0 + 11); return 0.0; }      // NaN (radicand <= 0 somewhere) or overflow
+    {
+        // the block that may contain the stop: close the coarse range at an even coarse node
         const double g0 = z0 * c0, g1 = z1 * c1, dl = (1.02 * TS_TOL) * In;
         if (g0 > dl && g1 > dl) { Sg += g0 + g1; Eg += g1; bj = j0 + 1; gb = g1; }
-        else { bj = j0 - 1; gb = glast; }
-        break;
+        else {
+            bj = j0 - 1;
+            if (j0 == 1) gb = ga;
+            else { double r0[2 + NT], z, c; R.load(2 + S * bj, r0); ts_fast<NT>(r0, Ap, c2, z, c); gb = z * c; }     // g of the last accepted coarse node
+        }
     }
     const double E = ga + Eg, O = Sg - Eg;
     if (bj * S < 64) { redo_early = true; exec_nodes += (unsigned) (j0 + 11); return 0.0; }      // the sum ends within the first ~70 nodes (g = 1e-7 column): cheap node by node
@@ -501,30 +551,58 @@ __device__ double theta_integral_em(const double* __restrict__ srows, const doub
     if (!(fabs(is - i2s) <= ACCEPT * fabs(is))) { exec_nodes += (unsigned) (bj + 17); return 0.0; }
     double I = t1 + (is + ends + ((1. / 12.) * D1 - (1. / 720.) * D3 + (1. / 30240.) * D5));
     int k = b;
-    ts_tail<NT>(srows, grows, KS, Ap, c2, I, k, status);      // the reference's loop from node b + 1
+    ts_tail<NT>(R, Ap, c2, I, k, status);                     // the reference's loop from node b + 1
     redo = false;
     nodes += (unsigned) k;
     exec_nodes += (unsigned) (bj + 13 + (k - b) + 4);
     return I;
 }
 
-// Node-by-node sum of ONE theta integral by a whole warp: lane l evaluates node base + 1 + l in the exact form, a warp scan
-// gives the running sums the reference's stop rule needs, a ballot finds the first node that fails it. Used by the batched
-// kernel for the few integrals its strided sum rejects, so that no lane ever walks ~2000 nodes alone while 31 others wait.
+// Node-by-node sum of ONE theta integral by a whole warp (third tier: the few integrals both strided sums reject, so that no
+// lane ever walks ~2000 nodes alone while 31 others wait). Lane l owns nodes base + 1 + l + 32 i. Far from the stop the lanes add
+// fast terms to private partial sums for WARP_RUN iterations (32 WARP_RUN nodes) and one warp reduction then checks, conservatively,
+// that no node of the run could have triggered the reference's stop rule (every term above 1.02 tol x the sum after the run,
+// everything finite); a run that fails the check is replayed from its start in the exact form with a warp scan, which gives the
+// running sums the reference's rule needs term by term, and a ballot finds the first node that fails it.
 // All lanes must call with the same (Ap, c2). Returns I; k_out = index of the last node examined.
+constexpr int WARP_RUN = 8;
 template<int NT>
-__device__ double theta_integral_warp(const double* __restrict__ srows, const double* __restrict__ grows, int KS,
-                                      const double (&Ap)[NT], double c2, int& k_out, int& status) {
-    constexpr int W = 2 + NT;
+__device__ double theta_integral_warp(const NodeRows<NT>& R, const double (&Ap)[NT], double c2, int& k_out, int& status) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    double I = ts_term<NT>(srows, Ap, c2);                   // node 1, added unconditionally (Integration.cpp:425)
-    for (int base = 1; ; base += 32) {
+    double row[2 + NT];
+    R.load_s(1, row);
+    double I = ts_term<NT>(row, Ap, c2);                      // node 1, added unconditionally (Integration.cpp:425)
+    int base = 1;                                             // nodes <= base are summed
+    // fast runs
+    while (base + 32 * WARP_RUN <= R.KS) {
+        double P = 0.0;
+        int zmin = 0x7fffffff;
+        unsigned a = R.addr(base + 1 + lane);
+#pragma unroll
+        for (int i = 0; i < WARP_RUN; i++) {
+            double z, c;
+            R.load_at(a, row);
+            ts_fast<NT>(row, Ap, c2, z, c);
+            P = fma(z, c, P);
+            zmin = min(zmin, __double2hiint(z));
+            a += 32u * NodeRows<NT>::W * 8u;
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) { P += __shfl_xor_sync(full, P, off); zmin = min(zmin, __shfl_xor_sync(full, zmin, off)); }
+        const double In = I + P;
+        const int lim = __double2hiint((0.5 * 1.02 * TS_TOL) * In);
+        if (!((zmin > lim + 2) && (lim < HI_1E100) && (lim >= 0))) break;      // NaN sums give lim < 0 or a failed compare
+        I = In; base += 32 * WARP_RUN;
+    }
+    // exact replay from `base`
+    for (;; base += 32) {
         const int k = base + 1 + lane;
         double t = 0.0;
         bool ok = false;
         if (k <= KMAX) {
-            t = ts_term<NT>(((k <= KS) ? srows : grows) + (size_t) (k - 1) * W, Ap, c2);
+            R.load(k, row);
+            t = ts_term<NT>(row, Ap, c2);
             ok = !(isnan(t) || isinf(t));
         }
         double P = ok ? t : 0.0;                              // inclusive prefix sum over the lanes
@@ -574,8 +652,10 @@ __device__ double lane_get_R(const PairParams& pp, const double* coeff, double T
 
 // Generic potentials: the reference's loop node for node (cpp/Integration/Integration.cpp:417-437) with
 // f(u) = (R/u^2) [ r^4/b^2 (1 - u(r)/(kT g^2)) - r^2 ]^(-1/2) = (1/u) X^(-1/2), X = (R/b)^2 (1/u^2) (1 - U) - 1, r = R/u.
-static __device__ double theta_integral_gen(const double* __restrict__ srows, const double* __restrict__ grows, int KS,
-                                     const Lane<1>& c, double R, unsigned& nodes, int& status) {
+static __device__ double theta_integral_gen(const NodeRows<1>& NR, const Lane<1>& c, double R, unsigned& nodes, int& status) {
+    const double* __restrict__ srows = NR.sp;
+    const double* __restrict__ grows = NR.g;
+    const int KS = NR.KS;
     const double q = R / c.b, c2 = q * q;
     const int zero_neg = c.gp->zero_on_negative;
     auto term = [&](int k, bool& bad) {
@@ -606,8 +686,7 @@ static __device__ double theta_integral_gen(const double* __restrict__ srows, co
 
 // Full single-lane evaluation of the theta integral for (g, b): R, A_t, c2, then the sum. Returns I; R_out in sigma.
 template<int NT>
-__device__ double lane_theta_integral(const PairParams& pp, const double* coeff, const double* __restrict__ srows,
-                                      const double* __restrict__ grows, int KS, double T, double g, double b,
+__device__ double lane_theta_integral(const PairParams& pp, const double* coeff, const NodeRows<NT>& NR, double T, double g, double b,
                                       double& R_out, unsigned& nodes, int& status) {
     Lane<NT> c;
     make_lane<NT>(c, pp, coeff, T, g, b);
@@ -618,20 +697,19 @@ __device__ double lane_theta_integral(const PairParams& pp, const double* coeff,
     const double q = R / b;
     if (!c_ts_exact) {
         bool redo, early; unsigned ex = 0;
-        double I = theta_integral_em<NT, 16>(srows, grows, KS, A, q * q, nodes, ex, status, redo, early);
+        double I = theta_integral_em<NT, 16>(NR, A, q * q, nodes, ex, status, redo, early);
         if (!redo) return I;
         if (!early) {
-            I = theta_integral_em<NT, 8>(srows, grows, KS, A, q * q, nodes, ex, status, redo, early);
+            I = theta_integral_em<NT, 8>(NR, A, q * q, nodes, ex, status, redo, early);
             if (!redo) return I;
         }
     }
-    return theta_integral<NT>(srows, grows, KS, A, q * q, nodes, status);
+    return theta_integral<NT>(NR, A, q * q, nodes, status);
 }
 
 // For the batched Omega kernel of the generic potentials (declaration; the power-law kernels use lane_setup + lane_sum_defer)
 template<int NT>
-__device__ double lane_theta_integral_defer(const PairParams& pp, const double* coeff, const double* __restrict__ srows,
-                                            const double* __restrict__ grows, int KS, double T, double g, double b,
+__device__ double lane_theta_integral_defer(const PairParams& pp, const double* coeff, const NodeRows<NT>& NR, double T, double g, double b,
                                             unsigned& nodes, unsigned& exec_nodes, int& status, bool& redo, double (&Ap_out)[NT], double& c2_out);
 // The same work in two phases, for the batched Omega kernels: lane_setup does the root finding (its own kernel: every lane
 // is in get_R, small code), lane_sum_defer the strided sum from the stored A_t = Bt (sigma/R)^lam_t and c2 = (R/b)^2.
@@ -645,45 +723,42 @@ __device__ void lane_setup(const PairParams& pp, const double* coeff, double T, 
     c2 = q * q;
 }
 template<int NT, int S>
-__device__ double lane_sum_defer(const double* __restrict__ srows, const double* __restrict__ grows, int KS, const double (&A)[NT], double c2,
+__device__ double lane_sum_defer(const NodeRows<NT>& NR, const double (&A)[NT], double c2,
                                  unsigned& nodes, unsigned& exec_nodes, int& status, bool& redo, double (&Ap_out)[NT]) {
 #pragma unroll
     for (int t = 0; t < NT; t++) Ap_out[t] = c2 * A[t];
     unsigned nd = 0;
     int st = 0;
     double I;
-    if (c_ts_exact) { redo = false; I = theta_integral<NT>(srows, grows, KS, A, c2, nd, st); exec_nodes += nd; }
+    if (c_ts_exact) { redo = false; I = theta_integral<NT>(NR, A, c2, nd, st); exec_nodes += nd; }
     else {
         bool early;
-        I = theta_integral_em<NT, S>(srows, grows, KS, A, c2, nd, exec_nodes, st, redo, early);
+        I = theta_integral_em<NT, S>(NR, A, c2, nd, exec_nodes, st, redo, early);
         // whole columns end early together (neighbouring lanes share g), so summing them here costs no divergence
-        if (redo && early) { redo = false; nd = 0; I = theta_integral<NT>(srows, grows, KS, A, c2, nd, st); exec_nodes += nd; }
+        if (redo && early) { redo = false; nd = 0; I = theta_integral<NT>(NR, A, c2, nd, st); exec_nodes += nd; }
     }
     if (!redo) { nodes += nd; status |= st; }
     return I;
 }
 template<>
-__device__ inline double lane_theta_integral_defer<1>(const PairParams& pp, const double* coeff, const double* __restrict__ srows,
-                                                      const double* __restrict__ grows, int KS, double T, double g, double b,
+__device__ inline double lane_theta_integral_defer<1>(const PairParams& pp, const double* coeff, const NodeRows<1>& NR, double T, double g, double b,
                                                       unsigned& nodes, unsigned& exec_nodes, int& status, bool& redo, double (&Ap_out)[1], double& c2_out);
 template<>
-__device__ inline double lane_theta_integral<1>(const PairParams& pp, const double* coeff, const double* __restrict__ srows,
-                                                const double* __restrict__ grows, int KS, double T, double g, double b,
+__device__ inline double lane_theta_integral<1>(const PairParams& pp, const double* coeff, const NodeRows<1>& NR, double T, double g, double b,
                                                 double& R_out, unsigned& nodes, int& status) {
     Lane<1> c;
     make_lane<1>(c, pp, coeff, T, g, b);
     const double R = get_R<1>(c, g, status);
     R_out = R;
-    return theta_integral_gen(srows, grows, KS, c, R, nodes, status);
+    return theta_integral_gen(NR, c, R, nodes, status);
 }
 template<>
-__device__ inline double lane_theta_integral_defer<1>(const PairParams& pp, const double* coeff, const double* __restrict__ srows,
-                                                      const double* __restrict__ grows, int KS, double T, double g, double b,
+__device__ inline double lane_theta_integral_defer<1>(const PairParams& pp, const double* coeff, const NodeRows<1>& NR, double T, double g, double b,
                                                       unsigned& nodes, unsigned& exec_nodes, int& status, bool& redo, double (&Ap_out)[1], double& c2_out) {
     Ap_out[0] = 0.0; c2_out = 0.0;
     redo = false;                  // generic potentials are always summed node by node (piecewise potentials are not smooth in k)
     double R; unsigned nd = 0;
-    const double I = lane_theta_integral<1>(pp, coeff, srows, grows, KS, T, g, b, R, nd, status);
+    const double I = lane_theta_integral<1>(pp, coeff, NR, T, g, b, R, nd, status);
     nodes += nd; exec_nodes += nd;
     return I;
 }

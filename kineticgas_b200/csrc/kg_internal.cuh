@@ -46,6 +46,8 @@ struct kg_model {
     kg::PairParams* d_pairs = nullptr;
     cudaStream_t stream = nullptr;
     bool own_stream = true;
+    cudaStream_t aux_stream[2] = {nullptr, nullptr};   // chunk pipeline of kg_transport_batch (created on first use)
+    cudaEvent_t aux_done[2] = {nullptr, nullptr};
     std::string err;
     int sm_count = 148;
     // stage timings of the last kg_tcache_create / kg_transport_batch on this model (kg_last_timings)

@@ -21,11 +21,11 @@ struct TlItem { int pair; int coeff_off; double T; };
 
 // chi for arbitrary (g, b/sigma) with the column's theta_lim integral already known (cpp/Spherical.cpp:259-270,455-465)
 template<int NT>
-__device__ double chi_with_lim(const PairParams& pp, const double* coeff, const double* srows, const double* grows,
+__device__ double chi_with_lim(const PairParams& pp, const double* coeff, const NodeRows<NT>& NR,
                                double T, double g, double b, double I_lim, double& R, unsigned& nodes, int& st) {
     if (b > 100) return 0.0;
     if (b < 1e-3) return PI_REF;
-    const double I = lane_theta_integral<NT>(pp, coeff, srows, grows, KS_ROWS, T, g, b, R, nodes, st);
+    const double I = lane_theta_integral<NT>(pp, coeff, NR, T, g, b, R, nodes, st);
     const double th = __dadd_rn(__dsub_rn(I, I_lim), PI_REF / 2);
     return __dsub_rn(PI_REF, __dmul_rn(2.0, th));
 }
@@ -43,6 +43,7 @@ __global__ void __launch_bounds__(256) tl_search_kernel(const PairParams* __rest
     for (int i = threadIdx.x; i < KS_ROWS * W; i += blockDim.x) srows[i] = rows[i];
     if (threadIdx.x == 0) pp = pairs[pair];
     __syncthreads();
+    const NodeRows<NT> NR{(unsigned) __cvta_generic_to_shared(srows), srows, rows, KS_ROWS};
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= nitems * TL_NG) return;
     const int it = item0 + e / TL_NG, q = e % TL_NG;
@@ -52,8 +53,8 @@ __global__ void __launch_bounds__(256) tl_search_kernel(const PairParams* __rest
     const long long o = (long long) it * TL_NG + q;
     if (g == 0) { ilim[o] = 0.0; bmid_out[o] = 5.0; bmax_out[o] = 10.0; return; }   // transfer_lengths.cpp:223,235
     int st = 0; unsigned nodes = 0; double R;
-    const double I_lim = lane_theta_integral<NT>(pp, coeff, srows, rows, KS_ROWS, T, g, 100.0, R, nodes, st);
-    auto chi = [&](double b) { return chi_with_lim<NT>(pp, coeff, srows, rows, T, g, b, I_lim, R, nodes, st); };
+    const double I_lim = lane_theta_integral<NT>(pp, coeff, NR, T, g, 100.0, R, nodes, st);
+    auto chi = [&](double b) { return chi_with_lim<NT>(pp, coeff, NR, T, g, b, I_lim, R, nodes, st); };
     // get_bmid, cpp/transfer_lengths.cpp:234-266
     double b = 0.9, db = 0.1;
     double chi_val = chi(b), next_chi_val, dchidb;
@@ -118,6 +119,7 @@ __global__ void __launch_bounds__(256) tl_node_kernel(const PairParams* __restri
     for (int i = threadIdx.x; i < KS_ROWS * W; i += blockDim.x) srows[i] = rows[i];
     if (threadIdx.x == 0) pp = pairs[pair];
     __syncthreads();
+    const NodeRows<NT> NR{(unsigned) __cvta_generic_to_shared(srows), srows, rows, KS_ROWS};
     const long long e = (long long) blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= (long long) nitems * TL_NG * TL_NB) return;
     const int k = (int) (e % TL_NB), q = (int) ((e / TL_NB) % TL_NG), it = item0 + (int) (e / (TL_NB * TL_NG));
@@ -130,7 +132,7 @@ __global__ void __launch_bounds__(256) tl_node_kernel(const PairParams* __restri
         double coef;
         const double b = tl_bnode(k, bmid_in[o], bmax_in[o], coef);
         int st = 0; unsigned nodes = 0; double R = 0.0;
-        const double chi = chi_with_lim<NT>(pp, coeff, srows, rows, T, g, b, ilim[o], R, nodes, st);
+        const double chi = chi_with_lim<NT>(pp, coeff, NR, T, g, b, ilim[o], R, nodes, st);
         if (b < 1e-3 || b > 100) {        // chi short-cuts do not compute R; the integrand's func(b) = get_R still needs it
             R = lane_get_R<NT>(pp, coeff, T, g, b, st);
         }

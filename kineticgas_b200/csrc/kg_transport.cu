@@ -1325,7 +1325,11 @@ int launch_state(kg_tcache* c, StateArgs& a, cudaStream_t s, const double* d_x_f
         else rdf_kernel<<<(unsigned) ((tot + 127) / 128), 128, 0, s>>>(n, a.nslots, tm, a.tidx, a.T_of, a.Vm, d_x_for_rdf, c->d_dbh, c->d_mp_int, d_rdf);
     }
     const int nn = tm.N * tm.nc, grid = (n + 127) / 128;
-    if (nn <= 8) state_kernel<8><<<grid, 128, 0, s>>>(tm, a);
+    // the matrix of one state point lives in the thread's local memory: the tightest leading dimension keeps it in L1
+    if (nn <= 6) state_kernel<6><<<grid, 128, 0, s>>>(tm, a);
+    else if (nn <= 8) state_kernel<8><<<grid, 128, 0, s>>>(tm, a);
+    else if (nn <= 10) state_kernel<10><<<grid, 128, 0, s>>>(tm, a);
+    else if (nn <= 12) state_kernel<12><<<grid, 128, 0, s>>>(tm, a);
     else if (nn <= 16) state_kernel<16><<<grid, 128, 0, s>>>(tm, a);
     else state_kernel<24><<<grid, 128, 0, s>>>(tm, a);
     const cudaError_t e = cudaGetLastError();
@@ -1390,17 +1394,18 @@ extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const do
     a.nslots = (props & KG_PROP_CONDUCTIVITY) ? 2 : 1;
     const int N = opts->N, nn = N * nc, nD = a.opt.do_compress ? nc - 1 : nc;
 #define NEED(p) do { if (!(p)) { set_error("kg_transport_batch: device allocation or copy failed"); return -2; } } while (0)
-    a.tidx = db.put(tidx.data(), n, s); NEED(a.tidx);
+    const bool chunked = n >= 32768;              // large batches: the copies go chunk by chunk on the auxiliary streams (below)
+    a.tidx = db.put(chunked ? nullptr : tidx.data(), n, s); NEED(a.tidx);
     a.T_of = c->d_T;
-    a.Vm = db.put(Vm, n, s); NEED(a.Vm);
-    a.x = m->is_singlecomp ? nullptr : db.put(x, (size_t) n * nc, s); if (!m->is_singlecomp) NEED(a.x);
+    a.Vm = db.put(chunked ? nullptr : Vm, n, s); NEED(a.Vm);
+    a.x = m->is_singlecomp ? nullptr : db.put(chunked ? nullptr : x, (size_t) n * nc, s); if (!m->is_singlecomp) NEED(a.x);
     a.mtl = c->d_mtl; a.etl = c->d_etl; a.brk = c->d_brk;
     double* d_rdf = nullptr;
     if (!opts->is_idealgas) { d_rdf = db.alloc<double>((size_t) n * a.nslots * nc * nc); NEED(d_rdf); }
     a.rdf = d_rdf;
-    if (eos && eos->dmudn && (props & (KG_PROP_DIFFUSION | KG_PROP_THERMAL_DIFFUSION))) { a.dmudn = db.put(eos->dmudn, (size_t) n * nce * nce, s); NEED(a.dmudn); }
-    if (eos && eos->cp_ideal && (props & KG_PROP_CONDUCTIVITY)) { a.cp_ideal = db.put(eos->cp_ideal, (size_t) n * nce, s); NEED(a.cp_ideal); }
-    if (eos && eos->dvdn && opts->frame_of_reference == KG_FOR_COV) { a.dvdn = db.put(eos->dvdn, (size_t) n * nce, s); NEED(a.dvdn); }
+    if (eos && eos->dmudn && (props & (KG_PROP_DIFFUSION | KG_PROP_THERMAL_DIFFUSION))) { a.dmudn = db.put(chunked ? nullptr : eos->dmudn, (size_t) n * nce * nce, s); NEED(a.dmudn); }
+    if (eos && eos->cp_ideal && (props & KG_PROP_CONDUCTIVITY)) { a.cp_ideal = db.put(chunked ? nullptr : eos->cp_ideal, (size_t) n * nce, s); NEED(a.cp_ideal); }
+    if (eos && eos->dvdn && opts->frame_of_reference == KG_FOR_COV) { a.dvdn = db.put(chunked ? nullptr : eos->dvdn, (size_t) n * nce, s); NEED(a.dvdn); }
     struct OutMap { double* host; double** dev; size_t count; };
     OutMap maps[] = {{out->viscosity, &a.viscosity, (size_t) n}, {out->conductivity, &a.conductivity, (size_t) n},
                      {out->conductivity_contribs, &a.contribs, (size_t) n * 3}, {out->D, &a.D, (size_t) n * nD * nD}, {out->DT, &a.DT, (size_t) n * nc}, {out->thermal_diffusion_ratio, &a.kT, (size_t) n * nc}, {out->soret_zarate, &a.soret, (size_t) n * nc},
@@ -1410,22 +1415,80 @@ extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const do
     for (auto& mp : maps) if (mp.host) { *mp.dev = db.alloc<double>(mp.count); NEED(*mp.dev); CUDA_OK(cudaMemsetAsync(*mp.dev, 0, mp.count * sizeof(double), s)); }
     a.status = db.alloc<int>(n); NEED(a.status);
 #undef NEED
-    cudaEvent_t ev0, ev1;
-    CUDA_OK(cudaEventCreate(&ev0)); CUDA_OK(cudaEventCreate(&ev1));
-    CUDA_OK(cudaEventRecord(ev0, s));
-    if (launch_state(c, a, s, a.x, d_rdf)) { set_error("kg_transport_batch: kernel launch failed (" + m->err + ")"); return -2; }
-    CUDA_OK(cudaEventRecord(ev1, s));
-    for (auto& mp : maps) if (mp.host) CUDA_OK(cudaMemcpyAsync(mp.host, *mp.dev, mp.count * sizeof(double), cudaMemcpyDeviceToHost, s));
-    if (out->rdf) {
-        if (opts->is_idealgas) for (size_t k = 0; k < (size_t) n * nc * nc; k++) out->rdf[k] = 1.0;
-        else CUDA_OK(cudaMemcpy2DAsync(out->rdf, (size_t) nc * nc * sizeof(double), d_rdf, (size_t) a.nslots * nc * nc * sizeof(double),
-                                       (size_t) nc * nc * sizeof(double), n, cudaMemcpyDeviceToHost, s));
-    }
+    // Chunked pipeline over two auxiliary streams: H2D of chunk k+1, the rdf + state kernels of chunk k and the D2H of chunk k-1
+    // overlap (truly so when the caller's buffers are pinned, kg_host_alloc; pageable buffers are staged by the driver and only
+    // the kernels overlap). Inputs were enqueued above on the model stream in one piece when the batch is small.
     std::vector<int> st(n);
-    CUDA_OK(cudaMemcpyAsync(st.data(), a.status, n * sizeof(int), cudaMemcpyDeviceToHost, s));
-    CUDA_OK(cudaStreamSynchronize(s));
-    float kms = 0; cudaEventElapsedTime(&kms, ev0, ev1); cudaEventDestroy(ev0); cudaEventDestroy(ev1);
-    m->timings[0] = kms; m->timings[5] = opts->is_idealgas ? 1 : 2;
+    const int nchunk = (n >= 32768) ? 4 : 1;
+    float kms = 0;
+    if (nchunk == 1) {
+        cudaEvent_t ev0, ev1;
+        CUDA_OK(cudaEventCreate(&ev0)); CUDA_OK(cudaEventCreate(&ev1));
+        CUDA_OK(cudaEventRecord(ev0, s));
+        if (launch_state(c, a, s, a.x, d_rdf)) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); set_error("kg_transport_batch: kernel launch failed (" + m->err + ")"); return -2; }
+        CUDA_OK(cudaEventRecord(ev1, s));
+        for (auto& mp : maps) if (mp.host) CUDA_OK(cudaMemcpyAsync(mp.host, *mp.dev, mp.count * sizeof(double), cudaMemcpyDeviceToHost, s));
+        if (out->rdf && !opts->is_idealgas)
+            CUDA_OK(cudaMemcpy2DAsync(out->rdf, (size_t) nc * nc * sizeof(double), d_rdf, (size_t) a.nslots * nc * nc * sizeof(double),
+                                      (size_t) nc * nc * sizeof(double), n, cudaMemcpyDeviceToHost, s));
+        CUDA_OK(cudaMemcpyAsync(st.data(), a.status, n * sizeof(int), cudaMemcpyDeviceToHost, s));
+        CUDA_OK(cudaStreamSynchronize(s));
+        cudaEventElapsedTime(&kms, ev0, ev1); cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+    } else {
+        if (!m->aux_stream[0]) for (int k = 0; k < 2; k++) {
+            CUDA_OK(cudaStreamCreateWithFlags(&m->aux_stream[k], cudaStreamNonBlocking));
+            CUDA_OK(cudaEventCreateWithFlags(&m->aux_done[k], cudaEventDisableTiming));
+        }
+        cudaEvent_t fork, kev[8];
+        CUDA_OK(cudaEventCreateWithFlags(&fork, cudaEventDisableTiming));
+        for (auto& e : kev) CUDA_OK(cudaEventCreate(&e));
+        CUDA_OK(cudaEventRecord(fork, s));                      // allocations, memsets and the small tables are on the model stream
+        for (int k = 0; k < 2; k++) CUDA_OK(cudaStreamWaitEvent(m->aux_stream[k], fork, 0));
+        const int per = ((n + nchunk - 1) / nchunk + 127) & ~127;
+        int rc_launch = 0;
+        for (int k = 0; k < nchunk && !rc_launch; k++) {
+            const int lo = k * per, cnt = std::min(per, n - lo);
+            if (cnt <= 0) break;
+            cudaStream_t cs = m->aux_stream[k & 1];
+            StateArgs ac = a;
+            ac.n = cnt;
+            ac.tidx = a.tidx + lo; ac.Vm = a.Vm + lo; ac.status = a.status + lo;
+            auto h2d = [&](const double* host, const double* dev, size_t per_pt) {
+                return cudaMemcpyAsync(const_cast<double*>(dev) + (size_t) lo * per_pt, host + (size_t) lo * per_pt, (size_t) cnt * per_pt * sizeof(double), cudaMemcpyHostToDevice, cs);
+            };
+            CUDA_OK(cudaMemcpyAsync(const_cast<int*>(ac.tidx), tidx.data() + lo, cnt * sizeof(int), cudaMemcpyHostToDevice, cs));
+            CUDA_OK(h2d(Vm, a.Vm, 1));
+            if (a.x) { CUDA_OK(h2d(x, a.x, nc)); ac.x = a.x + (size_t) lo * nc; }
+            if (a.dmudn) { CUDA_OK(h2d(eos->dmudn, a.dmudn, (size_t) nce * nce)); ac.dmudn = a.dmudn + (size_t) lo * nce * nce; }
+            if (a.cp_ideal) { CUDA_OK(h2d(eos->cp_ideal, a.cp_ideal, nce)); ac.cp_ideal = a.cp_ideal + (size_t) lo * nce; }
+            if (a.dvdn) { CUDA_OK(h2d(eos->dvdn, a.dvdn, nce)); ac.dvdn = a.dvdn + (size_t) lo * nce; }
+            double* rdf_c = d_rdf ? d_rdf + (size_t) lo * a.nslots * nc * nc : nullptr;
+            ac.rdf = rdf_c;
+            double** outs[] = {&ac.viscosity, &ac.conductivity, &ac.contribs, &ac.D, &ac.DT, &ac.kT, &ac.soret, &ac.K, &ac.Kp, &ac.cond_matrix, &ac.cond_vector,
+                               &ac.visc_matrix, &ac.visc_vector};
+            const size_t per_pt[] = {1, 1, 3, (size_t) nD * nD, (size_t) nc, (size_t) nc, (size_t) nc, (size_t) nc, (size_t) nc, (size_t) nn * nn, (size_t) nn,
+                                     (size_t) nn * nn, (size_t) nn};
+            for (int q = 0; q < 13; q++) if (*outs[q]) *outs[q] += (size_t) lo * per_pt[q];
+            CUDA_OK(cudaEventRecord(kev[2 * k], cs));
+            rc_launch = launch_state(c, ac, cs, ac.x, rdf_c);
+            CUDA_OK(cudaEventRecord(kev[2 * k + 1], cs));
+            int q = 0;
+            for (auto& mp : maps) { if (mp.host) CUDA_OK(cudaMemcpyAsync(mp.host + (size_t) lo * per_pt[q], *outs[q], (size_t) cnt * per_pt[q] * sizeof(double), cudaMemcpyDeviceToHost, cs)); q++; }
+            if (out->rdf && !opts->is_idealgas)
+                CUDA_OK(cudaMemcpy2DAsync(out->rdf + (size_t) lo * nc * nc, (size_t) nc * nc * sizeof(double), rdf_c, (size_t) a.nslots * nc * nc * sizeof(double),
+                                          (size_t) nc * nc * sizeof(double), cnt, cudaMemcpyDeviceToHost, cs));
+            CUDA_OK(cudaMemcpyAsync(st.data() + lo, ac.status, cnt * sizeof(int), cudaMemcpyDeviceToHost, cs));
+        }
+        for (int k = 0; k < 2; k++) { CUDA_OK(cudaEventRecord(m->aux_done[k], m->aux_stream[k])); CUDA_OK(cudaStreamWaitEvent(s, m->aux_done[k], 0)); }
+        CUDA_OK(cudaStreamSynchronize(s));
+        for (int k = 0; k < nchunk; k++) { float t = 0; if (cudaEventElapsedTime(&t, kev[2 * k], kev[2 * k + 1]) == cudaSuccess) kms += t; }
+        cudaGetLastError();
+        cudaEventDestroy(fork);
+        for (auto& e : kev) cudaEventDestroy(e);
+        if (rc_launch) { set_error("kg_transport_batch: kernel launch failed (" + m->err + ")"); return -2; }
+    }
+    if (out->rdf && opts->is_idealgas) for (size_t k = 0; k < (size_t) n * nc * nc; k++) out->rdf[k] = 1.0;
+    m->timings[0] = kms; m->timings[5] = (opts->is_idealgas ? 1 : 2) * nchunk;
     if (status) for (int k = 0; k < n; k++) status[k] = st[k];
     return 0;
 }

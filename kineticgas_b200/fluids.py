@@ -9,6 +9,11 @@ BOLTZMANN = 1.38064852e-23           # reference: cpp/global_params.h:4
 GAS_CONSTANT = 8.31446261815324      # cpp/global_params.h:5
 AVOGADRO = GAS_CONSTANT / BOLTZMANN  # cpp/global_params.h:6
 PI_REF = 3.14159265359               # cpp/global_params.h:7 (truncated on purpose: parity)
+# pykingas forms the constructor arguments of the C++ core with scipy.constants (CODATA 2018): eps = eps_div_k * Boltzmann
+# (pykingas/MieType.py:214), m = Mw 1e-3 / Avogadro (pykingas/py_KineticGas.py:61) -- while the core itself uses the 2014 values
+# above. The host mirror does the same, so that its numbers are pykingas' numbers (upstream's golden CSVs to 1e-13).
+BOLTZMANN_PY = 1.380649e-23
+AVOGADRO_PY = 6.02214076e23
 PLANCK = 6.62607015e-34
 HBAR = PLANCK / (2.0 * PI_REF)
 

@@ -13,7 +13,7 @@ import numpy as np
 from . import _lib
 from ._lib import dp, ip
 from .model import DeviceModel, mie_desc, raise_on_status
-from .fluids import MIE, BOLTZMANN, AVOGADRO
+from .fluids import MIE, BOLTZMANN, AVOGADRO, BOLTZMANN_PY, AVOGADRO_PY
 
 FLT_EPS = 1e-12
 FRAMES = {"CoM": 0, "CoN": 1, "CoV": 2, "solvent": 3, "zarate": 4, "zarate_x": 5, "zarate_w": 6}      # cpp/utils.h:37-45, KineticGas::frame_of_reference_map
@@ -104,13 +104,13 @@ class MieKinGas:
             return np.array([db[i] if given[i] is None else given[i] for i in range(self.ncomps)], float)
 
         Mw, sig, epsk, la_, lr_ = (pick(v, k) for k, v in enumerate((mole_weights, sigma, eps_div_k, la, lr)))
-        self.mole_weights = Mw * 1e-3 / AVOGADRO
+        self.mole_weights = Mw * 1e-3 / AVOGADRO_PY            # pykingas/py_KineticGas.py:61 (scipy's Avogadro)
         self.m = self.mole_weights.copy()
         nc = self.ncomps
         off = np.ones((nc, nc)) - np.identity(nc)
         # mixing rules: pykingas/MieType.py:201-249
         self.sigma_ij = (np.ones((nc, nc)) - lij * off) * 0.5 * (sig[None, :] + sig[:, None])
-        eps = epsk * BOLTZMANN
+        eps = epsk * BOLTZMANN_PY                               # pykingas/MieType.py:214 (scipy's Boltzmann)
         self.epsilon_ij = (np.ones((nc, nc)) - kij * off) * np.sqrt(eps[None, :] * eps[:, None])
         self.la = 3 + (1 - lij) * np.sqrt((la_[None, :] - 3) * (la_[:, None] - 3))
         self.lr = 3 + (1 - lij) * np.sqrt((lr_[None, :] - 3) * (lr_[:, None] - 3))
@@ -213,7 +213,8 @@ class MieKinGas:
         shapes = {"viscosity": (n,), "conductivity": (n,), "conductivity_contribs": (n, 3), "D": (n, nD, nD), "DT": (n, nc),
                   "rdf": (n, nc, nc), "K": (n, nc), "K_prime": (n, nc), "cond_matrix": (n, nn, nn), "cond_vector": (n, nn),
                   "visc_matrix": (n, nn, nn), "visc_vector": (n, nn), "thermal_diffusion_ratio": (n, nc), "soret_zarate": (n, nc)}
-        bufs = {k: np.zeros(shapes[k]) for k in want}
+        # large batches: results land in page-locked arrays (asynchronous D2H, overlapped chunk by chunk with the kernels)
+        bufs = {k: (_lib.pinned_empty(shapes[k]) if n >= 32768 else np.zeros(shapes[k])) for k in want}
         out = TransportOut()
         for k, b in bufs.items():
             setattr(out, k, _ptr(b))

@@ -19,7 +19,7 @@ def chi_w_golden():
     cases = [("AR", 300.0), ("AR", 60.0), ("CO2", 250.0), ("LJF", 40.0), ("LJF", 25.0), ("H2", 15.0)]
     for comp, T in cases:
         ids, Mw, s, e, la, lr = mie_parameters(comp)
-        m = ref.RefMie(Mw, s, e, la, lr, is_idealgas=True)
+        m = ref.RefMie(Mw, s, e, la, lr, is_idealgas=True, py_constants=False)
         m.set_omega_correlation_active(False)
         g = np.concatenate([rng.uniform(0.01, 8, 60), [1e-7, 0.25, 3.0]])
         b = np.concatenate([rng.uniform(0.002, 5, 60), [0.7, 1e-7, 2.0]])
@@ -32,7 +32,7 @@ def chi_w_golden():
               ("LJF", 45.0, [(2, 2)]), ("LJF", 30.0, [(1, 1)])]
     for comp, T, lrs in wcases:
         ids, Mw, s, e, la, lr = mie_parameters(comp)
-        m = ref.RefMie(Mw, s, e, la, lr, is_idealgas=True)
+        m = ref.RefMie(Mw, s, e, la, lr, is_idealgas=True, py_constants=False)
         m.set_omega_correlation_active(False)
         for (l, r) in lrs:
             out[f"W_{comp}_{T:g}_{l}_{r}"] = np.array([m.w_integral(0, 0, T, l, r), m.omega(0, 0, l, r, T)])
@@ -361,12 +361,12 @@ def _regime_worker(task):
     t0 = time.time()
     if kind == "mie":
         ids, Mw, s, e, la, lr = mie_parameters(comp)
-        m = ref.RefMie(Mw, s, e, la, lr, is_idealgas=True)
+        m = ref.RefMie(Mw, s, e, la, lr, is_idealgas=True, py_constants=False)
         m.set_omega_correlation_active(False)
     else:
         from kineticgas_b200.fluids import MIE, MIE_FH
         sig, epsk, la, lr = MIE_FH[(comp, 1)]
-        m = ref.RefQuantumMie([MIE[comp][0]], [sig], [epsk], [la], [lr], 1, is_idealgas=True)
+        m = ref.RefQuantumMie([MIE[comp][0]], [sig], [epsk], [la], [lr], 1, is_idealgas=True, py_constants=False)
     val = m.omega(0, 0, l, r, T)
     return {"kind": kind, "comp": comp, "T": T, "l": l, "r": r, "omega": val, "cpu_s": time.time() - t0}
 

@@ -7,8 +7,13 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
-BOLTZMANN = 1.38064852e-23
-AVOGADRO = 8.31446261815324 / BOLTZMANN
+BOLTZMANN = 1.38064852e-23                  # cpp/global_params.h:4 (CODATA 2014), what the C++ core computes with
+AVOGADRO = 8.31446261815324 / BOLTZMANN     # cpp/global_params.h:6
+# pykingas builds its constructor arguments with scipy.constants (CODATA 2018, exact): eps = eps_div_k * Boltzmann
+# (pykingas/MieType.py:214), m = Mw 1e-3 / Avogadro (pykingas/py_KineticGas.py:61). The C++ core then forms T* = kT / eps with ITS
+# Boltzmann constant, so T* is off by 3.5e-7 relative -- which every number pykingas returns (and upstream's golden CSVs) carries.
+BOLTZMANN_PY = 1.380649e-23
+AVOGADRO_PY = 6.02214076e23
 
 dp = C.POINTER(C.c_double)
 ip = C.POINTER(C.c_int)
@@ -131,15 +136,16 @@ class RefMie:
     """The reference's MieKinGas built through its vector constructor (cpp/MieKinGas.cpp:14-17), parameters mixed
     the way pykingas/MieType.py:201-260 does (kij = lij = 0)."""
 
-    def __init__(self, Mw, sigma, eps_div_k, la, lr, is_idealgas=False):
+    def __init__(self, Mw, sigma, eps_div_k, la, lr, is_idealgas=False, py_constants=True):
         single = len(Mw) == 1
         if single:
             Mw, sigma, eps_div_k, la, lr = [list(v) * 2 for v in (Mw, sigma, eps_div_k, la, lr)]
         self.nc = len(Mw)
         self.single = single
-        self.m = np.array(Mw, float) * 1e-3 / AVOGADRO
+        kB, NA = (BOLTZMANN_PY, AVOGADRO_PY) if py_constants else (BOLTZMANN, AVOGADRO)
+        self.m = np.array(Mw, float) * 1e-3 / NA
         s = np.array(sigma, float)
-        e = np.array(eps_div_k, float) * BOLTZMANN
+        e = np.array(eps_div_k, float) * kB
         self.sigma = 0.5 * (s[:, None] + s[None, :])
         self.eps = np.sqrt(e[None, :] * e[:, None])
         la_, lr_ = np.array(la, float), np.array(lr, float)
@@ -306,15 +312,16 @@ class RefQuantumMie(RefMie):
     pykingas/MieType.py (kij = lij = 0). Every call that needs the T-dependent coefficients first calls set_internals,
     as the reference's public property methods do."""
 
-    def __init__(self, Mw, sigma, eps_div_k, la, lr, fh_order, is_idealgas=True):
+    def __init__(self, Mw, sigma, eps_div_k, la, lr, fh_order, is_idealgas=True, py_constants=True):
         single = len(Mw) == 1
         if single:
             Mw, sigma, eps_div_k, la, lr = [list(v) * 2 for v in (Mw, sigma, eps_div_k, la, lr)]
         self.nc = len(Mw)
         self.single = single
-        self.m = np.array(Mw, float) * 1e-3 / AVOGADRO
+        kB, NA = (BOLTZMANN_PY, AVOGADRO_PY) if py_constants else (BOLTZMANN, AVOGADRO)
+        self.m = np.array(Mw, float) * 1e-3 / NA
         s = np.array(sigma, float)
-        e = np.array(eps_div_k, float) * BOLTZMANN
+        e = np.array(eps_div_k, float) * kB
         self.sigma = np.ascontiguousarray(0.5 * (s[:, None] + s[None, :]))
         self.eps = np.ascontiguousarray(np.sqrt(e[None, :] * e[:, None]))
         la_, lr_ = np.array(la, float), np.array(lr, float)

