@@ -25,15 +25,12 @@ sys.path.insert(0, ROOT)
 
 NT_PER_GPU = 4096
 LR = [(l, r) for l in range(1, 5) for r in range(l, 5)]
-# FP64-pipe instructions (DFMA / DMUL / DADD / DSETP, one per lane) per unit of work of the 2-term kernels, counted in the SASS
-# (profiles/r2_theta_sass.md) and checked against ncu's smsp__sass_thread_inst_executed_op_* sums of the same launches:
-FP64_PER_NODE = 8.0          # coarse node of the strided sum: 3 DFMA (radicand) + DMUL, DFMA (Newton step) + DMUL (weight) + DFMA (sum),
-                             # + 4 per block of four (running-sum FMA, stop threshold, two even-node FMAs)
-FP64_PER_INTEGRAL = 420.0    # per theta integral: first node (12), 13 fine end nodes (104), two 7-point difference sets (78), closing
-                             # formulas (40), continuation of the reference's loop to the stop (~18 nodes: 2 fast blocks + 2 exact blocks, ~190)
-FP64_PER_REDO_NODE = 14.0    # node-by-node sums: exact node form (12) + scan
-FP64_PER_SETUP = 330.0       # root finding per work entry (~22 potential evaluations x 15)
-FP64_PER_CELL = 330.0        # mesh cell: ten (l,r) members x ~33 (integrand values, second differences, triangle sums)
+# FP64-pipe lane instructions (DFMA + DMUL + DADD, predicated-on threads) per unit of work, calibrated on ncu's
+# smsp__sass_thread_inst_executed_op_{dfma,dmul,dadd}_pred_on sums of full-size launches of this build (profiles/r2_fp64_calibration.md):
+FP64_PER_NODE = 9.07         # theta_kernel<2>: 3.20e10 lane instructions of the largest launch / its 3.53e9 executed node evaluations (all-in:
+                             # coarse nodes 8.0 each, end nodes, difference formulas, continuation to the stop, node-by-node tier)
+FP64_PER_SETUP = 330.0       # theta_setup_kernel<2>: root finding per work entry (~22 potential evaluations x 15)
+FP64_PER_CELL = 240.0        # mesh_level_kernel, leaf level: 6.05e9 lane instructions / 25.2 M cells (ten (l,r) members x 24)
 F_NODE = 98.0    # nominal FP64 flop per tanh-sinh node for a 2-term (Mie/LJ) potential, SURVEY.md 8(d): 52 + 23 n_terms
 METRIC = "collision integrals/s"
 
@@ -633,7 +630,7 @@ def main():
         import __graft_entry__ as ge
         # FP64-pipe instructions issued per executed node evaluation, per theta integral and per root finding, counted in the SASS of
         # this build (profiles/r2_theta_sass.md) and cross-checked against ncu's smsp__sass_thread_inst_executed_op_{dfma,dmul,dadd}
-        fp64_theta = exec_nodes * FP64_PER_NODE + n_theta * FP64_PER_INTEGRAL + redo * FP64_PER_REDO_NODE * 2000.0
+        fp64_theta = exec_nodes * FP64_PER_NODE
         fp64_setup = n_theta * FP64_PER_SETUP
         issue_peak = peak_tflops * 1e12 / 2.0            # FP64 lane instructions per second (a DFMA counts 2 flop)
         theta_s = theta_ms * 1e-3
@@ -649,10 +646,10 @@ def main():
                             "frac": (fp64_theta + fp64_setup) / theta_s / issue_peak if theta_ms > 0 else None,
                             "frac_step": (fp64_theta + fp64_setup + mesh_cells * FP64_PER_CELL) / (ms * 1e-3) / issue_peak,
                             "traffic": None,
-                            "definition": "frac = FP64-pipe lane instructions executed by the two theta kernels (device counters: node evaluations incl. rejected "
-                                          "attempts, integrals, node-by-node sums; x per-unit instruction counts from the SASS) / (peak/2 x their summed "
-                                          "duration); `achieved` prices every such instruction as one DFMA (2 flop). frac_step = the same plus the mesh "
-                                          "kernel's FP64 instructions over the whole step time",
+                            "definition": "frac = FP64-pipe lane instructions executed by the two theta kernels (device counters of node evaluations, incl. "
+                                          "rejected attempts and node-by-node sums, and of root findings, x the per-unit instruction counts calibrated with "
+                                          "ncu) / (peak/2 x their summed duration); `achieved` prices every such instruction as one DFMA (2 flop). "
+                                          "frac_step = the same plus the mesh kernel's FP64 instructions over the whole step time",
                             "peak_source": "kg_measure_fp64_peak: DFMA chain measured in this run (MEASURED_PEAKS.json has no FP64 figure; "
                                            "datasheet 37 TFLOP/s)",
                             "algorithmic_equivalent_tflops": algo_tflops,
@@ -663,7 +660,7 @@ def main():
                             "executed": {"node_evaluations_per_step": exec_nodes / args.steps, "fraction_of_reference_nodes": exec_nodes / nodes if nodes else None,
                                          "theta_integrals_per_step": n_theta / args.steps, "second_tier_stride8_per_step": tier2 / args.steps,
                                          "summed_node_by_node_per_step": redo / args.steps,
-                                         "fp64_instr_per_node_evaluation": FP64_PER_NODE, "fp64_instr_per_integral_overhead": FP64_PER_INTEGRAL,
+                                         "fp64_instr_per_node_evaluation": FP64_PER_NODE,
                                          "fp64_instr_per_root_finding": FP64_PER_SETUP, "fp64_instr_per_mesh_cell": FP64_PER_CELL,
                                          "mesh_cells_per_step": mesh_cells / args.steps}}}
         if cfg0 is not None:

@@ -1386,7 +1386,13 @@ extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const do
     struct Guard { kg_tcache* c; bool own; ~Guard() { if (own) kg_tcache_destroy(c); } } guard{c, own};
     cudaStream_t s = m->stream;
     std::vector<int> tidx(n);
-    for (int k = 0; k < n; k++) { auto f = c->index_of.find(T[k]); tidx[k] = (f == c->index_of.end()) ? -1 : f->second; }
+    {   // state points usually come in runs of equal temperature: one map look-up per run
+        double lastT = std::nan(""); int lastI = -1;
+        for (int k = 0; k < n; k++) {
+            if (T[k] != lastT) { auto f = c->index_of.find(T[k]); lastI = (f == c->index_of.end()) ? -1 : f->second; lastT = T[k]; }
+            tidx[k] = lastI;
+        }
+    }
     DevBuf db(m);
     StateArgs a; memset(&a, 0, sizeof(a));
     a.n = n; a.nT = c->nT; a.opt = *opts; a.opt.properties = props;
