@@ -29,7 +29,7 @@ LR = [(l, r) for l in range(1, 5) for r in range(l, 5)]
 # smsp__sass_thread_inst_executed_op_{dfma,dmul,dadd}_pred_on sums of full-size launches of this build (profiles/r2_fp64_calibration.md):
 FP64_PER_NODE = 9.07         # theta_kernel<2>: 3.20e10 lane instructions of the largest launch / its 3.53e9 executed node evaluations (all-in:
                              # coarse nodes 8.0 each, end nodes, difference formulas, continuation to the stop, node-by-node tier)
-FP64_PER_SETUP = 330.0       # theta_setup_kernel<2>: root finding per work entry (~22 potential evaluations x 15)
+FP64_PER_SETUP = 390.0       # theta_setup_kernel<2>: 7.47e9 lane instructions of the largest launch / its 19.16 M work entries (root finding)
 FP64_PER_CELL = 240.0        # mesh_level_kernel, leaf level: 6.05e9 lane instructions / 25.2 M cells (ten (l,r) members x 24)
 F_NODE = 98.0    # nominal FP64 flop per tanh-sinh node for a 2-term (Mie/LJ) potential, SURVEY.md 8(d): 52 + 23 n_terms
 METRIC = "collision integrals/s"
@@ -228,6 +228,7 @@ def run_state_points(local_rank, rank, world, n_gpus, steps):
     res = None
     for step in range(steps + 1):                 # first pass is the warm-up
         kin._caches = {}
+        res = None                                # results of the previous step are consumed: their page-locked blocks return to the pool
         t0 = time.perf_counter()
         cache = kin.tcache(T, SP_N, props)
         t1 = time.perf_counter()
@@ -238,7 +239,7 @@ def run_state_points(local_rank, rank, world, n_gpus, steps):
             out["ms"].append(1e3 * (t2 - t0)); out["ms_tables"].append(1e3 * (t1 - t0)); out["ms_state_kernels"].append(tm["ms_state_kernels"])
             out["launches"] += int(tm["launches_tcache"] + tm["launches_batch"])
     out["n"] = int(T.size)
-    out["stage_ms"] = {k: tm[k] for k in ("ms_omega_stage", "ms_tl_stage", "ms_bracket_stage", "ms_state_kernels")}
+    out["stage_ms"] = {k: tm[k] for k in ("ms_omega_stage", "ms_tl_stage", "ms_bracket_stage", "ms_state_kernels", "ms_batch_call")}
     out["h2d"] = int(T.nbytes + Vm.nbytes + x.nbytes + eos["dmudn"].nbytes)
     out["d2h"] = int(res["D"].nbytes + res["DT"].nbytes + 4 * T.size)
     out["finite"] = bool(np.isfinite(res["D"]).all() and np.isfinite(res["DT"]).all())
@@ -304,6 +305,7 @@ def run_five_comp(local_rank, rank, n_gpus, steps):
     res = None
     for step in range(steps + 1):
         kin._caches = {}
+        res = None                                # results of the previous step are consumed: their page-locked blocks return to the pool
         t0 = time.perf_counter()
         cache = kin.tcache(T, FC_N)
         t1 = time.perf_counter()
@@ -313,11 +315,93 @@ def run_five_comp(local_rank, rank, n_gpus, steps):
             out["ms"].append(1e3 * (t2 - t0)); out["ms_tables"].append(1e3 * (t1 - t0))
     tm = kin.dev.last_timings()
     out["n"] = int(T.size)
-    out["stage_ms"] = {k: tm[k] for k in ("ms_omega_stage", "ms_tl_stage", "ms_bracket_stage", "ms_state_kernels")}
+    out["stage_ms"] = {k: tm[k] for k in ("ms_omega_stage", "ms_tl_stage", "ms_bracket_stage", "ms_state_kernels", "ms_batch_call")}
     out["h2d"] = int(T.nbytes + Vm.nbytes + x.nbytes + eos["dmudn"].nbytes + eos["cp_ideal"].nbytes)
     out["d2h"] = int(sum(res[k].nbytes for k in ("viscosity", "conductivity", "conductivity_contribs", "D", "DT")) + 4 * T.size)
     out["finite"] = bool(all(np.isfinite(res[k]).all() for k in ("viscosity", "conductivity", "D", "DT")))
     return out
+
+
+# ------------------------------------------------------------------------------------------------ strong scaling (fixed total work)
+def _rank_values(v, world):
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([float(v)], dtype=torch.float64, device="cuda")
+    if world == 1:
+        return [float(v)]
+    out = [torch.zeros_like(t) for _ in range(world)]
+    dist.all_gather(out, t)
+    return [float(o.item()) for o in out]
+
+
+def run_strong_omega(model, rank, world, steps, barrier):
+    """configs[1] as BASELINE.json states it: ONE 4096-point T* grid, dealt over the ranks by kineticgas_b200.sharding (cost-balanced),
+    every rank ends up with the full Omega table. Fixed total work: strong scaling."""
+    import torch
+    from kineticgas_b200 import sharding
+    T1 = grid(1, 0)
+    deal = sharding.TemperatureDeal(T1, world, device="cuda")
+    Tl = deal.local(rank)
+    ls = np.array([l for l, r in LR], np.int32)
+    rs = np.array([r for l, r in LR], np.int32)
+    plan = model.omega_plan(Tl, ls, rs)
+    loc = torch.empty((Tl.size, len(LR)), dtype=torch.float64, device="cuda")
+
+    def share(_):
+        plan.run(sync=False)
+        plan.export_dev(loc.data_ptr())
+        return loc
+
+    for _ in range(3):
+        sharding.sharded_temperature_tables(share, T1, rank, world, device="cuda", deal=deal)
+    barrier()
+    stream = torch.cuda.current_stream()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    th = 0.0
+    for _ in range(steps):
+        full = sharding.sharded_temperature_tables(share, T1, rank, world, device="cuda", deal=deal)
+        th += plan.counters()["ms_theta"]
+    e1.record(stream)
+    barrier()
+    ms = max(_rank_values(e0.elapsed_time(e1), world)) / steps
+    th_ranks = [v / steps for v in _rank_values(th, world)]
+    plan.close()
+    return {"workload": "configs[1], ONE 4096-point grid x 10 (l,r) dealt over the ranks (strong scaling)", "value": T1.size * len(LR) / (ms * 1e-3),
+            "unit": "Omega/s", "ms_per_step": ms, "theta_ms_per_rank": th_ranks,
+            "imbalance_max_over_mean_theta_ms": max(th_ranks) / (sum(th_ranks) / len(th_ranks)),
+            "modelled_cost_max_over_mean": float(deal.modelled_cost.max() / deal.modelled_cost.mean()), "all_finite": bool(torch.isfinite(full).all().item())}
+
+
+def run_strong_five(local_rank, rank, world, steps, barrier):
+    """configs[4] as BASELINE.json states it: 10^5 state points IN TOTAL, contiguous blocks over the ranks (kineticgas_b200.sharding.
+    sharded_state_points), each rank builds the device tables of the temperatures in its block, the results (eta, lambda, D 4x4, D_T) are
+    all-gathered. Host buffers in, gathered device table out."""
+    import torch
+    from kineticgas_b200 import MieKinGas, pinned_copy, sharding
+    kin = MieKinGas(FC_COMPS, N=FC_N, is_idealgas=False, device=local_rank)
+    T, Vm, x = fc_grid(1, 0)
+    T, Vm, x = pinned_copy(T), pinned_copy(Vm), pinned_copy(x)
+    dm, cp = pinned_copy(sp_eos(T, Vm, x)), pinned_copy(np.full((T.size, 5), 4.5 * R_GAS))
+    n = int(T.size)
+
+    def block(lo, hi):
+        kin._caches = {}
+        r = kin.transport_batch(T[lo:hi], Vm[lo:hi], x[lo:hi], N=FC_N, eos_inputs={"dmudn": dm[lo:hi], "cp_ideal": cp[lo:hi]})
+        packed = np.concatenate([r["viscosity"][:, None], r["conductivity"][:, None], r["D"].reshape(hi - lo, -1), r["DT"]], axis=1)
+        return torch.from_numpy(np.ascontiguousarray(packed)).cuda()
+
+    out = sharding.sharded_state_points(block, n, rank, world, device="cuda")     # warm-up
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        out = sharding.sharded_state_points(block, n, rank, world, device="cuda")
+    torch.cuda.synchronize()
+    barrier()
+    ms = max(_rank_values(1e3 * (time.perf_counter() - t0), world)) / steps
+    return {"workload": f"configs[4], {n} state points IN TOTAL in contiguous blocks over the ranks (strong scaling), tables of each block's "
+                        "temperatures rebuilt every step, results all-gathered", "value": n / (ms * 1e-3), "unit": "state points/s",
+            "ms_per_step": ms, "all_finite": bool(torch.isfinite(out).all().item())}
 
 
 # ------------------------------------------------------------------------------------------------ parity + configs[0]
@@ -484,7 +568,8 @@ def main():
     config = {"workload": "configs[1]: LJF (Mie 12-6) Omega(l,r), 1<=l<=r<=4, 4096-point T* grid 0.3-100 (T = 30 T* K) per GPU",
               "n_T_per_gpu": NT_PER_GPU, "n_lr": len(LR), "omega_per_step": NT_PER_GPU * len(LR) * n_gpus,
               "l2": "working set (cos(chi) lattices + masks, ~0.5 GB per GPU) is rebuilt every step and exceeds the 126 MB L2",
-              "sharding": "T grid interleaved over ranks, no data-path collective; one all_gather of the Omega tables per step"}
+              "sharding": "kineticgas_b200.sharding: T grid dealt cost-balanced over ranks (equal counts per lattice regime), no data-path "
+                          "collective; one all_gather of the Omega tables per step puts the full table on every rank"}
     cores = host_cores()
 
     if args.impl == "reference":
@@ -516,19 +601,28 @@ def main():
     model = DeviceModel([mie_desc(s, e * KB, la, lr)], [Mw * 1e-3 / NA], True, device=local_rank)
     stream = torch.cuda.current_stream()
     model.set_stream(stream.cuda_stream)
-    T = grid(n_gpus, rank)
+    # The multi-GPU path is the product's own sharding layer (kineticgas_b200/sharding.py): the temperatures of the N-times denser grid
+    # are dealt cost-balanced over the ranks (every rank gets the same number of points of every lattice regime), each rank integrates
+    # its share, one all_gather puts the table together in grid order on every rank.
+    from kineticgas_b200 import sharding
+    T_all = np.sort(np.concatenate([grid(world, k) for k in range(world)]))
+    deal = sharding.TemperatureDeal(T_all, world, device="cuda")
+    T = deal.local(rank)
     ls = np.array([l for l, r in LR], np.int32)
     rs = np.array([r for l, r in LR], np.int32)
     plan = model.omega_plan(T, ls, rs)
     n_out = T.size * len(LR)
-    om_local = torch.empty(n_out, dtype=torch.float64, device="cuda")
-    om_all = torch.empty(n_out * world, dtype=torch.float64, device="cuda") if world > 1 else None
+    om_local = torch.empty((T.size, len(LR)), dtype=torch.float64, device="cuda")
+    om_all = None
 
-    def step():
+    def compute_share(_T_local):
         plan.run(sync=False)
         plan.export_dev(om_local.data_ptr())
-        if world > 1:
-            dist.all_gather_into_tensor(om_all, om_local)
+        return om_local
+
+    def step():
+        nonlocal om_all
+        om_all = sharding.sharded_temperature_tables(compute_share, T_all, rank, world, device="cuda", deal=deal)
 
     def barrier():
         if world > 1:
@@ -561,7 +655,8 @@ def main():
     if world > 1:
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
     ms = float(tmax.item())
-    value = n_out * world * args.steps / (ms * 1e-3)
+    n_total = T_all.size * len(LR)
+    value = n_total * args.steps / (ms * 1e-3)
 
     # end to end through the public host-buffer call: plan creation (H2D of the work description), kernels, D2H of the tables
     for _ in range(max(args.warmup, 3)):          # untimed warm-up of this path too (first plan of this size grows the device pool)
@@ -582,14 +677,14 @@ def main():
         h2d, d2h = int(cc["h2d_bytes"]) + T.nbytes, int(cc["d2h_bytes"])
         p2.close()
         if world > 1:
-            dist.all_gather_into_tensor(om_all, torch.from_numpy(om_host.ravel()).cuda())
+            deal.gather(torch.from_numpy(om_host.reshape(T.size, len(LR))).cuda(), rank)
     e1.record(stream)
     barrier()
     e2e_ms = max(e0.elapsed_time(e1), 1e3 * (time.perf_counter() - e2e0))
     t2 = torch.tensor([e2e_ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t2, op=dist.ReduceOp.MAX)
-    e2e_value = n_out * world * args.steps / (float(t2.item()) * 1e-3)
+    e2e_value = n_total * args.steps / (float(t2.item()) * 1e-3)
 
     clocks = sampler.stop(wall0, wall1) if sampler else None
 
@@ -624,6 +719,14 @@ def main():
             cfg0 = config0_latency(local_rank)
             if not args.no_cpu_baseline:
                 cfg0["cpu_reference"] = config0_reference()
+
+    strong = None
+    if not args.no_extra_configs and not args.no_state_points and not args.nt:
+        barrier()
+        strong = {"omega": run_strong_omega(model, rank, world, max(1, min(args.steps, 3)), barrier),
+                  "five_component": run_strong_five(local_rank, rank, world, max(1, min(args.steps, 2)), barrier)}
+        barrier()
+    th_ranks = _rank_values(theta_ms / args.steps, world)
 
     if rank == 0:
         from kineticgas_b200 import _lib
@@ -665,6 +768,10 @@ def main():
                                          "mesh_cells_per_step": mesh_cells / args.steps}}}
         if cfg0 is not None:
             out["config0_latency"] = cfg0
+        out["load_balance"] = {"theta_ms_per_rank": th_ranks, "max_over_mean": max(th_ranks) / (sum(th_ranks) / len(th_ranks)),
+                               "modelled_cost_max_over_mean": float(deal.modelled_cost.max() / deal.modelled_cost.mean())}
+        if strong is not None:
+            out["strong_scaling"] = strong
         if sp is not None:
             out["gpu_launches"] = launches + sp["launches"]
             n_sp = sp["n"] * world

@@ -84,6 +84,11 @@ const char* kg_build_info(void);
 void* kg_host_alloc(size_t bytes);
 void kg_host_free(void* p);
 int kg_model_npairs(const kg_model* m);
+/* Declares that the coefficients C[k] of a power-sum model depend on temperature (Feynman-Hibbs Mie: C_eff(T), cpp/ExtendedSutherland.cpp:
+ * 182-200). Afterwards every call that integrates -- kg_omega_batch, kg_omega_plan_create*, kg_transfer_lengths_batch, kg_tcache_create,
+ * kg_chi_points and kg_transport_batch with cache == NULL -- fails with an error unless it is given coeff_T, instead of silently using the
+ * base coefficients. */
+int kg_model_set_temperature_dependent(kg_model* m, int flag);
 /* Run all work of this model on a caller-owned CUDA stream (cudaStream_t passed as void*), e.g. the host framework's
  * current stream, so that the caller's events bracket the kernels. */
 int kg_model_set_stream(kg_model* m, void* cuda_stream);

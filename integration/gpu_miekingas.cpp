@@ -2,6 +2,7 @@
 #include "gpu_miekingas.h"
 #include "kgcuda.h"
 #include <stdexcept>
+#include <algorithm>
 
 namespace {
 int pair_count(int nc) { return nc * (nc + 1) / 2; }
@@ -177,4 +178,37 @@ std::vector<double> GpuMieKinGas::omega_table(const std::vector<double>& T, cons
         }
     }
     return om;
+}
+
+GpuMieKinGas::BatchResult GpuMieKinGas::transport_batch(const std::vector<double>& T, const std::vector<double>& Vm, const std::vector<double>& x,
+                                                        int N, const std::vector<double>& dmudn, const std::vector<double>& cp_ideal) {
+    const int n = (int) T.size(), nc = (int) Ncomps;
+    if ((int) Vm.size() != n || (!is_singlecomp && (int) x.size() != n * nc)) throw std::invalid_argument("transport_batch: array sizes do not match");
+    kg_transport_opts o{};
+    o.N = N; o.is_idealgas = is_idealgas ? 1 : 0; o.omega_correlation_active = omega_correlation_active ? 1 : 0;
+    o.frame_of_reference = KG_FOR_CON; o.dependent_idx = -1; o.solvent_idx = -1; o.do_compress = 1;
+    o.properties = KG_PROP_VISCOSITY | (cp_ideal.empty() ? 0u : KG_PROP_CONDUCTIVITY) | (dmudn.empty() ? 0u : (KG_PROP_DIFFUSION | KG_PROP_THERMAL_DIFFUSION));
+    std::vector<double> Tu(T);
+    std::sort(Tu.begin(), Tu.end());
+    Tu.erase(std::unique(Tu.begin(), Tu.end()), Tu.end());
+    kg_tcache* c = nullptr;
+    if (kg_tcache_create(gpu, &o, (int) Tu.size(), Tu.data(), nullptr, &c)) fail("kg_tcache_create failed");
+    BatchResult res;
+    res.nD = nc - 1;
+    res.viscosity.resize(n);
+    kg_transport_out out{};
+    out.viscosity = res.viscosity.data();
+    kg_eos_inputs eos{};
+    if (!cp_ideal.empty()) { res.conductivity.resize(n); out.conductivity = res.conductivity.data(); eos.cp_ideal = cp_ideal.data(); }
+    if (!dmudn.empty()) {
+        res.D.resize((size_t) n * res.nD * res.nD); res.DT.resize((size_t) n * nc);
+        out.D = res.D.data(); out.DT = res.DT.data(); eos.dmudn = dmudn.data();
+    }
+    std::vector<int32_t> st(n);
+    const int rc = kg_transport_batch(gpu, c, n, T.data(), Vm.data(), is_singlecomp ? nullptr : x.data(), &o, &eos, &out, st.data());
+    kg_tcache_destroy(c);
+    if (rc) fail("kg_transport_batch failed");
+    n_feeds++;
+    for (int s_ : st) if (s_ & KG_STATUS_SINGULAR) throw std::runtime_error("singular Sonine-expansion system");
+    return res;
 }

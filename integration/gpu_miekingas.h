@@ -48,6 +48,12 @@ public:
     // Additive batched entry points (bound as `omega_table` / `transport_batch` in integration/bindings_addon.cpp)
     // omega_table: [nT][npairs][nlr] by quadrature on the device; also feeds the cache.
     std::vector<double> omega_table(const std::vector<double>& T, const std::vector<int>& l, const std::vector<int>& r);
+    // transport_batch: n state points in one device pass (kg_tcache_create on the distinct temperatures + kg_transport_batch).
+    // x is [n][Ncomps] (ignored for single-component models), dmudn [n][nce][nce] and cp_ideal [n][nce] are the EoS-derived inputs
+    // (nce = 1 for single-component models); either may be empty, the properties that need it are then skipped.
+    struct BatchResult { std::vector<double> viscosity, conductivity, D, DT; int nD = 0; };
+    BatchResult transport_batch(const std::vector<double>& T, const std::vector<double>& Vm, const std::vector<double>& x, int N,
+                                const std::vector<double>& dmudn, const std::vector<double>& cp_ideal);
 
     // Test hooks: CPU theta-integrand evaluations (every CPU chi / w_integral / transfer-length quadrature goes through it),
     // device feeds, and values stored into the reference cache.

@@ -38,6 +38,7 @@ struct kg_model {
     std::vector<kg::PairParams> pairs;
     // generic (non-power-law) models: ntpad == 1, node rows { w/2u, 1/u^2, 1/u }
     bool generic = false, gen_T_dependent = false;
+    bool coeff_T_required = false;      // power-sum model whose coefficients depend on T (kg_model_set_temperature_dependent)
     std::vector<kg_potential_desc_ex> gdescs;
     kg::GenPot* d_gpots = nullptr;      // base potentials, one per pair
     int coeff_stride = KG_MAX_TERMS;    // doubles per (T, pair) block of a coefficient pool (GP_DOUBLES for generic models)

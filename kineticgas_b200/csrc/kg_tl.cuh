@@ -212,6 +212,7 @@ extern "C" int kg_transfer_lengths_batch(kg_model* m, int nT, const double* T, c
     if (!m) return -1;
     auto set_error = [&](const std::string& s) { m->err = s; };
     if (nT < 1 || !T || !mtl || !etl) { set_error("kg_transfer_lengths_batch: invalid argument"); return -1; }
+    if (m->coeff_T_required && !coeff_T) { set_error(KG_NEED_COEFF); return -1; }
     CUDA_OK(cudaSetDevice(m->device));
     const int Np = m->npairs, nitems = nT * Np;
     std::vector<double> coeff_buf;

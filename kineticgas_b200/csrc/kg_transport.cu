@@ -158,6 +158,8 @@ struct TModel {                 // per-model constants of the state-point stage
     int npairs_dev;             // pairs of the kg_model (1 for single-component models)
     int is_singlecomp, is_idealgas, N, nlr;
     double m[MAXC];             // particle masses
+    double sqmm[MAXC][MAXC];    // sqrt(m_i m_j)                 (host libm, once per model: the state kernel used to take ~150 pow / sqrt per point)
+    double sqred[MAXC][MAXC];   // sqrt(m_i m_j / (m_i + m_j))
     int pair_of[MAXC][MAXC];    // (i,j) -> pair index in the kg_model's tables
     int lr_l[MAXLR], lr_r[MAXLR];
 };
@@ -264,77 +266,116 @@ struct RdfCommon {      // what every pair of one (state point, density) shares
     double rho, zx, dzx, zxs, KHS, dKHS, k0, k1, k2, k3;
 };
 
-__device__ void rdf_common(int nc, double rho, const double* x, const double* d /*[nc] BH diag*/, const MiePair* mp /*[nc*nc]*/, RdfCommon& c) {
+__device__ __forceinline__ double p2(double x) { return x * x; }
+__device__ __forceinline__ double p3(double x) { return x * x * x; }
+__device__ __forceinline__ double p4(double x) { const double y = x * x; return y * y; }
+
+// Everything of MieKinGas::saft_rdf (cpp/MieKinGas.cpp:157-276, 314-786) that depends on the temperature and the pair only, computed once
+// per (T, i, j) by rdf_T_kernel: the per-state-point kernel used to spend ~280 pow() calls per pair on these.
+struct RdfT {
+    double d3, sig3, x0, eps, la, lr, C;
+    double lam[5];             // la, lr, 2 la, 2 lr, la + lr
+    double ck[5][4];           // zeta_eff coefficients c_k(lam) = sum_j c_Cm[k][j] lam^-j
+    double I[5], J[5];         // I(lam), J(lam) of the B term
+    double xp[5];              // x0^lam
+    double f[3];               // f_i(alpha) of the chi correction
+    double gam0;               // 10 (1 - tanh(10 (0.57 - alpha))) (exp(eps / kT) - 1)
+    double be;                 // eps / kT
+};
+
+__global__ void rdf_T_kernel(int nT, int nc, const double* __restrict__ T, const double* __restrict__ dbh, const MiePair* __restrict__ mp,
+                             RdfT* __restrict__ out) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nT * nc * nc) return;
+    const int j = e % nc, i = (e / nc) % nc, t = e / (nc * nc);
+    const MiePair q = mp[i * nc + j];
+    const double* d = dbh + (size_t) t * nc;
+    const double dij = (i == j) ? d[i] : (d[i] + d[j]) / 2.0;
+    RdfT r;
+    r.d3 = pow(dij, 3); r.sig3 = pow(q.sigma, 3); r.x0 = q.sigma / dij; r.eps = q.eps; r.la = q.la; r.lr = q.lr; r.C = q.C;
+    r.lam[0] = q.la; r.lam[1] = q.lr; r.lam[2] = 2 * q.la; r.lam[3] = 2 * q.lr; r.lam[4] = q.la + q.lr;
+    for (int k = 0; k < 5; k++) {
+        const double lam = r.lam[k];
+        for (int a = 0; a < 4; a++) { double c = 0; for (int b = 0; b < 4; b++) c += c_Cm[a][b] * pow(lam, (double) -b); r.ck[k][a] = c; }
+        r.I[k] = -(pow(r.x0, 3. - lam) - 1.) / (lam - 3.);
+        r.J[k] = -(pow(r.x0, 4. - lam) * (lam - 3.) - pow(r.x0, 3. - lam) * (lam - 4.) - 1.) / ((lam - 3.) * (lam - 4.));
+        r.xp[k] = pow(r.x0, lam);
+    }
+    for (int a = 0; a < 3; a++) {
+        double num = 0.0, den = 1.0;
+        for (int n = 0; n <= 3; n++) num += c_phi[n][a] * pow(q.alpha, (double) n);
+        for (int n = 4; n <= 6; n++) den += c_phi[n][a] * pow(q.alpha, (double) (n - 3));
+        r.f[a] = num / den;
+    }
+    const double theta = exp(q.eps / (BOLTZMANN * T[t])) - 1.;
+    r.gam0 = 10. * (1 - tanh(10. * (0.57 - q.alpha))) * theta;
+    r.be = (1. / (BOLTZMANN * T[t])) * q.eps;
+    out[e] = r;
+}
+
+__device__ void rdf_common(int nc, double rho, const double* x, const RdfT* __restrict__ rt /*[nc*nc] of this T*/, RdfCommon& c) {
     double s = 0, ss = 0;
     for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) {
-        const double dij = (i == j) ? d[i] : (d[i] + d[j]) / 2.0;
-        s += x[i] * x[j] * pow(dij, 3);
-        ss += x[i] * x[j] * pow(mp[i * nc + j].sigma, 3);
+        s += x[i] * x[j] * rt[i * nc + j].d3;
+        ss += x[i] * x[j] * rt[i * nc + j].sig3;
     }
     c.rho = rho;
     c.zx = s * (PI_REF * rho / 6.0);           // zeta_x_func
     c.dzx = s * (PI_REF / 6.0);                // dzetax_drho_func
     c.zxs = ss * (PI_REF * rho / 6.0);         // zeta_x with sigma (rdf_chi_func, gamma_corr)
-    const double z = c.zx;
-    c.KHS = pow(1 - z, 4) / (1 + 4 * z + 4 * pow(z, 2) - 4 * pow(z, 3) + pow(z, 4));
+    const double z = c.zx, z2 = z * z, z3 = z2 * z, z4 = z2 * z2, omz = 1 - z, omz2 = omz * omz, omz3 = omz2 * omz;
+    c.KHS = (omz2 * omz2) / (1 + 4 * z + 4 * z2 - 4 * z3 + z4);
     // sign of the z^4 term differs from K_HS in the reference (cpp/MieKinGas.h:176-179); kept
-    c.dKHS = -4 * c.dzx * pow(1 - z, 3) * (2 + 5 * z - pow(z, 2) - 2 * pow(z, 3)) / pow(1 + 4 * z + 4 * pow(z, 2) - 4 * pow(z, 3) - pow(z, 4), 2);
-    c.k0 = -log(1 - z) + (42. * z - 39. * pow(z, 2) + 9. * pow(z, 3) - 2 * pow(z, 4)) / (6 * pow(1 - z, 3));
-    c.k1 = (pow(z, 4) + 6. * pow(z, 2) - 12. * z) / (2. * pow(1 - z, 3));
-    c.k2 = -3. * pow(z, 2) / (8. * pow(1 - z, 2));
-    c.k3 = (-pow(z, 4.) + 3. * pow(z, 2) + 3. * z) / (6. * pow(1 - z, 3));
+    c.dKHS = -4 * c.dzx * omz3 * (2 + 5 * z - z2 - 2 * z3) / p2(1 + 4 * z + 4 * z2 - 4 * z3 - z4);
+    c.k0 = -log(1 - z) + (42. * z - 39. * z2 + 9. * z3 - 2 * z4) / (6 * omz3);
+    c.k1 = (z4 + 6. * z2 - 12. * z) / (2. * omz3);
+    c.k2 = -3. * z2 / (8. * omz2);
+    c.k3 = (-z4 + 3. * z2 + 3. * z) / (6. * omz3);
 }
 
-// a1s + B and d(a1s + B)/drho for one exponent lambda of one pair
-__device__ void a1s_B(const RdfCommon& c, double eps, double d3, double x0, double lam, double& aB, double& daB) {
-    double ck[4];
-    for (int i = 0; i < 4; i++) { ck[i] = 0; for (int j = 0; j < 4; j++) ck[i] += c_Cm[i][j] * pow(lam, (double) -j); }
-    double ze = 0, dze = 0;
-    for (int i = 0; i < 4; i++) { ze += ck[i] * pow(c.zx, (double) (i + 1)); dze += ck[i] * (i + 1) * pow(c.zx, (double) i) * c.dzx; }
-    const double a1s = (-2. * c.rho * PI_REF * eps * d3 / (lam - 3)) * (1. - ze / 2.) / pow(1. - ze, 3);
-    const double da1s = -2. * (PI_REF * eps * d3 / (lam - 3)) * (((1. - ze / 2.) / pow(1 - ze, 3)) + c.rho * dze * (2.5 - ze) / pow(1 - ze, 4));
-    const double I = -(pow(x0, 3. - lam) - 1.) / (lam - 3.);
-    const double J = -(pow(x0, 4. - lam) * (lam - 3.) - pow(x0, 3. - lam) * (lam - 4.) - 1.) / ((lam - 3.) * (lam - 4.));
-    const double zx = c.zx;
-    const double B = 2. * PI_REF * c.rho * d3 * eps * (I * (1. - zx / 2.) / pow(1. - zx, 3) - J * 9. * zx * (1. + zx) / (2. * pow(1. - zx, 3)));
+// a1s + B and d(a1s + B)/drho for exponent k (lam[k]) of one pair
+__device__ __forceinline__ void a1s_B(const RdfCommon& c, const RdfT& r, int k, double& aB, double& daB) {
+    const double lam = r.lam[k], eps = r.eps, d3 = r.d3, zx = c.zx, zx2 = zx * zx, zx3 = zx2 * zx;
+    const double ze = r.ck[k][0] * zx + r.ck[k][1] * zx2 + r.ck[k][2] * zx3 + r.ck[k][3] * (zx2 * zx2);
+    const double dze = (r.ck[k][0] + r.ck[k][1] * 2 * zx + r.ck[k][2] * 3 * zx2 + r.ck[k][3] * 4 * zx3) * c.dzx;
+    const double omze = 1. - ze, omze3 = p3(omze), omze4 = omze3 * omze;
+    const double a1s = (-2. * c.rho * PI_REF * eps * d3 / (lam - 3)) * (1. - ze / 2.) / omze3;
+    const double da1s = -2. * (PI_REF * eps * d3 / (lam - 3)) * (((1. - ze / 2.) / omze3) + c.rho * dze * (2.5 - ze) / omze4);
+    const double I = r.I[k], J = r.J[k];
+    const double omz = 1. - zx, omz3 = p3(omz), omz4 = omz3 * omz;
+    const double B = 2. * PI_REF * c.rho * d3 * eps * (I * (1. - zx / 2.) / omz3 - J * 9. * zx * (1. + zx) / (2. * omz3));
     const double dB = B / c.rho + 2. * PI_REF * c.rho * eps * d3
-                      * (I * (-0.5 * (1 - zx) + 3. * (1. - 0.5 * zx)) / pow(1 - zx, 4)
-                         - J * (9. * (1. + 2. * zx) * (1. - zx) + 27. * zx * (1. + zx)) / (2. * pow(1 - zx, 4))) * c.dzx;
+                      * (I * (-0.5 * (1 - zx) + 3. * (1. - 0.5 * zx)) / omz4
+                         - J * (9. * (1. + 2. * zx) * (1. - zx) + 27. * zx * (1. + zx)) / (2. * omz4)) * c.dzx;
     aB = a1s + B;
     daB = da1s + dB;
 }
 
-__device__ double rdf_pair(const RdfCommon& c, const MiePair& q, double dij, double T) {
-    const double x0 = q.sigma / dij, d3 = pow(dij, 3), eps = q.eps, la = q.la, lr = q.lr, C = q.C, rho = c.rho;
-    const double gHS = exp(c.k0 + c.k1 * x0 + c.k2 * pow(x0, 2) + c.k3 * pow(x0, 3));
+__device__ double rdf_pair(const RdfCommon& c, const RdfT& r) {
+    const double x0 = r.x0, d3 = r.d3, eps = r.eps, la = r.la, lr = r.lr, C = r.C, rho = c.rho;
+    const double gHS = exp(c.k0 + c.k1 * x0 + c.k2 * (x0 * x0) + c.k3 * (x0 * x0 * x0));
     double aB_la, daB_la, aB_lr, daB_lr, aB_2la, daB_2la, aB_2lr, daB_2lr, aB_lalr, daB_lalr;
-    a1s_B(c, eps, d3, x0, la, aB_la, daB_la);
-    a1s_B(c, eps, d3, x0, lr, aB_lr, daB_lr);
-    a1s_B(c, eps, d3, x0, 2 * la, aB_2la, daB_2la);
-    a1s_B(c, eps, d3, x0, 2 * lr, aB_2lr, daB_2lr);
-    a1s_B(c, eps, d3, x0, la + lr, aB_lalr, daB_lalr);
-    const double x_la = pow(x0, la), x_lr = pow(x0, lr), x_2la = pow(x0, 2 * la), x_2lr = pow(x0, 2 * lr), x_lalr = pow(x0, la + lr);
+    a1s_B(c, r, 0, aB_la, daB_la);
+    a1s_B(c, r, 1, aB_lr, daB_lr);
+    a1s_B(c, r, 2, aB_2la, daB_2la);
+    a1s_B(c, r, 3, aB_2lr, daB_2lr);
+    a1s_B(c, r, 4, aB_lalr, daB_lalr);
+    const double x_la = r.xp[0], x_lr = r.xp[1], x_2la = r.xp[2], x_2lr = r.xp[3], x_lalr = r.xp[4];
     // g1 (rdf_g1_func)
     const double da1 = C * (x_la * daB_la - x_lr * daB_lr);
     const double g1 = (1.0 / (2. * PI_REF * eps * d3)) * (3. * da1 - C * la * x_la * aB_la / rho + C * lr * x_lr * aB_lr / rho);
     // g2 (rdf_g2_func with g2_correction = true)
-    double f[3];
-    for (int i = 0; i < 3; i++) {
-        double num = 0.0, den = 1.0;
-        for (int n = 0; n <= 3; n++) num += c_phi[n][i] * pow(q.alpha, (double) n);
-        for (int n = 4; n <= 6; n++) den += c_phi[n][i] * pow(q.alpha, (double) (n - 3));
-        f[i] = num / den;
-    }
-    const double chi = f[0] * c.zxs + f[1] * pow(c.zxs, 5) + f[2] * pow(c.zxs, 8);
-    const double a2 = .5 * c.KHS * (1 + chi) * eps * pow(C, 2) * (x_2la * aB_2la - 2 * x_lalr * aB_lalr + x_2lr * aB_2lr);
+    const double zs = c.zxs, zs2 = zs * zs, zs4 = zs2 * zs2;
+    const double chi = r.f[0] * zs + r.f[1] * (zs4 * zs) + r.f[2] * (zs4 * zs4);
+    const double C2 = C * C;
+    const double a2 = .5 * c.KHS * (1 + chi) * eps * C2 * (x_2la * aB_2la - 2 * x_lalr * aB_lalr + x_2lr * aB_2lr);
     const double da2_div_chi = c.dKHS * (a2 / (c.KHS * (1 + chi)))
-                             + .5 * c.KHS * eps * pow(C, 2) * (x_2la * daB_2la - 2 * x_lalr * daB_lalr + x_2lr * daB_2lr);
-    const double theta = exp(eps / (BOLTZMANN * T)) - 1.;
-    const double gamma_c = 10. * (1 - tanh(10. * (0.57 - q.alpha))) * c.zxs * theta * exp(-6.7 * c.zxs + -8. * pow(c.zxs, 2));
-    const double g2 = (1 + gamma_c) * (1. / (2 * PI_REF * pow(eps, 2) * d3))
-                    * (3 * da2_div_chi + eps * c.KHS * pow(C, 2) * (-lr * x_2lr * aB_2lr / rho + (la + lr) * x_lalr * aB_lalr / rho - la * x_2la * aB_2la / rho));
-    const double be = (1. / (BOLTZMANN * T)) * eps;
-    return gHS * exp(be * (g1 / gHS) + pow(be, 2) * (g2 / gHS));
+                             + .5 * c.KHS * eps * C2 * (x_2la * daB_2la - 2 * x_lalr * daB_lalr + x_2lr * daB_2lr);
+    const double gamma_c = r.gam0 * zs * exp(-6.7 * zs + -8. * zs2);
+    const double g2 = (1 + gamma_c) * (1. / (2 * PI_REF * (eps * eps) * d3))
+                    * (3 * da2_div_chi + eps * c.KHS * C2 * (-lr * x_2lr * aB_2lr / rho + (la + lr) * x_lalr * aB_lalr / rho - la * x_2la * aB_2la / rho));
+    const double be = r.be;
+    return gHS * exp(be * (g1 / gHS) + (be * be) * (g2 / gHS));
 }
 
 // ---- LJ/spline: collision-integral correlation (cpp/LJSpline.cpp:123-165, table cpp/LJSpline.h:138-142) and the RDF at
@@ -575,8 +616,8 @@ __global__ void es_rdf_kernel(int n, int nslots, TModel tm, const int* __restric
 
 // One thread per (state point, slot, i <= j). slot 0: the state point's density; slot 1: N_A / 1e12 (the dilute viscosity of the
 // internal-conductivity term, cpp/KineticGas_properties.cpp:133). rdf [n][nslots][nc][nc].
-__global__ void rdf_kernel(int n, int nslots, TModel tm, const int* __restrict__ tidx, const double* __restrict__ T_of, const double* __restrict__ Vm,
-                           const double* __restrict__ x, const double* __restrict__ dbh, const MiePair* __restrict__ mp, double* __restrict__ rdf) {
+__global__ void rdf_kernel(int n, int nslots, TModel tm, const int* __restrict__ tidx, const double* __restrict__ Vm,
+                           const double* __restrict__ x, const RdfT* __restrict__ rdfT, double* __restrict__ rdf) {
     const int nc = tm.nc, npu = nc * (nc + 1) / 2;
     const long long e = (long long) blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= (long long) n * nslots * npu) return;
@@ -589,11 +630,10 @@ __global__ void rdf_kernel(int n, int nslots, TModel tm, const int* __restrict__
     const int t = tidx[sp];
     if (t < 0) return;                              // temperature not in the cache: state_kernel reports KG_STATUS_T_NOT_CACHED
     const double rho = (slot == 0) ? AVOGADRO / Vm[sp] : AVOGADRO / 1e12;
-    const double* d = dbh + (size_t) t * nc;
+    const RdfT* rt = rdfT + (size_t) t * nc * nc;
     RdfCommon c;
-    rdf_common(nc, rho, xs, d, mp, c);
-    const double dij = (i == j) ? d[i] : (d[i] + d[j]) / 2.0;
-    const double g = rdf_pair(c, mp[i * nc + j], dij, T_of[t]);
+    rdf_common(nc, rho, xs, rt, c);
+    const double g = rdf_pair(c, rt[i * nc + j]);
     double* out = rdf + ((size_t) sp * nslots + slot) * nc * nc;
     out[i * nc + j] = g;
     out[j * nc + i] = g;
@@ -606,6 +646,7 @@ struct StateArgs {
     const int* tidx; const double* T_of; const double* Vm; const double* x;
     const double* rdf;          // [n][nslots][nc][nc]
     const double *mtl, *etl;    // [nT][npairs_dev] (null for ideal gas)
+    const double* tlpow;        // [nT][npairs_dev][4]: etl^3, mtl^3, mtl^4, etl^4 (host libm pow, as the reference forms them)
     const double* brk;          // [nT][4][nc][nc][N][N]
     const double *dmudn, *cp_ideal, *pressure, *dvdn;
     double *viscosity, *conductivity, *contribs, *D, *DT, *kT, *soret, *K, *Kp, *cond_matrix, *cond_vector, *visc_matrix, *visc_vector;
@@ -614,32 +655,38 @@ struct StateArgs {
 
 // Unblocked partial-pivot LU, the algorithm Eigen's partialPivLu runs for sizes <= 16 (row-max pivot, first maximum wins,
 // column scaled by division, rank-1 update with separately rounded multiply and subtract). A is n x n row-major, stride ld.
+// ES = element stride: 1 for the small matrices in thread-local memory; the block size for the Sonine system, which lives in shared
+// memory interleaved over the threads of the block (element e of thread t at [e * ES + t]: conflict-free, and an order of magnitude
+// closer than the L2-backed local memory a 10 x 10 system per thread otherwise streams through).
+template<int ES>
 __device__ int lu_factor(double* A, int n, int ld, int* piv, double zero_pivot_rel = 0.0) {
+#define AT(i, j) A[((i) * ld + (j)) * ES]
     int singular = 0;
     double scale = 0.0;
-    if (zero_pivot_rel > 0.0) for (int i = 0; i < n; i++) for (int j = 0; j < n; j++) scale = fmax(scale, fabs(A[i * ld + j]));
+    if (zero_pivot_rel > 0.0) for (int i = 0; i < n; i++) for (int j = 0; j < n; j++) scale = fmax(scale, fabs(AT(i, j)));
     for (int k = 0; k < n; k++) {
-        int pr = k; double best = fabs(A[k * ld + k]);
-        for (int i = k + 1; i < n; i++) { const double v = fabs(A[i * ld + k]); if (v > best) { best = v; pr = i; } }
+        int pr = k; double best = fabs(AT(k, k));
+        for (int i = k + 1; i < n; i++) { const double v = fabs(AT(i, k)); if (v > best) { best = v; pr = i; } }
         piv[k] = pr;
         if (best != 0.0) {
-            if (pr != k) for (int j = 0; j < n; j++) { const double t = A[k * ld + j]; A[k * ld + j] = A[pr * ld + j]; A[pr * ld + j] = t; }
-            const double d = A[k * ld + k];
-            for (int i = k + 1; i < n; i++) A[i * ld + k] /= d;
+            if (pr != k) for (int j = 0; j < n; j++) { const double t = AT(k, j); AT(k, j) = AT(pr, j); AT(pr, j) = t; }
+            const double d = AT(k, k);
+            for (int i = k + 1; i < n; i++) AT(i, k) /= d;
         }
-        else if (zero_pivot_rel > 0.0) A[k * ld + k] = zero_pivot_rel * scale;
+        else if (zero_pivot_rel > 0.0) AT(k, k) = zero_pivot_rel * scale;
         else singular = 1;
         for (int i = k + 1; i < n; i++) {
-            const double lik = A[i * ld + k];
-            for (int j = k + 1; j < n; j++) A[i * ld + j] = __dsub_rn(A[i * ld + j], __dmul_rn(lik, A[k * ld + j]));
+            const double lik = AT(i, k);
+            for (int j = k + 1; j < n; j++) AT(i, j) = __dsub_rn(AT(i, j), __dmul_rn(lik, AT(k, j)));
         }
     }
     return singular;
 }
+template<int ES>
 __device__ void lu_solve(const double* A, int n, int ld, const int* piv, double* b) {
     for (int k = 0; k < n; k++) if (piv[k] != k) { const double t = b[k]; b[k] = b[piv[k]]; b[piv[k]] = t; }
-    for (int i = 1; i < n; i++) { double s = b[i]; for (int j = 0; j < i; j++) s = __dsub_rn(s, __dmul_rn(A[i * ld + j], b[j])); b[i] = s; }
-    for (int i = n - 1; i >= 0; i--) { double s = b[i]; for (int j = i + 1; j < n; j++) s = __dsub_rn(s, __dmul_rn(A[i * ld + j], b[j])); b[i] = s / A[i * ld + i]; }
+    for (int i = 1; i < n; i++) { double s = b[i]; for (int j = 0; j < i; j++) s = __dsub_rn(s, __dmul_rn(AT(i, j), b[j])); b[i] = s; }
+    for (int i = n - 1; i >= 0; i--) { double s = b[i]; for (int j = i + 1; j < n; j++) s = __dsub_rn(s, __dmul_rn(AT(i, j), b[j])); b[i] = s / AT(i, i); }
 }
 
 struct SP {                     // one state point's scalars, all lanes keep them in registers / local memory
@@ -654,30 +701,34 @@ __device__ __forceinline__ double brk_at(const StateArgs& a, const TModel& tm, i
 }
 
 // Lambda (cpp/KineticGas.cpp:271-318) into A (n x n, n = N nc)
+template<int ES>
 __device__ void build_cond_matrix(const StateArgs& a, const TModel& tm, const SP& s, const double* g, double* A, int ld) {
     const int nc = s.nc, N = s.N, n = N * nc;
-    for (int r = 0; r < n; r++) for (int c = 0; c < n; c++) A[r * ld + c] = 0.0;
-    for (int i = 0; i < nc; i++) A[i] = s.wt[i];
+    for (int r = 0; r < n; r++) for (int c = 0; c < n; c++) AT(r, c) = 0.0;
+    for (int i = 0; i < nc; i++) AT(0, i) = s.wt[i];
+    const double c75 = 75. * (BOLTZMANN * BOLTZMANN) * s.T;
     for (int p = 0; p < N; p++) for (int i = 0; i < nc; i++) {
         if (i == 0 && p == 0) continue;                     // replaced by the weight-fraction row
         const int row = (i == 0) ? p : N + (nc - 1) * p + (i - 1);
         for (int q = 0; q < N; q++) for (int j = 0; j < nc; j++) {
             double v = s.x[i] * s.x[j] * g[i * nc + j] * brk_at(a, tm, s.t, 0, i, j, p, q);
             if (i == j) for (int l = 0; l < nc; l++) v += s.x[i] * s.x[l] * g[i * nc + l] * brk_at(a, tm, s.t, 1, i, l, p, q);
-            v *= 8. * sqrt(tm.m[i] * tm.m[j]) / (75. * pow(BOLTZMANN, 2) * s.T);
-            A[row * ld + nc * q + j] = v;
+            v *= 8. * tm.sqmm[i][j] / c75;
+            AT(row, nc * q + j) = v;
         }
     }
 }
 
 // B (cpp/KineticGas.cpp:418-439)
+template<int ES>
 __device__ void build_visc_matrix(const StateArgs& a, const TModel& tm, const SP& s, const double* g, double* A, int ld) {
     const int nc = s.nc, N = s.N;
+    const double c5 = 2. / (5. * BOLTZMANN * s.T);
     for (int p = 0; p < N; p++) for (int i = 0; i < nc; i++) for (int q = 0; q < N; q++) for (int j = 0; j < nc; j++) {
         double v = s.x[i] * s.x[j] * g[i * nc + j] * brk_at(a, tm, s.t, 2, i, j, p, q);
         if (i == j) for (int k = 0; k < nc; k++) v += s.x[i] * s.x[k] * g[i * nc + k] * brk_at(a, tm, s.t, 3, i, k, p, q);
-        v *= 2. / (5. * BOLTZMANN * s.T);
-        A[(p * nc + i) * ld + q * nc + j] = v;
+        v *= c5;
+        AT(p * nc + i, q * nc + j) = v;
     }
 }
 
@@ -690,9 +741,9 @@ __device__ void k_factors(const StateArgs& a, const TModel& tm, const SP& s, dou
         for (int j = 0; j < nc; j++) {
             const int pr = tm.pair_of[i][j];
             const double Mij = tm.m[i] / (tm.m[i] + tm.m[j]), Mji = tm.m[j] / (tm.m[j] + tm.m[i]);
-            const double etl = a.etl[(size_t) s.t * tm.npairs_dev + pr], mtl = a.mtl[(size_t) s.t * tm.npairs_dev + pr];
-            k += s.x[j] * pow(etl, 3) * Mij * Mji * g[i * nc + j];
-            kp += s.x[j] * Mji * pow(mtl, 3.) * g[i * nc + j];
+            const double* tp = a.tlpow + ((size_t) s.t * tm.npairs_dev + pr) * 4;
+            k += s.x[j] * tp[0] * Mij * Mji * g[i * nc + j];
+            kp += s.x[j] * Mji * tp[1] * g[i * nc + j];
         }
         K[i] = k * (24. * PI_REF * rho / 15) + 1;
         Kp[i] = kp * (8. * PI_REF * rho / 15) + 1.;
@@ -700,31 +751,35 @@ __device__ void k_factors(const StateArgs& a, const TModel& tm, const SP& s, dou
 }
 
 // KineticGas::viscosity at (T, rho) with the given rdf (cpp/KineticGas_properties.cpp:28-58). A, piv, b are scratch.
+template<int ES>
 __device__ double viscosity_at(const StateArgs& a, const TModel& tm, const SP& s, double rho, const double* g, const double* Kp,
                                double* A, int ld, int* piv, double* b, int& st, double* mat_out, double* vec_out) {
     const int nc = s.nc, N = s.N, n = N * nc;
-    build_visc_matrix(a, tm, s, g, A, ld);
+    build_visc_matrix<ES>(a, tm, s, g, A, ld);
     for (int i = 0; i < n; i++) b[i] = 0.0;
     for (int i = 0; i < nc; i++) b[i] = 2. * s.x[i] * Kp[i] / (BOLTZMANN * s.T);
-    if (mat_out) for (int r = 0; r < n; r++) for (int c = 0; c < n; c++) mat_out[r * n + c] = A[r * ld + c];
+    if (mat_out) for (int r = 0; r < n; r++) for (int c = 0; c < n; c++) mat_out[r * n + c] = AT(r, c);
     if (vec_out) for (int i = 0; i < n; i++) vec_out[i] = b[i];
-    if (lu_factor(A, n, ld, piv)) st |= KG_STATUS_SINGULAR;
-    lu_solve(A, n, ld, piv, b);
+    if (lu_factor<ES>(A, n, ld, piv)) st |= KG_STATUS_SINGULAR;
+    lu_solve<ES>(A, n, ld, piv, b);
     double eta_p = 0.0;
     for (int i = 0; i < nc; i++) eta_p += Kp[i] * s.x[i] * b[i];
     eta_p *= BOLTZMANN * s.T / 2.0;
     if (tm.is_idealgas) return eta_p;
     double eta_pp = 0.0;
     for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) {
-        const double mtl = a.mtl[(size_t) s.t * tm.npairs_dev + tm.pair_of[i][j]];
-        eta_pp += sqrt(tm.m[i] * tm.m[j] / (tm.m[i] + tm.m[j])) * s.x[i] * s.x[j] * pow(mtl, 4) * g[i * nc + j];
+        const double mtl4 = a.tlpow[((size_t) s.t * tm.npairs_dev + tm.pair_of[i][j]) * 4 + 2];
+        eta_pp += tm.sqred[i][j] * s.x[i] * s.x[j] * mtl4 * g[i * nc + j];
     }
-    eta_pp *= 4.0 * pow(rho, 2) * sqrt(2.0 * PI_REF * BOLTZMANN * s.T) / 15.0;
+    eta_pp *= 4.0 * (rho * rho) * sqrt(2.0 * PI_REF * BOLTZMANN * s.T) / 15.0;
     return eta_p + eta_pp;
 }
 
+__host__ __device__ constexpr int state_tpb(int maxn) { return maxn <= 12 ? 64 : 32; }      // threads per block: the block's Sonine systems fill its shared memory
 template<int MAXN>
-__global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
+__global__ void __launch_bounds__(state_tpb(MAXN)) state_kernel(TModel tm, StateArgs a) {
+    extern __shared__ double s_sys[];                   // [MAXN * MAXN][block] : the N nc x N nc system of every thread, interleaved
+    constexpr int ES = state_tpb(MAXN);
     const int sp = blockIdx.x * blockDim.x + threadIdx.x;
     if (sp >= a.n) return;
     const int nc = tm.nc, N = tm.N, n = N * nc, ld = MAXN;
@@ -760,13 +815,14 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
     if (a.K) for (int i = 0; i < nc; i++) a.K[(size_t) sp * nc + i] = K[i];
     if (a.Kp) for (int i = 0; i < nc; i++) a.Kp[(size_t) sp * nc + i] = Kp[i];
 
-    double A[MAXN * MAXN], b[MAXN], th[MAXN], dsol[MAXC * MAXN];
+    double* A = s_sys + threadIdx.x;
+    double b[MAXN], th[MAXN], dsol[MAXC * MAXN];
     int piv[MAXN];
     const bool single = tm.is_singlecomp != 0;
     if (props & (KG_PROP_CONDUCTIVITY | KG_PROP_DIFFUSION | KG_PROP_THERMAL_DIFFUSION)) {
-        build_cond_matrix(a, tm, s, g, A, ld);
-        if (a.cond_matrix) for (int r = 0; r < n; r++) for (int c = 0; c < n; c++) a.cond_matrix[((size_t) sp * n + r) * n + c] = A[r * ld + c];
-        if (lu_factor(A, n, ld, piv)) st |= KG_STATUS_SINGULAR;
+        build_cond_matrix<ES>(a, tm, s, g, A, ld);
+        if (a.cond_matrix) for (int r = 0; r < n; r++) for (int c = 0; c < n; c++) a.cond_matrix[((size_t) sp * n + r) * n + c] = AT(r, c);
+        if (lu_factor<ES>(A, n, ld, piv)) st |= KG_STATUS_SINGULAR;
         const bool need_th = (props & (KG_PROP_CONDUCTIVITY | KG_PROP_THERMAL_DIFFUSION)) != 0;
         const bool need_d = (props & (KG_PROP_DIFFUSION | KG_PROP_THERMAL_DIFFUSION)) || ((props & KG_PROP_CONDUCTIVITY) && !single && N > 1);
         if (need_th || a.cond_vector) {
@@ -777,7 +833,7 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
                 for (int i = 1; i < nc; i++) th[N + (nc - 1) + (i - 1)] = s.x[i] * K[i] * 4. / (5. * BOLTZMANN);
             }
             if (a.cond_vector) for (int i = 0; i < n; i++) a.cond_vector[(size_t) sp * n + i] = th[i];
-            lu_solve(A, n, ld, piv, th);
+            lu_solve<ES>(A, n, ld, piv, th);
         }
         if (need_d) {
             // get_diffusion_vector, cpp/KineticGas.cpp:390-403: block k of the block-diagonal system, d[q][i][k] = dsol[k][nc q + i]
@@ -789,7 +845,7 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
                     if (i == k) v += 8. / (25. * BOLTZMANN);
                     dk[N + (i - 1)] = v;
                 }
-                lu_solve(A, n, ld, piv, dk);
+                lu_solve<ES>(A, n, ld, piv, dk);
             }
         }
         // E_ij and ksi (cpp/KineticGas_properties.cpp:459-500), frame matrices (:348-396), D in the centre-of-mass frame (:332-346)
@@ -847,14 +903,14 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
                 Xm[i * MAXC + j] = ((i == j) ? s.x[idm[i]] : 0.0) - s.x[idm[i]] * s.x[idm[j]];
                 Xlu[i * MAXC + j] = Xm[i * MAXC + j];
             }
-            if (lu_factor(Xlu, nm, MAXC, pz)) st |= KG_STATUS_SINGULAR;
+            if (lu_factor<1>(Xlu, nm, MAXC, pz)) st |= KG_STATUS_SINGULAR;
             if (fr == KG_FOR_ZARATE_X) { for (int k = 0; k < nm; k++) for (int j = 0; j < nm; j++) Dz[k * MAXC + j] = Dx[k * MAXC + j]; }
             else {
                 // D = X^-1 D^(x) X, column by column
                 for (int cidx = 0; cidx < nm; cidx++) {
                     double col[MAXC];
                     for (int i = 0; i < nm; i++) { double v = 0.; for (int k = 0; k < nm; k++) v += Dx[i * MAXC + k] * Xm[k * MAXC + cidx]; col[i] = v; }
-                    lu_solve(Xlu, nm, MAXC, pz, col);
+                    lu_solve<1>(Xlu, nm, MAXC, pz, col);
                     for (int i = 0; i < nm; i++) Dz[i * MAXC + cidx] = col[i];
                 }
                 if (fr == KG_FOR_ZARATE_W) {
@@ -865,11 +921,11 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
                         WT[j * MAXC + i] = Wm[i * MAXC + j];
                     }
                     for (int i = 0; i < nm; i++) for (int j = 0; j < nm; j++) { double v = 0.; for (int k = 0; k < nm; k++) v += Wm[i * MAXC + k] * Dz[k * MAXC + j]; WD[i * MAXC + j] = v; }
-                    if (lu_factor(WT, nm, MAXC, pw)) st |= KG_STATUS_SINGULAR;
+                    if (lu_factor<1>(WT, nm, MAXC, pw)) st |= KG_STATUS_SINGULAR;
                     for (int r = 0; r < nm; r++) {
                         double row[MAXC];
                         for (int j = 0; j < nm; j++) row[j] = WD[r * MAXC + j];
-                        lu_solve(WT, nm, MAXC, pw, row);
+                        lu_solve<1>(WT, nm, MAXC, pw, row);
                         for (int j = 0; j < nm; j++) Dz[r * MAXC + j] = row[j];
                     }
                 }
@@ -895,8 +951,8 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
             for (int j = 0; j < nc; j++) for (int k = 0; k < nc; k++) {
                 double v = (j == k) ? 1.0 : 0.0;
                 if (!tm.is_idealgas) {
-                    const double etl = a.etl[(size_t) s.t * tm.npairs_dev + tm.pair_of[j][k]];
-                    v += (4. * PI_REF / 3) * s.rho * s.x[k] * pow(etl, 3) * (tm.m[j] / (tm.m[j] + tm.m[k])) * g[j * nc + k];
+                    const double etl3 = a.tlpow[((size_t) s.t * tm.npairs_dev + tm.pair_of[j][k]) * 4];
+                    v += (4. * PI_REF / 3) * s.rho * s.x[k] * etl3 * (tm.m[j] / (tm.m[j] + tm.m[k])) * g[j * nc + k];
                 }
                 bm[j * nc + k] = v;
             }
@@ -923,15 +979,15 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
                     rhs[i] = v / s.T;
                     for (int j = 0; j < nm; j++) XL[i * MAXC + j] = -cm * Xm[i * MAXC + j];
                 }
-                if (lu_factor(XL, nm, MAXC, px)) st |= KG_STATUS_SINGULAR;
-                lu_solve(XL, nm, MAXC, px, rhs);
+                if (lu_factor<1>(XL, nm, MAXC, px)) st |= KG_STATUS_SINGULAR;
+                lu_solve<1>(XL, nm, MAXC, px, rhs);
                 if (a.DT) for (int i = 0; i < nm; i++) a.DT[(size_t) sp * nc + i] = rhs[i];
                 if (a.soret) {
                     // KineticGas::soret_coefficient (:325-330): S_T = D^-1 D_T, both in the Zarate frame
                     double DL[MAXC * MAXC]; int pd[MAXC];
                     for (int i = 0; i < nm; i++) for (int j = 0; j < nm; j++) DL[i * MAXC + j] = Dz[i * MAXC + j];
-                    if (lu_factor(DL, nm, MAXC, pd)) st |= KG_STATUS_SINGULAR;
-                    lu_solve(DL, nm, MAXC, pd, rhs);
+                    if (lu_factor<1>(DL, nm, MAXC, pd)) st |= KG_STATUS_SINGULAR;
+                    lu_solve<1>(DL, nm, MAXC, pd, rhs);
                     for (int i = 0; i < nm; i++) a.soret[(size_t) sp * nc + i] = rhs[i];
                 }
             }
@@ -955,8 +1011,8 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
                     for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) v += s.x[i] * bm[i * nc + j];     // bm = delta_ij + (4 pi / 3) rho x_j etl^3 M_ij g_ij
                     rhs[last] = v;
                 }
-                if (lu_factor(Am, nc, MAXC, pv)) st |= KG_STATUS_SINGULAR;
-                lu_solve(Am, nc, MAXC, pv, rhs);
+                if (lu_factor<1>(Am, nc, MAXC, pv)) st |= KG_STATUS_SINGULAR;
+                lu_solve<1>(Am, nc, MAXC, pv, rhs);
                 for (int i = 0; i < nc; i++) a.kT[(size_t) sp * nc + i] = rhs[i];
             }
         }
@@ -973,8 +1029,8 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
                 // the reference's partialPivLu ends on a pivot that is pure rounding noise and lambda' does not depend on it
                 // (d[1] annihilates the null vector). When that noise happens to be exactly 0.0 the reference would return NaN;
                 // here the pivot is replaced by one ulp of the matrix scale, which is what it is in every other case.
-                lu_factor(dm, nc, MAXC, pv, DBL_EPSILON);
-                lu_solve(dm, nc, MAXC, pv, dth);
+                lu_factor<1>(dm, nc, MAXC, pv, DBL_EPSILON);
+                lu_solve<1>(dm, nc, MAXC, pv, dth);
             }
             double lam_t = 0.;
             for (int i = 0; i < nc; i++) {
@@ -986,9 +1042,9 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
             double lam_d = 0.;
             if (!tm.is_idealgas) {
                 for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) {
-                    const double etl = a.etl[(size_t) s.t * tm.npairs_dev + tm.pair_of[i][j]];
-                    lam_d += pow(s.rho, 2) * sqrt(2 * PI_REF * tm.m[i] * tm.m[j] * BOLTZMANN * s.T / (tm.m[i] + tm.m[j]))
-                             * (s.x[i] * s.x[j]) / (tm.m[i] + tm.m[j]) * pow(etl, 4) * g[i * nc + j];
+                    const double etl4 = a.tlpow[((size_t) s.t * tm.npairs_dev + tm.pair_of[i][j]) * 4 + 3];
+                    lam_d += (s.rho * s.rho) * sqrt(2 * PI_REF * tm.m[i] * tm.m[j] * BOLTZMANN * s.T / (tm.m[i] + tm.m[j]))
+                             * (s.x[i] * s.x[j]) / (tm.m[i] + tm.m[j]) * etl4 * g[i * nc + j];
                 }
                 lam_d *= (4. * BOLTZMANN / 3.);
             }
@@ -1001,7 +1057,7 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
                 const double rho0 = AVOGADRO / 1e12;
                 for (int k = 0; k < nc * nc; k++) g0[k] = tm.is_idealgas ? 1.0 : a.rdf[((size_t) sp * a.nslots + 1) * nc * nc + k];
                 k_factors(a, tm, s, rho0, g0, K0, Kp0);
-                const double eta0 = viscosity_at(a, tm, s, rho0, g0, Kp0, A, ld, piv, b, st, nullptr, nullptr);
+                const double eta0 = viscosity_at<ES>(a, tm, s, rho0, g0, Kp0, A, ld, piv, b, st, nullptr, nullptr);
                 lam_i = 1.32e3 * eta0 * cpf;
             }
             if (a.contribs) { a.contribs[(size_t) sp * 3] = lam_t; a.contribs[(size_t) sp * 3 + 1] = lam_d; a.contribs[(size_t) sp * 3 + 2] = lam_i; }
@@ -1009,13 +1065,14 @@ __global__ void __launch_bounds__(128) state_kernel(TModel tm, StateArgs a) {
         }
     }
     if (props & KG_PROP_VISCOSITY) {
-        const double eta = viscosity_at(a, tm, s, s.rho, g, Kp, A, ld, piv, b, st,
+        const double eta = viscosity_at<ES>(a, tm, s, s.rho, g, Kp, A, ld, piv, b, st,
                                         a.visc_matrix ? a.visc_matrix + (size_t) sp * n * n : nullptr, a.visc_vector ? a.visc_vector + (size_t) sp * n : nullptr);
         if (a.viscosity) a.viscosity[sp] = eta;
     }
     if (a.status) a.status[sp] = st;
 }
 
+#undef AT
 } // namespace
 
 // ================================================================================================================
@@ -1031,8 +1088,9 @@ struct kg_tcache {
     std::vector<double> T;
     std::map<double, int> index_of;
     std::vector<unsigned char> is_corr;              // [nT][npairs][nlr]
-    double *d_T = nullptr, *d_omega = nullptr, *d_mtl = nullptr, *d_etl = nullptr, *d_dbh = nullptr, *d_brk = nullptr;
+    double *d_T = nullptr, *d_omega = nullptr, *d_mtl = nullptr, *d_etl = nullptr, *d_dbh = nullptr, *d_brk = nullptr, *d_tlpow = nullptr;
     MiePair* d_mp_int = nullptr;                     // [nc][nc] internal pairs
+    void* d_rdfT = nullptr;                          // RdfT [nT][nc][nc] (Mie RDF: T- and pair-only part)
     EsPair* d_es_int = nullptr;                      // [nc][nc] internal pairs (es)
     EsParams* d_es_prm = nullptr;                    // [nT][nc][nc] effective parameters (es)
     MiePair mp00{};                                  // pair (0,0) on the host (LJ/spline RDF kernel argument)
@@ -1057,7 +1115,7 @@ bool desc_is_mie(const kg_potential_desc& d) {
 
 static void tcache_free(kg_tcache* c) {
     cudaSetDevice(c->device);
-    void* ptrs[] = {c->d_T, c->d_omega, c->d_mtl, c->d_etl, c->d_dbh, c->d_brk, c->d_mp_int, c->d_es_int, c->d_es_prm};
+    void* ptrs[] = {c->d_T, c->d_omega, c->d_mtl, c->d_etl, c->d_dbh, c->d_brk, c->d_tlpow, c->d_mp_int, c->d_es_int, c->d_es_prm, c->d_rdfT};
     for (void* p : ptrs) c->m->dfree(p);
     delete c;
 }
@@ -1094,6 +1152,7 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
     if (!m) return -1;
     auto set_error = [&](const std::string& s) { m->err = s; };
     if (!opts || nT < 1 || !T || !out) { set_error("kg_tcache_create: invalid argument"); return -1; }
+    if (m->coeff_T_required && !coeff_T) { set_error("this model's coefficients depend on temperature: coeff_T is required (kg_model_set_temperature_dependent)"); return -1; }
     const int N = opts->N;
     if (N < 1 || N > MAXO) { set_error("kg_tcache_create: Enskog order N out of range"); return -1; }
     const int nc = m->is_singlecomp ? 2 : m->ncomps;
@@ -1119,6 +1178,10 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
     TModel& tm = c->tm;
     tm.nc = nc; tm.npairs_dev = m->npairs; tm.is_singlecomp = m->is_singlecomp; tm.is_idealgas = opts->is_idealgas; tm.N = N;
     for (int i = 0; i < nc; i++) tm.m[i] = m->mass[m->is_singlecomp ? 0 : i];
+    for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) {
+        tm.sqmm[i][j] = sqrt(tm.m[i] * tm.m[j]);
+        tm.sqred[i][j] = sqrt(tm.m[i] * tm.m[j] / (tm.m[i] + tm.m[j]));
+    }
     std::vector<int> pair_i, pair_j;
     for (int i = 0; i < m->ncomps; i++) for (int j = i; j < m->ncomps; j++) { pair_i.push_back(i); pair_j.push_back(j); }
     for (int i = 0; i < nc; i++) for (int j = 0; j < nc; j++) {
@@ -1249,6 +1312,13 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
         if (bad & KG_STATUS_GETR_MAXITER) { set_error("get_R reached max iter!"); tcache_free(c); return -4; }
         m->timings[2] = ms_since(t_stage); m->timings[4] += m->tl_launches;
         TC_CUDA(upload(m, &c->d_mtl, c->h_mtl)); TC_CUDA(upload(m, &c->d_etl, c->h_etl));
+        {
+            std::vector<double> tp((size_t) nT * Np * 4);
+            for (size_t k = 0; k < (size_t) nT * Np; k++) {
+                tp[4 * k] = pow(c->h_etl[k], 3); tp[4 * k + 1] = pow(c->h_mtl[k], 3.); tp[4 * k + 2] = pow(c->h_mtl[k], 4); tp[4 * k + 3] = pow(c->h_etl[k], 4);
+            }
+            TC_CUDA(upload(m, &c->d_tlpow, tp));
+        }
         if (es) {
             std::vector<EsPair> ep_dev(Np), ep_int((size_t) nc * nc);
             for (int p = 0; p < Np; p++) {
@@ -1278,6 +1348,11 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
             TC_CUDA(kg_dmalloc(m, &c->d_dbh, (size_t) nT * nc * sizeof(double)));
             bh_kernel<<<(nT * nc + 127) / 128, 128, 0, s>>>(nT, nc, c->d_T, d_diag, c->d_dbh);
             TC_CUDA(cudaGetLastError());
+            if (!ljs) {
+                TC_CUDA(kg_dmalloc(m, (RdfT**) &c->d_rdfT, (size_t) nT * nc * nc * sizeof(RdfT)));
+                rdf_T_kernel<<<(nT * nc * nc + 63) / 64, 64, 0, s>>>(nT, nc, c->d_T, c->d_dbh, c->d_mp_int, (RdfT*) c->d_rdfT);
+                TC_CUDA(cudaGetLastError());
+            }
             TC_CUDA(cudaStreamSynchronize(s));
             m->dfree(d_diag);
         }
@@ -1322,16 +1397,21 @@ int launch_state(kg_tcache* c, StateArgs& a, cudaStream_t s, const double* d_x_f
         const long long tot = (long long) n * a.nslots * (tm.nc * (tm.nc + 1) / 2);
         if (c->ljs) ljs_rdf_kernel<<<(unsigned) (((long long) n * a.nslots + 127) / 128), 128, 0, s>>>(n, a.nslots, tm.nc, a.tidx, a.T_of, a.Vm, c->d_dbh, c->mp00, d_rdf);
         else if (c->es) es_rdf_kernel<<<(unsigned) ((tot + 63) / 64), 64, 0, s>>>(n, a.nslots, tm, a.tidx, a.T_of, a.Vm, d_x_for_rdf, c->d_es_int, c->d_es_prm, d_rdf);
-        else rdf_kernel<<<(unsigned) ((tot + 127) / 128), 128, 0, s>>>(n, a.nslots, tm, a.tidx, a.T_of, a.Vm, d_x_for_rdf, c->d_dbh, c->d_mp_int, d_rdf);
+        else rdf_kernel<<<(unsigned) ((tot + 127) / 128), 128, 0, s>>>(n, a.nslots, tm, a.tidx, a.Vm, d_x_for_rdf, (const RdfT*) c->d_rdfT, d_rdf);
     }
-    const int nn = tm.N * tm.nc, grid = (n + 127) / 128;
-    // the matrix of one state point lives in the thread's local memory: the tightest leading dimension keeps it in L1
-    if (nn <= 6) state_kernel<6><<<grid, 128, 0, s>>>(tm, a);
-    else if (nn <= 8) state_kernel<8><<<grid, 128, 0, s>>>(tm, a);
-    else if (nn <= 10) state_kernel<10><<<grid, 128, 0, s>>>(tm, a);
-    else if (nn <= 12) state_kernel<12><<<grid, 128, 0, s>>>(tm, a);
-    else if (nn <= 16) state_kernel<16><<<grid, 128, 0, s>>>(tm, a);
-    else state_kernel<24><<<grid, 128, 0, s>>>(tm, a);
+    const int nn = tm.N * tm.nc;
+    // the Sonine system of a state point lives in shared memory (interleaved over the block's threads), sized by the tightest
+    // leading dimension that holds N nc
+#define LAUNCH_STATE(MX) do { constexpr int TPB = state_tpb(MX); const size_t smem = (size_t) MX * MX * TPB * sizeof(double); \
+        cudaFuncSetAttribute(state_kernel<MX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem); \
+        state_kernel<MX><<<(n + TPB - 1) / TPB, TPB, smem, s>>>(tm, a); } while (0)
+    if (nn <= 6) LAUNCH_STATE(6);
+    else if (nn <= 8) LAUNCH_STATE(8);
+    else if (nn <= 10) LAUNCH_STATE(10);
+    else if (nn <= 12) LAUNCH_STATE(12);
+    else if (nn <= 16) LAUNCH_STATE(16);
+    else LAUNCH_STATE(24);
+#undef LAUNCH_STATE
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { c->m->err = std::string("state kernels: ") + cudaGetErrorString(e); return -2; }
     return 0;
@@ -1343,6 +1423,7 @@ extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const do
                                   const kg_transport_opts* opts, const kg_eos_inputs* eos, const kg_transport_out* out, int32_t* status) {
     KG_TRACE();
     if (!m) return -1;
+    const auto t_enter = std::chrono::steady_clock::now();
     auto set_error = [&](const std::string& s) { m->err = s; };
     if (n < 0 || !T || !Vm || !opts || !out) { set_error("kg_transport_batch: invalid argument"); return -1; }
     if (n == 0) return 0;
@@ -1400,12 +1481,12 @@ extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const do
     a.nslots = (props & KG_PROP_CONDUCTIVITY) ? 2 : 1;
     const int N = opts->N, nn = N * nc, nD = a.opt.do_compress ? nc - 1 : nc;
 #define NEED(p) do { if (!(p)) { set_error("kg_transport_batch: device allocation or copy failed"); return -2; } } while (0)
-    const bool chunked = n >= 32768;              // large batches: the copies go chunk by chunk on the auxiliary streams (below)
+    const bool chunked = n >= 262144;             // very large batches: the copies go chunk by chunk on the auxiliary streams (below)
     a.tidx = db.put(chunked ? nullptr : tidx.data(), n, s); NEED(a.tidx);
     a.T_of = c->d_T;
     a.Vm = db.put(chunked ? nullptr : Vm, n, s); NEED(a.Vm);
     a.x = m->is_singlecomp ? nullptr : db.put(chunked ? nullptr : x, (size_t) n * nc, s); if (!m->is_singlecomp) NEED(a.x);
-    a.mtl = c->d_mtl; a.etl = c->d_etl; a.brk = c->d_brk;
+    a.mtl = c->d_mtl; a.etl = c->d_etl; a.tlpow = c->d_tlpow; a.brk = c->d_brk;
     double* d_rdf = nullptr;
     if (!opts->is_idealgas) { d_rdf = db.alloc<double>((size_t) n * a.nslots * nc * nc); NEED(d_rdf); }
     a.rdf = d_rdf;
@@ -1425,7 +1506,7 @@ extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const do
     // overlap (truly so when the caller's buffers are pinned, kg_host_alloc; pageable buffers are staged by the driver and only
     // the kernels overlap). Inputs were enqueued above on the model stream in one piece when the batch is small.
     std::vector<int> st(n);
-    const int nchunk = (n >= 32768) ? 4 : 1;
+    const int nchunk = chunked ? 4 : 1;
     float kms = 0;
     if (nchunk == 1) {
         cudaEvent_t ev0, ev1;
@@ -1495,6 +1576,7 @@ extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const do
     }
     if (out->rdf && opts->is_idealgas) for (size_t k = 0; k < (size_t) n * nc * nc; k++) out->rdf[k] = 1.0;
     m->timings[0] = kms; m->timings[5] = (opts->is_idealgas ? 1 : 2) * nchunk;
+    m->timings[6] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_enter).count();     // whole call on the host clock
     if (status) for (int k = 0; k < n; k++) status[k] = st[k];
     return 0;
 }

@@ -163,13 +163,28 @@ class MieKinGas:
             raise IndexError(f"{x.shape[-1]} mole fractions were supplied for a {self.ncomps} component mixture!")
         return x
 
+    CACHE_LIMIT = 8          # device table sets kept per model (least recently used goes first)
+
     def tcache(self, T, N=None, properties=PROP_VISCOSITY | PROP_CONDUCTIVITY | PROP_DIFFUSION | PROP_THERMAL_DIFFUSION):
-        """Build (or reuse) the device tables for the distinct temperatures in T."""
+        """Build (or reuse) the device tables for the distinct temperatures in T. Like the reference's KineticGasCache the tables are
+        shared by all properties: a set is keyed on (N, correlation switch, ideal-gas switch, temperatures), small sets are built
+        for every property at once (viscosity followed by thermal_conductivity at the same T integrates nothing twice), a set that
+        lacks a requested property is rebuilt with the union. At most CACHE_LIMIT sets are kept."""
         N = self.default_N if N is None else N
         Tu = np.unique(np.asarray(T, float))
-        key = (N, properties, self.omega_correlation_active, Tu.tobytes())
-        if key not in self._caches:
-            self._caches[key] = TCache(self, Tu, N, properties, self._coeff_T(Tu))
+        key = (N, self.omega_correlation_active, bool(self.is_idealgas), Tu.tobytes())
+        c = self._caches.get(key)
+        if c is not None and (properties & ~c.opts.properties) == 0:
+            self._caches[key] = self._caches.pop(key)          # most recently used last
+            return c
+        props = properties | (c.opts.properties if c is not None else 0)
+        if Tu.size <= 16:
+            props |= PROP_VISCOSITY | PROP_CONDUCTIVITY | PROP_DIFFUSION | PROP_THERMAL_DIFFUSION
+        if c is not None:
+            self._caches.pop(key).close()
+        self._caches[key] = TCache(self, Tu, N, props, self._coeff_T(Tu))
+        while len(self._caches) > self.CACHE_LIMIT:
+            self._caches.pop(next(iter(self._caches))).close()
         return self._caches[key]
 
     def _eos_arrays(self, T, Vm, x, need_dmudn, need_cp, need_dvdn, eos_inputs):
@@ -390,10 +405,10 @@ class MieKinGas:
         return out
 
     def get_mtl(self, particle_density, T, x):
-        return self._pair_matrix(self.dev.transfer_lengths([T])[0][0])
+        return self._pair_matrix(self.dev.transfer_lengths([T], coeff_T=self._coeff_T([T]))[0][0])
 
     def get_etl(self, particle_density, T, x):
-        return self._pair_matrix(self.dev.transfer_lengths([T])[1][0])
+        return self._pair_matrix(self.dev.transfer_lengths([T], coeff_T=self._coeff_T([T]))[1][0])
 
 
 class QuantumMie(MieKinGas):
@@ -451,6 +466,8 @@ class QuantumMie(MieKinGas):
                 descs.append(power_sum_desc(sig, eps, Ck, lam))
         self._pair_eps = [d.eps for d in descs]
         self.dev = DeviceModel(descs, self.m[:ncd], self._is_singlecomp, device=self._device)
+        if self.FH_order > 0:
+            self.dev.set_temperature_dependent(True)       # every call must carry the per-temperature coefficients (coeff_T)
         self._caches = {}
 
     def _coeff_T(self, T):

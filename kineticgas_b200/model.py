@@ -127,6 +127,10 @@ class DeviceModel:
     def set_stream(self, cuda_stream_ptr):
         self._chk(self.L.kg_model_set_stream(self.h, C.c_void_p(int(cuda_stream_ptr))), "kg_model_set_stream")
 
+    def set_temperature_dependent(self, flag=True):
+        """Declare that the power-law coefficients of this model depend on T (Feynman-Hibbs Mie): calls without coeff_T are refused."""
+        self._chk(self.L.kg_model_set_temperature_dependent(self.h, int(bool(flag))), "kg_model_set_temperature_dependent")
+
     def pair_index(self, i, j):
         i, j = min(i, j), max(i, j)
         return i * self.ncomps - i * (i - 1) // 2 + (j - i)
@@ -173,7 +177,7 @@ class DeviceModel:
     def last_timings(self):
         out = np.zeros(8)
         self.L.kg_last_timings(self.h, _p(out))
-        return dict(zip(["ms_state_kernels", "ms_omega_stage", "ms_tl_stage", "ms_bracket_stage", "launches_tcache", "launches_batch"], out.tolist()))
+        return dict(zip(["ms_state_kernels", "ms_omega_stage", "ms_tl_stage", "ms_bracket_stage", "launches_tcache", "launches_batch", "ms_batch_call"], out.tolist()))
 
     def omega_plan(self, T, l, r, coeff_T=None):
         return OmegaPlan(self, T, l, r, coeff_T)

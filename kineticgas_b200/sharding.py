@@ -21,18 +21,25 @@ def regime_index(T):
 
 
 def partition_temperatures(T, world):
-    """Cost-balanced deal of temperature indices over ranks (longest processing time first). Returns a list of index
-    arrays, one per rank, each sorted ascending; every index appears exactly once."""
+    """Cost-balanced deal of temperature indices over ranks. The cost of an item takes one of five values (its lattice regime), so
+    dealing every regime's items round-robin -- most expensive regime first, each regime starting at the rank where the previous one
+    stopped -- gives every rank the same number of items of every regime to within one. Returns a list of index arrays, one per
+    rank, each sorted ascending; every index appears exactly once."""
     T = np.asarray(T, float)
-    cost = REGIME_COST[regime_index(T)]
-    order = np.argsort(-cost, kind="stable")
-    load = np.zeros(world)
-    parts = [[] for _ in range(world)]
-    for i in order:
-        r = int(np.argmin(load))
-        parts[r].append(int(i))
-        load[r] += cost[i]
-    return [np.array(sorted(p), dtype=np.int64) for p in parts]
+    reg = regime_index(T)
+    owner = np.empty(T.size, dtype=np.int64)
+    start = 0
+    for k in np.argsort(-REGIME_COST, kind="stable"):
+        idx = np.flatnonzero(reg == k)
+        owner[idx] = (start + np.arange(idx.size)) % world
+        start = (start + idx.size) % world
+    return [np.flatnonzero(owner == r) for r in range(world)]
+
+
+def partition_cost(T, parts):
+    """Modelled cost of every rank's share (sum of REGIME_COST): what the deal balances; bench.py compares it with measured kernel time."""
+    reg = regime_index(np.asarray(T, float))
+    return np.array([REGIME_COST[reg[p]].sum() for p in parts])
 
 
 def partition_blocks(n, world):
@@ -53,24 +60,42 @@ def _all_gather_padded(local, counts, group=None):
     return buf.view((world, nmax) + tuple(local.shape[1:]))
 
 
-def sharded_temperature_tables(compute_fn, T, rank, world, device="cpu", group=None):
-    """Every rank returns the full table [nT, ...] in the caller's temperature order. compute_fn(T_local) -> tensor
-    [n_local, ...] (on `device`) is this rank's share of stage 1 (e.g. OmegaPlan run + export)."""
-    T = np.asarray(T, float)
-    parts = partition_temperatures(T, world)
-    local = compute_fn(T[parts[rank]])
-    local = torch.as_tensor(local, device=device)
-    if world == 1:
-        out = torch.empty_like(local)
-        out[torch.as_tensor(parts[0])] = local
+class TemperatureDeal:
+    """The deal of one temperature grid over `world` ranks, with the index tensors of the gather kept on `device` (a sweep that
+    repeats the same grid pays for the partition once)."""
+
+    def __init__(self, T, world, device="cpu"):
+        self.T = np.asarray(T, float)
+        self.world = world
+        self.parts = partition_temperatures(self.T, world)
+        self.counts = [len(p) for p in self.parts]
+        self.index = [torch.as_tensor(p, device=device) for p in self.parts]
+        self.modelled_cost = partition_cost(self.T, self.parts)
+
+    def local(self, rank):
+        return self.T[self.parts[rank]]
+
+    def gather(self, local, rank, group=None):
+        """local [counts[rank], ...] of this rank -> the full table [nT, ...] in the caller's temperature order, on every rank."""
+        out = torch.empty((self.T.size,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+        if self.world == 1:
+            out[self.index[0]] = local
+            return out
+        g = _all_gather_padded(local, self.counts, group)
+        for r in range(self.world):
+            if self.counts[r]:
+                out[self.index[r]] = g[r, : self.counts[r]]
         return out
-    counts = [len(p) for p in parts]
-    g = _all_gather_padded(local, counts, group)
-    out = torch.empty((T.size,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
-    for r in range(world):
-        if counts[r]:
-            out[torch.as_tensor(parts[r], device=local.device)] = g[r, : counts[r]]
-    return out
+
+
+def sharded_temperature_tables(compute_fn, T, rank, world, device="cpu", group=None, deal=None):
+    """Every rank returns the full table [nT, ...] in the caller's temperature order. compute_fn(T_local) -> tensor
+    [n_local, ...] (on `device`) is this rank's share of stage 1 (e.g. OmegaPlan run + export). deal: a TemperatureDeal of the
+    same grid built earlier (sweeps that repeat one grid)."""
+    if deal is None:
+        deal = TemperatureDeal(T, world, device)
+    local = torch.as_tensor(compute_fn(deal.local(rank)), device=device)
+    return deal.gather(local, rank, group)
 
 
 def sharded_state_points(compute_fn, n, rank, world, device="cpu", group=None):

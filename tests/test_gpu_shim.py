@@ -117,3 +117,52 @@ def test_omega_table_feeds_the_reference_cache():
             assert gpu.omega(0, 0, l[k], r[k], T) == tab[t, 0, k]                 # cache hit: the stored device value, bit for bit
             assert abs(tab[t, 0, k] / stock.omega(0, 0, l[k], r[k], T) - 1) < TOL
     assert gpu.counters()["cpu_theta_integrand_calls"] == 0
+
+
+def _pybind_module():
+    import importlib
+    import os
+    import sys
+    d = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "integration", "_build")
+    if d not in sys.path:
+        sys.path.insert(0, d)
+    try:
+        return importlib.import_module("libkgshim_py")
+    except ImportError:
+        pytest.skip("integration/_build/libkgshim_py*.so not built")
+
+
+def test_pybind_surface_tp_calls_and_transport_batch():
+    """integration/bindings_addon.cpp compiled: `cpp_GpuMieKinGas` takes cpp_MieKinGas' constructor arguments (cpp/bindings.cpp:171-179); the
+    reference's viscosity_tp / thermal_conductivity_tp (north_star) run on device-fed collision integrals and equal the stock build, and the
+    additive `transport_batch` returns the same numbers for a batch of state points in one device pass."""
+    k = _pybind_module()
+    stock, _, Mw, s = _both("CO2,C1,N2")
+    g = k.cpp_GpuMieKinGas(list(stock.m), stock.sigma.tolist(), stock.eps.tolist(), stock.la.tolist(), stock.lr.tolist(), False, False)
+    T, p, x, N = 330.0, 1e5, [0.2, 0.3, 0.5], 2
+    Vm = ref.AVOGADRO * s[0] ** 3 / 0.25
+    dmudn, cp_id, dvdn = synthetic_eos(T, Vm, x, Mw)
+    stock.set_eos(dmudn=dmudn, cp_id=cp_id, p=p, vm=Vm, dvdn=dvdn)
+    g.set_eos_tables(3, dmudn.ravel().tolist(), cp_id.tolist(), p, Vm, dvdn.tolist())
+    eta_tp, lam_tp = g.viscosity_tp(T, p, x, N), g.thermal_conductivity_tp(T, p, x, N)          # specific_volume(T, p, x) of the table EoS is Vm
+    assert abs(eta_tp / stock.viscosity(T, Vm, x, N) - 1) < TOL
+    lam_stock = stock.thermal_conductivity(T, Vm, x, N)
+    if np.isfinite(lam_stock) and np.isfinite(lam_tp):
+        assert abs(lam_tp / lam_stock - 1) < TOL
+    D, DT = g.interdiffusion(T, Vm, x, N), g.thermal_diffusion_coeff(T, Vm, x, N)
+    assert np.max(np.abs(D / stock.interdiffusion(T, Vm, x, N, frame=1) - 1)) < TOL
+    assert np.max(np.abs(DT / stock.thermal_diffusion_coeff(T, Vm, x, N, frame=1) - 1)) < TOL
+    assert g.counters()["cpu_theta_integrand_calls"] == 0
+    # the batched entry point: three state points at two temperatures
+    Tb = np.array([330.0, 330.0, 410.0])
+    Vb = np.array([Vm, 2 * Vm, Vm])
+    xb = np.array([x, [0.5, 0.25, 0.25], x])
+    dm = np.array([synthetic_eos(Tb[i], Vb[i], xb[i], Mw)[0] for i in range(3)])
+    cp = np.array([synthetic_eos(Tb[i], Vb[i], xb[i], Mw)[1] for i in range(3)])
+    out = g.transport_batch(Tb, Vb, xb, N, dm, cp)
+    for i in range(3):
+        d_i, c_i, v_i = synthetic_eos(Tb[i], Vb[i], xb[i], Mw)
+        stock.set_eos(dmudn=d_i, cp_id=c_i, p=p, vm=Vb[i], dvdn=v_i)
+        assert abs(out["viscosity"][i] / stock.viscosity(Tb[i], Vb[i], list(xb[i]), N) - 1) < TOL
+        assert np.max(np.abs(out["D"][i] / stock.interdiffusion(Tb[i], Vb[i], list(xb[i]), N, frame=1) - 1)) < TOL
+        assert np.max(np.abs(out["DT"][i] / stock.thermal_diffusion_coeff(Tb[i], Vb[i], list(xb[i]), N, frame=1) - 1)) < TOL
