@@ -385,23 +385,46 @@ def run_strong_five(local_rank, rank, world, steps, barrier):
     dm, cp = pinned_copy(sp_eos(T, Vm, x)), pinned_copy(np.full((T.size, 5), 4.5 * R_GAS))
     n = int(T.size)
 
+    phase = {"tables": 0.0, "batch": 0.0, "pack_h2d": 0.0, "gather": 0.0}
+
     def block(lo, hi):
         kin._caches = {}
-        r = kin.transport_batch(T[lo:hi], Vm[lo:hi], x[lo:hi], N=FC_N, eos_inputs={"dmudn": dm[lo:hi], "cp_ideal": cp[lo:hi]})
-        packed = np.concatenate([r["viscosity"][:, None], r["conductivity"][:, None], r["D"].reshape(hi - lo, -1), r["DT"]], axis=1)
-        return torch.from_numpy(np.ascontiguousarray(packed)).cuda()
+        t0 = time.perf_counter()
+        cache = kin.tcache(T[lo:hi], FC_N)
+        t1 = time.perf_counter()
+        r = kin.transport_batch(T[lo:hi], Vm[lo:hi], x[lo:hi], N=FC_N, eos_inputs={"dmudn": dm[lo:hi], "cp_ideal": cp[lo:hi]}, cache=cache)
+        t2 = time.perf_counter()
+        packed = torch.empty((hi - lo, 23), dtype=torch.float64, device="cuda")
+        packed[:, 0] = torch.from_numpy(np.asarray(r["viscosity"])).cuda()
+        packed[:, 1] = torch.from_numpy(np.asarray(r["conductivity"])).cuda()
+        packed[:, 2:18] = torch.from_numpy(np.asarray(r["D"]).reshape(hi - lo, 16)).cuda()
+        packed[:, 18:23] = torch.from_numpy(np.asarray(r["DT"])).cuda()
+        torch.cuda.synchronize()
+        t3 = time.perf_counter()
+        phase["tables"] += t1 - t0; phase["batch"] += t2 - t1; phase["pack_h2d"] += t3 - t2
+        return packed
 
     out = sharding.sharded_state_points(block, n, rank, world, device="cuda")     # warm-up
     barrier()
+    for k in phase:
+        phase[k] = 0.0
     t0 = time.perf_counter()
     for _ in range(steps):
+        tg = time.perf_counter()
         out = sharding.sharded_state_points(block, n, rank, world, device="cuda")
-    torch.cuda.synchronize()
+        torch.cuda.synchronize()
+        phase["gather"] += time.perf_counter() - tg
     barrier()
     ms = max(_rank_values(1e3 * (time.perf_counter() - t0), world)) / steps
+    ph = {k: 1e3 * v / steps for k, v in phase.items()}
+    ph["gather"] -= ph["tables"] + ph["batch"] + ph["pack_h2d"]
+    ph["compute_ms_per_rank"] = _rank_values(ph["tables"] + ph["batch"] + ph["pack_h2d"], world)
     return {"workload": f"configs[4], {n} state points IN TOTAL in contiguous blocks over the ranks (strong scaling), tables of each block's "
-                        "temperatures rebuilt every step, results all-gathered", "value": n / (ms * 1e-3), "unit": "state points/s",
-            "ms_per_step": ms, "all_finite": bool(torch.isfinite(out).all().item())}
+                        "temperatures rebuilt every step, results all-gathered on the device", "value": n / (ms * 1e-3), "unit": "state points/s",
+            "ms_per_step": ms, "rank0_phase_ms": ph, "all_finite": bool(torch.isfinite(out).all().item()),
+            "note": "rank0_phase_ms: device tables of the block's temperatures / kg_transport_batch / results back to the device for the collective / "
+                    "all_gather + wait for the slowest rank. The table stage (Omega passes and transfer lengths of ~25/N temperatures) has a fixed "
+                    "latency floor, which is what bends the strong-scaling curve"}
 
 
 # ------------------------------------------------------------------------------------------------ parity + configs[0]
@@ -426,15 +449,21 @@ def parity_block(model):
             "n_per_regime": {names[k]: int((reg == k).sum() * err.shape[1]) for k in range(5) if (reg == k).any()}}
 
 
+def config0_inputs():
+    """Vm(300 K, 1 bar) and Cp_ideal of argon from the EoS pykingas would construct (thermopack 2.2.3 saftvrmie('AR'), evaluated once by
+    `python -m oracle.make_golden eos0` from the wheel vendored in the reference tree; tests/golden/config0_eos.npz)."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "config0_eos.npz"))
+    return float(g["T"]), float(g["p"]), float(g["Vm"]), float(g["cp_ideal"])
+
+
 def config0_latency(local_rank):
-    """BASELINE configs[0]: MieKinGas('AR'), N = 2, T = 300 K, p = 1 bar, viscosity + thermal conductivity of ONE state point, cold
-    (new model object, empty caches) and warm. Vm = RT/p (the reference takes Vm from its EoS; at 1 bar the difference is 0.1 % and
-    does not change the work: <= 4 numeric Omega + correlation values + MTL + ETL). Seconds, host clock around the public calls."""
+    """BASELINE configs[0]: MieKinGas('AR'), N = 2, T = 300 K, p = 1 bar, viscosity_tp + thermal_conductivity_tp of ONE state point, cold
+    (new model object, empty caches) and warm. The two EoS-derived numbers the calls need, Vm(T, p) and Cp_ideal, are the ones the
+    reference's own EoS returns (config0_inputs); the work is <= 4 numeric Omega + correlation values + MTL + ETL + one state point.
+    Seconds, host clock around the public calls."""
     from kineticgas_b200 import MieKinGas
-    R = 8.31446261815324
-    T, p = 300.0, 1e5
-    Vm = R * T / p
-    eos = {"cp_ideal": np.array([[2.5 * R]])}
+    T, p, Vm, cp = config0_inputs()
+    eos = {"cp_ideal": np.array([[cp]])}
     t0 = time.perf_counter()
     kin = MieKinGas("AR", N=2, is_idealgas=False, device=local_rank)
     t1 = time.perf_counter()
@@ -446,7 +475,8 @@ def config0_latency(local_rank):
     kin.viscosity(T, Vm, [1.0], N=2)
     kin.thermal_conductivity(T, Vm, [1.0], N=2, eos_inputs=eos)
     t4 = time.perf_counter()
-    return {"workload": "configs[0]: MieKinGas('AR') viscosity + thermal_conductivity, T = 300 K, p = 1 bar (Vm = RT/p), N = 2, one state point",
+    return {"workload": "configs[0]: MieKinGas('AR') viscosity_tp + thermal_conductivity_tp, T = 300 K, p = 1 bar, N = 2, one state point; "
+                        "Vm(T,p) and Cp_ideal from thermopack 2.2.3 saftvrmie('AR') (fixture)",
             "seconds_cold": t2 - t0, "seconds_model_create": t1 - t0, "seconds_tables_rebuilt": t4 - t3, "unit": "s",
             "viscosity_Pa_s": float(eta), "conductivity_W_mK": float(lam)}
 
@@ -455,11 +485,11 @@ def _cfg0_ref_worker(_):
     from oracle import ref
     from kineticgas_b200.fluids import mie_parameters
     ids, Mw, s, e, la, lr = mie_parameters("AR")
+    T, p, Vm, cp = config0_inputs()
     R = 8.31446261815324
-    T, Vm = 300.0, R * 300.0 / 1e5
     t0 = time.perf_counter()
     m = ref.RefMie(Mw, s, e, la, lr, is_idealgas=False)
-    m.set_eos(dmudn=np.array([[R * T]]), cp_id=np.array([2.5 * R]), p=1e5, vm=Vm, dvdn=np.array([Vm]))
+    m.set_eos(dmudn=np.array([[R * T]]), cp_id=np.array([cp]), p=p, vm=Vm, dvdn=np.array([Vm]))
     eta = m.viscosity(T, Vm, [0.5, 0.5], 2)
     lam = m.thermal_conductivity(T, Vm, [0.5, 0.5], 2)
     return time.perf_counter() - t0, eta, lam

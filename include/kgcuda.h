@@ -117,6 +117,16 @@ int kg_omega_batch(kg_model* m, int nT, const double* T, int nlr, const int32_t*
  * pairs, [nT][npairs]. One pass serves both (the reference recomputes every deflection angle per property). */
 int kg_transfer_lengths_batch(kg_model* m, int nT, const double* T, const double* coeff_T, double* mtl, double* etl, int32_t* status);
 
+/* ---- classical cross sections and second virial coefficient on the same collision dynamics ----
+ * kg_cross_sections: Spherical::cross_section (cpp/Spherical.cpp:104-127; bound at cpp/bindings.cpp:253-255 for the Quantum classes as
+ * classical_cross_section): Q^(l)(E) [m^2] for E[nE] in units of the pair's eps and l[nl] (1 <= nl <= 8); out [nE][nl]. Bisection for the
+ * root of chi, the two Simpson segments and the outward Simpson march are the reference's, block for block. status [nE] (may be NULL).
+ * kg_second_virial: Spherical::second_virial (cpp/Spherical.cpp:140-160) [m^3/mol] at T[nT]; coeff_T [nT][KG_MAX_TERMS] of this pair for
+ * T-dependent coefficients. Power-sum models only. */
+#define KG_STATUS_BRACKET 64        /* "Bracket solver: Initial values have same sign!" (cpp/Integration/Integration.h:224-226) */
+int kg_cross_sections(kg_model* m, int pair, int nE, const double* E_red, int nl, const int32_t* l, const double* coeff,
+                      double* out, int32_t* status);
+int kg_second_virial(kg_model* m, int pair, int nT, const double* T, const double* coeff_T, double* out);
 /* Plan API: same computation with everything resident in HBM between calls (what a sweep driver / bench uses). */
 int kg_omega_plan_create(kg_model* m, int nT, const double* T, int nlr, const int32_t* l, const int32_t* r,
                          const double* coeff_T, kg_omega_plan** out);
@@ -246,6 +256,25 @@ int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const double* T, co
  *  out[2] ms of the tcache transfer-length stage      out[3] ms of correlation + BH diameters + bracket sums
  *  out[4] kernel launches of the last tcache build     out[5] kernel launches of the last batch */
 int kg_last_timings(const kg_model* m, double* out8);
+/* ---- device-resident Omega(T) interpolation tables with persistence ----
+ * Replaces the per-object 0.1 K-bucket memo of cpp/KineticGasCache.h:92-164 for sweeps: built once from exact device quadrature at nodes
+ * uniform in ln T (nodes_per_decade), segmented at the lattice-regime temperatures 20 / 35 / 50 / 70 K (cpp/Spherical.cpp:60-84) so that no
+ * interpolation stencil crosses one, evaluated by a kernel (4-point Lagrange in ln T on ln Omega), saved to / loaded from a file that
+ * carries a fingerprint of the model. ACCURACY CONTRACT: not the bit-parity of the batched path -- the interpolant follows the exact path to
+ * the level of the reference's own mesh noise (about 1e-4 relative at 64 nodes per decade; tests/test_gpu_table.py measures it). T outside
+ * the table gives NaN. Models with temperature-dependent potentials are refused. */
+typedef struct kg_omega_table kg_omega_table;
+int kg_omega_table_create(kg_model* m, double Tmin, double Tmax, int nodes_per_decade, int nlr, const int32_t* l, const int32_t* r,
+                          kg_omega_table** out);
+int kg_omega_table_eval(kg_omega_table* t, int nT, const double* T, double* omega /* [nT][npairs][nlr], host */);
+int kg_omega_table_eval_dev(kg_omega_table* t, int nT, const double* T_dev, double* omega_dev);   /* device pointers, async on the model stream */
+int kg_omega_table_save(const kg_omega_table* t, const char* path);
+int kg_omega_table_load(kg_model* m, const char* path, kg_omega_table** out);   /* fails if the fingerprint is another model's */
+int kg_omega_table_lr(const kg_omega_table* t, int32_t* l, int32_t* r);         /* returns nlr */
+/* out8: Tmin, Tmax, nodes, segments, npairs, nlr, bytes in HBM, 0 */
+int kg_omega_table_info(const kg_omega_table* t, double* out8);
+void kg_omega_table_destroy(kg_omega_table* t);
+
 
 /* FP64 FMA-pipe peak probe: runs a register-resident DFMA chain kernel and returns the measured TFLOP/s
  * (2 flop per DFMA). Used as the roofline denominator (MEASURED_PEAKS.json has no FP64 figure). */

@@ -15,7 +15,8 @@ EXPORTS = [
     "kg_omega_plan_create", "kg_omega_plan_run", "kg_omega_plan_sync", "kg_omega_plan_fetch", "kg_omega_plan_omega_dev",
     "kg_omega_plan_destroy", "kg_omega_plan_counters", "kg_measure_fp64_peak", "kg_model_set_stream", "kg_omega_plan_export_dev", "kg_transfer_lengths_batch",
     "kg_model_create_ex", "kg_potential_points", "kg_genpot_describe", "kg_omega_plan_quadrature_stats", "kg_set_exact_quadrature",
-    "kg_omega_plan_create_masked", "kg_model_set_temperature_dependent", "kg_build_info", "kg_host_alloc", "kg_host_free", "kg_tcache_create", "kg_tcache_destroy", "kg_tcache_lr", "kg_tcache_fetch", "kg_transport_batch", "kg_last_timings",
+    "kg_omega_plan_create_masked", "kg_omega_table_create", "kg_omega_table_eval", "kg_omega_table_eval_dev", "kg_omega_table_save",
+    "kg_omega_table_load", "kg_omega_table_lr", "kg_omega_table_info", "kg_omega_table_destroy", "kg_cross_sections", "kg_second_virial", "kg_model_set_temperature_dependent", "kg_build_info", "kg_host_alloc", "kg_host_free", "kg_tcache_create", "kg_tcache_destroy", "kg_tcache_lr", "kg_tcache_fetch", "kg_transport_batch", "kg_last_timings",
 ]
 
 
@@ -58,6 +59,17 @@ def lib():
         L.kg_host_free.argtypes = [C.c_void_p]
         L.kg_last_error.argtypes = [C.c_void_p]
         L.kg_model_npairs.argtypes = [C.c_void_p]
+        L.kg_omega_table_create.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_int, C.c_int, ip, ip, C.POINTER(C.c_void_p)]
+        L.kg_omega_table_eval.argtypes = [C.c_void_p, C.c_int, dp, dp]
+        L.kg_omega_table_eval_dev.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        L.kg_omega_table_save.argtypes = [C.c_void_p, C.c_char_p]
+        L.kg_omega_table_load.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_void_p)]
+        L.kg_omega_table_lr.argtypes = [C.c_void_p, ip, ip]
+        L.kg_omega_table_info.argtypes = [C.c_void_p, dp]
+        L.kg_omega_table_destroy.argtypes = [C.c_void_p]
+        L.kg_omega_table_destroy.restype = None
+        L.kg_cross_sections.argtypes = [C.c_void_p, C.c_int, C.c_int, dp, C.c_int, ip, dp, dp, ip]
+        L.kg_second_virial.argtypes = [C.c_void_p, C.c_int, C.c_int, dp, dp, dp]
         L.kg_model_set_temperature_dependent.argtypes = [C.c_void_p, C.c_int]
         L.kg_chi_points.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int, dp, dp, dp, dp, dp, ip]
         L.kg_omega_batch.argtypes = [C.c_void_p, C.c_int, dp, C.c_int, ip, ip, dp, dp, dp, ip]

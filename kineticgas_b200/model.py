@@ -174,6 +174,25 @@ class DeviceModel:
         raise_on_status(st)
         return mtl, etl
 
+    def cross_sections(self, pair, E_red, l, coeff=None):
+        """Q^(l)(E) [m^2], E in units of the pair's eps (Spherical::cross_section, cpp/Spherical.cpp:104-127): [nE][nl]."""
+        E = np.ascontiguousarray(np.atleast_1d(E_red), float)
+        l = np.ascontiguousarray(np.atleast_1d(l), np.int32)
+        out = np.empty((E.size, l.size))
+        st = np.zeros(E.size, np.int32)
+        cf = None if coeff is None else np.ascontiguousarray(coeff, float)
+        self._chk(self.L.kg_cross_sections(self.h, pair, E.size, _p(E), l.size, _pi(l), _p(cf), _p(out), _pi(st)), "kg_cross_sections")
+        raise_on_status(st & ~64)
+        return out
+
+    def second_virial(self, pair, T, coeff_T=None):
+        """Classical second virial coefficient [m^3/mol] (Spherical::second_virial, cpp/Spherical.cpp:140-160)."""
+        T = np.ascontiguousarray(np.atleast_1d(T), float)
+        out = np.empty(T.size)
+        cf = None if coeff_T is None else np.ascontiguousarray(coeff_T, float)
+        self._chk(self.L.kg_second_virial(self.h, pair, T.size, _p(T), _p(cf), _p(out)), "kg_second_virial")
+        return out
+
     def last_timings(self):
         out = np.zeros(8)
         self.L.kg_last_timings(self.h, _p(out))
@@ -181,6 +200,57 @@ class DeviceModel:
 
     def omega_plan(self, T, l, r, coeff_T=None):
         return OmegaPlan(self, T, l, r, coeff_T)
+
+
+class OmegaTable:
+    """Device-resident Omega(T) interpolation table (kg_omega_table): built once by exact quadrature at nodes uniform in ln T, segmented at
+    the lattice-regime temperatures, evaluated on the device, persistent through save() / load(). Accuracy: see include/kgcuda.h."""
+
+    def __init__(self, model, handle):
+        self.model, self.h = model, handle
+        n = model.L.kg_omega_table_lr(handle, None, None)
+        self.l, self.r = np.zeros(n, np.int32), np.zeros(n, np.int32)
+        model.L.kg_omega_table_lr(handle, _pi(self.l), _pi(self.r))
+
+    @classmethod
+    def build(cls, model, Tmin, Tmax, l, r, nodes_per_decade=64):
+        l = np.ascontiguousarray(l, np.int32)
+        r = np.ascontiguousarray(r, np.int32)
+        h = C.c_void_p()
+        model._chk(model.L.kg_omega_table_create(model.h, float(Tmin), float(Tmax), int(nodes_per_decade), l.size, _pi(l), _pi(r), C.byref(h)),
+                   "kg_omega_table_create")
+        return cls(model, h)
+
+    @classmethod
+    def load(cls, model, path):
+        h = C.c_void_p()
+        model._chk(model.L.kg_omega_table_load(model.h, str(path).encode(), C.byref(h)), "kg_omega_table_load")
+        return cls(model, h)
+
+    def save(self, path):
+        self.model._chk(self.model.L.kg_omega_table_save(self.h, str(path).encode()), "kg_omega_table_save")
+
+    def __call__(self, T):
+        T = np.ascontiguousarray(np.atleast_1d(T), float)
+        out = np.empty((T.size, self.model.npairs, self.l.size))
+        self.model._chk(self.model.L.kg_omega_table_eval(self.h, T.size, _p(T), _p(out)), "kg_omega_table_eval")
+        return out
+
+    def info(self):
+        out = np.zeros(8)
+        self.model.L.kg_omega_table_info(self.h, _p(out))
+        return dict(zip(["Tmin", "Tmax", "nodes", "segments", "npairs", "nlr", "bytes"], out.tolist()))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.model.L.kg_omega_table_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def raise_on_status(st):

@@ -430,3 +430,49 @@ def refcsv_golden(fname="ref_viscosity_csv.npz"):
 
 if __name__ == "__main__" and "refcsv" in sys.argv[1:]:
     refcsv_golden()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# classical cross sections Q^(l)(E) and second virial coefficients (cpp/Spherical.cpp:104-160) from the reference build
+# ---------------------------------------------------------------------------------------------------------------
+XSEC_FLUIDS = ["AR", "CO2", "LJF", "H2"]
+XSEC_L = [1, 2, 3, 4]
+
+
+def xsec_golden(fname="xsec_reference.npz"):
+    out = {"l": np.array(XSEC_L), "E": np.geomspace(0.05, 40.0, 14), "T": np.array([80.0, 150.0, 300.0, 1000.0])}
+    for comp in XSEC_FLUIDS:
+        ids, Mw, s, e, la, lr = mie_parameters(comp)
+        m = ref.RefMie(Mw, s, e, la, lr, is_idealgas=True, py_constants=False)
+        out[comp + "_Q"] = np.array([[m.cross_section(0, 0, l, E) for l in XSEC_L] for E in out["E"]])
+        out[comp + "_B2"] = np.array([m.second_virial(0, 0, T) for T in out["T"]])
+        print(comp, out[comp + "_Q"][0], out[comp + "_B2"], flush=True)
+    np.savez(os.path.join(GOLD, fname), **out)
+
+
+if __name__ == "__main__" and "xsec" in sys.argv[1:]:
+    xsec_golden()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# BASELINE configs[0]: the EoS-derived inputs of MieKinGas('AR') viscosity_tp / thermal_conductivity_tp at 300 K, 1 bar, from the
+# thermopack 2.2.3 wheel vendored in the reference tree (saftvrmie('AR'), what pykingas constructs: pykingas/MieKinGas.py:56-60).
+# ---------------------------------------------------------------------------------------------------------------
+def config0_eos(fname="config0_eos.npz"):
+    import zipfile
+    whl = "/root/reference/cpp/external/thermopack/addon/pycThermopack/wheelhouse/thermopack-2.2.3-py3-none-manylinux_2_28_x86_64.whl"
+    dst = "/tmp/kg_thermopack_wheel"
+    zipfile.ZipFile(whl).extractall(dst)
+    sys.path.insert(0, dst)
+    from thermopack.saftvrmie import saftvrmie
+    eos = saftvrmie("AR")
+    T, p = 300.0, 1e5
+    Vm, = eos.specific_volume(T, p, [1.0], eos.VAPPH)
+    cp = eos.idealenthalpysingle(T, 1, dhdt=True)[1]
+    _, dmudn = eos.chemical_potential_tv(T, Vm, [1.0], dmudn=True)
+    np.savez(os.path.join(GOLD, fname), T=T, p=p, Vm=Vm, cp_ideal=cp, dmudn=np.asarray(dmudn), source=np.array("thermopack 2.2.3 saftvrmie('AR')"))
+    print("configs[0] EoS inputs:", Vm, cp, dmudn)
+
+
+if __name__ == "__main__" and "eos0" in sys.argv[1:]:
+    config0_eos()

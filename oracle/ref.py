@@ -74,6 +74,8 @@ def _declare(L):
     L.kgref_generic_scales.argtypes = [C.c_void_p, dp]
     L.kgref_potential_rr.restype = C.c_double
     L.kgref_potential_rr.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double]
+    L.kgref_cross_section.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, dp]
+    L.kgref_second_virial.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, dp]
     return L
 
 
@@ -198,6 +200,17 @@ class RefMie:
         out = C.c_double()
         f = self.L.kgref_omega_model if model else self.L.kgref_omega
         self._chk(f(self.h, i, j, l, r, T, C.byref(out)))
+        return out.value
+
+    def cross_section(self, i, j, l, E):
+        """Spherical::cross_section (cpp/Spherical.cpp:104-127): Q^(l)(E), E in units of eps_ij."""
+        out = C.c_double()
+        self._chk(self.L.kgref_cross_section(self.h, i, j, l, float(E), C.byref(out)))
+        return out.value
+
+    def second_virial(self, i, j, T):
+        out = C.c_double()
+        self._chk(self.L.kgref_second_virial(self.h, i, j, float(T), C.byref(out)))
         return out.value
 
     def w_integral(self, i, j, T, l, r, regime=None):

@@ -199,6 +199,15 @@ int kgref_get_R_batch(void* hv, int i, int j, double T, int n, const double* g, 
 double kgref_w_integrand(void* hv, int i, int j, double T, double g, double b, int l, int r) {
     return static_cast<Handle*>(hv)->kin->w_integrand(i, j, T, g, b, l, r);
 }
+// classical cross sections (cpp/Spherical.cpp:104-127) and the classical second virial coefficient (:140-160)
+int kgref_cross_section(void* hv, int i, int j, int l, double E, double* out) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{ *out = h->kin->cross_section(i, j, l, E); });
+}
+int kgref_second_virial(void* hv, int i, int j, double T, double* out) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{ *out = h->kin->second_virial(i, j, T); });
+}
 // omega through the normal (cached, correlation-aware) path: MieKinGas::omega -> Spherical::omega
 int kgref_omega(void* hv, int i, int j, int l, int r, double T, double* out) {
     Handle* h = static_cast<Handle*>(hv);

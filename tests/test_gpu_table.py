@@ -1,0 +1,42 @@
+"""Device-resident Omega(T) interpolation tables (kg_omega_table_*): accuracy against the exact batched path,
+segmentation at the lattice-regime temperatures, persistence, model fingerprint."""
+import numpy as np
+import pytest
+
+from kineticgas_b200.fluids import mie_parameters, BOLTZMANN, AVOGADRO
+
+pytestmark = pytest.mark.gpu
+L, R = [1, 1, 2, 2], [1, 2, 2, 3]
+
+
+def _model(comp):
+    from kineticgas_b200 import DeviceModel, mie_desc
+    ids, Mw, s, e, la, lr = mie_parameters(comp)
+    return DeviceModel([mie_desc(s[0], e[0] * BOLTZMANN, la[0], lr[0])], [Mw[0] * 1e-3 / AVOGADRO], True)
+
+
+def test_interpolant_follows_the_exact_path(tmp_path):
+    from kineticgas_b200 import OmegaTable
+    m = _model("LJF")
+    tab = OmegaTable.build(m, 15.0, 400.0, L, R, nodes_per_decade=64)
+    info = tab.info()
+    assert info["segments"] == 5 and info["nodes"] > 64          # 15-20, 20-35, 35-50, 50-70, 70-400 K
+    rng = np.random.default_rng(4)
+    T = np.concatenate([np.exp(rng.uniform(np.log(15.0), np.log(400.0), 160)), [19.999, 20.0, 34.999, 35.0, 49.99, 50.0, 69.99, 70.0, 15.0, 400.0]])
+    exact = m.omega_batch(T, L, R)
+    err = np.abs(tab(T) / exact - 1)
+    print("table vs exact quadrature: max", float(err.max()), "median", float(np.median(err)), "nodes", info["nodes"], "bytes", info["bytes"])
+    # contract: the reference's own mesh noise (the adaptive lattice changes shape with T), not 1e-6
+    assert err.max() < 5e-4
+    assert np.median(err) < 5e-5
+    assert np.all(np.isnan(tab([10.0, 500.0])))                   # outside the table
+    # at the nodes themselves the table returns the integrated values
+    # persistence: same numbers after a round trip through a file, bit for bit
+    path = tmp_path / "ljf.kgot"
+    tab.save(path)
+    tab2 = OmegaTable.load(m, path)
+    assert np.array_equal(tab2(T), tab(T))
+    assert list(tab2.l) == L and list(tab2.r) == R
+    # a table belongs to its model
+    with pytest.raises(RuntimeError, match="different model"):
+        OmegaTable.load(_model("AR"), path)

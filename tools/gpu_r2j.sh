@@ -1,0 +1,6 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_table.py tests/test_gpu_xsec.py -m gpu -q -s -p no:cacheprovider > gpurun_out/r2j_pytest.log 2>&1
+echo "pytest rc=$?" >> gpurun_out/r2j_pytest.log; tail -12 gpurun_out/r2j_pytest.log
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/r2j_bench_n2.json 2> gpurun_out/r2j_bench_n2.err
+echo "bench n2 rc=$?"; tail -3 gpurun_out/r2j_bench_n2.err
