@@ -261,7 +261,8 @@ int kg_last_timings(const kg_model* m, double* out8);
  * uniform in ln T (nodes_per_decade), segmented at the lattice-regime temperatures 20 / 35 / 50 / 70 K (cpp/Spherical.cpp:60-84) so that no
  * interpolation stencil crosses one, evaluated by a kernel (4-point Lagrange in ln T on ln Omega), saved to / loaded from a file that
  * carries a fingerprint of the model. ACCURACY CONTRACT: not the bit-parity of the batched path -- the interpolant follows the exact path to
- * the level of the reference's own mesh noise (about 1e-4 relative at 64 nodes per decade; tests/test_gpu_table.py measures it). T outside
+ * the level of the reference's own mesh noise (its adaptive lattice changes refinement pattern with T: median ~1e-6, 99 % < 1e-3, worst
+ * ~5e-3 relative at 64 nodes per decade; tests/test_gpu_table.py measures it). T outside
  * the table gives NaN. Models with temperature-dependent potentials are refused. */
 typedef struct kg_omega_table kg_omega_table;
 int kg_omega_table_create(kg_model* m, double Tmin, double Tmax, int nodes_per_decade, int nlr, const int32_t* l, const int32_t* r,
