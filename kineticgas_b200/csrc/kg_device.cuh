@@ -259,6 +259,156 @@ __device__ double get_R(const Lane<NT>& c, double g, int& status) {
     return R;
 }
 
+// ---- get_R for integer exponents, written for the set-up kernel (every lane of the grid is in here) -------------------------
+// Same algorithm, same sequence of iterates as get_R above (cpp/Spherical.cpp:358-435); what changes is the arithmetic around it:
+// the lane context stays in registers (nothing is called out of line on the common path), the powers of one evaluation share a
+// squaring chain, 1/r and f/f' use a MUFU reciprocal seed with two Newton steps (1-2 ulp instead of correctly rounded, no range
+// check), and the shrink loop carries (b/r0)^2 along instead of dividing. Iterates therefore differ from the reference's in the last
+// bits only; the step criterion sees the same values except on a knife edge, where R moves by the convergence noise (< 1e-12).
+// Everything past the first Newton attempt (its failure modes) goes to the general code.
+__device__ __forceinline__ double rcp_fast(double x) {
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    double e = fma(-x, y, 1.0);
+    y = fma(y, e, y);
+    e = fma(-x, y, 1.0);
+    return fma(y, e, y);
+}
+
+template<int NT>
+struct LaneIP {
+    double Bt[NT];
+    int n[NT];
+    int nbits;         // bits of the largest exponent
+    double b, two_over_b;
+};
+
+template<int NT>
+__device__ __forceinline__ void ip_powers(const LaneIP<NT>& c, double inv, double (&p)[NT]) {
+#pragma unroll
+    for (int t = 0; t < NT; t++) p[t] = c.Bt[t];
+    double x = inv;
+    for (int bit = 0; bit < c.nbits; bit++) {
+#pragma unroll
+        for (int t = 0; t < NT; t++) if ((c.n[t] >> bit) & 1) p[t] *= x;
+        x *= x;
+    }
+}
+template<int NT>
+__device__ __forceinline__ double ip_rootfun(const LaneIP<NT>& c, double ri) {
+    const double inv = rcp_fast(ri);
+    double p[NT];
+    ip_powers<NT>(c, inv, p);
+    double u = 0.0;
+#pragma unroll
+    for (int t = 0; t < NT; t++) u += p[t];
+    const double q = c.b * inv;
+    return fma(q, q, u) - 1.0;
+}
+template<int NT>
+__device__ __forceinline__ void ip_rootfun_d(const LaneIP<NT>& c, double ri, double& f, double& df) {
+    const double inv = rcp_fast(ri);
+    double p[NT];
+    ip_powers<NT>(c, inv, p);
+    double u = 0.0, du = 0.0;
+#pragma unroll
+    for (int t = 0; t < NT; t++) { u += p[t]; du = fma(-(double) c.n[t], p[t], du); }
+    const double q = c.b * inv, q2 = q * q;
+    f = (u + q2) - 1.0;
+    df = fma(du, inv, -c.two_over_b * (q2 * q));
+}
+template<int NT>
+__device__ __forceinline__ double ip_newton(const LaneIP<NT>& c, double x0, double dtol, int& ierr) {
+    int niter = 0;
+    double prev_x, f, df;
+    do {
+        prev_x = x0;
+        ip_rootfun_d<NT>(c, x0, f, df);
+        x0 = fma(-f, rcp_fast(df), x0);
+        if (niter++ > 50) { ierr = 1; return x0; }
+    } while (fabs(x0 - prev_x) > dtol);
+    if (isnan(x0)) { ierr = 2; return x0; }
+    if (isinf(x0)) { ierr = 3; return x0; }
+    return x0;
+}
+
+// the rare remainder of get_R: the first Newton attempt failed
+template<int NT>
+__device__ __noinline__ double get_R_after_failure(const Lane<NT>& c, double r0, double r1, double f0, double f1, double bracket_dtol, int& status) {
+    const double newton_dtol = 1e-6;
+    int ierr = 0;
+    double R = newton_usafe<NT>(c, r1, newton_dtol, ierr);
+    if (ierr != 0) { ierr = 0; R = newton_usafe<NT>(c, 0.5 * (r0 + r1), newton_dtol, ierr); }
+    int niter = 0;
+    while (ierr != 0) {
+        const double prev_r0 = r0;
+        while ((prev_r0 == r0) && (bracket_dtol > newton_dtol)) {
+            if (fabs(r1 - r0) < bracket_dtol) bracket_dtol /= 2;
+            bracket_root_usafe<NT>(c, r0, r1, f0, f1, bracket_dtol);
+        }
+        if (bracket_dtol < newton_dtol) { R = r0; break; }
+        ierr = 0;
+        R = newton_usafe<NT>(c, r0, newton_dtol, ierr);
+        if (niter++ > 50) { status |= 1; return nan(""); }
+    }
+    return R;
+}
+
+template<int NT>
+__device__ __forceinline__ double get_R_ip(const Lane<NT>& lane, double g, int& status) {
+    if ((lane.b < 1e-5) || (g < 1e-6)) return get_R0<NT>(lane);
+    LaneIP<NT> c;
+    int nmax = 1;
+#pragma unroll
+    for (int t = 0; t < NT; t++) { c.Bt[t] = lane.Bt[t]; c.n[t] = (int) lane.lam[t]; nmax = max(nmax, c.n[t]); }
+    c.nbits = 32 - __clz(nmax);
+    c.b = lane.b; c.two_over_b = 2.0 / lane.b;
+    double r0, r1, bracket_dtol;
+    if (c.b > 1) { r0 = r1 = c.b; bracket_dtol = 0.1; }
+    else { r0 = r1 = 1; bracket_dtol = 0.05; }
+    double f0 = ip_rootfun<NT>(c, r0);
+    double f1 = f0;
+    if (f0 < 0) {                                              // r0 *= 0.95 until f(r0) >= 0 (cpp/Spherical.cpp:381-384)
+        double p[NT], F[NT];
+        const double inv0 = rcp_fast(r0);
+        ip_powers<NT>(c, inv0, p);
+        {   // F[t] = 0.95^-n[t] on the same chain
+            LaneIP<NT> one = c;
+#pragma unroll
+            for (int t = 0; t < NT; t++) one.Bt[t] = 1.0;
+            ip_powers<NT>(one, 1.0 / 0.95, F);
+        }
+        double q2 = (c.b * inv0) * (c.b * inv0);
+        const double k2 = (1.0 / 0.95) * (1.0 / 0.95);
+        int guard = 0;
+        while (f0 < 0 && guard++ < 4000) {
+            r0 *= 0.95;
+            q2 *= k2;
+            double u = 0.0;
+#pragma unroll
+            for (int t = 0; t < NT; t++) { p[t] *= F[t]; u += p[t]; }
+            f0 = (u + q2) - 1.0;
+        }
+    }
+    if (r1 - r0 > bracket_dtol) {                              // cpp/Integration/Integration.cpp:494-510
+        while (fabs(r0 - r1) > bracket_dtol) {
+            const double xm = 0.5 * (r0 + r1);
+            const double fm = ip_rootfun<NT>(c, xm);
+            if (f0 * fm > 0) { r0 = xm; f0 = fm; }
+            else { r1 = xm; f1 = fm; }
+        }
+        if (fabs(f0) > fabs(f1)) {
+            double t = r0; r0 = r1; r1 = t;
+            t = f0; f0 = f1; f1 = t;
+        }
+    }
+    if (fabs(f0) < 1e-8) return r0;
+    int ierr = 0;
+    const double R = ip_newton<NT>(c, r0, 1e-6, ierr);
+    if (ierr == 0) return R;
+    return get_R_after_failure<NT>(lane, r0, r1, f0, f1, bracket_dtol, status);
+}
+
 // MUFU.RSQ64H seed (max relative error ~2^-22); negative -> NaN, +0 -> +Inf, which is exactly what the stop rule needs
 __device__ __forceinline__ double rsqrt_seed(double x) {
     double y;
@@ -717,7 +867,7 @@ template<int NT>
 __device__ void lane_setup(const PairParams& pp, const double* coeff, double T, double g, double b, double (&A)[NT], double& c2, int& status) {
     Lane<NT> c;
     make_lane<NT>(c, pp, coeff, T, g, b);
-    const double R = get_R<NT>(c, g, status);
+    const double R = c.ipath ? get_R_ip<NT>(c, g, status) : get_R<NT>(c, g, status);
     lane_powers<NT>(c, 1.0 / R, A);
     const double q = R / b;
     c2 = q * q;
