@@ -280,11 +280,20 @@ struct LaneIP {
     double Bt[NT];
     int n[NT];
     int nbits;         // bits of the largest exponent
+    bool lj;           // exponents (12, 6)
     double b, two_over_b;
 };
 
 template<int NT>
 __device__ __forceinline__ void ip_powers(const LaneIP<NT>& c, double inv, double (&p)[NT]) {
+    if constexpr (NT == 2) {
+        if (c.lj) {                                            // 12-6 (Lennard-Jones and the default Mie): five multiplications, no exponent loop
+            const double x2 = inv * inv, x6 = (x2 * x2) * x2;
+            p[1] = c.Bt[1] * x6;
+            p[0] = c.Bt[0] * (x6 * x6);
+            return;
+        }
+    }
 #pragma unroll
     for (int t = 0; t < NT; t++) p[t] = c.Bt[t];
     double x = inv;
@@ -362,7 +371,8 @@ __device__ __forceinline__ double get_R_ip(const Lane<NT>& lane, double g, int& 
 #pragma unroll
     for (int t = 0; t < NT; t++) { c.Bt[t] = lane.Bt[t]; c.n[t] = (int) lane.lam[t]; nmax = max(nmax, c.n[t]); }
     c.nbits = 32 - __clz(nmax);
-    c.b = lane.b; c.two_over_b = 2.0 / lane.b;
+    c.lj = (NT == 2) && (c.n[0] == 12) && (c.n[NT - 1] == 6);
+    c.b = lane.b; c.two_over_b = 2.0 * rcp_fast(lane.b);
     double r0, r1, bracket_dtol;
     if (c.b > 1) { r0 = r1 = c.b; bracket_dtol = 0.1; }
     else { r0 = r1 = 1; bracket_dtol = 0.05; }

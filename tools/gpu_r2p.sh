@@ -1,0 +1,8 @@
+#!/bin/bash
+mkdir -p gpurun_out
+bash tools/gpu_quick.sh base
+KGCUDA_LIB=$PWD/_variants/libkgcuda_mesh2.so bash tools/gpu_quick.sh mesh2
+for p in 3 4; do
+timeout 600 ncu --set full --import-source on --clock-control none --kernel-name regex:mesh_level --launch-skip $p --launch-count 1 \
+    -o gpurun_out/r2p_mesh_p$p -f python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-state-points --no-extra-configs > /dev/null 2> gpurun_out/r2p_ncu.err
+done
