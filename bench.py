@@ -35,6 +35,33 @@ F_NODE = 98.0    # nominal FP64 flop per tanh-sinh node for a 2-term (Mie/LJ) po
 METRIC = "collision integrals/s"
 
 
+def hbm_peak():
+    """(GB/s, source): MEASURED_PEAKS.json (driver-written copy bandwidth of this pool's B200s), else the profiling recipe's fallback."""
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs"
+    except Exception:
+        return 6550.0, "fallback of B200_PROFILING.md (MEASURED_PEAKS.json absent)"
+
+
+# DRAM bytes per state point moved by the state kernels, from ncu --set full captures of this build (dram__bytes_read.sum + dram__bytes_write.sum
+# of rdf_kernel + state_kernel over the launch's points; profiles/r2_summary.md)
+STATE_TRAFFIC_PER_POINT = {"state_points": None, "five_component": 3360.0}
+
+
+def state_roofline(leg, n_points, h2d, d2h, ms_kernels):
+    """The state-point kernels against the HBM roofline: algorithmic bytes = the caller's inputs and outputs of one step (what h2d/d2h count;
+    per-temperature tables are shared by ~100-1500 points and stay in L2), over the summed duration of the rdf + state kernels."""
+    peak, src = hbm_peak()
+    ach = (h2d + d2h) / (ms_kernels * 1e-3) / 1e9 if ms_kernels > 0 else 0.0
+    tpp = STATE_TRAFFIC_PER_POINT.get(leg)
+    return {"bound": "hbm", "kernel": "rdf_kernel + state_kernel<N nc> (one thread per state point: RDF at contact, Sonine systems assembled in shared "
+            "memory, LU in Eigen's pivot order, properties)", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+            "traffic": None if tpp is None else tpp * n_points, "algorithmic_bytes_per_step": int(h2d + d2h), "kernel_ms_per_step": ms_kernels,
+            "peak_source": src,
+            "note": "far below the HBM roofline by construction: a state point is ~2e4 FP64 operations (matrix assembly + two dense LU solves of "
+                    "order N nc) on ~0.5 kB of input; the kernels are latency / FP64-issue bound, the fraction is reported for completeness"}
+
+
 def grid(n_gpus, rank):
     tstar = np.geomspace(0.3, 100.0, NT_PER_GPU * n_gpus)[rank::n_gpus]
     return 30.0 * tstar
@@ -812,6 +839,7 @@ def main():
                                    "e2e": {"value": n_sp / (sp["ms_max"] * 1e-3), "unit": "state points/s", "h2d_bytes_per_step": sp["h2d"],
                                            "d2h_bytes_per_step": sp["d2h"]},
                                    "all_finite": sp["finite"],
+                                   "roofline": state_roofline("state_points", sp["n"], sp["h2d"], sp["d2h"], float(np.mean(sp["ms_state_kernels"]))),
                                    "note": "host buffers in and out through kg_tcache_create + kg_transport_batch (the e2e path); EoS inputs (dmu/dn) "
                                            "are synthetic arrays prepared outside the timed region"}
             if not args.no_cpu_baseline:
@@ -832,6 +860,7 @@ def main():
                                      "e2e": {"value": n_fc / (fc["ms_max"] * 1e-3), "unit": "state points/s", "h2d_bytes_per_step": fc["h2d"],
                                              "d2h_bytes_per_step": fc["d2h"]},
                                      "all_finite": fc["finite"],
+                                     "roofline": state_roofline("five_component", fc["n"], fc["h2d"], fc["d2h"], fc["stage_ms"]["ms_state_kernels"]),
                                      "note": "host buffers in and out through kg_tcache_create + kg_transport_batch; EoS inputs (dmu/dn, Cp_id) are synthetic "
                                              "arrays prepared outside the timed region"}
         if not args.no_cpu_baseline:

@@ -63,6 +63,7 @@ struct kg_model {
     std::multimap<size_t, void*> pool_free;
     std::unordered_map<void*, size_t> pool_live;
     size_t pool_cached = 0;
+    bool tl_warp_search = false;        // KG_TL_WARP_SEARCH=1: one warp per b_mid / b_max search (comparison runs; measured slower)
     int* h_pinned = nullptr;            // 16 ints of pinned host memory for the small D2H reads of the pass loop
     cudaError_t dmalloc_bytes(void** out, size_t bytes) {
         bytes = (std::max<size_t>(bytes, 1) + 511) & ~(size_t) 511;

@@ -87,6 +87,86 @@ __global__ void __launch_bounds__(256) tl_search_kernel(const PairParams* __rest
     if (st) atomicOr(&status[it], st);
 }
 
+// The same searches with one WARP per (pair, T, g-node), for the power-law potentials (opt-in: KG_TL_WARP_SEARCH=1). The searches are
+// sequential in b and a transfer-length call has only nT x 26 of them per pair, so one lane per search leaves the GPU mostly empty;
+// here all 32 lanes follow the same search and share each theta integral node by node (theta_integral_warp). MEASURED SLOWER than the
+// lane version on B200 (configs[2]: TL stage 1.26 ms against 0.90 ms; configs[4]: 1.80 against 1.16 ms): the shared sum visits every
+// node (the lane version's strided sum visits 9 %), and 63 nodes per lane plus the reductions of each run of 256 is no shorter a chain
+// than ~190 strided nodes in one lane. Kept for comparison runs; the lane kernel is the product path.
+template<int NT>
+__global__ void __launch_bounds__(256) tl_search_warp_kernel(const PairParams* __restrict__ pairs, const double* const* __restrict__ rows_by_pair,
+                                                             const TlItem* __restrict__ items, int pair0, int nitems, const double* __restrict__ coeff_pool,
+                                                             const double* __restrict__ gnodes, double* __restrict__ ilim,
+                                                             double* __restrict__ bmid_out, double* __restrict__ bmax_out, int* __restrict__ status) {
+    if constexpr (NT != 1) {
+    extern __shared__ double srows[];
+    __shared__ PairParams pp;
+    constexpr int W = 2 + NT;
+    const int pair = pair0 + blockIdx.y, item0 = pair * nitems;
+    const double* __restrict__ rows = rows_by_pair[pair];
+    for (int i = threadIdx.x; i < KS_ROWS * W; i += blockDim.x) srows[i] = rows[i];
+    if (threadIdx.x == 0) pp = pairs[pair];
+    __syncthreads();
+    const NodeRows<NT> NR{(unsigned) __cvta_generic_to_shared(srows), srows, rows, KS_ROWS};
+    const int e = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;      // one search per warp
+    if (e >= nitems * TL_NG) return;
+    const int it = item0 + e / TL_NG, q = e % TL_NG;
+    const TlItem item = items[it];
+    const double* coeff = (item.coeff_off >= 0) ? coeff_pool + item.coeff_off : nullptr;
+    const double g = gnodes[q], T = item.T;
+    const long long o = (long long) it * TL_NG + q;
+    if (g == 0) { if (lane == 0) { ilim[o] = 0.0; bmid_out[o] = 5.0; bmax_out[o] = 10.0; } return; }   // transfer_lengths.cpp:223,235
+    int st = 0;
+    auto theta = [&](double b) {                               // theta integral at (g, b): root finding in every lane (same result), sum shared
+        double A[NT], c2, Ap[NT];
+        lane_setup<NT>(pp, coeff, T, g, b, A, c2, st);
+#pragma unroll
+        for (int t = 0; t < NT; t++) Ap[t] = c2 * A[t];
+        int kk = 0;
+        return theta_integral_warp<NT>(NR, Ap, c2, kk, st);
+    };
+    const double I_lim = theta(100.0);
+    auto chi = [&](double b) {                                 // cpp/Spherical.cpp:259-270,455-465
+        if (b > 100) return 0.0;
+        if (b < 1e-3) return PI_REF;
+        const double th = __dadd_rn(__dsub_rn(theta(b), I_lim), PI_REF / 2);
+        return __dsub_rn(PI_REF, __dmul_rn(2.0, th));
+    };
+    // get_bmid, cpp/transfer_lengths.cpp:234-266
+    double b = 0.9, db = 0.1;
+    double chi_val = chi(b), next_chi_val, dchidb;
+    const double step_tol = 1e-6, chi_tol = 1e-6;
+    int guard = 0;
+    while ((fabs(chi_val) > chi_tol) && (fabs(db) > step_tol) && guard++ < 10000) {
+        if ((chi_val < 0 && db > 0) || (chi_val > 0 && db < 0)) db *= -0.9;
+        next_chi_val = chi(b + db);
+        while (fabs(next_chi_val) >= fabs(chi_val)) {
+            db *= 0.1;
+            next_chi_val = chi(b + db);
+            if (fabs(db) < step_tol) break;
+        }
+        if (fabs(db) > step_tol) {
+            b += db;
+            dchidb = (chi_val - next_chi_val) / db;
+            chi_val = next_chi_val;
+            db = -chi_val / dchidb;
+        }
+        if ((b > 10) || (b < 0)) { st |= 8; break; }       // "Unable to converge bmid!"
+    }
+    const double bmid = b;
+    // get_b_max_g, cpp/transfer_lengths.cpp:221-232
+    b = 2 * bmid;
+    chi_val = chi(b);
+    guard = 0;
+    while (fabs(chi_val + 1e-5) > 1e-3 && guard++ < 400) { b += 0.5; chi_val = chi(b); }
+    if (guard >= 400) st |= 8;
+    if (lane == 0) {
+        ilim[o] = I_lim; bmid_out[o] = bmid; bmax_out[o] = b;
+        if (st) atomicOr(&status[it], st);
+    }
+    }
+}
+
 // b node k (evaluation order of weighted_simpson, Integration.cpp:375-394) of the two b intervals
 __device__ __forceinline__ double tl_bnode(int k, double bmid, double bmax, double& coef) {
     double x0, xN; int N, kk;
@@ -250,12 +330,15 @@ extern "C" int kg_transfer_lengths_batch(kg_model* m, int nT, const double* T, c
     for (int p0 = 0; p0 < Np; p0 += pairs_per_launch) {
         const int np = std::min(pairs_per_launch, Np - p0);
         const dim3 g1((nT * TL_NG + 255) / 256, np);
+        const dim3 g1w((nT * TL_NG + 7) / 8, np);          // one warp per search
         const long long n2 = (long long) nT * TL_NG * TL_NB;
         const dim3 g2((unsigned) ((n2 + 255) / 256), np);
 #define TL_LAUNCH(NT) do { \
         cudaFuncSetAttribute(tl_search_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem); \
         cudaFuncSetAttribute(tl_node_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem); \
-        tl_search_kernel<NT><<<g1, 256, smem, s>>>(m->d_pairs, m->d_rows_by_pair, d_items, p0, nT, d_coeff, d_g, d_ilim, d_bmid, d_bmax, d_status); \
+        if (NT == 1 || !m->tl_warp_search) tl_search_kernel<NT><<<g1, 256, smem, s>>>(m->d_pairs, m->d_rows_by_pair, d_items, p0, nT, d_coeff, d_g, d_ilim, d_bmid, d_bmax, d_status); \
+        else { cudaFuncSetAttribute(tl_search_warp_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem); \
+               tl_search_warp_kernel<NT><<<g1w, 256, smem, s>>>(m->d_pairs, m->d_rows_by_pair, d_items, p0, nT, d_coeff, d_g, d_ilim, d_bmid, d_bmax, d_status); } \
         tl_node_kernel<NT><<<g2, 256, smem, s>>>(m->d_pairs, m->d_rows_by_pair, d_items, p0, nT, d_coeff, d_g, d_ilim, d_bmid, d_bmax, d_fw, d_status); } while (0)
         switch (m->ntpad) { case 1: TL_LAUNCH(1); break; case 2: TL_LAUNCH(2); break; case 4: TL_LAUNCH(4); break; default: TL_LAUNCH(6); break; }
 #undef TL_LAUNCH
