@@ -26,11 +26,13 @@ sys.path.insert(0, ROOT)
 NT_PER_GPU = 4096
 LR = [(l, r) for l in range(1, 5) for r in range(l, 5)]
 # FP64-pipe lane instructions (DFMA + DMUL + DADD, predicated-on threads) per unit of work, calibrated on ncu's
-# smsp__sass_thread_inst_executed_op_{dfma,dmul,dadd}_pred_on sums of full-size launches of this build (profiles/r2_fp64_calibration.md):
-FP64_PER_NODE = 9.07         # theta_kernel<2>: 3.20e10 lane instructions of the largest launch / its 3.53e9 executed node evaluations (all-in:
-                             # coarse nodes 8.0 each, end nodes, difference formulas, continuation to the stop, node-by-node tier)
-FP64_PER_SETUP = 390.0       # theta_setup_kernel<2>: 7.47e9 lane instructions of the largest launch / its 19.16 M work entries (root finding)
-FP64_PER_CELL = 240.0        # mesh_level_kernel, leaf level: 6.05e9 lane instructions / 25.2 M cells (ten (l,r) members x 24)
+# smsp__sass_thread_inst_executed_op_{dfma,dmul,dadd}_pred_on summed over ALL launches of one full-size headline step of this build
+# (tools/gpu_calib.sh; profiles/r2_summary.md) and divided by the step's device counters:
+FP64_PER_NODE = 8.99         # theta_kernel<2>: 5.402e10 lane instructions / 6.012e9 executed node evaluations (all-in: coarse nodes 8 each,
+                             # end nodes, difference formulas, continuation to the stop, node-by-node tier)
+FP64_PER_SETUP = 228.0       # theta_setup_kernel<2>: 7.43e9 lane instructions / 32.63 M root findings (integer-exponent get_R in registers)
+FP64_PER_CELL = 406.0        # mesh_level_kernel: 8.42e9 lane instructions / 20.73 M cell records of all levels (a group record holds up to 4 leaves;
+                             # ten (l,r) members each)
 F_NODE = 98.0    # nominal FP64 flop per tanh-sinh node for a 2-term (Mie/LJ) potential, SURVEY.md 8(d): 52 + 23 n_terms
 METRIC = "collision integrals/s"
 
