@@ -98,6 +98,19 @@ int kg_model_set_stream(kg_model* m, void* cuda_stream);
  * coeff (optional, nterms doubles) overrides C[] for this call (T-dependent effective coefficients). */
 int kg_chi_points(kg_model* m, int pair, double T, int n, const double* g, const double* b_red,
                   const double* coeff, double* chi_out, double* R_out, int32_t* status);
+
+/* kg_chi_points_noalloc: kg_chi_points without any device allocation, for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it). NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, results and status bits as kg_chi_points. The device staging buffers are one fixed file-scope array in the library
+ * (36 bytes per point, KG_CHI_NOALLOC_MAX_POINTS points = 2.25 MiB, held by every GPU that loads the library until exit); n beyond the
+ * maximum is rejected (-1, kg_last_error says so), as are temperature-dependent generic (Feynman-Hibbs tabulated) potentials. All calls
+ * on one device share the array: calls that overlap on the GPU race on it -- serialise them. Calls cudaMalloc / cudaFree never.
+ * kg_chi_points_noalloc_max() returns the limit. */
+#define KG_CHI_NOALLOC_MAX_POINTS 65536
+int kg_chi_points_noalloc(kg_model* m, int pair, double T, int n, const double* g, const double* b_red,
+                          const double* coeff, double* chi_out, double* R_out, int32_t* status);
+int kg_chi_points_noalloc_max(void);
+
 /* Replaces Spherical::potential / potential_derivative_r (cpp/bindings.cpp:187-189) for n radii r [m] at temperature T
  * (T matters for Feynman-Hibbs corrected models only): u [J], du/dr [J/m]. Either output may be NULL. */
 int kg_potential_points(kg_model* m, int pair, double T, int n, const double* r, double* u_out, double* du_out);

@@ -17,6 +17,7 @@ EXPORTS = [
     "kg_model_create_ex", "kg_potential_points", "kg_genpot_describe", "kg_omega_plan_quadrature_stats", "kg_set_exact_quadrature",
     "kg_omega_plan_create_masked", "kg_omega_table_create", "kg_omega_table_eval", "kg_omega_table_eval_dev", "kg_omega_table_save",
     "kg_omega_table_load", "kg_omega_table_lr", "kg_omega_table_info", "kg_omega_table_destroy", "kg_cross_sections", "kg_second_virial", "kg_model_set_temperature_dependent", "kg_build_info", "kg_host_alloc", "kg_host_free", "kg_tcache_create", "kg_tcache_destroy", "kg_tcache_lr", "kg_tcache_fetch", "kg_transport_batch", "kg_last_timings",
+    "kg_chi_points_noalloc", "kg_chi_points_noalloc_max",
 ]
 
 
@@ -72,6 +73,8 @@ def lib():
         L.kg_second_virial.argtypes = [C.c_void_p, C.c_int, C.c_int, dp, dp, dp]
         L.kg_model_set_temperature_dependent.argtypes = [C.c_void_p, C.c_int]
         L.kg_chi_points.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int, dp, dp, dp, dp, dp, ip]
+        L.kg_chi_points_noalloc.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int, dp, dp, dp, dp, dp, ip]
+        L.kg_chi_points_noalloc_max.argtypes = []
         L.kg_omega_batch.argtypes = [C.c_void_p, C.c_int, dp, C.c_int, ip, ip, dp, dp, dp, ip]
         L.kg_omega_plan_create.argtypes = [C.c_void_p, C.c_int, dp, C.c_int, ip, ip, dp, C.POINTER(C.c_void_p)]
         for n in ("kg_omega_plan_run", "kg_omega_plan_sync", "kg_omega_plan_destroy"):
