@@ -199,6 +199,8 @@ int kg_set_exact_quadrature(int exact);
 
 #define KG_STATUS_SINGULAR      16  /* zero pivot in a Sonine-expansion system */
 #define KG_STATUS_T_NOT_CACHED  32  /* state-point temperature absent from the kg_tcache it was run against */
+#define KG_STATUS_COMPOSITION   128 /* WARNING only, results are computed: "Mole fractions do not sum to unity" (pykingas/py_KineticGas.py:119-141,
+                                       |sum x - 1| > 1e-12), reported per state point so that callers need no host pass over x */
 
 typedef struct {
     int32_t N;                        /* Enskog approximation order (>= 1; conductivity needs >= 2) */

@@ -64,7 +64,14 @@ struct kg_model {
     std::unordered_map<void*, size_t> pool_live;
     size_t pool_cached = 0;
     bool tl_warp_search = false;        // KG_TL_WARP_SEARCH=1: one warp per b_mid / b_max search (comparison runs; measured slower)
-    int* h_pinned = nullptr;            // 16 ints of pinned host memory for the small D2H reads of the pass loop
+    int* h_pinned = nullptr;            // page-locked host memory: 16 ints of the model + 32 slots of 8 ints handed to plans (run flags)
+    unsigned pinned_used = 0;           // slot bitmap (cudaMallocHost / cudaFreeHost per plan cost ~1 ms each and synchronise the device)
+    int* pinned_slot_acquire(int& slot) {
+        for (slot = 0; slot < 32; slot++) if (!(pinned_used >> slot & 1u)) { pinned_used |= 1u << slot; return h_pinned + 16 + 8 * slot; }
+        slot = -1;
+        return nullptr;
+    }
+    void pinned_slot_release(int slot) { if (slot >= 0) pinned_used &= ~(1u << slot); }
     cudaError_t dmalloc_bytes(void** out, size_t bytes) {
         bytes = (std::max<size_t>(bytes, 1) + 511) & ~(size_t) 511;
         auto f = pool_free.lower_bound(bytes);

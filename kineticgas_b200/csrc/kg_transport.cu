@@ -806,8 +806,9 @@ __global__ void __launch_bounds__(state_tpb(MAXN)) state_kernel(TModel tm, State
         return;
     }
     s.T = a.T_of[s.t]; s.Vm = a.Vm[sp]; s.rho = AVOGADRO / s.Vm;
-    double wsum = 0.0;
-    for (int i = 0; i < nc; i++) { s.x[i] = tm.is_singlecomp ? 0.5 : a.x[(size_t) sp * nc + i]; wsum += s.x[i] * tm.m[i]; }
+    double wsum = 0.0, xsum = 0.0;
+    for (int i = 0; i < nc; i++) { s.x[i] = tm.is_singlecomp ? 0.5 : a.x[(size_t) sp * nc + i]; wsum += s.x[i] * tm.m[i]; xsum += s.x[i]; }
+    if (fabs(xsum - 1.0) > 1e-12) st |= KG_STATUS_COMPOSITION;      // warning bit: the check of pykingas/py_KineticGas.py:119-141 (FLTEPS = 1e-12)
     for (int i = 0; i < nc; i++) s.wt[i] = s.x[i] * tm.m[i] / wsum;
     double g[MAXC * MAXC], K[MAXC], Kp[MAXC];
     for (int k = 0; k < nc * nc; k++) g[k] = tm.is_idealgas ? 1.0 : a.rdf[((size_t) sp * a.nslots) * nc * nc + k];
