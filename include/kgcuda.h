@@ -296,6 +296,30 @@ void kg_omega_table_destroy(kg_omega_table* t);
  * (2 flop per DFMA). Used as the roofline denominator (MEASURED_PEAKS.json has no FP64 figure). */
 int kg_measure_fp64_peak(int device, double* tflops, double* sm_mhz_est);
 
+/* ---------------------------------------------------------------------------------------------------------------------------
+ * EoS-derived inputs on the device. Replaces, for batches of state points, the calls the reference makes on its
+ * thermopack EoS object one point at a time (cpp/eos_interface.h:121-181; pykingas/MieKinGas.py:55-65 constructs `saftvrmie`):
+ *   chemical_potential_tv(T, V, n, dmudn)  ->  dmudn     [n][nc][nc]  J/mol^2  (total: ideal + residual), at n = x (one mole)
+ *   idealenthalpysingle(T, j, dhdt)        ->  cp_ideal  [n][nc]      J/(mol K)
+ *   pressure_tv(T, V, n)                   ->  pressure  [n]          Pa
+ *   specific_volume(T, p, n, dvdn)         ->  dvdn      [n][nc]      m^3/mol  (dV/dn_i at constant T, p; CoV frame)
+ *   specific_volume(T, p, x, VAPPH)        ->  kg_eos_specific_volume_batch: vapour-like root Vm [m^3/mol], status 1 = not converged
+ * Model: SAFT-VR Mie (Lafitte et al. 2013) with thermopack's default options; m[nc] segments, pair matrices [nc][nc] sigma [m],
+ * eps_div_k [K], la, lr (the caller applies its combining rules / k_ij). cp_type[nc], cp_par[nc][KG_EOS_CP_PARAMS], mw[nc] (g/mol):
+ * thermopack's ideal-gas Cp correlation of each component (compdata.f90:14-26; types 10 and 11 are not available) -- may be NULL
+ * when cp_ideal is never requested. Single-component models take nc = 1 (x may be NULL). Any output pointer may be NULL. Host
+ * buffers in and out; the handle owns a stream and grow-only device buffers. */
+#define KG_EOS_CP_PARAMS 21
+typedef struct kg_eos kg_eos;
+int kg_eos_saftvrmie_create(int device, int nc, const double* m, const double* sigma, const double* eps_div_k, const double* la,
+                            const double* lr, const int32_t* cp_type, const double* cp_par, const double* mw, kg_eos** out);
+void kg_eos_destroy(kg_eos* e);
+const char* kg_eos_last_error(const kg_eos* e);
+int kg_eos_tv_batch(kg_eos* e, int n, const double* T, const double* Vm, const double* x,
+                    double* dmudn, double* cp_ideal, double* pressure, double* dvdn);
+int kg_eos_specific_volume_batch(kg_eos* e, int n, const double* T, const double* p, const double* x, double* Vm, int32_t* status);
+double kg_eos_last_kernel_ms(const kg_eos* e);     /* summed kernel time of the last batch call (CUDA events) */
+
 #ifdef __cplusplus
 }
 #endif

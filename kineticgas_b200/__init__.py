@@ -2,3 +2,4 @@
 from .model import DeviceModel, OmegaPlan, OmegaTable, mie_desc, power_sum_desc, measure_fp64_peak  # noqa: F401
 from .kingas import MieKinGas, QuantumMie, TCache, LJSpline, LJTS, ModTangToennis, HFD_B2, Patowski  # noqa: F401
 from ._lib import pinned_empty, pinned_copy  # noqa: F401
+from .eos import DeviceSaftVRMie  # noqa: F401

@@ -117,6 +117,14 @@ class MieKinGas:
         self.lr = 3 + (1 - lij) * np.sqrt((lr_[None, :] - 3) * (lr_[:, None] - 3))
         self.sigma, self.epsilon = self.sigma_ij, self.epsilon_ij
         self.eos = use_eos
+        if isinstance(use_eos, str) and use_eos == "device":
+            # the EoS pykingas would construct (saftvrmie(comps), pykingas/MieKinGas.py:55-60), evaluated on the GPU; with explicitly given
+            # potential parameters the EoS takes the RET model's, segment numbers kept (pykingas/MieKinGas.py:46-65, MieType.py:167-191)
+            from .eos import DeviceSaftVRMie
+            self.eos = DeviceSaftVRMie(comps, device=device)
+            if any(v is not None for v in (mole_weights, sigma, eps_div_k, la, lr)):
+                for i in range(self.eos.nc):
+                    self.eos.set_pure_fluid_param(i + 1, self.eos.m[i], self.sigma_ij[i, i], self.epsilon_ij[i, i] / BOLTZMANN_PY, self.la[i, i], self.lr[i, i])
         self.omega_correlation_active = True
         self._device = device
         self._build_device_model()
@@ -197,6 +205,11 @@ class MieKinGas:
         nce = 1 if self._is_singlecomp else self.ncomps
         out = dict(eos_inputs or {})
         xe = np.ones((n, 1)) if self._is_singlecomp else x
+        if hasattr(self.eos, "tv_batch"):
+            # device EoS (kineticgas_b200.eos.DeviceSaftVRMie): every missing input of the whole batch in one GPU pass
+            miss = {"dmudn": need_dmudn and "dmudn" not in out, "cp_ideal": need_cp and "cp_ideal" not in out, "dvdn": need_dvdn and "dvdn" not in out}
+            if any(miss.values()):
+                out.update(self.eos.tv_batch(T, Vm, xe, dmudn=miss["dmudn"], cp_ideal=miss["cp_ideal"], dvdn=miss["dvdn"]))
         if need_dmudn and "dmudn" not in out:
             if self.eos is None:
                 raise RuntimeError("EoS is not set")
@@ -358,6 +371,8 @@ class MieKinGas:
             return Vm
         T, p = np.broadcast_arrays(np.asarray(T, float), np.asarray(p, float))
         xx = np.broadcast_to(np.asarray(x, float), T.shape + (np.shape(x)[-1],))
+        if hasattr(self.eos, "specific_volume_batch"):
+            return self.eos.specific_volume_batch(T, p, np.ones(T.shape + (1,)) if self._is_singlecomp else xx)
         return np.array([self.eos.specific_volume(T[k], p[k], list(xx[k]), self.eos.VAPPH)[0] for k in range(T.size)])
 
     def viscosity_tp(self, T, p, x, N=None):

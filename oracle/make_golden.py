@@ -476,3 +476,108 @@ def config0_eos(fname="config0_eos.npz"):
 
 if __name__ == "__main__" and "eos0" in sys.argv[1:]:
     config0_eos()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# the EoS-derived inputs (thermopack saftvrmie, the EoS pykingas constructs). Two products, both from the thermopack
+# 2.2.3 wheel vendored in the reference tree (it cannot travel to the GPU box):
+#   kineticgas_b200/saft_db.json      the SAFT-VR Mie parameters, binary parameters, molar masses and ideal-gas Cp correlations thermopack's
+#                                     database holds for the fluids of kineticgas_b200/fluids.py (what `saftvrmie(comps)` would load)
+#   tests/golden/eos_reference.npz    dmudn, Cp_ideal, p, dV/dn and Vm(T,p) of thermopack at seeded state points of four mixtures, plus the
+#                                     Helmholtz terms used to pin the device model term by term
+# ---------------------------------------------------------------------------------------------------------------
+def _thermopack():
+    import zipfile
+    whl = "/root/reference/cpp/external/thermopack/addon/pycThermopack/wheelhouse/thermopack-2.2.3-py3-none-manylinux_2_28_x86_64.whl"
+    dst = "/tmp/kg_thermopack_wheel"
+    if not os.path.exists(dst):
+        zipfile.ZipFile(whl).extractall(dst)
+    if dst not in sys.path:
+        sys.path.insert(0, dst)
+    if not hasattr(np, "product"):
+        np.product = np.prod                      # the wheel predates numpy 2
+    from thermopack.saftvrmie import saftvrmie
+    return saftvrmie
+
+
+def eos_database(fname="saft_db.json"):
+    import json
+    from kineticgas_b200.fluids import MIE
+    saftvrmie = _thermopack()
+    comps = list(MIE)
+    db = {"source": "thermopack 2.2.3 saftvrmie database (default parameter reference), read through the python wrapper", "pure": {}, "binary": {}}
+    for c in comps:
+        eos = saftvrmie(c)
+        m, s, e, la, lr = eos.get_pure_fluid_param(1)
+        t, par = eos.get_ideal_cp(1)
+        db["pure"][c] = {"m": m, "sigma": s, "eps_div_k": e, "la": la, "lr": lr, "mw": float(eos.compmoleweight(1)),
+                         "cp_type": int(t), "cp_par": [float(v) for v in par]}
+    # binary parameters: one child process per pair (thermopack stops the process on pairs it cannot initialise)
+    import subprocess
+    code = ("import sys, numpy as np; np.product = np.prod; sys.path.insert(0, '/tmp/kg_thermopack_wheel'); "
+            "from thermopack.saftvrmie import saftvrmie; e = saftvrmie(sys.argv[1]); "
+            "print('BIN', float(e.get_eps_kij(1, 2)), float(e.get_sigma_lij(1, 2)), float(e.get_lr_gammaij(1, 2)))")
+    db["binary_unavailable"] = []
+    for i, a in enumerate(comps):
+        for b in comps[i + 1:]:
+            r = subprocess.run([sys.executable, "-c", code, a + "," + b], capture_output=True, text=True)
+            line = [l for l in r.stdout.splitlines() if l.startswith("BIN")]
+            if not line:
+                db["binary_unavailable"].append(a + "," + b)
+                continue
+            k, l, g = (float(v) for v in line[0].split()[1:])
+            if k or l or g:
+                db["binary"][a + "," + b] = {"kij": k, "lij": l, "gammaij": g}
+    json.dump(db, open(os.path.join(ROOT, "kineticgas_b200", fname), "w"), indent=1)
+    print("saft_db.json:", len(db["pure"]), "fluids,", len(db["binary"]), "pairs with binary parameters")
+
+
+def eos_reference(fname="eos_reference.npz"):
+    saftvrmie = _thermopack()
+    rng = np.random.default_rng(20251105)
+    out = {}
+    for tag, comps in (("ar", "AR"), ("co2c1n2", "CO2,C1,N2"), ("c1nc10", "C1,NC10"), ("five", "CO2,C1,N2,AR,KR")):
+        eos = saftvrmie(comps)
+        nc = eos.nc
+        pure = [eos.get_pure_fluid_param(i + 1) for i in range(nc)]
+        sig = np.array([[eos.sigma_ij(i + 1, j + 1) for j in range(nc)] for i in range(nc)])
+        eps = np.array([[eos.epsilon_ij(i + 1, j + 1) for j in range(nc)] for i in range(nc)])
+        npts = 24
+        T = rng.uniform(200.0, 700.0, npts)
+        if tag == "c1nc10":
+            T = rng.uniform(450.0, 800.0, npts)
+        x = rng.dirichlet(np.ones(nc), npts) if nc > 1 else np.ones((npts, 1))
+        eta = rng.uniform(0.002, 0.45, npts)                        # segment packing fraction (pi/6) rho sum_i x_i m_i sigma_ii^3
+        mvec = np.array([q[0] for q in pure])
+        Vm = (np.pi / 6) * 6.02214076e23 * (x * mvec * np.diag(sig) ** 3).sum(axis=1) / eta
+        dm, cp, p, dv, terms = [], [], [], [], []
+        for k in range(npts):
+            n = list(x[k])
+            mu, dmudn = eos.chemical_potential_tv(T[k], Vm[k], n, dmudn=True)
+            dm.append(np.asarray(dmudn))
+            cp.append([eos.idealenthalpysingle(T[k], j + 1, dhdt=True)[1] for j in range(nc)])
+            pk, = eos.pressure_tv(T[k], Vm[k], n)
+            p.append(pk)
+            a_hs, = eos.a_hard_sphere(T[k], Vm[k], n)
+            a_d, = eos.a_dispersion(T[k], Vm[k], n)
+            A, = eos.helmholtz_tv(T[k], Vm[k], n, property_flag="R")
+            terms.append([a_hs, a_d, A / (eos.Rgas * T[k])])
+        # Vm(T, p) on the vapour side and dV/dn there, at moderate pressures
+        Tp = rng.uniform(250.0 if tag != "c1nc10" else 600.0, 700.0, npts)
+        pp = 10.0 ** rng.uniform(4.0, 6.3, npts)
+        vm_tp, dvdn_tp = [], []
+        for k in range(npts):
+            v, dvdn = eos.specific_volume(Tp[k], pp[k], list(x[k]), eos.VAPPH, dvdn=True)
+            vm_tp.append(v); dvdn_tp.append(np.asarray(dvdn))
+        out.update({f"{tag}_comps": np.array(comps), f"{tag}_m": np.array([q[0] for q in pure]), f"{tag}_sigma": sig, f"{tag}_eps": eps,
+                    f"{tag}_la1": np.array([q[3] for q in pure]), f"{tag}_lr1": np.array([q[4] for q in pure]),
+                    f"{tag}_T": T, f"{tag}_Vm": Vm, f"{tag}_x": x, f"{tag}_dmudn": np.array(dm), f"{tag}_cp": np.array(cp), f"{tag}_p": np.array(p),
+                    f"{tag}_terms": np.array(terms), f"{tag}_Tp": Tp, f"{tag}_pp": pp, f"{tag}_vm_tp": np.array(vm_tp), f"{tag}_dvdn_tp": np.array(dvdn_tp),
+                    f"{tag}_d": np.array([eos.hard_sphere_diameters(t)[0] for t in T[:4]])})
+        print(tag, "done")
+    np.savez(os.path.join(GOLD, fname), **out)
+
+
+if __name__ == "__main__" and "eos" in sys.argv[1:]:
+    eos_database()
+    eos_reference()
