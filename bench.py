@@ -351,6 +351,51 @@ def run_five_comp(local_rank, rank, n_gpus, steps):
     return out
 
 
+# ------------------------------------------------------------------------------------------------ EoS-derived inputs on the device
+# thermopack 2.2.3 (the EoS object pykingas constructs) cannot travel to the GPU box; its cost per state point of this 5-component mixture was
+# measured in the build container on one core through the python calls cpp/eos_interface.h makes: chemical_potential_tv(dmudn) 203 us,
+# five idealenthalpysingle calls 72 us, specific_volume(T, p) 851 us.
+THERMOPACK_US_PER_POINT = {"dmudn": 203.0, "cp_ideal": 72.0, "specific_volume": 851.0}
+
+
+def run_eos_leg(local_rank, steps):
+    """dmu/dn (5x5) + Cp_ideal of configs[4]'s 10^5 state points from DeviceSaftVRMie (host arrays in, host arrays out), and the whole
+    configs[4] surface with the EoS inputs computed on the GPU (use_eos='device') instead of handed in as arrays."""
+    from kineticgas_b200 import DeviceSaftVRMie, MieKinGas
+    T, Vm, x = fc_grid(1, 0)
+    eos = DeviceSaftVRMie(FC_COMPS, device=local_rank)
+    ms, kms = [], []
+    for step in range(steps + 1):
+        t0 = time.perf_counter()
+        r = eos.tv_batch(T, Vm, x, dmudn=True, cp_ideal=True)
+        t1 = time.perf_counter()
+        if step > 0:
+            ms.append(1e3 * (t1 - t0)); kms.append(eos.last_kernel_ms())
+    finite = bool(np.isfinite(r["dmudn"]).all() and np.isfinite(r["cp_ideal"]).all())
+    t0 = time.perf_counter()
+    Vtp = eos.specific_volume_batch(T, np.full(T.size, 1e5), x)
+    ms_vol = 1e3 * (time.perf_counter() - t0)
+    kin = MieKinGas(FC_COMPS, N=FC_N, is_idealgas=False, use_eos="device", device=local_rank)
+    full = []
+    for step in range(steps + 1):
+        kin._caches = {}
+        t0 = time.perf_counter()
+        res = kin.transport_batch(T, Vm, x, N=FC_N)
+        if step > 0:
+            full.append(1e3 * (time.perf_counter() - t0))
+    n = int(T.size)
+    tp_s = n * (THERMOPACK_US_PER_POINT["dmudn"] + THERMOPACK_US_PER_POINT["cp_ideal"]) * 1e-6
+    return {"workload": f"SURVEY 8f row 1: SAFT-VR Mie dmu/dn (5x5) + Cp_ideal of the {n} state points of configs[4] ({FC_COMPS}), host arrays in and out",
+            "value": n / (np.mean(ms) * 1e-3), "unit": "state points/s", "ms_per_step": float(np.mean(ms)), "kernel_ms": float(np.mean(kms)),
+            "h2d_bytes_per_step": int(T.nbytes + Vm.nbytes + x.nbytes), "d2h_bytes_per_step": int(r["dmudn"].nbytes + r["cp_ideal"].nbytes),
+            "all_finite": finite and bool(np.isfinite(Vtp).all()),
+            "specific_volume": {"value": n / (ms_vol * 1e-3), "unit": "state points/s", "ms": ms_vol, "workload": "Vm(T, 1 bar, x) of the same points"},
+            "five_component_with_device_eos": {"value": n / (np.mean(full) * 1e-3), "unit": "state points/s", "ms_per_step": float(np.mean(full)),
+                                               "all_finite": bool(all(np.isfinite(res[k]).all() for k in ("viscosity", "conductivity", "D", "DT")))},
+            "cpu_reference": {"kind": "reference", "where": "build container, one core (thermopack 2.2.3 is not on the GPU box)",
+                              "us_per_point": THERMOPACK_US_PER_POINT, "seconds_for_this_batch": tp_s, "value": n / tp_s, "unit": "state points/s"}}
+
+
 # ------------------------------------------------------------------------------------------------ strong scaling (fixed total work)
 def _rank_values(v, world):
     import torch
@@ -771,7 +816,9 @@ def main():
             dist.all_reduce(t4, op=dist.ReduceOp.MAX)
         qm["ms_max"], fc["ms_max"] = float(t4[0].item()), float(t4[1].item())
 
-    par = cfg0 = None
+    par = cfg0 = eos_leg = None
+    if rank == 0 and not args.nt and not args.no_extra_configs and not args.no_state_points:
+        eos_leg = run_eos_leg(local_rank, max(1, min(args.steps, 2)))
     if rank == 0 and not args.nt:
         par = parity_block(model)
         if not args.no_state_points:
@@ -865,6 +912,8 @@ def main():
                                      "roofline": state_roofline("five_component", fc["n"], fc["h2d"], fc["d2h"], fc["stage_ms"]["ms_state_kernels"]),
                                      "note": "host buffers in and out through kg_tcache_create + kg_transport_batch; EoS inputs (dmu/dn, Cp_id) are synthetic "
                                              "arrays prepared outside the timed region"}
+        if eos_leg is not None:
+            out["eos_inputs"] = eos_leg
         if not args.no_cpu_baseline:
             n_sample = args.cpu_sample or min(64, max(16, cores))
             cb, _ = run_cpu_reference(n_gpus, n_sample, min(cores, n_sample))
