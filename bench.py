@@ -358,7 +358,12 @@ def run_five_comp(local_rank, rank, n_gpus, steps):
 THERMOPACK_US_PER_POINT = {"dmudn": 203.0, "cp_ideal": 72.0, "specific_volume": 851.0}
 
 
-def run_eos_leg(local_rank, steps):
+# FP64 lane instructions (DFMA + DMUL + DADD) of one eos_hess_kernel thread = one hyper-dual Helmholtz evaluation of the 5-component model:
+# ncu's SASS op counters of a 10^5-point launch, 2.4111e10 / (10^5 points x 15 Hessian entries) (profiles/r2_eos_fp64_ops.csv)
+FP64_PER_EOS_EVAL = 16074.0
+
+
+def run_eos_leg(local_rank, steps, peak_tflops):
     """dmu/dn (5x5) + Cp_ideal of configs[4]'s 10^5 state points from DeviceSaftVRMie (host arrays in, host arrays out), and the whole
     configs[4] surface with the EoS inputs computed on the GPU (use_eos='device') instead of handed in as arrays."""
     from kineticgas_b200 import DeviceSaftVRMie, MieKinGas
@@ -389,6 +394,12 @@ def run_eos_leg(local_rank, steps):
             "value": n / (np.mean(ms) * 1e-3), "unit": "state points/s", "ms_per_step": float(np.mean(ms)), "kernel_ms": float(np.mean(kms)),
             "h2d_bytes_per_step": int(T.nbytes + Vm.nbytes + x.nbytes), "d2h_bytes_per_step": int(r["dmudn"].nbytes + r["cp_ideal"].nbytes),
             "all_finite": finite and bool(np.isfinite(Vtp).all()),
+            "roofline": {"bound": "fp64", "kernel": "eos_tpre_kernel + eos_hess_kernel + eos_out_kernel (timed together; the Hessian kernel is 95 %)",
+                         "achieved": n * 15 * FP64_PER_EOS_EVAL * 2.0 / (np.mean(kms) * 1e-3) / 1e12, "peak": peak_tflops, "unit": "TFLOP/s",
+                         "frac": n * 15 * FP64_PER_EOS_EVAL / (np.mean(kms) * 1e-3) / (peak_tflops * 1e12 / 2.0), "traffic": 11.3e6,
+                         "definition": "FP64 lane instructions of the 15 hyper-dual evaluations per state point (ncu-calibrated count) / (peak/2 x summed "
+                                       "kernel time); ncu of the Hessian kernel alone: FP64 pipe 71.9 % busy, 77.5 % of its warp instructions are FP64, "
+                                       "DRAM traffic 11 MB (inputs 5.6 MB + Hessian 12 MB stay in L2)"},
             "specific_volume": {"value": n / (ms_vol * 1e-3), "unit": "state points/s", "ms": ms_vol, "workload": "Vm(T, 1 bar, x) of the same points"},
             "five_component_with_device_eos": {"value": n / (np.mean(full) * 1e-3), "unit": "state points/s", "ms_per_step": float(np.mean(full)),
                                                "all_finite": bool(all(np.isfinite(res[k]).all() for k in ("viscosity", "conductivity", "D", "DT")))},
@@ -818,7 +829,7 @@ def main():
 
     par = cfg0 = eos_leg = None
     if rank == 0 and not args.nt and not args.no_extra_configs and not args.no_state_points:
-        eos_leg = run_eos_leg(local_rank, max(1, min(args.steps, 2)))
+        eos_leg = run_eos_leg(local_rank, max(1, min(args.steps, 2)), peak_tflops)
     if rank == 0 and not args.nt:
         par = parity_block(model)
         if not args.no_state_points:

@@ -214,7 +214,8 @@ typedef struct {
 } kg_transport_opts;
 
 /* EoS-derived inputs (thermopack on the host in the reference, cpp/eos_interface.h:57-135); nc_eos = 1 for a
- * single-component model else ncomps. Any pointer may be NULL when the requested properties do not need it. */
+ * single-component model else ncomps. Any pointer may be NULL when the requested properties do not need it. The arrays may live in host
+ * or in device memory (unified addressing; e.g. the outputs of kg_eos_tv_batch_dev). */
 typedef struct {
     const double* dmudn;      /* [n][nc_eos][nc_eos]  (dmu_i/dn_j)_{T,V} at V = Vm, n = x (1 mol)  [J/mol^2]  -> diffusion */
     const double* cp_ideal;   /* [n][nc_eos]          ideal-gas Cp of each pure component [J/mol K]         -> conductivity */
@@ -317,6 +318,10 @@ void kg_eos_destroy(kg_eos* e);
 const char* kg_eos_last_error(const kg_eos* e);
 int kg_eos_tv_batch(kg_eos* e, int n, const double* T, const double* Vm, const double* x,
                     double* dmudn, double* cp_ideal, double* pressure, double* dvdn);
+/* The same with the results LEFT ON THE DEVICE: dev[0..3] = device addresses of dmudn, cp_ideal, pressure, dvdn (NULL where `want` -- bit 0
+ * dmudn, 1 cp_ideal, 2 pressure, 3 dvdn -- does not select them), inside the handle's buffers and valid until its next call. They can be
+ * passed to kg_transport_batch as kg_eos_inputs: its EoS arrays may live in host or device memory (unified addressing). */
+int kg_eos_tv_batch_dev(kg_eos* e, int n, const double* T, const double* Vm, const double* x, unsigned want, const double** dev);
 int kg_eos_specific_volume_batch(kg_eos* e, int n, const double* T, const double* p, const double* x, double* Vm, int32_t* status);
 double kg_eos_last_kernel_ms(const kg_eos* e);     /* summed kernel time of the last batch call (CUDA events) */
 

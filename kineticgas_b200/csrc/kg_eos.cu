@@ -42,10 +42,26 @@ static thread_local std::string g_eos_create_error;
 
 namespace {
 
-__global__ void eos_tpre_kernel(const Model* __restrict__ M, int nruns, const double* __restrict__ Trun, TPre* __restrict__ pre) {
-    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+// one CTA per temperature run: the nc diameters side by side, then the nc x nc x 5 table entries side by side (kgsaft::init_T does the same
+// serially; one thread per run took 0.5 ms for a 5-component model -- a fifth of the whole batch)
+__global__ void __launch_bounds__(128) eos_tpre_kernel(const Model* __restrict__ M, int nruns, const double* __restrict__ Trun, TPre* __restrict__ pre) {
+    const int r = blockIdx.x;
     if (r >= nruns) return;
-    init_T(*M, Trun[r], pre[r]);
+    const int nc = M->nc, t = threadIdx.x;
+    TPre& P = pre[r];
+    const double T = Trun[r];
+    if (t == 0) P.T = T;
+    if (t < nc) P.d[t] = bh_diameter(M->p[t][t], T);
+    __syncthreads();
+    for (int idx = t; idx < nc * nc * 5; idx += blockDim.x) {
+        const int k = idx % 5, j = (idx / 5) % nc, i = idx / (5 * nc);
+        const PairC& q = M->p[i][j];
+        const double dij = 0.5 * (P.d[i] + P.d[j]), x0 = q.sigma / dij, l = q.lam[k];
+        if (k == 0) { P.d3[i][j] = dij * dij * dij; P.x0[i][j] = x0; }
+        P.x0p[i][j][k] = pow(x0, l);
+        P.I[i][j][k] = -(pow(x0, 3.0 - l) - 1.0) / (l - 3.0);
+        P.J[i][j][k] = -(pow(x0, 4.0 - l) * (l - 3.0) - pow(x0, 3.0 - l) * (l - 4.0) - 1.0) / ((l - 3.0) * (l - 4.0));
+    }
 }
 
 // entry e of the upper triangle of an nv x nv symmetric matrix, row-major: (a, b), a <= b
@@ -286,13 +302,29 @@ static int eos_stage(kg_eos* e, kg_eos_bufs* b, int n, const double* T, const do
     EOS_OK(cudaMemcpyAsync(b->Trun.p, Trun.data(), nruns * sizeof(double), cudaMemcpyHostToDevice, s));
     EOS_OK(cudaStreamSynchronize(s));                        // run_of / Trun are stack-lifetime host vectors
     EOS_OK(cudaEventRecord(b->ev[0], s));
-    eos_tpre_kernel<<<(nruns + 63) / 64, 64, 0, s>>>(e->d_M, nruns, (const double*) b->Trun.p, (TPre*) b->pre.p);
+    eos_tpre_kernel<<<nruns, 128, 0, s>>>(e->d_M, nruns, (const double*) b->Trun.p, (TPre*) b->pre.p);
     EOS_OK(cudaGetLastError());
     return 0;
 }
 
+static int eos_tv(kg_eos* e, int n, const double* T, const double* Vm, const double* x, double* dmudn, double* cp_ideal_out, double* pressure,
+                  double* dvdn, const double** dev_out);
 extern "C" int kg_eos_tv_batch(kg_eos* e, int n, const double* T, const double* Vm, const double* x,
                                double* dmudn, double* cp_ideal_out, double* pressure, double* dvdn) {
+    return eos_tv(e, n, T, Vm, x, dmudn, cp_ideal_out, pressure, dvdn, nullptr);
+}
+// Results left on the device: dev[0..3] receive the addresses of dmudn, cp_ideal, pressure, dvdn inside the handle's buffers (NULL for
+// what `want` does not select: bit 0 dmudn, 1 cp_ideal, 2 pressure, 3 dvdn), valid until the next call on this handle. The stream is
+// synchronised before return, so the arrays can be handed to kg_transport_batch as kg_eos_inputs right away.
+extern "C" int kg_eos_tv_batch_dev(kg_eos* e, int n, const double* T, const double* Vm, const double* x, unsigned want, const double** dev) {
+    if (!e) return -1;
+    if (!dev) { e->err = "kg_eos_tv_batch_dev: invalid argument"; return -1; }
+    double dummy = 0;       // non-NULL selects an output; nothing is written through these in device-output mode
+    return eos_tv(e, n, T, Vm, x, (want & 1u) ? &dummy : nullptr, (want & 2u) ? &dummy : nullptr, (want & 4u) ? &dummy : nullptr,
+                  (want & 8u) ? &dummy : nullptr, dev);
+}
+static int eos_tv(kg_eos* e, int n, const double* T, const double* Vm, const double* x, double* dmudn, double* cp_ideal_out, double* pressure,
+                  double* dvdn, const double** dev_out) {
     if (!e) return -1;
     auto set_error = [&](const std::string& s) { e->err = s; };
     kg_eos_bufs* b = bufs_of(e);
@@ -325,6 +357,13 @@ extern "C" int kg_eos_tv_batch(kg_eos* e, int n, const double* T, const double* 
         dvdn ? (double*) b->dvdn.p : nullptr);
     EOS_OK(cudaGetLastError());
     EOS_OK(cudaEventRecord(b->ev[1], s));
+    if (dev_out) {
+        dev_out[0] = dmudn ? (const double*) b->dmudn.p : nullptr; dev_out[1] = cp_ideal_out ? (const double*) b->cp.p : nullptr;
+        dev_out[2] = pressure ? (const double*) b->pout.p : nullptr; dev_out[3] = dvdn ? (const double*) b->dvdn.p : nullptr;
+        EOS_OK(cudaStreamSynchronize(s));
+        float msd = 0; if (cudaEventElapsedTime(&msd, b->ev[0], b->ev[1]) == cudaSuccess) e->last_ms = msd;
+        return 0;
+    }
     if (dmudn) EOS_OK(cudaMemcpyAsync(dmudn, b->dmudn.p, (size_t) n * nc * nc * sizeof(double), cudaMemcpyDeviceToHost, s));
     if (cp_ideal_out) EOS_OK(cudaMemcpyAsync(cp_ideal_out, b->cp.p, (size_t) n * nc * sizeof(double), cudaMemcpyDeviceToHost, s));
     if (pressure) EOS_OK(cudaMemcpyAsync(pressure, b->pout.p, n * sizeof(double), cudaMemcpyDeviceToHost, s));

@@ -1389,6 +1389,12 @@ struct DevBuf {      // scoped device allocations of one batch call
         if (p && h && cudaMemcpyAsync(p, h, n * sizeof(T), cudaMemcpyHostToDevice, s) != cudaSuccess) return nullptr;
         return p;
     }
+    // source in host OR device memory (unified addressing decides): the EoS inputs may come straight from kg_eos_tv_batch_dev
+    template<class T> T* put_any(const T* src, size_t n, cudaStream_t s) {
+        T* p = alloc<T>(n);
+        if (p && src && cudaMemcpyAsync(p, src, n * sizeof(T), cudaMemcpyDefault, s) != cudaSuccess) return nullptr;
+        return p;
+    }
 };
 
 int launch_state(kg_tcache* c, StateArgs& a, cudaStream_t s, const double* d_x_for_rdf, double* d_rdf) {
@@ -1491,9 +1497,9 @@ extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const do
     double* d_rdf = nullptr;
     if (!opts->is_idealgas) { d_rdf = db.alloc<double>((size_t) n * a.nslots * nc * nc); NEED(d_rdf); }
     a.rdf = d_rdf;
-    if (eos && eos->dmudn && (props & (KG_PROP_DIFFUSION | KG_PROP_THERMAL_DIFFUSION))) { a.dmudn = db.put(chunked ? nullptr : eos->dmudn, (size_t) n * nce * nce, s); NEED(a.dmudn); }
-    if (eos && eos->cp_ideal && (props & KG_PROP_CONDUCTIVITY)) { a.cp_ideal = db.put(chunked ? nullptr : eos->cp_ideal, (size_t) n * nce, s); NEED(a.cp_ideal); }
-    if (eos && eos->dvdn && opts->frame_of_reference == KG_FOR_COV) { a.dvdn = db.put(chunked ? nullptr : eos->dvdn, (size_t) n * nce, s); NEED(a.dvdn); }
+    if (eos && eos->dmudn && (props & (KG_PROP_DIFFUSION | KG_PROP_THERMAL_DIFFUSION))) { a.dmudn = db.put_any(chunked ? nullptr : eos->dmudn, (size_t) n * nce * nce, s); NEED(a.dmudn); }
+    if (eos && eos->cp_ideal && (props & KG_PROP_CONDUCTIVITY)) { a.cp_ideal = db.put_any(chunked ? nullptr : eos->cp_ideal, (size_t) n * nce, s); NEED(a.cp_ideal); }
+    if (eos && eos->dvdn && opts->frame_of_reference == KG_FOR_COV) { a.dvdn = db.put_any(chunked ? nullptr : eos->dvdn, (size_t) n * nce, s); NEED(a.dvdn); }
     struct OutMap { double* host; double** dev; size_t count; };
     OutMap maps[] = {{out->viscosity, &a.viscosity, (size_t) n}, {out->conductivity, &a.conductivity, (size_t) n},
                      {out->conductivity_contribs, &a.contribs, (size_t) n * 3}, {out->D, &a.D, (size_t) n * nD * nD}, {out->DT, &a.DT, (size_t) n * nc}, {out->thermal_diffusion_ratio, &a.kT, (size_t) n * nc}, {out->soret_zarate, &a.soret, (size_t) n * nc},
@@ -1542,7 +1548,7 @@ extern "C" int kg_transport_batch(kg_model* m, kg_tcache* cache, int n, const do
             ac.n = cnt;
             ac.tidx = a.tidx + lo; ac.Vm = a.Vm + lo; ac.status = a.status + lo;
             auto h2d = [&](const double* host, const double* dev, size_t per_pt) {
-                return cudaMemcpyAsync(const_cast<double*>(dev) + (size_t) lo * per_pt, host + (size_t) lo * per_pt, (size_t) cnt * per_pt * sizeof(double), cudaMemcpyHostToDevice, cs);
+                return cudaMemcpyAsync(const_cast<double*>(dev) + (size_t) lo * per_pt, host + (size_t) lo * per_pt, (size_t) cnt * per_pt * sizeof(double), cudaMemcpyDefault, cs);
             };
             CUDA_OK(cudaMemcpyAsync(const_cast<int*>(ac.tidx), tidx.data() + lo, cnt * sizeof(int), cudaMemcpyHostToDevice, cs));
             CUDA_OK(h2d(Vm, a.Vm, 1));

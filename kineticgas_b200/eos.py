@@ -32,6 +32,13 @@ def _ptr(a):
     return None if a is None else a.ctypes.data_as(dp)
 
 
+class DevicePtr:
+    """A device-resident double array handed from one C-ABI call to the next (address + logical shape)."""
+
+    def __init__(self, address, shape):
+        self.address, self.shape = int(address), tuple(shape)
+
+
 class DeviceSaftVRMie:
     VAPPH, LIQPH = 2, 1                     # thermopack's phase flags (only the vapour-like root is implemented)
     Rgas = 6.02214076e23 * 1.380649e-23
@@ -133,6 +140,19 @@ class DeviceSaftVRMie:
         self._chk(self.L.kg_eos_tv_batch(self.h, n, _ptr(T), _ptr(Vm), _ptr(x), _ptr(out.get("dmudn")), _ptr(out.get("cp_ideal")),
                                          _ptr(out.get("pressure")), _ptr(out.get("dvdn"))), "kg_eos_tv_batch")
         return out
+
+    def tv_batch_dev(self, T, Vm, x, dmudn=True, cp_ideal=False, dvdn=False):
+        """As tv_batch, results left on the GPU: dict of DevicePtr (valid until the next call on this object), accepted by
+        MieKinGas.transport_batch(eos_inputs=...) -- the 5x5 matrices of 10^5 points never cross the PCIe bus."""
+        T = np.ascontiguousarray(np.atleast_1d(T), float)
+        n, nc = T.size, self.nc
+        Vm = np.ascontiguousarray(np.broadcast_to(np.asarray(Vm, float), (n,)))
+        x = np.ascontiguousarray(np.broadcast_to(np.asarray(x, float), (n, nc)))
+        dev = (C.c_void_p * 4)()
+        want = (1 if dmudn else 0) | (2 if cp_ideal else 0) | (8 if dvdn else 0)
+        self._chk(self.L.kg_eos_tv_batch_dev(self.h, n, _ptr(T), _ptr(Vm), _ptr(x), want, dev), "kg_eos_tv_batch_dev")
+        shapes = {"dmudn": (n, nc, nc), "cp_ideal": (n, nc), "dvdn": (n, nc)}
+        return {k: DevicePtr(dev[i], shapes[k]) for i, k in ((0, "dmudn"), (1, "cp_ideal"), (3, "dvdn")) if dev[i]}
 
     def specific_volume_batch(self, T, p, x):
         """Vapour-like molar volume [m^3/mol] of n state points (T, p, x)."""

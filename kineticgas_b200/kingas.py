@@ -36,7 +36,11 @@ class TransportOut(C.Structure):
 
 
 def _ptr(a):
-    return None if a is None else a.ctypes.data_as(dp)
+    if a is None:
+        return None
+    if hasattr(a, "address"):                       # eos.DevicePtr: a device-resident array from kg_eos_tv_batch_dev
+        return C.cast(C.c_void_p(a.address), dp)
+    return a.ctypes.data_as(dp)
 
 
 class TCache:
@@ -209,7 +213,8 @@ class MieKinGas:
             # device EoS (kineticgas_b200.eos.DeviceSaftVRMie): every missing input of the whole batch in one GPU pass
             miss = {"dmudn": need_dmudn and "dmudn" not in out, "cp_ideal": need_cp and "cp_ideal" not in out, "dvdn": need_dvdn and "dvdn" not in out}
             if any(miss.values()):
-                out.update(self.eos.tv_batch(T, Vm, xe, dmudn=miss["dmudn"], cp_ideal=miss["cp_ideal"], dvdn=miss["dvdn"]))
+                call = self.eos.tv_batch_dev if (n >= 4096 and hasattr(self.eos, "tv_batch_dev")) else self.eos.tv_batch
+                out.update(call(T, Vm, xe, dmudn=miss["dmudn"], cp_ideal=miss["cp_ideal"], dvdn=miss["dvdn"]))
         if need_dmudn and "dmudn" not in out:
             if self.eos is None:
                 raise RuntimeError("EoS is not set")
@@ -226,7 +231,7 @@ class MieKinGas:
                 p, = self.eos.pressure_tv(T[k], Vm[k], list(xe[k]))
                 rows.append(np.asarray(self.eos.specific_volume(T[k], p, list(xe[k]), self.eos.VAPPH, None, None, True)[1]))
             out["dvdn"] = np.array(rows)
-        return {k: np.ascontiguousarray(np.asarray(v, float).reshape(n, -1)) for k, v in out.items()}
+        return {k: (v if hasattr(v, "address") else np.ascontiguousarray(np.asarray(v, float).reshape(n, -1))) for k, v in out.items()}
 
     def _run(self, T, Vm, x, N, properties, want, frame=1, dependent_idx=-1, solvent_idx=-1, do_compress=True, eos_inputs=None, cache=None):
         """One kg_transport_batch call. want: names of kg_transport_out fields to return. Returns dict of arrays + 'scalar' flag."""

@@ -77,3 +77,26 @@ def test_transport_with_device_eos_equals_transport_with_thermopack_inputs():
     eta_tp = a.viscosity_tp(G[tag + "_Tp"][:4], G[tag + "_pp"][:4], G[tag + "_x"][:4], N=2)
     eta_tv = b.viscosity(G[tag + "_Tp"][:4], G[tag + "_vm_tp"][:4], G[tag + "_x"][:4], N=2)
     assert np.max(np.abs(eta_tp / eta_tv - 1)) < 1e-8
+
+
+def test_device_resident_hand_over_for_large_batches():
+    """n >= 4096: the EoS results stay on the GPU (kg_eos_tv_batch_dev) and kg_transport_batch reads them there (its EoS arrays may be
+    device pointers); same numbers as the host-array route."""
+    from kineticgas_b200 import MieKinGas, DeviceSaftVRMie
+    tag = "co2c1n2"
+    keep = G[tag + "_Vm"] > 2e-4
+    rep = 6000 // int(keep.sum()) + 1
+    T, Vm, x = (np.tile(G[tag + k][keep], (rep,) + (1,) * (G[tag + k].ndim - 1)) for k in ("_T", "_Vm", "_x"))
+    order = np.argsort(T, kind="stable")                        # runs of equal temperature, as sweeps have them
+    T, Vm, x = T[order], Vm[order], np.ascontiguousarray(x[order])
+    a = MieKinGas("CO2,C1,N2", N=2, use_eos="device")
+    ra = a.transport_batch(T, Vm, x, N=2)                       # device hand-over
+    eos = DeviceSaftVRMie("CO2,C1,N2")
+    host = eos.tv_batch(T, Vm, x, dmudn=True, cp_ideal=True)
+    rb = MieKinGas("CO2,C1,N2", N=2).transport_batch(T, Vm, x, N=2, eos_inputs=host)
+    for k in ("viscosity", "conductivity", "D", "DT"):
+        ok = np.isfinite(rb[k])
+        # not bit-equal: two model objects integrate Omega separately and the leaf sums are accumulated with atomics (order-dependent last bits)
+        assert np.max(np.abs(ra[k][ok] - rb[k][ok])) / np.max(np.abs(rb[k][ok])) < 1e-12, k
+    dev = eos.tv_batch_dev(T, Vm, x, dmudn=True, cp_ideal=True)
+    assert set(dev) == {"dmudn", "cp_ideal"} and dev["dmudn"].shape == (T.size, 3, 3)
