@@ -429,6 +429,17 @@ class ShimGpuMie(RefMie):
             raise RuntimeError("not a GpuMieKinGas handle")
         return {"cpu_theta_integrand_calls": out[0], "device_feeds": out[1], "omega_values_stored": out[2]}
 
+    def set_gpu_eos(self, eos):
+        """Install the device SAFT-VR Mie EoS (integration/gpu_saft_eos.h) through the reference's set_eos; `eos` is a
+        kineticgas_b200.DeviceSaftVRMie whose parameters are handed over (the C++ side creates its own handle)."""
+        sig, eps, la, lr = (np.ascontiguousarray(a, float) for a in eos.pair_matrices())
+        m, cpt = np.ascontiguousarray(eos.m, float), np.ascontiguousarray(eos.cp_type, np.int32)
+        cpp, mw = np.ascontiguousarray(eos.cp_par, float), np.ascontiguousarray(eos.mw, float)
+        err = C.create_string_buffer(512)
+        self.L.kgshim_set_gpu_eos.argtypes = [C.c_void_p, C.c_int, dp, dp, dp, dp, dp, ip, dp, dp, C.c_char_p, C.c_int]
+        if self.L.kgshim_set_gpu_eos(self.h, eos.nc, _p(m), _p(sig), _p(eps), _p(la), _p(lr), cpt.ctypes.data_as(ip), _p(cpp), _p(mw), err, 512):
+            raise RuntimeError(err.value.decode())
+
     def omega_table(self, T, l, r):
         T = np.ascontiguousarray(np.atleast_1d(T), float)
         l = np.ascontiguousarray(l, np.int32)

@@ -17,6 +17,7 @@
 #include <set>
 #include <mutex>
 #ifdef KG_WITH_GPU_SHIM
+#include "gpu_saft_eos.h"
 #include "gpu_miekingas.h"      // integration/gpu_miekingas.h: the reference-side shim over libkgcuda.so (integration/Makefile)
 #endif
 
@@ -362,6 +363,20 @@ int kgref_soret_coefficient(void* hv, double T, double Vm, const double* x, int 
 // integration/_build/libkgshim.so only: the same driver over a GpuMieKinGas (the reference's MieKinGas with precompute_* and the
 // transfer-length entry routed to the device). Every kgref_* property call works on the returned handle unchanged.
 extern "C" {
+// installs the device SAFT-VR Mie EoS (integration/gpu_saft_eos.h) into any handle through the reference's own set_eos
+// (cpp/eos_interface.h:57-135): pair matrices [nc_eos][nc_eos], Cp correlations as thermopack's database holds them
+int kgshim_set_gpu_eos(void* hv, int nc_eos, const double* m, const double* sigma, const double* eps_div_k, const double* la, const double* lr,
+                       const int32_t* cp_type, const double* cp_par, const double* mw, char* errbuf, int errcap) {
+    try {
+        Handle* h = static_cast<Handle*>(hv);
+        const size_t n2 = (size_t) nc_eos * nc_eos;
+        GpuSaftEoS e(nc_eos, vector1d(m, m + nc_eos), vector1d(sigma, sigma + n2), vector1d(eps_div_k, eps_div_k + n2), vector1d(la, la + n2),
+                     vector1d(lr, lr + n2), std::vector<int32_t>(cp_type, cp_type + nc_eos), vector1d(cp_par, cp_par + (size_t) nc_eos * KG_EOS_CP_PARAMS),
+                     vector1d(mw, mw + nc_eos));
+        h->kin->set_eos(GenericEoS(std::move(e)));
+        return 0;
+    } catch (const std::exception& e) { if (errbuf) { strncpy(errbuf, e.what(), errcap - 1); errbuf[errcap - 1] = 0; } return -1; }
+}
 void* kgshim_mie_create(int nc, const double* m, const double* sigma, const double* eps, const double* la, const double* lr,
                         int is_idealgas, int is_singlecomp, int device, char* errbuf, int errcap) {
     try {

@@ -166,3 +166,28 @@ def test_pybind_surface_tp_calls_and_transport_batch():
         assert abs(out["viscosity"][i] / stock.viscosity(Tb[i], Vb[i], list(xb[i]), N) - 1) < TOL
         assert np.max(np.abs(out["D"][i] / stock.interdiffusion(Tb[i], Vb[i], list(xb[i]), N, frame=1) - 1)) < TOL
         assert np.max(np.abs(out["DT"][i] / stock.thermal_diffusion_coeff(Tb[i], Vb[i], list(xb[i]), N, frame=1) - 1)) < TOL
+
+
+def test_reference_properties_with_the_device_eos_through_set_eos():
+    """The reference's own property code (diffusion needs dmudn, conductivity needs Cp_ideal: cpp/KineticGas_properties.cpp:459-500) with
+    integration/gpu_saft_eos.h installed through its set_eos (cpp/eos_interface.h:57-135) in place of thermopack, against the same object
+    fed thermopack's numbers as tables (tests/golden/eos_reference.npz, generated from the wheel vendored in the reference tree)."""
+    import os
+    from kineticgas_b200 import DeviceSaftVRMie
+    g = dict(np.load(os.path.join(os.path.dirname(__file__), "golden", "eos_reference.npz")))
+    stock, gpu, Mw, s = _both("CO2,C1,N2")
+    gpu.set_gpu_eos(DeviceSaftVRMie("CO2,C1,N2"))
+    done = 0
+    for k in range(g["co2c1n2_T"].size):
+        T, Vm, x = float(g["co2c1n2_T"][k]), float(g["co2c1n2_Vm"][k]), list(g["co2c1n2_x"][k])
+        if Vm < 3e-4 or done == 3:
+            continue
+        stock.set_eos(dmudn=g["co2c1n2_dmudn"][k], cp_id=g["co2c1n2_cp"][k], p=float(g["co2c1n2_p"][k]), vm=Vm)
+        D0, D1 = stock.interdiffusion(T, Vm, x, 2, frame=1), gpu.interdiffusion(T, Vm, x, 2, frame=1)
+        DT0, DT1 = stock.thermal_diffusion_coeff(T, Vm, x, 2, frame=1), gpu.thermal_diffusion_coeff(T, Vm, x, 2, frame=1)
+        c0, c1 = stock.thermal_conductivity_contribs(T, Vm, x, 2), gpu.thermal_conductivity_contribs(T, Vm, x, 2)
+        assert np.max(np.abs(np.array(D1) / np.array(D0) - 1)) < TOL
+        assert np.max(np.abs(np.array(DT1) - np.array(DT0))) / np.max(np.abs(DT0)) < TOL
+        assert abs(c1[2] / c0[2] - 1) < TOL                   # internal part: Cp_ideal from the device correlations
+        done += 1
+    assert done == 3
