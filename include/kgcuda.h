@@ -298,6 +298,21 @@ void kg_omega_table_destroy(kg_omega_table* t);
 int kg_measure_fp64_peak(int device, double* tflops, double* sm_mhz_est);
 
 /* ---------------------------------------------------------------------------------------------------------------------------
+ * Quantum-mechanical collision integrals (cpp/Quantum.cpp). Reduced energies E_red = E / eps_ij.
+ * kg_quantum_phase_shifts: Quantum::phase_shift / quantum_phase_shift / JKWB_phase_shift (cpp/Quantum.cpp:251-318,418-528) for n pairs
+ *   (l[k], E_red[k]); which = 0 as the reference switches (JKWB for l >= 1000 or E_red > 120), 1 Numerov, 2 JKWB. */
+int kg_quantum_phase_shifts(kg_model* m, int pair, int n, const int32_t* l, const double* E_red, int which, double* out, int32_t* status);
+/* kg_quantum_cross_sections: Quantum::cross_section (cpp/Quantum.cpp:1176-1236): Q^(n)(E) [m^2], out[nE][nn], orders n[k] in 0..6.
+ *   w_sym / w_anti weight the even-l / odd-l partial-wave sums (Quantum::get_symmetry_weights, :208-223: 0.5 / 0.5 for unlike particles,
+ *   1 / 0 for spin-0 bosons such as He-4, (s+1)/(2s+1) and s/(2s+1) swapped for fermions). status[nE] may be NULL.
+ * kg_quantum_omega: Quantum::quantum_omega (:1242-1259): Omega^(l,r)(T) [m^3/s ... the reference's units] for nT temperatures x nlr (l, r),
+ *   omega[nT][nlr]; status[nT] may be NULL. Not available for temperature-dependent (Feynman-Hibbs) potentials. */
+int kg_quantum_cross_sections(kg_model* m, int pair, double w_sym, double w_anti, int nn, const int32_t* n, int nE, const double* E_red,
+                              double* out, int32_t* status);
+int kg_quantum_omega(kg_model* m, int pair, double w_sym, double w_anti, int nT, const double* T, int nlr, const int32_t* l, const int32_t* r,
+                     double* omega, int32_t* status);
+
+/* ---------------------------------------------------------------------------------------------------------------------------
  * EoS-derived inputs on the device. Replaces, for batches of state points, the calls the reference makes on its
  * thermopack EoS object one point at a time (cpp/eos_interface.h:121-181; pykingas/MieKinGas.py:55-65 constructs `saftvrmie`):
  *   chemical_potential_tv(T, V, n, dmudn)  ->  dmudn     [n][nc][nc]  J/mol^2  (total: ideal + residual), at n = x (one mole)

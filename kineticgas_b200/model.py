@@ -145,6 +145,34 @@ class DeviceModel:
         raise_on_status(st)
         return (chi, R) if want_R else chi
 
+    def quantum_phase_shifts(self, pair, l, E_red, which=0):
+        """Partial-wave phase shifts (Quantum::phase_shift, cpp/Quantum.cpp:522-528) at angular momenta l and reduced energies E / eps;
+        which = 1 forces the Numerov solution, 2 the JKWB approximation."""
+        l = np.ascontiguousarray(np.atleast_1d(l), np.int32)
+        E = np.ascontiguousarray(np.broadcast_to(np.asarray(E_red, float), l.shape))
+        out, st = np.empty(l.size), np.zeros(l.size, np.int32)
+        self._chk(self.L.kg_quantum_phase_shifts(self.h, pair, l.size, _pi(l), _p(E), which, _p(out), _pi(st)), "kg_quantum_phase_shifts")
+        raise_on_status(st)
+        return out
+
+    def quantum_cross_sections(self, pair, n, E_red, w_sym=0.5, w_anti=0.5):
+        """Q^(n)(E) [m^2] (Quantum::cross_section, cpp/Quantum.cpp:1200-1236): [nE][nn]."""
+        n = np.ascontiguousarray(np.atleast_1d(n), np.int32)
+        E = np.ascontiguousarray(np.atleast_1d(E_red), float)
+        out, st = np.empty((E.size, n.size)), np.zeros(E.size, np.int32)
+        self._chk(self.L.kg_quantum_cross_sections(self.h, pair, w_sym, w_anti, n.size, _pi(n), E.size, _p(E), _p(out), _pi(st)), "kg_quantum_cross_sections")
+        raise_on_status(st)
+        return out
+
+    def quantum_omega(self, pair, T, l, r, w_sym=0.5, w_anti=0.5):
+        """Omega^(l,r)(T) from partial-wave phase shifts (Quantum::quantum_omega, cpp/Quantum.cpp:1242-1259): [nT][nlr]."""
+        T = np.ascontiguousarray(np.atleast_1d(T), float)
+        l, r = np.ascontiguousarray(l, np.int32), np.ascontiguousarray(r, np.int32)
+        out, st = np.empty((T.size, l.size)), np.zeros(T.size, np.int32)
+        self._chk(self.L.kg_quantum_omega(self.h, pair, w_sym, w_anti, T.size, _p(T), l.size, _pi(l), _pi(r), _p(out), _pi(st)), "kg_quantum_omega")
+        raise_on_status(st)
+        return out
+
     def potential_points(self, pair, T, r):
         """u(r) [J] and du/dr [J/m] (Spherical::potential / potential_derivative_r) at temperature T."""
         r = np.ascontiguousarray(np.atleast_1d(r), float)

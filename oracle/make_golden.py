@@ -581,3 +581,66 @@ def eos_reference(fname="eos_reference.npz"):
 if __name__ == "__main__" and "eos" in sys.argv[1:]:
     eos_database()
     eos_reference()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# quantum-mechanical collision integrals of the unmodified reference build (cpp/Quantum.cpp) for the ab-initio potentials
+# whose models are quantum by default (pykingas/multiparam.py): phase shifts (Numerov, JKWB, the reference's switch), cross sections Q^(n)(E)
+# and Omega^(n,s)(T) with quantum_active = true.  tests/golden/quantum_reference.npz
+# ---------------------------------------------------------------------------------------------------------------
+def quantum_reference(fname="quantum_reference.npz"):
+    import ctypes as C
+    from oracle import ref
+    L = ref.lib()
+    L.kgref_generic_create.restype = C.c_void_p
+    L.kgref_generic_create.argtypes = [C.c_int, C.c_char_p, C.c_int, C.c_char_p, C.c_int]
+    L.kgref_set_quantum_active.argtypes = [C.c_void_p, C.c_int]
+    L.kgref_phase_shift.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.POINTER(C.c_double)]
+    L.kgref_quantum_cross_section.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.POINTER(C.c_double)]
+    L.kgref_omega.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.POINTER(C.c_double)]
+    rng = np.random.default_rng(4)
+    out = {}
+    val = C.c_double()
+    for tag, kind, comp in (("hfd_he", 4, b"HE"), ("mtt_ne", 3, b"NE"), ("pat_h2", 5, b"H2")):
+        err = C.create_string_buffer(512)
+        h = L.kgref_generic_create(kind, comp, 0, err, 512)
+        assert h, err.value
+        assert L.kgref_set_quantum_active(h, 1) == 0
+        # Numerov phase shifts: low l over a wide energy range, and l near the centrifugal cut-off
+        l = np.concatenate([rng.integers(0, 12, 40), rng.integers(12, 80, 24)]).astype(np.int32)
+        E = np.concatenate([10.0 ** rng.uniform(-3.2, 2.0, 40), 10.0 ** rng.uniform(0.5, 2.05, 24)])
+        num = np.zeros(l.size)
+        for k in range(l.size):
+            assert L.kgref_phase_shift(h, 0, 0, int(l[k]), float(E[k]), 1, C.byref(val)) == 0
+            num[k] = val.value
+        # JKWB: the energies and angular momenta where the reference switches to it, and a few below
+        lj = rng.integers(0, 400, 40).astype(np.int32)
+        Ej = np.concatenate([10.0 ** rng.uniform(2.08, 3.0, 30), 10.0 ** rng.uniform(0.0, 2.0, 10)])
+        jk = np.zeros(lj.size)
+        for k in range(lj.size):
+            assert L.kgref_phase_shift(h, 0, 0, int(lj[k]), float(Ej[k]), 2, C.byref(val)) == 0
+            jk[k] = val.value
+        # cross sections Q^(n)(E), n = 0..4 (n >= 3 takes the general branch of cross_section_kernel)
+        nq = np.tile(np.arange(0, 5), 6).astype(np.int32)
+        Eq = np.repeat(10.0 ** np.linspace(-3.5, 2.4, 6), 5)
+        Q = np.zeros(nq.size)
+        for k in range(nq.size):
+            assert L.kgref_quantum_cross_section(h, 0, 0, int(nq[k]), float(Eq[k]), C.byref(val)) == 0
+            Q[k] = val.value
+        # Omega^(n,s)(T): the N = 2 viscosity / conductivity set at three temperatures
+        Tom = np.array([30.0, 120.0, 400.0]) if tag != "hfd_he" else np.array([15.0, 80.0, 300.0])
+        lr = np.array([(1, 1), (1, 2), (2, 2), (2, 3), (3, 3)], np.int32)
+        om = np.zeros((Tom.size, len(lr)))
+        for t in range(Tom.size):
+            for k, (a, b) in enumerate(lr):
+                assert L.kgref_omega(h, 0, 0, int(a), int(b), float(Tom[t]), C.byref(val)) == 0
+                om[t, k] = val.value
+            print(tag, "omega at", Tom[t], om[t], flush=True)
+        out.update({f"{tag}_l": l, f"{tag}_E": E, f"{tag}_numerov": num, f"{tag}_lj": lj, f"{tag}_Ej": Ej, f"{tag}_jkwb": jk,
+                    f"{tag}_nq": nq, f"{tag}_Eq": Eq, f"{tag}_Q": Q, f"{tag}_Tom": Tom, f"{tag}_lr": lr, f"{tag}_omega": om})
+        np.savez(os.path.join(GOLD, fname), **out)
+    print("quantum fixture written")
+
+
+if __name__ == "__main__" and "quantum" in sys.argv[1:]:
+    quantum_reference()

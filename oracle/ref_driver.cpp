@@ -119,6 +119,32 @@ int kgref_generic_scales(void* hv, double* out4) {
     Handle* h = static_cast<Handle*>(hv);
     return guarded(h, [&]{ if (!h->scales) throw std::runtime_error("not a generic model"); h->scales(out4); });
 }
+// ---- quantum-mechanical collision integrals (cpp/Quantum.cpp): phase shifts, cross sections; omega follows the active switch ----
+static Quantum* as_quantum(void* hv) {
+    Quantum* q = dynamic_cast<Quantum*>(static_cast<Handle*>(hv)->kin.get());
+    if (!q) throw std::runtime_error("not a Quantum model");
+    return q;
+}
+int kgref_set_quantum_active(void* hv, int active) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{ as_quantum(hv)->set_quantum_active(active != 0); });
+}
+int kgref_phase_shift(void* hv, int i, int j, int l, double E_red, int which, double* out) {      // which: 0 phase_shift, 1 Numerov, 2 JKWB
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{
+        Quantum* q = as_quantum(hv);
+        double r_lev = 0;
+        *out = (which == 0) ? q->phase_shift(i, j, l, E_red) : (which == 1) ? q->quantum_phase_shift(i, j, l, E_red, r_lev) : q->JKWB_phase_shift(i, j, l, E_red);
+    });
+}
+int kgref_quantum_cross_section(void* hv, int i, int j, int n, double E_red, double* out) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{ *out = as_quantum(hv)->cross_section(i, j, n, E_red); });
+}
+int kgref_r_classical_forbidden(void* hv, int i, int j, int l, double E_red, double* out) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{ *out = as_quantum(hv)->r_classical_forbidden(i, j, l, E_red); });
+}
 double kgref_potential_rr(void* hv, int i, int j, double r) { return static_cast<Handle*>(hv)->kin->potential_dblderivative_rr(i, j, r); }
 
 void* kgref_mie_create(int nc, const double* m, const double* sigma, const double* eps,
