@@ -407,6 +407,49 @@ def run_eos_leg(local_rank, steps, peak_tflops):
                               "us_per_point": THERMOPACK_US_PER_POINT, "seconds_for_this_batch": tp_s, "value": n / tp_s, "unit": "state points/s"}}
 
 
+# ------------------------------------------------------------------------------------------------ quantum collision integrals
+def run_quantum_leg(local_rank, with_cpu):
+    """Omega^(l,r)(T) of HFD-B2 helium from partial-wave phase shifts (the pykingas default for the ab-initio potentials) on a 64-point
+    T grid 10-1000 K x the five (l,r) of the N = 2 viscosity / conductivity set; host arrays in and out. CPU: the unmodified reference
+    build (oracle/_ref) on a bounded sample, one fresh object per value."""
+    from kineticgas_b200 import HFD_B2
+    kin = HFD_B2("HE", device=local_rank)
+    T = np.geomspace(10.0, 1000.0, 64)
+    l, r = [1, 1, 2, 2, 3], [1, 2, 2, 3, 3]
+    ws, wa = kin.symmetry_weights()
+    kin.dev.quantum_omega(0, T[:2], l, r, ws, wa)              # warm-up
+    t0 = time.perf_counter()
+    om = kin.dev.quantum_omega(0, T, l, r, ws, wa)
+    dt = time.perf_counter() - t0
+    out = {"workload": "SURVEY 8f row 4: quantum Omega(l,r)(T) of HFD-B2 helium, 64 temperatures 10-1000 K x 5 (l,r), phase shifts by Numerov / JKWB",
+           "value": om.size / dt, "unit": "Omega/s", "seconds": dt, "all_finite": bool(np.isfinite(om).all())}
+    if with_cpu:
+        try:
+            import ctypes as C
+            from oracle import ref
+            L = ref.lib()
+            L.kgref_generic_create.restype = C.c_void_p
+            L.kgref_generic_create.argtypes = [C.c_int, C.c_char_p, C.c_int, C.c_char_p, C.c_int]
+            L.kgref_set_quantum_active.argtypes = [C.c_void_p, C.c_int]
+            L.kgref_omega_model.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.POINTER(C.c_double)]
+            err, val = C.create_string_buffer(512), C.c_double()
+            secs, errs = [], []
+            for (a, b, Tk) in ((2, 2, 300.0), (1, 1, 77.0), (2, 2, 20.0)):
+                h = L.kgref_generic_create(4, b"HE", 0, err, 512)
+                L.kgref_set_quantum_active(h, 1)
+                t0 = time.perf_counter()
+                L.kgref_omega_model(h, 0, 0, a, b, Tk, C.byref(val))
+                secs.append(time.perf_counter() - t0)
+                errs.append(abs(float(kin.dev.quantum_omega(0, [Tk], [a], [b], ws, wa)[0, 0]) / val.value - 1))
+            out["cpu_baseline"] = {"kind": "reference", "cores": 1, "value": len(secs) / sum(secs), "unit": "Omega/s",
+                                   "sample": "Quantum::omega of the unmodified reference build, fresh object per value: (2,2) at 300 K, (1,1) at 77 K, (2,2) at 20 K",
+                                   "seconds_each": secs}
+            out["parity"] = {"max_rel_err": max(errs), "tolerance": 1e-6, "against": "the same three reference values"}
+        except Exception as ex:                                 # the reference build is test infrastructure; absent -> no CPU leg
+            out["cpu_baseline"] = {"unavailable": str(ex)[:200]}
+    return out
+
+
 # ------------------------------------------------------------------------------------------------ strong scaling (fixed total work)
 def _rank_values(v, world):
     import torch
@@ -827,9 +870,10 @@ def main():
             dist.all_reduce(t4, op=dist.ReduceOp.MAX)
         qm["ms_max"], fc["ms_max"] = float(t4[0].item()), float(t4[1].item())
 
-    par = cfg0 = eos_leg = None
+    par = cfg0 = eos_leg = quantum_leg = None
     if rank == 0 and not args.nt and not args.no_extra_configs and not args.no_state_points:
         eos_leg = run_eos_leg(local_rank, max(1, min(args.steps, 2)), peak_tflops)
+        quantum_leg = run_quantum_leg(local_rank, not args.no_cpu_baseline)
     if rank == 0 and not args.nt:
         par = parity_block(model)
         if not args.no_state_points:
@@ -925,6 +969,8 @@ def main():
                                              "arrays prepared outside the timed region"}
         if eos_leg is not None:
             out["eos_inputs"] = eos_leg
+        if quantum_leg is not None:
+            out["quantum_omega"] = quantum_leg
         if not args.no_cpu_baseline:
             n_sample = args.cpu_sample or min(64, max(16, cores))
             cb, _ = run_cpu_reference(n_gpus, n_sample, min(cores, n_sample))

@@ -311,6 +311,9 @@ int kg_quantum_cross_sections(kg_model* m, int pair, double w_sym, double w_anti
                               double* out, int32_t* status);
 int kg_quantum_omega(kg_model* m, int pair, double w_sym, double w_anti, int nT, const double* T, int nlr, const int32_t* l, const int32_t* r,
                      double* omega, int32_t* status);
+/* kg_model_set_quantum: Quantum::set_quantum_active (cpp/Quantum.cpp:1520-1528) for the device tables: while active, kg_tcache_create (and
+ * with it kg_transport_batch) takes every Omega^(l,r)_ij(T) from kg_quantum_omega with the weights w_sym[npairs], w_anti[npairs]. */
+int kg_model_set_quantum(kg_model* m, int active, const double* w_sym, const double* w_anti);
 
 /* ---------------------------------------------------------------------------------------------------------------------------
  * EoS-derived inputs on the device. Replaces, for batches of state points, the calls the reference makes on its

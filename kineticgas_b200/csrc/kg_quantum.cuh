@@ -92,15 +92,17 @@ __device__ double q_numerov_phase(const PairParams& pp, double kappa2, int l, do
     double r0 = 0, r1 = 0, r2 = 0, r3 = x0, r4 = x0 + h;
     double g0 = 0, g1 = 0, g2 = 0, g3 = gfun(r3), g4 = gfun(r4);
     double p0 = 0, p1 = 0, p2 = 0, p3 = 0, p4 = h;
+    double Ul = 0, dUl = 0;                          // potential at the newest node: one evaluation serves the recurrence and the free test
     auto step = [&]() {
         r0 = r1; r1 = r2; r2 = r3; r3 = r4; g0 = g1; g1 = g2; g2 = g3; g3 = g4; p0 = p1; p1 = p2; p2 = p3; p3 = p4;
         r4 = r3 + h;
-        g4 = gfun(r4);
+        qpot<NT>(pp, r4, Ul, dUl);
+        g4 = LL / (r4 * r4) + kappa2 * (Ul - E);
         p4 = (p3 * (2.0 + 10.0 * s2 * g3) - p2 * (1.0 - s2 * g2)) / (1.0 - s2 * g4);
     };
     step(); step();
     int guard = 0;
-    do { step(); } while (!is_free(r4) && guard++ < 4000000);
+    do { step(); } while (!((fabs(Ul / E) < 1e-7) && (fabs(dUl / (ks * E)) < 1e-7)) && guard++ < 4000000);
     if (guard >= 4000000) st |= KG_STATUS_TS_EXHAUSTED;
     const double A1 = 0.5 * (p3 - p1), A2 = 0.5 * (p4 - p0);
     const double B1 = s2 * (g3 * p3 - g1 * p1), B2 = s2 * (g4 * p4 - g0 * p0);
@@ -477,5 +479,17 @@ extern "C" int kg_quantum_omega(kg_model* m, int pair, double w_sym, double w_an
         }
     }
     for (const Seq& sq : seqs) omega[(size_t) sq.t * nlr + sq.k] = sq.I * sqrt(2. * BOLTZMANN * T[sq.t] / (3.14159265359 * mu));
+    return 0;
+}
+
+// Quantum::set_quantum_active (cpp/Quantum.cpp:1520-1528) for the device tables: while active, kg_tcache_create takes every Omega^(l,r)_ij(T)
+// from kg_quantum_omega with the given symmetry weights per pair (w_sym[npairs], w_anti[npairs]) instead of the classical quadrature.
+extern "C" int kg_model_set_quantum(kg_model* m, int active, const double* w_sym, const double* w_anti) {
+    KG_TRACE();
+    if (!m) return -1;
+    if (active && (!w_sym || !w_anti)) { m->err = "kg_model_set_quantum: symmetry weights required"; return -1; }
+    if (active && (m->coeff_T_required || (m->generic && m->gen_T_dependent))) { m->err = "kg_model_set_quantum: temperature-dependent (Feynman-Hibbs) potentials have no quantum engine"; return -1; }
+    m->quantum_active = active != 0;
+    if (active) { m->q_wsym.assign(w_sym, w_sym + m->npairs); m->q_wanti.assign(w_anti, w_anti + m->npairs); }
     return 0;
 }

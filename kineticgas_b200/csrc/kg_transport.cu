@@ -1263,6 +1263,21 @@ extern "C" int kg_tcache_create(kg_model* m, const kg_transport_opts* opts, int 
     auto ms_since = [&](std::chrono::steady_clock::time_point t0) { return std::chrono::duration<double, std::milli>(now() - t0).count(); };
     auto t_stage = now();
     m->timings[1] = m->timings[2] = m->timings[3] = m->timings[4] = 0;
+    if (m->quantum_active) {
+        // Quantum::omega (cpp/Quantum.cpp:1266-1268): every collision integral from partial-wave phase shifts
+        std::vector<int32_t> ll(tm.lr_l, tm.lr_l + nlr), rr(tm.lr_r, tm.lr_r + nlr);
+        std::vector<double> hom((size_t) nT * Np * nlr, 0.0), tmp((size_t) nT * nlr);
+        std::vector<int32_t> qst(nT);
+        for (int p = 0; p < Np; p++) {
+            rc = kg_quantum_omega(m, p, m->q_wsym[p], m->q_wanti[p], nT, T, nlr, ll.data(), rr.data(), tmp.data(), qst.data());
+            if (rc) { tcache_free(c); return rc; }
+            for (int t = 0; t < nT; t++) for (int k = 0; k < nlr; k++) hom[((size_t) t * Np + p) * nlr + k] = tmp[(size_t) t * nlr + k];
+        }
+        TC_CUDA(cudaMemcpyAsync(c->d_omega, hom.data(), hom.size() * sizeof(double), cudaMemcpyHostToDevice, s));
+        TC_CUDA(cudaStreamSynchronize(s));
+        std::fill(c->is_corr.begin(), c->is_corr.end(), 0);
+        any_numeric = any_corr = false;
+    }
     if (any_numeric) {
         kg_omega_plan* plan = nullptr;
         std::vector<int32_t> ll(tm.lr_l, tm.lr_l + nlr), rr(tm.lr_r, tm.lr_r + nlr);

@@ -575,6 +575,46 @@ class _GenericSpherical(MieKinGas):
         if int(order) != self.FH_order:
             self.FH_order = int(order)
             self._build_device_model()
+            self.set_quantum_active(self._quantum_active)
+
+    # ---- quantum-mechanical collision integrals (pykingas/Quantum.py:125-135, cpp/Quantum.cpp:1266-1268, 1520-1528)
+    _quantum_active = False
+    HALF_SPIN, ROT_GROUND_STATE = 0, 0            # fluids/*.json "Quantum" blocks of HE, NE, AR: spin-0 bosons in the rotational ground state
+
+    def symmetry_weights(self):
+        """Quantum::get_symmetry_weights (cpp/Quantum.cpp:208-223) of the like pair."""
+        s, j = self.HALF_SPIN / 2.0, self.ROT_GROUND_STATE
+        w = [((s + 1) * (j + 1) + s * j) / ((2 * s + 1) * (2 * j + 1)), ((s + 1) * j + s * (j + 1)) / ((2 * s + 1) * (2 * j + 1))]
+        return w[::-1] if self.HALF_SPIN % 2 else w
+
+    def set_quantum_active(self, active):
+        """While active the collision integrals of every property come from partial-wave phase shifts (Quantum::quantum_omega) instead of
+        classical trajectories. Not available for Feynman-Hibbs corrected potentials (the reference classes FH_* are classical)."""
+        active = bool(active) and self.FH_order == 0
+        ws, wa = self.symmetry_weights()
+        a, b = np.array([ws], float), np.array([wa], float)
+        self.dev._chk(self.dev.L.kg_model_set_quantum(self.dev.h, int(active), _ptr(a), _ptr(b)), "kg_model_set_quantum")
+        if active != self._quantum_active:
+            self._caches = {}
+        self._quantum_active = active
+
+    def get_quantum_active(self):
+        return self._quantum_active
+
+    def omega(self, i, j, l, r, T):
+        """Quantum::omega: quantum or classical by the active switch."""
+        if self._quantum_active:
+            ws, wa = self.symmetry_weights()
+            return float(self.dev.quantum_omega(0, [T], [l], [r], ws, wa)[0, 0])
+        return float(self.dev.omega_batch([T], [l], [r])[0, 0, 0])
+
+    def cross_section(self, i, j, n, E_red):
+        """Quantum::cross_section at reduced energy E / eps (quantum engine)."""
+        ws, wa = self.symmetry_weights()
+        return float(self.dev.quantum_cross_sections(0, [n], [E_red], ws, wa)[0, 0])
+
+    def phase_shift(self, i, j, l, E_red):
+        return float(self.dev.quantum_phase_shifts(0, [l], [E_red])[0])
 
     def potential(self, i, j, r, T=300.0):
         return self.dev.potential_points(0, T, r)[0]
@@ -617,30 +657,33 @@ class ModTangToennis(_GenericSpherical):
     """pykingas.multiparam.ModTangToennis / FH_ModTangToennies (cpp/multiparam.cpp:5-89): Ar, Ne, He."""
     KIND = 3
 
-    def __init__(self, comps, FH_order=0, N=4, device=0, use_eos=None):
+    def __init__(self, comps, FH_order=0, N=4, device=0, use_eos=None, quantum_active=True):
         from .fluids import TANG_TOENNIES
         from .model import tang_toennies_params
         p = TANG_TOENNIES[comps]
         self._setup(comps, MIE[comps][0], p["sigma"], p["eps_div_k"], tang_toennies_params(p), FH_order, N, device, use_eos)
+        self.set_quantum_active(quantum_active)          # pykingas/multiparam.py:94-104: quantum by default
 
 
 class HFD_B2(_GenericSpherical):
     """pykingas.multiparam.HFD_B2 / FH_HFD_B2 (cpp/multiparam.cpp:91-182): helium."""
     KIND = 4
 
-    def __init__(self, comps="HE", FH_order=0, N=4, device=0, use_eos=None):
+    def __init__(self, comps="HE", FH_order=0, N=4, device=0, use_eos=None, quantum_active=True):
         from .fluids import HFD_B2 as TAB
         from .model import hfd_b2_params
         p = TAB[comps]
         self._setup(comps, MIE[comps][0], p["sigma"], p["eps_div_k"], hfd_b2_params(p), FH_order, N, device, use_eos)
+        self.set_quantum_active(quantum_active)          # pykingas/multiparam.py:126-129
 
 
 class Patowski(_GenericSpherical):
     """pykingas.multiparam.Patowski / PatowskiFH (cpp/multiparam.cpp:184-279): hydrogen."""
     KIND = 5
 
-    def __init__(self, comps="H2", FH_order=0, N=4, device=0, use_eos=None):
+    def __init__(self, comps="H2", FH_order=0, N=4, device=0, use_eos=None, quantum_active=True):
         from .fluids import PATKOWSKI
         from .model import patkowski_params
         p = PATKOWSKI[comps]
         self._setup(comps, MIE[comps][0], p["sigma"], p["eps_div_k"], patkowski_params(p), FH_order, N, device, use_eos)
+        self.set_quantum_active(quantum_active)

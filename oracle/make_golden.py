@@ -625,17 +625,69 @@ def quantum_reference(fname="quantum_reference.npz"):
         Eq = np.repeat(10.0 ** np.linspace(-3.5, 2.4, 6), 5)
         Q = np.zeros(nq.size)
         for k in range(nq.size):
+            L.kgref_set_quantum_active(h, 0); L.kgref_set_quantum_active(h, 1)      # empties the bucketed cross-section cache
             assert L.kgref_quantum_cross_section(h, 0, 0, int(nq[k]), float(Eq[k]), C.byref(val)) == 0
             Q[k] = val.value
-        # Omega^(n,s)(T): the N = 2 viscosity / conductivity set at three temperatures
-        Tom = np.array([30.0, 120.0, 400.0]) if tag != "hfd_he" else np.array([15.0, 80.0, 300.0])
+        # Omega^(n,s)(T). The reference memoises cross sections in buckets of 0.01 eps (CrossSectionPoint, cpp/KineticGasCache.h:125-136:
+        # round(100 E)), first come first served, so its own Omega depends on which energies were asked for before (1e-3 at low T, where
+        # the nodes of one integral already share buckets). Two references are therefore stored:
+        #   omega_native : Quantum::omega of a FRESH object per value (kgref_omega_model), kept where no two nodes of the integral can share a bucket
+        #   omega_exact  : the reference's quadrature (quantum_omega, cpp/Quantum.cpp:1242-1259 + simpson_inf, Integration.cpp:346-373) restated
+        #                  here over the reference's own cross_section with the cache emptied before every call
+        L.kgref_omega_model.argtypes = L.kgref_omega.argtypes
+        L.kgref_generic_scales.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        sc = (C.c_double * 4)()
+        L.kgref_generic_scales(h, sc)
+        eps_J, mu = sc[1], sc[2] / 2
+        KB = 1.38064852e-23
+        w2 = (C.c_double * 2)()
+        L.kgref_symmetry_weights.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_double)]
+        assert L.kgref_symmetry_weights(h, 0, 0, w2) == 0
+
+        def q_uncached(n, E):
+            L.kgref_set_quantum_active(h, 0); L.kgref_set_quantum_active(h, 1)          # state change empties the cache (cpp/Quantum.cpp:1524-1526)
+            assert L.kgref_quantum_cross_section(h, 0, 0, int(n), float(E), C.byref(val)) == 0
+            return val.value
+
+        def omega_exact(n, s, T):
+            kern = lambda x: np.exp(-x) * x ** (s + 1) * q_uncached(n, x * KB * T / eps_J)
+
+            def simpson(a, b):
+                dx = (b - a) / 10
+                v = kern(a) + kern(b)
+                for i in range(1, 5):
+                    v += 4 * kern(a + (2 * i - 1) * dx) + 2 * kern(a + 2 * i * dx)
+                v += 4 * kern(b - dx)
+                return v * dx / 3
+            x0, xe = 0.0, (s + 1) / 3
+            I = simpson(x0, xe)
+            dx, tol, part = (xe - x0) / 10, 1e-8, 1e-2
+            while True:
+                x0, xe = xe, xe + 10 * dx
+                Ip = simpson(x0, xe)
+                I += Ip
+                c = abs(Ip / I)
+                if c < tol:
+                    break
+                if c < part:
+                    dx *= 2; part *= 0.1
+                if not part > tol:
+                    break
+            return I * np.sqrt(2 * KB * T / (np.pi * mu))
+
+        Tom = {"hfd_he": np.array([15.0, 80.0, 300.0]), "mtt_ne": np.array([60.0, 300.0]), "pat_h2": np.array([50.0, 300.0])}[tag]
         lr = np.array([(1, 1), (1, 2), (2, 2), (2, 3), (3, 3)], np.int32)
-        om = np.zeros((Tom.size, len(lr)))
+        om, om_native = np.zeros((Tom.size, len(lr))), np.full((Tom.size, len(lr)), np.nan)
         for t in range(Tom.size):
             for k, (a, b) in enumerate(lr):
-                assert L.kgref_omega(h, 0, 0, int(a), int(b), float(Tom[t]), C.byref(val)) == 0
-                om[t, k] = val.value
-            print(tag, "omega at", Tom[t], om[t], flush=True)
+                om[t, k] = omega_exact(a, b, Tom[t])
+                if (b + 1) / 30 * KB * Tom[t] / eps_J > 0.02:          # node spacing of the first block in reduced energy: no shared buckets
+                    hf = L.kgref_generic_create(kind, comp, 0, err, 512)
+                    L.kgref_set_quantum_active(hf, 1)
+                    assert L.kgref_omega_model(hf, 0, 0, int(a), int(b), float(Tom[t]), C.byref(val)) == 0
+                    om_native[t, k] = val.value
+            print(tag, "omega at", Tom[t], om[t], om_native[t] / om[t] - 1, flush=True)
+        out[f"{tag}_wts"] = np.array([w2[0], w2[1]]); out[f"{tag}_omega_native"] = om_native
         out.update({f"{tag}_l": l, f"{tag}_E": E, f"{tag}_numerov": num, f"{tag}_lj": lj, f"{tag}_Ej": Ej, f"{tag}_jkwb": jk,
                     f"{tag}_nq": nq, f"{tag}_Eq": Eq, f"{tag}_Q": Q, f"{tag}_Tom": Tom, f"{tag}_lr": lr, f"{tag}_omega": om})
         np.savez(os.path.join(GOLD, fname), **out)
@@ -644,3 +696,37 @@ def quantum_reference(fname="quantum_reference.npz"):
 
 if __name__ == "__main__" and "quantum" in sys.argv[1:]:
     quantum_reference()
+
+
+def quantum_transport(fname="quantum_transport_reference.npz"):
+    """Dilute-gas viscosity and thermal conductivity (N = 2) of the reference's HFD-B2 helium with quantum_active = true (the pykingas
+    default, pykingas/multiparam.py:126-129): every collision integral from Quantum::quantum_omega."""
+    import ctypes as C
+    from oracle import ref
+    L = ref.lib()
+    L.kgref_generic_create.restype = C.c_void_p
+    L.kgref_generic_create.argtypes = [C.c_int, C.c_char_p, C.c_int, C.c_char_p, C.c_int]
+    L.kgref_set_quantum_active.argtypes = [C.c_void_p, C.c_int]
+    L.kgref_viscosity.argtypes = [C.c_void_p, C.c_double, C.c_double, C.POINTER(C.c_double), C.c_int, C.c_int, C.POINTER(C.c_double)]
+    L.kgref_thermal_conductivity.argtypes = L.kgref_viscosity.argtypes
+    L.kgref_set_eos_tables_nc.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_double, C.c_double, C.POINTER(C.c_double)]
+    err = C.create_string_buffer(512)
+    T = np.array([20.0, 77.0, 300.0])
+    eta, lam = np.zeros(T.size), np.zeros(T.size)
+    x = (C.c_double * 2)(0.5, 0.5)
+    cp = (C.c_double * 1)(2.5 * 8.31446261815324)
+    val = C.c_double()
+    for t in range(T.size):
+        h = L.kgref_generic_create(4, b"HE", 0, err, 512)          # fresh object per temperature: nothing shared through the bucketed caches
+        L.kgref_set_quantum_active(h, 1)
+        L.kgref_set_eos_tables_nc(h, 1, None, cp, 1e5, 0.024, None)
+        assert L.kgref_viscosity(h, float(T[t]), 0.024, x, 2, 2, C.byref(val)) == 0
+        eta[t] = val.value
+        assert L.kgref_thermal_conductivity(h, float(T[t]), 0.024, x, 2, 2, C.byref(val)) == 0
+        lam[t] = val.value
+        print("He quantum", T[t], eta[t], lam[t], flush=True)
+    np.savez(os.path.join(GOLD, fname), T=T, viscosity=eta, conductivity=lam, cp_ideal=cp[0])
+
+
+if __name__ == "__main__" and "quantum_eta" in sys.argv[1:]:
+    quantum_transport()

@@ -141,6 +141,10 @@ int kgref_quantum_cross_section(void* hv, int i, int j, int n, double E_red, dou
     Handle* h = static_cast<Handle*>(hv);
     return guarded(h, [&]{ *out = as_quantum(hv)->cross_section(i, j, n, E_red); });
 }
+int kgref_symmetry_weights(void* hv, int i, int j, double* out2) {
+    Handle* h = static_cast<Handle*>(hv);
+    return guarded(h, [&]{ auto w = as_quantum(hv)->get_symmetry_weights(i, j); out2[0] = w[0]; out2[1] = w[1]; });
+}
 int kgref_r_classical_forbidden(void* hv, int i, int j, int l, double E_red, double* out) {
     Handle* h = static_cast<Handle*>(hv);
     return guarded(h, [&]{ *out = as_quantum(hv)->r_classical_forbidden(i, j, l, E_red); });

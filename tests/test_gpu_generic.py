@@ -54,6 +54,7 @@ def test_w_and_omega(wk):
 
 def test_ideal_gas_viscosity_runs_on_generic_model():
     kin = model("tt_ar")
+    kin.set_quantum_active(False)           # classical collision integrals here; the partial-wave engine is tests/test_gpu_quantum.py
     eta = kin.viscosity(300.0, 0.024, [1.0], N=2)
     assert 2.0e-5 < eta < 2.6e-5            # argon at 300 K: 22.7 uPa s
 

@@ -1,0 +1,65 @@
+"""SURVEY 8f row 4 on the GPU: quantum-mechanical collision integrals (csrc/kg_quantum.cuh, C-ABI kg_quantum_*) against the unmodified
+reference build with quantum_active = true (cpp/Quantum.cpp; fixture tests/golden/quantum_reference.npz from oracle/make_golden.py quantum):
+Numerov and JKWB partial-wave phase shifts, cross sections Q^(n)(E) incl. the general-n branch, and Omega^(l,r)(T) for the ab-initio
+potentials whose pykingas classes are quantum by default (HFD-B2 helium, modified Tang-Toennies neon, Patkowski hydrogen).
+Tolerances: phase shifts 1e-7 absolute (the same Numerov recurrence on the same grid; what differs is the rounding of the potential and
+the Bessel functions), cross sections and Omega 1e-6 relative (north_star)."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+G = dict(np.load(os.path.join(os.path.dirname(__file__), "golden", "quantum_reference.npz")))
+TAGS = [t for t in ("hfd_he", "mtt_ne", "pat_h2") if t + "_omega" in G]
+
+
+def model(tag):
+    from kineticgas_b200 import HFD_B2, ModTangToennis, Patowski
+    kin = {"hfd_he": lambda: HFD_B2("HE"), "mtt_ne": lambda: ModTangToennis("NE"), "pat_h2": lambda: Patowski("H2")}[tag]()
+    return kin, [float(v) for v in G.get(tag + "_wts", [1.0, 0.0])]
+
+
+@pytest.mark.parametrize("tag", TAGS)
+def test_numerov_phase_shifts(tag):
+    kin, _ = model(tag)
+    d = kin.dev.quantum_phase_shifts(0, G[tag + "_l"], G[tag + "_E"], which=1)
+    err = np.abs(d - G[tag + "_numerov"])
+    print(tag, "numerov max abs err", err.max())
+    assert err.max() < 1e-7
+
+
+@pytest.mark.parametrize("tag", TAGS)
+def test_jkwb_phase_shifts(tag):
+    kin, _ = model(tag)
+    d = kin.dev.quantum_phase_shifts(0, G[tag + "_lj"], G[tag + "_Ej"], which=2)
+    ref = G[tag + "_jkwb"]
+    err = np.abs(d - ref) / np.maximum(np.abs(ref), 1.0)
+    print(tag, "jkwb max err", err.max())
+    # the JKWB integrals come from simpson_inf with its interval-doubling decisions (tol 1e-8): at a knife edge a last-bit difference in the
+    # integrand flips a decision and moves the result by ~1e-7 relative
+    assert err.max() < 1e-6 and np.median(err) < 1e-9
+
+
+@pytest.mark.parametrize("tag", TAGS)
+def test_cross_sections(tag):
+    kin, (ws, wa) = model(tag)
+    E = np.unique(G[tag + "_Eq"])
+    n = np.arange(0, 5)
+    Q = kin.dev.quantum_cross_sections(0, n, E, ws, wa)
+    ref = np.array([[G[tag + "_Q"][(G[tag + "_Eq"] == e) & (G[tag + "_nq"] == k)][0] for k in n] for e in E])
+    err = np.abs(Q / ref - 1)
+    print(tag, "Q max rel err per n", err.max(axis=0))
+    assert err.max() < 1e-6
+
+
+@pytest.mark.parametrize("tag", TAGS)
+def test_quantum_omega(tag):
+    kin, (ws, wa) = model(tag)
+    lr = G[tag + "_lr"]
+    om = kin.dev.quantum_omega(0, G[tag + "_Tom"], lr[:, 0], lr[:, 1], ws, wa)
+    err = np.abs(om / G[tag + "_omega"] - 1)                  # the reference's quadrature over its own un-bucketed cross sections
+    nat = G[tag + "_omega_native"]
+    err_nat = np.abs(om / nat - 1)[np.isfinite(nat)]           # Quantum::omega of a fresh reference object
+    print(tag, "Omega max rel err per T", err.max(axis=1), "against the native call", err_nat.max() if err_nat.size else None)
+    assert err.max() < 1e-6 and (err_nat.size == 0 or err_nat.max() < 1e-6)
