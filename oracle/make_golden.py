@@ -588,7 +588,7 @@ if __name__ == "__main__" and "eos" in sys.argv[1:]:
 # whose models are quantum by default (pykingas/multiparam.py): phase shifts (Numerov, JKWB, the reference's switch), cross sections Q^(n)(E)
 # and Omega^(n,s)(T) with quantum_active = true.  tests/golden/quantum_reference.npz
 # ---------------------------------------------------------------------------------------------------------------
-def quantum_reference(fname="quantum_reference.npz"):
+def quantum_reference(fname="quantum_reference.npz", only=None):
     import ctypes as C
     from oracle import ref
     L = ref.lib()
@@ -602,6 +602,8 @@ def quantum_reference(fname="quantum_reference.npz"):
     out = {}
     val = C.c_double()
     for tag, kind, comp in (("hfd_he", 4, b"HE"), ("mtt_ne", 3, b"NE"), ("pat_h2", 5, b"H2")):
+        if only and tag not in only:
+            continue
         err = C.create_string_buffer(512)
         h = L.kgref_generic_create(kind, comp, 0, err, 512)
         assert h, err.value
@@ -696,6 +698,8 @@ def quantum_reference(fname="quantum_reference.npz"):
 
 if __name__ == "__main__" and "quantum" in sys.argv[1:]:
     quantum_reference()
+if __name__ == "__main__" and "quantum_h2" in sys.argv[1:]:
+    quantum_reference("quantum_reference_h2.npz", only=("pat_h2",))
 
 
 def quantum_transport(fname="quantum_transport_reference.npz"):
