@@ -429,23 +429,29 @@ extern "C" int kg_quantum_omega(kg_model* m, int pair, double w_sym, double w_an
     }
     if (status) for (int t = 0; t < nT; t++) status[t] = 0;
     const double tol = 1e-8;
+    constexpr int AHEAD = 3;       // blocks evaluated per round and integral: the pending one and two more on the assumption that the interval
+                                   // is not doubled (it is doubled a handful of times per integral; those speculative blocks are thrown away)
+    auto node_x = [](double x0, double xe, int i) {                  // simpson(func, x0, xe, 10)'s node expressions
+        const double dxb = (xe - x0) / 10.;
+        return (i == 0) ? x0 : (i == 10) ? xe : (i == 9) ? xe - dxb : x0 + i * dxb;
+    };
     for (int round = 0; round < 4000; round++) {
-        // nodes of the pending block of every unfinished integral; equal energies are evaluated once
         std::vector<double> E; std::map<double, int> index;
-        std::vector<std::array<int, 11>> node_of(seqs.size());
+        std::vector<std::array<int, 11 * AHEAD>> node_of(seqs.size());
         bool any = false;
         for (size_t q = 0; q < seqs.size(); q++) {
-            Seq& sq = seqs[q];
+            const Seq& sq = seqs[q];
             if (sq.done) continue;
             any = true;
-            const double dxb = (sq.xe - sq.x0) / 10.;
-            for (int i = 0; i <= 10; i++) {
-                const double x = (i == 0) ? sq.x0 : (i == 10) ? sq.xe : (i == 9) ? sq.xe - dxb : sq.x0 + i * dxb;      // simpson's node expressions
-                const double Er = x * BOLTZMANN * T[sq.t] / pp.eps;
-                auto f = index.find(Er);
-                if (f == index.end()) { f = index.emplace(Er, (int) E.size()).first; E.push_back(Er); }
-                node_of[q][i] = f->second;
-                (void) x;
+            double x0 = sq.x0, xe = sq.xe;
+            for (int bk = 0; bk < AHEAD; bk++) {
+                for (int i = 0; i <= 10; i++) {
+                    const double Er = node_x(x0, xe, i) * BOLTZMANN * T[sq.t] / pp.eps;
+                    auto f = index.find(Er);
+                    if (f == index.end()) { f = index.emplace(Er, (int) E.size()).first; E.push_back(Er); }
+                    node_of[q][11 * bk + i] = f->second;
+                }
+                x0 = xe; xe += 10 * sq.dx;
             }
         }
         if (!any) break;
@@ -454,28 +460,31 @@ extern "C" int kg_quantum_omega(kg_model* m, int pair, double w_sym, double w_an
         if (rc) return rc;
         for (size_t q = 0; q < seqs.size(); q++) {
             Seq& sq = seqs[q];
-            if (sq.done) continue;
-            const double dxb = (sq.xe - sq.x0) / 10.;
-            auto kern = [&](int i) {
-                const double x = (i == 0) ? sq.x0 : (i == 10) ? sq.xe : (i == 9) ? sq.xe - dxb : sq.x0 + i * dxb;
-                if (status) status[sq.t] |= st[node_of[q][i]];
-                return exp(-x) * pow(x, r[sq.k] + 1) * Q[(size_t) node_of[q][i] * nn + sq.ni];
-            };
-            double val = kern(0) + kern(10);
-            for (int i = 1; i <= 4; i++) val += 4. * kern(2 * i - 1) + 2. * kern(2 * i);
-            val += 4. * kern(9);
-            const double Ip = val * (dxb / 3.);
-            sq.I += Ip;
-            if (sq.first) { sq.first = false; }
-            else {
-                const double conv = fabs(Ip / sq.I);
-                if (conv < tol) { sq.done = true; continue; }
-                if (conv < sq.part_tol) { sq.dx *= 2; sq.part_tol *= 0.1; }
-                if (!(sq.part_tol > tol)) { sq.done = true; continue; }
+            for (int bk = 0; bk < AHEAD && !sq.done; bk++) {
+                auto kern = [&](int i) {
+                    const double x = node_x(sq.x0, sq.xe, i);
+                    const int e = node_of[q][11 * bk + i];
+                    if (status) status[sq.t] |= st[e];
+                    return exp(-x) * pow(x, r[sq.k] + 1) * Q[(size_t) e * nn + sq.ni];
+                };
+                double val = kern(0) + kern(10);
+                for (int i = 1; i <= 4; i++) val += 4. * kern(2 * i - 1) + 2. * kern(2 * i);
+                val += 4. * kern(9);
+                const double Ip = val * ((sq.xe - sq.x0) / 10. / 3.);
+                sq.I += Ip;
+                bool doubled = false;
+                if (sq.first) sq.first = false;
+                else {
+                    const double conv = fabs(Ip / sq.I);
+                    if (conv < tol) { sq.done = true; break; }
+                    if (conv < sq.part_tol) { sq.dx *= 2; sq.part_tol *= 0.1; doubled = true; }
+                    if (!(sq.part_tol > tol)) { sq.done = true; break; }
+                }
+                if (std::isnan(sq.I)) { if (status) status[sq.t] |= KG_STATUS_NAN; sq.done = true; break; }
+                sq.x0 = sq.xe;
+                sq.xe += 10 * sq.dx;
+                if (doubled) break;                                  // the blocks evaluated ahead assumed the old interval
             }
-            if (std::isnan(sq.I)) { if (status) status[sq.t] |= KG_STATUS_NAN; sq.done = true; continue; }
-            sq.x0 = sq.xe;
-            sq.xe += 10 * sq.dx;
         }
     }
     for (const Seq& sq : seqs) omega[(size_t) sq.t * nlr + sq.k] = sq.I * sqrt(2. * BOLTZMANN * T[sq.t] / (3.14159265359 * mu));

@@ -4,7 +4,7 @@
 tag=${1:-r2}
 cd "$(dirname "$0")/.."
 mkdir -p profiles
-for f in bench_n1.json bench_reference_arm.json pytest_gpu.log smoke.log launches.csv fp64_ops.csv fp64_ops_bench.json; do
+for f in bench_n1.json bench_reference_arm.json pytest_gpu.log smoke.log launches.csv fp64_ops.csv fp64_ops_bench.json eos_fp64_ops.csv quantum_fp64_ops.csv quantum_ops.log; do
   [ -s gpurun_out/${tag}_$f ] && cp gpurun_out/${tag}_$f profiles/${tag}_$f
 done
 cp gpurun_out/${tag}_ncu_*_raw.csv gpurun_out/${tag}_ncu_*_digest.txt profiles/ 2>/dev/null

@@ -17,8 +17,13 @@ done
 ncu --set full --import-source on --clock-control none --kernel-name regex:mesh_level --launch-skip 3 --launch-count 1 -f -o gpurun_out/${tag}_mesh_level_p4 python bench.py --steps 1 --warmup 3 $B > /dev/null 2>> gpurun_out/${tag}_ncu_mesh_level.err
 ncu --set full --import-source on --clock-control none --kernel-name regex:state_kernel --launch-skip 2 --launch-count 1 -f -o gpurun_out/${tag}_state python tools/profile_state.py > /dev/null 2> gpurun_out/${tag}_ncu_state.err
 ncu --set full --import-source on --clock-control none --kernel-name regex:rdf_kernel --launch-skip 2 --launch-count 1 -f -o gpurun_out/${tag}_rdf python tools/profile_state.py > /dev/null 2>> gpurun_out/${tag}_ncu_state.err
+# EoS and quantum kernels: FP64 op counters of every launch, one full capture each
+ncu --metrics $M --clock-control none --kernel-name regex:"eos_" --csv --log-file gpurun_out/${tag}_eos_fp64_ops.csv python tools/profile_eos.py > /dev/null 2>&1
+ncu --set full --import-source on --clock-control none --kernel-name regex:eos_hess --launch-skip 2 --launch-count 1 -f -o gpurun_out/${tag}_eos_hess python tools/profile_eos.py > /dev/null 2> gpurun_out/${tag}_ncu_eos.err
+ncu --metrics $M --clock-control none --kernel-name regex:"q_xsec" --csv --log-file gpurun_out/${tag}_quantum_fp64_ops.csv python tools/profile_quantum.py > gpurun_out/${tag}_quantum_ops.log 2>&1
+ncu --set full --import-source on --clock-control none --kernel-name regex:q_xsec --launch-skip 2 --launch-count 1 -f -o gpurun_out/${tag}_q_xsec python tools/profile_quantum.py > /dev/null 2> gpurun_out/${tag}_ncu_quantum.err
 # digest the captures here (ncu reads them on the box) and drop the reports: gpurun brings back at most 64 MiB
-for k in theta_setup theta_kernel mesh_level mesh_level_p4 state rdf; do
+for k in theta_setup theta_kernel mesh_level mesh_level_p4 state rdf eos_hess q_xsec; do
   rep=gpurun_out/${tag}_$k.ncu-rep
   [ -s $rep ] || continue
   ncu -i $rep --page raw --csv > gpurun_out/${tag}_ncu_${k}_raw.csv 2>/dev/null
