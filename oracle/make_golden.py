@@ -588,7 +588,7 @@ if __name__ == "__main__" and "eos" in sys.argv[1:]:
 # whose models are quantum by default (pykingas/multiparam.py): phase shifts (Numerov, JKWB, the reference's switch), cross sections Q^(n)(E)
 # and Omega^(n,s)(T) with quantum_active = true.  tests/golden/quantum_reference.npz
 # ---------------------------------------------------------------------------------------------------------------
-def quantum_reference(fname="quantum_reference.npz", only=None):
+def quantum_reference(fname="quantum_reference.npz", only=None, with_omega=True):
     import ctypes as C
     from oracle import ref
     L = ref.lib()
@@ -678,6 +678,8 @@ def quantum_reference(fname="quantum_reference.npz", only=None):
             return I * np.sqrt(2 * KB * T / (np.pi * mu))
 
         Tom = {"hfd_he": np.array([15.0, 80.0, 300.0]), "mtt_ne": np.array([60.0, 300.0]), "pat_h2": np.array([50.0, 300.0])}[tag]
+        if not with_omega:
+            Tom = Tom[:0]
         lr = np.array([(1, 1), (1, 2), (2, 2), (2, 3), (3, 3)], np.int32)
         om, om_native = np.zeros((Tom.size, len(lr))), np.full((Tom.size, len(lr)), np.nan)
         for t in range(Tom.size):
@@ -698,6 +700,8 @@ def quantum_reference(fname="quantum_reference.npz", only=None):
 
 if __name__ == "__main__" and "quantum" in sys.argv[1:]:
     quantum_reference()
+if __name__ == "__main__" and "quantum_quick" in sys.argv[1:]:
+    quantum_reference("quantum_reference_quick.npz", only=("mtt_ne", "pat_h2"), with_omega=False)
 if __name__ == "__main__" and "quantum_h2" in sys.argv[1:]:
     quantum_reference("quantum_reference_h2.npz", only=("pat_h2",))
 
