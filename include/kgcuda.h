@@ -314,6 +314,8 @@ int kg_quantum_omega(kg_model* m, int pair, double w_sym, double w_anti, int nT,
 /* kg_model_set_quantum: Quantum::set_quantum_active (cpp/Quantum.cpp:1520-1528) for the device tables: while active, kg_tcache_create (and
  * with it kg_transport_batch) takes every Omega^(l,r)_ij(T) from kg_quantum_omega with the weights w_sym[npairs], w_anti[npairs]. */
 int kg_model_set_quantum(kg_model* m, int active, const double* w_sym, const double* w_anti);
+/* Quantum::set_JKWB_limits (cpp/Quantum.h:128-130; defaults 120, 1000): JKWB phase shifts for E_red > E_limit or l >= l_limit. */
+int kg_model_set_jkwb_limits(kg_model* m, double E_limit, int l_limit);
 
 /* ---------------------------------------------------------------------------------------------------------------------------
  * EoS-derived inputs on the device. Replaces, for batches of state points, the calls the reference makes on its

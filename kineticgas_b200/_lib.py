@@ -18,7 +18,7 @@ EXPORTS = [
     "kg_omega_plan_create_masked", "kg_omega_table_create", "kg_omega_table_eval", "kg_omega_table_eval_dev", "kg_omega_table_save",
     "kg_omega_table_load", "kg_omega_table_lr", "kg_omega_table_info", "kg_omega_table_destroy", "kg_cross_sections", "kg_second_virial", "kg_model_set_temperature_dependent", "kg_build_info", "kg_host_alloc", "kg_host_free", "kg_tcache_create", "kg_tcache_destroy", "kg_tcache_lr", "kg_tcache_fetch", "kg_transport_batch", "kg_last_timings",
     "kg_chi_points_noalloc", "kg_chi_points_noalloc_max",
-    "kg_eos_saftvrmie_create", "kg_eos_destroy", "kg_eos_last_error", "kg_eos_tv_batch", "kg_eos_specific_volume_batch", "kg_eos_last_kernel_ms", "kg_eos_tv_batch_dev", "kg_quantum_phase_shifts", "kg_quantum_cross_sections", "kg_quantum_omega", "kg_model_set_quantum",
+    "kg_eos_saftvrmie_create", "kg_eos_destroy", "kg_eos_last_error", "kg_eos_tv_batch", "kg_eos_specific_volume_batch", "kg_eos_last_kernel_ms", "kg_eos_tv_batch_dev", "kg_quantum_phase_shifts", "kg_quantum_cross_sections", "kg_quantum_omega", "kg_model_set_quantum", "kg_model_set_jkwb_limits",
 ]
 
 
@@ -62,6 +62,7 @@ def lib():
         L.kg_quantum_phase_shifts.argtypes = [C.c_void_p, C.c_int, C.c_int, ip, dp, C.c_int, dp, ip]
         L.kg_quantum_cross_sections.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_int, ip, C.c_int, dp, dp, ip]
         L.kg_quantum_omega.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_int, dp, C.c_int, ip, ip, dp, ip]
+        L.kg_model_set_jkwb_limits.argtypes = [C.c_void_p, C.c_double, C.c_int]
         L.kg_model_set_quantum.argtypes = [C.c_void_p, C.c_int, dp, dp]
         L.kg_eos_tv_batch_dev.argtypes = [C.c_void_p, C.c_int, dp, dp, dp, C.c_uint, C.POINTER(C.c_void_p)]
         L.kg_eos_specific_volume_batch.argtypes = [C.c_void_p, C.c_int, dp, dp, dp, dp, ip]

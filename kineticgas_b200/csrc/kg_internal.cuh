@@ -65,6 +65,7 @@ struct kg_model {
     size_t pool_cached = 0;
     bool quantum_active = false;        // kg_model_set_quantum: device tables take Omega from the partial-wave engine (kg_quantum_omega)
     std::vector<double> q_wsym, q_wanti;   // per pair: weights of the even-l / odd-l sums
+    double q_jkwb_E = 120.0; int q_jkwb_l = 1000;   // Quantum::set_JKWB_limits (defaults cpp/Quantum.h:153-154)
     bool tl_warp_search = false;        // KG_TL_WARP_SEARCH=1: one warp per b_mid / b_max search (comparison runs; measured slower)
     int* h_pinned = nullptr;            // page-locked host memory: 16 ints of the model + 32 slots of 8 ints handed to plans (run flags)
     unsigned pinned_used = 0;           // slot bitmap (cudaMallocHost / cudaFreeHost per plan cost ~1 ms each and synchronise the device)

@@ -210,19 +210,19 @@ __device__ double q_potential_root(const PairParams& pp, int& st) {
 
 // Quantum::phase_shift (cpp/Quantum.cpp:522-528); which: 0 the reference's switch, 1 Numerov, 2 JKWB
 template<int NT>
-__device__ double q_phase(const PairParams& pp, double kappa2, double s0, int l, double E, int which, int& st) {
-    const bool jk = (which == 2) || (which == 0 && (l >= Q_JKWB_L || E > Q_JKWB_E));
+__device__ double q_phase(const PairParams& pp, double kappa2, double s0, int l, double E, int which, int& st, double jE = Q_JKWB_E, int jL = Q_JKWB_L) {
+    const bool jk = (which == 2) || (which == 0 && (l >= jL || E > jE));
     return jk ? q_jkwb_phase<NT>(pp, kappa2, s0, l, E, st) : q_numerov_phase<NT>(pp, kappa2, l, E, st);
 }
 
 template<int NT>
-__global__ void __launch_bounds__(128) q_phase_kernel(PairParams pp, double kappa2, int n, const int* __restrict__ l, const double* __restrict__ E,
+__global__ void __launch_bounds__(128) q_phase_kernel(PairParams pp, double kappa2, double jE, int jL, int n, const int* __restrict__ l, const double* __restrict__ E,
                                                       int which, double* __restrict__ out, int* __restrict__ status) {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= n) return;
     int st = 0;
     const double s0 = q_potential_root<NT>(pp, st);
-    out[e] = q_phase<NT>(pp, kappa2, s0, l[e], E[e], which, st);
+    out[e] = q_phase<NT>(pp, kappa2, s0, l[e], E[e], which, st, jE, jL);
     if (status) status[e] = st;
 }
 
@@ -260,7 +260,7 @@ __device__ double q_xsec_term(int n, int l, const double* __restrict__ d) {
 // into the warp's cache; lanes 0 .. 2 nn - 1 each own one (n, parity) sum and advance it with the reference's stop rule as far as the cache allows.
 constexpr int Q_MAXN = 8;
 template<int NT>
-__global__ void __launch_bounds__(128) q_xsec_kernel(PairParams pp, double kappa2, double w_sym, double w_anti, int nE, const double* __restrict__ E_in,
+__global__ void __launch_bounds__(128) q_xsec_kernel(PairParams pp, double kappa2, double jE, int jL, double w_sym, double w_anti, int nE, const double* __restrict__ E_in,
                                                      int nn, const int* __restrict__ nlist, double* __restrict__ dcache, int Lcap,
                                                      double* __restrict__ out, int* __restrict__ status) {
     const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(128) q_xsec_kernel(PairParams pp, double kappa
     int Lhave = 0;
     while (__any_sync(full, !done)) {
         if (Lhave + 32 > Lcap) { st |= KG_STATUS_TS_EXHAUSTED; break; }
-        d[Lhave + lane] = q_phase<NT>(pp, kappa2, s0, Lhave + lane, E, 0, st);
+        d[Lhave + lane] = q_phase<NT>(pp, kappa2, s0, Lhave + lane, E, 0, st, jE, jL);
         Lhave += 32;
         __syncwarp();
         while (!done && lnext + myn < Lhave) {
@@ -327,10 +327,10 @@ extern "C" int kg_quantum_phase_shifts(kg_model* m, int pair, int n, const int32
     CUDA_OK(cudaMemcpyAsync(dE, E_red, n * sizeof(double), cudaMemcpyHostToDevice, s));
     const int grid = (n + 127) / 128;
     switch (m->ntpad) {
-        case 1: q_phase_kernel<1><<<grid, 128, 0, s>>>(pp, kappa2, n, dl, dE, which, dout, dst); break;
-        case 2: q_phase_kernel<2><<<grid, 128, 0, s>>>(pp, kappa2, n, dl, dE, which, dout, dst); break;
-        case 4: q_phase_kernel<4><<<grid, 128, 0, s>>>(pp, kappa2, n, dl, dE, which, dout, dst); break;
-        default: q_phase_kernel<6><<<grid, 128, 0, s>>>(pp, kappa2, n, dl, dE, which, dout, dst); break;
+        case 1: q_phase_kernel<1><<<grid, 128, 0, s>>>(pp, kappa2, m->q_jkwb_E, m->q_jkwb_l, n, dl, dE, which, dout, dst); break;
+        case 2: q_phase_kernel<2><<<grid, 128, 0, s>>>(pp, kappa2, m->q_jkwb_E, m->q_jkwb_l, n, dl, dE, which, dout, dst); break;
+        case 4: q_phase_kernel<4><<<grid, 128, 0, s>>>(pp, kappa2, m->q_jkwb_E, m->q_jkwb_l, n, dl, dE, which, dout, dst); break;
+        default: q_phase_kernel<6><<<grid, 128, 0, s>>>(pp, kappa2, m->q_jkwb_E, m->q_jkwb_l, n, dl, dE, which, dout, dst); break;
     }
     CUDA_OK(cudaGetLastError());
     CUDA_OK(cudaMemcpyAsync(out, dout, n * sizeof(double), cudaMemcpyDeviceToHost, s));
@@ -362,10 +362,10 @@ static int q_cross_sections_dev(kg_model* m, int pair, double w_sym, double w_an
     CUDA_OK(cudaMemcpyAsync(dE, E_red, nE * sizeof(double), cudaMemcpyHostToDevice, s));
     const int grid = (nE + 3) / 4;                       // 4 warps per CTA, one warp per energy
     switch (m->ntpad) {
-        case 1: q_xsec_kernel<1><<<grid, 128, 0, s>>>(pp, kappa2, w_sym, w_anti, nE, dE, nn, dn, dcache, Lcap, dout, dst); break;
-        case 2: q_xsec_kernel<2><<<grid, 128, 0, s>>>(pp, kappa2, w_sym, w_anti, nE, dE, nn, dn, dcache, Lcap, dout, dst); break;
-        case 4: q_xsec_kernel<4><<<grid, 128, 0, s>>>(pp, kappa2, w_sym, w_anti, nE, dE, nn, dn, dcache, Lcap, dout, dst); break;
-        default: q_xsec_kernel<6><<<grid, 128, 0, s>>>(pp, kappa2, w_sym, w_anti, nE, dE, nn, dn, dcache, Lcap, dout, dst); break;
+        case 1: q_xsec_kernel<1><<<grid, 128, 0, s>>>(pp, kappa2, m->q_jkwb_E, m->q_jkwb_l, w_sym, w_anti, nE, dE, nn, dn, dcache, Lcap, dout, dst); break;
+        case 2: q_xsec_kernel<2><<<grid, 128, 0, s>>>(pp, kappa2, m->q_jkwb_E, m->q_jkwb_l, w_sym, w_anti, nE, dE, nn, dn, dcache, Lcap, dout, dst); break;
+        case 4: q_xsec_kernel<4><<<grid, 128, 0, s>>>(pp, kappa2, m->q_jkwb_E, m->q_jkwb_l, w_sym, w_anti, nE, dE, nn, dn, dcache, Lcap, dout, dst); break;
+        default: q_xsec_kernel<6><<<grid, 128, 0, s>>>(pp, kappa2, m->q_jkwb_E, m->q_jkwb_l, w_sym, w_anti, nE, dE, nn, dn, dcache, Lcap, dout, dst); break;
     }
     CUDA_OK(cudaGetLastError());
     CUDA_OK(cudaMemcpyAsync(q, dout, (size_t) nE * nn * sizeof(double), cudaMemcpyDeviceToHost, s));
@@ -500,5 +500,14 @@ extern "C" int kg_model_set_quantum(kg_model* m, int active, const double* w_sym
     if (active && (m->coeff_T_required || (m->generic && m->gen_T_dependent))) { m->err = "kg_model_set_quantum: temperature-dependent (Feynman-Hibbs) potentials have no quantum engine"; return -1; }
     m->quantum_active = active != 0;
     if (active) { m->q_wsym.assign(w_sym, w_sym + m->npairs); m->q_wanti.assign(w_anti, w_anti + m->npairs); }
+    return 0;
+}
+
+// Quantum::set_JKWB_limits (cpp/Quantum.h:128-130): the semiclassical phase shift replaces the Numerov solution for E / eps > E_limit or l >= l_limit
+extern "C" int kg_model_set_jkwb_limits(kg_model* m, double E_limit, int l_limit) {
+    KG_TRACE();
+    if (!m) return -1;
+    if (!(E_limit > 0) || l_limit < 1) { m->err = "kg_model_set_jkwb_limits: invalid argument"; return -1; }
+    m->q_jkwb_E = E_limit; m->q_jkwb_l = l_limit;
     return 0;
 }

@@ -601,6 +601,11 @@ class _GenericSpherical(MieKinGas):
     def get_quantum_active(self):
         return self._quantum_active
 
+    def set_JKWB_limits(self, E, l):
+        """Quantum::set_JKWB_limits (cpp/Quantum.h:128-130): JKWB phase shifts for E / eps > E or angular momentum >= l."""
+        self.dev._chk(self.dev.L.kg_model_set_jkwb_limits(self.dev.h, float(E), int(l)), "kg_model_set_jkwb_limits")
+        self._caches = {}
+
     def omega(self, i, j, l, r, T):
         """Quantum::omega: quantum or classical by the active switch."""
         if self._quantum_active:
