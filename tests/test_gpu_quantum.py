@@ -11,7 +11,7 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 G = dict(np.load(os.path.join(os.path.dirname(__file__), "golden", "quantum_reference.npz")))
-for _extra in ("quantum_reference_h2.npz", "quantum_reference_quick.npz"):        # generated separately by the same script (long-running parts)
+for _extra in ("quantum_reference_h2.npz", "quantum_reference_ne60.npz", "quantum_reference_quick.npz"):        # generated separately by the same script (long-running parts)
     _p = os.path.join(os.path.dirname(__file__), "golden", _extra)
     if os.path.exists(_p):
         G.update({k: v for k, v in np.load(_p).items() if k not in G})
