@@ -593,7 +593,8 @@ class _GenericSpherical(MieKinGas):
         active = bool(active) and self.FH_order == 0
         ws, wa = self.symmetry_weights()
         a, b = np.array([ws], float), np.array([wa], float)
-        self.dev._chk(self.dev.L.kg_model_set_quantum(self.dev.h, int(active), _ptr(a), _ptr(b)), "kg_model_set_quantum")
+        if getattr(self, "dev", None) is not None:          # host-only descriptions (tests of the descriptor blocks) have no device model
+            self.dev._chk(self.dev.L.kg_model_set_quantum(self.dev.h, int(active), _ptr(a), _ptr(b)), "kg_model_set_quantum")
         if active != self._quantum_active:
             self._caches = {}
         self._quantum_active = active
