@@ -28,6 +28,7 @@ LR = [(l, r) for l in range(1, 5) for r in range(l, 5)]
 # FP64-pipe lane instructions (DFMA + DMUL + DADD, predicated-on threads) per unit of work, calibrated on ncu's
 # smsp__sass_thread_inst_executed_op_{dfma,dmul,dadd}_pred_on summed over ALL launches of one full-size headline step of this build
 # (tools/gpu_calib.sh; profiles/r2_summary.md) and divided by the step's device counters:
+NCU_THETA_TRAFFIC_BYTES = 757.5e6 + 261.1e6 + 153.7e6 + 412.3e6     # ncu DRAM read + write of the largest theta + set-up launch pair (see roofline.traffic_note)
 FP64_PER_NODE = 8.99         # theta_kernel<2>: 5.402e10 lane instructions / 6.012e9 executed node evaluations (all-in: coarse nodes 8 each,
                              # end nodes, difference formulas, continuation to the stop, node-by-node tier)
 FP64_PER_SETUP = 228.0       # theta_setup_kernel<2>: 7.43e9 lane instructions / 32.63 M root findings (integer-exponent get_R in registers)
@@ -892,7 +893,12 @@ def main():
                             "achieved": (fp64_theta + fp64_setup) * 2.0 / theta_s / 1e12 if theta_ms > 0 else None, "peak": peak_tflops, "unit": "TFLOP/s",
                             "frac": (fp64_theta + fp64_setup) / theta_s / issue_peak if theta_ms > 0 else None,
                             "frac_step": (fp64_theta + fp64_setup + mesh_cells * FP64_PER_CELL) / (ms * 1e-3) / issue_peak,
-                            "traffic": None,
+                            "traffic": NCU_THETA_TRAFFIC_BYTES,
+                            "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of the largest theta_kernel<2> + theta_setup_kernel<2> launch pair of a "
+                                            "full-size step (pass 5: 19.2 M integrals), one `ncu --set full` capture (profiles/r2_ncu_theta_kernel_digest.txt, "
+                                            "r2_ncu_theta_setup_digest.txt): 1.02 + 0.57 GB against 1.38 GB algorithmic (per integral: set-up reads the 8 B "
+                                            "work-list entry and writes 24 B of parameters, the sum reads both and writes an 8 B result) -- 0.4 TB/s over "
+                                            "the pair's 4.2 ms, the kernels are not HBM-bound",
                             "definition": "frac = FP64-pipe lane instructions executed by the two theta kernels (device counters of node evaluations, incl. "
                                           "rejected attempts and node-by-node sums, and of root findings, x the per-unit instruction counts calibrated with "
                                           "ncu) / (peak/2 x their summed duration); `achieved` prices every such instruction as one DFMA (2 flop). "
