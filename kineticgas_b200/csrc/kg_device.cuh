@@ -93,6 +93,86 @@ static __device__ __noinline__ void gen_eval(const GenPot* __restrict__ gp, doub
     dU = du * (gp->e_scale * gp->len_scale);
 }
 
+// ---- the same evaluation for the serial marches of the quantum engine (kg_quantum.cuh), where a lane calls it millions of times --------
+// x^(2^i) once per call; a power is then a product of the selected squares in the order ipow_pos multiplies them (bit-identical results)
+struct PowLadder { double x[6]; };
+__device__ __forceinline__ PowLadder make_ladder(double x) {
+    PowLadder L;
+    L.x[0] = x;
+#pragma unroll
+    for (int i = 1; i < 6; i++) L.x[i] = L.x[i - 1] * L.x[i - 1];
+    return L;
+}
+__device__ __forceinline__ double ladder_pow(const PowLadder& L, int n) {      // 0 <= n < 64
+    // branches, not selects: the exponent belongs to the term, so a warp takes them together (selects cost two FSEL per bit and
+    // were 20 % of the cross-section kernel's instructions)
+    double r = (n & 1) ? L.x[0] : 1.0;
+#pragma unroll
+    for (int i = 1; i < 6; i++) if ((n >> i) & 1) r *= L.x[i];
+    return r;
+}
+__device__ __forceinline__ double laurent_scale(int e, double r, double s, const PowLadder& Lr, const PowLadder& Ls) {
+    const int a = e >= 0 ? e : -e;
+    if (a >= 64) return e >= 0 ? ipow_pos(r, a) : ipow_pos(s, a);
+    if (e >= 0) return ladder_pow(Lr, a);
+    return ladder_pow(Ls, a);
+}
+
+// gen_eval with the prefactor and derivative polynomials of a term run as two interleaved Horner chains, coefficients fetched four
+// ahead, powers from the ladders: same operations in the same order per chain, so U and dU are bit-identical to gen_eval's.
+// `gp` may point to a copy of the potential in shared memory.
+static __device__ __noinline__ void gen_eval_march(const GenPot* __restrict__ gp, double ri, double& U, double& dU) {
+    const double r = ri * gp->len_scale;
+    int p = 0;
+    while (p < gp->npieces && !(r < gp->piece[p].r_hi)) p++;
+    U = 0.0; dU = 0.0;
+    if (p == gp->npieces) return;
+    const GenPiece& pc = gp->piece[p];
+    const double s = 1.0 / r;
+    const bool up = r >= 1.0;                   // Horner in s from the lowest power, else in r from the highest
+    const double x = up ? s : r;
+    const PowLadder Lr = make_ladder(r), Ls = make_ladder(s);
+    double u = 0.0, du = 0.0;
+    for (int t = 0; t < pc.nterms; t++) {
+        const GenTerm& tm = pc.t[t];
+        double E = 1.0;
+        if (tm.qn > 0) {
+            const int n = tm.qn;
+            double acc = up ? tm.qc[0] : tm.qc[n - 1];
+            for (int k = 1; k < n; k++) acc = fma(acc, x, tm.qc[up ? k : n - 1 - k]);
+            E = exp(acc * laurent_scale(up ? tm.qmin + n - 1 : tm.qmin, r, s, Lr, Ls));
+        }
+        const int pn = tm.pn, dn = tm.dn;
+        double ap = 0.0, ad = 0.0;
+        if (pn > 0) ap = up ? tm.pc[0] : tm.pc[pn - 1];
+        if (dn > 0) ad = up ? tm.dc[0] : tm.dc[dn - 1];
+        const int nmax = pn > dn ? pn : dn;
+        const int pb = up ? 0 : pn - 1, db = up ? 0 : dn - 1, sg = up ? 1 : -1;
+        int k = 1;
+        for (; k + 3 < nmax; k += 4) {
+            double cp[4], cd[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                cp[q] = (k + q < pn) ? tm.pc[pb + sg * (k + q)] : 0.0;
+                cd[q] = (k + q < dn) ? tm.dc[db + sg * (k + q)] : 0.0;
+            }
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                if (k + q < pn) ap = fma(ap, x, cp[q]);
+                if (k + q < dn) ad = fma(ad, x, cd[q]);
+            }
+        }
+        for (; k < nmax; k++) {
+            if (k < pn) ap = fma(ap, x, tm.pc[pb + sg * k]);
+            if (k < dn) ad = fma(ad, x, tm.dc[db + sg * k]);
+        }
+        if (pn > 0) u = fma(ap * laurent_scale(up ? tm.pmin + pn - 1 : tm.pmin, r, s, Lr, Ls), E, u);
+        if (dn > 0) du = fma(ad * laurent_scale(up ? tm.dmin + dn - 1 : tm.dmin, r, s, Lr, Ls), E, du);
+    }
+    U = u * gp->e_scale;
+    dU = du * (gp->e_scale * gp->len_scale);
+}
+
 // Bt_t (sigma/r)^lam_t at r = sigma / inv: binary powers for integer exponents (the pair-uniform common case, LJ and most
 // Mie fluids), else s^lam = exp(lam ln s) with one shared log
 template<int NT>

@@ -25,7 +25,7 @@ constexpr int Q_JKWB_L = 1000;
 template<int NT>
 __device__ __forceinline__ void qpot(const PairParams& pp, double x, double& U, double& dU) {
     if constexpr (NT == 1) {
-        gen_eval(pp.gen, x, 1, U, dU);
+        gen_eval_march(pp.gen, x, U, dU);
         const double ie = 1.0 / pp.eps;
         U *= ie; dU *= ie;
     } else {
@@ -215,9 +215,24 @@ __device__ double q_phase(const PairParams& pp, double kappa2, double s0, int l,
     return jk ? q_jkwb_phase<NT>(pp, kappa2, s0, l, E, st) : q_numerov_phase<NT>(pp, kappa2, l, E, st);
 }
 
+// A CTA's copy of the generic potential in shared memory (8.7 KB): the Numerov / JKWB marches read its coefficients at every step
 template<int NT>
-__global__ void __launch_bounds__(128) q_phase_kernel(PairParams pp, double kappa2, double jE, int jL, int n, const int* __restrict__ l, const double* __restrict__ E,
+__device__ __forceinline__ PairParams q_stage_potential(const PairParams& pp, double* s_gp) {
+    PairParams pq = pp;
+    if constexpr (NT == 1) {
+        const double* src = reinterpret_cast<const double*>(pp.gen);
+        for (int i = threadIdx.x; i < GP_DOUBLES; i += blockDim.x) s_gp[i] = src[i];
+        __syncthreads();
+        pq.gen = reinterpret_cast<const GenPot*>(s_gp);
+    }
+    return pq;
+}
+
+template<int NT>
+__global__ void __launch_bounds__(128) q_phase_kernel(PairParams pp_in, double kappa2, double jE, int jL, int n, const int* __restrict__ l, const double* __restrict__ E,
                                                       int which, double* __restrict__ out, int* __restrict__ status) {
+    __shared__ double s_gp[NT == 1 ? GP_DOUBLES : 1];
+    const PairParams pp = q_stage_potential<NT>(pp_in, s_gp);
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= n) return;
     int st = 0;
@@ -260,9 +275,11 @@ __device__ double q_xsec_term(int n, int l, const double* __restrict__ d) {
 // into the warp's cache; lanes 0 .. 2 nn - 1 each own one (n, parity) sum and advance it with the reference's stop rule as far as the cache allows.
 constexpr int Q_MAXN = 8;
 template<int NT>
-__global__ void __launch_bounds__(128) q_xsec_kernel(PairParams pp, double kappa2, double jE, int jL, double w_sym, double w_anti, int nE, const double* __restrict__ E_in,
+__global__ void __launch_bounds__(128) q_xsec_kernel(PairParams pp_in, double kappa2, double jE, int jL, double w_sym, double w_anti, int nE, const double* __restrict__ E_in,
                                                      int nn, const int* __restrict__ nlist, double* __restrict__ dcache, int Lcap,
                                                      double* __restrict__ out, int* __restrict__ status) {
+    __shared__ double s_gp[NT == 1 ? GP_DOUBLES : 1];
+    const PairParams pp = q_stage_potential<NT>(pp_in, s_gp);
     const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (wid >= nE) return;
     const unsigned full = 0xffffffffu;
@@ -358,8 +375,24 @@ static int q_cross_sections_dev(kg_model* m, int pair, double w_sym, double w_an
     CUDA_OK(kg_dmalloc(m, &dE, nE * sizeof(double))); CUDA_OK(kg_dmalloc(m, &dout, (size_t) nE * nn * sizeof(double)));
     CUDA_OK(kg_dmalloc(m, &dcache, (size_t) nE * Lcap * sizeof(double)));
     cudaStream_t s = m->stream;
+    // Longest first: a warp's serial work grows from ~1e3 to ~1e5 potential evaluations with the energy (Numerov: steps x chunks of 32 partial
+    // waves; JKWB: quadratures x chunks), and CTAs are dispatched in index order, so the energies are launched in descending estimated cost
+    // (the launch no longer ends on a few heavy warps that started last) and the results are put back in the caller's order.
+    std::vector<int> order(nE);
+    std::vector<double> cost(nE), E_sorted(nE);
+    for (int e = 0; e < nE; e++) {
+        const double E = std::max(E_red[e], 5e-4), ks = std::sqrt(kappa2 * E);
+        const double chunks = std::ceil((4.0 * ks + 8.0) / 32.0);
+        const double steps = (E > m->q_jkwb_E) ? 600.0 : std::max(2.0, std::pow(1e7 / E, 1.0 / 6.0)) * std::max(ks, 1.0) / 0.025;
+        cost[e] = steps * chunks;
+        order[e] = e;
+    }
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return cost[a] > cost[b]; });
+    for (int e = 0; e < nE; e++) E_sorted[e] = E_red[order[e]];
+    std::vector<double> q_sorted((size_t) nE * nn);
+    std::vector<int32_t> st_sorted(nE);
     CUDA_OK(cudaMemcpyAsync(dn, nlist, nn * sizeof(int), cudaMemcpyHostToDevice, s));
-    CUDA_OK(cudaMemcpyAsync(dE, E_red, nE * sizeof(double), cudaMemcpyHostToDevice, s));
+    CUDA_OK(cudaMemcpyAsync(dE, E_sorted.data(), nE * sizeof(double), cudaMemcpyHostToDevice, s));
     const int grid = (nE + 3) / 4;                       // 4 warps per CTA, one warp per energy
     switch (m->ntpad) {
         case 1: q_xsec_kernel<1><<<grid, 128, 0, s>>>(pp, kappa2, m->q_jkwb_E, m->q_jkwb_l, w_sym, w_anti, nE, dE, nn, dn, dcache, Lcap, dout, dst); break;
@@ -368,10 +401,14 @@ static int q_cross_sections_dev(kg_model* m, int pair, double w_sym, double w_an
         default: q_xsec_kernel<6><<<grid, 128, 0, s>>>(pp, kappa2, m->q_jkwb_E, m->q_jkwb_l, w_sym, w_anti, nE, dE, nn, dn, dcache, Lcap, dout, dst); break;
     }
     CUDA_OK(cudaGetLastError());
-    CUDA_OK(cudaMemcpyAsync(q, dout, (size_t) nE * nn * sizeof(double), cudaMemcpyDeviceToHost, s));
-    if (status) CUDA_OK(cudaMemcpyAsync(status, dst, nE * sizeof(int), cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaMemcpyAsync(q_sorted.data(), dout, (size_t) nE * nn * sizeof(double), cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaMemcpyAsync(st_sorted.data(), dst, nE * sizeof(int), cudaMemcpyDeviceToHost, s));
     CUDA_OK(cudaStreamSynchronize(s));
     m->dfree(dn); m->dfree(dst); m->dfree(dE); m->dfree(dout); m->dfree(dcache);
+    for (int e = 0; e < nE; e++) {
+        for (int k = 0; k < nn; k++) q[(size_t) order[e] * nn + k] = q_sorted[(size_t) e * nn + k];
+        if (status) status[order[e]] = st_sorted[e];
+    }
     return 0;
 }
 
@@ -429,15 +466,19 @@ extern "C" int kg_quantum_omega(kg_model* m, int pair, double w_sym, double w_an
     }
     if (status) for (int t = 0; t < nT; t++) status[t] = 0;
     const double tol = 1e-8;
-    constexpr int AHEAD = 3;       // blocks evaluated per round and integral: the pending one and two more on the assumption that the interval
-                                   // is not doubled (it is doubled a handful of times per integral; those speculative blocks are thrown away)
+    constexpr int AHEAD_MAX = 8;
+    int AHEAD = 3;                 // blocks evaluated per round and integral: the pending one and more on the assumption that the interval
+                                   // is not doubled (it is doubled a handful of times per integral; those speculative blocks are thrown away).
+                                   // A round cannot be shorter than the slowest single energy (25-40 ms: one warp's serial march), so fewer,
+                                   // larger rounds win until the discarded blocks outweigh them (KG_Q_AHEAD: tuning hook)
+    if (const char* ev = getenv("KG_Q_AHEAD")) AHEAD = std::min(AHEAD_MAX, std::max(1, atoi(ev)));
     auto node_x = [](double x0, double xe, int i) {                  // simpson(func, x0, xe, 10)'s node expressions
         const double dxb = (xe - x0) / 10.;
         return (i == 0) ? x0 : (i == 10) ? xe : (i == 9) ? xe - dxb : x0 + i * dxb;
     };
     for (int round = 0; round < 4000; round++) {
         std::vector<double> E; std::map<double, int> index;
-        std::vector<std::array<int, 11 * AHEAD>> node_of(seqs.size());
+        std::vector<std::array<int, 11 * AHEAD_MAX>> node_of(seqs.size());
         bool any = false;
         for (size_t q = 0; q < seqs.size(); q++) {
             const Seq& sq = seqs[q];
