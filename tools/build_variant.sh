@@ -7,5 +7,5 @@ cd "$(dirname "$0")/.."
 mkdir -p _variants
 nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC "$@" -c -o _variants/kg_omega_$name.o kineticgas_b200/csrc/kg_omega.cu
 nvcc -shared -gencode arch=compute_100a,code=sm_100a -o _variants/libkgcuda_$name.so _variants/kg_omega_$name.o \
-    kineticgas_b200/csrc/kg_transport.o kineticgas_b200/csrc/kg_genpot.o kineticgas_b200/csrc/kg_table.o
+    kineticgas_b200/csrc/kg_transport.o kineticgas_b200/csrc/kg_genpot.o kineticgas_b200/csrc/kg_table.o kineticgas_b200/csrc/kg_eos.o
 echo built _variants/libkgcuda_$name.so
