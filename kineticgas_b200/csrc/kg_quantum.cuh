@@ -274,11 +274,13 @@ __device__ double q_xsec_term(int n, int l, const double* __restrict__ d) {
 // Quantum::cross_section (cpp/Quantum.cpp:1200-1236): one warp per energy. The lanes compute the phase shifts of 32 consecutive l at a time
 // into the warp's cache; lanes 0 .. 2 nn - 1 each own one (n, parity) sum and advance it with the reference's stop rule as far as the cache allows.
 constexpr int Q_MAXN = 8;
-#ifndef KG_Q_MIN_CTAS
-#define KG_Q_MIN_CTAS 4            // 128 registers per thread; 6 (80 registers) and 8 (64) were measured too, see DESIGN 4c
+#ifdef KG_Q_MIN_CTAS               // build-time experiment: 6 (80 registers) and 8 (64) CTAs per SM were measured, see DESIGN 4c. The default
+#define KG_Q_BOUNDS __launch_bounds__(128, KG_Q_MIN_CTAS)          // leaves the allocation to ptxas (128 registers, 4 CTAs): stating
+#else                                                              // "4" explicitly gave a different, slower schedule (329 against 358 Omega/s)
+#define KG_Q_BOUNDS __launch_bounds__(128)
 #endif
 template<int NT>
-__global__ void __launch_bounds__(128, KG_Q_MIN_CTAS) q_xsec_kernel(PairParams pp_in, double kappa2, double jE, int jL, double w_sym, double w_anti, int nE, const double* __restrict__ E_in,
+__global__ void KG_Q_BOUNDS q_xsec_kernel(PairParams pp_in, double kappa2, double jE, int jL, double w_sym, double w_anti, int nE, const double* __restrict__ E_in,
                                                      int nn, const int* __restrict__ nlist, double* __restrict__ dcache, int Lcap,
                                                      double* __restrict__ out, int* __restrict__ status) {
     __shared__ double s_gp[NT == 1 ? GP_DOUBLES : 1];
